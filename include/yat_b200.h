@@ -1,0 +1,149 @@
+/*
+ * yat_b200 — C-ABI of the B200-native diffusion-training hot path.
+ *
+ * The reference (frutiemax92/YAT) is 100 % Python; its hot path is reached through a Python
+ * plugin surface, not an FFI.  This header is the boundary a binding for that surface sits
+ * on: plain pointers and sizes, no torch types.  Every entry point
+ *   - takes device pointers owned by the caller (inputs are never written, outputs are
+ *     caller-allocated), an explicit CUDA stream (a cudaStream_t passed as void*),
+ *   - never allocates, never synchronises, and is CUDA-graph capturable,
+ *   - returns 0 on success or a negative yat_status; yat_last_error() gives the text.
+ * There is no CPU fallback behind any of them.
+ *
+ * Reference interfaces replaced (paths relative to the upstream tree):
+ *   yat_noise_flowmatch   train_sana.py:183-207,217  train_sd35.py:180-185,192
+ *   yat_noise_ddpm        train_pixart_sigma.py:171-176,183
+ *   yat_loss_fused        train_sana.py:182,218  train_sd35.py:179,193
+ *                         train_pixart_sigma.py:170,182-184  README.md:81-82 (preservation)
+ *   yat_repa_cos          common/repa.py:137-154 (re-specified)
+ *   yat_linattn_fwd/bwd   diffusers SanaLinearAttnProcessor2_0, reached from
+ *                         utils/patch_sana_attention_layers.py:94
+ *   yat_pad_embeddings    train_sana.py:167-179  train_pixart_sigma.py:158-169
+ *   yat_bucket_assign     common/trainer.py:109-120  common/bucket_sampler.py:314-322
+ */
+#ifndef YAT_B200_H_
+#define YAT_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  YAT_OK = 0,
+  YAT_ERR_BAD_ARG = -1,      /* null pointer, non-positive size, misaligned pointer */
+  YAT_ERR_UNSUPPORTED = -2,  /* shape / dtype outside what the kernels implement     */
+  YAT_ERR_CUDA = -3          /* a CUDA call failed; see yat_last_error()             */
+} yat_status;
+
+/* element types of latent-shaped tensors */
+#define YAT_DTYPE_BF16 0
+#define YAT_DTYPE_F32 1
+
+/* loss target modes */
+#define YAT_TARGET_VELOCITY 0 /* target = noise - x0  (flow matching: SANA, SD3.5) */
+#define YAT_TARGET_EPS 1      /* target = noise       (DDPM eps-prediction: PixArt)  */
+
+/* loss output semantics */
+#define YAT_LOSS_F32 0  /* MSELoss(pred.float(), target.float())      train_sana.py:218 */
+#define YAT_LOSS_LOWP 1 /* MSELoss(pred.to(bf16), target) in bf16      train_sd35.py:193 */
+
+int yat_version(void);
+const char* yat_last_error(void);
+
+/* ---- (1) fused flow-matching noising ------------------------------------------------
+ * Per sample b: u -> idx=(long)(u*T) (clamped to T-1) -> t=timesteps_tab[idx] ->
+ * sigma=cast(sigmas_tab[idx]); x_t=(1-sigma)*x0+sigma*eps with the reference's per-op
+ * rounding in the latent dtype; target=eps-x0.
+ *   x0            [B, chw] latents (dtype), read-only
+ *   noise_in      [B, chw] or NULL.  NULL => eps generated in-kernel (Philox4x32-10 keyed
+ *                 by seed, counter (quad, sample, offset); see csrc/philox.cuh)
+ *   u_in          [B] fp32 in (0,1] or NULL.  NULL => u=sigmoid(N(0,1)) from the same stream
+ *   sigmas_tab, timesteps_tab   fp32 [T] device tables (built once by the host side)
+ *   x_t           [B, chw] out
+ *   target        [B, chw] out or NULL
+ *   noise_out     [B, chw] out or NULL (generated eps, if the caller wants it materialised)
+ *   idx_out int64 [B], t_out fp32 [B], sigma_out fp32 [B] (value after the dtype cast)
+ */
+int yat_noise_flowmatch(const void* x0, const void* noise_in, const float* u_in,
+                        const float* sigmas_tab, const float* timesteps_tab, int T,
+                        uint64_t seed, uint64_t offset, int B, int64_t chw, int dtype,
+                        void* x_t, void* target, void* noise_out,
+                        int64_t* idx_out, float* t_out, float* sigma_out, void* stream);
+
+/* ---- (1b) DDPM add_noise ------------------------------------------------------------
+ * t = T-1-idx (int64), x_t = sqrt(acp[t])*x0 + sqrt(1-acp[t])*eps with acp cast to the
+ * latent dtype first and per-op rounding (diffusers DDPMScheduler.add_noise).
+ */
+int yat_noise_ddpm(const void* x0, const void* noise_in, const float* u_in,
+                   const float* alphas_cumprod_tab, int T,
+                   uint64_t seed, uint64_t offset, int B, int64_t chw, int dtype,
+                   void* x_t, void* noise_out, int64_t* idx_out, int64_t* t_out, void* stream);
+
+/* ---- (2) fused denoising loss, forward + backward in one pass ----------------------------
+ *   pred        [B, pred_channels, hw]  model output (bf16); only channels [0, C) are used
+ *               (PixArt learned-sigma head: pred_channels = 2C), dpred of the rest is 0
+ *   x0          [B, C, hw] latents (bf16); may be NULL when target_mode == EPS
+ *   noise       [B, C, hw] eps (bf16) or NULL => regenerated from (seed, offset)
+ *   pred_frozen [B, pred_channels, hw] or NULL (use_preservation reconstruction term)
+ *   weights     fp32 [B] or NULL (=> all ones, the reference's plain mean)
+ *   rho         preservation_ratio;  gscale  upstream gradient of the scalar loss
+ *               (accelerate's 1/gradient_accumulation_steps)
+ *   loss_out    fp32 [3]: total, noise term, preservation term
+ *   dpred       [B, pred_channels, hw] bf16 out or NULL (forward only)
+ *   workspace   device scratch of yat_loss_workspace_bytes(), zero-initialised once by the
+ *               caller; the kernel leaves it zeroed for the next call
+ */
+int64_t yat_loss_workspace_bytes(void);
+int yat_loss_fused(const void* pred, const void* x0, const void* noise, const void* pred_frozen,
+                   const float* weights, float rho, float gscale, int target_mode, int loss_mode,
+                   uint64_t seed, uint64_t offset,
+                   int B, int C, int pred_channels, int64_t hw,
+                   float* loss_out, void* dpred, void* workspace, void* stream);
+
+/* ---- (2b) REPA cosine alignment, forward + backward ----------------------------------
+ *   z   [B, gh*gw, E] bf16 projected student tokens;  y [B, th*tw, E] teacher (y_dtype)
+ *   loss_out fp32 [1] = -(1/(B*th*tw)) sum cos(pool(z), y);  dz [B, gh*gw, E] bf16 or NULL,
+ *   already multiplied by gscale.  gbuf: fp32 scratch [B, th*tw, E] (pooled-gradient staging).
+ */
+int64_t yat_repa_workspace_bytes(int B, int th, int tw, int E);
+int yat_repa_cos(const void* z, const void* y, int y_dtype, int B, int gh, int gw, int th, int tw,
+                 int E, float gscale, float* loss_out, void* dz, void* workspace, void* stream);
+
+/* ---- (3) SANA ReLU linear attention ---------------------------------------------------
+ *   q,k,v,o,(do,dq,dk,dv)  [B, N, H*D] bf16 row-major (outputs of to_q/to_k/to_v), D == 32
+ *   O_n = relu(Q_n)(relu(K)^T V) / (relu(Q_n) . sum_m relu(K_m) + 1e-15)
+ *   tcgen05/TMEM kernels (csrc/linattn_sm100.cu); bwd recomputes K^T V, no saved state.
+ */
+int yat_linattn_fwd(const void* q, const void* k, const void* v, int B, int N, int H, int D,
+                    void* o, void* stream);
+int yat_linattn_bwd(const void* q, const void* k, const void* v, const void* dout,
+                    int B, int N, int H, int D, void* dq, void* dk, void* dv, void* stream);
+/* CUDA-core fp32 restatement of the same math; exists so the GPU tests can cross-check the
+ * tensor-core kernels at full size, where the CPU oracle is too slow.  Not a product path. */
+int yat_linattn_fwd_simt(const void* q, const void* k, const void* v, int B, int N, int H, int D,
+                         void* o, void* stream);
+int yat_linattn_bwd_simt(const void* q, const void* k, const void* v, const void* dout,
+                         int B, int N, int H, int D, void* dq, void* dk, void* dv, void* stream);
+
+/* ---- (next) ragged text-embedding pad + mask -------------------------------------------
+ *   packed [sum L_i, E] bf16, offsets int32 [B+1] -> padded [B, Lmax, E] bf16 (zero fill),
+ *   mask int64 [B, Lmax] (1 for real tokens).  train_sana.py:167-179.
+ */
+int yat_pad_embeddings(const void* packed, const int32_t* offsets, int B, int Lmax, int E,
+                       void* padded, int64_t* mask, void* stream);
+
+/* ---- bucket assignment (host function; float64 compare, first-minimum wins) ---------------
+ *   out[i] = argmin_j |keys[j] - ratios[i]| with strict '<' in table order, or -1 if nkeys==0.
+ */
+int yat_bucket_assign(const double* ratios, int n, const double* keys, int nkeys, int32_t* out);
+
+/* ---- test hook: raw Philox words for (seed, offset, sample, stream), quads [0, n_quads) ----- */
+int yat_philox_raw(uint64_t seed, uint64_t offset, uint32_t sample, uint32_t stream_id,
+                   int n_quads, uint32_t* out /* device [n_quads,4] */, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* YAT_B200_H_ */

@@ -1,0 +1,199 @@
+"""CPU: host-side mirror of the reference interfaces (schedulers, parameters, buckets, model
+structure, RNG state), plus the world_size-2 gloo path of the bucket agreement rule and DDP glue."""
+import os
+import sys
+
+import pytest
+import torch
+
+from oracle import schedule as oschedule
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_scheduler_mirrors_match_oracle_tables(kat):
+    from yat_b200.schedulers import DDPMScheduler, FlowMatchEulerDiscreteScheduler
+    for shift in (1.0, 3.0):
+        s = FlowMatchEulerDiscreteScheduler(shift=shift)
+        tt, ss = oschedule.flow_match_tables(1000, shift)
+        assert torch.equal(s.timesteps, tt) and torch.equal(s.sigmas, ss)
+        assert s.config.num_train_timesteps == 1000
+    d = DDPMScheduler()
+    dt, acp = oschedule.ddpm_tables()
+    assert torch.equal(d.alphas_cumprod, acp) and torch.equal(d.timesteps, dt)
+
+
+def test_training_parameters_reader(tmp_path):
+    from yat_b200.training_parameters_reader import TrainingParameters
+    cfg = tmp_path / "c.yaml"
+    cfg.write_text("batch_size: 16\nlearning_rate: 1e-5\nsteps: 10\nnum_steps_per_validation: 100\n"
+                   "validation_prompts: [a, b]\nbfloat16:\nuse_repa:\nrepa_lambda: 0.1\nexploration_steps: 2\n"
+                   "gradient_accumulation_steps: 4\nuse_preservation:\npreservation_ratio: 0.5\n"
+                   "train_unconditional_prob: 0.1\nwarmup_steps: 5\ntimesteps: [1, 2]\n")
+    p = TrainingParameters()
+    p.read_yaml(str(cfg))
+    assert p.batch_size == 16 and p.learning_rate == 1e-5 and p.bfloat16 and p.use_repa
+    assert p.repa_lambda == 0.1 and p.exploration_steps == 2 and p.gradient_accumulation_steps == 4
+    assert p.use_preservation and p.preservation_ratio == 0.5 and p.train_unconditional_prob == 0.1
+    assert p.timesteps == ["1", "2"] and p.warmup_steps == 5 and not p.use_ema and not p.use_adamw_8bit
+    q = TrainingParameters()
+    assert q.repa_lambda == 0.05 and q.use_preservation is None  # reference defaults
+
+
+def test_philox_generator_state_roundtrip():
+    from yat_b200.noise import PhiloxGenerator
+    g = PhiloxGenerator()
+    assert g.initial_seed() == 67280421310721
+    s0 = g.get_state()
+    a = g.advance()
+    b = g.advance()
+    assert a != b and a[1] + 1 == b[1]
+    g.set_state(s0)
+    assert g.advance() == a   # exploration (common/trainer.py:326-336) replays a draw
+    assert PhiloxGenerator(rank=1).seed != PhiloxGenerator(rank=0).seed
+
+
+def test_product_model_structure_matches_oracle_model():
+    """Same weights -> same output (CPU), with a test-local processor standing in for the CUDA
+    linear-attention kernel, and with the softmax swap of patch_sana_attention_layers."""
+    from oracle.linear_attention import sana_linear_attention_core
+    from oracle.sana_model import sana_forward
+    from yat_b200.sana_transformer import PatchedSanaTransformer2DModel, patch_sana_attention_layers, unfreeze_sana_blocks
+    from train_sana import SANA_CONFIGS
+
+    class OracleProc:
+        def __call__(self, attn, hs, encoder_hidden_states=None, attention_mask=None):
+            q, k, v = attn.to_q(hs), attn.to_k(hs), attn.to_v(hs)
+            return attn.to_out[1](attn.to_out[0](sana_linear_attention_core(q, k, v, attn.heads)))
+
+    torch.manual_seed(0)
+    m = PatchedSanaTransformer2DModel(**SANA_CONFIGS["sana_tiny"])
+    x = torch.randn(2, 32, 16, 16)
+    enc = torch.randn(2, 512, 64)
+    t = torch.tensor([326.0, 811.0])
+    mask = torch.zeros(2, 512, dtype=torch.long)
+    mask[0, :20] = 1
+    mask[1, :300] = 1
+    assert len(m.attn_processors) == 4
+    for b in m.transformer_blocks:
+        b.attn1.set_processor(OracleProc())
+    with torch.no_grad():
+        y = m(x, enc, t, encoder_attention_mask=mask).sample
+        y_ref = sana_forward(m.state_dict(), dict(vars(m.config)), x, enc, t, mask)
+    assert y.shape == (2, 32, 16, 16) and torch.allclose(y, y_ref, atol=1e-6)
+    patch_sana_attention_layers(m, [1])
+    assert m.config.modified_blocks == [1]
+    with torch.no_grad():
+        y2 = m(x, enc, t, encoder_attention_mask=mask).sample
+        y2_ref = sana_forward(m.state_dict(), dict(vars(m.config)), x, enc, t, mask)
+    assert torch.allclose(y2, y2_ref, atol=1e-6) and not torch.allclose(y, y2, atol=1e-4)
+    unfreeze_sana_blocks(m, [0])
+    assert all(p.requires_grad for p in m.transformer_blocks[0].parameters())
+    assert not any(p.requires_grad for p in m.transformer_blocks[1].parameters())
+    keys = m.state_dict().keys()
+    for k in ("patch_embed.proj.weight", "time_embed.emb.timestep_embedder.linear_1.weight", "time_embed.linear.bias",
+              "caption_projection.linear_2.weight", "caption_norm.weight", "transformer_blocks.0.attn1.to_q.weight",
+              "transformer_blocks.1.attn2.to_out.0.bias", "transformer_blocks.0.ff.conv_depth.weight",
+              "transformer_blocks.0.scale_shift_table", "scale_shift_table", "proj_out.weight"):
+        assert k in keys, k
+
+
+def test_sana_1600m_parameter_count():
+    from yat_b200.sana_transformer import PatchedSanaTransformer2DModel
+    with torch.device("meta"):
+        m = PatchedSanaTransformer2DModel()
+    n = sum(p.numel() for p in m.parameters())
+    assert 1.55e9 < n < 1.65e9, n
+
+
+def test_save_and_load_roundtrip(tmp_path):
+    from yat_b200.repa import RepaConfig, RepaModel
+    from yat_b200.sana_transformer import PatchedSanaTransformer2DModel
+    from train_sana import SANA_CONFIGS
+    m = PatchedSanaTransformer2DModel(**SANA_CONFIGS["sana_tiny"], modified_blocks=[0])
+    rm = RepaModel(m, RepaConfig(target_modules=["transformer_blocks.1"], hidden_shape=[128], target_shape=48))
+    w = rm.model.get_submodule("transformer_blocks.1").proj_mlp.fc1.weight.detach().clone()
+    rm.save_pretrained(str(tmp_path / "ck"))
+    assert sorted(os.listdir(tmp_path / "ck")) == ["config.json", "diffusion_pytorch_model.safetensors",
+                                                   "repa_config.json", "repa_model_weights.bin"]
+    assert torch.equal(rm.model.get_submodule("transformer_blocks.1").proj_mlp.fc1.weight, w)  # heads survive a save
+    m2 = PatchedSanaTransformer2DModel.from_pretrained(str(tmp_path / "ck"))
+    assert m2.config.modified_blocks == [0]
+    rm2 = RepaModel.from_pretrained(m2, str(tmp_path / "ck"))
+    assert torch.equal(rm2.model.get_submodule("transformer_blocks.1").proj_mlp.fc1.weight, w)
+    base, base2 = rm.get_base_model().state_dict(), rm2.get_base_model().state_dict()
+    assert base.keys() == base2.keys() and all(torch.equal(v, base2[k]) for k, v in base.items())
+
+
+def _worker(rank, world, port, q):
+    try:
+        _worker_body(rank, world, port, q)
+    except Exception as e:  # surface the failure instead of letting the parent time out
+        import traceback
+        q.put({"rank": rank, "error": traceback.format_exc() + str(e)})
+
+
+def _worker_body(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from yat_b200.accelerator import Accelerator
+    from yat_b200.bucket_sampler import BucketAccumulator
+    acc = Accelerator(gradient_accumulation_steps=2, backend="gloo")
+    out = {"rank": acc.process_index, "world": acc.num_processes}
+    # bucket agreement: rank 0 fills bucket 1.0 twice and 0.5 once; rank 1 fills 1.0 twice only
+    ba = BucketAccumulator(batch_size=2)
+    keys = [0.5, 1.0, 2.0]
+    ba.add(1.0, torch.zeros(4), torch.zeros(3, 8))
+    out["ready_1"] = ba.ready_keys(keys)
+    ba.add(1.0, torch.ones(4), torch.zeros(5, 8))
+    if rank == 0:
+        ba.add(0.5, torch.ones(4), torch.zeros(5, 8))
+        ba.add(0.5, torch.ones(4), torch.zeros(5, 8))
+    out["ready_2"] = ba.ready_keys(keys)
+    b = ba.pop_batch(1.0)
+    out["batch"] = (b.ratio, tuple(b.vae_features.shape), [e.shape[0] for e in b.embeddings])
+    out["ready_3"] = ba.ready_keys(keys)
+    # DDP glue: gradient averaging + accumulate/no_sync + gather/reduce
+    torch.manual_seed(0)
+    model = torch.nn.Linear(4, 1, bias=False)
+    model = acc.prepare(model)
+    x = torch.full((1, 4), float(rank + 1))
+    syncs = []
+    for _ in range(2):
+        with acc.accumulate(model):
+            acc.backward(model(x).sum())
+            syncs.append(acc.sync_gradients)
+    out["syncs"] = syncs
+    out["grad"] = acc.unwrap_model(model).weight.grad.flatten().tolist()
+    out["gather"] = acc.gather(torch.tensor(float(rank))).tolist()
+    out["reduce"] = acc.reduce(torch.tensor(float(rank)), "mean").item()
+    acc.wait_for_everyone()
+    q.put(out)
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(180)
+def test_world_size_2_gloo_bucket_rule_and_ddp():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in procs]
+    res = sorted([q.get(timeout=150) for _ in procs], key=lambda d: d["rank"])
+    [p.join(30) for p in procs]
+    for r in res:
+        assert "error" not in r, r.get("error")
+        assert r["world"] == 2
+        assert r["ready_1"] == []              # nobody has a full bucket yet
+        assert r["ready_2"] == [1.0]           # 0.5 is full on rank 0 only -> not ready anywhere
+        assert r["batch"][0] == 1.0 and r["batch"][1] == (2, 4) and r["batch"][2] == [3, 5]
+        assert r["ready_3"] == []
+        assert r["syncs"] == [False, True]
+        # two micro-steps of loss/2 each (rank0 x=1, rank1 x=2): the first accumulates locally under
+        # no_sync, the second all-reduces the *accumulated* gradient: mean(1.0, 2.0) on both ranks
+        assert r["grad"] == pytest.approx([1.5] * 4)
+        assert r["gather"] == [0.0, 1.0] and r["reduce"] == 0.5

@@ -1,0 +1,415 @@
+// SANA ReLU linear attention on the 5th-gen tensor cores (tcgen05 + TMEM + TMA), forward.
+//
+//   O_n = relu(Q_n) (relu(K)^T V) / (relu(Q_n) . sum_m relu(K_m) + 1e-15)          per (batch, head)
+//
+// replaces diffusers' SanaLinearAttnProcessor2_0 core (transposes, .float() copies, F.pad and two
+// fp32 SIMT batched matmuls; reached from utils/patch_sana_attention_layers.py:94).
+//
+// Layout: q,k,v,o are [B, N, H*32] bf16 row-major, head h = columns [32h, 32h+32).  A work item is
+// (batch b, group of 4 heads) = a 128-column stripe; it is streamed in 128-token tiles of
+// [2 halves][128 tokens][64 cols] (two SWIZZLE_128B TMA boxes, 32 KB) through one shared-memory ring:
+//   K0 V0 K1 V1 ... | Q0 Q1 ...         (3 * ceil(N/128) tiles per item; O tiles leave from the Q slot)
+// The grid is persistent (one CTA per SM, 1 item at a time, loads run ahead across items).
+//
+// Roles (320 threads): warp 0 = TMA producer, warp 1 = tcgen05 issuer, warps 2..9 = transform/epilogue.
+//   phase 1  transform: relu(K) in place (+ fp32 column sums -> Ks)     MMA1: D1[128x128] += relu(K)^T V
+//            (A and B both MN-major straight from the TMA tiles; the four 32x32 diagonal blocks of D1
+//             are the per-head K^T V, the off-diagonal blocks are discarded — the kernel is HBM-bound)
+//   build    D1 diagonal -> registers -> bf16 hi + bf16 lo split -> smem B operand (so the second
+//            contraction keeps ~fp32 accuracy: Q·hi + Q·lo)
+//   phase 2  transform: relu(Q) in place + den = relu(Q)·Ks (fp32, CUDA cores)
+//            MMA2 per head: D2[128 tokens x 32] = relu(Q_h) · KV_h   (K-major A, MN-major B)
+//            epilogue: TMEM -> registers, divide, bf16, swizzled smem (the Q slot), TMA store.
+// Rows beyond N and heads beyond H are zero-filled by TMA on load and clipped on store.
+#include "common.cuh"
+#include "sm100.cuh"
+
+namespace yat {
+namespace {
+using namespace sm100;
+
+constexpr int kD = 32;
+constexpr int kHeadsPerItem = 4;
+constexpr int kTile = 128;                       // tokens per tile
+constexpr int kHalfBytes = kTile * 128;          // [128 tokens][64 cols] bf16
+constexpr int kSlotBytes = 2 * kHalfBytes;       // 32 KB
+constexpr int kStages = 5;
+constexpr int kEpiWarps = 8;
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kThreads = 64 + kEpiThreads;
+constexpr int kTmemCols = 512;                   // D1 [0,128) + D2 double buffer [128,384)
+constexpr int kBmatBytes = 2048;                 // one 32x32 bf16 B operand
+
+struct FwdSmem {
+  uint8_t slots[kStages][kSlotBytes];                       // 1024-aligned
+  uint8_t bmat[kHeadsPerItem][2][kBmatBytes];               // [head][hi|lo], MN-major no-swizzle
+  float den[2][kTile][kHeadsPerItem];
+  float ks[kHeadsPerItem * kD];
+  float red[kEpiWarps][kHeadsPerItem * kD];
+  uint64_t full[kStages], ready[kStages], empty[kStages];
+  uint64_t d1_full, b_ready, d2_full[2], d2_empty[2];
+  uint32_t tmem_base;
+};
+constexpr int kFwdSmemBytes = (int)sizeof(FwdSmem) + 1024;
+
+constexpr uint32_t kIdesc1 = make_idesc_bf16(128, 128, 1, 1);  // relu(K)^T V : A, B MN-major
+constexpr uint32_t kIdesc2 = make_idesc_bf16(128, 32, 0, 1);   // relu(Q) KV  : A K-major, B MN-major
+
+__device__ __forceinline__ uint4 relu8(uint4 v) {
+  const __nv_bfloat162 z = __float2bfloat162_rn(0.f);
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __hmax2_nan(h[i], z);
+  return v;
+}
+__device__ __forceinline__ void unpack8f(const uint4& v, float f[8]) {
+  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+  f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                         const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_o,
+                         int B, int N, int groups) {
+  extern __shared__ uint8_t smem_raw[];
+  FwdSmem& S = *reinterpret_cast<FwdSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tiles = (N + kTile - 1) / kTile;
+  const int n_items = B * groups;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(smem_u32(&S.full[s]), 1);
+      mbar_init(smem_u32(&S.ready[s]), kEpiWarps);
+      mbar_init(smem_u32(&S.empty[s]), 1);
+    }
+    mbar_init(smem_u32(&S.d1_full), 1);
+    mbar_init(smem_u32(&S.b_ready), kEpiWarps);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(smem_u32(&S.d2_full[i]), 1);
+      mbar_init(smem_u32(&S.d2_empty[i]), kEpiWarps);
+    }
+    fence_barrier_init();
+    tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v); tma_prefetch_desc(&tm_o);
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(&S.tmem_base), kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = S.tmem_base;
+
+  if (warp == 0) {
+    // ======================= TMA producer =======================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int b = item / groups, c0 = (item % groups) * (kHeadsPerItem * kD);
+        for (int j = 0; j < 3 * n_tiles; ++j, ++it) {
+          const CUtensorMap* tm;
+          int tile;
+          if (j < 2 * n_tiles) { tm = (j & 1) ? &tm_v : &tm_k; tile = j >> 1; }
+          else                 { tm = &tm_q; tile = j - 2 * n_tiles; }
+          const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+          mbar_wait(smem_u32(&S.empty[s]), ph ^ 1);
+          const uint32_t full = smem_u32(&S.full[s]);
+          mbar_arrive_expect_tx(full, kSlotBytes);
+          const uint32_t dst = smem_u32(&S.slots[s][0]);
+          tma_load_3d(dst, tm, full, c0, tile * kTile, b);
+          tma_load_3d(dst + kHalfBytes, tm, full, c0 + 64, tile * kTile, b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ======================= tcgen05 issuer =======================
+    if (lane == 0) {
+      uint32_t it = 0, qt = 0, item_iter = 0;
+      uint32_t ready_ph = 0;  // per-slot parity of `ready` (only K and Q uses of a slot complete a phase)
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++item_iter) {
+        // ---- phase 1: D1 += relu(K)^T V over all token tiles
+        for (int t = 0; t < n_tiles; ++t, it += 2) {
+          const uint32_t sk = it % kStages;
+          const uint32_t sv = (it + 1) % kStages, pv = ((it + 1) / kStages) & 1;
+          mbar_wait(smem_u32(&S.ready[sk]), (ready_ph >> sk) & 1);
+          ready_ph ^= 1u << sk;
+          mbar_wait(smem_u32(&S.full[sv]), pv);  // V is consumed as loaded
+          tc_fence_after();
+          const uint32_t ka = smem_u32(&S.slots[sk][0]), va = smem_u32(&S.slots[sv][0]);
+#pragma unroll
+          for (int ks = 0; ks < kTile / 16; ++ks) {
+            // MN-major SW128: LBO = stride between the two 64-column halves, SBO = 8-token group (1 KB)
+            const uint64_t da = make_smem_desc(ka + ks * 2048, kHalfBytes, 1024, kLayoutSw128);
+            const uint64_t db = make_smem_desc(va + ks * 2048, kHalfBytes, 1024, kLayoutSw128);
+            umma_bf16(tmem, da, db, kIdesc1, (t | ks) != 0);
+          }
+          tc_commit(smem_u32(&S.empty[sk]));
+          tc_commit(smem_u32(&S.empty[sv]));
+        }
+        tc_commit(smem_u32(&S.d1_full));
+        mbar_wait(smem_u32(&S.b_ready), item_iter & 1);
+        tc_fence_after();
+        // ---- phase 2: D2[buf] = relu(Q_h) (KV_h hi + KV_h lo), per head
+        for (int t = 0; t < n_tiles; ++t, ++it, ++qt) {
+          const uint32_t sq = it % kStages;
+          const uint32_t buf = qt & 1, pb = (qt >> 1) & 1;
+          mbar_wait(smem_u32(&S.ready[sq]), (ready_ph >> sq) & 1);
+          ready_ph ^= 1u << sq;
+          mbar_wait(smem_u32(&S.d2_empty[buf]), pb ^ 1);
+          tc_fence_after();
+          const uint32_t qa = smem_u32(&S.slots[sq][0]);
+#pragma unroll
+          for (int h = 0; h < kHeadsPerItem; ++h) {
+            const uint32_t d2 = tmem + 128 + buf * 128 + h * kD;
+            const uint32_t qh = qa + (h >> 1) * kHalfBytes + (h & 1) * 64;  // 32 columns = 64 B inside the 128 B row
+#pragma unroll
+            for (int hl = 0; hl < 2; ++hl) {
+              const uint32_t ba = smem_u32(&S.bmat[h][hl][0]);
+#pragma unroll
+              for (int ks = 0; ks < 2; ++ks) {
+                // A: K-major SW128, 8-row groups 1 KB apart; K step of 16 columns = 32 B
+                const uint64_t da = make_smem_desc(qh + ks * 32, 16, 1024, kLayoutSw128);
+                // B: MN-major no-swizzle, core matrix = 8 k-rows x 16 B; k-group stride (LBO) 128 B,
+                //    mn-group stride (SBO) 512 B; K step of 16 = 2 k-groups = 256 B
+                const uint64_t db = make_smem_desc(ba + ks * 256, 128, 512, kLayoutNone);
+                umma_bf16(d2, da, db, kIdesc2, (hl | ks) != 0);
+              }
+            }
+          }
+          tc_commit(smem_u32(&S.d2_full[buf]));
+        }
+      }
+    }
+  } else {
+    // ======================= transform + epilogue warps =======================
+    const int te = threadIdx.x - 64;          // 0..255
+    const int we = te >> 5;                   // 0..7
+    const int cc = te & 15;                   // logical 16-byte chunk column of the 256-byte item row
+    const int rbase = te >> 4;                // 0..15; rows rbase + 16 i
+    const int half = cc >> 3, chunk = cc & 7;
+    const int quad = warp & 3;                // TMEM lane quadrant this warp may access
+    const int colhalf = we >> 2;              // which 64-column half of the item this warp finishes
+    const int row = quad * 32 + lane;         // token row in the tile (TMEM lane)
+    uint32_t it = 0, qt = 0, item_iter = 0;
+    int pending_slot = -1;                    // O tile whose TMA store may still be reading smem (te == 0)
+
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++item_iter) {
+      const int b = item / groups, c0 = (item % groups) * (kHeadsPerItem * kD);
+      // ---- phase 1: relu(K) in place, column sums
+      float csum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      for (int t = 0; t < n_tiles; ++t, it += 2) {
+        const uint32_t sk = it % kStages, pk = (it / kStages) & 1;
+        mbar_wait(smem_u32(&S.full[sk]), pk);
+        uint8_t* base = &S.slots[sk][half * kHalfBytes];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int r = rbase + 16 * i;
+          uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
+          const uint4 v = relu8(*p);
+          *p = v;
+          float f[8];
+          unpack8f(v, f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) csum[j] += f[j];
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&S.ready[sk]));  // (V needs no transform: the issuer waits on `full`)
+      }
+      // Ks[col] = sum over threads sharing the chunk column
+#pragma unroll
+      for (int j = 0; j < 8; ++j) csum[j] += __shfl_xor_sync(0xffffffffu, csum[j], 16);
+      if (lane < 16) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) S.red[we][cc * 8 + j] = csum[j];
+      }
+      named_bar_sync(1, kEpiThreads);
+      if (te < kHeadsPerItem * kD) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < kEpiWarps; ++w) s += S.red[w][te];
+        S.ks[te] = s;
+      }
+      // ---- build the B operands of phase 2 from the diagonal blocks of D1
+      mbar_wait(smem_u32(&S.d1_full), item_iter & 1);
+      tc_fence_after();
+      if (we < 4) {
+        uint32_t r[32];
+        tmem_ld32(tmem + ((uint32_t)(quad * 32) << 16) + quad * kD, r);  // KV_head[dk = lane][dv = 0..31]
+        tmem_ld_wait();
+        uint8_t* bh = &S.bmat[quad][0][0];
+        uint8_t* bl = &S.bmat[quad][1][0];
+        const int off = (lane >> 3) * 128 + (lane & 7) * 16;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint32_t hi[4], lo[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float a0 = __uint_as_float(r[g * 8 + 2 * j]), a1 = __uint_as_float(r[g * 8 + 2 * j + 1]);
+            hi[j] = pack_bf16(a0, a1);
+            lo[j] = pack_bf16(a0 - bf16_lo(hi[j]), a1 - bf16_hi(hi[j]));
+          }
+          *reinterpret_cast<uint4*>(bh + g * 512 + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+          *reinterpret_cast<uint4*>(bl + g * 512 + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        }
+        fence_proxy_async();
+      }
+      tc_fence_before();
+      named_bar_sync(1, kEpiThreads);  // ks visible, D1 drained, bmat written
+      if (lane == 0) mbar_arrive(smem_u32(&S.b_ready));
+      float ksr[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ksr[j] = S.ks[cc * 8 + j];
+
+      // ---- phase 2
+      for (int t = 0; t < n_tiles; ++t, ++it, ++qt) {
+        const uint32_t sq = it % kStages, pq = (it / kStages) & 1;
+        const uint32_t buf = qt & 1, pb = (qt >> 1) & 1;
+        mbar_wait(smem_u32(&S.full[sq]), pq);
+        uint8_t* base = &S.slots[sq][half * kHalfBytes];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int r = rbase + 16 * i;
+          uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
+          const uint4 v = relu8(*p);
+          *p = v;
+          float f[8], d = 0.f;
+          unpack8f(v, f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) d = fmaf(f[j], ksr[j], d);
+          d += __shfl_xor_sync(0xffffffffu, d, 1);
+          d += __shfl_xor_sync(0xffffffffu, d, 2);
+          if ((cc & 3) == 0) S.den[qt & 1][r][cc >> 2] = d;
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&S.ready[sq]));
+        named_bar_sync(1, kEpiThreads);  // den visible to the epilogue mapping
+
+        mbar_wait(smem_u32(&S.d2_full[buf]), pb);
+        tc_fence_after();
+        uint32_t acc[2][32];
+        const uint32_t taddr = tmem + ((uint32_t)(quad * 32) << 16) + 128 + buf * 128 + colhalf * 64;
+        tmem_ld32(taddr, acc[0]);
+        tmem_ld32(taddr + 32, acc[1]);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&S.d2_empty[buf]));
+
+        uint8_t* orow = &S.slots[sq][colhalf * kHalfBytes + row * 128];
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const float rden = __frcp_rn(S.den[qt & 1][row][colhalf * 2 + hh] + 1e-15f);
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            uint32_t w[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              w[j] = pack_bf16(__uint_as_float(acc[hh][g * 8 + 2 * j]) * rden,
+                               __uint_as_float(acc[hh][g * 8 + 2 * j + 1]) * rden);
+            const int c = hh * 4 + g;
+            *reinterpret_cast<uint4*>(orow + ((c ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+          }
+        }
+        fence_proxy_async();
+        named_bar_sync(1, kEpiThreads);
+        if (te == 0) {
+          const uint32_t src = smem_u32(&S.slots[sq][0]);
+          tma_store_3d(&tm_o, src, c0, t * kTile, b);
+          tma_store_3d(&tm_o, src + kHalfBytes, c0 + 64, t * kTile, b);
+          tma_store_commit();
+          if (pending_slot >= 0) {  // the previous tile's store has finished reading its slot
+            tma_store_wait_read<1>();
+            mbar_arrive(smem_u32(&S.empty[pending_slot]));
+          }
+          pending_slot = (int)sq;
+          if (t == n_tiles - 1) {   // item boundary: the next Q tile is 2*n_tiles loads away, release now
+            tma_store_wait_read<0>();
+            mbar_arrive(smem_u32(&S.empty[pending_slot]));
+            pending_slot = -1;
+          }
+        }
+      }
+    }
+    if (te == 0) tma_store_wait_all<0>();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, kTmemCols);
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+  static PFN_encodeTiled fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = (PFN_encodeTiled)p;
+  }
+  return fn;
+}
+
+int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t N, uint64_t B, uint32_t box_c,
+                      uint32_t box_n) {
+  PFN_encodeTiled enc = get_encode_fn();
+  YAT_REQUIRE(enc != nullptr, YAT_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  const cuuint64_t dims[3] = {C, N, B};
+  const cuuint64_t strides[2] = {C * 2, N * C * 2};
+  const cuuint32_t box[3] = {box_c, box_n, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  const CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  YAT_REQUIRE(r == CUDA_SUCCESS, YAT_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return YAT_OK;
+}
+
+}  // namespace yat
+
+extern "C" int yat_linattn_fwd(const void* q, const void* k, const void* v, int B, int N, int H, int D, void* o,
+                               void* stream) {
+  using namespace yat;
+  YAT_REQUIRE(q && k && v && o, YAT_ERR_BAD_ARG, "yat_linattn_fwd: null pointer argument");
+  YAT_REQUIRE(B > 0 && N > 0 && H > 0, YAT_ERR_BAD_ARG, "yat_linattn_fwd: non-positive dimension");
+  YAT_REQUIRE(D == kD, YAT_ERR_UNSUPPORTED, "yat_linattn_fwd: head_dim %d not supported (SANA uses 32)", D);
+  YAT_REQUIRE((((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o) & 15u) == 0, YAT_ERR_BAD_ARG,
+              "yat_linattn_fwd: tensors must be 16-byte aligned");
+  CUtensorMap tq, tk, tv, to;
+  const uint64_t C = (uint64_t)H * D;
+  int rc;
+  if ((rc = make_tmap_3d_bf16(&tq, q, C, N, B, 64, kTile)) != YAT_OK) return rc;
+  if ((rc = make_tmap_3d_bf16(&tk, k, C, N, B, 64, kTile)) != YAT_OK) return rc;
+  if ((rc = make_tmap_3d_bf16(&tv, v, C, N, B, 64, kTile)) != YAT_OK) return rc;
+  if ((rc = make_tmap_3d_bf16(&to, o, C, N, B, 64, kTile)) != YAT_OK) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    const cudaError_t e =
+        cudaFuncSetAttribute(linattn_fwd_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes);
+    YAT_REQUIRE(e == cudaSuccess, YAT_ERR_CUDA, "yat_linattn_fwd: cannot reserve %d B of shared memory (%s)",
+                kFwdSmemBytes, cudaGetErrorString(e));
+    attr_set = true;
+  }
+  const int groups = (H + kHeadsPerItem - 1) / kHeadsPerItem;
+  const int items = B * groups;
+  const int grid = items < kNumSMs ? items : kNumSMs;
+  linattn_fwd_sm100_kernel<<<grid, kThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(tq, tk, tv, to, B, N, groups);
+  return check_launch("linattn_fwd_sm100");
+}
+
+extern "C" int yat_linattn_bwd(const void* q, const void* k, const void* v, const void* dout, int B, int N, int H,
+                               int D, void* dq, void* dk, void* dv, void* stream) {
+  // tensor-core backward lands next; until then the call is refused rather than silently rerouted
+  yat::set_error("yat_linattn_bwd: tcgen05 backward not built yet");
+  return YAT_ERR_UNSUPPORTED;
+}

@@ -1,0 +1,47 @@
+"""Ragged text embeddings -> padded batch + mask on the device (host side of ``yat_pad_embeddings``).
+
+Replaces the Python loop of train_sana.py:167-179 / train_pixart_sigma.py:158-169: the real tokens
+are packed into one pinned staging buffer, copied once (no padding zeros cross PCIe), and the
+kernel writes ``[B, Lmax, E]`` + the int64 mask.
+"""
+import torch
+
+from . import _lib
+
+_staging = {}
+
+
+def _pinned(nbytes):
+    buf = _staging.get("buf")
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8).pin_memory()
+        _staging["buf"] = buf
+    return buf
+
+
+def pad_embeddings(embeddings, max_len, device, dtype=torch.bfloat16):
+    """embeddings: list of [L_i, E] tensors (host or device). Returns (padded [B,Lmax,E], mask int64 [B,Lmax])."""
+    if dtype != torch.bfloat16:
+        raise ValueError("pad_embeddings produces bf16 (the training dtype of the reference hooks)")
+    B = len(embeddings)
+    E = embeddings[0].shape[1]
+    lens = [min(int(e.shape[0]), max_len) for e in embeddings]
+    total = sum(lens)
+    offsets = torch.zeros(B + 1, dtype=torch.int32)
+    offsets[1:] = torch.tensor(lens, dtype=torch.int32).cumsum(0)
+    if embeddings[0].is_cuda:
+        packed = torch.cat([e[:l].to(dtype) for e, l in zip(embeddings, lens)], dim=0).contiguous()
+    else:
+        stage = _pinned(total * E * 2).narrow(0, 0, total * E * 2).view(torch.bfloat16).view(total, E)
+        o = 0
+        for e, l in zip(embeddings, lens):
+            stage[o:o + l].copy_(e[:l])
+            o += l
+        packed = stage.to(device, non_blocking=True)
+    offsets_d = offsets.to(device, non_blocking=True)
+    padded = torch.empty((B, max_len, E), dtype=dtype, device=device)
+    mask = torch.empty((B, max_len), dtype=torch.int64, device=device)
+    rc = _lib.lib().yat_pad_embeddings(_lib.ptr(packed), _lib.ptr(offsets_d), B, max_len, E, _lib.ptr(padded),
+                                       _lib.ptr(mask), _lib.current_stream())
+    _lib.check(rc, "yat_pad_embeddings")
+    return padded, mask

@@ -1,0 +1,60 @@
+"""SANA ReLU linear attention op (host side of ``yat_linattn_fwd`` / ``yat_linattn_bwd``).
+
+``sana_linear_attention(q, k, v, heads)`` takes the outputs of ``to_q/to_k/to_v``
+([B, N, heads*32] bf16) and returns the attention output in the same layout — the part of
+diffusers' ``SanaLinearAttnProcessor2_0`` between the projections and ``to_out``.  Forward and
+backward are tcgen05/TMEM kernels; the backward recomputes K^T V (nothing but q, k, v is saved,
+which is also what gradient checkpointing — train_sana.py:63 — wants).
+"""
+import torch
+
+from . import _lib
+
+
+def _launch_fwd(q, k, v, heads, impl):
+    B, N, C = q.shape
+    o = torch.empty_like(q)
+    fn = _lib.lib().yat_linattn_fwd if impl == "sm100" else _lib.lib().yat_linattn_fwd_simt
+    rc = fn(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), B, N, heads, C // heads, _lib.ptr(o), _lib.current_stream())
+    _lib.check(rc, "yat_linattn_fwd")
+    return o
+
+
+def _launch_bwd(q, k, v, do, heads, impl):
+    B, N, C = q.shape
+    dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+    fn = _lib.lib().yat_linattn_bwd if impl == "sm100" else _lib.lib().yat_linattn_bwd_simt
+    rc = fn(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(do), B, N, heads, C // heads,
+            _lib.ptr(dq), _lib.ptr(dk), _lib.ptr(dv), _lib.current_stream())
+    _lib.check(rc, "yat_linattn_bwd")
+    return dq, dk, dv
+
+
+class _SanaLinearAttention(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, k, v, heads, impl):
+        for t in (q, k, v):
+            if not t.is_cuda:
+                raise ValueError("yat_b200 ops run on CUDA tensors only (no CPU fallback)")
+            if t.dtype != torch.bfloat16:
+                raise ValueError("linear attention expects bf16 q, k, v")
+        if q.shape != k.shape or q.shape != v.shape or q.dim() != 3 or q.shape[-1] % heads:
+            raise ValueError(f"bad q/k/v shapes {tuple(q.shape)} {tuple(k.shape)} {tuple(v.shape)} for {heads} heads")
+        q, k, v = q.contiguous(), k.contiguous(), v.contiguous()
+        ctx.save_for_backward(q, k, v)
+        ctx.heads, ctx.impl = heads, impl
+        return _launch_fwd(q, k, v, heads, impl)
+
+    @staticmethod
+    def backward(ctx, do):
+        q, k, v = ctx.saved_tensors
+        dq, dk, dv = _launch_bwd(q, k, v, do.contiguous(), ctx.heads, ctx.impl)
+        return dq, dk, dv, None, None
+
+
+def sana_linear_attention(q, k, v, heads, impl="sm100"):
+    """impl: "sm100" = tensor-core kernels (the product path); "simt" = the CUDA-core fp32
+    restatement kept for GPU-side cross-checks in tests."""
+    if impl not in ("sm100", "simt"):
+        raise ValueError(f"unknown impl {impl!r}")
+    return _SanaLinearAttention.apply(q, k, v, heads, impl)
