@@ -72,10 +72,12 @@ def glumbconv(x, sd, pre):
     return F.conv2d(x, sd[pre + "conv_point.weight"], None)
 
 
-def sana_forward(sd, cfg, hidden_states, encoder_hidden_states, timestep, encoder_attention_mask=None):
+def sana_forward(sd, cfg, hidden_states, encoder_hidden_states, timestep, encoder_attention_mask=None,
+                 gradient_checkpointing=False):
     """cfg: dict with num_attention_heads, attention_head_dim, num_layers, num_cross_attention_heads,
     patch_size, norm_eps, modified_blocks (softmax self-attention on those blocks,
-    utils/patch_sana_attention_layers.py:125-137).  Returns the ``sample`` tensor."""
+    utils/patch_sana_attention_layers.py:125-137).  ``gradient_checkpointing`` recomputes each block
+    in backward like the reference does (train_sana.py:63, patched:301-312).  Returns ``sample``."""
     heads, n_layers = cfg["num_attention_heads"], cfg["num_layers"]
     xheads, p = cfg["num_cross_attention_heads"], cfg.get("patch_size", 1)
     eps = cfg.get("norm_eps", 1e-6)
@@ -105,7 +107,7 @@ def sana_forward(sd, cfg, hidden_states, encoder_hidden_states, timestep, encode
     enc = rms_norm(enc, sd["caption_norm.weight"], 1e-5)
 
     C = x.shape[-1]
-    for i in range(n_layers):
+    def block(i, x, temb, enc):
         pre = f"transformer_blocks.{i}."
         mod = (sd[pre + "scale_shift_table"][None] + temb.reshape(B, 6, -1)).chunk(6, dim=1)
         shift_msa, scale_msa, gate_msa, shift_mlp, scale_mlp, gate_mlp = mod
@@ -123,7 +125,14 @@ def sana_forward(sd, cfg, hidden_states, encoder_hidden_states, timestep, encode
         n = n.unflatten(1, (ph, pw)).permute(0, 3, 1, 2)
         f = glumbconv(n, sd, pre + "ff.")
         f = f.flatten(2, 3).permute(0, 2, 1)
-        x = x + gate_mlp * f
+        return x + gate_mlp * f
+
+    for i in range(n_layers):
+        if gradient_checkpointing and torch.is_grad_enabled():
+            from torch.utils.checkpoint import checkpoint
+            x = checkpoint(block, i, x, temb, enc, use_reentrant=False)
+        else:
+            x = block(i, x, temb, enc)
 
     shift, scale = (sd["scale_shift_table"][None] + embedded_timestep[:, None]).chunk(2, dim=1)
     x = F.layer_norm(x, (C,), None, None, 1e-6) * (1 + scale) + shift

@@ -41,6 +41,33 @@ SIGNATURES = {
 
 _lib = None
 
+# C-ABI calls that launch at least one of our kernels, counted per entry point (bench.py reports the
+# sum over its timed region as `gpu_launches`).
+LAUNCHING = ("yat_noise_flowmatch", "yat_noise_ddpm", "yat_loss_fused", "yat_repa_cos", "yat_linattn_fwd",
+             "yat_linattn_bwd", "yat_linattn_fwd_simt", "yat_linattn_bwd_simt", "yat_pad_embeddings",
+             "yat_philox_raw")
+launch_counts = {name: 0 for name in LAUNCHING}
+
+
+def total_launches():
+    return sum(launch_counts.values())
+
+
+class _Counted:
+    """ctypes function + a call counter (a Python int increment; no device work)."""
+    __slots__ = ("fn", "name")
+
+    def __init__(self, fn, name):
+        self.fn, self.name = fn, name
+
+    def __call__(self, *args):
+        launch_counts[self.name] += 1
+        return self.fn(*args)
+
+
+class _Handle:
+    pass
+
 
 class YatError(RuntimeError):
     pass
@@ -54,11 +81,14 @@ def lib():
             raise YatError(
                 f"{LIB_PATH} is missing: build it with `python -m yat_b200.build` "
                 "(yat_b200 has no CPU or eager fallback)")
-        handle = ctypes.CDLL(LIB_PATH)
+        cdll = ctypes.CDLL(LIB_PATH)
+        handle = _Handle()
+        handle.cdll = cdll
         for name, (res, args) in SIGNATURES.items():
-            fn = getattr(handle, name)  # AttributeError if a declared symbol is not exported
+            fn = getattr(cdll, name)  # AttributeError if a declared symbol is not exported
             fn.restype = res
             fn.argtypes = args
+            setattr(handle, name, _Counted(fn, name) if name in LAUNCHING else fn)
         _lib = handle
     return _lib
 
@@ -81,3 +111,31 @@ def ptr(t):
 def current_stream():
     import torch
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+# Optional in-situ kernel timing: bench.py sets ``timing_sink`` to a list and every op wrapper then
+# brackets its C-ABI call with CUDA events recorded on the launching (current) stream.
+timing_sink = None
+
+
+class timed:
+    __slots__ = ("name", "e0")
+
+    def __init__(self, name):
+        self.name = name
+        self.e0 = None
+
+    def __enter__(self):
+        if timing_sink is not None:
+            import torch
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *exc):
+        if self.e0 is not None:
+            import torch
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            timing_sink.append((self.name, self.e0, e1))
+        return False

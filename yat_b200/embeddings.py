@@ -41,7 +41,8 @@ def pad_embeddings(embeddings, max_len, device, dtype=torch.bfloat16):
     offsets_d = offsets.to(device, non_blocking=True)
     padded = torch.empty((B, max_len, E), dtype=dtype, device=device)
     mask = torch.empty((B, max_len), dtype=torch.int64, device=device)
-    rc = _lib.lib().yat_pad_embeddings(_lib.ptr(packed), _lib.ptr(offsets_d), B, max_len, E, _lib.ptr(padded),
-                                       _lib.ptr(mask), _lib.current_stream())
+    with _lib.timed("pad_embeddings"):
+        rc = _lib.lib().yat_pad_embeddings(_lib.ptr(packed), _lib.ptr(offsets_d), B, max_len, E, _lib.ptr(padded),
+                                           _lib.ptr(mask), _lib.current_stream())
     _lib.check(rc, "yat_pad_embeddings")
     return padded, mask

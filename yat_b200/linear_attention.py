@@ -15,7 +15,8 @@ def _launch_fwd(q, k, v, heads, impl):
     B, N, C = q.shape
     o = torch.empty_like(q)
     fn = _lib.lib().yat_linattn_fwd if impl == "sm100" else _lib.lib().yat_linattn_fwd_simt
-    rc = fn(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), B, N, heads, C // heads, _lib.ptr(o), _lib.current_stream())
+    with _lib.timed("linattn_fwd_" + impl):
+        rc = fn(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), B, N, heads, C // heads, _lib.ptr(o), _lib.current_stream())
     _lib.check(rc, "yat_linattn_fwd")
     return o
 
@@ -24,8 +25,9 @@ def _launch_bwd(q, k, v, do, heads, impl):
     B, N, C = q.shape
     dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
     fn = _lib.lib().yat_linattn_bwd if impl == "sm100" else _lib.lib().yat_linattn_bwd_simt
-    rc = fn(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(do), B, N, heads, C // heads,
-            _lib.ptr(dq), _lib.ptr(dk), _lib.ptr(dv), _lib.current_stream())
+    with _lib.timed("linattn_bwd_" + impl):
+        rc = fn(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(do), B, N, heads, C // heads,
+                _lib.ptr(dq), _lib.ptr(dk), _lib.ptr(dv), _lib.current_stream())
     _lib.check(rc, "yat_linattn_bwd")
     return dq, dk, dv
 

@@ -43,10 +43,11 @@ class _FusedDenoiseLoss(torch.autograd.Function):
         need_grad = pred.requires_grad
         dpred = torch.empty_like(pred_c) if need_grad else None
         out = torch.empty(3, dtype=torch.float32, device=pred.device)
-        rc = _lib.lib().yat_loss_fused(
-            _lib.ptr(pred_c), _lib.ptr(x0_c), _lib.ptr(noise_c), _lib.ptr(pf_c), _lib.ptr(w_c), float(rho),
-            float(gscale), int(target_mode), 1 if lowp else 0, seed, offset, B, C, pred.shape[1], hw,
-            _lib.ptr(out), _lib.ptr(dpred), _lib.ptr(_workspace(pred.device)), _lib.current_stream())
+        with _lib.timed("loss_fused"):
+            rc = _lib.lib().yat_loss_fused(
+                _lib.ptr(pred_c), _lib.ptr(x0_c), _lib.ptr(noise_c), _lib.ptr(pf_c), _lib.ptr(w_c), float(rho),
+                float(gscale), int(target_mode), 1 if lowp else 0, seed, offset, B, C, pred.shape[1], hw,
+                _lib.ptr(out), _lib.ptr(dpred), _lib.ptr(_workspace(pred.device)), _lib.current_stream())
         _lib.check(rc, "yat_loss_fused")
         ctx.save_for_backward(dpred)
         ctx.gscale = float(gscale)

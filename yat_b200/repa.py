@@ -67,8 +67,9 @@ class _RepaCos(torch.autograd.Function):
         ws = torch.zeros(lib.yat_repa_workspace_bytes(B, th, tw, E), dtype=torch.uint8, device=z.device)
         loss = torch.empty(1, dtype=torch.float32, device=z.device)
         dz = torch.empty_like(z_c) if z.requires_grad else None
-        rc = lib.yat_repa_cos(_lib.ptr(z_c), _lib.ptr(y_c), 0 if y.dtype == torch.bfloat16 else 1, B, gh, gw, th, tw,
-                              E, 1.0, _lib.ptr(loss), _lib.ptr(dz), _lib.ptr(ws), _lib.current_stream())
+        with _lib.timed("repa_cos"):
+            rc = lib.yat_repa_cos(_lib.ptr(z_c), _lib.ptr(y_c), 0 if y.dtype == torch.bfloat16 else 1, B, gh, gw, th, tw,
+                                  E, 1.0, _lib.ptr(loss), _lib.ptr(dz), _lib.ptr(ws), _lib.current_stream())
         _lib.check(rc, "yat_repa_cos")
         ctx.save_for_backward(dz)
         return loss[0]
