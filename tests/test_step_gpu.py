@@ -107,6 +107,8 @@ def test_k1_train_step_loss_and_grads_vs_oracle(cuda):
         gref = sd[name].grad
         if gref is None or gref.norm() == 0:
             continue
+        if name.endswith("to_k.bias"):
+            continue    # softmax is invariant to a key bias: the exact gradient is 0, both sides hold only rounding noise
         rel = ((p.grad.float().cpu() - gref).norm() / gref.norm()).item()
         assert rel < 6e-2, (name, rel)     # bf16 weights + bf16 activations through 2 blocks
         checked += 1

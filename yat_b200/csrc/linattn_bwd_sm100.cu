@@ -1,0 +1,661 @@
+// SANA ReLU linear attention, backward, on the 5th-gen tensor cores (tcgen05 + TMEM + TMA).
+//
+// Per (batch, head), Q = relu(q), K = relu(k), D = 32 (derivation: SURVEY.md §8 A10, oracle/linear_attention.py):
+//   KV = K^T V   Ks = sum_n K_n   den_n = Q_n.Ks + 1e-15   num_n = Q_n KV   r_n = 1/den_n
+//   dDen_n = -(dO_n . num_n) r_n^2
+//   dQ_n  = (r_n (dO_n KV^T) + dDen_n Ks) * [q_n > 0]
+//   dKV   = sum_n (r_n Q_n)^T dO_n          dKs = sum_n Q_n dDen_n
+//   dK_n  = (V_n dKV^T + dKs) * [k_n > 0]    dV_n = K_n dKV
+// Nothing but q, k, v, dO is read (O is recomputed: it is what gradient checkpointing would do anyway),
+// so the algorithmic traffic is 7 tensors; k and v are streamed twice (pass A and pass C), the second time
+// mostly out of L2.
+//
+// Work item = (batch, 4 heads) = a 128-column stripe, streamed in 128-token tiles through a ring of 32 KB
+// shared-memory slots ([2 halves][128 tokens][64 cols], SWIZZLE_128B), exactly like the forward kernel:
+//   pass A   K V  pairs -> D_KV [128x128] += relu(K)^T V (diagonal 32x32 blocks = per-head KV), Ks
+//   pass B   Q dO pairs -> num = Q KV -> r, dDen; Q~ = r Q split into bf16 hi (in place) + lo;
+//            dQ~ = dO KV^T (raw dO, exact) ; D_dKV += (Q~hi + Q~lo)^T dO ; dQ leaves from the dO slot
+//   pass C   K V  pairs -> dV = relu(K) dKV, dK = V dKV^T + dKs ; both leave from their own slots
+// Every per-row scale is applied in fp32 (in the epilogue or through a hi/lo bf16 split), and the 32x32
+// KV / dKV operands are split hi/lo as well, so all five contractions keep ~fp32 accuracy like the
+// reference's `.float()` matmuls.
+//
+// Roles (352 threads): warp 0 TMA producer, warp 1 tcgen05 issuer, warps 2..9 transform/epilogue,
+// warp 10 TMA-store + slot release.  Parity waits follow one rule: every waiter observes every phase of
+// the barriers it waits on, in order.
+#include <cstdio>
+#include <cstdlib>
+
+#include "common.cuh"
+#include "sm100.cuh"
+
+namespace yat {
+namespace {
+using namespace sm100;
+
+constexpr int kD = 32;
+constexpr int kHeadsPerItem = 4;
+constexpr int kTile = 128;
+constexpr int kHalfBytes = kTile * 128;
+constexpr int kSlotBytes = 2 * kHalfBytes;
+constexpr int kStages = 5;
+constexpr int kEpiWarps = 8;
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kThreads = 64 + kEpiThreads + 32;
+constexpr int kTmemCols = 512;
+constexpr int kBmatBytes = 2048;
+// TMEM columns
+constexpr uint32_t kColKV = 0;     // pass A accumulator; pass C: dV
+constexpr uint32_t kColDKV = 128;  // pass B accumulator
+constexpr uint32_t kColNum = 256;  // pass B: num, pass C: dK
+constexpr uint32_t kColDQ = 384;   // pass B: dQ~
+constexpr uint32_t kColDK = 256;
+constexpr uint32_t kColDV = 0;
+
+struct BwdSmem {
+  uint8_t slots[kStages][kSlotBytes];           // 1024-aligned
+  uint8_t lo[kSlotBytes];                       // low halves of Q~ = r * relu(Q)
+  uint8_t bmat[kHeadsPerItem][2][kBmatBytes];   // [head][hi|lo] 32x32: KV in pass B, dKV in pass C
+  float den[kTile][kHeadsPerItem];
+  float wrow[kTile][kHeadsPerItem];             // dDen / r per row and head (weights of the dKs sum)
+  float ks[kHeadsPerItem * kD];
+  float dks[kHeadsPerItem * kD];
+  float red[kEpiWarps][kHeadsPerItem * kD];
+  uint64_t full[kStages], empty[kStages], ready[kStages], out_ready[kStages];
+  uint64_t kv_full, b_ready, dkv_full, b2_ready;
+  uint64_t num_full, num_empty, dq_full, dq_empty, pair_done, c_full, c_empty;
+  uint32_t tmem_base;
+};
+constexpr int kBwdSmemBytes = (int)sizeof(BwdSmem) + 1024;
+static_assert(kBwdSmemBytes <= 232448, "backward kernel exceeds the 227 KB shared-memory limit");
+
+constexpr uint32_t kIdescTT = make_idesc_bf16(128, 128, 1, 1);  // X^T Y over tokens: A, B MN-major
+constexpr uint32_t kIdescMN = make_idesc_bf16(128, 32, 0, 1);   // rows x 32x32 operand read as [k][n]
+constexpr uint32_t kIdescK = make_idesc_bf16(128, 32, 0, 0);    // rows x transposed 32x32 operand
+
+__device__ __forceinline__ uint4 relu8(uint4 v) {
+  const __nv_bfloat162 z = __float2bfloat162_rn(0.f);
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __hmax2_nan(h[i], z);
+  return v;
+}
+__device__ __forceinline__ void unpack8f(const uint4& v, float f[8]) {
+  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+  f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+}
+__device__ __forceinline__ uint4 pack8(const float f[8]) {
+  return make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+}
+
+// 32x32 fp32 block held as one row (32 values) per lane -> bf16 hi + lo, MN-major no-swizzle core matrices:
+// element [k][n] at (n/8)*512 + (k/8)*128 + (k%8)*16 + (n%8)*2.  Read with b_major = MN it is the operand
+// X[k][n]; read with b_major = K (LBO 512, SBO 128) the very same bytes are X^T.
+__device__ __forceinline__ void store_bmat_hilo(uint8_t* bh, uint8_t* bl, int lane, const uint32_t (&r)[32]) {
+  const int off = (lane >> 3) * 128 + (lane & 7) * 16;
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    uint32_t hi[4], lo[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float a0 = __uint_as_float(r[g * 8 + 2 * j]), a1 = __uint_as_float(r[g * 8 + 2 * j + 1]);
+      hi[j] = pack_bf16(a0, a1);
+      lo[j] = pack_bf16(a0 - bf16_lo(hi[j]), a1 - bf16_hi(hi[j]));
+    }
+    *reinterpret_cast<uint4*>(bh + g * 512 + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<uint4*>(bl + g * 512 + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+  }
+}
+
+struct BwdMaps {
+  CUtensorMap q, k, v, d_o, dq, dk, dv;
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int groups, int dbg) {
+  const int max_pass = dbg & 3 ? (dbg & 3) : 3;  // debug: run only the first passes
+  extern __shared__ uint8_t smem_raw[];
+  BwdSmem& S = *reinterpret_cast<BwdSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tiles = (N + kTile - 1) / kTile;
+  const int n_items = B * groups;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(smem_u32(&S.full[s]), 1);
+      mbar_init(smem_u32(&S.empty[s]), 1);
+      mbar_init(smem_u32(&S.ready[s]), kEpiWarps);
+      mbar_init(smem_u32(&S.out_ready[s]), kEpiWarps);
+    }
+    mbar_init(smem_u32(&S.kv_full), 1);
+    mbar_init(smem_u32(&S.b_ready), kEpiWarps);
+    mbar_init(smem_u32(&S.dkv_full), 1);
+    mbar_init(smem_u32(&S.b2_ready), kEpiWarps);
+    mbar_init(smem_u32(&S.num_full), 1);
+    mbar_init(smem_u32(&S.num_empty), kEpiWarps);
+    mbar_init(smem_u32(&S.dq_full), 1);
+    mbar_init(smem_u32(&S.dq_empty), kEpiWarps);
+    mbar_init(smem_u32(&S.pair_done), 1);
+    mbar_init(smem_u32(&S.c_full), 1);
+    mbar_init(smem_u32(&S.c_empty), kEpiWarps);
+    fence_barrier_init();
+    tma_prefetch_desc(&M.q); tma_prefetch_desc(&M.k); tma_prefetch_desc(&M.v); tma_prefetch_desc(&M.d_o);
+    tma_prefetch_desc(&M.dq); tma_prefetch_desc(&M.dk); tma_prefetch_desc(&M.dv);
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(&S.tmem_base), kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = S.tmem_base;
+
+  if (warp == 0) {
+    // ======================= TMA producer =======================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int b = item / groups, c0 = (item % groups) * (kHeadsPerItem * kD);
+        for (int pass = 0; pass < max_pass; ++pass) {
+          for (int t = 0; t < n_tiles; ++t) {
+#pragma unroll
+            for (int w = 0; w < 2; ++w, ++it) {
+              const CUtensorMap* tm = pass == 1 ? (w ? &M.d_o : &M.q) : (w ? &M.v : &M.k);
+              const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+              mbar_wait(smem_u32(&S.empty[s]), ph ^ 1);
+              const uint32_t full = smem_u32(&S.full[s]);
+              mbar_arrive_expect_tx(full, kSlotBytes);
+              const uint32_t dst = smem_u32(&S.slots[s][0]);
+              tma_load_3d(dst, tm, full, c0, t * kTile, b);
+              tma_load_3d(dst + kHalfBytes, tm, full, c0 + 64, t * kTile, b);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ======================= tcgen05 issuer =======================
+    if (lane == 0) {
+      uint32_t it = 0, bt = 0, ct = 0, item_iter = 0;
+      uint32_t ready_ph = 0;  // per-slot parity of `ready` (V uses of a slot do not complete a phase)
+      auto wait_ready = [&](uint32_t s) {
+        mbar_wait(smem_u32(&S.ready[s]), (ready_ph >> s) & 1);
+        ready_ph ^= 1u << s;
+      };
+      // rows x (32x32 operand): 4 heads x (hi, lo) x 2 K-steps into 32-column accumulators
+      auto small_mmas = [&](uint32_t acc_col, uint32_t a_slot, bool transposed) {
+#pragma unroll
+        for (int h = 0; h < kHeadsPerItem; ++h) {
+          const uint32_t d = tmem + acc_col + h * kD;
+          const uint32_t ah = a_slot + (h >> 1) * kHalfBytes + (h & 1) * 64;  // 32 columns = 64 B inside the 128 B row
+#pragma unroll
+          for (int hl = 0; hl < 2; ++hl) {
+            const uint32_t ba = smem_u32(&S.bmat[h][hl][0]);
+#pragma unroll
+            for (int ks = 0; ks < 2; ++ks) {
+              const uint64_t da = make_smem_desc(ah + ks * 32, 16, 1024, kLayoutSw128);
+              if (!transposed) {
+                // operand [k][n] as stored: MN-major, 8-k group stride (LBO) 128 B, 8-n group stride (SBO) 512 B
+                const uint64_t db = make_smem_desc(ba + ks * 256, 128, 512, kLayoutNone);
+                umma_bf16(d, da, db, kIdescMN, (hl | ks) != 0);
+              } else {
+                // same bytes read as the transpose: K-major, 8-k chunk stride (LBO) 512 B, 8-n group stride (SBO) 128 B
+                const uint64_t db = make_smem_desc(ba + ks * 1024, 512, 128, kLayoutNone);
+                umma_bf16(d, da, db, kIdescK, (hl | ks) != 0);
+              }
+            }
+          }
+        }
+      };
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++item_iter) {
+        // TMEM columns [0,128) were dV of the previous item's last tile: wait until it has been read
+        mbar_wait(smem_u32(&S.c_empty), (ct & 1) ^ 1);
+        // ---- pass A: D_KV += relu(K)^T V
+        for (int t = 0; t < n_tiles; ++t, it += 2) {
+          const uint32_t sk = it % kStages, sv = (it + 1) % kStages, pv = ((it + 1) / kStages) & 1;
+          wait_ready(sk);
+          mbar_wait(smem_u32(&S.full[sv]), pv);
+          tc_fence_after();
+          const uint32_t ka = smem_u32(&S.slots[sk][0]), va = smem_u32(&S.slots[sv][0]);
+#pragma unroll
+          for (int ks = 0; ks < kTile / 16; ++ks) {
+            const uint64_t da = make_smem_desc(ka + ks * 2048, kHalfBytes, 1024, kLayoutSw128);
+            const uint64_t db = make_smem_desc(va + ks * 2048, kHalfBytes, 1024, kLayoutSw128);
+            umma_bf16(tmem + kColKV, da, db, kIdescTT, (t | ks) != 0);
+          }
+          tc_commit(smem_u32(&S.empty[sk]));
+          tc_commit(smem_u32(&S.empty[sv]));
+        }
+        tc_commit(smem_u32(&S.kv_full));
+        mbar_wait(smem_u32(&S.b_ready), item_iter & 1);
+        tc_fence_after();
+        if (max_pass < 2) continue;
+        // ---- pass B
+        for (int t = 0; t < n_tiles; ++t, it += 2, ++bt) {
+          const uint32_t sq = it % kStages, sd = (it + 1) % kStages;
+          const uint32_t qa = smem_u32(&S.slots[sq][0]), da_ = smem_u32(&S.slots[sd][0]), la = smem_u32(&S.lo[0]);
+          wait_ready(sq);                                        // relu(Q) in place, den written
+          mbar_wait(smem_u32(&S.num_empty), (bt & 1) ^ 1);
+          tc_fence_after();
+          if (!(dbg & 128)) small_mmas(kColNum, qa, false);      // num = relu(Q) KV
+          tc_commit(smem_u32(&S.num_full));
+          wait_ready(sd);                                        // Q~ hi (Q slot) / lo written, dO landed
+          mbar_wait(smem_u32(&S.dq_empty), (bt & 1) ^ 1);
+          tc_fence_after();
+          if (!(dbg & 4)) small_mmas(kColDQ, da_, true);         // dQ~ = dO KV^T
+          tc_commit(smem_u32(&S.dq_full));
+          if (!(dbg & 256))
+#pragma unroll
+          for (int part = 0; part < 2; ++part) {                 // D_dKV += (Q~hi + Q~lo)^T dO
+            const uint32_t aa = part ? la : qa;
+#pragma unroll
+            for (int ks = 0; ks < kTile / 16; ++ks) {
+              const uint64_t da = make_smem_desc(aa + ks * 2048, kHalfBytes, 1024, kLayoutSw128);
+              const uint64_t db = make_smem_desc(da_ + ks * 2048, kHalfBytes, 1024, kLayoutSw128);
+              umma_bf16(tmem + kColDKV, da, db, kIdescTT, (t | part | ks) != 0);
+            }
+          }
+          tc_commit(smem_u32(&S.pair_done));
+        }
+        tc_commit(smem_u32(&S.dkv_full));
+        mbar_wait(smem_u32(&S.b2_ready), item_iter & 1);
+        tc_fence_after();
+        if (max_pass < 3) continue;
+        // ---- pass C: dV = relu(K) dKV, dK~ = V dKV^T
+        for (int t = 0; t < n_tiles; ++t, it += 2, ++ct) {
+          const uint32_t sk = it % kStages, sv = (it + 1) % kStages, pv = ((it + 1) / kStages) & 1;
+          wait_ready(sk);
+          mbar_wait(smem_u32(&S.full[sv]), pv);
+          mbar_wait(smem_u32(&S.c_empty), (ct & 1) ^ 1);
+          tc_fence_after();
+          small_mmas(kColDV, smem_u32(&S.slots[sk][0]), false);
+          if (!(dbg & 4)) small_mmas(kColDK, smem_u32(&S.slots[sv][0]), true);
+          tc_commit(smem_u32(&S.c_full));
+        }
+      }
+    }
+  } else if (warp == 10) {
+    // ======================= TMA store + slot release =======================
+    if (lane == 0) {
+      uint32_t it = 0, out_ph = 0;
+      auto wait_out = [&](uint32_t s) {
+        mbar_wait(smem_u32(&S.out_ready[s]), (out_ph >> s) & 1);
+        out_ph ^= 1u << s;
+      };
+      auto store = [&](const CUtensorMap* tm, uint32_t s, int c0, int row0, int b) {
+        const uint32_t src = smem_u32(&S.slots[s][0]);
+        tma_store_3d(tm, src, c0, row0, b);
+        tma_store_3d(tm, src + kHalfBytes, c0 + 64, row0, b);
+      };
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int b = item / groups, c0 = (item % groups) * (kHeadsPerItem * kD);
+        it += 2 * n_tiles;  // pass A: slots are released by the issuer's commits
+        if (max_pass < 2) continue;
+        for (int t = 0; t < n_tiles; ++t, it += 2) {
+          const uint32_t sq = it % kStages, sd = (it + 1) % kStages;
+          wait_out(sd);                                  // dQ sits in the dO slot; nobody reads the Q slot any more
+          mbar_arrive(smem_u32(&S.empty[sq]));
+          if (!(dbg & 8)) store(&M.dq, sd, c0, t * kTile, b);
+          tma_store_commit();
+          tma_store_wait_read<0>();
+          mbar_arrive(smem_u32(&S.empty[sd]));
+        }
+        if (max_pass < 3) continue;
+        for (int t = 0; t < n_tiles; ++t, it += 2) {
+          const uint32_t sk = it % kStages, sv = (it + 1) % kStages;
+          wait_out(sk);
+          if (!(dbg & 8)) store(&M.dk, sk, c0, t * kTile, b);
+          tma_store_commit();
+          wait_out(sv);
+          if (!(dbg & 8)) store(&M.dv, sv, c0, t * kTile, b);
+          tma_store_commit();
+          tma_store_wait_read<1>();
+          mbar_arrive(smem_u32(&S.empty[sk]));
+          tma_store_wait_read<0>();
+          mbar_arrive(smem_u32(&S.empty[sv]));
+        }
+      }
+      tma_store_wait_all<0>();
+    }
+  } else {
+    // ======================= transform + epilogue warps (2..9) =======================
+    const int te = threadIdx.x - 64;          // 0..255
+    const int we = te >> 5;                   // 0..7
+    const int cc = te & 15;                   // transform mapping: 16-byte chunk column of the 256-byte item row
+    const int rbase = te >> 4;                //                    rows rbase + 16 i
+    const int half = cc >> 3, chunk = cc & 7;
+    // Head (0..3) owning this thread's chunk column.  Kept opaque to the optimiser: nvcc 12.9 otherwise folds
+    // `[r][cc >> 2]` into `base + 16 r + cc` (valid only under the `(cc & 3) == 0` predicate of the den store)
+    // and reuses that address for the unpredicated wrow load, which then faults as a misaligned access.
+    int hsel = cc >> 2;
+    asm volatile("" : "+r"(hsel));
+    const int quad = warp & 3;                // TMEM lane quadrant this warp may access
+    const int colhalf = we >> 2;              // row mapping: which 64-column half (2 heads) this warp finishes
+    const int row = quad * 32 + lane;         //              token row in the tile (TMEM lane)
+    const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+    const int row_off = colhalf * kHalfBytes + row * 128;
+    uint32_t it = 0, bt = 0, ct = 0, item_iter = 0;
+
+    // column sums held per thread (transform mapping) -> dst[128] through S.red; all epilogue threads call it
+    auto reduce_columns = [&](float (&cs)[8], float* dst) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 16);
+      if (lane < 16) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) S.red[we][cc * 8 + j] = cs[j];
+      }
+      named_bar_sync(1, kEpiThreads);
+      if (te < kHeadsPerItem * kD) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < kEpiWarps; ++w) s += S.red[w][te];
+        dst[te] = s;
+      }
+    };
+    // diagonal 32x32 blocks of a [128x128] accumulator -> hi/lo operands in S.bmat (warps with we < 4: head = quad)
+    auto build_bmat = [&](uint32_t col) {
+      if (we < 4) {
+        uint32_t r[32];
+        tmem_ld32(tmem + lane_addr + col + quad * kD, r);   // X_head[k = lane][n = 0..31]
+        tmem_ld_wait();
+        store_bmat_hilo(&S.bmat[quad][0][0], &S.bmat[quad][1][0], lane, r);
+        fence_proxy_async();
+      }
+      tc_fence_before();
+      named_bar_sync(1, kEpiThreads);
+    };
+
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++item_iter) {
+      // ---------------- pass A: relu(K) in place, Ks ----------------
+      float csum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      for (int t = 0; t < n_tiles; ++t, it += 2) {
+        const uint32_t sk = it % kStages, pk = (it / kStages) & 1;
+        mbar_wait(smem_u32(&S.full[sk]), pk);
+        uint8_t* base = &S.slots[sk][half * kHalfBytes];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int r = rbase + 16 * i;
+          uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
+          const uint4 v = relu8(*p);
+          *p = v;
+          float f[8];
+          unpack8f(v, f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) csum[j] += f[j];
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&S.ready[sk]));
+        mbar_wait(smem_u32(&S.full[(it + 1) % kStages]), ((it + 1) / kStages) & 1);  // observe the V phase too
+      }
+      reduce_columns(csum, S.ks);
+      mbar_wait(smem_u32(&S.kv_full), item_iter & 1);
+      tc_fence_after();
+      build_bmat(kColKV);                       // barrier inside: ks visible, D_KV drained, bmat written
+      if (lane == 0) mbar_arrive(smem_u32(&S.b_ready));
+      float ksr[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ksr[j] = S.ks[cc * 8 + j];
+
+      if (max_pass < 2) continue;
+      // ---------------- pass B ----------------
+      float dcs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      for (int t = 0; t < n_tiles; ++t, it += 2, ++bt) {
+        const uint32_t sq = it % kStages, pq = (it / kStages) & 1;
+        const uint32_t sd = (it + 1) % kStages, pd = ((it + 1) / kStages) & 1;
+        // E1: relu(Q) in place, den = relu(Q).Ks
+        mbar_wait(smem_u32(&S.full[sq]), pq);
+        {
+          uint8_t* base = &S.slots[sq][half * kHalfBytes];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int r = rbase + 16 * i;
+            uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
+            const uint4 v = relu8(*p);
+            *p = v;
+            float f[8], d = 0.f;
+            unpack8f(v, f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) d = fmaf(f[j], ksr[j], d);
+            d += __shfl_xor_sync(0xffffffffu, d, 1);
+            d += __shfl_xor_sync(0xffffffffu, d, 2);
+            if ((cc & 3) == 0) S.den[r][hsel] = d;
+          }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&S.ready[sq]));
+        named_bar_sync(1, kEpiThreads);         // den visible in the row mapping
+
+        // E2: num -> r, dDen; Q~ = r * relu(Q) as bf16 hi (in place) + lo
+        mbar_wait(smem_u32(&S.full[sd]), pd);
+        mbar_wait(smem_u32(&S.num_full), bt & 1);
+        tc_fence_after();
+        float rr[2], dd[2];
+        uint8_t* qrow = &S.slots[sq][row_off];
+        uint8_t* lrow = &S.lo[row_off];
+        const uint8_t* drow = &S.slots[sd][row_off];
+        rr[0] = rr[1] = dd[0] = dd[1] = 0.f;
+        if (!(dbg & 16))
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const int h = colhalf * 2 + hh;
+          uint32_t acc[32];
+          tmem_ld32(tmem + lane_addr + kColNum + h * kD, acc);
+          tmem_ld_wait();
+          float s = 0.f;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            float f[8];
+            unpack8f(*reinterpret_cast<const uint4*>(drow + (((hh * 4 + g) ^ (row & 7)) << 4)), f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) s = fmaf(f[j], __uint_as_float(acc[g * 8 + j]), s);
+          }
+          const float r = 1.0f / (S.den[row][h] + 1e-15f);
+          rr[hh] = r;
+          dd[hh] = -s * r * r;
+          S.wrow[row][h] = -s * r;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const int o = ((hh * 4 + g) ^ (row & 7)) << 4;
+            float f[8], hi[8], lo[8];
+            unpack8f(*reinterpret_cast<const uint4*>(qrow + o), f);
+            uint4 hv;
+            uint32_t* hw = reinterpret_cast<uint32_t*>(&hv);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float a0 = f[2 * j] * r, a1 = f[2 * j + 1] * r;
+              hw[j] = pack_bf16(a0, a1);
+              hi[2 * j] = bf16_lo(hw[j]);
+              hi[2 * j + 1] = bf16_hi(hw[j]);
+              lo[2 * j] = a0 - hi[2 * j];
+              lo[2 * j + 1] = a1 - hi[2 * j + 1];
+            }
+            *reinterpret_cast<uint4*>(qrow + o) = hv;
+            *reinterpret_cast<uint4*>(lrow + o) = pack8(lo);
+          }
+        }
+        tc_fence_before();
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(smem_u32(&S.num_empty));
+          mbar_arrive(smem_u32(&S.ready[sd]));
+        }
+        named_bar_sync(1, kEpiThreads);         // wrow and Q~ visible in the transform mapping
+
+        // E3a: dKs += sum_n Q~_n (dDen_n / r_n)
+        if (!(dbg & 32)) {
+          const uint8_t* bh = &S.slots[sq][half * kHalfBytes];
+          const uint8_t* bl = &S.lo[half * kHalfBytes];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int r = rbase + 16 * i;
+            const int o = r * 128 + ((chunk ^ (r & 7)) << 4);
+            float fh[8], fl[8];
+            unpack8f(*reinterpret_cast<const uint4*>(bh + o), fh);
+            unpack8f(*reinterpret_cast<const uint4*>(bl + o), fl);
+            const float w = S.wrow[r][hsel];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) dcs[j] = fmaf(fh[j] + fl[j], w, dcs[j]);
+          }
+        }
+        // E3b: dQ = (r * dQ~ + dDen * Ks) * [q > 0]
+        mbar_wait(smem_u32(&S.dq_full), bt & 1);
+        tc_fence_after();
+        uint4 outv[2][4];
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh)
+#pragma unroll
+          for (int g = 0; g < 4; ++g) outv[hh][g] = make_uint4(0, 0, 0, 0);
+        if (!(dbg & 64))
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const int h = colhalf * 2 + hh;
+          uint32_t acc[32];
+          tmem_ld32(tmem + lane_addr + kColDQ + h * kD, acc);
+          tmem_ld_wait();
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            float m[8], o8[8];
+            unpack8f(*reinterpret_cast<const uint4*>(qrow + (((hh * 4 + g) ^ (row & 7)) << 4)), m);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float val = fmaf(rr[hh], __uint_as_float(acc[g * 8 + j]), dd[hh] * S.ks[h * kD + g * 8 + j]);
+              o8[j] = m[j] > 0.f ? val : 0.f;
+            }
+            outv[hh][g] = pack8(o8);
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&S.dq_empty));
+        mbar_wait(smem_u32(&S.pair_done), bt & 1);   // the MMAs have finished reading the dO / Q~ tiles
+        uint8_t* orow = &S.slots[sd][row_off];
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh)
+#pragma unroll
+          for (int g = 0; g < 4; ++g)
+            *reinterpret_cast<uint4*>(orow + (((hh * 4 + g) ^ (row & 7)) << 4)) = outv[hh][g];
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&S.out_ready[sd]));
+      }
+      reduce_columns(dcs, S.dks);
+      mbar_wait(smem_u32(&S.dkv_full), item_iter & 1);
+      tc_fence_after();
+      build_bmat(kColDKV);                      // barrier inside: dks visible, D_dKV drained, bmat rewritten
+      if (lane == 0) mbar_arrive(smem_u32(&S.b2_ready));
+
+      if (max_pass < 3) continue;
+      // ---------------- pass C ----------------
+      for (int t = 0; t < n_tiles; ++t, it += 2, ++ct) {
+        const uint32_t sk = it % kStages, pk = (it / kStages) & 1;
+        const uint32_t sv = (it + 1) % kStages, pv = ((it + 1) / kStages) & 1;
+        mbar_wait(smem_u32(&S.full[sk]), pk);
+        {
+          uint8_t* base = &S.slots[sk][half * kHalfBytes];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int r = rbase + 16 * i;
+            uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
+            *p = relu8(*p);
+          }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&S.ready[sk]));
+        mbar_wait(smem_u32(&S.full[sv]), pv);       // observe the V phase
+        mbar_wait(smem_u32(&S.c_full), ct & 1);     // both MMAs done: K and V tiles may be overwritten
+        tc_fence_after();
+        // dK = (V dKV^T + dKs) * [k > 0]  -> K slot
+        uint8_t* krow = &S.slots[sk][row_off];
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const int h = colhalf * 2 + hh;
+          uint32_t acc[32];
+          tmem_ld32(tmem + lane_addr + kColDK + h * kD, acc);
+          tmem_ld_wait();
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            uint4* p = reinterpret_cast<uint4*>(krow + (((hh * 4 + g) ^ (row & 7)) << 4));
+            float m[8], o8[8];
+            unpack8f(*p, m);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              o8[j] = m[j] > 0.f ? __uint_as_float(acc[g * 8 + j]) + S.dks[h * kD + g * 8 + j] : 0.f;
+            *p = pack8(o8);
+          }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&S.out_ready[sk]));
+        // dV = relu(K) dKV -> V slot
+        uint8_t* vrow = &S.slots[sv][row_off];
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const int h = colhalf * 2 + hh;
+          uint32_t acc[32];
+          tmem_ld32(tmem + lane_addr + kColDV + h * kD, acc);
+          tmem_ld_wait();
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            float o8[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o8[j] = __uint_as_float(acc[g * 8 + j]);
+            *reinterpret_cast<uint4*>(vrow + (((hh * 4 + g) ^ (row & 7)) << 4)) = pack8(o8);
+          }
+        }
+        tc_fence_before();
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(smem_u32(&S.c_empty));
+          mbar_arrive(smem_u32(&S.out_ready[sv]));
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, kTmemCols);
+}
+
+}  // namespace
+}  // namespace yat
+
+extern "C" int yat_linattn_bwd(const void* q, const void* k, const void* v, const void* dout, int B, int N, int H,
+                               int D, void* dq, void* dk, void* dv, void* stream) {
+  using namespace yat;
+  YAT_REQUIRE(q && k && v && dout && dq && dk && dv, YAT_ERR_BAD_ARG, "yat_linattn_bwd: null pointer argument");
+  YAT_REQUIRE(B > 0 && N > 0 && H > 0, YAT_ERR_BAD_ARG, "yat_linattn_bwd: non-positive dimension");
+  YAT_REQUIRE(D == kD, YAT_ERR_UNSUPPORTED, "yat_linattn_bwd: head_dim %d not supported (SANA uses 32)", D);
+  YAT_REQUIRE((((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)dout | (uintptr_t)dq | (uintptr_t)dk |
+                (uintptr_t)dv) & 15u) == 0,
+              YAT_ERR_BAD_ARG, "yat_linattn_bwd: tensors must be 16-byte aligned");
+  BwdMaps maps;
+  const uint64_t C = (uint64_t)H * D;
+  const void* ptrs[7] = {q, k, v, dout, dq, dk, dv};
+  CUtensorMap* tms[7] = {&maps.q, &maps.k, &maps.v, &maps.d_o, &maps.dq, &maps.dk, &maps.dv};
+  for (int i = 0; i < 7; ++i) {
+    const int rc = make_tmap_3d_bf16(tms[i], ptrs[i], C, N, B, 64, kTile);
+    if (rc != YAT_OK) return rc;
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    const cudaError_t e =
+        cudaFuncSetAttribute(linattn_bwd_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmemBytes);
+    YAT_REQUIRE(e == cudaSuccess, YAT_ERR_CUDA, "yat_linattn_bwd: cannot reserve %d B of shared memory (%s)",
+                kBwdSmemBytes, cudaGetErrorString(e));
+    attr_set = true;
+  }
+  const int groups = (H + kHeadsPerItem - 1) / kHeadsPerItem;
+  const int items = B * groups;
+  const int grid = items < kNumSMs ? items : kNumSMs;
+  const char* dbg_env = getenv("YAT_BWD_DEBUG");  // development aid: bits 0-1 = passes to run, 4 = no transposed MMAs, 8 = no stores
+  const int dbg = dbg_env ? atoi(dbg_env) : 0;
+  linattn_bwd_sm100_kernel<<<grid, kThreads, kBwdSmemBytes, (cudaStream_t)stream>>>(maps, B, N, groups, dbg);
+  return check_launch("linattn_bwd_sm100");
+}

@@ -216,6 +216,11 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&S.ready[sk]));  // (V needs no transform: the issuer waits on `full`)
+        // Observe the V slot's phase as well: a parity wait is only sound if the waiter sees every phase
+        // of the barrier in order.  Skipping the V phases let these warps reach "K in the same slot, 5 loads
+        // later" while the V load was still in flight, where the parity of the wanted phase equals the
+        // parity of the last completed one and the wait falls through (seen as a rare hang on B200).
+        mbar_wait(smem_u32(&S.full[(it + 1) % kStages]), ((it + 1) / kStages) & 1);
       }
       // Ks[col] = sum over threads sharing the chunk column
 #pragma unroll
@@ -368,9 +373,16 @@ int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t N
   const cuuint64_t strides[2] = {C * 2, N * C * 2};
   const cuuint32_t box[3] = {box_c, box_n, 1};
   const cuuint32_t estr[3] = {1, 1, 1};
-  const CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r == CUDA_ERROR_INVALID_CONTEXT) {
+    // first driver-API call on this thread (autograd's backward worker): bind the primary context and retry
+    cudaFree(nullptr);
+    r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
   YAT_REQUIRE(r == CUDA_SUCCESS, YAT_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
   return YAT_OK;
 }
@@ -405,11 +417,4 @@ extern "C" int yat_linattn_fwd(const void* q, const void* k, const void* v, int 
   const int grid = items < kNumSMs ? items : kNumSMs;
   linattn_fwd_sm100_kernel<<<grid, kThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(tq, tk, tv, to, B, N, groups);
   return check_launch("linattn_fwd_sm100");
-}
-
-extern "C" int yat_linattn_bwd(const void* q, const void* k, const void* v, const void* dout, int B, int N, int H,
-                               int D, void* dq, void* dk, void* dv, void* stream) {
-  // tensor-core backward lands next; until then the call is refused rather than silently rerouted
-  yat::set_error("yat_linattn_bwd: tcgen05 backward not built yet");
-  return YAT_ERR_UNSUPPORTED;
 }
