@@ -47,6 +47,8 @@ def parse_args():
     ap.add_argument("--debug-linattn", default=None, choices=["simt"],
                     help="debug only: run linear attention on the CUDA-core restatement (flagged in config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--kernels-only", action="store_true",
+                    help="debug only: print the stand-alone kernel roofline table and exit (not a bench line)")
     ap.add_argument("--cpu-budget-s", type=float, default=30.0)
     return ap.parse_args()
 
@@ -455,6 +457,13 @@ def run_own_arm(args):
 
 def main():
     args = parse_args()
+    if args.kernels_only:
+        import torch
+        from yat_b200 import build as _build
+        _build.build()
+        for name, e in _standalone_kernels(torch.device("cuda", 0), peaks()).items():
+            print(json.dumps({"kernel": name, **e}), flush=True)
+        return
     if args.impl == "reference":
         run_reference_arm(args)
         return

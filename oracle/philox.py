@@ -4,7 +4,8 @@ The reference draws noise and timesteps from a torch CPU generator (train_sana.p
 common/trainer.py:325).  A counter-based stream cannot reproduce mt19937, so bit-parity with
 the reference is tested in *inject* mode (noise/u supplied); this module restates the
 device's own Philox4x32-10 + Box-Muller stream (yat_b200/csrc/philox.cuh) so the *generate*
-mode has a CPU oracle too: the integer stream is exact, normals agree to a few fp32 ulp.
+mode has a CPU oracle too: the integer stream is exact, timestep normals agree to a few fp32 ulp and
+latent normals to ~1e-6 absolute (special-function-unit evaluation on the device).
 
 Layout (must match philox.cuh):
   key     = (seed & 0xffffffff, seed >> 32)
@@ -50,14 +51,27 @@ def box_muller(xa, xb):
     return r * np.cos(2.0 * np.pi * a), r * np.sin(2.0 * np.pi * a)
 
 
+def box_muller_fast(xa, xb):
+    """Latent-noise stream (stream 0), float64 evaluation of the device map (philox.cuh
+    box_muller_fast): u1 = 1 - (xa>>9)*2^-23 in (0,1], theta = 2*pi*((xb>>9)*2^-23 - 0.5) in
+    [-pi,pi).  The device evaluates lg2/sqrt/sin/cos on the special-function unit, so its fp32
+    normals sit within ~1e-6 absolute of these before rounding to the latent dtype."""
+    u1 = 1.0 - (xa >> np.uint32(9)).astype(np.float64) * 2.0 ** -23
+    theta = 2.0 * np.pi * ((xb >> np.uint32(9)).astype(np.float64) * 2.0 ** -23 - 0.5)
+    r = np.sqrt(-2.0 * np.log(u1))
+    return r * np.cos(theta), r * np.sin(theta)
+
+
 def normal_quads(seed, offset, sample, n_quads, stream=0):
-    """Normals for quads 0..n_quads-1 of ``sample`` -> float64 array [n_quads*4]."""
+    """Normals for quads 0..n_quads-1 of ``sample`` -> float64 array [n_quads*4].  Stream 0
+    (latent noise) uses the fast map, stream 1 (timestep draw) the precise one."""
     quad = np.arange(n_quads, dtype=np.uint64)
     x0, x1, x2, x3 = philox4x32_10(quad, np.uint64(sample), np.uint64(int(offset) & 0xFFFFFFFF),
                                    np.uint64(_counter_hi(offset, stream)),
                                    int(seed) & 0xFFFFFFFF, (int(seed) >> 32) & 0xFFFFFFFF)
-    z0, z1 = box_muller(x0, x1)
-    z2, z3 = box_muller(x2, x3)
+    bm = box_muller_fast if stream == 0 else box_muller
+    z0, z1 = bm(x0, x1)
+    z2, z3 = bm(x2, x3)
     return np.stack([z0, z1, z2, z3], axis=1).reshape(-1)
 
 

@@ -107,13 +107,14 @@ def test_generate_mode_matches_the_philox_oracle(cuda):
     lat = torch.randn((B, chw), generator=torch.Generator().manual_seed(3)).to(torch.bfloat16)
     sch = FlowMatchEulerDiscreteScheduler()
     out = flowmatch_noise(lat.to(cuda), sch, seed=seed, offset=offset, want_noise=True)
-    # normals: a few fp32 ulp from the float64 oracle -> after bf16 rounding at most rare 1-ulp flips
+    # normals: ~1e-6 absolute from the float64 oracle -> after bf16 rounding at most rare 1-ulp flips
     z = torch.from_numpy(philox.noise(seed, offset, B, chw))
     got = out.noise.cpu().float()
     ref = z.to(torch.bfloat16).float()
     mism = (got != ref)
     assert mism.float().mean().item() < 2e-3
-    assert ((got - ref).abs() <= 2.0 ** -7 * ref.abs().clamp_min(2.0 ** -120) * 1.01)[mism].all()
+    # a flip is one bf16 ulp, or (values near zero, where sin/cos.approx are absolute-accurate) < 4e-6
+    assert (((got - ref).abs() <= 2.0 ** -7 * ref.abs() * 1.01) | ((got - ref).abs() < 4e-6))[mism].all()
     assert abs(got.mean().item()) < 0.02 and abs(got.std().item() - 1.0) < 0.02
     # timestep indices: equal to the oracle unless u*T sits on an integer boundary
     zt = philox.timestep_normals(seed, offset, B)

@@ -63,6 +63,7 @@ __global__ void __launch_bounds__(kThreads) loss_fused_kernel(const LossParams p
   const PhiloxKey key = make_philox_key(p.seed, p.offset, 0u);
   const bool velocity = p.target_mode == YAT_TARGET_VELOCITY;
   const bool need_x0 = velocity;
+  const bool unit_g = p.gscale == 1.0f;   // (x * 1.0f) is the identity: skip the multiply
   float acc_noise = 0.f, acc_pres = 0.f;
 
   for (int64_t tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
@@ -92,12 +93,7 @@ __global__ void __launch_bounds__(kThreads) loss_fused_kernel(const LossParams p
     for (int j = 0; j < kUnroll; ++j) {
       const int64_t v = v0 + j * kThreads;
       if (v >= p.vec_per_sample) continue;
-      if (GEN) {
-        float z[8];
-        normal4(key, (uint32_t)(2 * v), (uint32_t)b, z);
-        normal4(key, (uint32_t)(2 * v + 1), (uint32_t)b, z + 4);
-        ev[j] = make_uint4(pack_bf16(z[0], z[1]), pack_bf16(z[2], z[3]), pack_bf16(z[4], z[5]), pack_bf16(z[6], z[7]));
-      }
+      if (GEN) ev[j] = normal8_bf16(key, (uint32_t)v, (uint32_t)b);
       const uint32_t pw[4] = {pv[j].x, pv[j].y, pv[j].z, pv[j].w};
       const uint32_t ew[4] = {ev[j].x, ev[j].y, ev[j].z, ev[j].w};
       uint32_t xw[4] = {0, 0, 0, 0}, fw[4] = {0, 0, 0, 0}, gw[4];
@@ -105,19 +101,16 @@ __global__ void __launch_bounds__(kThreads) loss_fused_kernel(const LossParams p
       if (HAS_PF) { fw[0] = fv[j].x; fw[1] = fv[j].y; fw[2] = fv[j].z; fw[3] = fv[j].w; }
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        float tg_lo = bf16_lo(ew[k]), tg_hi = bf16_hi(ew[k]);
-        if (velocity) {  // target = noise - latents, rounded to bf16 (train_sana.py:217)
-          const uint32_t t = pack_bf16(__fsub_rn(tg_lo, bf16_lo(xw[k])), __fsub_rn(tg_hi, bf16_hi(xw[k])));
-          tg_lo = bf16_lo(t);
-          tg_hi = bf16_hi(t);
-        }
+        // target = noise - latents, rounded once to bf16 (train_sana.py:217): packed subtract
+        const uint32_t t = velocity ? as_u32(__hsub2_rn(as_bf162(ew[k]), as_bf162(xw[k]))) : ew[k];
+        const float tg_lo = bf16_lo(t), tg_hi = bf16_hi(t);
         const float p_lo = bf16_lo(pw[k]), p_hi = bf16_hi(pw[k]);
         const float d_lo = __fsub_rn(p_lo, tg_lo), d_hi = __fsub_rn(p_hi, tg_hi);
         t_noise = fmaf(d_lo, d_lo, t_noise);
         t_noise = fmaf(d_hi, d_hi, t_noise);
         // mse_loss_backward: (norm * (input - target)) * grad_output, one fp32 rounding per op
-        float g_lo = __fmul_rn(__fmul_rn(p.coef, d_lo), p.gscale);
-        float g_hi = __fmul_rn(__fmul_rn(p.coef, d_hi), p.gscale);
+        float g_lo = __fmul_rn(p.coef, d_lo), g_hi = __fmul_rn(p.coef, d_hi);
+        if (!unit_g) { g_lo = __fmul_rn(g_lo, p.gscale); g_hi = __fmul_rn(g_hi, p.gscale); }
         if (p.weights) { g_lo *= w; g_hi *= w; }
         if (HAS_PF) {
           const float r_lo = __fsub_rn(p_lo, bf16_lo(fw[k])), r_hi = __fsub_rn(p_hi, bf16_hi(fw[k]));

@@ -86,15 +86,7 @@ __global__ void __launch_bounds__(kThreads) noise_bf16_kernel(const NoiseParams 
   __shared__ float s_coef[2];
   const int b = blockIdx.x / p.blocks_per_sample;
   const int chunk = blockIdx.x - b * p.blocks_per_sample;
-  if (threadIdx.x == 0) {
-    float ca, cb;
-    sample_scalars<__nv_bfloat16, MODE>(p, b, chunk == 0, ca, cb);
-    s_coef[0] = ca;
-    s_coef[1] = cb;
-  }
-  __syncthreads();
-  const float ca = s_coef[0], cb = s_coef[1];
-  const int64_t nvec = p.chw >> 3;
+  const int nvec = (int)(p.chw >> 3);                       // < 2^31 vectors per sample (checked by the launcher)
   const int64_t base = (int64_t)b * nvec;
   const uint4* x0 = reinterpret_cast<const uint4*>(p.x0) + base;
   const uint4* nz = GEN ? nullptr : reinterpret_cast<const uint4*>(p.noise_in) + base;
@@ -102,42 +94,70 @@ __global__ void __launch_bounds__(kThreads) noise_bf16_kernel(const NoiseParams 
   uint4* tg = p.target ? reinterpret_cast<uint4*>(p.target) + base : nullptr;
   uint4* no = p.noise_out ? reinterpret_cast<uint4*>(p.noise_out) + base : nullptr;
   const PhiloxKey key = make_philox_key(p.seed, p.offset, 0u);
+  constexpr int kTile = kThreads * kUnroll;
+  const int stride = p.blocks_per_sample * kTile;           // this block's tiles: chunk, chunk + bps, ...
 
-  const int64_t v0 = (int64_t)chunk * (kThreads * kUnroll) + threadIdx.x;
+  // order: loads in flight -> (thread 0: per-sample scalars | everyone: eps from the counter RNG)
+  // -> barrier -> interpolation.  Neither the loads nor eps depend on the scalars, so the table
+  // lookup of one thread hides behind the bulk work of the block, and it is paid once per block.
+  int v0 = chunk * kTile + threadIdx.x;
   uint4 xv[kUnroll], ev[kUnroll];
+  auto fetch = [&]() {
 #pragma unroll
-  for (int j = 0; j < kUnroll; ++j) {
-    const int64_t v = v0 + j * kThreads;
-    if (v < nvec) {
-      xv[j] = ld_stream(x0 + v);
-      if (!GEN) ev[j] = ld_stream(nz + v);
+    for (int j = 0; j < kUnroll; ++j) {
+      const int v = v0 + j * kThreads;
+      if (v < nvec) {
+        xv[j] = ld_stream(x0 + v);
+        if (!GEN) ev[j] = ld_stream(nz + v);
+      }
     }
-  }
-#pragma unroll
-  for (int j = 0; j < kUnroll; ++j) {
-    const int64_t v = v0 + j * kThreads;
-    if (v >= nvec) continue;
+  };
+  auto generate = [&]() {
     if (GEN) {
-      float z[8];
-      normal4(key, (uint32_t)(2 * v), (uint32_t)b, z);
-      normal4(key, (uint32_t)(2 * v + 1), (uint32_t)b, z + 4);
-      ev[j] = make_uint4(pack_bf16(z[0], z[1]), pack_bf16(z[2], z[3]), pack_bf16(z[4], z[5]), pack_bf16(z[6], z[7]));
-    }
-    const uint32_t xw[4] = {xv[j].x, xv[j].y, xv[j].z, xv[j].w};
-    const uint32_t ew[4] = {ev[j].x, ev[j].y, ev[j].z, ev[j].w};
-    uint32_t ow[4], tw[4];
 #pragma unroll
-    for (int w = 0; w < 4; ++w) {
-      const float x_lo = bf16_lo(xw[w]), x_hi = bf16_hi(xw[w]);
-      const float e_lo = bf16_lo(ew[w]), e_hi = bf16_hi(ew[w]);
-      const uint32_t p1 = pack_bf16(__fmul_rn(ca, x_lo), __fmul_rn(ca, x_hi));
-      const uint32_t p2 = pack_bf16(__fmul_rn(cb, e_lo), __fmul_rn(cb, e_hi));
-      ow[w] = pack_bf16(__fadd_rn(bf16_lo(p1), bf16_lo(p2)), __fadd_rn(bf16_hi(p1), bf16_hi(p2)));
-      tw[w] = pack_bf16(__fsub_rn(e_lo, x_lo), __fsub_rn(e_hi, x_hi));
+      for (int j = 0; j < kUnroll; ++j) {
+        const int v = v0 + j * kThreads;
+        if (v < nvec) ev[j] = normal8_bf16(key, (uint32_t)v, (uint32_t)b);
+      }
     }
-    st_stream(xt + v, make_uint4(ow[0], ow[1], ow[2], ow[3]));
-    if (tg) st_stream(tg + v, make_uint4(tw[0], tw[1], tw[2], tw[3]));
-    if (no) st_stream(no + v, ev[j]);
+  };
+  fetch();
+  if (threadIdx.x == 0) {
+    float ca, cb;
+    sample_scalars<__nv_bfloat16, MODE>(p, b, chunk == 0, ca, cb);
+    s_coef[0] = ca;
+    s_coef[1] = cb;
+  }
+  generate();
+  __syncthreads();
+  // p1 = bf16(ca*x0), p2 = bf16(cb*eps), x_t = bf16(p1+p2), target = bf16(eps-x0): the packed
+  // bf16x2 *_rn intrinsics round once per op from the exact result (never contracted to an fma),
+  // which is what the fp32-compute-then-round chain of the reference gives: the fp32 product of
+  // two bf16 values is exact, and an fp32 sum of two bf16 values is either exact or further than
+  // 2^-16 relative from any bf16 rounding boundary.
+  const __nv_bfloat162 ca2 = __float2bfloat162_rn(s_coef[0]), cb2 = __float2bfloat162_rn(s_coef[1]);
+  while (true) {
+#pragma unroll
+    for (int j = 0; j < kUnroll; ++j) {
+      const int v = v0 + j * kThreads;
+      if (v >= nvec) continue;
+      const uint32_t xw[4] = {xv[j].x, xv[j].y, xv[j].z, xv[j].w};
+      const uint32_t ew[4] = {ev[j].x, ev[j].y, ev[j].z, ev[j].w};
+      uint32_t ow[4], tw[4];
+#pragma unroll
+      for (int w = 0; w < 4; ++w) {
+        const __nv_bfloat162 x2 = as_bf162(xw[w]), e2 = as_bf162(ew[w]);
+        ow[w] = as_u32(__hadd2_rn(__hmul2_rn(ca2, x2), __hmul2_rn(cb2, e2)));
+        tw[w] = as_u32(__hsub2_rn(e2, x2));
+      }
+      st_stream(xt + v, make_uint4(ow[0], ow[1], ow[2], ow[3]));
+      if (tg) st_stream(tg + v, make_uint4(tw[0], tw[1], tw[2], tw[3]));
+      if (no) st_stream(no + v, ev[j]);
+    }
+    v0 += stride;
+    if (v0 - (int)threadIdx.x >= nvec) break;                // block-uniform exit
+    fetch();
+    generate();
   }
 }
 
@@ -190,7 +210,12 @@ int launch_noise(NoiseParams p, int dtype, cudaStream_t st) {
                       (!p.noise_out || aligned16(p.noise_out));
   if (vec_ok) {
     const int64_t nvec = p.chw / 8;
-    p.blocks_per_sample = (int)((nvec + kThreads * kUnroll - 1) / (kThreads * kUnroll));
+    YAT_REQUIRE(nvec < (1ll << 30), YAT_ERR_UNSUPPORTED, "noise: chw=%lld too large", (long long)p.chw);
+    // enough blocks to fill the machine (148 SMs x 8 resident), each looping over its sample's
+    // tiles so the per-sample scalar prologue is paid once per block
+    const int tiles = (int)((nvec + kThreads * kUnroll - 1) / (kThreads * kUnroll));
+    const int want = (kNumSMs * 8 + p.B - 1) / p.B;
+    p.blocks_per_sample = tiles < want ? tiles : want;
     const int64_t grid = (int64_t)p.B * p.blocks_per_sample;
     YAT_REQUIRE(grid < (1ll << 31), YAT_ERR_UNSUPPORTED, "noise: grid too large (%lld blocks)", (long long)grid);
     if (gen) noise_bf16_kernel<MODE, true><<<(unsigned)grid, kThreads, 0, st>>>(p);
