@@ -9,17 +9,24 @@
 // (batch b, group of 4 heads) = a 128-column stripe; it is streamed in 128-token tiles of
 // [2 halves][128 tokens][64 cols] (two SWIZZLE_128B TMA boxes, 32 KB) through one shared-memory ring:
 //   K0 V0 K1 V1 ... | Q0 Q1 ...         (3 * ceil(N/128) tiles per item; O tiles leave from the Q slot)
-// The grid is persistent (one CTA per SM, 1 item at a time, loads run ahead across items).
+// The grid is persistent (one CTA per SM, loads run ahead across items).
 //
-// Roles (320 threads): warp 0 = TMA producer, warp 1 = tcgen05 issuer, warps 2..9 = transform/epilogue.
+// Roles (352 threads):
+//   warp 0      TMA producer
+//   warp 1      tcgen05 issuer (one thread)
+//   warps 2-5   transform/epilogue group 0   } the two groups own alternate tiles, so the ReLU pass of
+//   warps 6-9   transform/epilogue group 1   } tile t+1 overlaps the MMA + epilogue of tile t
+//   warp 10     TMA-store warp: O tile out, then the slot goes back to the producer
+//
 //   phase 1  transform: relu(K) in place (+ fp32 column sums -> Ks)     MMA1: D1[128x128] += relu(K)^T V
 //            (A and B both MN-major straight from the TMA tiles; the four 32x32 diagonal blocks of D1
 //             are the per-head K^T V, the off-diagonal blocks are discarded — the kernel is HBM-bound)
-//   build    D1 diagonal -> registers -> bf16 hi + bf16 lo split -> smem B operand (so the second
-//            contraction keeps ~fp32 accuracy: Q·hi + Q·lo)
-//   phase 2  transform: relu(Q) in place + den = relu(Q)·Ks (fp32, CUDA cores)
-//            MMA2 per head: D2[128 tokens x 32] = relu(Q_h) · KV_h   (K-major A, MN-major B)
-//            epilogue: TMEM -> registers, divide, bf16, swizzled smem (the Q slot), TMA store.
+//   build    (group 0) D1 diagonal -> registers -> bf16 hi + bf16 lo split -> smem B operand
+//            [32 x 48] per head: columns 0..31 = KV_h, column 32 = Ks_h, rest 0.  hi + lo keeps the
+//            second contraction at ~fp32 accuracy (the reference does both matmuls in fp32).
+//   phase 2  transform: relu(Q) in place          MMA2 per head: D2[128 x 48] = relu(Q_h) [KV_h | Ks_h]
+//            (K-major A, MN-major B): columns 0..31 are the numerator, column 32 the normaliser
+//            epilogue: TMEM -> registers, divide, bf16, swizzled smem (the Q slot) -> store warp.
 // Rows beyond N and heads beyond H are zero-filled by TMA on load and clipped on store.
 #include "common.cuh"
 #include "sm100.cuh"
@@ -33,27 +40,30 @@ constexpr int kHeadsPerItem = 4;
 constexpr int kTile = 128;                       // tokens per tile
 constexpr int kHalfBytes = kTile * 128;          // [128 tokens][64 cols] bf16
 constexpr int kSlotBytes = 2 * kHalfBytes;       // 32 KB
-constexpr int kStages = 5;
-constexpr int kEpiWarps = 8;
+constexpr int kStages = 6;
+constexpr int kGroups = 2, kGroupWarps = 4;
+constexpr int kEpiWarps = kGroups * kGroupWarps;
 constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kThreads = 64 + kEpiThreads;
-constexpr int kTmemCols = 512;                   // D1 [0,128) + D2 double buffer [128,384)
-constexpr int kBmatBytes = 2048;                 // one 32x32 bf16 B operand
+constexpr int kStoreWarp = 2 + kEpiWarps;
+constexpr int kThreads = 32 * (kStoreWarp + 1);
+constexpr int kNB = 48;                          // N of the phase-2 MMA: 32 KV columns + Ks + padding to 16
+constexpr int kD2Cols = kHeadsPerItem * kNB;     // 192 TMEM columns per D2 buffer
+constexpr int kTmemCols = 512;                   // D1 [0,128) + D2[group] [128 + 192 g, +192)
+constexpr int kBmatBytes = kD * kNB * 2;         // one [32 x 48] bf16 B operand
 
 struct FwdSmem {
   uint8_t slots[kStages][kSlotBytes];                       // 1024-aligned
   uint8_t bmat[kHeadsPerItem][2][kBmatBytes];               // [head][hi|lo], MN-major no-swizzle
-  float den[2][kTile][kHeadsPerItem];
-  float ks[kHeadsPerItem * kD];
   float red[kEpiWarps][kHeadsPerItem * kD];
-  uint64_t full[kStages], ready[kStages], empty[kStages];
-  uint64_t d1_full, b_ready, d2_full[2], d2_empty[2];
+  uint64_t full[kStages], ready[kStages], empty[kStages], o_ready[kStages];
+  uint64_t d1_full, b_ready, d2_full[kGroups], d2_empty[kGroups];
   uint32_t tmem_base;
 };
 constexpr int kFwdSmemBytes = (int)sizeof(FwdSmem) + 1024;
+static_assert(kFwdSmemBytes <= 232448, "forward shared memory exceeds the 227 KB per-CTA limit");
 
 constexpr uint32_t kIdesc1 = make_idesc_bf16(128, 128, 1, 1);  // relu(K)^T V : A, B MN-major
-constexpr uint32_t kIdesc2 = make_idesc_bf16(128, 32, 0, 1);   // relu(Q) KV  : A K-major, B MN-major
+constexpr uint32_t kIdesc2 = make_idesc_bf16(128, kNB, 0, 1);  // relu(Q) [KV|Ks] : A K-major, B MN-major
 
 __device__ __forceinline__ uint4 relu8(uint4 v) {
   const __nv_bfloat162 z = __float2bfloat162_rn(0.f);
@@ -80,18 +90,23 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
       mbar_init(smem_u32(&S.full[s]), 1);
-      mbar_init(smem_u32(&S.ready[s]), kEpiWarps);
+      mbar_init(smem_u32(&S.ready[s]), kGroupWarps);
       mbar_init(smem_u32(&S.empty[s]), 1);
+      mbar_init(smem_u32(&S.o_ready[s]), kGroupWarps);
     }
     mbar_init(smem_u32(&S.d1_full), 1);
-    mbar_init(smem_u32(&S.b_ready), kEpiWarps);
-    for (int i = 0; i < 2; ++i) {
+    mbar_init(smem_u32(&S.b_ready), kGroupWarps);
+    for (int i = 0; i < kGroups; ++i) {
       mbar_init(smem_u32(&S.d2_full[i]), 1);
-      mbar_init(smem_u32(&S.d2_empty[i]), kEpiWarps);
+      mbar_init(smem_u32(&S.d2_empty[i]), kGroupWarps);
     }
     fence_barrier_init();
     tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v); tma_prefetch_desc(&tm_o);
   }
+  // the padding columns of the B operands stay zero for the whole kernel
+  for (int i = threadIdx.x; i < (int)sizeof(S.bmat) / 16; i += kThreads)
+    reinterpret_cast<uint4*>(&S.bmat[0][0][0])[i] = make_uint4(0, 0, 0, 0);
+  fence_proxy_async();
   if (warp == 1) {
     tmem_alloc(smem_u32(&S.tmem_base), kTmemCols);
     tmem_relinquish();
@@ -125,8 +140,9 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
   } else if (warp == 1) {
     // ======================= tcgen05 issuer =======================
     if (lane == 0) {
-      uint32_t it = 0, qt = 0, item_iter = 0;
-      uint32_t ready_ph = 0;  // per-slot parity of `ready` (only K and Q uses of a slot complete a phase)
+      uint32_t it = 0, item_iter = 0;
+      uint32_t ready_ph = 0;        // per-slot parity of `ready` (only K and Q uses of a slot complete a phase)
+      uint32_t d2_use[kGroups] = {0, 0};
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++item_iter) {
         // ---- phase 1: D1 += relu(K)^T V over all token tiles
         for (int t = 0; t < n_tiles; ++t, it += 2) {
@@ -150,18 +166,19 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
         tc_commit(smem_u32(&S.d1_full));
         mbar_wait(smem_u32(&S.b_ready), item_iter & 1);
         tc_fence_after();
-        // ---- phase 2: D2[buf] = relu(Q_h) (KV_h hi + KV_h lo), per head
-        for (int t = 0; t < n_tiles; ++t, ++it, ++qt) {
+        // ---- phase 2: D2[group] = relu(Q_h) ([KV_h|Ks_h] hi + lo), per head
+        for (int t = 0; t < n_tiles; ++t, ++it) {
           const uint32_t sq = it % kStages;
-          const uint32_t buf = qt & 1, pb = (qt >> 1) & 1;
+          const uint32_t g = t & 1, pb = d2_use[g] & 1;
+          ++d2_use[g];
           mbar_wait(smem_u32(&S.ready[sq]), (ready_ph >> sq) & 1);
           ready_ph ^= 1u << sq;
-          mbar_wait(smem_u32(&S.d2_empty[buf]), pb ^ 1);
+          mbar_wait(smem_u32(&S.d2_empty[g]), pb ^ 1);
           tc_fence_after();
           const uint32_t qa = smem_u32(&S.slots[sq][0]);
 #pragma unroll
           for (int h = 0; h < kHeadsPerItem; ++h) {
-            const uint32_t d2 = tmem + 128 + buf * 128 + h * kD;
+            const uint32_t d2 = tmem + 128 + g * kD2Cols + h * kNB;
             const uint32_t qh = qa + (h >> 1) * kHalfBytes + (h & 1) * 64;  // 32 columns = 64 B inside the 128 B row
 #pragma unroll
             for (int hl = 0; hl < 2; ++hl) {
@@ -177,52 +194,77 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
               }
             }
           }
-          tc_commit(smem_u32(&S.d2_full[buf]));
+          tc_commit(smem_u32(&S.d2_full[g]));
         }
       }
     }
+  } else if (warp == kStoreWarp) {
+    // ======================= TMA-store warp =======================
+    if (lane == 0) {
+      uint32_t it = 0, o_ph = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int b = item / groups, c0 = (item % groups) * (kHeadsPerItem * kD);
+        it += 2 * n_tiles;
+        for (int t = 0; t < n_tiles; ++t, ++it) {
+          const uint32_t sq = it % kStages;
+          mbar_wait(smem_u32(&S.o_ready[sq]), (o_ph >> sq) & 1);
+          o_ph ^= 1u << sq;
+          const uint32_t src = smem_u32(&S.slots[sq][0]);
+          tma_store_3d(&tm_o, src, c0, t * kTile, b);
+          tma_store_3d(&tm_o, src + kHalfBytes, c0 + 64, t * kTile, b);
+          tma_store_commit();
+          tma_store_wait_read<0>();                       // smem has been read: the slot can be refilled
+          mbar_arrive(smem_u32(&S.empty[sq]));
+        }
+      }
+      tma_store_wait_all<0>();
+    }
   } else {
-    // ======================= transform + epilogue warps =======================
-    const int te = threadIdx.x - 64;          // 0..255
-    const int we = te >> 5;                   // 0..7
-    const int cc = te & 15;                   // logical 16-byte chunk column of the 256-byte item row
-    const int rbase = te >> 4;                // 0..15; rows rbase + 16 i
+    // ======================= transform + epilogue groups =======================
+    const int we = warp - 2;                  // 0..7
+    const int grp = we >> 2;                  // tiles with (t & 1) == grp belong to this group
+    const int tg = threadIdx.x - 64 - grp * 128;   // 0..127 inside the group
+    const int cc = tg & 15;                   // logical 16-byte chunk column of the 256-byte item row
+    const int rbase = tg >> 4;                // 0..7; rows rbase + 8 i
     const int half = cc >> 3, chunk = cc & 7;
     const int quad = warp & 3;                // TMEM lane quadrant this warp may access
-    const int colhalf = we >> 2;              // which 64-column half of the item this warp finishes
     const int row = quad * 32 + lane;         // token row in the tile (TMEM lane)
-    uint32_t it = 0, qt = 0, item_iter = 0;
-    int pending_slot = -1;                    // O tile whose TMA store may still be reading smem (te == 0)
+    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    uint32_t it = 0, item_iter = 0, d2_use = 0;
 
-    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++item_iter) {
-      const int b = item / groups, c0 = (item % groups) * (kHeadsPerItem * kD);
-      // ---- phase 1: relu(K) in place, column sums
-      float csum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-      for (int t = 0; t < n_tiles; ++t, it += 2) {
-        const uint32_t sk = it % kStages, pk = (it / kStages) & 1;
-        mbar_wait(smem_u32(&S.full[sk]), pk);
-        uint8_t* base = &S.slots[sk][half * kHalfBytes];
+    // relu in place over this group's share of a [2][128][64] tile; returns nothing, adds column sums
+    auto relu_tile = [&](uint32_t slot, float* csum) {
+      uint8_t* base = &S.slots[slot][half * kHalfBytes];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int r = rbase + 16 * i;
-          uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
-          const uint4 v = relu8(*p);
-          *p = v;
+      for (int i = 0; i < 16; ++i) {
+        const int r = rbase + 8 * i;
+        uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
+        const uint4 v = relu8(*p);
+        *p = v;
+        if (csum) {
           float f[8];
           unpack8f(v, f);
 #pragma unroll
           for (int j = 0; j < 8; ++j) csum[j] += f[j];
         }
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&S.ready[sk]));  // (V needs no transform: the issuer waits on `full`)
-        // Observe the V slot's phase as well: a parity wait is only sound if the waiter sees every phase
-        // of the barrier in order.  Skipping the V phases let these warps reach "K in the same slot, 5 loads
-        // later" while the V load was still in flight, where the parity of the wanted phase equals the
-        // parity of the last completed one and the wait falls through (seen as a rare hang on B200).
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&S.ready[slot]));
+    };
+
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++item_iter) {
+      // ---- phase 1: relu(K) in place, column sums.  Every `full` phase is observed in order by both
+      // groups (a parity wait is only sound if the waiter sees every phase of the barrier); only the
+      // owner touches the tile.  V needs no transform: the issuer waits on its `full`.
+      float csum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      for (int t = 0; t < n_tiles; ++t, it += 2) {
+        const uint32_t sk = it % kStages, pk = (it / kStages) & 1;
+        mbar_wait(smem_u32(&S.full[sk]), pk);
+        if ((t & 1) == grp) relu_tile(sk, csum);
         mbar_wait(smem_u32(&S.full[(it + 1) % kStages]), ((it + 1) / kStages) & 1);
       }
-      // Ks[col] = sum over threads sharing the chunk column
+      // Ks partials: lanes l and l^16 share the chunk column
 #pragma unroll
       for (int j = 0; j < 8; ++j) csum[j] += __shfl_xor_sync(0xffffffffu, csum[j], 16);
       if (lane < 16) {
@@ -230,18 +272,15 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
         for (int j = 0; j < 8; ++j) S.red[we][cc * 8 + j] = csum[j];
       }
       named_bar_sync(1, kEpiThreads);
-      if (te < kHeadsPerItem * kD) {
-        float s = 0.f;
+      if (grp == 0) {
+        // ---- build the B operands of phase 2: head `quad`, k row `lane`
+        float ksum = 0.f;
 #pragma unroll
-        for (int w = 0; w < kEpiWarps; ++w) s += S.red[w][te];
-        S.ks[te] = s;
-      }
-      // ---- build the B operands of phase 2 from the diagonal blocks of D1
-      mbar_wait(smem_u32(&S.d1_full), item_iter & 1);
-      tc_fence_after();
-      if (we < 4) {
+        for (int w = 0; w < kEpiWarps; ++w) ksum += S.red[w][quad * kD + lane];
+        mbar_wait(smem_u32(&S.d1_full), item_iter & 1);
+        tc_fence_after();
         uint32_t r[32];
-        tmem_ld32(tmem + ((uint32_t)(quad * 32) << 16) + quad * kD, r);  // KV_head[dk = lane][dv = 0..31]
+        tmem_ld32(tmem + lane_base + quad * kD, r);  // KV_head[dk = lane][dv = 0..31]
         tmem_ld_wait();
         uint8_t* bh = &S.bmat[quad][0][0];
         uint8_t* bl = &S.bmat[quad][1][0];
@@ -258,87 +297,56 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
           *reinterpret_cast<uint4*>(bh + g * 512 + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
           *reinterpret_cast<uint4*>(bl + g * 512 + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
         }
-        fence_proxy_async();
-      }
-      tc_fence_before();
-      named_bar_sync(1, kEpiThreads);  // ks visible, D1 drained, bmat written
-      if (lane == 0) mbar_arrive(smem_u32(&S.b_ready));
-      float ksr[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) ksr[j] = S.ks[cc * 8 + j];
-
-      // ---- phase 2
-      for (int t = 0; t < n_tiles; ++t, ++it, ++qt) {
-        const uint32_t sq = it % kStages, pq = (it / kStages) & 1;
-        const uint32_t buf = qt & 1, pb = (qt >> 1) & 1;
-        mbar_wait(smem_u32(&S.full[sq]), pq);
-        uint8_t* base = &S.slots[sq][half * kHalfBytes];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int r = rbase + 16 * i;
-          uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
-          const uint4 v = relu8(*p);
-          *p = v;
-          float f[8], d = 0.f;
-          unpack8f(v, f);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) d = fmaf(f[j], ksr[j], d);
-          d += __shfl_xor_sync(0xffffffffu, d, 1);
-          d += __shfl_xor_sync(0xffffffffu, d, 2);
-          if ((cc & 3) == 0) S.den[qt & 1][r][cc >> 2] = d;
+        {  // column 32 = Ks (mn-group 4, first element); the other 7 elements of the chunk stay zero
+          const uint32_t khi = pack_bf16(ksum, 0.f);
+          const uint32_t klo = pack_bf16(ksum - bf16_lo(khi), 0.f);
+          *reinterpret_cast<uint4*>(bh + 4 * 512 + off) = make_uint4(khi, 0, 0, 0);
+          *reinterpret_cast<uint4*>(bl + 4 * 512 + off) = make_uint4(klo, 0, 0, 0);
         }
         fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&S.ready[sq]));
-        named_bar_sync(1, kEpiThreads);  // den visible to the epilogue mapping
-
-        mbar_wait(smem_u32(&S.d2_full[buf]), pb);
-        tc_fence_after();
-        uint32_t acc[2][32];
-        const uint32_t taddr = tmem + ((uint32_t)(quad * 32) << 16) + 128 + buf * 128 + colhalf * 64;
-        tmem_ld32(taddr, acc[0]);
-        tmem_ld32(taddr + 32, acc[1]);
-        tmem_ld_wait();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&S.d2_empty[buf]));
+        if (lane == 0) mbar_arrive(smem_u32(&S.b_ready));
+      }
 
-        uint8_t* orow = &S.slots[sq][colhalf * kHalfBytes + row * 128];
+      // ---- phase 2
+      for (int t = 0; t < n_tiles; ++t, ++it) {
+        const uint32_t sq = it % kStages, pq = (it / kStages) & 1;
+        mbar_wait(smem_u32(&S.full[sq]), pq);
+        if ((t & 1) != grp) continue;
+        relu_tile(sq, nullptr);
+
+        mbar_wait(smem_u32(&S.d2_full[grp]), d2_use & 1);
+        ++d2_use;
+        tc_fence_after();
+        const uint32_t d2 = tmem + lane_base + 128 + grp * kD2Cols;
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-          const float rden = __frcp_rn(S.den[qt & 1][row][colhalf * 2 + hh] + 1e-15f);
+        for (int h = 0; h < kHeadsPerItem; ++h) {
+          uint32_t acc[32], dn;
+          tmem_ld32(d2 + h * kNB, acc);
+          tmem_ld1(d2 + h * kNB + kD, dn);
+          tmem_ld_wait();
+          const float rden = __frcp_rn(__uint_as_float(dn) + 1e-15f);
+          uint8_t* orow = &S.slots[sq][(h >> 1) * kHalfBytes + row * 128];
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             uint32_t w[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j)
-              w[j] = pack_bf16(__uint_as_float(acc[hh][g * 8 + 2 * j]) * rden,
-                               __uint_as_float(acc[hh][g * 8 + 2 * j + 1]) * rden);
-            const int c = hh * 4 + g;
+              w[j] = pack_bf16(__uint_as_float(acc[g * 8 + 2 * j]) * rden, __uint_as_float(acc[g * 8 + 2 * j + 1]) * rden);
+            const int c = (h & 1) * 4 + g;
             *reinterpret_cast<uint4*>(orow + ((c ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
           }
         }
+        tc_fence_before();
         fence_proxy_async();
-        named_bar_sync(1, kEpiThreads);
-        if (te == 0) {
-          const uint32_t src = smem_u32(&S.slots[sq][0]);
-          tma_store_3d(&tm_o, src, c0, t * kTile, b);
-          tma_store_3d(&tm_o, src + kHalfBytes, c0 + 64, t * kTile, b);
-          tma_store_commit();
-          if (pending_slot >= 0) {  // the previous tile's store has finished reading its slot
-            tma_store_wait_read<1>();
-            mbar_arrive(smem_u32(&S.empty[pending_slot]));
-          }
-          pending_slot = (int)sq;
-          if (t == n_tiles - 1) {   // item boundary: the next Q tile is 2*n_tiles loads away, release now
-            tma_store_wait_read<0>();
-            mbar_arrive(smem_u32(&S.empty[pending_slot]));
-            pending_slot = -1;
-          }
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(smem_u32(&S.d2_empty[grp]));
+          mbar_arrive(smem_u32(&S.o_ready[sq]));
         }
       }
     }
-    if (te == 0) tma_store_wait_all<0>();
   }
 
   tc_fence_before();
