@@ -5,7 +5,7 @@
 
 One "step" = one pass of the per-step training hot path over one bucket batch: pad/mask of the text
 embeddings, fused noising, SANA-1.6B forward (tcgen05 linear attention inside), fused loss, backward
-(gradient checkpointing on, like train_sana.py:63), DDP gradient all-reduce (N>1), grad-norm clip,
+(gradient checkpointing only if the activations would not fit in HBM), DDP gradient all-reduce (N>1), grad-norm clip,
 AdamW.  Workload = BASELINE.json configs[1]: 32x32x32 DC-AE latents, batch 16 per GPU, bf16.
 
 Own arm prints ONE JSON line on rank 0 with
@@ -46,6 +46,8 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=16)
     ap.add_argument("--debug-linattn", default=None, choices=["simt"],
                     help="debug only: run linear attention on the CUDA-core restatement (flagged in config)")
+    ap.add_argument("--ckpt", default="auto", choices=["auto", "on", "off"],
+                    help="gradient checkpointing: auto = only if the activations do not fit in HBM (default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--kernels-only", action="store_true",
                     help="debug only: print the stand-alone kernel roofline table and exit (not a bench line)")
@@ -249,6 +251,10 @@ def _algo_bytes(name, B, chw, N, C):
         "loss_fused": 6 * elems,                 # read pred 2 + x0 2, write dpred 2 (eps regenerated)
         "linattn_fwd_sm100": 8 * B * N * C,      # q,k,v in + o out, bf16
         "linattn_bwd_sm100": 14 * B * N * C,     # q,k,v,do in + dq,dk,dv out, bf16 (o is recomputed, not read)
+        "ln_modulate_fwd": 4 * B * N * C,        # x in, y out
+        "ln_modulate_bwd": 6 * B * N * C,        # x, dy in, dx out (the column pass re-reads x, dy: counted as waste)
+        "gate_residual_fwd": 6 * B * N * C,      # res, y in, out
+        "gate_residual_bwd": 6 * B * N * C,      # dout, y in, dy out
     }.get(name)
 
 
@@ -296,6 +302,22 @@ def _standalone_kernels(device, pk):
     B, N, H = 16, 1024, 70
     C = H * 32
     q, k, v, do = [torch.randn((B, N, C), device=device, dtype=torch.bfloat16) for _ in range(4)]
+    from yat_b200.block_ops import gate_residual, ln_modulate
+    mod = torch.randn((B, 6, C), device=device, dtype=torch.bfloat16).requires_grad_(True)
+    sh, sc, gt = mod.chunk(6, dim=1)[:3]
+    ms = timeit(lambda: ln_modulate(q, sc.detach(), sh.detach()))
+    entry("ln_modulate_fwd", 4 * B * N * C, ms, [B, N, C])
+    ms = timeit(lambda: gate_residual(q, k, gt.detach()))
+    entry("gate_residual_fwd", 6 * B * N * C, ms, [B, N, C])
+    xg = q.clone().requires_grad_(True)
+    y1 = ln_modulate(xg, sc, sh)
+    ms = timeit(lambda: torch.autograd.grad(y1, (xg, mod), do, retain_graph=True))
+    entry("ln_modulate_bwd", 6 * B * N * C, ms, [B, N, C])
+    yg = k.clone().requires_grad_(True)
+    y2 = gate_residual(q, yg, gt)
+    ms = timeit(lambda: torch.autograd.grad(y2, (yg, mod), do, retain_graph=True))
+    entry("gate_residual_bwd", 6 * B * N * C, ms, [B, N, C])
+    del xg, yg, y1, y2, mod
     ms = timeit(lambda: sana_linear_attention(q, k, v, H))
     entry("linattn_fwd_sm100", 8 * B * N * C, ms, [B, N, C], flops=4 * 32 * 33 * N * H * B)
     qg, kg, vg = [t.clone().requires_grad_(True) for t in (q, k, v)]
@@ -331,6 +353,7 @@ def run_own_arm(args):
     params.learning_rate = 1e-5
     params.weight_decay = 0.0
     params.steps = args.steps
+    params.gradient_checkpointing = {"auto": "auto", "on": True, "off": False}[args.ckpt]
     cwd = os.getcwd()
     import tempfile
     tmp = tempfile.mkdtemp(prefix="yat_bench_")
@@ -440,7 +463,7 @@ def run_own_arm(args):
         "config": {"workload": (WORKLOAD if args.model == "sana_1600m_1024" else f"DEBUG {args.model}")
                    + (f" DEBUG linattn={args.debug_linattn}" if args.debug_linattn else ""),
                    "global_batch": world * B, "parallelism": f"dp{world}", "optimizer": "AdamW bf16 (fused)",
-                   "gradient_checkpointing": True,
+                   "gradient_checkpointing": bool(trainer.pipe.transformer.gradient_checkpointing),
                    "l2": "no explicit flush: one step streams ~3.2 GB of weights + >10 GB of activations (>> 126 MB L2)"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                 "ms_per_step": ms_e2e / args.steps},

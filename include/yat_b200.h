@@ -18,6 +18,8 @@
  *   yat_repa_cos          common/repa.py:137-154 (re-specified)
  *   yat_linattn_fwd/bwd   diffusers SanaLinearAttnProcessor2_0, reached from
  *                         utils/patch_sana_attention_layers.py:94
+ *   yat_ln_modulate_*     utils/patch_sana_attention_layers.py:84-90,104-105 (+ norm_out)
+ *   yat_gate_residual_*   utils/patch_sana_attention_layers.py:95,113
  *   yat_pad_embeddings    train_sana.py:167-179  train_pixart_sigma.py:158-169
  *   yat_bucket_assign     common/trainer.py:109-120  common/bucket_sampler.py:314-322
  */
@@ -126,6 +128,30 @@ int yat_linattn_fwd_simt(const void* q, const void* k, const void* v, int B, int
                          void* o, void* stream);
 int yat_linattn_bwd_simt(const void* q, const void* k, const void* v, const void* dout,
                          int B, int N, int H, int D, void* dq, void* dk, void* dv, void* stream);
+
+/* ---- (next, N1) fused neighbours of the attention / feed-forward sub-layers -----------------
+ * SANA block body, utils/patch_sana_attention_layers.py:84-95,104-113 (adaLN-single modulate, gate,
+ * residual) and SanaModulatedNorm (norm_out).  x,y,res,out,dx,dy,dout: [B, N, C] bf16 token-major;
+ * scale/shift/gate: per-sample rows, element (b, c) at ptr[b * mod_batch_stride + c] (bf16; they are
+ * chunks of one [B, 6, C] tensor); C % 8 == 0, C <= 4096.
+ *   ln_modulate     y   = LayerNorm(x; eps, no affine) * (1 + scale_b) + shift_b
+ *                   fwd optionally saves mean / rstd fp32 [B*N] for the backward
+ *                   bwd: dx, dscale [B, C] bf16 = sum_n dy * xhat, dshift [B, C] bf16 = sum_n dy
+ *   gate_residual   out = res + gate_b * y
+ *                   bwd: dy = gate_b * dout, dgate [B, C] bf16 = sum_n dout * y  (dres == dout)
+ * workspace: yat_block_workspace_bytes(B, N, C) bytes of device scratch (split partial sums; the
+ * reduction order is fixed, results are run-to-run identical).
+ */
+int64_t yat_block_workspace_bytes(int B, int N, int C);
+int yat_ln_modulate_fwd(const void* x, const void* scale, const void* shift, int64_t mod_batch_stride,
+                        int B, int N, int C, float eps, void* y, float* mean, float* rstd, void* stream);
+int yat_ln_modulate_bwd(const void* x, const void* dy, const void* scale, int64_t mod_batch_stride,
+                        const float* mean, const float* rstd, int B, int N, int C,
+                        void* dx, void* dscale, void* dshift, void* workspace, void* stream);
+int yat_gate_residual_fwd(const void* res, const void* y, const void* gate, int64_t mod_batch_stride,
+                          int B, int N, int C, void* out, void* stream);
+int yat_gate_residual_bwd(const void* dout, const void* y, const void* gate, int64_t mod_batch_stride,
+                          int B, int N, int C, void* dy, void* dgate, void* workspace, void* stream);
 
 /* ---- (next) ragged text-embedding pad + mask -------------------------------------------
  *   packed [sum L_i, E] bf16, offsets int32 [B+1] -> padded [B, Lmax, E] bf16 (zero fill),

@@ -1,0 +1,137 @@
+"""GPU parity of the fused modulate / gate / residual kernels (yat_ln_modulate_*, yat_gate_residual_*)
+against the reference's op-by-op expressions (utils/patch_sana_attention_layers.py:84-95,104-113)
+evaluated in fp32/fp64 by torch.  Tolerance: bf16 outputs and gradients <= 2e-2 relative by spec
+(asserted much tighter: the kernels compute in fp32 and round once)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    a, b = a.double().cpu(), b.double().cpu()
+    return ((a - b).norm() / b.norm().clamp_min(1e-30)).item()
+
+
+def _inputs(B, N, C, seed, dev):
+    g = torch.Generator().manual_seed(seed)
+    x = (torch.randn((B, N, C), generator=g) * 1.5 + 0.3).to(torch.bfloat16).to(dev)
+    y = torch.randn((B, N, C), generator=g).to(torch.bfloat16).to(dev)
+    mod = (torch.randn((B, 6, C), generator=g) * 0.5).to(torch.bfloat16).to(dev)   # [B, 6, C]: chunks are strided views
+    dout = torch.randn((B, N, C), generator=g).to(torch.bfloat16).to(dev)
+    return x, y, mod, dout
+
+
+def _ref_ln_modulate(x, scale, shift, eps):
+    xd = x.double()
+    xh = torch.nn.functional.layer_norm(xd, (x.shape[-1],), eps=eps)
+    return xh * (1 + scale.double()) + shift.double()
+
+
+@pytest.mark.parametrize("B,N,C", [(2, 256, 128), (16, 1024, 2240), (3, 100, 2240), (1, 7, 64), (2, 33, 4096)])
+def test_ln_modulate_forward_backward(cuda, B, N, C):
+    from yat_b200.block_ops import ln_modulate
+    x, _, mod, dout = _inputs(B, N, C, 1, cuda)
+    shift, scale = mod.chunk(6, dim=1)[0], mod.chunk(6, dim=1)[1]
+    xg = x.clone().requires_grad_(True)
+    modg = mod.clone().requires_grad_(True)
+    sh, sc = modg.chunk(6, dim=1)[0], modg.chunk(6, dim=1)[1]
+    y = ln_modulate(xg, sc, sh, 1e-6)
+    y.backward(dout)
+
+    xr = x.double().requires_grad_(True)
+    modr = mod.double().requires_grad_(True)
+    yr = _ref_ln_modulate(xr, modr.chunk(6, dim=1)[1], modr.chunk(6, dim=1)[0], 1e-6)
+    yr.backward(dout.double())
+    assert _rel(y, yr) < 4e-3
+    assert _rel(xg.grad, xr.grad) < 5e-3
+    assert _rel(modg.grad[:, :2], modr.grad[:, :2]) < 5e-3
+    assert torch.count_nonzero(modg.grad[:, 2:]) == 0
+    # run-to-run identical (fixed reduction order)
+    xg2 = x.clone().requires_grad_(True)
+    modg2 = mod.clone().requires_grad_(True)
+    ln_modulate(xg2, modg2.chunk(6, dim=1)[1], modg2.chunk(6, dim=1)[0], 1e-6).backward(dout)
+    assert torch.equal(xg2.grad, xg.grad) and torch.equal(modg2.grad, modg.grad)
+    del shift, scale
+
+
+def test_ln_modulate_matches_reference_expression_in_bf16(cuda):
+    """Against the reference's own bf16 op chain (LayerNorm -> *(1+scale) -> +shift, each rounding to bf16):
+    the fused kernel rounds once, so the two agree to bf16 rounding noise."""
+    from yat_b200.block_ops import ln_modulate
+    x, _, mod, _ = _inputs(4, 512, 2240, 2, cuda)
+    shift, scale = mod.chunk(6, dim=1)[0], mod.chunk(6, dim=1)[1]
+    ref = torch.nn.functional.layer_norm(x, (2240,), eps=1e-6) * (1 + scale) + shift
+    got = ln_modulate(x, scale, shift, 1e-6)
+    assert _rel(got, ref) < 8e-3
+    exact = _ref_ln_modulate(x, scale, shift, 1e-6)
+    assert _rel(got, exact) <= _rel(ref, exact)   # and it is the more accurate of the two
+
+
+@pytest.mark.parametrize("B,N,C", [(2, 256, 128), (16, 1024, 2240), (3, 100, 2240), (1, 7, 64)])
+def test_gate_residual_forward_backward(cuda, B, N, C):
+    from yat_b200.block_ops import gate_residual
+    x, y, mod, dout = _inputs(B, N, C, 3, cuda)
+    xg, yg = x.clone().requires_grad_(True), y.clone().requires_grad_(True)
+    modg = mod.clone().requires_grad_(True)
+    out = gate_residual(xg, yg, modg.chunk(6, dim=1)[2])
+    out.backward(dout)
+    xr, yr = x.double().requires_grad_(True), y.double().requires_grad_(True)
+    modr = mod.double().requires_grad_(True)
+    outr = xr + modr.chunk(6, dim=1)[2] * yr
+    outr.backward(dout.double())
+    assert _rel(out, outr) < 4e-3
+    assert torch.equal(xg.grad, dout)                       # the residual branch passes the gradient through
+    assert _rel(yg.grad, yr.grad) < 4e-3
+    assert _rel(modg.grad[:, 2], modr.grad[:, 2]) < 5e-3
+    assert torch.count_nonzero(modg.grad[:, :2]) == 0 and torch.count_nonzero(modg.grad[:, 3:]) == 0
+
+
+def test_block_ops_argument_errors(cuda):
+    from yat_b200.block_ops import gate_residual, ln_modulate
+    x = torch.zeros((2, 8, 64), dtype=torch.bfloat16, device=cuda)
+    m = torch.zeros((2, 1, 64), dtype=torch.bfloat16, device=cuda)
+    with pytest.raises(ValueError):
+        ln_modulate(x.float(), m, m)
+    with pytest.raises(ValueError):
+        ln_modulate(x, m[:, :, :32], m)
+    with pytest.raises(ValueError):
+        gate_residual(x, x[:, :4], m)
+    with pytest.raises(ValueError):
+        ln_modulate(x.cpu(), m.cpu(), m.cpu())
+    with pytest.raises(ValueError):
+        ln_modulate(torch.zeros((2, 8, 60), dtype=torch.bfloat16, device=cuda),
+                    torch.zeros((2, 1, 60), dtype=torch.bfloat16, device=cuda),
+                    torch.zeros((2, 1, 60), dtype=torch.bfloat16, device=cuda))
+
+
+def test_fused_block_matches_reference_block(cuda):
+    """A whole SanaTransformerBlock: fused block ops vs the reference's op-by-op expressions, same
+    weights.  Truth = the op-by-op block in fp32; the fused bf16 block must be at least as close to
+    it as the op-by-op bf16 block is (both within the 2e-2 spec on the output)."""
+    from yat_b200.sana_transformer import SanaTransformerBlock
+    torch.manual_seed(0)
+    blk = SanaTransformerBlock(dim=128, num_attention_heads=4, attention_head_dim=32, num_cross_attention_heads=2,
+                               cross_attention_head_dim=64, cross_attention_dim=128, attention_bias=False).to(cuda)
+    B, H, W = 2, 16, 16
+    x = torch.randn((B, H * W, 128), device=cuda).to(torch.bfloat16)
+    enc = torch.randn((B, 40, 128), device=cuda).to(torch.bfloat16)
+    temb = (torch.randn((B, 6 * 128), device=cuda) * 0.3).to(torch.bfloat16)
+
+    def run(impl, dtype):
+        b = SanaTransformerBlock(dim=128, num_attention_heads=4, attention_head_dim=32, num_cross_attention_heads=2,
+                                 cross_attention_head_dim=64, cross_attention_dim=128, attention_bias=False)
+        b.load_state_dict(blk.state_dict())
+        b = b.to(cuda, dtype)
+        b.block_ops = impl
+        xi = x.to(dtype).requires_grad_(True)
+        o = b(xi, None, enc.to(dtype), None, temb.to(dtype), H, W)
+        o.float().square().mean().backward()
+        return o.detach(), xi.grad, b.scale_shift_table.grad, b.attn1.to_q.weight.grad, b.ff.conv_point.weight.grad
+
+    truth = run("torch", torch.float32)
+    fused = run("sm100", torch.bfloat16)
+    plain = run("torch", torch.bfloat16)
+    assert _rel(fused[0], truth[0]) < 2e-2
+    for f, p, t in zip(fused, plain, truth):
+        assert _rel(f, t) <= 1.25 * _rel(p, t) + 2e-3, (_rel(f, t), _rel(p, t))

@@ -70,6 +70,9 @@ def test_product_model_structure_matches_oracle_model():
     m = PatchedSanaTransformer2DModel(**SANA_CONFIGS["sana_tiny"])
     x = torch.randn(2, 32, 16, 16)
     enc = torch.randn(2, 512, 64)
+    with pytest.raises(ValueError):       # default block ops are the CUDA kernels: no CPU fallback
+        m(x, enc, torch.tensor([1.0, 2.0]))
+    m.set_block_ops("torch")              # op-by-op reference expressions for this CPU structure check
     t = torch.tensor([326.0, 811.0])
     mask = torch.zeros(2, 512, dtype=torch.long)
     mask[0, :20] = 1

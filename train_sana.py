@@ -64,7 +64,11 @@ class SanaModel(Model):
         self.aspect_ratios = {256: ASPECT_RATIO_256_BIN, 512: ASPECT_RATIO_512_BIN,
                               1024: ASPECT_RATIO_1024_BIN}.get(resolution, ASPECT_RATIO_2048_BIN)
         self.model = transformer
-        self.model.enable_gradient_checkpointing()                           # train_sana.py:63
+        # train_sana.py:63 turns gradient checkpointing on unconditionally (a 24-48 GB-card habit); with
+        # 180 GB of HBM3e the saved activations of SANA-1.6B at batch 16 (~50 GB) fit, so "auto" keeps them
+        # and skips the recompute forward.  Numerically identical either way.
+        if self._want_checkpointing(transformer, params):
+            self.model.enable_gradient_checkpointing()
         self.frozen_model = None
         self.patch_size = transformer.config.patch_size
         self._trust_gscale = False
@@ -74,6 +78,22 @@ class SanaModel(Model):
             self.model = RepaModel(transformer, RepaConfig(target_modules=[blk], hidden_shape=[inner]))
         if params.use_preservation:
             self.frozen_model = copy.deepcopy(transformer).requires_grad_(False).eval()
+
+    def _want_checkpointing(self, transformer, params):
+        mode = getattr(params, "gradient_checkpointing", "auto")
+        if mode != "auto":
+            return bool(mode)
+        cfg = transformer.config
+        if self.accelerator.device.type != "cuda":
+            return True
+        tokens = (cfg.sample_size // cfg.patch_size) ** 2
+        inner = cfg.num_attention_heads * cfg.attention_head_dim
+        # ~35 [B, N, C] bf16 tensors are kept per block (projections, attention, the 5x-wide GLUMBConv)
+        need = 35 * params.batch_size * tokens * inner * 2 * cfg.num_layers * 1.25
+        n_params = sum(p.numel() for p in transformer.parameters())
+        need += n_params * 2 * 5 + (8 << 30)                 # weights, grads, 2 Adam moments, DDP buckets, workspace
+        free, _ = torch.cuda.mem_get_info(self.accelerator.device)
+        return need > free
 
     def initialize(self):
         super().initialize()

@@ -23,6 +23,7 @@ from torch import nn
 from torch.utils.checkpoint import checkpoint
 
 from .attention import Attention, AttnProcessor2_0, SanaLinearAttnProcessorB200
+from .block_ops import gate_residual, ln_modulate
 
 
 class Transformer2DModelOutput:
@@ -144,10 +145,13 @@ class SanaModulatedNorm(nn.Module):
     def __init__(self, dim, elementwise_affine=False, eps=1e-6):
         super().__init__()
         self.norm = nn.LayerNorm(dim, elementwise_affine=elementwise_affine, eps=eps)
+        self.block_ops = "sm100"
 
     def forward(self, hidden_states, temb, scale_shift_table):
-        hidden_states = self.norm(hidden_states)
         shift, scale = (scale_shift_table[None] + temb[:, None].to(scale_shift_table.device)).chunk(2, dim=1)
+        if self.block_ops == "sm100" and self.norm.weight is None:
+            return ln_modulate(hidden_states, scale, shift, self.norm.eps)   # one kernel, fp32 math
+        hidden_states = self.norm(hidden_states)
         return hidden_states * (1 + scale) + shift
 
 
@@ -172,6 +176,9 @@ class SanaTransformerBlock(nn.Module):
                                    processor=AttnProcessor2_0())
         self.ff = GLUMBConv(dim, dim, mlp_ratio)
         self.scale_shift_table = nn.Parameter(torch.randn(6, dim) / dim ** 0.5)
+        # "sm100": fused CUDA kernels (the product path, CUDA bf16 only, raises otherwise);
+        # "torch": the reference's op-by-op expressions (CPU structure tests)
+        self.block_ops = "sm100" if not norm_elementwise_affine else "torch"
 
     def forward(self, hidden_states, attention_mask=None, encoder_hidden_states=None, encoder_attention_mask=None,
                 timestep=None, height=None, width=None):
@@ -179,6 +186,9 @@ class SanaTransformerBlock(nn.Module):
         shift_msa, scale_msa, gate_msa, shift_mlp, scale_mlp, gate_mlp = (
             self.scale_shift_table[None] + timestep.reshape(batch_size, 6, -1)).chunk(6, dim=1)
 
+        if self.block_ops == "sm100":
+            return self._forward_fused(hidden_states, encoder_hidden_states, encoder_attention_mask, height, width,
+                                       shift_msa, scale_msa, gate_msa, shift_mlp, scale_mlp, gate_mlp)
         norm_hidden_states = self.norm1(hidden_states)
         norm_hidden_states = norm_hidden_states * (1 + scale_msa) + shift_msa
         norm_hidden_states = norm_hidden_states.to(hidden_states.dtype)
@@ -196,6 +206,23 @@ class SanaTransformerBlock(nn.Module):
         ff_output = self.ff(norm_hidden_states)
         ff_output = ff_output.flatten(2, 3).permute(0, 2, 1)
         return hidden_states + gate_mlp * ff_output
+
+    def _forward_fused(self, hidden_states, encoder_hidden_states, encoder_attention_mask, height, width,
+                       shift_msa, scale_msa, gate_msa, shift_mlp, scale_mlp, gate_mlp):
+        """Same block with the modulate / gate / residual arithmetic as fused kernels
+        (yat_b200/csrc/block_ops.cu); everything stays token-major [B, N, C]."""
+        norm_hidden_states = ln_modulate(hidden_states, scale_msa, shift_msa, self.norm1.eps)
+        attn_output = self.attn1(norm_hidden_states)
+        hidden_states = gate_residual(hidden_states, attn_output, gate_msa)
+        if self.attn2 is not None:
+            attn_output = self.attn2(hidden_states, encoder_hidden_states=encoder_hidden_states,
+                                     attention_mask=encoder_attention_mask)
+            hidden_states = attn_output + hidden_states
+        norm_hidden_states = ln_modulate(hidden_states, scale_mlp, shift_mlp, self.norm2.eps)
+        norm_hidden_states = norm_hidden_states.unflatten(1, (height, width)).permute(0, 3, 1, 2)
+        ff_output = self.ff(norm_hidden_states)
+        ff_output = ff_output.flatten(2, 3).permute(0, 2, 1)
+        return gate_residual(hidden_states, ff_output, gate_mlp)
 
 
 def unfreeze_sana_blocks(transformer, layers):
@@ -309,6 +336,14 @@ class PatchedSanaTransformer2DModel(nn.Module):
         if device_map is not None:
             model = model.to(device_map)
         return model
+
+    def set_block_ops(self, impl: str):
+        """"sm100" (fused kernels, default) or "torch" (op-by-op reference expressions)."""
+        if impl not in ("sm100", "torch"):
+            raise ValueError(f"unknown block_ops {impl!r}")
+        for m in self.modules():
+            if hasattr(m, "block_ops"):
+                m.block_ops = impl
 
     # ---- attention processors (utils/patched_sana_transformer.py:169-227) ----
     @property

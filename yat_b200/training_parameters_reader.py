@@ -42,6 +42,9 @@ class TrainingParameters:
         self.aspect_ratios = None
         self.exploration_steps = None
         self.use_repa = False
+        # "auto" (default): recompute block activations only when they would not fit in HBM; True = always
+        # (the reference's behaviour, train_sana.py:63); False = never
+        self.gradient_checkpointing = "auto"
         self.repa_lambda = 0.05
         self.repa_pretrained_model = None
         self.num_shards = None
@@ -98,6 +101,9 @@ class TrainingParameters:
             self.lora_algo = y["lora_algo"]
         self.low_vram = has("low_vram")
         self.use_repa = has("use_repa")
+        if has("gradient_checkpointing"):
+            v = y["gradient_checkpointing"]
+            self.gradient_checkpointing = "auto" if str(v).lower() == "auto" else bool(v)
         self.repa_lambda = float(y["repa_lambda"]) if has("repa_lambda") else 0.05
         self.repa_pretrained_model = y.get("repa_pretrained_model")
         self.bucket_repeat = int(y["bucket_repeat"]) if has("bucket_repeat") else 1
