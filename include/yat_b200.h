@@ -20,6 +20,7 @@
  *                         utils/patch_sana_attention_layers.py:94
  *   yat_ln_modulate_*     utils/patch_sana_attention_layers.py:84-90,104-105 (+ norm_out)
  *   yat_gate_residual_*   utils/patch_sana_attention_layers.py:95,113
+ *   yat_glumb_mid_*       GLUMBConv middle, utils/patch_sana_attention_layers.py:106-111
  *   yat_pad_embeddings    train_sana.py:167-179  train_pixart_sigma.py:158-169
  *   yat_bucket_assign     common/trainer.py:109-120  common/bucket_sampler.py:314-322
  */
@@ -152,6 +153,21 @@ int yat_gate_residual_fwd(const void* res, const void* y, const void* gate, int6
                           int B, int N, int C, void* out, void* stream);
 int yat_gate_residual_bwd(const void* dout, const void* y, const void* gate, int64_t mod_batch_stride,
                           int B, int N, int C, void* dy, void* dgate, void* workspace, void* stream);
+
+/* ---- (next, N1) fused middle of GLUMBConv ---------------------------------------------------
+ * utils/patch_sana_attention_layers.py:106-111 -> GLUMBConv: SiLU, depthwise 3x3 (+bias, zero pad 1),
+ * chunk, x * SiLU(gate).  Token-major (NHWC):
+ *   u [B, H, W, 2*Hd] bf16 (conv_inverted output)   w_dw [2*Hd, 9] bf16   b_dw [2*Hd] bf16
+ *   mid [B, H, W, Hd] bf16 (conv_point input);  Hd % 8 == 0 (any H, W: the image is tiled in 8-column strips)
+ * bwd: dmid -> du [B,H,W,2*Hd], dw [2*Hd, 9] bf16, db [2*Hd] bf16; dc is a caller-provided scratch
+ * tensor shaped like u; workspace = yat_glumb_workspace_bytes(B, W, Hd) bytes (fixed-order partial sums).
+ */
+int64_t yat_glumb_workspace_bytes(int B, int W, int Hd);
+int yat_glumb_mid_fwd(const void* u, const void* w_dw, const void* b_dw, int B, int H, int W, int Hd,
+                      void* mid, void* stream);
+int yat_glumb_mid_bwd(const void* u, const void* w_dw, const void* b_dw, const void* dmid,
+                      int B, int H, int W, int Hd, void* dc, void* du, void* dw, void* db,
+                      void* workspace, void* stream);
 
 /* ---- (next) ragged text-embedding pad + mask -------------------------------------------
  *   packed [sum L_i, E] bf16, offsets int32 [B+1] -> padded [B, Lmax, E] bf16 (zero fill),

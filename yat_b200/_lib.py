@@ -42,6 +42,10 @@ SIGNATURES = {
     "yat_gate_residual_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p]),
     "yat_gate_residual_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p,
                                       c_void_p, c_void_p]),
+    "yat_glumb_workspace_bytes": (c_int64, [c_int, c_int, c_int]),
+    "yat_glumb_mid_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "yat_glumb_mid_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
+                                  c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "yat_pad_embeddings": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "yat_bucket_assign": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p]),
     "yat_philox_raw": (c_int, [c_uint64, c_uint64, c_uint32, c_uint32, c_int, c_void_p, c_void_p]),
@@ -54,7 +58,7 @@ _lib = None
 LAUNCHING = ("yat_noise_flowmatch", "yat_noise_ddpm", "yat_loss_fused", "yat_repa_cos", "yat_linattn_fwd",
              "yat_linattn_bwd", "yat_linattn_fwd_simt", "yat_linattn_bwd_simt", "yat_pad_embeddings",
              "yat_philox_raw", "yat_ln_modulate_fwd", "yat_ln_modulate_bwd", "yat_gate_residual_fwd",
-             "yat_gate_residual_bwd")
+             "yat_gate_residual_bwd", "yat_glumb_mid_fwd", "yat_glumb_mid_bwd")
 launch_counts = {name: 0 for name in LAUNCHING}
 
 

@@ -24,6 +24,7 @@ from torch.utils.checkpoint import checkpoint
 
 from .attention import Attention, AttnProcessor2_0, SanaLinearAttnProcessorB200
 from .block_ops import gate_residual, ln_modulate
+from .glumb import glumb_mid
 
 
 class Transformer2DModelOutput:
@@ -140,6 +141,14 @@ class GLUMBConv(nn.Module):
         hidden_states = hidden_states * self.nonlinearity(gate)
         return self.conv_point(hidden_states)
 
+    def forward_tokens(self, hidden_states, height, width):
+        """Same module on token-major data [B, H*W, C] (the product path): the 1x1 convolutions are
+        GEMMs on the conv weights viewed as [out, in], the middle is one fused kernel."""
+        w_inv, w_pt = self.conv_inverted.weight, self.conv_point.weight
+        u = F.linear(hidden_states, w_inv.view(w_inv.shape[0], w_inv.shape[1]), self.conv_inverted.bias)
+        mid = glumb_mid(u, self.conv_depth.weight, self.conv_depth.bias, height, width)
+        return F.linear(mid, w_pt.view(w_pt.shape[0], w_pt.shape[1]), self.conv_point.bias)
+
 
 class SanaModulatedNorm(nn.Module):
     def __init__(self, dim, elementwise_affine=False, eps=1e-6):
@@ -219,9 +228,7 @@ class SanaTransformerBlock(nn.Module):
                                      attention_mask=encoder_attention_mask)
             hidden_states = attn_output + hidden_states
         norm_hidden_states = ln_modulate(hidden_states, scale_mlp, shift_mlp, self.norm2.eps)
-        norm_hidden_states = norm_hidden_states.unflatten(1, (height, width)).permute(0, 3, 1, 2)
-        ff_output = self.ff(norm_hidden_states)
-        ff_output = ff_output.flatten(2, 3).permute(0, 2, 1)
+        ff_output = self.ff.forward_tokens(norm_hidden_states, height, width)
         return gate_residual(hidden_states, ff_output, gate_mlp)
 
 
