@@ -43,9 +43,10 @@ SIGNATURES = {
     "yat_gate_residual_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p,
                                       c_void_p, c_void_p]),
     "yat_glumb_workspace_bytes": (c_int64, [c_int, c_int, c_int]),
-    "yat_glumb_mid_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "yat_glumb_mid_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
+                                  c_void_p]),
     "yat_glumb_mid_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
-                                  c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+                                  c_void_p, c_void_p, c_void_p, c_void_p]),
     "yat_pad_embeddings": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "yat_bucket_assign": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p]),
     "yat_philox_raw": (c_int, [c_uint64, c_uint64, c_uint32, c_uint32, c_int, c_void_p, c_void_p]),

@@ -18,10 +18,10 @@
 // are issued before the stencil of row y and committed after it.  The kernels are instruction-bound
 // (~40 thread instructions per output), which is why the activation costs a single MUFU op.
 //
-// Backward (two kernels, same sweep):
-//   dc kernel   recompute c; dxa = dmid * silu(g), dg = dmid * xa * silu'(g)          -> dc [B,H,W,2Hd]
-//               dw[k] += s[window tap k] * dc, db += dc; per-CTA partial sums -> fixed-order finish
-//   du kernel   ds = depthwise3x3^T(dc), du = ds * silu'(u)
+// Backward (one kernel, same sweep, 512 threads): the forward also stores c = conv output (bf16, what the
+// reference keeps for autograd anyway); the loader forms dc = [dmid * silu(g) | dmid * xa * silu'(g)] on the
+// way into the ring, the stencil threads compute du = (depthwise3x3^T dc) * silu'(u) and accumulate
+// dw[k] += silu(u) * dc[tap k], db += dc; per-CTA partial sums -> fixed-order finish (deterministic).
 #include "common.cuh"
 
 namespace yat {
@@ -44,16 +44,9 @@ __device__ __forceinline__ float silu_f(float x) {
   const float h = 0.5f * x;
   return fmaf(h, tanh_approx(h), h);
 }
-// d silu / dx = sig * (1 + x * (1 - sig))
-__device__ __forceinline__ float dsilu_f(float x) {
-  const float sg = fmaf(0.5f, tanh_approx(0.5f * x), 0.5f);
-  return sg * fmaf(x, 1.0f - sg, 1.0f);
-}
-
 __device__ __forceinline__ void unpack4(uint2 v, float f[4]) {
   f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
 }
-__device__ __forceinline__ uint2 pack4(const float f[4]) { return make_uint2(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3])); }
 __device__ __forceinline__ void unpack8(const uint4& v, float f[8]) {
   f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
   f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
@@ -65,9 +58,9 @@ struct GlumbParams {
   const __nv_bfloat16* bias;  // [2*Hd]
   const __nv_bfloat16* dmid;  // [B, H, W, Hd]   (dc kernel)
   __nv_bfloat16* mid;         // [B, H, W, Hd]   (forward)
-  __nv_bfloat16* dc;          // [B, H, W, 2*Hd] (dc kernel out, du kernel in)
+  __nv_bfloat16* c;           // [B, H, W, 2*Hd] conv output: forward out (optional), backward in
   __nv_bfloat16* du;          // [B, H, W, 2*Hd]
-  float* partial;             // [B, 2*Hd, 10]   (du kernel)
+  float* partial;             // [B * x-tiles, 2*Hd, 10] (backward)
   int B, H, W, Hd;
 };
 
@@ -116,14 +109,12 @@ struct RowLoader {
 };
 
 // ---------------------------------------------------------------------------------------------
-// forward (BWD = false) and dc (+ dw, db) kernel (BWD = true).  Thread values [0,1] = the two A
-// channels ca, ca+1; [2,3] = their gates Hd+ca, Hd+ca+1.
+// forward.  Thread values [0,1] = the two A channels ca, ca+1; [2,3] = their gates Hd+ca, Hd+ca+1.
+// Optionally writes c (the depthwise-conv output, bf16) for the backward.
 // ---------------------------------------------------------------------------------------------
-template <bool BWD>
-__global__ void __launch_bounds__(kThreads, BWD ? 1 : 2) glumb_mid_kernel(const GlumbParams p) {
+__global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const GlumbParams p) {
   __shared__ __align__(16) float ring[kRing][kRowFloats];
   __shared__ __align__(16) uint4 stage[kDepth][RowLoader::kStageRowVecs];
-  __shared__ float red[8][4][33];
   const int W = p.W, H = p.H, Hd = p.Hd;
   const int tiles_x = (W + kTW - 1) / kTW;
   const int b = blockIdx.y / tiles_x, tile = blockIdx.y - b * tiles_x;
@@ -142,13 +133,12 @@ __global__ void __launch_bounds__(kThreads, BWD ? 1 : 2) glumb_mid_kernel(const 
     L.valid = (x0 - 1 + L.j) >= 0 && (x0 - 1 + L.j) < W && cl < Hd;
     L.stage = &stage[0][L.active ? tid : 0];
   }
-
   const int ca = c0 + 2 * lane;
   const int x = x0 + warp;
-  const bool ch_ok = ca < Hd;                                   // Hd is even
-  const bool ok = ch_ok && x < W;
-  // weights / bias of the CTA's 64 + 64 channels: coalesced into shared memory (the stage ring is still idle),
-  // then 36 + 4 values per thread into registers
+  const bool ok = ca < Hd && x < W;                             // Hd is even
+
+  // weights / bias of the CTA's 64 + 64 channels: coalesced into shared memory (the stage ring is still
+  // idle), then 36 + 4 values per thread into registers
   float w[9][4], bias[4];
   {
     __nv_bfloat16* wsm = reinterpret_cast<__nv_bfloat16*>(&stage[0][0]);     // [2][64][9] then bias [2][64]
@@ -171,13 +161,6 @@ __global__ void __launch_bounds__(kThreads, BWD ? 1 : 2) glumb_mid_kernel(const 
       for (int k = 0; k < 9; ++k) w[k][j] = __bfloat162float(wsm[base + cl * 9 + k]);
     }
     __syncthreads();
-  }
-  float dw[9][4], db[4];
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    db[j] = 0.f;
-#pragma unroll
-    for (int k = 0; k < 9; ++k) dw[k][j] = 0.f;
   }
   float win0[3][4], win1[3][4], win2[3][4];
 #pragma unroll
@@ -204,23 +187,13 @@ __global__ void __launch_bounds__(kThreads, BWD ? 1 : 2) glumb_mid_kernel(const 
   __syncthreads();
   load_cols(ring[0], win1);                        // row 0; row -1 (win0) is zero
 
-  // dc kernel: dmid of this thread's pixel, fetched two rows ahead of its use
-  const __nv_bfloat16* dm_ptr = BWD && ok ? p.dmid + (((int64_t)b * H) * W + x) * Hd + ca : nullptr;
-  const int64_t dm_row = (int64_t)W * Hd;
-  uint32_t dm_a = 0, dm_b = 0;
-  if (BWD && ok) {
-    dm_a = __ldg(reinterpret_cast<const uint32_t*>(dm_ptr));
-    if (H > 1) dm_b = __ldg(reinterpret_cast<const uint32_t*>(dm_ptr + dm_row));
-  }
+  __nv_bfloat16* mid_ptr = p.mid + (((int64_t)b * H) * W + x) * Hd + ca;
+  __nv_bfloat16* c_ptr = p.c ? p.c + (((int64_t)b * H) * W + x) * C2 + ca : nullptr;
+  const int64_t mid_row = (int64_t)W * Hd, c_row = (int64_t)W * C2;
 
   // rows (y-1, y) are in (ra, rb); row y+1 comes out of the ring into rc
   auto step = [&](int y, float (&ra)[3][4], float (&rb)[3][4], float (&rc)[3][4]) {
     L.issue(y + 1 + kDepth);                       // its stage slot held row y+1, activated during step y-1
-    uint32_t dmr = dm_a;
-    if (BWD) {
-      dm_a = dm_b;
-      if (ok && y + 2 < H) dm_b = __ldg(reinterpret_cast<const uint32_t*>(dm_ptr + (y + 2) * dm_row));
-    }
     load_cols(ring[(y + 1) % kRing], rc);
     float acc[4];
 #pragma unroll
@@ -234,27 +207,15 @@ __global__ void __launch_bounds__(kThreads, BWD ? 1 : 2) glumb_mid_kernel(const 
       }
       acc[j] = a;
     }
-    const int64_t pix = ((int64_t)b * H + y) * W + x;
-    if (!BWD) {
-      if (ok)
-        *reinterpret_cast<uint32_t*>(p.mid + pix * Hd + ca) = pack_bf16(acc[0] * silu_f(acc[2]), acc[1] * silu_f(acc[3]));
-    } else if (ok) {
-      const float dm0 = bf16_lo(dmr), dm1 = bf16_hi(dmr);
-      const uint32_t da = pack_bf16(dm0 * silu_f(acc[2]), dm1 * silu_f(acc[3]));
-      const uint32_t dg = pack_bf16(dm0 * acc[0] * dsilu_f(acc[2]), dm1 * acc[1] * dsilu_f(acc[3]));
-      *reinterpret_cast<uint32_t*>(p.dc + pix * C2 + ca) = da;
-      *reinterpret_cast<uint32_t*>(p.dc + pix * C2 + Hd + ca) = dg;
-      const float d[4] = {bf16_lo(da), bf16_hi(da), bf16_lo(dg), bf16_hi(dg)};   // what the du kernel will read
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        db[j] += d[j];
-#pragma unroll
-        for (int kx = 0; kx < 3; ++kx) {
-          dw[kx][j] = fmaf(ra[kx][j], d[j], dw[kx][j]);
-          dw[3 + kx][j] = fmaf(rb[kx][j], d[j], dw[3 + kx][j]);
-          dw[6 + kx][j] = fmaf(rc[kx][j], d[j], dw[6 + kx][j]);
-        }
+    if (ok) {
+      // c is what the reference keeps as the bf16 conv output; the GLU uses the same rounded values
+      const uint32_t cxa = pack_bf16(acc[0], acc[1]), cg = pack_bf16(acc[2], acc[3]);
+      if (c_ptr) {
+        *reinterpret_cast<uint32_t*>(c_ptr + y * c_row) = cxa;
+        *reinterpret_cast<uint32_t*>(c_ptr + y * c_row + Hd) = cg;
       }
+      *reinterpret_cast<uint32_t*>(mid_ptr + y * mid_row) =
+          pack_bf16(bf16_lo(cxa) * silu_f(bf16_lo(cg)), bf16_hi(cxa) * silu_f(bf16_hi(cg)));
     }
     L.commit<true>(ring[(y + 2) % kRing], y + 2);
     __syncthreads();
@@ -264,132 +225,186 @@ __global__ void __launch_bounds__(kThreads, BWD ? 1 : 2) glumb_mid_kernel(const 
     if (y0 + 1 < H) step(y0 + 1, win1, win2, win0);
     if (y0 + 2 < H) step(y0 + 2, win2, win0, win1);
   }
-
-  if (BWD) {
-    // per-CTA sums over the 8 columns, four values at a time (fixed order), -> partial[(b, tile)][channel][10]
-    float* part = p.partial + ((int64_t)b * tiles_x + tile) * C2 * 10;
-#pragma unroll
-    for (int g = 0; g < 10; ++g) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) red[warp][j][lane] = g < 9 ? dw[g][j] : db[j];
-      __syncthreads();
-      if (tid < 128) {
-        const int j = tid >> 5, l = tid & 31;
-        float s = 0.f;
-#pragma unroll
-        for (int wv = 0; wv < 8; ++wv) s += red[wv][j][l];
-        const int cq = c0 + 2 * l;
-        if (cq < Hd) part[((j < 2 ? cq : Hd + cq - 2) + j) * 10 + g] = s;
-      }
-      __syncthreads();
-    }
-  }
 }
 
 // ---------------------------------------------------------------------------------------------
-// du kernel: one CTA = (sample b, 8 columns, 128 of the 2*Hd channels); ring of raw dc rows.
-//   ds[q] = sum_k w[k] * dc[q - k + 1]        du = ds * silu'(u)
+// backward, ONE kernel (512 threads): the loader turns the saved conv output c = [xa | g] and dmid into
+//   dc_A = dmid * silu(g)        dc_G = dmid * xa * silu'(g)
+// on the way into the fp32 ring (dc never touches HBM); 16 warps = 8 columns x {A half, gate half}, lane l
+// owns channels 2l, 2l+1 of its half:
+//   ds[q]  = sum_k w[k] * dc[q - k + 1]        du = ds * silu'(u)
+//   dw[k] += silu(u)[q] * dc[q - k + 1]        db += dc[q]
+// dw / db: per-CTA sums over the 8 columns in fixed order -> partial[(b, tile)][channel][10].
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 2) glumb_du_kernel(const GlumbParams p) {
+constexpr int kBwdThreads = 512;
+constexpr int kDepthB = 6;
+constexpr int kItems = (kTW + 2) * 16;            // loader work items per row: (column, group of 4 channel pairs)
+
+__global__ void __launch_bounds__(kBwdThreads, 1) glumb_bwd_kernel(const GlumbParams p) {
   __shared__ __align__(16) float ring[kRing][kRowFloats];
-  __shared__ __align__(16) uint4 stage[kDepth][RowLoader::kStageRowVecs];
-  const int W = p.W, H = p.H;
-  const int64_t C2 = 2 * (int64_t)p.Hd;
+  __shared__ __align__(16) uint2 stage[kDepthB][3][kItems];
+  const int W = p.W, H = p.H, Hd = p.Hd;
   const int tiles_x = (W + kTW - 1) / kTW;
   const int b = blockIdx.y / tiles_x, tile = blockIdx.y - b * tiles_x;
-  const int x0 = tile * kTW, c0 = blockIdx.x * 128;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int x0 = tile * kTW, c0 = blockIdx.x * 64;
+  const int tid = threadIdx.x, wv = tid >> 5, lane = tid & 31;
+  const int64_t C2 = 2 * (int64_t)Hd;
+  const int64_t img = (int64_t)b * H * W;
 
-  RowLoader L;
-  L.src = p.dc + (int64_t)b * H * W * C2;
-  L.pix_stride = C2; L.H = H; L.W = W; L.x0 = x0;
-  L.active = tid < (kTW + 2) * 16;
-  L.j = tid >> 4; L.v = tid & 15;
-  L.ch = c0 + 8 * L.v;
-  L.valid = (x0 - 1 + L.j) >= 0 && (x0 - 1 + L.j) < W && L.ch < C2;
-  L.stage = &stage[0][L.active ? tid : 0];
+  // ---- loader role (threads 0..159)
+  const bool l_active = tid < kItems;
+  const int lj = tid >> 4, lq = tid & 15;
+  const int lcol = x0 - 1 + lj, lcl = c0 + 4 * lq;
+  const bool l_valid = l_active && lcol >= 0 && lcol < W && lcl < Hd;
+  const __nv_bfloat16* l_c = p.c + (img + lcol) * C2 + lcl;
+  const __nv_bfloat16* l_dm = p.dmid + (img + lcol) * Hd + lcl;
+  auto issue = [&](int r) {
+    if (l_valid && r >= 0 && r < H) {
+      const int s = r % kDepthB;
+      const int64_t ro = (int64_t)r * W;
+      const uint32_t d0 = (uint32_t)__cvta_generic_to_shared(&stage[s][0][tid]);
+      const uint32_t d1 = (uint32_t)__cvta_generic_to_shared(&stage[s][1][tid]);
+      const uint32_t d2 = (uint32_t)__cvta_generic_to_shared(&stage[s][2][tid]);
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d0), "l"(l_c + ro * C2) : "memory");
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d1), "l"(l_c + ro * C2 + Hd) : "memory");
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d2), "l"(l_dm + ro * Hd) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  auto commit = [&](float* ring_row, int r) {
+    asm volatile("cp.async.wait_group %0;" ::"n"(kDepthB - 1) : "memory");
+    if (!l_active) return;
+    float da[4] = {0.f, 0.f, 0.f, 0.f}, dg[4] = {0.f, 0.f, 0.f, 0.f};
+    if (l_valid && r >= 0 && r < H) {
+      const int s = r % kDepthB;
+      float xa[4], g[4], dm[4];
+      unpack4(stage[s][0][tid], xa);
+      unpack4(stage[s][1][tid], g);
+      unpack4(stage[s][2][tid], dm);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float t = tanh_approx(0.5f * g[e]);
+        const float sg = fmaf(0.5f, t, 0.5f);                       // sigmoid(g)
+        da[e] = dm[e] * (g[e] * sg);                                // dmid * silu(g)
+        dg[e] = dm[e] * xa[e] * (sg * fmaf(g[e], 1.0f - sg, 1.0f)); // dmid * xa * silu'(g)
+      }
+    }
+    *reinterpret_cast<float4*>(ring_row + lj * 128 + 4 * lq) = make_float4(da[0], da[1], da[2], da[3]);
+    *reinterpret_cast<float4*>(ring_row + lj * 128 + 64 + 4 * lq) = make_float4(dg[0], dg[1], dg[2], dg[3]);
+  };
 
-  const int64_t ch = c0 + 4 * lane;
-  const int x = x0 + warp;
-  const bool ok = ch < C2 && x < W;
-  const __nv_bfloat16* ub = p.u + (int64_t)b * H * W * C2;
-  __nv_bfloat16* dub = p.du + (int64_t)b * H * W * C2;
-  float w[9][4];
+  // ---- compute role: warp = (column, half), lane = channel pair
+  const int col = wv >> 1, kind = wv & 1;
+  const int x = x0 + col;
+  const int cl = c0 + 2 * lane;
+  const bool ok = cl < Hd && x < W;
+  const int64_t ch = (kind ? Hd : 0) + cl;
+  const int roff = kind * 64 + 2 * lane;
+  float w[9][2];
   {
-    __nv_bfloat16* wsm = reinterpret_cast<__nv_bfloat16*>(&stage[0][0]);     // [128][9], coalesced
-    for (int i = tid; i < 128 * 9; i += kThreads)
-      wsm[i] = (c0 + i / 9) < C2 ? p.w[(int64_t)c0 * 9 + i] : __float2bfloat16_rn(0.f);
+    __nv_bfloat16* wsm = reinterpret_cast<__nv_bfloat16*>(&stage[0][0][0]);  // [2][64][9], coalesced
+    for (int i = tid; i < 2 * 576; i += kBwdThreads) {
+      const int half = i / 576, r = i - half * 576;
+      wsm[i] = (c0 + r / 9) < Hd ? p.w[((int64_t)(half ? Hd : 0) + c0) * 9 + r] : __float2bfloat16_rn(0.f);
+    }
     __syncthreads();
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
+    for (int j = 0; j < 2; ++j)
 #pragma unroll
-      for (int k = 0; k < 9; ++k) w[k][j] = __bfloat162float(wsm[(4 * lane + j) * 9 + k]);
+      for (int k = 0; k < 9; ++k) w[k][j] = __bfloat162float(wsm[kind * 576 + (2 * lane + j) * 9 + k]);
     __syncthreads();
   }
-
-  float win0[3][4], win1[3][4], win2[3][4];
+  float dw[9][2], db[2] = {0.f, 0.f};
+#pragma unroll
+  for (int k = 0; k < 9; ++k) dw[k][0] = dw[k][1] = 0.f;
+  float win0[3][2], win1[3][2], win2[3][2];
 #pragma unroll
   for (int kx = 0; kx < 3; ++kx)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) win0[kx][j] = win1[kx][j] = win2[kx][j] = 0.f;
-
-  auto load_cols = [&](const float* ring_row, float (&dst)[3][4]) {
+    for (int j = 0; j < 2; ++j) win0[kx][j] = win1[kx][j] = win2[kx][j] = 0.f;
+  auto load_cols = [&](const float* ring_row, float (&dst)[3][2]) {
 #pragma unroll
     for (int kx = 0; kx < 3; ++kx) {
-      const float4 d = *reinterpret_cast<const float4*>(ring_row + (warp + kx) * 128 + 4 * lane);
-      dst[kx][0] = d.x; dst[kx][1] = d.y; dst[kx][2] = d.z; dst[kx][3] = d.w;
+      const float2 d = *reinterpret_cast<const float2*>(ring_row + (col + kx) * 128 + roff);
+      dst[kx][0] = d.x; dst[kx][1] = d.y;
     }
   };
 
 #pragma unroll
-  for (int r = 0; r < kDepth; ++r) L.issue(r);
-  L.commit<false>(ring[0], 0);
-  L.issue(kDepth);
-  L.commit<false>(ring[1], 1);
+  for (int r = 0; r < kDepthB; ++r) issue(r);
+  commit(ring[0], 0);
+  issue(kDepthB);
+  commit(ring[1], 1);
   __syncthreads();
   load_cols(ring[0], win1);
 
-  // u of this thread's pixel, fetched two rows ahead of its use
-  const __nv_bfloat16* u_ptr = ub + (int64_t)x * C2 + ch;
+  // u of this thread's pixel: three rotating registers, requested three rows ahead of their use
+  const __nv_bfloat16* u_ptr = p.u + (img + x) * C2 + ch;
+  __nv_bfloat16* du_ptr = p.du + (img + x) * C2 + ch;
   const int64_t u_row = (int64_t)W * C2;
-  uint2 u_a = make_uint2(0, 0), u_b = make_uint2(0, 0);
+  uint32_t u0 = 0, u1 = 0, u2 = 0;
   if (ok) {
-    u_a = __ldg(reinterpret_cast<const uint2*>(u_ptr));
-    if (H > 1) u_b = __ldg(reinterpret_cast<const uint2*>(u_ptr + u_row));
+    u0 = __ldg(reinterpret_cast<const uint32_t*>(u_ptr));
+    if (H > 1) u1 = __ldg(reinterpret_cast<const uint32_t*>(u_ptr + u_row));
+    if (H > 2) u2 = __ldg(reinterpret_cast<const uint32_t*>(u_ptr + 2 * u_row));
   }
 
   // dc rows (y-1, y) are in (ra, rb); row y+1 comes out of the ring into rc.
   // tap (ky, kx) pairs with dc at (y - ky + 1, x - kx + 1): window row 2-ky, window column 2-kx.
-  auto step = [&](int y, float (&ra)[3][4], float (&rb)[3][4], float (&rc)[3][4]) {
-    L.issue(y + 1 + kDepth);
-    const int64_t pix = (int64_t)y * W + x;
-    const uint2 uraw = u_a;
-    u_a = u_b;
-    if (ok && y + 2 < H) u_b = __ldg(reinterpret_cast<const uint2*>(u_ptr + (y + 2) * u_row));
+  auto step = [&](int y, float (&ra)[3][2], float (&rb)[3][2], float (&rc)[3][2], uint32_t& ureg) {
+    issue(y + 1 + kDepthB);
+    const uint32_t uraw = ureg;
+    if (ok && y + 3 < H) ureg = __ldg(reinterpret_cast<const uint32_t*>(u_ptr + (y + 3) * u_row));
     load_cols(ring[(y + 1) % kRing], rc);
     if (ok) {
-      float uu[4], o[4];
-      unpack4(uraw, uu);
+      const float uu[2] = {bf16_lo(uraw), bf16_hi(uraw)};
+      float o[2];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
+      for (int j = 0; j < 2; ++j) {
+        const float t = tanh_approx(0.5f * uu[j]);
+        const float sg = fmaf(0.5f, t, 0.5f);
+        const float s = uu[j] * sg;                                  // silu(u)
         float a = 0.f;
 #pragma unroll
         for (int kx = 0; kx < 3; ++kx) {
           a = fmaf(w[kx][j], rc[2 - kx][j], a);
           a = fmaf(w[3 + kx][j], rb[2 - kx][j], a);
           a = fmaf(w[6 + kx][j], ra[2 - kx][j], a);
+          dw[kx][j] = fmaf(s, rc[2 - kx][j], dw[kx][j]);
+          dw[3 + kx][j] = fmaf(s, rb[2 - kx][j], dw[3 + kx][j]);
+          dw[6 + kx][j] = fmaf(s, ra[2 - kx][j], dw[6 + kx][j]);
         }
-        o[j] = a * dsilu_f(uu[j]);
+        db[j] += rb[1][j];
+        o[j] = a * (sg * fmaf(uu[j], 1.0f - sg, 1.0f));
       }
-      *reinterpret_cast<uint2*>(dub + pix * C2 + ch) = pack4(o);
+      *reinterpret_cast<uint32_t*>(du_ptr + y * u_row) = pack_bf16(o[0], o[1]);
     }
-    L.commit<false>(ring[(y + 2) % kRing], y + 2);
+    commit(ring[(y + 2) % kRing], y + 2);
     __syncthreads();
   };
   for (int y0 = 0; y0 < H; y0 += 3) {
-    step(y0, win0, win1, win2);
-    if (y0 + 1 < H) step(y0 + 1, win1, win2, win0);
-    if (y0 + 2 < H) step(y0 + 2, win2, win0, win1);
+    step(y0, win0, win1, win2, u0);
+    if (y0 + 1 < H) step(y0 + 1, win1, win2, win0, u1);
+    if (y0 + 2 < H) step(y0 + 2, win2, win0, win1, u2);
+  }
+
+  // per-CTA sums over the 8 columns, fixed order (scratch aliases the ring: every read of it is done)
+  float (*red)[2][33] = reinterpret_cast<float (*)[2][33]>(&ring[0][0]);    // [16 warps][2][33]
+  float* part = p.partial + ((int64_t)b * tiles_x + tile) * C2 * 10;
+#pragma unroll
+  for (int g = 0; g < 10; ++g) {
+    red[wv][0][lane] = g < 9 ? dw[g][0] : db[0];
+    red[wv][1][lane] = g < 9 ? dw[g][1] : db[1];
+    __syncthreads();
+    if (tid < 128) {
+      const int half = tid >> 6, j = (tid >> 5) & 1, l = tid & 31;
+      float s = 0.f;
+#pragma unroll
+      for (int cw = 0; cw < 8; ++cw) s += red[(cw << 1) | half][j][l];
+      const int cq = c0 + 2 * l;
+      if (cq < Hd) part[((half ? Hd : 0) + cq + j) * 10 + g] = s;
+    }
+    __syncthreads();
   }
 }
 
@@ -423,38 +438,37 @@ extern "C" int64_t yat_glumb_workspace_bytes(int B, int W, int Hd) {
 }
 
 extern "C" int yat_glumb_mid_fwd(const void* u, const void* w_dw, const void* b_dw, int B, int H, int W, int Hd,
-                                 void* mid, void* stream) {
+                                 void* mid, void* c_out, void* stream) {
   using namespace yat;
   YAT_REQUIRE(u && w_dw && b_dw && mid, YAT_ERR_BAD_ARG, "yat_glumb_mid_fwd: null pointer argument");
   int rc = check_shape("yat_glumb_mid_fwd", B, H, W, Hd);
   if (rc != YAT_OK) return rc;
-  YAT_REQUIRE(aligned16(u) && aligned16(mid), YAT_ERR_BAD_ARG, "yat_glumb_mid_fwd: tensors must be 16-byte aligned");
+  YAT_REQUIRE(aligned16(u) && aligned16(mid) && aligned16(c_out), YAT_ERR_BAD_ARG,
+              "yat_glumb_mid_fwd: tensors must be 16-byte aligned");
   GlumbParams p{};
   p.u = (const __nv_bfloat16*)u; p.w = (const __nv_bfloat16*)w_dw; p.bias = (const __nv_bfloat16*)b_dw;
-  p.mid = (__nv_bfloat16*)mid; p.B = B; p.H = H; p.W = W; p.Hd = Hd;
-  glumb_mid_kernel<false><<<dim3((Hd + 63) / 64, B * tiles_of(W)), kThreads, 0, (cudaStream_t)stream>>>(p);
+  p.mid = (__nv_bfloat16*)mid; p.c = (__nv_bfloat16*)c_out; p.B = B; p.H = H; p.W = W; p.Hd = Hd;
+  glumb_fwd_kernel<<<dim3((Hd + 63) / 64, B * tiles_of(W)), kThreads, 0, (cudaStream_t)stream>>>(p);
   return check_launch("glumb_mid_fwd");
 }
 
-extern "C" int yat_glumb_mid_bwd(const void* u, const void* w_dw, const void* b_dw, const void* dmid, int B, int H,
-                                 int W, int Hd, void* dc, void* du, void* dw, void* db, void* workspace, void* stream) {
+extern "C" int yat_glumb_mid_bwd(const void* u, const void* c, const void* w_dw, const void* dmid, int B, int H, int W,
+                                 int Hd, void* du, void* dw, void* db, void* workspace, void* stream) {
   using namespace yat;
-  YAT_REQUIRE(u && w_dw && b_dw && dmid && dc && du && dw && db && workspace, YAT_ERR_BAD_ARG,
+  YAT_REQUIRE(u && c && w_dw && dmid && du && dw && db && workspace, YAT_ERR_BAD_ARG,
               "yat_glumb_mid_bwd: null pointer argument");
   int rc = check_shape("yat_glumb_mid_bwd", B, H, W, Hd);
   if (rc != YAT_OK) return rc;
-  YAT_REQUIRE(aligned16(u) && aligned16(dmid) && aligned16(dc) && aligned16(du), YAT_ERR_BAD_ARG,
+  YAT_REQUIRE(aligned16(u) && aligned16(c) && aligned16(dmid) && aligned16(du), YAT_ERR_BAD_ARG,
               "yat_glumb_mid_bwd: tensors must be 16-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
   GlumbParams p{};
-  p.u = (const __nv_bfloat16*)u; p.w = (const __nv_bfloat16*)w_dw; p.bias = (const __nv_bfloat16*)b_dw;
-  p.dmid = (const __nv_bfloat16*)dmid; p.dc = (__nv_bfloat16*)dc; p.du = (__nv_bfloat16*)du;
+  p.u = (const __nv_bfloat16*)u; p.c = (__nv_bfloat16*)const_cast<void*>(c); p.w = (const __nv_bfloat16*)w_dw;
+  p.dmid = (const __nv_bfloat16*)dmid; p.du = (__nv_bfloat16*)du;
   p.partial = (float*)workspace; p.B = B; p.H = H; p.W = W; p.Hd = Hd;
   const int parts = B * tiles_of(W);
-  glumb_mid_kernel<true><<<dim3((Hd + 63) / 64, parts), kThreads, 0, st>>>(p);
-  if ((rc = check_launch("glumb_dc")) != YAT_OK) return rc;
-  glumb_du_kernel<<<dim3((2 * Hd + 127) / 128, parts), kThreads, 0, st>>>(p);
-  if ((rc = check_launch("glumb_du")) != YAT_OK) return rc;
+  glumb_bwd_kernel<<<dim3((Hd + 63) / 64, parts), kBwdThreads, 0, st>>>(p);
+  if ((rc = check_launch("glumb_bwd")) != YAT_OK) return rc;
   const int64_t n10 = (int64_t)2 * Hd * 10;
   glumb_finish_kernel<<<(unsigned)((n10 + 255) / 256), 256, 0, st>>>(p.partial, parts, n10, (__nv_bfloat16*)dw,
                                                                    (__nv_bfloat16*)db);
