@@ -44,9 +44,6 @@ __device__ __forceinline__ float silu_f(float x) {
   const float h = 0.5f * x;
   return fmaf(h, tanh_approx(h), h);
 }
-__device__ __forceinline__ void unpack4(uint2 v, float f[4]) {
-  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
-}
 __device__ __forceinline__ void unpack8(const uint4& v, float f[8]) {
   f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
   f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
@@ -71,32 +68,35 @@ struct GlumbParams {
 constexpr int kDepth = 8;                                     // rows in flight per CTA
 
 struct RowLoader {
-  const __nv_bfloat16* src;   // sample base
-  int64_t pix_stride;         // elements per pixel
-  int H, W, x0;
+  // rows are issued and committed strictly in order 0, 1, 2, ...: running pointers, no per-row index math
+  const __nv_bfloat16* next;  // source of this thread's vector in the next row to issue
+  int64_t row_stride;         // elements between image rows
+  int H;
   int j, v;                   // this thread's ring column / vector
   bool active, valid;         // valid: inside the image and inside the channel range
-  int64_t ch;                 // first of its 8 channels in the source tensor
   uint4* stage;               // this thread's slot in stage row 0; rows are kStageRowVecs apart
+  int issue_row = 0, commit_row = 0;
   static constexpr int kStageRowVecs = (kTW + 2) * 16;
-  __device__ __forceinline__ void issue(int r) {               // always commits a group (possibly empty)
-    if (active && valid && r >= 0 && r < H) {
-      const uint32_t dst = (uint32_t)__cvta_generic_to_shared(stage + (r % kDepth) * kStageRowVecs);
-      const void* g = src + ((int64_t)r * W + (x0 - 1 + j)) * pix_stride + ch;
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(g) : "memory");
+  __device__ __forceinline__ void issue() {                    // always commits a group (possibly empty)
+    if (active && valid && issue_row < H) {
+      const uint32_t dst = (uint32_t)__cvta_generic_to_shared(stage + (issue_row & (kDepth - 1)) * kStageRowVecs);
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(next) : "memory");
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
+    next += row_stride;
+    ++issue_row;
   }
-  // row r was issued kDepth - 1 groups before the newest one
+  // the row being committed was issued kDepth - 1 groups before the newest one
   template <bool SILU>
-  __device__ __forceinline__ void commit(float* ring_row, int r) {
+  __device__ __forceinline__ void commit(float* ring_row) {
     asm volatile("cp.async.wait_group %0;" ::"n"(kDepth - 1) : "memory");
+    const int r = commit_row++;
     if (!active) return;
     float f[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) f[e] = 0.f;
-    if (valid && r >= 0 && r < H) {
-      unpack8(stage[(r % kDepth) * kStageRowVecs], f);
+    if (valid && r < H) {
+      unpack8(stage[(r & (kDepth - 1)) * kStageRowVecs], f);
       if (SILU) {
 #pragma unroll
         for (int e = 0; e < 8; ++e) f[e] = silu_f(f[e]);
@@ -123,14 +123,15 @@ __global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const GlumbParam
   const int64_t C2 = 2 * (int64_t)Hd;
 
   RowLoader L;
-  L.src = p.u + (int64_t)b * H * W * C2;
-  L.pix_stride = C2; L.H = H; L.W = W; L.x0 = x0;
+  L.H = H;
+  L.row_stride = (int64_t)W * C2;
   L.active = tid < (kTW + 2) * 16;
   L.j = tid >> 4; L.v = tid & 15;
   {
     const int cl = c0 + 8 * (L.v & 7);                          // A-half channel index
-    L.ch = L.v < 8 ? cl : Hd + cl;
-    L.valid = (x0 - 1 + L.j) >= 0 && (x0 - 1 + L.j) < W && cl < Hd;
+    const int col = x0 - 1 + L.j;
+    L.valid = col >= 0 && col < W && cl < Hd;
+    L.next = p.u + ((int64_t)b * H * W + (L.valid ? col : 0)) * C2 + (L.v < 8 ? cl : Hd + cl);
     L.stage = &stage[0][L.active ? tid : 0];
   }
   const int ca = c0 + 2 * lane;
@@ -180,10 +181,10 @@ __global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const GlumbParam
 
   // prologue: rows 0 .. kDepth-1 in flight; rows 0 and 1 activated into the ring
 #pragma unroll
-  for (int r = 0; r < kDepth; ++r) L.issue(r);
-  L.commit<true>(ring[0], 0);
-  L.issue(kDepth);
-  L.commit<true>(ring[1], 1);
+  for (int r = 0; r < kDepth; ++r) L.issue();
+  L.commit<true>(ring[0]);
+  L.issue();
+  L.commit<true>(ring[1]);
   __syncthreads();
   load_cols(ring[0], win1);                        // row 0; row -1 (win0) is zero
 
@@ -193,7 +194,7 @@ __global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const GlumbParam
 
   // rows (y-1, y) are in (ra, rb); row y+1 comes out of the ring into rc
   auto step = [&](int y, float (&ra)[3][4], float (&rb)[3][4], float (&rc)[3][4]) {
-    L.issue(y + 1 + kDepth);                       // its stage slot held row y+1, activated during step y-1
+    L.issue();                                     // row y+1+kDepth: its stage slot held row y+1, activated in step y-1
     load_cols(ring[(y + 1) % kRing], rc);
     float acc[4];
 #pragma unroll
@@ -217,7 +218,7 @@ __global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const GlumbParam
       *reinterpret_cast<uint32_t*>(mid_ptr + y * mid_row) =
           pack_bf16(bf16_lo(cxa) * silu_f(bf16_lo(cg)), bf16_hi(cxa) * silu_f(bf16_hi(cg)));
     }
-    L.commit<true>(ring[(y + 2) % kRing], y + 2);
+    L.commit<true>(ring[(y + 2) % kRing]);          // row y+2
     __syncthreads();
   };
   for (int y0 = 0; y0 < H; y0 += 3) {
@@ -237,12 +238,13 @@ __global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const GlumbParam
 // dw / db: per-CTA sums over the 8 columns in fixed order -> partial[(b, tile)][channel][10].
 // ---------------------------------------------------------------------------------------------
 constexpr int kBwdThreads = 512;
-constexpr int kDepthB = 6;
-constexpr int kItems = (kTW + 2) * 16;            // loader work items per row: (column, group of 4 channel pairs)
+constexpr int kDepthB = 8;
+constexpr int kRingB = 2;                          // row y+1 is read while row y+2 is written
+constexpr int kItems = (kTW + 2) * 32;            // loader work items per row: (column, channel pair): 10 warps' worth
 
 __global__ void __launch_bounds__(kBwdThreads, 1) glumb_bwd_kernel(const GlumbParams p) {
-  __shared__ __align__(16) float ring[kRing][kRowFloats];
-  __shared__ __align__(16) uint2 stage[kDepthB][3][kItems];
+  __shared__ __align__(16) float ring[kRingB][kRowFloats];
+  __shared__ __align__(16) uint32_t stage[kDepthB][3][kItems];
   const int W = p.W, H = p.H, Hd = p.Hd;
   const int tiles_x = (W + kTW - 1) / kTW;
   const int b = blockIdx.y / tiles_x, tile = blockIdx.y - b * tiles_x;
@@ -251,46 +253,48 @@ __global__ void __launch_bounds__(kBwdThreads, 1) glumb_bwd_kernel(const GlumbPa
   const int64_t C2 = 2 * (int64_t)Hd;
   const int64_t img = (int64_t)b * H * W;
 
-  // ---- loader role (threads 0..159)
+  // ---- loader role (threads 0..319): one channel pair (xa, g, dmid of 2 channels) of one ring column
   const bool l_active = tid < kItems;
-  const int lj = tid >> 4, lq = tid & 15;
-  const int lcol = x0 - 1 + lj, lcl = c0 + 4 * lq;
+  const int lj = tid >> 5, lp = tid & 31;
+  const int lcol = x0 - 1 + lj, lcl = c0 + 2 * lp;
   const bool l_valid = l_active && lcol >= 0 && lcol < W && lcl < Hd;
-  const __nv_bfloat16* l_c = p.c + (img + lcol) * C2 + lcl;
-  const __nv_bfloat16* l_dm = p.dmid + (img + lcol) * Hd + lcl;
-  auto issue = [&](int r) {
-    if (l_valid && r >= 0 && r < H) {
-      const int s = r % kDepthB;
-      const int64_t ro = (int64_t)r * W;
+  // rows are issued and committed strictly in order: running pointers and counters
+  const __nv_bfloat16* l_c = p.c + (img + (l_valid ? lcol : 0)) * C2 + lcl;
+  const __nv_bfloat16* l_dm = p.dmid + (img + (l_valid ? lcol : 0)) * Hd + lcl;
+  const int64_t c_row = (int64_t)W * C2, dm_row = (int64_t)W * Hd;
+  int issue_row = 0, commit_row = 0;
+  auto issue = [&]() {
+    if (l_valid && issue_row < H) {
+      const int s = issue_row & (kDepthB - 1);
       const uint32_t d0 = (uint32_t)__cvta_generic_to_shared(&stage[s][0][tid]);
-      const uint32_t d1 = (uint32_t)__cvta_generic_to_shared(&stage[s][1][tid]);
-      const uint32_t d2 = (uint32_t)__cvta_generic_to_shared(&stage[s][2][tid]);
-      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d0), "l"(l_c + ro * C2) : "memory");
-      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d1), "l"(l_c + ro * C2 + Hd) : "memory");
-      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d2), "l"(l_dm + ro * Hd) : "memory");
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d0), "l"(l_c) : "memory");
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d0 + 4 * kItems), "l"(l_c + Hd) : "memory");
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d0 + 8 * kItems), "l"(l_dm) : "memory");
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
+    l_c += c_row;
+    l_dm += dm_row;
+    ++issue_row;
   };
-  auto commit = [&](float* ring_row, int r) {
+  auto commit = [&](float* ring_row) {
     asm volatile("cp.async.wait_group %0;" ::"n"(kDepthB - 1) : "memory");
+    const int r = commit_row++;
     if (!l_active) return;
-    float da[4] = {0.f, 0.f, 0.f, 0.f}, dg[4] = {0.f, 0.f, 0.f, 0.f};
-    if (l_valid && r >= 0 && r < H) {
-      const int s = r % kDepthB;
-      float xa[4], g[4], dm[4];
-      unpack4(stage[s][0][tid], xa);
-      unpack4(stage[s][1][tid], g);
-      unpack4(stage[s][2][tid], dm);
+    float da[2] = {0.f, 0.f}, dg[2] = {0.f, 0.f};
+    if (l_valid && r < H) {
+      const int s = r & (kDepthB - 1);
+      const uint32_t rx = stage[s][0][tid], rg = stage[s][1][tid], rd = stage[s][2][tid];
+      const float xa[2] = {bf16_lo(rx), bf16_hi(rx)}, g[2] = {bf16_lo(rg), bf16_hi(rg)}, dm[2] = {bf16_lo(rd), bf16_hi(rd)};
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
+      for (int e = 0; e < 2; ++e) {
         const float t = tanh_approx(0.5f * g[e]);
         const float sg = fmaf(0.5f, t, 0.5f);                       // sigmoid(g)
         da[e] = dm[e] * (g[e] * sg);                                // dmid * silu(g)
         dg[e] = dm[e] * xa[e] * (sg * fmaf(g[e], 1.0f - sg, 1.0f)); // dmid * xa * silu'(g)
       }
     }
-    *reinterpret_cast<float4*>(ring_row + lj * 128 + 4 * lq) = make_float4(da[0], da[1], da[2], da[3]);
-    *reinterpret_cast<float4*>(ring_row + lj * 128 + 64 + 4 * lq) = make_float4(dg[0], dg[1], dg[2], dg[3]);
+    *reinterpret_cast<float2*>(ring_row + lj * 128 + 2 * lp) = make_float2(da[0], da[1]);
+    *reinterpret_cast<float2*>(ring_row + lj * 128 + 64 + 2 * lp) = make_float2(dg[0], dg[1]);
   };
 
   // ---- compute role: warp = (column, half), lane = channel pair
@@ -331,12 +335,13 @@ __global__ void __launch_bounds__(kBwdThreads, 1) glumb_bwd_kernel(const GlumbPa
   };
 
 #pragma unroll
-  for (int r = 0; r < kDepthB; ++r) issue(r);
-  commit(ring[0], 0);
-  issue(kDepthB);
-  commit(ring[1], 1);
+  for (int r = 0; r < kDepthB; ++r) issue();
+  commit(ring[0]);
   __syncthreads();
-  load_cols(ring[0], win1);
+  load_cols(ring[0], win1);                        // row 0
+  issue();
+  commit(ring[1]);                                 // row 1
+  __syncthreads();
 
   // u of this thread's pixel: three rotating registers, requested three rows ahead of their use
   const __nv_bfloat16* u_ptr = p.u + (img + x) * C2 + ch;
@@ -352,10 +357,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1) glumb_bwd_kernel(const GlumbPa
   // dc rows (y-1, y) are in (ra, rb); row y+1 comes out of the ring into rc.
   // tap (ky, kx) pairs with dc at (y - ky + 1, x - kx + 1): window row 2-ky, window column 2-kx.
   auto step = [&](int y, float (&ra)[3][2], float (&rb)[3][2], float (&rc)[3][2], uint32_t& ureg) {
-    issue(y + 1 + kDepthB);
+    issue();
     const uint32_t uraw = ureg;
     if (ok && y + 3 < H) ureg = __ldg(reinterpret_cast<const uint32_t*>(u_ptr + (y + 3) * u_row));
-    load_cols(ring[(y + 1) % kRing], rc);
+    load_cols(ring[(y + 1) & (kRingB - 1)], rc);
     if (ok) {
       const float uu[2] = {bf16_lo(uraw), bf16_hi(uraw)};
       float o[2];
@@ -379,7 +384,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) glumb_bwd_kernel(const GlumbPa
       }
       *reinterpret_cast<uint32_t*>(du_ptr + y * u_row) = pack_bf16(o[0], o[1]);
     }
-    commit(ring[(y + 2) % kRing], y + 2);
+    commit(ring[(y + 2) & (kRingB - 1)]);          // row y+2 -> the slot of row y (last read in step y-1)
     __syncthreads();
   };
   for (int y0 = 0; y0 < H; y0 += 3) {
