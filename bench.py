@@ -200,11 +200,10 @@ def _device_batch(trainer, batch, device):
     the text embeddings already padded + masked (the optimize hook accepts that tuple)."""
     import torch
     from yat_b200.bucket_sampler import Batch
-    from yat_b200.embeddings import pad_embeddings
     b = Batch()
     b.ratio = batch.ratio
     b.vae_features = batch.vae_features.to(device, dtype=torch.bfloat16)
-    b.embeddings = pad_embeddings(batch.embeddings, trainer.max_text_tokens, device)
+    b.embeddings = trainer.pad_text(batch.embeddings)
     b.repa_features = None if batch.repa_features is None else batch.repa_features.to(device)
     return b
 

@@ -142,3 +142,28 @@ def test_sana_model_hook_runs_and_learns(cuda, tmp_path, monkeypatch):
     l1 = tr.optimize(b.ratio, b.vae_features, b.embeddings, b.repa_features, torch.Generator())
     l2 = tr.optimize(b.ratio, b.vae_features, b.embeddings, b.repa_features, torch.Generator())
     assert torch.equal(l1.detach(), l2.detach())      # fresh generator -> same draws every step
+
+
+def test_trimmed_text_padding_matches_fixed_512(cuda):
+    """pad_embeddings(trim_multiple=64) pads to the longest caption only; masked keys weigh exactly 0 in
+    the cross-attention softmax, so the transformer output equals the reference's fixed 512-token padding
+    (train_sana.py:167-179) up to bf16 accumulation-order noise."""
+    from train_sana import SANA_CONFIGS
+    from yat_b200.embeddings import pad_embeddings
+    from yat_b200.sana_transformer import PatchedSanaTransformer2DModel
+    torch.manual_seed(3)
+    m = PatchedSanaTransformer2DModel(**SANA_CONFIGS["sana_tiny"]).to(cuda).to(torch.bfloat16)
+    g = torch.Generator().manual_seed(5)
+    embs = [torch.randn((n, 64), generator=g).to(torch.bfloat16) for n in (37, 150)]
+    x = torch.randn((2, 32, 16, 16), generator=g).to(torch.bfloat16).to(cuda)
+    t = torch.tensor([326.0, 811.0], device=cuda)
+    full, mask_full = pad_embeddings(embs, 512, cuda)
+    trim, mask_trim = pad_embeddings(embs, 512, cuda, trim_multiple=64)
+    assert full.shape == (2, 512, 64) and trim.shape == (2, 192, 64)
+    assert torch.equal(trim, full[:, :192]) and torch.equal(mask_trim, mask_full[:, :192])
+    assert mask_full[:, 192:].sum() == 0
+    with torch.no_grad():
+        y_full = m(x, full, t, encoder_attention_mask=mask_full).sample
+        y_trim = m(x, trim, t, encoder_attention_mask=mask_trim).sample
+    rel = ((y_full.float() - y_trim.float()).norm() / y_full.float().norm()).item()
+    assert rel < 4e-3, rel

@@ -45,6 +45,9 @@ SANA_CONFIGS = {
 
 class SanaModel(Model):
     max_text_tokens = 512
+    # pad the text batch only up to its longest caption (rounded up to 64 tokens) instead of always 512:
+    # identical cross-attention result (masked keys weigh exactly 0), ~1.6x less K/V projection + SDPA work
+    trim_text_padding = 64
 
     def __init__(self, params: TrainingParameters):
         super().__init__(params)
@@ -122,6 +125,11 @@ class SanaModel(Model):
         finally:
             self._trust_gscale = False
 
+    def pad_text(self, embeddings):
+        """Ragged caption embeddings -> (padded [B, L, E] bf16, mask int64 [B, L]) on the device."""
+        return pad_embeddings(embeddings, self.max_text_tokens, self.accelerator.device,
+                              trim_multiple=self.trim_text_padding)
+
     def optimize(self, ratio, latents, embeddings, repa_tokens, generator=None):
         params = self.params
         device = self.accelerator.device
@@ -130,7 +138,7 @@ class SanaModel(Model):
         if isinstance(embeddings, tuple):
             embeddings, attention_mask = embeddings
         else:
-            embeddings, attention_mask = pad_embeddings(embeddings, self.max_text_tokens, device)
+            embeddings, attention_mask = self.pad_text(embeddings)
         latents = latents.to(device=device, dtype=torch.bfloat16, non_blocking=True)
 
         # (2) noising.  A torch.Generator reproduces the reference draw for draw (noise, then u,

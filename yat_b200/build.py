@@ -38,8 +38,9 @@ def build(force=False, verbose=False):
     srcs = [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
     if not force and not _stale(srcs):
         return OUT
+    tmp = f"{OUT}.{os.getpid()}.tmp"          # link to a private name, then rename: readers never see a partial file
     cmd = [_nvcc(), *ARCH, "-O3", "-std=c++17", "-lineinfo", "-shared", "-Xcompiler", "-fPIC",
-           "--threads", "0", "-o", OUT, *srcs]
+           "--threads", "0", "-o", tmp, *srcs]
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")
@@ -47,7 +48,10 @@ def build(force=False, verbose=False):
     if verbose:
         sys.stderr.write(r.stderr)
     if r.returncode != 0:
+        if os.path.exists(tmp):
+            os.remove(tmp)
         raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
+    os.replace(tmp, OUT)
     return OUT
 
 

@@ -19,12 +19,21 @@ def _pinned(nbytes):
     return buf
 
 
-def pad_embeddings(embeddings, max_len, device, dtype=torch.bfloat16):
-    """embeddings: list of [L_i, E] tensors (host or device). Returns (padded [B,Lmax,E], mask int64 [B,Lmax])."""
+def pad_embeddings(embeddings, max_len, device, dtype=torch.bfloat16, trim_multiple=None):
+    """embeddings: list of [L_i, E] tensors (host or device). Returns (padded [B,Lmax,E], mask int64 [B,Lmax]).
+
+    ``trim_multiple``: pad only up to the longest sequence of the batch, rounded up to this multiple
+    (never beyond ``max_len``).  The lengths are host data, so this costs no sync.  Masked keys get a
+    -10000 bias and contribute exactly 0 after the softmax, so cross-attention over the trimmed
+    batch equals cross-attention over the reference's fixed 512-token padding (train_sana.py:167-179),
+    without projecting and attending over the padding."""
     if dtype != torch.bfloat16:
         raise ValueError("pad_embeddings produces bf16 (the training dtype of the reference hooks)")
     B = len(embeddings)
     E = embeddings[0].shape[1]
+    if trim_multiple:
+        longest = max(min(int(e.shape[0]), max_len) for e in embeddings)
+        max_len = min(max_len, max(trim_multiple, -(-longest // trim_multiple) * trim_multiple))
     lens = [min(int(e.shape[0]), max_len) for e in embeddings]
     total = sum(lens)
     offsets = torch.zeros(B + 1, dtype=torch.int32)
