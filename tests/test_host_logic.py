@@ -200,3 +200,19 @@ def test_world_size_2_gloo_bucket_rule_and_ddp():
         # no_sync, the second all-reduces the *accumulated* gradient: mean(1.0, 2.0) on both ranks
         assert r["grad"] == pytest.approx([1.5] * 4)
         assert r["gather"] == [0.0, 1.0] and r["reduce"] == 0.5
+
+
+def test_pixart_and_sd35_hook_surface():
+    """The other two reference hook files exist with the reference's class / hook names and refuse to
+    build a pipeline without weights (no silent fallback)."""
+    import train_pixart_sigma
+    import train_sd35
+    from yat_b200.trainer import Model
+    from yat_b200.training_parameters_reader import TrainingParameters
+    for cls in (train_pixart_sigma.PixartSigmaTrainer, train_sd35.SD35Trainer):
+        assert issubclass(cls, Model)
+        for hook in ("extract_latents", "extract_embeddings", "optimize", "initialize", "validate"):
+            assert callable(getattr(cls, hook))
+        with pytest.raises(NotImplementedError):
+            cls(TrainingParameters())
+    assert train_pixart_sigma.PixartSigmaTrainer.max_text_tokens == 300
