@@ -10,8 +10,9 @@ latent normals to ~1e-6 absolute (special-function-unit evaluation on the device
 Layout (must match philox.cuh):
   key     = (seed & 0xffffffff, seed >> 32)
   counter = (quad, sample, offset & 0xffffffff, ((offset >> 32) & 0x7fffffff) | stream << 31)
-  stream 0 = latent noise (quad = element_index // 4 inside the sample, 4 normals per call),
-  stream 1 = timestep draw (quad = 0, first normal of the call).
+  stream 0 = latent noise (c0 = oct = element_index // 8 inside the sample; one 32-bit word per
+             Box-Muller pair -> 8 normals per call),
+  stream 1 = timestep draw (c0 = 0, first normal of the call; two words per pair).
 """
 import numpy as np
 
@@ -51,36 +52,54 @@ def box_muller(xa, xb):
     return r * np.cos(2.0 * np.pi * a), r * np.sin(2.0 * np.pi * a)
 
 
-def box_muller_fast(xa, xb):
-    """Latent-noise stream (stream 0), float64 evaluation of the device map (philox.cuh
-    box_muller_fast): u1 = 1 - (xa>>9)*2^-23 in (0,1], theta = 2*pi*((xb>>9)*2^-23 - 0.5) in
-    [-pi,pi).  The device evaluates lg2/sqrt/sin/cos on the special-function unit, so its fp32
-    normals sit within ~1e-6 absolute of these before rounding to the latent dtype."""
-    u1 = 1.0 - (xa >> np.uint32(9)).astype(np.float64) * 2.0 ** -23
-    theta = 2.0 * np.pi * ((xb >> np.uint32(9)).astype(np.float64) * 2.0 ** -23 - 0.5)
+def box_muller_word(x):
+    """Latent-noise stream (stream 0): ONE 32-bit word per pair, 20 radius bits + 12 angle bits
+    (philox.cuh box_muller_word): u1 = 1 - (x>>12)*2^-20 in (0,1], theta = fl32(fma(g, fl32(2 pi),
+    fl32(-3 pi + pi/4096))) with g = 1 + (x&0xfff)*2^-12, i.e. 2 pi ((a+0.5)/4096 - 0.5) in (-pi,pi).
+    The device evaluates lg2/sqrt/sin/cos on the special-function unit, so its fp32 normals sit
+    within ~1e-6 absolute of this float64 evaluation before rounding to the latent dtype."""
+    x = np.asarray(x, dtype=np.uint32)
+    u1 = 1.0 - (x >> np.uint32(12)).astype(np.float64) * 2.0 ** -20
+    g = 1.0 + (x & np.uint32(0xFFF)).astype(np.float64) * 2.0 ** -12
+    two_pi = np.float64(np.float32(6.283185307179586))
+    c = np.float64(np.float32(-9.424010970375436))
+    theta = (g * two_pi + c).astype(np.float32).astype(np.float64)
     r = np.sqrt(-2.0 * np.log(u1))
     return r * np.cos(theta), r * np.sin(theta)
 
 
-def normal_quads(seed, offset, sample, n_quads, stream=0):
-    """Normals for quads 0..n_quads-1 of ``sample`` -> float64 array [n_quads*4].  Stream 0
-    (latent noise) uses the fast map, stream 1 (timestep draw) the precise one."""
-    quad = np.arange(n_quads, dtype=np.uint64)
-    x0, x1, x2, x3 = philox4x32_10(quad, np.uint64(sample), np.uint64(int(offset) & 0xFFFFFFFF),
-                                   np.uint64(_counter_hi(offset, stream)),
-                                   int(seed) & 0xFFFFFFFF, (int(seed) >> 32) & 0xFFFFFFFF)
-    bm = box_muller_fast if stream == 0 else box_muller
-    z0, z1 = bm(x0, x1)
-    z2, z3 = bm(x2, x3)
+def _words(seed, offset, sample, n_calls, stream):
+    ctr = np.arange(n_calls, dtype=np.uint64)
+    return philox4x32_10(ctr, np.uint64(sample), np.uint64(int(offset) & 0xFFFFFFFF),
+                         np.uint64(_counter_hi(offset, stream)),
+                         int(seed) & 0xFFFFFFFF, (int(seed) >> 32) & 0xFFFFFFFF)
+
+
+def normal_octs(seed, offset, sample, n_octs):
+    """Latent normals for octs 0..n_octs-1 of ``sample`` -> float64 array [n_octs*8]: word w of
+    call ``oct`` gives elements 8*oct + 2w (cos) and 8*oct + 2w + 1 (sin)."""
+    xs = _words(seed, offset, sample, n_octs, 0)
+    cols = []
+    for x in xs:
+        z0, z1 = box_muller_word(x)
+        cols += [z0, z1]
+    return np.stack(cols, axis=1).reshape(-1)
+
+
+def normal_quads(seed, offset, sample, n_quads, stream=1):
+    """Timestep stream (stream 1): two full words per pair, precise map -> float64 [n_quads*4]."""
+    x0, x1, x2, x3 = _words(seed, offset, sample, n_quads, stream)
+    z0, z1 = box_muller(x0, x1)
+    z2, z3 = box_muller(x2, x3)
     return np.stack([z0, z1, z2, z3], axis=1).reshape(-1)
 
 
 def noise(seed, offset, batch, chw):
     """fp32 noise [batch, chw] of the generate mode (before rounding to the latent dtype)."""
-    n_quads = (chw + 3) // 4
+    n_octs = (chw + 7) // 8
     out = np.empty((batch, chw), dtype=np.float32)
     for b in range(batch):
-        out[b] = normal_quads(seed, offset, b, n_quads, stream=0)[:chw].astype(np.float32)
+        out[b] = normal_octs(seed, offset, b, n_octs)[:chw].astype(np.float32)
     return out
 
 
@@ -91,8 +110,4 @@ def timestep_normals(seed, offset, batch):
 
 def raw_stream(seed, offset, sample, n_quads, stream=0):
     """Raw uint32 words [n_quads,4] — compared bit-exactly against ``yat_philox_raw``."""
-    quad = np.arange(n_quads, dtype=np.uint64)
-    xs = philox4x32_10(quad, np.uint64(sample), np.uint64(int(offset) & 0xFFFFFFFF),
-                       np.uint64(_counter_hi(offset, stream)),
-                       int(seed) & 0xFFFFFFFF, (int(seed) >> 32) & 0xFFFFFFFF)
-    return np.stack(xs, axis=1)
+    return np.stack(_words(seed, offset, sample, n_quads, stream), axis=1)

@@ -40,6 +40,7 @@ struct LossParams {
   uint4* dpred;
   float* partials;  // [gridDim.x][2]
   unsigned int* counter;
+  PhiloxPlan plan;  // latent-noise stream (noise == NULL), filled by the launcher
 };
 
 __device__ __forceinline__ float block_sum(float v, float* smem) {
@@ -57,10 +58,9 @@ __device__ __forceinline__ float block_sum(float v, float* smem) {
 }
 
 template <bool GEN, bool HAS_PF>
-__global__ void __launch_bounds__(kThreads) loss_fused_kernel(const LossParams p) {
+__global__ void __launch_bounds__(kThreads) loss_fused_kernel(const __grid_constant__ LossParams p) {
   __shared__ float s_red[kThreads / 32];
   __shared__ bool s_last;
-  const PhiloxKey key = make_philox_key(p.seed, p.offset, 0u);
   const bool velocity = p.target_mode == YAT_TARGET_VELOCITY;
   const bool need_x0 = velocity;
   const bool unit_g = p.gscale == 1.0f;   // (x * 1.0f) is the identity: skip the multiply
@@ -70,6 +70,7 @@ __global__ void __launch_bounds__(kThreads) loss_fused_kernel(const LossParams p
     const int b = (int)(tile / p.tiles_per_sample);
     const int chunk = (int)(tile - (int64_t)b * p.tiles_per_sample);
     const float w = p.weights ? p.weights[b] : 1.0f;
+    const PhiloxSample smp = philox_sample(p.plan, (uint32_t)b);
     const uint4* pr = p.pred + (int64_t)b * p.pred_vec_per_sample;
     const uint4* pf = HAS_PF ? p.pred_frozen + (int64_t)b * p.pred_vec_per_sample : nullptr;
     const uint4* x0 = need_x0 ? p.x0 + (int64_t)b * p.vec_per_sample : nullptr;
@@ -93,7 +94,7 @@ __global__ void __launch_bounds__(kThreads) loss_fused_kernel(const LossParams p
     for (int j = 0; j < kUnroll; ++j) {
       const int64_t v = v0 + j * kThreads;
       if (v >= p.vec_per_sample) continue;
-      if (GEN) ev[j] = normal8_bf16(key, (uint32_t)v, (uint32_t)b);
+      if (GEN) ev[j] = normal8_bf16(p.plan, smp, (uint32_t)v);
       const uint32_t pw[4] = {pv[j].x, pv[j].y, pv[j].z, pv[j].w};
       const uint32_t ew[4] = {ev[j].x, ev[j].y, ev[j].z, ev[j].w};
       uint32_t xw[4] = {0, 0, 0, 0}, fw[4] = {0, 0, 0, 0}, gw[4];
@@ -212,6 +213,7 @@ extern "C" int yat_loss_fused(const void* pred, const void* x0, const void* nois
   p.tiles_per_sample = (int)((p.vec_per_sample + kTileVecs - 1) / kTileVecs);
   p.total_tiles = (int64_t)B * p.tiles_per_sample;
   p.loss_out = loss_out; p.dpred = (uint4*)dpred;
+  p.plan = make_philox_plan(seed, offset, 0u);
   p.partials = (float*)workspace;
   p.counter = (unsigned int*)((float*)workspace + 2 * kMaxBlocks);
   const int grid = (int)(p.total_tiles < kMaxBlocks ? p.total_tiles : kMaxBlocks);

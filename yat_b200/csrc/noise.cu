@@ -37,6 +37,7 @@ struct NoiseParams {
   float* sigma_out;    // flow
   int64_t* t_out_i;    // ddpm
   int blocks_per_sample;
+  PhiloxPlan plan;     // latent-noise stream (generate mode), filled by the launcher
 };
 
 template <typename T>
@@ -82,7 +83,7 @@ __device__ __forceinline__ void sample_scalars(const NoiseParams& p, int b, bool
 
 // ---- bf16: 8 elements per 128-bit vector -------------------------------------------------
 template <int MODE, bool GEN>
-__global__ void __launch_bounds__(kThreads) noise_bf16_kernel(const NoiseParams p) {
+__global__ void __launch_bounds__(kThreads) noise_bf16_kernel(const __grid_constant__ NoiseParams p) {
   __shared__ float s_coef[2];
   const int b = blockIdx.x / p.blocks_per_sample;
   const int chunk = blockIdx.x - b * p.blocks_per_sample;
@@ -93,7 +94,7 @@ __global__ void __launch_bounds__(kThreads) noise_bf16_kernel(const NoiseParams 
   uint4* xt = reinterpret_cast<uint4*>(p.x_t) + base;
   uint4* tg = p.target ? reinterpret_cast<uint4*>(p.target) + base : nullptr;
   uint4* no = p.noise_out ? reinterpret_cast<uint4*>(p.noise_out) + base : nullptr;
-  const PhiloxKey key = make_philox_key(p.seed, p.offset, 0u);
+  const PhiloxSample smp = philox_sample(p.plan, (uint32_t)b);
   constexpr int kTile = kThreads * kUnroll;
   const int stride = p.blocks_per_sample * kTile;           // this block's tiles: chunk, chunk + bps, ...
 
@@ -117,7 +118,7 @@ __global__ void __launch_bounds__(kThreads) noise_bf16_kernel(const NoiseParams 
 #pragma unroll
       for (int j = 0; j < kUnroll; ++j) {
         const int v = v0 + j * kThreads;
-        if (v < nvec) ev[j] = normal8_bf16(key, (uint32_t)v, (uint32_t)b);
+        if (v < nvec) ev[j] = normal8_bf16(p.plan, smp, (uint32_t)v);
       }
     }
   };
@@ -163,7 +164,7 @@ __global__ void __launch_bounds__(kThreads) noise_bf16_kernel(const NoiseParams 
 
 // ---- generic: one quad (4 elements) per thread, any dtype / any chw / any alignment ---------
 template <typename T, int MODE, bool GEN>
-__global__ void __launch_bounds__(kThreads) noise_generic_kernel(const NoiseParams p) {
+__global__ void __launch_bounds__(kThreads) noise_generic_kernel(const __grid_constant__ NoiseParams p) {
   __shared__ float s_coef[2];
   const int b = blockIdx.x / p.blocks_per_sample;
   const int chunk = blockIdx.x - b * p.blocks_per_sample;
@@ -185,7 +186,7 @@ __global__ void __launch_bounds__(kThreads) noise_generic_kernel(const NoisePara
   T* tg = p.target ? reinterpret_cast<T*>(p.target) + base : nullptr;
   T* no = p.noise_out ? reinterpret_cast<T*>(p.noise_out) + base : nullptr;
   float z[4];
-  if (GEN) normal4(make_philox_key(p.seed, p.offset, 0u), (uint32_t)quad, (uint32_t)b, z);
+  if (GEN) normal4(p.plan, philox_sample(p.plan, (uint32_t)b), (uint32_t)quad, z);
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int64_t e = quad * 4 + i;
@@ -205,6 +206,7 @@ inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 template <int MODE>
 int launch_noise(NoiseParams p, int dtype, cudaStream_t st) {
   const bool gen = p.noise_in == nullptr;
+  p.plan = make_philox_plan(p.seed, p.offset, 0u);
   const bool vec_ok = dtype == YAT_DTYPE_BF16 && (p.chw % 8 == 0) && aligned16(p.x0) && aligned16(p.x_t) &&
                       (gen || aligned16(p.noise_in)) && (!p.target || aligned16(p.target)) &&
                       (!p.noise_out || aligned16(p.noise_out));

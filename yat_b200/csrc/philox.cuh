@@ -4,8 +4,9 @@
 //
 //   key     = (seed lo, seed hi)
 //   counter = (quad, sample, offset lo, (offset hi & 0x7fffffff) | stream << 31)
-//   stream 0: latent noise — quad = element_index / 4 inside the sample, 4 normals per call
-//   stream 1: timestep draw — quad 0, first normal of the call
+//   stream 0: latent noise — c0 = oct = element_index / 8 inside the sample, 8 normals per call
+//             (one 32-bit word per Box-Muller pair)
+//   stream 1: timestep draw — c0 = 0, first normal of the call (two full words per pair)
 #pragma once
 #include <cuda_bf16.h>
 #include <stdint.h>
@@ -26,12 +27,18 @@ __host__ __device__ __forceinline__ PhiloxKey make_philox_key(uint64_t seed, uin
 }
 
 // 32x32 -> 64 product as ONE IMAD.WIDE.U32 (a C++ 64-bit multiply leaves dead add-zero instructions)
-__device__ __forceinline__ void mul_wide(uint32_t a, uint32_t b, uint32_t& lo, uint32_t& hi) {
+__host__ __device__ __forceinline__ void mul_wide(uint32_t a, uint32_t b, uint32_t& lo, uint32_t& hi) {
+#ifdef __CUDA_ARCH__
   asm("{\n\t.reg .b64 p;\n\tmul.wide.u32 p, %2, %3;\n\tmov.b64 {%0, %1}, p;\n\t}" : "=r"(lo), "=r"(hi) : "r"(a), "r"(b));
+#else
+  const uint64_t p = (uint64_t)a * b;
+  lo = (uint32_t)p;
+  hi = (uint32_t)(p >> 32);
+#endif
 }
 
-__device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
-                                               uint32_t k1) {
+__host__ __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                                        uint32_t k0, uint32_t k1) {
   // one IMAD.WIDE per product and one 3-input LOP3 per xor; the round keys depend on kernel
   // parameters only, so the compiler keeps them in uniform registers.
 #pragma unroll
@@ -49,6 +56,73 @@ __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_
   return make_uint4(c0, c1, c2, c3);
 }
 
+// ---- the bulk stream's Philox with everything launch- or sample-uniform taken out of the loop ----
+// Only counter word c0 (the oct index) varies per thread.  c2/c3/key are launch constants and c1 is
+// the sample, so the second product of round 1, the first product of round 2 and all round keys are
+// uniform: the host folds the launch-level part into PhiloxPlan (kernel parameter -> constant bank
+// operands of the LOP3s), philox_sample() does the per-sample part once per block / tile, and
+// philox_oct() is left with 18 IMAD.WIDE + 19 LOP3 per call, bit-identical to philox4x32_10.
+struct PhiloxPlan {
+  uint32_t rk0[10], rk1[10];  // round keys k0 + r*W0, k1 + r*W1
+  uint32_t m1c2_lo, m1c2_hi;  // 0xCD9E8D57 * c2
+  uint32_t c3k;               // c3 ^ rk1[0]
+};
+struct PhiloxSample {
+  uint32_t a2, b2, b3;        // round-2 / round-3 xor constants of this sample
+};
+
+__host__ __device__ inline PhiloxPlan make_philox_plan(uint64_t seed, uint64_t offset, uint32_t stream_id) {
+  const PhiloxKey k = make_philox_key(seed, offset, stream_id);
+  PhiloxPlan pl;
+  for (int r = 0; r < 10; ++r) {
+    pl.rk0[r] = k.k0 + (uint32_t)r * 0x9E3779B9u;
+    pl.rk1[r] = k.k1 + (uint32_t)r * 0xBB67AE85u;
+  }
+  mul_wide(0xCD9E8D57u, k.c2, pl.m1c2_lo, pl.m1c2_hi);
+  pl.c3k = k.c3 ^ pl.rk1[0];
+  return pl;
+}
+
+__host__ __device__ __forceinline__ PhiloxSample philox_sample(const PhiloxPlan& pl, uint32_t sample) {
+  // after round 1: c0 = hi(M1*c2) ^ sample ^ rk0[0] (uniform), c1 = lo(M1*c2) (uniform)
+  const uint32_t u0 = pl.m1c2_hi ^ sample ^ pl.rk0[0];
+  uint32_t p_lo, p_hi;
+  mul_wide(0xD2511F53u, u0, p_lo, p_hi);          // round 2's first product
+  PhiloxSample s;
+  s.a2 = pl.m1c2_lo ^ pl.rk0[1];
+  s.b2 = p_hi ^ pl.rk1[1];
+  s.b3 = p_lo ^ pl.rk1[2];
+  return s;
+}
+
+__host__ __device__ __forceinline__ uint4 philox_oct(const PhiloxPlan& pl, const PhiloxSample& s, uint32_t oct) {
+  uint32_t lo0, hi0, lo1, hi1;
+  // round 1: only M0*c0 is per-thread
+  mul_wide(0xD2511F53u, oct, lo0, hi0);
+  uint32_t c2 = hi0 ^ pl.c3k, c3 = lo0;
+  // round 2: only M1*c2 is per-thread; c3 of its output is uniform and folded into s.b3
+  mul_wide(0xCD9E8D57u, c2, lo1, hi1);
+  uint32_t c0 = hi1 ^ s.a2, c1 = lo1;
+  c2 = c3 ^ s.b2;
+  // round 3: c3 (uniform) ^ rk1[2] = s.b3
+  mul_wide(0xD2511F53u, c0, lo0, hi0);
+  mul_wide(0xCD9E8D57u, c2, lo1, hi1);
+  c0 = hi1 ^ c1 ^ pl.rk0[2];
+  c1 = lo1;
+  c2 = hi0 ^ s.b3;
+  c3 = lo0;
+#pragma unroll
+  for (int r = 3; r < 10; ++r) {
+    mul_wide(0xD2511F53u, c0, lo0, hi0);
+    mul_wide(0xCD9E8D57u, c2, lo1, hi1);
+    c0 = hi1 ^ c1 ^ pl.rk0[r];
+    c1 = lo1;
+    c2 = hi0 ^ c3 ^ pl.rk1[r];
+    c3 = lo0;
+  }
+  return make_uint4(c0, c1, c2, c3);
+}
+
 // ---- stream 1 (timestep draw, one value per sample): precise Box-Muller -------------------
 // u1 = (2*(xa>>9)+1) * 2^-24 in (0,1) and a = (xb>>8) * 2^-24 in [0,1) are exact in fp32.
 __device__ __forceinline__ void box_muller_precise(uint32_t xa, uint32_t xb, float& z0, float& z1) {
@@ -61,15 +135,21 @@ __device__ __forceinline__ void box_muller_precise(uint32_t xa, uint32_t xb, flo
   z1 = r * s;
 }
 
-// ---- stream 0 (latent noise, the bulk): Box-Muller on the special-function unit --------------
-// The latent stream feeds bf16 (or fp32) tensors at HBM rate, so its transform is 4 MUFU ops per
-// pair (lg2, sqrt, sin, cos) and no integer->float conversion:
-//   f = 1 + (xa>>9)*2^-23 in [1,2)      u1 = 2 - f in (0,1]  (exact)      r = sqrt(-2 ln u1)
-//   g = 1 + (xb>>9)*2^-23 in [1,2)      theta = 2*pi*(g - 1.5) in [-pi,pi)
+// ---- stream 0 (latent noise, the bulk): one 32-bit word per Box-Muller pair -----------------
+// The latent stream feeds bf16 tensors at HBM rate, where the Philox rounds (10 thread
+// instructions per 32-bit word) are the cost that decides the roofline fraction.  A pair of
+// normals therefore takes ONE word - 20 radius bits + 12 angle bits - so a Philox call yields the
+// 8 normals of one 128-bit bf16 vector, and the transform is 4 MUFU ops per pair (lg2, sqrt, sin,
+// cos) with no integer->float conversion:
+//   f = 1 + (x>>12)*2^-20 in [1,2)       u1 = 2 - f in (0,1]  (exact)      r = sqrt(-2 ln u1)
+//   g = 1 + (x&0xfff)*2^-12 in [1,2)     theta = 2*pi*(g - 1.5) + pi/4096 in (-pi,pi)
 //   z0 = r cos(theta), z1 = r sin(theta)
-// |theta| <= pi keeps sin.approx/cos.approx at their 2^-21 absolute accuracy; the oracle
-// (oracle/philox.py box_muller_fast) evaluates the same map in float64 and the test allows the
-// resulting ~1e-6 absolute difference before rounding.  Largest |z| = sqrt(46 ln 2) = 5.65.
+// 4096 angles are finer than the bf16 grid (2^-8 relative) the result is rounded to; the
+// half-step offset keeps the angle set symmetric.  Largest |z| = sqrt(40 ln 2) = 5.27 (the
+// reference's fp32 CPU randn stops at sqrt(48 ln 2) = 5.77).  |theta| < pi keeps sin.approx /
+// cos.approx at their 2^-21 absolute accuracy; the oracle (oracle/philox.py box_muller_word)
+// evaluates the same map in float64 and the test allows the ~1e-6 absolute difference before
+// rounding.  Element e of a sample lives in call (oct) e/8, word (e%8)/2, cos for even e.
 __device__ __forceinline__ float mufu_lg2(float x) {
   float y;
   asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -80,28 +160,41 @@ __device__ __forceinline__ float mufu_sqrt(float x) {
   asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-__device__ __forceinline__ void box_muller_fast(uint32_t xa, uint32_t xb, float& z0, float& z1) {
-  const float f = __uint_as_float((xa >> 9) | 0x3f800000u);
-  const float g = __uint_as_float((xb >> 9) | 0x3f800000u);
+__device__ __forceinline__ void box_muller_word(uint32_t x, float& z0, float& z1) {
+  // mantissa fields placed with one integer multiply-add each (written in PTX: the compiler
+  // otherwise re-expands "shift, and, or" into three instructions per field)
+  uint32_t fb, gb;
+  asm("mad.lo.u32 %0, %1, 8, 0x3f800000;" : "=r"(fb) : "r"(x >> 12));
+  asm("mad.lo.u32 %0, %1, 2048, 0x3f800000;" : "=r"(gb) : "r"(x & 0xfffu));
+  const float f = __uint_as_float(fb), g = __uint_as_float(gb);
   const float u1 = 2.0f - f;
-  const float theta = fmaf(g, 6.283185307179586f, -9.42477796076938f);
-  const float r = mufu_sqrt(-1.3862943611198906f * mufu_lg2(u1));  // -2 ln2 * log2(u1)
+  const float theta = fmaf(g, 6.283185307179586f, -9.424010970375436f);  // -3 pi + pi/4096
+  const float r = mufu_sqrt(-1.3862943611198906f * mufu_lg2(u1));       // -2 ln2 * log2(u1)
   z0 = r * __cosf(theta);
   z1 = r * __sinf(theta);
 }
 
-// four latent-noise normals for quad `quad` of sample `sample`
-__device__ __forceinline__ void normal4(const PhiloxKey& k, uint32_t quad, uint32_t sample, float z[4]) {
-  const uint4 x = philox4x32_10(quad, sample, k.c2, k.c3, k.k0, k.k1);
-  box_muller_fast(x.x, x.y, z[0], z[1]);
-  box_muller_fast(x.z, x.w, z[2], z[3]);
+// eight latent-noise normals of oct `oct` (= 128-bit bf16 vector index) of sample `sample`
+__device__ __forceinline__ void normal8(const PhiloxPlan& pl, const PhiloxSample& s, uint32_t oct, float z[8]) {
+  const uint4 x = philox_oct(pl, s, oct);
+  box_muller_word(x.x, z[0], z[1]);
+  box_muller_word(x.y, z[2], z[3]);
+  box_muller_word(x.z, z[4], z[5]);
+  box_muller_word(x.w, z[6], z[7]);
 }
 
-// eight latent-noise normals of 128-bit vector `v` (quads 2v, 2v+1), rounded to bf16 and packed
-__device__ __forceinline__ uint4 normal8_bf16(const PhiloxKey& k, uint32_t v, uint32_t sample) {
+// four normals of quad `quad` (elements 4*quad .. 4*quad+3): half of oct quad/2 (generic kernel)
+__device__ __forceinline__ void normal4(const PhiloxPlan& pl, const PhiloxSample& s, uint32_t quad, float z[4]) {
+  const uint4 x = philox_oct(pl, s, quad >> 1);
+  const bool odd = quad & 1u;
+  box_muller_word(odd ? x.z : x.x, z[0], z[1]);
+  box_muller_word(odd ? x.w : x.y, z[2], z[3]);
+}
+
+// the same eight normals rounded to bf16 and packed
+__device__ __forceinline__ uint4 normal8_bf16(const PhiloxPlan& pl, const PhiloxSample& s, uint32_t v) {
   float z[8];
-  normal4(k, 2u * v, sample, z);
-  normal4(k, 2u * v + 1u, sample, z + 4);
+  normal8(pl, s, v, z);
   __nv_bfloat162 a = __floats2bfloat162_rn(z[0], z[1]), b = __floats2bfloat162_rn(z[2], z[3]);
   __nv_bfloat162 c = __floats2bfloat162_rn(z[4], z[5]), d = __floats2bfloat162_rn(z[6], z[7]);
   return make_uint4(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b),
