@@ -243,9 +243,11 @@ def _max_over_ranks(ms, dist, device):
 
 
 # algorithmic HBM bytes per launch: per latent element / token
-def _algo_bytes(name, B, chw, N, C):
+def _algo_bytes(name, B, chw, N, C, P=0):
     elems = B * chw
     return {
+        "grad_clip_coef": 2 * P,                 # every bf16 gradient read once
+        "adamw_step": 14 * P,                    # p, g, m, v in + p, m, v out, bf16
         "noise_flowmatch": 4 * elems,            # generate mode: read x0 2 B + write x_t 2 B
         "loss_fused": 6 * elems,                 # read pred 2 + x0 2, write dpred 2 (eps regenerated)
         "linattn_fwd_sm100": 8 * B * N * C,      # q,k,v in + o out, bf16
@@ -379,6 +381,8 @@ def run_own_arm(args):
     N = (cfg.sample_size // cfg.patch_size) ** 2
     C = cfg.num_attention_heads * cfg.attention_head_dim
 
+    n_params = sum(p.numel() for p in trainer.model.parameters() if p.requires_grad)
+
     losses = []
 
     def step_resident(i):
@@ -408,7 +412,7 @@ def run_own_arm(args):
     kernels = {}
     step_ms = ms_local / args.steps
     for name, ts in insitu.items():
-        nbytes = _algo_bytes(name, B, chw, N, C)
+        nbytes = _algo_bytes(name, B, chw, N, C, n_params)
         avg = statistics.mean(ts)
         k = {"timing": "in-situ", "launches_per_step": len(ts) / args.steps, "us": avg * 1e3,
              "share_of_step": (sum(ts) / args.steps) / step_ms}
@@ -463,7 +467,7 @@ def run_own_arm(args):
         "dtype": "bf16", "data": "synthetic",
         "config": {"workload": (WORKLOAD if args.model == "sana_1600m_1024" else f"DEBUG {args.model}")
                    + (f" DEBUG linattn={args.debug_linattn}" if args.debug_linattn else ""),
-                   "global_batch": world * B, "parallelism": f"dp{world}", "optimizer": "AdamW bf16 (fused)",
+                   "global_batch": world * B, "parallelism": f"dp{world}", "optimizer": "AdamW bf16, clip + update as 2 own kernels",
                    "gradient_checkpointing": bool(trainer.pipe.transformer.gradient_checkpointing),
                    "l2": "no explicit flush: one step streams ~3.2 GB of weights + >10 GB of activations (>> 126 MB L2)"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,

@@ -22,6 +22,7 @@
  *   yat_gate_residual_*   utils/patch_sana_attention_layers.py:95,113
  *   yat_glumb_mid_*       GLUMBConv middle, utils/patch_sana_attention_layers.py:106-111
  *   yat_pad_embeddings    train_sana.py:167-179  train_pixart_sigma.py:158-169
+ *   yat_grad_clip_coef / yat_adamw_step   common/trainer.py:245-248,347-348 (clip_grad_norm_ + AdamW.step)
  *   yat_bucket_assign     common/trainer.py:109-120  common/bucket_sampler.py:314-322
  */
 #ifndef YAT_B200_H_
@@ -176,6 +177,28 @@ int yat_glumb_mid_bwd(const void* u, const void* c, const void* w_dw, const void
  */
 int yat_pad_embeddings(const void* packed, const int32_t* offsets, int B, int Lmax, int E,
                        void* padded, int64_t* mask, void* stream);
+
+/* ---- optimiser step: global-norm clip + AdamW (common/trainer.py:347-348) ---------------------
+ * The parameters of one group are described by device tables built once by the caller:
+ *   tensor_tab [T][4] int64 = {param ptr, exp_avg ptr, exp_avg_sq ptr, numel}
+ *   grad_ptrs  [T]    int64 = gradient pointer of each tensor (refreshed every step)
+ *   chunks     [n_chunks][2] int32 = {tensor index, chunk index}; chunk c of a tensor covers elements
+ *              [c * yat_optim_chunk_elems(), ...) of it
+ * yat_grad_clip_coef: norm_coef_out[0] = ||g||_2 over all tensors (fp32 accumulation, fixed order),
+ *   norm_coef_out[1] = min(1, max_norm / (norm + 1e-6))  (torch.nn.utils.clip_grad_norm_).
+ *   workspace = yat_optim_workspace_bytes(n_chunks) bytes, zero before the first call.
+ * yat_adamw_step: torch.optim.AdamW arithmetic (decoupled weight decay, bias correction for `step`
+ *   >= 1) in fp32 on bf16 / fp32 storage; the gradient is first scaled by *clip_coef (device scalar,
+ *   may be NULL = 1) and rounded to its dtype, as clip_grad_norm_ would have left it.  p, m, v are
+ *   updated in place; gradients are not written.
+ */
+int yat_optim_chunk_elems(void);
+int64_t yat_optim_workspace_bytes(int n_chunks);
+int yat_grad_clip_coef(const int64_t* tensor_tab, const int64_t* grad_ptrs, const int32_t* chunks, int n_chunks,
+                       int dtype, float max_norm, float* norm_coef_out, void* workspace, void* stream);
+int yat_adamw_step(const int64_t* tensor_tab, const int64_t* grad_ptrs, const int32_t* chunks, int n_chunks,
+                   int dtype, const float* clip_coef, float lr, float beta1, float beta2, float eps,
+                   float weight_decay, int64_t step, void* stream);
 
 /* ---- bucket assignment (host function; float64 compare, first-minimum wins) ---------------
  *   out[i] = argmin_j |keys[j] - ratios[i]| with strict '<' in table order, or -1 if nkeys==0.

@@ -216,3 +216,29 @@ def test_pixart_and_sd35_hook_surface():
         with pytest.raises(NotImplementedError):
             cls(TrainingParameters())
     assert train_pixart_sigma.PixartSigmaTrainer.max_text_tokens == 300
+
+
+def test_optimizer_oracle_forms_agree_and_no_cpu_fallback():
+    """oracle/optimizer.py: the float64 restatement equals the reference's own torch calls
+    (clip_grad_norm_ + torch.optim.AdamW, common/trainer.py:347-348) in fp32; the product optimizer
+    refuses CPU parameters."""
+    import pytest
+    from oracle import optimizer as oopt
+    g = torch.Generator().manual_seed(0)
+    ps = [torch.randn(s, generator=g) for s in [(5,), (33, 7), (128,)]]
+    m = [torch.zeros_like(p) for p in ps]
+    v = [torch.zeros_like(p) for p in ps]
+    cur, state = [p.clone() for p in ps], None
+    for step in range(1, 4):
+        grads = [torch.randn(p.shape, generator=g) * (0.05 * step) for p in ps]
+        cur, m, v, norm, coef = oopt.exact_step(cur, grads, m, v, step, 1e-2, 0.05)
+        ref, ref_norm, state = oopt.reference_step(ps, grads, state, 1e-2, 0.05)
+        assert abs(float(ref_norm) - norm) <= 1e-5 * norm
+        for a, b in zip(cur, ref):
+            assert (a - b).norm() <= 1e-5 * b.norm()
+    assert coef < 1.0
+    from yat_b200.optim import FusedClipAdamW
+    p = torch.nn.Parameter(torch.zeros(4))
+    p.grad = torch.ones(4)
+    with pytest.raises(ValueError):
+        FusedClipAdamW([p]).step()

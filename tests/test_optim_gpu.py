@@ -1,0 +1,104 @@
+"""Clip + AdamW kernels (yat_grad_clip_coef / yat_adamw_step) vs the oracle restatement of
+common/trainer.py:347-348 (clip_grad_norm_ + torch.optim.AdamW.step)."""
+import pytest
+import torch
+
+from oracle import optimizer as oopt
+
+pytestmark = pytest.mark.gpu
+
+SIZES = [(7,), (2240,), (6, 2240), (65536,), (65537,), (300, 1001), (2240, 2240), (3,), (131072 + 8,)]
+
+
+def _make(dtype, seed, gscale):
+    g = torch.Generator().manual_seed(seed)
+    ps = [torch.randn(s, generator=g).to(dtype) for s in SIZES]
+    gs = [(torch.randn(s, generator=g) * gscale).to(dtype) for s in SIZES]
+    return ps, gs
+
+
+def _ulp_close(got, ref, dtype, max_flip_frac):
+    got, ref = got.float().cpu(), ref.float()
+    mism = got != ref
+    # bf16: one ulp; fp32: the fp32 op chain of the kernel vs one rounding of the float64 result
+    ulp = (2.0 ** -7 if dtype == torch.bfloat16 else 2.0 ** -20) * ref.abs().clamp_min(1e-30)
+    assert ((got - ref).abs() <= ulp * 1.01)[mism].all(), (got - ref).abs().max()
+    assert mism.sum().item() <= max(1, max_flip_frac * mism.numel()), mism.float().mean().item()
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("gscale", [1e-4, 1e-2])   # total norm below / above max_norm = 1
+def test_clip_adamw_matches_oracle(cuda, dtype, gscale):
+    from yat_b200.optim import FusedClipAdamW
+    lr, wd = 1e-2, 0.05
+    ps, gs = _make(dtype, 5, gscale)
+    dev_ps = [torch.nn.Parameter(p.to(cuda)) for p in ps]
+    opt = FusedClipAdamW(dev_ps, lr=lr, weight_decay=wd)
+    ref_ps, ref_state = [p.clone() for p in ps], None
+    for step in range(1, 4):
+        grads = [(g * (1.0 + 0.25 * step)).to(dtype) for g in gs]
+        for p, g in zip(dev_ps, grads):
+            p.grad = g.to(cuda)
+        # the oracle starts every step from the device's own stored state, so one-ulp rounding flips of
+        # an earlier step do not compound into the comparison
+        cur = [p.detach().cpu().clone() for p in dev_ps]
+        m = [opt.state[p]["exp_avg"].cpu().clone() if len(opt.state[p]) else torch.zeros_like(q) for p, q in zip(dev_ps, ps)]
+        v = [opt.state[p]["exp_avg_sq"].cpu().clone() if len(opt.state[p]) else torch.zeros_like(q) for p, q in zip(dev_ps, ps)]
+        opt.step(max_norm=1.0)
+        cur, m, v, norm, coef = oopt.exact_step(cur, grads, m, v, step, lr, wd, max_norm=1.0)
+        ref_ps, ref_norm, ref_state = oopt.reference_step(ps, grads, ref_state, lr, wd, max_norm=1.0)
+        assert abs(opt.last_norm.item() - norm) <= 1e-5 * norm
+        assert (coef < 1.0) == (gscale == 1e-2)
+        # same arithmetic evaluated in float64: identical up to rare one-ulp rounding flips
+        flips = 2e-3 if dtype == torch.bfloat16 else 0.5
+        for p, q in zip(dev_ps, cur):
+            _ulp_close(p.detach(), q, dtype, flips)
+        for p, a, b in zip(dev_ps, m, v):
+            _ulp_close(opt.state[p]["exp_avg"], a, dtype, flips)
+            _ulp_close(opt.state[p]["exp_avg_sq"], b, dtype, flips)
+        # the reference's own torch calls (per-op rounding in the storage dtype): bf16 tolerance of the spec
+        for p0, p, r in zip(ps, dev_ps, ref_ps):
+            du, dr = p.detach().float().cpu() - p0.float(), r.float() - p0.float()
+            tol = 2e-2 if dtype == torch.bfloat16 else 1e-5
+            # updates below the storage resolution of p are rounded away on both sides: compare what moved
+            assert (du - dr).norm() <= tol * dr.norm() + (2.0 ** -8 if dtype == torch.bfloat16 else 1e-7) * p0.float().norm()
+    assert int(opt.state[dev_ps[0]]["step"]) == 3
+
+
+def test_plain_step_and_misaligned_views(cuda):
+    """No clip (coef pointer NULL) and parameters / gradients that are odd-offset views of flat buffers
+    (DDP bucket views): the scalar path must give the same numbers."""
+    from yat_b200.optim import FusedClipAdamW
+    g = torch.Generator().manual_seed(9)
+    n = 70001
+    flat_p = torch.randn(n + 3, generator=g).to(torch.bfloat16)
+    flat_g = (torch.randn(n + 3, generator=g) * 0.1).to(torch.bfloat16)
+    p_view = torch.nn.Parameter(flat_p.to(cuda)[3:])           # 6-byte offset: not 16-byte aligned
+    p_view.grad = flat_g.to(cuda)[1:n + 1]
+    p_al = torch.nn.Parameter(flat_p[3:].clone().to(cuda))
+    p_al.grad = flat_g[1:n + 1].clone().to(cuda)
+    for p in (p_view, p_al):
+        FusedClipAdamW([p], lr=1e-2, weight_decay=0.0).step()
+    assert torch.equal(p_view.detach(), p_al.detach())
+    q, _, _, _, _ = oopt.exact_step([flat_p[3:]], [flat_g[1:n + 1]], [torch.zeros(n, dtype=torch.bfloat16)],
+                                    [torch.zeros(n, dtype=torch.bfloat16)], 1, 1e-2, 0.0, max_norm=None)
+    _ulp_close(p_al.detach(), q[0], torch.bfloat16, 2e-3)
+
+
+def test_deterministic_and_state_dict(cuda):
+    from yat_b200.optim import FusedClipAdamW
+    ps, gs = _make(torch.bfloat16, 11, 1e-2)
+    outs = []
+    for _ in range(2):
+        dev = [torch.nn.Parameter(p.to(cuda)) for p in ps]
+        opt = FusedClipAdamW(dev, lr=1e-3)
+        for p, g in zip(dev, gs):
+            p.grad = g.to(cuda)
+        opt.clip_and_step(1.0)
+        outs.append(([p.detach().clone() for p in dev], opt.last_norm.clone()))
+    assert all(torch.equal(a, b) for a, b in zip(outs[0][0], outs[1][0])) and torch.equal(outs[0][1], outs[1][1])
+    sd = opt.state_dict()
+    ref = torch.optim.AdamW([torch.nn.Parameter(p.clone()) for p in ps], lr=1e-3)
+    assert set(sd["param_groups"][0]) >= {"lr", "betas", "eps", "weight_decay", "params"}
+    assert set(sd["state"][0]) == {"step", "exp_avg", "exp_avg_sq"}
+    ref.load_state_dict(sd)   # layout-compatible with torch.optim.AdamW

@@ -47,6 +47,11 @@ SIGNATURES = {
                                   c_void_p]),
     "yat_glumb_mid_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                                   c_void_p, c_void_p, c_void_p, c_void_p]),
+    "yat_optim_chunk_elems": (c_int, []),
+    "yat_optim_workspace_bytes": (c_int64, [c_int]),
+    "yat_grad_clip_coef": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p]),
+    "yat_adamw_step": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_float, c_float, c_float,
+                               c_float, c_float, c_int64, c_void_p]),
     "yat_pad_embeddings": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "yat_bucket_assign": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p]),
     "yat_philox_raw": (c_int, [c_uint64, c_uint64, c_uint32, c_uint32, c_int, c_void_p, c_void_p]),
@@ -59,7 +64,8 @@ _lib = None
 LAUNCHING = ("yat_noise_flowmatch", "yat_noise_ddpm", "yat_loss_fused", "yat_repa_cos", "yat_linattn_fwd",
              "yat_linattn_bwd", "yat_linattn_fwd_simt", "yat_linattn_bwd_simt", "yat_pad_embeddings",
              "yat_philox_raw", "yat_ln_modulate_fwd", "yat_ln_modulate_bwd", "yat_gate_residual_fwd",
-             "yat_gate_residual_bwd", "yat_glumb_mid_fwd", "yat_glumb_mid_bwd")
+             "yat_gate_residual_bwd", "yat_glumb_mid_fwd", "yat_glumb_mid_bwd", "yat_grad_clip_coef",
+             "yat_adamw_step")
 launch_counts = {name: 0 for name in LAUNCHING}
 
 

@@ -117,8 +117,12 @@ class Model:
             os.makedirs("models", exist_ok=True)
         self.sampler = self.make_sampler()
         trainable = [p for p in self.model.parameters() if p.requires_grad]
-        self.optimizer = torch.optim.AdamW(trainable, lr=params.learning_rate, weight_decay=params.weight_decay,
-                                           fused=self.accelerator.device.type == "cuda")
+        if self.accelerator.device.type == "cuda":
+            # clip_grad_norm_ + AdamW.step as two persistent kernels (common/trainer.py:245-248,347-348)
+            from .optim import FusedClipAdamW
+            self.optimizer = FusedClipAdamW(trainable, lr=params.learning_rate, weight_decay=params.weight_decay)
+        else:   # host-logic tests only (gloo, world_size 2): the product path is CUDA
+            self.optimizer = torch.optim.AdamW(trainable, lr=params.learning_rate, weight_decay=params.weight_decay)
         self.model = self.accelerator.prepare(self.model)
         if params.warmup_steps is not None:
             warm = params.warmup_steps
@@ -142,8 +146,11 @@ class Model:
             loss = self.optimize(ratio, latents, embeddings, repa_features, generator)
             self.accelerator.backward(loss)
             if self.accelerator.sync_gradients:
-                self.accelerator.clip_grad_norm_(self.model.parameters(), max_norm=1.0)
-                self.optimizer.step()
+                if hasattr(self.optimizer, "clip_and_step"):
+                    self.optimizer.clip_and_step(max_norm=1.0)                  # (:347-348) fused
+                else:
+                    self.accelerator.clip_grad_norm_(self.model.parameters(), max_norm=1.0)
+                    self.optimizer.step()
                 if self.lr_scheduler is not None:
                     self.lr_scheduler.step()
                 self.optimizer.zero_grad(set_to_none=True)
