@@ -256,8 +256,8 @@ def _algo_bytes(name, B, chw, N, C, P=0):
         "ln_modulate_bwd": 6 * B * N * C,        # x, dy in, dx out (the column pass re-reads x, dy: counted as waste)
         "gate_residual_fwd": 6 * B * N * C,      # res, y in, out
         "gate_residual_bwd": 6 * B * N * C,      # dout, y in, dy out
-        "glumb_mid_fwd": 15 * B * N * C,         # u in (2 * 2.5 C * 2 B) + mid out (2.5 C * 2 B) per token
-        "glumb_mid_bwd": 25 * B * N * C,         # u, dmid in, du out (dc scratch write + read not counted)
+        "glumb_mid_fwd": 25 * B * N * C,         # u in (10 C) + mid out (5 C) + c out (10 C, kept for the backward)
+        "glumb_mid_bwd": 35 * B * N * C,         # u, c (10 C each), dmid (5 C) in; du (10 C) out
     }.get(name)
 
 

@@ -159,12 +159,12 @@ int yat_gate_residual_bwd(const void* dout, const void* y, const void* gate, int
  * utils/patch_sana_attention_layers.py:106-111 -> GLUMBConv: SiLU, depthwise 3x3 (+bias, zero pad 1),
  * chunk, x * SiLU(gate).  Token-major (NHWC):
  *   u [B, H, W, 2*Hd] bf16 (conv_inverted output)   w_dw [2*Hd, 9] bf16   b_dw [2*Hd] bf16
- *   mid [B, H, W, Hd] bf16 (conv_point input);  Hd % 8 == 0 (any H, W: the image is tiled in 8-column strips)
+ *   mid [B, H, W, Hd] bf16 (conv_point input);  Hd % 8 == 0 (any H, W: the image is cut into 4-row strips)
  * fwd optionally writes c [B, H, W, 2*Hd] bf16 = the depthwise-conv output (what autograd would keep);
  * bwd: (u, c, dmid) -> du [B,H,W,2*Hd], dw [2*Hd, 9] bf16, db [2*Hd] bf16;
- * workspace = yat_glumb_workspace_bytes(B, W, Hd) bytes (fixed-order partial sums).
+ * workspace = yat_glumb_workspace_bytes(B, H, Hd) bytes (fixed-order partial sums).
  */
-int64_t yat_glumb_workspace_bytes(int B, int W, int Hd);
+int64_t yat_glumb_workspace_bytes(int B, int H, int Hd);
 int yat_glumb_mid_fwd(const void* u, const void* w_dw, const void* b_dw, int B, int H, int W, int Hd,
                       void* mid, void* c_out, void* stream);
 int yat_glumb_mid_bwd(const void* u, const void* c, const void* w_dw, const void* dmid,

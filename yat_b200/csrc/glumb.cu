@@ -7,30 +7,33 @@
 //   c   = depthwise3x3(s; w[2*Hd][3][3]) + b        (zero padding 1, fp32 accumulation)
 //   mid = c[:Hd] * silu(c[Hd:])        [B, H, W, Hd] bf16   -> input of conv_point (1x1 GEMM)
 //
-// Token-major (= NHWC) throughout: channels are the contiguous axis, so every global access is a
-// full 128-byte line per 64 channels and there are no NCHW<->NHWC permutes around the convolutions.
+// Token-major (= NHWC) throughout: channels are the contiguous axis, so every warp access is one full
+// 128-byte line (32 lanes x one bf16 channel pair) and there are no NCHW<->NHWC permutes.
 //
-// One CTA = (sample b, 8 image columns, 64 channel pairs) sweeping the rows y = 0..H-1.  A 4-row ring in
-// shared memory holds silu(u) in fp32 (each u element is loaded and activated once per tile, one halo
-// column each side); warp w owns column w, lane l the channel pairs (c0+2l, c0+2l+1) and their two gate
-// channels.  Each thread keeps its 3x3x4 window and its 9x4 weights in registers and slides down the
-// column: 6 shared-memory loads and 36 FMAs per row, no cross-lane traffic.  The global loads of row y+2
-// are issued before the stencil of row y and committed after it.  The kernels are instruction-bound
-// (~40 thread instructions per output), which is why the activation costs a single MUFU op.
+// Register-strip design, no shared memory, no barriers in the sweep: lane = channel pair, warp = a strip
+// of kR = 4 image rows, and the warp sweeps x = 0 .. W-1.  Each step loads ONE image column of the strip
+// (kR + 2 rows with the halo, straight from global memory into registers, issued one step ahead), applies
+// SiLU once per loaded element, and scatters the column into three sets of fp32 accumulators - the outputs
+// at x-1, x and x+1 - so every conv output costs its 9 FMAs and nothing else is kept: ~21 thread
+// instructions per conv output against 38 for the shared-memory ring version this replaces (ncu:
+// 222 M warp instructions per SANA-1.6B layer, 58 % issue-busy, 25 % occupancy, a barrier per row).  The
+// halo rows are re-read by the neighbouring warp of the same CTA (L1/L2 hits, not HBM).
 //
-// Backward (one kernel, same sweep, 512 threads): the forward also stores c = conv output (bf16, what the
-// reference keeps for autograd anyway); the loader forms dc = [dmid * silu(g) | dmid * xa * silu'(g)] on the
-// way into the ring, the stencil threads compute du = (depthwise3x3^T dc) * silu'(u) and accumulate
-// dw[k] += silu(u) * dc[tap k], db += dc; per-CTA partial sums -> fixed-order finish (deterministic).
+// Backward (same sweep; CTA = one half, A or gate; warp = row strip): the forward also stores c = conv output
+// (bf16, what the reference keeps for autograd anyway); every step forms one column of
+// dc = [dmid * silu(g) | dmid * xa * silu'(g)] in registers (dc never touches HBM), keeps a 3-column window of
+// it, and computes du = (depthwise3x3^T dc) * silu'(u) together with dw[k] += silu(u) * dc[tap k], db += dc;
+// per-CTA partial sums -> fixed-order finish (deterministic).
 #include "common.cuh"
 
 namespace yat {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kRing = 4;
-constexpr int kTW = 8;                                       // image columns per CTA (= warps)
-constexpr int kRowFloats = (kTW + 2) * 128;                  // one ring row: [kTW + 2][128] fp32
+constexpr int kR = 4;                              // output rows per warp
+constexpr int kIn = kR + 2;                        // input rows per column (halo above and below)
+constexpr int kFwdStrips = kThreads / 32;          // row strips per forward CTA (8 -> 32 rows)
+constexpr int kBwdStrips = kThreads / 32;          // row strips per backward CTA (8 -> 32 rows; one half per CTA)
 
 // silu through ONE special-function op:  sigmoid(x) = 0.5 + 0.5 tanh(x / 2)  =>  silu(x) = h + h tanh(h), h = x / 2.
 // tanh.approx.f32 has 2^-11 relative error, i.e. |error(silu)| <= 2.5e-4 |x|: below the bf16 rounding of the
@@ -44,373 +47,293 @@ __device__ __forceinline__ float silu_f(float x) {
   const float h = 0.5f * x;
   return fmaf(h, tanh_approx(h), h);
 }
-__device__ __forceinline__ void unpack8(const uint4& v, float f[8]) {
-  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
-  f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+// s = silu(x), d = silu'(x) = sg (1 + x (1 - sg))
+__device__ __forceinline__ void silu_and_grad(float x, float& s, float& d) {
+  const float sg = fmaf(0.5f, tanh_approx(0.5f * x), 0.5f);
+  s = x * sg;
+  d = sg * fmaf(x, 1.0f - sg, 1.0f);
+}
+__device__ __forceinline__ uint32_t ldg32(const __nv_bfloat16* q) {
+  return __ldg(reinterpret_cast<const uint32_t*>(q));
 }
 
 struct GlumbParams {
   const __nv_bfloat16* u;     // [B, H, W, 2*Hd]
   const __nv_bfloat16* w;     // [2*Hd, 9]
   const __nv_bfloat16* bias;  // [2*Hd]
-  const __nv_bfloat16* dmid;  // [B, H, W, Hd]   (dc kernel)
+  const __nv_bfloat16* dmid;  // [B, H, W, Hd]   (backward)
   __nv_bfloat16* mid;         // [B, H, W, Hd]   (forward)
   __nv_bfloat16* c;           // [B, H, W, 2*Hd] conv output: forward out (optional), backward in
   __nv_bfloat16* du;          // [B, H, W, 2*Hd]
-  float* partial;             // [B * x-tiles, 2*Hd, 10] (backward)
+  float* partial;             // [B * y-tiles, 2*Hd, 10] (backward)
   int B, H, W, Hd;
 };
 
-// One ring row = [kTW + 2 columns][128 channels] fp32; ring column j <-> image column x0 - 1 + j.
-// Row loader: 160 of the 256 threads own one 128-bit vector (8 bf16 channels) of every row.  The vector
-// travels global -> raw staging ring (cp.async, kDepth rows ahead, no registers held) -> [silu] -> fp32 ring.
-// Only the issuing thread reads its staged vector back, so cp.async.wait_group is all the ordering it needs.
-constexpr int kDepth = 8;                                     // rows in flight per CTA
-
-struct RowLoader {
-  // rows are issued and committed strictly in order 0, 1, 2, ...: running pointers, no per-row index math
-  const __nv_bfloat16* next;  // source of this thread's vector in the next row to issue
-  int64_t row_stride;         // elements between image rows
-  int H;
-  int j, v;                   // this thread's ring column / vector
-  bool active, valid;         // valid: inside the image and inside the channel range
-  uint4* stage;               // this thread's slot in stage row 0; rows are kStageRowVecs apart
-  int issue_row = 0, commit_row = 0;
-  static constexpr int kStageRowVecs = (kTW + 2) * 16;
-  __device__ __forceinline__ void issue() {                    // always commits a group (possibly empty)
-    if (active && valid && issue_row < H) {
-      const uint32_t dst = (uint32_t)__cvta_generic_to_shared(stage + (issue_row & (kDepth - 1)) * kStageRowVecs);
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(next) : "memory");
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    next += row_stride;
-    ++issue_row;
-  }
-  // the row being committed was issued kDepth - 1 groups before the newest one
-  template <bool SILU>
-  __device__ __forceinline__ void commit(float* ring_row) {
-    asm volatile("cp.async.wait_group %0;" ::"n"(kDepth - 1) : "memory");
-    const int r = commit_row++;
-    if (!active) return;
-    float f[8];
-#pragma unroll
-    for (int e = 0; e < 8; ++e) f[e] = 0.f;
-    if (valid && r < H) {
-      unpack8(stage[(r & (kDepth - 1)) * kStageRowVecs], f);
-      if (SILU) {
-#pragma unroll
-        for (int e = 0; e < 8; ++e) f[e] = silu_f(f[e]);
-      }
-    }
-    float4* d = reinterpret_cast<float4*>(ring_row + j * 128 + v * 8);
-    d[0] = make_float4(f[0], f[1], f[2], f[3]);
-    d[1] = make_float4(f[4], f[5], f[6], f[7]);
-  }
-};
+inline int fwd_ytiles(int H) { return ((H + kR - 1) / kR + kFwdStrips - 1) / kFwdStrips; }
+inline int bwd_ytiles(int H) { return ((H + kR - 1) / kR + kBwdStrips - 1) / kBwdStrips; }
 
 // ---------------------------------------------------------------------------------------------
 // forward.  Thread values [0,1] = the two A channels ca, ca+1; [2,3] = their gates Hd+ca, Hd+ca+1.
 // Optionally writes c (the depthwise-conv output, bf16) for the backward.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const GlumbParams p) {
-  __shared__ __align__(16) float ring[kRing][kRowFloats];
-  __shared__ __align__(16) uint4 stage[kDepth][RowLoader::kStageRowVecs];
   const int W = p.W, H = p.H, Hd = p.Hd;
-  const int tiles_x = (W + kTW - 1) / kTW;
-  const int b = blockIdx.y / tiles_x, tile = blockIdx.y - b * tiles_x;
-  const int x0 = tile * kTW, c0 = blockIdx.x * 64;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int ytiles = ((H + kR - 1) / kR + kFwdStrips - 1) / kFwdStrips;
+  const int b = blockIdx.y / ytiles, yt = blockIdx.y - b * ytiles;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int y0 = (yt * kFwdStrips + warp) * kR;
+  const int ca = blockIdx.x * 64 + 2 * lane;
+  if (y0 >= H || ca >= Hd) return;                              // no barriers below (Hd is even)
   const int64_t C2 = 2 * (int64_t)Hd;
 
-  RowLoader L;
-  L.H = H;
-  L.row_stride = (int64_t)W * C2;
-  L.active = tid < (kTW + 2) * 16;
-  L.j = tid >> 4; L.v = tid & 15;
-  {
-    const int cl = c0 + 8 * (L.v & 7);                          // A-half channel index
-    const int col = x0 - 1 + L.j;
-    L.valid = col >= 0 && col < W && cl < Hd;
-    L.next = p.u + ((int64_t)b * H * W + (L.valid ? col : 0)) * C2 + (L.v < 8 ? cl : Hd + cl);
-    L.stage = &stage[0][L.active ? tid : 0];
-  }
-  const int ca = c0 + 2 * lane;
-  const int x = x0 + warp;
-  const bool ok = ca < Hd && x < W;                             // Hd is even
-
-  // weights / bias of the CTA's 64 + 64 channels: coalesced into shared memory (the stage ring is still
-  // idle), then 36 + 4 values per thread into registers
   float w[9][4], bias[4];
-  {
-    __nv_bfloat16* wsm = reinterpret_cast<__nv_bfloat16*>(&stage[0][0]);     // [2][64][9] then bias [2][64]
-    for (int i = tid; i < 2 * 64 * 10; i += kThreads) {
-      const int half = i / 640, r = i - half * 640;                           // r < 576: weight, else bias
-      const int cl = r < 576 ? r / 9 : r - 576;
-      float val = 0.f;
-      if (c0 + cl < Hd) {
-        const int64_t cg = (half ? Hd : 0) + c0 + cl;
-        val = __bfloat162float(r < 576 ? p.w[cg * 9 + (r - cl * 9)] : p.bias[cg]);
-      }
-      wsm[i] = __float2bfloat16_rn(val);
-    }
-    __syncthreads();
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int base = (j >> 1) * 640, cl = 2 * lane + (j & 1);
-      bias[j] = __bfloat162float(wsm[base + 576 + cl]);
+  for (int j = 0; j < 4; ++j) {
+    const int64_t ch = (j >> 1) * (int64_t)Hd + ca + (j & 1);
+    bias[j] = __bfloat162float(p.bias[ch]);
 #pragma unroll
-      for (int k = 0; k < 9; ++k) w[k][j] = __bfloat162float(wsm[base + cl * 9 + k]);
-    }
-    __syncthreads();
+    for (int k = 0; k < 9; ++k) w[k][j] = __bfloat162float(p.w[ch * 9 + k]);
   }
-  float win0[3][4], win1[3][4], win2[3][4];
-#pragma unroll
-  for (int kx = 0; kx < 3; ++kx)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) win0[kx][j] = win1[kx][j] = win2[kx][j] = 0.f;
 
-  auto load_cols = [&](const float* ring_row, float (&dst)[3][4]) {
+  // Addressing: running byte pointers (next input column / next output column), advanced once per step; a
+  // row is reached with one 32x32->64 multiply-add (row bytes * constant + pointer).  Rows outside the image
+  // are masked (zero padding: silu(0) = 0); the pointer of row y0-1 = -1 is formed but never dereferenced.
+  const uint32_t col_b = (uint32_t)C2 * 2u, in_row_b = (uint32_t)W * col_b;      // bytes (checked < 2^32 by the launcher)
+  const uint32_t mcol_b = (uint32_t)Hd * 2u, mid_row_b = (uint32_t)W * mcol_b;
+  const char* in_a = reinterpret_cast<const char*>(p.u + (((int64_t)b * H + (y0 - 1)) * W) * C2 + ca);
+  const char* in_g = in_a + mcol_b;
+  uint32_t vmask = 0;
 #pragma unroll
-    for (int kx = 0; kx < 3; ++kx) {
-      const float* px = ring_row + (warp + kx) * 128 + 2 * lane;
-      const float2 a = *reinterpret_cast<const float2*>(px);
-      const float2 g = *reinterpret_cast<const float2*>(px + 64);
-      dst[kx][0] = a.x; dst[kx][1] = a.y; dst[kx][2] = g.x; dst[kx][3] = g.y;
+  for (int i = 0; i < kIn; ++i) vmask |= (y0 - 1 + i >= 0 && y0 - 1 + i < H) ? (1u << i) : 0u;
+  uint32_t ra[kIn], rg[kIn];                                      // raw bf16 pairs of the column in flight
+  auto load_col = [&](int x) {                                    // must be called for x = 0, 1, 2, ... in order
+    const uint32_t m = x < W ? vmask : 0u;
+#pragma unroll
+    for (int i = 0; i < kIn; ++i) {
+      const bool ok = (m >> i) & 1u;
+      ra[i] = ok ? __ldg(reinterpret_cast<const uint32_t*>(in_a + (uint64_t)in_row_b * (uint32_t)i)) : 0u;
+      rg[i] = ok ? __ldg(reinterpret_cast<const uint32_t*>(in_g + (uint64_t)in_row_b * (uint32_t)i)) : 0u;
     }
+    in_a += col_b;
+    in_g += col_b;
   };
 
-  // prologue: rows 0 .. kDepth-1 in flight; rows 0 and 1 activated into the ring
+  char* out_m = reinterpret_cast<char*>(p.mid + (((int64_t)b * H + y0) * W) * Hd + ca);
+  char* out_a = p.c ? reinterpret_cast<char*>(p.c + (((int64_t)b * H + y0) * W) * C2 + ca) : nullptr;
+  char* out_g = out_a + mcol_b;
+  uint32_t omask = 0;
 #pragma unroll
-  for (int r = 0; r < kDepth; ++r) L.issue();
-  L.commit<true>(ring[0]);
-  L.issue();
-  L.commit<true>(ring[1]);
-  __syncthreads();
-  load_cols(ring[0], win1);                        // row 0; row -1 (win0) is zero
+  for (int r = 0; r < kR; ++r) omask |= (y0 + r < H) ? (1u << r) : 0u;
 
-  __nv_bfloat16* mid_ptr = p.mid + (((int64_t)b * H) * W + x) * Hd + ca;
-  __nv_bfloat16* c_ptr = p.c ? p.c + (((int64_t)b * H) * W + x) * C2 + ca : nullptr;
-  const int64_t mid_row = (int64_t)W * Hd, c_row = (int64_t)W * C2;
+  float acc0[kR][4], acc1[kR][4], acc2[kR][4];
+#pragma unroll
+  for (int r = 0; r < kR; ++r)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc0[r][j] = acc1[r][j] = acc2[r][j] = bias[j];
 
-  // rows (y-1, y) are in (ra, rb); row y+1 comes out of the ring into rc
-  auto step = [&](int y, float (&ra)[3][4], float (&rb)[3][4], float (&rc)[3][4]) {
-    L.issue();                                     // row y+1+kDepth: its stage slot held row y+1, activated in step y-1
-    load_cols(ring[(y + 1) % kRing], rc);
-    float acc[4];
+  // step x: input column x feeds the outputs at x-1 (tap kx = 2: aP, finished and written here), x (kx = 1: aC)
+  // and x+1 (kx = 0: aN, started here from the bias).  x = W is the zero column right of the image.
+  auto step = [&](int x, float (&aP)[kR][4], float (&aC)[kR][4], float (&aN)[kR][4]) {
+    float s[kIn][4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      float a = bias[j];
+    for (int i = 0; i < kIn; ++i) {
+      s[i][0] = silu_f(bf16_lo(ra[i])); s[i][1] = silu_f(bf16_hi(ra[i]));
+      s[i][2] = silu_f(bf16_lo(rg[i])); s[i][3] = silu_f(bf16_hi(rg[i]));
+    }
+    load_col(x + 1);                                              // in flight during this step's arithmetic
 #pragma unroll
-      for (int kx = 0; kx < 3; ++kx) {
-        a = fmaf(w[kx][j], ra[kx][j], a);
-        a = fmaf(w[3 + kx][j], rb[kx][j], a);
-        a = fmaf(w[6 + kx][j], rc[kx][j], a);
+    for (int r = 0; r < kR; ++r)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float a = aP[r][j], c = aC[r][j], n = bias[j];
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky) {
+          a = fmaf(w[3 * ky + 2][j], s[r + ky][j], a);
+          c = fmaf(w[3 * ky + 1][j], s[r + ky][j], c);
+          n = fmaf(w[3 * ky + 0][j], s[r + ky][j], n);
+        }
+        aP[r][j] = a; aC[r][j] = c; aN[r][j] = n;
       }
-      acc[j] = a;
-    }
-    if (ok) {
-      // c is what the reference keeps as the bf16 conv output; the GLU uses the same rounded values
-      const uint32_t cxa = pack_bf16(acc[0], acc[1]), cg = pack_bf16(acc[2], acc[3]);
-      if (c_ptr) {
-        *reinterpret_cast<uint32_t*>(c_ptr + y * c_row) = cxa;
-        *reinterpret_cast<uint32_t*>(c_ptr + y * c_row + Hd) = cg;
+    if (x > 0) {
+#pragma unroll
+      for (int r = 0; r < kR; ++r) {
+        if ((omask >> r) & 1u) {
+          // c is what the reference keeps as the bf16 conv output; the GLU uses the same rounded values
+          const uint32_t cxa = pack_bf16(aP[r][0], aP[r][1]), cg = pack_bf16(aP[r][2], aP[r][3]);
+          if (out_a) {
+            *reinterpret_cast<uint32_t*>(out_a + (uint64_t)in_row_b * (uint32_t)r) = cxa;
+            *reinterpret_cast<uint32_t*>(out_g + (uint64_t)in_row_b * (uint32_t)r) = cg;
+          }
+          *reinterpret_cast<uint32_t*>(out_m + (uint64_t)mid_row_b * (uint32_t)r) =
+              pack_bf16(bf16_lo(cxa) * silu_f(bf16_lo(cg)), bf16_hi(cxa) * silu_f(bf16_hi(cg)));
+        }
       }
-      *reinterpret_cast<uint32_t*>(mid_ptr + y * mid_row) =
-          pack_bf16(bf16_lo(cxa) * silu_f(bf16_lo(cg)), bf16_hi(cxa) * silu_f(bf16_hi(cg)));
+      out_m += mcol_b;
+      if (out_a) { out_a += col_b; out_g += col_b; }
     }
-    L.commit<true>(ring[(y + 2) % kRing]);          // row y+2
-    __syncthreads();
   };
-  for (int y0 = 0; y0 < H; y0 += 3) {
-    step(y0, win0, win1, win2);
-    if (y0 + 1 < H) step(y0 + 1, win1, win2, win0);
-    if (y0 + 2 < H) step(y0 + 2, win2, win0, win1);
+  load_col(0);
+  for (int x0 = 0; x0 <= W; x0 += 3) {
+    step(x0, acc0, acc1, acc2);
+    if (x0 + 1 <= W) step(x0 + 1, acc1, acc2, acc0);
+    if (x0 + 2 <= W) step(x0 + 2, acc2, acc0, acc1);
   }
 }
 
 // ---------------------------------------------------------------------------------------------
-// backward, ONE kernel (512 threads): the loader turns the saved conv output c = [xa | g] and dmid into
+// backward, ONE kernel.  CTA = (64 channels of one half, 8 row strips): half 0 owns the A channels (xa), half 1
+// the gates (blockIdx.z); warp = row strip, lane l owns channels 2l, 2l+1 of its half.  With c = [xa | g] saved by the forward,
 //   dc_A = dmid * silu(g)        dc_G = dmid * xa * silu'(g)
-// on the way into the fp32 ring (dc never touches HBM); 16 warps = 8 columns x {A half, gate half}, lane l
-// owns channels 2l, 2l+1 of its half:
 //   ds[q]  = sum_k w[k] * dc[q - k + 1]        du = ds * silu'(u)
 //   dw[k] += silu(u)[q] * dc[q - k + 1]        db += dc[q]
-// dw / db: per-CTA sums over the 8 columns in fixed order -> partial[(b, tile)][channel][10].
+// Step t forms dc column t (kIn rows) into the newest slot of a 3-column register window and finishes the
+// outputs of column t-1.  dw / db: per-CTA sums over its strips in fixed order -> partial[(b, y-tile)][ch][10].
 // ---------------------------------------------------------------------------------------------
-constexpr int kBwdThreads = 512;
-constexpr int kDepthB = 8;
-constexpr int kRingB = 2;                          // row y+1 is read while row y+2 is written
-constexpr int kItems = (kTW + 2) * 32;            // loader work items per row: (column, channel pair): 10 warps' worth
-
-__global__ void __launch_bounds__(kBwdThreads, 1) glumb_bwd_kernel(const GlumbParams p) {
-  __shared__ __align__(16) float ring[kRingB][kRowFloats];
-  __shared__ __align__(16) uint32_t stage[kDepthB][3][kItems];
+template <int KIND>
+__device__ __forceinline__ void glumb_bwd_body(const GlumbParams& p, float (*red)[20][32]) {
   const int W = p.W, H = p.H, Hd = p.Hd;
-  const int tiles_x = (W + kTW - 1) / kTW;
-  const int b = blockIdx.y / tiles_x, tile = blockIdx.y - b * tiles_x;
-  const int x0 = tile * kTW, c0 = blockIdx.x * 64;
-  const int tid = threadIdx.x, wv = tid >> 5, lane = tid & 31;
+  const int ytiles = ((H + kR - 1) / kR + kBwdStrips - 1) / kBwdStrips;
+  constexpr int kind = KIND;
+  const int b = blockIdx.y / ytiles, yt = blockIdx.y - b * ytiles;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int y0 = (yt * kBwdStrips + warp) * kR;
+  const int cl = blockIdx.x * 64 + 2 * lane;
+  const bool live = y0 < H && cl < Hd;
   const int64_t C2 = 2 * (int64_t)Hd;
-  const int64_t img = (int64_t)b * H * W;
-
-  // ---- loader role (threads 0..319): one channel pair (xa, g, dmid of 2 channels) of one ring column
-  const bool l_active = tid < kItems;
-  const int lj = tid >> 5, lp = tid & 31;
-  const int lcol = x0 - 1 + lj, lcl = c0 + 2 * lp;
-  const bool l_valid = l_active && lcol >= 0 && lcol < W && lcl < Hd;
-  // rows are issued and committed strictly in order: running pointers and counters
-  const __nv_bfloat16* l_c = p.c + (img + (l_valid ? lcol : 0)) * C2 + lcl;
-  const __nv_bfloat16* l_dm = p.dmid + (img + (l_valid ? lcol : 0)) * Hd + lcl;
-  const int64_t c_row = (int64_t)W * C2, dm_row = (int64_t)W * Hd;
-  int issue_row = 0, commit_row = 0;
-  auto issue = [&]() {
-    if (l_valid && issue_row < H) {
-      const int s = issue_row & (kDepthB - 1);
-      const uint32_t d0 = (uint32_t)__cvta_generic_to_shared(&stage[s][0][tid]);
-      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d0), "l"(l_c) : "memory");
-      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d0 + 4 * kItems), "l"(l_c + Hd) : "memory");
-      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d0 + 8 * kItems), "l"(l_dm) : "memory");
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    l_c += c_row;
-    l_dm += dm_row;
-    ++issue_row;
-  };
-  auto commit = [&](float* ring_row) {
-    asm volatile("cp.async.wait_group %0;" ::"n"(kDepthB - 1) : "memory");
-    const int r = commit_row++;
-    if (!l_active) return;
-    float da[2] = {0.f, 0.f}, dg[2] = {0.f, 0.f};
-    if (l_valid && r < H) {
-      const int s = r & (kDepthB - 1);
-      const uint32_t rx = stage[s][0][tid], rg = stage[s][1][tid], rd = stage[s][2][tid];
-      const float xa[2] = {bf16_lo(rx), bf16_hi(rx)}, g[2] = {bf16_lo(rg), bf16_hi(rg)}, dm[2] = {bf16_lo(rd), bf16_hi(rd)};
-#pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const float t = tanh_approx(0.5f * g[e]);
-        const float sg = fmaf(0.5f, t, 0.5f);                       // sigmoid(g)
-        da[e] = dm[e] * (g[e] * sg);                                // dmid * silu(g)
-        dg[e] = dm[e] * xa[e] * (sg * fmaf(g[e], 1.0f - sg, 1.0f)); // dmid * xa * silu'(g)
-      }
-    }
-    *reinterpret_cast<float2*>(ring_row + lj * 128 + 2 * lp) = make_float2(da[0], da[1]);
-    *reinterpret_cast<float2*>(ring_row + lj * 128 + 64 + 2 * lp) = make_float2(dg[0], dg[1]);
-  };
-
-  // ---- compute role: warp = (column, half), lane = channel pair
-  const int col = wv >> 1, kind = wv & 1;
-  const int x = x0 + col;
-  const int cl = c0 + 2 * lane;
-  const bool ok = cl < Hd && x < W;
   const int64_t ch = (kind ? Hd : 0) + cl;
-  const int roff = kind * 64 + 2 * lane;
+
   float w[9][2];
-  {
-    __nv_bfloat16* wsm = reinterpret_cast<__nv_bfloat16*>(&stage[0][0][0]);  // [2][64][9], coalesced
-    for (int i = tid; i < 2 * 576; i += kBwdThreads) {
-      const int half = i / 576, r = i - half * 576;
-      wsm[i] = (c0 + r / 9) < Hd ? p.w[((int64_t)(half ? Hd : 0) + c0) * 9 + r] : __float2bfloat16_rn(0.f);
-    }
-    __syncthreads();
-#pragma unroll
-    for (int j = 0; j < 2; ++j)
-#pragma unroll
-      for (int k = 0; k < 9; ++k) w[k][j] = __bfloat162float(wsm[kind * 576 + (2 * lane + j) * 9 + k]);
-    __syncthreads();
-  }
   float dw[9][2], db[2] = {0.f, 0.f};
 #pragma unroll
-  for (int k = 0; k < 9; ++k) dw[k][0] = dw[k][1] = 0.f;
-  float win0[3][2], win1[3][2], win2[3][2];
-#pragma unroll
-  for (int kx = 0; kx < 3; ++kx)
-#pragma unroll
-    for (int j = 0; j < 2; ++j) win0[kx][j] = win1[kx][j] = win2[kx][j] = 0.f;
-  auto load_cols = [&](const float* ring_row, float (&dst)[3][2]) {
-#pragma unroll
-    for (int kx = 0; kx < 3; ++kx) {
-      const float2 d = *reinterpret_cast<const float2*>(ring_row + (col + kx) * 128 + roff);
-      dst[kx][0] = d.x; dst[kx][1] = d.y;
-    }
-  };
-
-#pragma unroll
-  for (int r = 0; r < kDepthB; ++r) issue();
-  commit(ring[0]);
-  __syncthreads();
-  load_cols(ring[0], win1);                        // row 0
-  issue();
-  commit(ring[1]);                                 // row 1
-  __syncthreads();
-
-  // u of this thread's pixel: three rotating registers, requested three rows ahead of their use
-  const __nv_bfloat16* u_ptr = p.u + (img + x) * C2 + ch;
-  __nv_bfloat16* du_ptr = p.du + (img + x) * C2 + ch;
-  const int64_t u_row = (int64_t)W * C2;
-  uint32_t u0 = 0, u1 = 0, u2 = 0;
-  if (ok) {
-    u0 = __ldg(reinterpret_cast<const uint32_t*>(u_ptr));
-    if (H > 1) u1 = __ldg(reinterpret_cast<const uint32_t*>(u_ptr + u_row));
-    if (H > 2) u2 = __ldg(reinterpret_cast<const uint32_t*>(u_ptr + 2 * u_row));
+  for (int k = 0; k < 9; ++k) {
+    dw[k][0] = dw[k][1] = 0.f;
+    w[k][0] = live ? __bfloat162float(p.w[ch * 9 + k]) : 0.f;
+    w[k][1] = live ? __bfloat162float(p.w[(ch + 1) * 9 + k]) : 0.f;
   }
 
-  // dc rows (y-1, y) are in (ra, rb); row y+1 comes out of the ring into rc.
-  // tap (ky, kx) pairs with dc at (y - ky + 1, x - kx + 1): window row 2-ky, window column 2-kx.
-  auto step = [&](int y, float (&ra)[3][2], float (&rb)[3][2], float (&rc)[3][2], uint32_t& ureg) {
-    issue();
-    const uint32_t uraw = ureg;
-    if (ok && y + 3 < H) ureg = __ldg(reinterpret_cast<const uint32_t*>(u_ptr + (y + 3) * u_row));
-    load_cols(ring[(y + 1) & (kRingB - 1)], rc);
-    if (ok) {
-      const float uu[2] = {bf16_lo(uraw), bf16_hi(uraw)};
-      float o[2];
+  if (live) {
+    // Addressing as in the forward: running byte pointers advanced once per step, rows by one multiply-add.
+    const uint32_t col_b = (uint32_t)C2 * 2u, c_row_b = (uint32_t)W * col_b;
+    const uint32_t dcol_b = (uint32_t)Hd * 2u, d_row_b = (uint32_t)W * dcol_b;
+    const char* in_x = reinterpret_cast<const char*>(p.c + (((int64_t)b * H + (y0 - 1)) * W) * C2 + cl);   // xa
+    const char* in_g = in_x + dcol_b;                                                                       // gate
+    const char* in_d = reinterpret_cast<const char*>(p.dmid + (((int64_t)b * H + (y0 - 1)) * W) * Hd + cl);
+    const char* in_u = reinterpret_cast<const char*>(p.u + (((int64_t)b * H + y0) * W) * C2 + ch);
+    char* out_u = reinterpret_cast<char*>(p.du + (((int64_t)b * H + y0) * W) * C2 + ch);
+    uint32_t vmask = 0;
 #pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        const float t = tanh_approx(0.5f * uu[j]);
-        const float sg = fmaf(0.5f, t, 0.5f);
-        const float s = uu[j] * sg;                                  // silu(u)
-        float a = 0.f;
+    for (int i = 0; i < kIn; ++i) vmask |= (y0 - 1 + i >= 0 && y0 - 1 + i < H) ? (1u << i) : 0u;
+    const uint32_t omask = (vmask >> 1) & ((1u << kR) - 1u);
+
+    uint32_t rx[kIn], rgt[kIn], rd[kIn], ru[kR];                  // raw loads in flight: xa (half 1 only), g, dmid, u
+    auto load_col = [&](int x) {                                  // inputs of dc column x; x = 0, 1, 2, ... in order
+      const uint32_t m = x < W ? vmask : 0u;
 #pragma unroll
-        for (int kx = 0; kx < 3; ++kx) {
-          a = fmaf(w[kx][j], rc[2 - kx][j], a);
-          a = fmaf(w[3 + kx][j], rb[2 - kx][j], a);
-          a = fmaf(w[6 + kx][j], ra[2 - kx][j], a);
-          dw[kx][j] = fmaf(s, rc[2 - kx][j], dw[kx][j]);
-          dw[3 + kx][j] = fmaf(s, rb[2 - kx][j], dw[3 + kx][j]);
-          dw[6 + kx][j] = fmaf(s, ra[2 - kx][j], dw[6 + kx][j]);
-        }
-        db[j] += rb[1][j];
-        o[j] = a * (sg * fmaf(uu[j], 1.0f - sg, 1.0f));
+      for (int i = 0; i < kIn; ++i) {
+        const bool ok = (m >> i) & 1u;
+        rgt[i] = ok ? __ldg(reinterpret_cast<const uint32_t*>(in_g + (uint64_t)c_row_b * (uint32_t)i)) : 0u;
+        rd[i] = ok ? __ldg(reinterpret_cast<const uint32_t*>(in_d + (uint64_t)d_row_b * (uint32_t)i)) : 0u;
+        rx[i] = (ok && kind) ? __ldg(reinterpret_cast<const uint32_t*>(in_x + (uint64_t)c_row_b * (uint32_t)i)) : 0u;
       }
-      *reinterpret_cast<uint32_t*>(du_ptr + y * u_row) = pack_bf16(o[0], o[1]);
+      in_x += col_b; in_g += col_b; in_d += dcol_b;
+    };
+    auto load_u = [&](int x) {                                    // u of output column x; x = 0, 1, 2, ... in order
+      const uint32_t m = x < W ? omask : 0u;
+#pragma unroll
+      for (int r = 0; r < kR; ++r)
+        ru[r] = ((m >> r) & 1u) ? __ldg(reinterpret_cast<const uint32_t*>(in_u + (uint64_t)c_row_b * (uint32_t)r)) : 0u;
+      in_u += col_b;
+    };
+
+    float win0[kIn][2], win1[kIn][2], win2[kIn][2];
+#pragma unroll
+    for (int i = 0; i < kIn; ++i) win0[i][0] = win0[i][1] = win1[i][0] = win1[i][1] = win2[i][0] = win2[i][1] = 0.f;
+
+    // step t: dc column t -> cP; outputs of column t-1 from (cM, cC, cP) = dc columns (t-2, t-1, t).
+    // tap (ky, kx) pairs with dc at (y - ky + 1, x - kx + 1): window row r - ky + 2, column kx = 0 -> cP, 1 -> cC, 2 -> cM.
+    auto step = [&](int t, float (&cM)[kIn][2], float (&cC)[kIn][2], float (&cP)[kIn][2]) {
+      if (kind) {
+#pragma unroll
+        for (int i = 0; i < kIn; ++i) {
+          const float g[2] = {bf16_lo(rgt[i]), bf16_hi(rgt[i])}, dm[2] = {bf16_lo(rd[i]), bf16_hi(rd[i])};
+          const float xa[2] = {bf16_lo(rx[i]), bf16_hi(rx[i])};
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const float sg = fmaf(0.5f, tanh_approx(0.5f * g[e]), 0.5f);
+            cP[i][e] = (dm[e] * xa[e]) * (sg * fmaf(g[e], 1.0f - sg, 1.0f));   // dmid * xa * silu'(g)
+          }
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < kIn; ++i) {
+          const float g[2] = {bf16_lo(rgt[i]), bf16_hi(rgt[i])}, dm[2] = {bf16_lo(rd[i]), bf16_hi(rd[i])};
+#pragma unroll
+          for (int e = 0; e < 2; ++e) cP[i][e] = dm[e] * silu_f(g[e]);          // dmid * silu(g)
+        }
+      }
+      load_col(t + 1);
+      if (t > 0) {
+#pragma unroll
+        for (int r = 0; r < kR; ++r) {
+          const float uu[2] = {bf16_lo(ru[r]), bf16_hi(ru[r])};
+          float o[2];
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            float s, d;
+            silu_and_grad(uu[j], s, d);
+            float a = 0.f;
+#pragma unroll
+            for (int ky = 0; ky < 3; ++ky) {
+              const float d0 = cP[r - ky + 2][j], d1 = cC[r - ky + 2][j], d2 = cM[r - ky + 2][j];
+              a = fmaf(w[3 * ky + 0][j], d0, a);
+              a = fmaf(w[3 * ky + 1][j], d1, a);
+              a = fmaf(w[3 * ky + 2][j], d2, a);
+              dw[3 * ky + 0][j] = fmaf(s, d0, dw[3 * ky + 0][j]);
+              dw[3 * ky + 1][j] = fmaf(s, d1, dw[3 * ky + 1][j]);
+              dw[3 * ky + 2][j] = fmaf(s, d2, dw[3 * ky + 2][j]);
+            }
+            db[j] += cC[r + 1][j];
+            o[j] = a * d;
+          }
+          if ((omask >> r) & 1u) *reinterpret_cast<uint32_t*>(out_u + (uint64_t)c_row_b * (uint32_t)r) = pack_bf16(o[0], o[1]);
+        }
+        out_u += col_b;
+      }
+      load_u(t);                                                  // used late in the next step
+    };
+    load_col(0);
+#pragma unroll
+    for (int r = 0; r < kR; ++r) ru[r] = 0u;
+    for (int t0 = 0; t0 <= W; t0 += 3) {
+      step(t0, win0, win1, win2);
+      if (t0 + 1 <= W) step(t0 + 1, win1, win2, win0);
+      if (t0 + 2 <= W) step(t0 + 2, win2, win0, win1);
     }
-    commit(ring[(y + 2) & (kRingB - 1)]);          // row y+2 -> the slot of row y (last read in step y-1)
-    __syncthreads();
-  };
-  for (int y0 = 0; y0 < H; y0 += 3) {
-    step(y0, win0, win1, win2, u0);
-    if (y0 + 1 < H) step(y0 + 1, win1, win2, win0, u1);
-    if (y0 + 2 < H) step(y0 + 2, win2, win0, win1, u2);
   }
 
-  // per-CTA sums over the 8 columns, fixed order (scratch aliases the ring: every read of it is done)
-  float (*red)[2][33] = reinterpret_cast<float (*)[2][33]>(&ring[0][0]);    // [16 warps][2][33]
-  float* part = p.partial + ((int64_t)b * tiles_x + tile) * C2 * 10;
+  // per-CTA sums over the strips, fixed order
 #pragma unroll
   for (int g = 0; g < 10; ++g) {
-    red[wv][0][lane] = g < 9 ? dw[g][0] : db[0];
-    red[wv][1][lane] = g < 9 ? dw[g][1] : db[1];
-    __syncthreads();
-    if (tid < 128) {
-      const int half = tid >> 6, j = (tid >> 5) & 1, l = tid & 31;
-      float s = 0.f;
-#pragma unroll
-      for (int cw = 0; cw < 8; ++cw) s += red[(cw << 1) | half][j][l];
-      const int cq = c0 + 2 * l;
-      if (cq < Hd) part[((half ? Hd : 0) + cq + j) * 10 + g] = s;
-    }
-    __syncthreads();
+    red[warp][2 * g + 0][lane] = g < 9 ? dw[g][0] : db[0];
+    red[warp][2 * g + 1][lane] = g < 9 ? dw[g][1] : db[1];
   }
+  __syncthreads();
+  float* part = p.partial + ((int64_t)b * ytiles + yt) * C2 * 10;
+  for (int i = tid; i < 2 * 10 * 32; i += kThreads) {              // (j, g, lane)
+    const int l = i & 31, g = (i >> 5) % 10, j = i / 320;
+    float s = 0.f;
+#pragma unroll
+    for (int st = 0; st < kBwdStrips; ++st) s += red[st][2 * g + j][l];
+    const int cq = blockIdx.x * 64 + 2 * l;
+    if (cq < Hd) part[((kind ? Hd : 0) + cq + j) * 10 + g] = s;
+  }
+}
+
+// blockIdx.z = half: 0 -> A channels, 1 -> gate channels (separate instantiations: the A half never loads xa)
+__global__ void __launch_bounds__(kThreads, 2) glumb_bwd_kernel(const GlumbParams p) {
+  __shared__ float red[kThreads / 32][20][32];
+  if (blockIdx.z) glumb_bwd_body<1>(p, red);
+  else            glumb_bwd_body<0>(p, red);
 }
 
 __global__ void __launch_bounds__(256) glumb_finish_kernel(const float* __restrict__ partial, int parts, int64_t n10,
@@ -426,20 +349,21 @@ __global__ void __launch_bounds__(256) glumb_finish_kernel(const float* __restri
 }
 
 inline bool aligned16(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; }
-inline int tiles_of(int W) { return (W + kTW - 1) / kTW; }
 
 int check_shape(const char* what, int B, int H, int W, int Hd) {
   YAT_REQUIRE(B > 0 && H > 0 && W > 0 && Hd > 0, YAT_ERR_BAD_ARG, "%s: B=%d H=%d W=%d Hd=%d must be positive", what, B, H, W, Hd);
   YAT_REQUIRE(Hd % 8 == 0, YAT_ERR_UNSUPPORTED, "%s: hidden width %d must be a multiple of 8", what, Hd);
-  YAT_REQUIRE((int64_t)B * tiles_of(W) < 65536, YAT_ERR_UNSUPPORTED, "%s: B * x-tiles = %lld exceeds the grid limit", what,
-              (long long)B * tiles_of(W));
+  YAT_REQUIRE((int64_t)W * Hd * 4 < (1ll << 32), YAT_ERR_UNSUPPORTED, "%s: one image row of u (%lld bytes) exceeds 4 GiB", what,
+              (long long)W * Hd * 4);
+  YAT_REQUIRE((int64_t)B * bwd_ytiles(H) < 65536, YAT_ERR_UNSUPPORTED, "%s: B * y-tiles = %lld exceeds the grid limit", what,
+              (long long)B * bwd_ytiles(H));
   return YAT_OK;
 }
 }  // namespace
 }  // namespace yat
 
-extern "C" int64_t yat_glumb_workspace_bytes(int B, int W, int Hd) {
-  return (int64_t)B * yat::tiles_of(W) * 2 * Hd * 10 * (int64_t)sizeof(float);
+extern "C" int64_t yat_glumb_workspace_bytes(int B, int H, int Hd) {
+  return (int64_t)B * yat::bwd_ytiles(H) * 2 * Hd * 10 * (int64_t)sizeof(float);
 }
 
 extern "C" int yat_glumb_mid_fwd(const void* u, const void* w_dw, const void* b_dw, int B, int H, int W, int Hd,
@@ -453,7 +377,7 @@ extern "C" int yat_glumb_mid_fwd(const void* u, const void* w_dw, const void* b_
   GlumbParams p{};
   p.u = (const __nv_bfloat16*)u; p.w = (const __nv_bfloat16*)w_dw; p.bias = (const __nv_bfloat16*)b_dw;
   p.mid = (__nv_bfloat16*)mid; p.c = (__nv_bfloat16*)c_out; p.B = B; p.H = H; p.W = W; p.Hd = Hd;
-  glumb_fwd_kernel<<<dim3((Hd + 63) / 64, B * tiles_of(W)), kThreads, 0, (cudaStream_t)stream>>>(p);
+  glumb_fwd_kernel<<<dim3((Hd + 63) / 64, B * fwd_ytiles(H)), kThreads, 0, (cudaStream_t)stream>>>(p);
   return check_launch("glumb_mid_fwd");
 }
 
@@ -471,8 +395,8 @@ extern "C" int yat_glumb_mid_bwd(const void* u, const void* c, const void* w_dw,
   p.u = (const __nv_bfloat16*)u; p.c = (__nv_bfloat16*)const_cast<void*>(c); p.w = (const __nv_bfloat16*)w_dw;
   p.dmid = (const __nv_bfloat16*)dmid; p.du = (__nv_bfloat16*)du;
   p.partial = (float*)workspace; p.B = B; p.H = H; p.W = W; p.Hd = Hd;
-  const int parts = B * tiles_of(W);
-  glumb_bwd_kernel<<<dim3((Hd + 63) / 64, parts), kBwdThreads, 0, st>>>(p);
+  const int parts = B * bwd_ytiles(H);
+  glumb_bwd_kernel<<<dim3((Hd + 63) / 64, parts, 2), kThreads, 0, st>>>(p);
   if ((rc = check_launch("glumb_bwd")) != YAT_OK) return rc;
   const int64_t n10 = (int64_t)2 * Hd * 10;
   glumb_finish_kernel<<<(unsigned)((n10 + 255) / 256), 256, 0, st>>>(p.partial, parts, n10, (__nv_bfloat16*)dw,

@@ -47,7 +47,7 @@ class _GlumbMid(torch.autograd.Function):
         du = torch.empty_like(u)
         dw = torch.empty((C2, 9), dtype=torch.bfloat16, device=u.device)
         db = torch.empty((C2,), dtype=torch.bfloat16, device=u.device)
-        ws = torch.empty(_lib.lib().yat_glumb_workspace_bytes(B, W, Hd), dtype=torch.uint8, device=u.device)
+        ws = torch.empty(_lib.lib().yat_glumb_workspace_bytes(B, H, Hd), dtype=torch.uint8, device=u.device)
         with _lib.timed("glumb_mid_bwd"):
             rc = _lib.lib().yat_glumb_mid_bwd(_lib.ptr(u), _lib.ptr(c), _lib.ptr(w), _lib.ptr(dmid), B, H, W, Hd,
                                               _lib.ptr(du), _lib.ptr(dw), _lib.ptr(db), _lib.ptr(ws),
