@@ -197,8 +197,8 @@ int64_t yat_optim_workspace_bytes(int n_chunks);
 int yat_grad_clip_coef(const int64_t* tensor_tab, const int64_t* grad_ptrs, const int32_t* chunks, int n_chunks,
                        int dtype, float max_norm, float* norm_coef_out, void* workspace, void* stream);
 int yat_adamw_step(const int64_t* tensor_tab, const int64_t* grad_ptrs, const int32_t* chunks, int n_chunks,
-                   int dtype, const float* clip_coef, float lr, float beta1, float beta2, float eps,
-                   float weight_decay, int64_t step, void* stream);
+                   int dtype, const float* clip_coef, double lr, double beta1, double beta2, double eps,
+                   double weight_decay, int64_t step, void* stream);
 
 /* ---- bucket assignment (host function; float64 compare, first-minimum wins) ---------------
  *   out[i] = argmin_j |keys[j] - ratios[i]| with strict '<' in table order, or -1 if nkeys==0.

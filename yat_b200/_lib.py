@@ -9,8 +9,8 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libyat_b200.so")
 
-c_void_p, c_int, c_int64, c_uint64, c_uint32, c_float = (
-    ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_float)
+c_void_p, c_int, c_int64, c_uint64, c_uint32, c_float, c_double = (
+    ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_float, ctypes.c_double)
 
 # name -> (restype, argtypes): must list every symbol include/yat_b200.h declares
 SIGNATURES = {
@@ -50,8 +50,8 @@ SIGNATURES = {
     "yat_optim_chunk_elems": (c_int, []),
     "yat_optim_workspace_bytes": (c_int64, [c_int]),
     "yat_grad_clip_coef": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p]),
-    "yat_adamw_step": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_float, c_float, c_float,
-                               c_float, c_float, c_int64, c_void_p]),
+    "yat_adamw_step": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_double, c_double, c_double,
+                               c_double, c_double, c_int64, c_void_p]),
     "yat_pad_embeddings": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "yat_bucket_assign": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p]),
     "yat_philox_raw": (c_int, [c_uint64, c_uint64, c_uint32, c_uint32, c_int, c_void_p, c_void_p]),

@@ -10,14 +10,16 @@
 // Token-major (= NHWC) throughout: channels are the contiguous axis, so every warp access is one full
 // 128-byte line (32 lanes x one bf16 channel pair) and there are no NCHW<->NHWC permutes.
 //
-// Register-strip design, no shared memory, no barriers in the sweep: lane = channel pair, warp = a strip
-// of kR = 4 image rows, and the warp sweeps x = 0 .. W-1.  Each step loads ONE image column of the strip
-// (kR + 2 rows with the halo, straight from global memory into registers, issued one step ahead), applies
-// SiLU once per loaded element, and scatters the column into three sets of fp32 accumulators - the outputs
-// at x-1, x and x+1 - so every conv output costs its 9 FMAs and nothing else is kept: ~21 thread
-// instructions per conv output against 38 for the shared-memory ring version this replaces (ncu:
-// 222 M warp instructions per SANA-1.6B layer, 58 % issue-busy, 25 % occupancy, a barrier per row).  The
-// halo rows are re-read by the neighbouring warp of the same CTA (L1/L2 hits, not HBM).
+// Register-strip design, no CTA barriers in the sweep: lane = channel pair, warp = a strip of kR = 4 image
+// rows, and the warp sweeps x = 0 .. W-1.  Each step consumes ONE image column of the strip (kR + 2 rows with
+// the halo).  The column arrives by TMA: lane 0 issues one cp.async.bulk.tensor box {64 channels, 1 column,
+// kR + 2 rows} per tensor into a warp-private 4-slot shared-memory ring three steps ahead (mbarrier per slot,
+// out-of-image rows / columns zero-filled by the TMA unit), so the threads spend no instructions on
+// addresses, bounds or zero padding and hold no registers for loads in flight.  SiLU is applied once per
+// loaded element and the column is scattered into three sets of fp32 accumulators - the outputs at x-1, x
+// and x+1 - so a conv output costs its 9 FMAs and nothing else is kept.  The halo rows are fetched twice
+// (by neighbouring warps; L2 hits, not HBM).  History (ncu, SANA-1.6B layer): shared-memory ring with a CTA
+// barrier per row 222 M warp instructions / 345 us; register strip with per-thread global loads 186 M / 240 us.
 //
 // Backward (same sweep; CTA = one half, A or gate; warp = row strip): the forward also stores c = conv output
 // (bf16, what the reference keeps for autograd anyway); every step forms one column of
@@ -25,15 +27,25 @@
 // it, and computes du = (depthwise3x3^T dc) * silu'(u) together with dw[k] += silu(u) * dc[tap k], db += dc;
 // per-CTA partial sums -> fixed-order finish (deterministic).
 #include "common.cuh"
+#include "sm100.cuh"
 
 namespace yat {
 namespace {
 
+using namespace sm100;
+
 constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;              // row strips per CTA (8 -> 32 rows)
 constexpr int kR = 4;                              // output rows per warp
 constexpr int kIn = kR + 2;                        // input rows per column (halo above and below)
-constexpr int kFwdStrips = kThreads / 32;          // row strips per forward CTA (8 -> 32 rows)
-constexpr int kBwdStrips = kThreads / 32;          // row strips per backward CTA (8 -> 32 rows; one half per CTA)
+constexpr int kStages = 4;                         // ring slots per warp: columns t .. t+3 resident / in flight
+constexpr int kRowB = 128;                         // bytes of one box row: 64 bf16 channels
+constexpr int kFwdSlotB = 2 * kIn * kRowB;                         // u: A rows | gate rows
+constexpr int kBwdSlotB0 = (2 * kIn + kR) * kRowB;                 // half A:  g | dmid | u
+constexpr int kBwdSlotB1 = (3 * kIn + kR) * kRowB;                 // half G:  g | dmid | u | xa
+constexpr int kBarBytes = kWarps * kStages * 8;
+constexpr int kFwdSmem = kWarps * kStages * kFwdSlotB + kBarBytes;
+constexpr int kBwdSmem = kWarps * kStages * kBwdSlotB1 + kBarBytes;
 
 // silu through ONE special-function op:  sigmoid(x) = 0.5 + 0.5 tanh(x / 2)  =>  silu(x) = h + h tanh(h), h = x / 2.
 // tanh.approx.f32 has 2^-11 relative error, i.e. |error(silu)| <= 2.5e-4 |x|: below the bf16 rounding of the
@@ -53,77 +65,82 @@ __device__ __forceinline__ void silu_and_grad(float x, float& s, float& d) {
   s = x * sg;
   d = sg * fmaf(x, 1.0f - sg, 1.0f);
 }
-__device__ __forceinline__ uint32_t ldg32(const __nv_bfloat16* q) {
-  return __ldg(reinterpret_cast<const uint32_t*>(q));
-}
 
 struct GlumbParams {
-  const __nv_bfloat16* u;     // [B, H, W, 2*Hd]
   const __nv_bfloat16* w;     // [2*Hd, 9]
   const __nv_bfloat16* bias;  // [2*Hd]
-  const __nv_bfloat16* dmid;  // [B, H, W, Hd]   (backward)
-  __nv_bfloat16* mid;         // [B, H, W, Hd]   (forward)
-  __nv_bfloat16* c;           // [B, H, W, 2*Hd] conv output: forward out (optional), backward in
-  __nv_bfloat16* du;          // [B, H, W, 2*Hd]
+  __nv_bfloat16* mid;         // [B, H, W, Hd]   (forward out)
+  __nv_bfloat16* c;           // [B, H, W, 2*Hd] conv output (forward out, optional)
+  __nv_bfloat16* du;          // [B, H, W, 2*Hd] (backward out)
   float* partial;             // [B * y-tiles, 2*Hd, 10] (backward)
   int B, H, W, Hd;
 };
+struct alignas(64) GlumbArgs {
+  CUtensorMap tm_u;           // u    {2*Hd, W, H, B}, box {64, 1, kIn, 1} (forward) / {64, 1, kR, 1} (backward)
+  CUtensorMap tm_c;           // c    {2*Hd, W, H, B}, box {64, 1, kIn, 1}                     (backward)
+  CUtensorMap tm_d;           // dmid {Hd,   W, H, B}, box {64, 1, kIn, 1}                     (backward)
+  GlumbParams p;
+};
 
-inline int fwd_ytiles(int H) { return ((H + kR - 1) / kR + kFwdStrips - 1) / kFwdStrips; }
-inline int bwd_ytiles(int H) { return ((H + kR - 1) / kR + kBwdStrips - 1) / kBwdStrips; }
+inline int ytiles_of(int H) { return ((H + kR - 1) / kR + kWarps - 1) / kWarps; }
 
 // ---------------------------------------------------------------------------------------------
 // forward.  Thread values [0,1] = the two A channels ca, ca+1; [2,3] = their gates Hd+ca, Hd+ca+1.
 // Optionally writes c (the depthwise-conv output, bf16) for the backward.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const GlumbParams p) {
+__global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const __grid_constant__ GlumbArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const GlumbParams& p = a.p;
   const int W = p.W, H = p.H, Hd = p.Hd;
-  const int ytiles = ((H + kR - 1) / kR + kFwdStrips - 1) / kFwdStrips;
+  const int ytiles = ((H + kR - 1) / kR + kWarps - 1) / kWarps;
   const int b = blockIdx.y / ytiles, yt = blockIdx.y - b * ytiles;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int y0 = (yt * kFwdStrips + warp) * kR;
-  const int ca = blockIdx.x * 64 + 2 * lane;
-  if (y0 >= H || ca >= Hd) return;                              // no barriers below (Hd is even)
+  const int y0 = (yt * kWarps + warp) * kR;
+  const int c0 = blockIdx.x * 64, ca = c0 + 2 * lane;
+  if (y0 >= H) return;                                            // whole warp; no CTA barriers below
+  const bool live = ca < Hd;                                      // Hd is even
   const int64_t C2 = 2 * (int64_t)Hd;
+
+  const uint32_t ring = smem_u32(smem) + warp * (kStages * kFwdSlotB);
+  const uint32_t bars = smem_u32(smem) + kWarps * kStages * kFwdSlotB + warp * (kStages * 8);
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < kStages; ++s) mbar_init(bars + 8 * s, 1);
+    fence_barrier_init();
+  }
+  __syncwarp();
+  // column t of this strip (rows y0-1 .. y0+kR, A half then gate half) -> slot t % kStages
+  auto issue = [&](int t) {
+    if (lane == 0) {
+      const int s = t & (kStages - 1);
+      const uint32_t bar = bars + 8 * s, dst = ring + s * kFwdSlotB;
+      mbar_arrive_expect_tx(bar, kFwdSlotB);
+      tma_load_4d(dst, &a.tm_u, bar, c0, t, y0 - 1, b);
+      tma_load_4d(dst + kIn * kRowB, &a.tm_u, bar, Hd + c0, t, y0 - 1, b);
+    }
+  };
+#pragma unroll
+  for (int t = 0; t < kStages - 1; ++t)
+    if (t <= W) issue(t);
 
   float w[9][4], bias[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     const int64_t ch = (j >> 1) * (int64_t)Hd + ca + (j & 1);
-    bias[j] = __bfloat162float(p.bias[ch]);
+    bias[j] = live ? __bfloat162float(p.bias[ch]) : 0.f;
 #pragma unroll
-    for (int k = 0; k < 9; ++k) w[k][j] = __bfloat162float(p.w[ch * 9 + k]);
+    for (int k = 0; k < 9; ++k) w[k][j] = live ? __bfloat162float(p.w[ch * 9 + k]) : 0.f;
   }
 
-  // Addressing: running byte pointers (next input column / next output column), advanced once per step; a
-  // row is reached with one 32x32->64 multiply-add (row bytes * constant + pointer).  Rows outside the image
-  // are masked (zero padding: silu(0) = 0); the pointer of row y0-1 = -1 is formed but never dereferenced.
-  const uint32_t col_b = (uint32_t)C2 * 2u, in_row_b = (uint32_t)W * col_b;      // bytes (checked < 2^32 by the launcher)
+  // outputs: running byte pointers advanced once per step; a row is one 32x32->64 multiply-add away
+  const uint32_t col_b = (uint32_t)C2 * 2u, row_b = (uint32_t)W * col_b;          // bytes (checked < 2^32 by the launcher)
   const uint32_t mcol_b = (uint32_t)Hd * 2u, mid_row_b = (uint32_t)W * mcol_b;
-  const char* in_a = reinterpret_cast<const char*>(p.u + (((int64_t)b * H + (y0 - 1)) * W) * C2 + ca);
-  const char* in_g = in_a + mcol_b;
-  uint32_t vmask = 0;
-#pragma unroll
-  for (int i = 0; i < kIn; ++i) vmask |= (y0 - 1 + i >= 0 && y0 - 1 + i < H) ? (1u << i) : 0u;
-  uint32_t ra[kIn], rg[kIn];                                      // raw bf16 pairs of the column in flight
-  auto load_col = [&](int x) {                                    // must be called for x = 0, 1, 2, ... in order
-    const uint32_t m = x < W ? vmask : 0u;
-#pragma unroll
-    for (int i = 0; i < kIn; ++i) {
-      const bool ok = (m >> i) & 1u;
-      ra[i] = ok ? __ldg(reinterpret_cast<const uint32_t*>(in_a + (uint64_t)in_row_b * (uint32_t)i)) : 0u;
-      rg[i] = ok ? __ldg(reinterpret_cast<const uint32_t*>(in_g + (uint64_t)in_row_b * (uint32_t)i)) : 0u;
-    }
-    in_a += col_b;
-    in_g += col_b;
-  };
-
   char* out_m = reinterpret_cast<char*>(p.mid + (((int64_t)b * H + y0) * W) * Hd + ca);
   char* out_a = p.c ? reinterpret_cast<char*>(p.c + (((int64_t)b * H + y0) * W) * C2 + ca) : nullptr;
   char* out_g = out_a + mcol_b;
   uint32_t omask = 0;
 #pragma unroll
-  for (int r = 0; r < kR; ++r) omask |= (y0 + r < H) ? (1u << r) : 0u;
+  for (int r = 0; r < kR; ++r) omask |= (live && y0 + r < H) ? (1u << r) : 0u;
 
   float acc0[kR][4], acc1[kR][4], acc2[kR][4];
 #pragma unroll
@@ -134,25 +151,32 @@ __global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const GlumbParam
   // step x: input column x feeds the outputs at x-1 (tap kx = 2: aP, finished and written here), x (kx = 1: aC)
   // and x+1 (kx = 0: aN, started here from the bias).  x = W is the zero column right of the image.
   auto step = [&](int x, float (&aP)[kR][4], float (&aC)[kR][4], float (&aN)[kR][4]) {
+    if (x + kStages - 1 <= W) issue(x + kStages - 1);             // into the slot read in step x-1
+    const int s_idx = x & (kStages - 1);
+    mbar_wait(bars + 8 * s_idx, (uint32_t)(x / kStages) & 1u);
+    const uint32_t col = ring + s_idx * kFwdSlotB + lane * 4;
     float s[kIn][4];
 #pragma unroll
     for (int i = 0; i < kIn; ++i) {
-      s[i][0] = silu_f(bf16_lo(ra[i])); s[i][1] = silu_f(bf16_hi(ra[i]));
-      s[i][2] = silu_f(bf16_lo(rg[i])); s[i][3] = silu_f(bf16_hi(rg[i]));
+      uint32_t ra, rg;
+      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(ra) : "r"(col + i * kRowB));
+      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(rg) : "r"(col + (kIn + i) * kRowB));
+      s[i][0] = silu_f(bf16_lo(ra)); s[i][1] = silu_f(bf16_hi(ra));
+      s[i][2] = silu_f(bf16_lo(rg)); s[i][3] = silu_f(bf16_hi(rg));
     }
-    load_col(x + 1);                                              // in flight during this step's arithmetic
+    __syncwarp();                                                 // every lane has read the slot: it may be refilled
 #pragma unroll
     for (int r = 0; r < kR; ++r)
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        float a = aP[r][j], c = aC[r][j], n = bias[j];
+        float pa = aP[r][j], cc = aC[r][j], n = bias[j];
 #pragma unroll
         for (int ky = 0; ky < 3; ++ky) {
-          a = fmaf(w[3 * ky + 2][j], s[r + ky][j], a);
-          c = fmaf(w[3 * ky + 1][j], s[r + ky][j], c);
+          pa = fmaf(w[3 * ky + 2][j], s[r + ky][j], pa);
+          cc = fmaf(w[3 * ky + 1][j], s[r + ky][j], cc);
           n = fmaf(w[3 * ky + 0][j], s[r + ky][j], n);
         }
-        aP[r][j] = a; aC[r][j] = c; aN[r][j] = n;
+        aP[r][j] = pa; aC[r][j] = cc; aN[r][j] = n;
       }
     if (x > 0) {
 #pragma unroll
@@ -161,8 +185,8 @@ __global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const GlumbParam
           // c is what the reference keeps as the bf16 conv output; the GLU uses the same rounded values
           const uint32_t cxa = pack_bf16(aP[r][0], aP[r][1]), cg = pack_bf16(aP[r][2], aP[r][3]);
           if (out_a) {
-            *reinterpret_cast<uint32_t*>(out_a + (uint64_t)in_row_b * (uint32_t)r) = cxa;
-            *reinterpret_cast<uint32_t*>(out_g + (uint64_t)in_row_b * (uint32_t)r) = cg;
+            *reinterpret_cast<uint32_t*>(out_a + (uint64_t)row_b * (uint32_t)r) = cxa;
+            *reinterpret_cast<uint32_t*>(out_g + (uint64_t)row_b * (uint32_t)r) = cg;
           }
           *reinterpret_cast<uint32_t*>(out_m + (uint64_t)mid_row_b * (uint32_t)r) =
               pack_bf16(bf16_lo(cxa) * silu_f(bf16_lo(cg)), bf16_hi(cxa) * silu_f(bf16_hi(cg)));
@@ -172,7 +196,6 @@ __global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const GlumbParam
       if (out_a) { out_a += col_b; out_g += col_b; }
     }
   };
-  load_col(0);
   for (int x0 = 0; x0 <= W; x0 += 3) {
     step(x0, acc0, acc1, acc2);
     if (x0 + 1 <= W) step(x0 + 1, acc1, acc2, acc0);
@@ -182,25 +205,28 @@ __global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const GlumbParam
 
 // ---------------------------------------------------------------------------------------------
 // backward, ONE kernel.  CTA = (64 channels of one half, 8 row strips): half 0 owns the A channels (xa), half 1
-// the gates (blockIdx.z); warp = row strip, lane l owns channels 2l, 2l+1 of its half.  With c = [xa | g] saved by the forward,
+// the gates (blockIdx.z); warp = row strip, lane l owns channels 2l, 2l+1 of its half.  With c = [xa | g] saved
+// by the forward,
 //   dc_A = dmid * silu(g)        dc_G = dmid * xa * silu'(g)
 //   ds[q]  = sum_k w[k] * dc[q - k + 1]        du = ds * silu'(u)
 //   dw[k] += silu(u)[q] * dc[q - k + 1]        db += dc[q]
 // Step t forms dc column t (kIn rows) into the newest slot of a 3-column register window and finishes the
-// outputs of column t-1.  dw / db: per-CTA sums over its strips in fixed order -> partial[(b, y-tile)][ch][10].
+// outputs of column t-1; ring slot t holds the dc inputs of column t and u of column t-1.
+// dw / db: per-CTA sums over its strips in fixed order -> partial[(b, y-tile)][ch][10].
 // ---------------------------------------------------------------------------------------------
 template <int KIND>
-__device__ __forceinline__ void glumb_bwd_body(const GlumbParams& p, float (*red)[20][32]) {
+__device__ __forceinline__ void glumb_bwd_body(const GlumbArgs& a, uint8_t* smem) {
+  constexpr int kSlotB = KIND ? kBwdSlotB1 : kBwdSlotB0;
+  const GlumbParams& p = a.p;
   const int W = p.W, H = p.H, Hd = p.Hd;
-  const int ytiles = ((H + kR - 1) / kR + kBwdStrips - 1) / kBwdStrips;
-  constexpr int kind = KIND;
+  const int ytiles = ((H + kR - 1) / kR + kWarps - 1) / kWarps;
   const int b = blockIdx.y / ytiles, yt = blockIdx.y - b * ytiles;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int y0 = (yt * kBwdStrips + warp) * kR;
-  const int cl = blockIdx.x * 64 + 2 * lane;
-  const bool live = y0 < H && cl < Hd;
+  const int y0 = (yt * kWarps + warp) * kR;
+  const int c0 = blockIdx.x * 64, cl = c0 + 2 * lane;
+  const bool live = cl < Hd;
   const int64_t C2 = 2 * (int64_t)Hd;
-  const int64_t ch = (kind ? Hd : 0) + cl;
+  const int64_t ch = (KIND ? Hd : 0) + cl;
 
   float w[9][2];
   float dw[9][2], db[2] = {0.f, 0.f};
@@ -211,39 +237,36 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbParams& p, float (*red
     w[k][1] = live ? __bfloat162float(p.w[(ch + 1) * 9 + k]) : 0.f;
   }
 
-  if (live) {
-    // Addressing as in the forward: running byte pointers advanced once per step, rows by one multiply-add.
-    const uint32_t col_b = (uint32_t)C2 * 2u, c_row_b = (uint32_t)W * col_b;
-    const uint32_t dcol_b = (uint32_t)Hd * 2u, d_row_b = (uint32_t)W * dcol_b;
-    const char* in_x = reinterpret_cast<const char*>(p.c + (((int64_t)b * H + (y0 - 1)) * W) * C2 + cl);   // xa
-    const char* in_g = in_x + dcol_b;                                                                       // gate
-    const char* in_d = reinterpret_cast<const char*>(p.dmid + (((int64_t)b * H + (y0 - 1)) * W) * Hd + cl);
-    const char* in_u = reinterpret_cast<const char*>(p.u + (((int64_t)b * H + y0) * W) * C2 + ch);
-    char* out_u = reinterpret_cast<char*>(p.du + (((int64_t)b * H + y0) * W) * C2 + ch);
-    uint32_t vmask = 0;
+  if (y0 < H) {                                                   // whole warp
+    const uint32_t ring = smem_u32(smem) + warp * (kStages * kSlotB);
+    const uint32_t bars = smem_u32(smem) + kWarps * kStages * kBwdSlotB1 + warp * (kStages * 8);
+    if (lane == 0) {
 #pragma unroll
-    for (int i = 0; i < kIn; ++i) vmask |= (y0 - 1 + i >= 0 && y0 - 1 + i < H) ? (1u << i) : 0u;
-    const uint32_t omask = (vmask >> 1) & ((1u << kR) - 1u);
-
-    uint32_t rx[kIn], rgt[kIn], rd[kIn], ru[kR];                  // raw loads in flight: xa (half 1 only), g, dmid, u
-    auto load_col = [&](int x) {                                  // inputs of dc column x; x = 0, 1, 2, ... in order
-      const uint32_t m = x < W ? vmask : 0u;
-#pragma unroll
-      for (int i = 0; i < kIn; ++i) {
-        const bool ok = (m >> i) & 1u;
-        rgt[i] = ok ? __ldg(reinterpret_cast<const uint32_t*>(in_g + (uint64_t)c_row_b * (uint32_t)i)) : 0u;
-        rd[i] = ok ? __ldg(reinterpret_cast<const uint32_t*>(in_d + (uint64_t)d_row_b * (uint32_t)i)) : 0u;
-        rx[i] = (ok && kind) ? __ldg(reinterpret_cast<const uint32_t*>(in_x + (uint64_t)c_row_b * (uint32_t)i)) : 0u;
+      for (int s = 0; s < kStages; ++s) mbar_init(bars + 8 * s, 1);
+      fence_barrier_init();
+    }
+    __syncwarp();
+    // slot t % kStages <- g, dmid (and xa) of column t, rows y0-1 .. y0+kR; u of column t-1, rows y0 .. y0+kR-1
+    auto issue = [&](int t) {
+      if (lane == 0) {
+        const int s = t & (kStages - 1);
+        const uint32_t bar = bars + 8 * s, dst = ring + s * kSlotB;
+        mbar_arrive_expect_tx(bar, kSlotB);
+        tma_load_4d(dst, &a.tm_c, bar, Hd + c0, t, y0 - 1, b);
+        tma_load_4d(dst + kIn * kRowB, &a.tm_d, bar, c0, t, y0 - 1, b);
+        tma_load_4d(dst + 2 * kIn * kRowB, &a.tm_u, bar, (KIND ? Hd : 0) + c0, t - 1, y0, b);
+        if (KIND) tma_load_4d(dst + (2 * kIn + kR) * kRowB, &a.tm_c, bar, c0, t, y0 - 1, b);
       }
-      in_x += col_b; in_g += col_b; in_d += dcol_b;
     };
-    auto load_u = [&](int x) {                                    // u of output column x; x = 0, 1, 2, ... in order
-      const uint32_t m = x < W ? omask : 0u;
 #pragma unroll
-      for (int r = 0; r < kR; ++r)
-        ru[r] = ((m >> r) & 1u) ? __ldg(reinterpret_cast<const uint32_t*>(in_u + (uint64_t)c_row_b * (uint32_t)r)) : 0u;
-      in_u += col_b;
-    };
+    for (int t = 0; t < kStages - 1; ++t)
+      if (t <= W) issue(t);
+
+    const uint32_t col_b = (uint32_t)C2 * 2u, row_b = (uint32_t)W * col_b;
+    char* out_u = reinterpret_cast<char*>(p.du + (((int64_t)b * H + y0) * W) * C2 + ch);
+    uint32_t omask = 0;
+#pragma unroll
+    for (int r = 0; r < kR; ++r) omask |= (live && y0 + r < H) ? (1u << r) : 0u;
 
     float win0[kIn][2], win1[kIn][2], win2[kIn][2];
 #pragma unroll
@@ -252,26 +275,34 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbParams& p, float (*red
     // step t: dc column t -> cP; outputs of column t-1 from (cM, cC, cP) = dc columns (t-2, t-1, t).
     // tap (ky, kx) pairs with dc at (y - ky + 1, x - kx + 1): window row r - ky + 2, column kx = 0 -> cP, 1 -> cC, 2 -> cM.
     auto step = [&](int t, float (&cM)[kIn][2], float (&cC)[kIn][2], float (&cP)[kIn][2]) {
-      if (kind) {
+      if (t + kStages - 1 <= W) issue(t + kStages - 1);           // into the slot read in step t-1
+      const int s_idx = t & (kStages - 1);
+      mbar_wait(bars + 8 * s_idx, (uint32_t)(t / kStages) & 1u);
+      const uint32_t col = ring + s_idx * kSlotB + lane * 4;
 #pragma unroll
-        for (int i = 0; i < kIn; ++i) {
-          const float g[2] = {bf16_lo(rgt[i]), bf16_hi(rgt[i])}, dm[2] = {bf16_lo(rd[i]), bf16_hi(rd[i])};
-          const float xa[2] = {bf16_lo(rx[i]), bf16_hi(rx[i])};
+      for (int i = 0; i < kIn; ++i) {
+        uint32_t rg, rd;
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(rg) : "r"(col + i * kRowB));
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(rd) : "r"(col + (kIn + i) * kRowB));
+        const float g[2] = {bf16_lo(rg), bf16_hi(rg)}, dm[2] = {bf16_lo(rd), bf16_hi(rd)};
+        if (KIND) {
+          uint32_t rx;
+          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(rx) : "r"(col + (2 * kIn + kR + i) * kRowB));
+          const float xa[2] = {bf16_lo(rx), bf16_hi(rx)};
 #pragma unroll
           for (int e = 0; e < 2; ++e) {
             const float sg = fmaf(0.5f, tanh_approx(0.5f * g[e]), 0.5f);
             cP[i][e] = (dm[e] * xa[e]) * (sg * fmaf(g[e], 1.0f - sg, 1.0f));   // dmid * xa * silu'(g)
           }
-        }
-      } else {
-#pragma unroll
-        for (int i = 0; i < kIn; ++i) {
-          const float g[2] = {bf16_lo(rgt[i]), bf16_hi(rgt[i])}, dm[2] = {bf16_lo(rd[i]), bf16_hi(rd[i])};
+        } else {
 #pragma unroll
           for (int e = 0; e < 2; ++e) cP[i][e] = dm[e] * silu_f(g[e]);          // dmid * silu(g)
         }
       }
-      load_col(t + 1);
+      uint32_t ru[kR];
+#pragma unroll
+      for (int r = 0; r < kR; ++r) asm volatile("ld.shared.b32 %0, [%1];" : "=r"(ru[r]) : "r"(col + (2 * kIn + r) * kRowB));
+      __syncwarp();                                               // every lane has read the slot: it may be refilled
       if (t > 0) {
 #pragma unroll
         for (int r = 0; r < kR; ++r) {
@@ -281,29 +312,25 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbParams& p, float (*red
           for (int j = 0; j < 2; ++j) {
             float s, d;
             silu_and_grad(uu[j], s, d);
-            float a = 0.f;
+            float acc = 0.f;
 #pragma unroll
             for (int ky = 0; ky < 3; ++ky) {
               const float d0 = cP[r - ky + 2][j], d1 = cC[r - ky + 2][j], d2 = cM[r - ky + 2][j];
-              a = fmaf(w[3 * ky + 0][j], d0, a);
-              a = fmaf(w[3 * ky + 1][j], d1, a);
-              a = fmaf(w[3 * ky + 2][j], d2, a);
+              acc = fmaf(w[3 * ky + 0][j], d0, acc);
+              acc = fmaf(w[3 * ky + 1][j], d1, acc);
+              acc = fmaf(w[3 * ky + 2][j], d2, acc);
               dw[3 * ky + 0][j] = fmaf(s, d0, dw[3 * ky + 0][j]);
               dw[3 * ky + 1][j] = fmaf(s, d1, dw[3 * ky + 1][j]);
               dw[3 * ky + 2][j] = fmaf(s, d2, dw[3 * ky + 2][j]);
             }
             db[j] += cC[r + 1][j];
-            o[j] = a * d;
+            o[j] = acc * d;
           }
-          if ((omask >> r) & 1u) *reinterpret_cast<uint32_t*>(out_u + (uint64_t)c_row_b * (uint32_t)r) = pack_bf16(o[0], o[1]);
+          if ((omask >> r) & 1u) *reinterpret_cast<uint32_t*>(out_u + (uint64_t)row_b * (uint32_t)r) = pack_bf16(o[0], o[1]);
         }
         out_u += col_b;
       }
-      load_u(t);                                                  // used late in the next step
     };
-    load_col(0);
-#pragma unroll
-    for (int r = 0; r < kR; ++r) ru[r] = 0u;
     for (int t0 = 0; t0 <= W; t0 += 3) {
       step(t0, win0, win1, win2);
       if (t0 + 1 <= W) step(t0 + 1, win1, win2, win0);
@@ -311,7 +338,15 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbParams& p, float (*red
     }
   }
 
-  // per-CTA sums over the strips, fixed order
+  // per-CTA sums over the strips, fixed order.  The scratch aliases the rings: every TMA write has been waited
+  // for and every slot read is done once all warps have passed the barrier.
+  __syncthreads();
+  float (*red)[20][32] = reinterpret_cast<float (*)[20][32]>(smem);
+  if (!live) {
+#pragma unroll
+    for (int k = 0; k < 9; ++k) dw[k][0] = dw[k][1] = 0.f;
+    db[0] = db[1] = 0.f;
+  }
 #pragma unroll
   for (int g = 0; g < 10; ++g) {
     red[warp][2 * g + 0][lane] = g < 9 ? dw[g][0] : db[0];
@@ -323,17 +358,17 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbParams& p, float (*red
     const int l = i & 31, g = (i >> 5) % 10, j = i / 320;
     float s = 0.f;
 #pragma unroll
-    for (int st = 0; st < kBwdStrips; ++st) s += red[st][2 * g + j][l];
-    const int cq = blockIdx.x * 64 + 2 * l;
-    if (cq < Hd) part[((kind ? Hd : 0) + cq + j) * 10 + g] = s;
+    for (int st = 0; st < kWarps; ++st) s += red[st][2 * g + j][l];
+    const int cq = c0 + 2 * l;
+    if (cq < Hd) part[((KIND ? Hd : 0) + cq + j) * 10 + g] = s;
   }
 }
 
 // blockIdx.z = half: 0 -> A channels, 1 -> gate channels (separate instantiations: the A half never loads xa)
-__global__ void __launch_bounds__(kThreads, 2) glumb_bwd_kernel(const GlumbParams p) {
-  __shared__ float red[kThreads / 32][20][32];
-  if (blockIdx.z) glumb_bwd_body<1>(p, red);
-  else            glumb_bwd_body<0>(p, red);
+__global__ void __launch_bounds__(kThreads, 2) glumb_bwd_kernel(const __grid_constant__ GlumbArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  if (blockIdx.z) glumb_bwd_body<1>(a, smem);
+  else            glumb_bwd_body<0>(a, smem);
 }
 
 __global__ void __launch_bounds__(256) glumb_finish_kernel(const float* __restrict__ partial, int parts, int64_t n10,
@@ -355,15 +390,22 @@ int check_shape(const char* what, int B, int H, int W, int Hd) {
   YAT_REQUIRE(Hd % 8 == 0, YAT_ERR_UNSUPPORTED, "%s: hidden width %d must be a multiple of 8", what, Hd);
   YAT_REQUIRE((int64_t)W * Hd * 4 < (1ll << 32), YAT_ERR_UNSUPPORTED, "%s: one image row of u (%lld bytes) exceeds 4 GiB", what,
               (long long)W * Hd * 4);
-  YAT_REQUIRE((int64_t)B * bwd_ytiles(H) < 65536, YAT_ERR_UNSUPPORTED, "%s: B * y-tiles = %lld exceeds the grid limit", what,
-              (long long)B * bwd_ytiles(H));
+  YAT_REQUIRE((int64_t)B * ytiles_of(H) < 65536, YAT_ERR_UNSUPPORTED, "%s: B * y-tiles = %lld exceeds the grid limit", what,
+              (long long)B * ytiles_of(H));
   return YAT_OK;
+}
+
+// tensor map of a token-major [B, H, W, C] bf16 tensor with a {64 channels, 1 column, rows, 1} box
+int image_tmap(CUtensorMap* out, const void* base, int B, int H, int W, int64_t C, int rows) {
+  const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)B};
+  const uint32_t box[4] = {64u, 1u, (uint32_t)rows, 1u};
+  return make_tmap_4d_bf16_plain(out, base, dims, box);
 }
 }  // namespace
 }  // namespace yat
 
 extern "C" int64_t yat_glumb_workspace_bytes(int B, int H, int Hd) {
-  return (int64_t)B * yat::bwd_ytiles(H) * 2 * Hd * 10 * (int64_t)sizeof(float);
+  return (int64_t)B * yat::ytiles_of(H) * 2 * Hd * 10 * (int64_t)sizeof(float);
 }
 
 extern "C" int yat_glumb_mid_fwd(const void* u, const void* w_dw, const void* b_dw, int B, int H, int W, int Hd,
@@ -374,10 +416,16 @@ extern "C" int yat_glumb_mid_fwd(const void* u, const void* w_dw, const void* b_
   if (rc != YAT_OK) return rc;
   YAT_REQUIRE(aligned16(u) && aligned16(mid) && aligned16(c_out), YAT_ERR_BAD_ARG,
               "yat_glumb_mid_fwd: tensors must be 16-byte aligned");
-  GlumbParams p{};
-  p.u = (const __nv_bfloat16*)u; p.w = (const __nv_bfloat16*)w_dw; p.bias = (const __nv_bfloat16*)b_dw;
-  p.mid = (__nv_bfloat16*)mid; p.c = (__nv_bfloat16*)c_out; p.B = B; p.H = H; p.W = W; p.Hd = Hd;
-  glumb_fwd_kernel<<<dim3((Hd + 63) / 64, B * fwd_ytiles(H)), kThreads, 0, (cudaStream_t)stream>>>(p);
+  GlumbArgs a{};
+  if ((rc = image_tmap(&a.tm_u, u, B, H, W, 2 * (int64_t)Hd, kIn)) != YAT_OK) return rc;
+  a.p.w = (const __nv_bfloat16*)w_dw; a.p.bias = (const __nv_bfloat16*)b_dw;
+  a.p.mid = (__nv_bfloat16*)mid; a.p.c = (__nv_bfloat16*)c_out; a.p.B = B; a.p.H = H; a.p.W = W; a.p.Hd = Hd;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(glumb_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem);
+    attr_set = true;
+  }
+  glumb_fwd_kernel<<<dim3((Hd + 63) / 64, B * ytiles_of(H)), kThreads, kFwdSmem, (cudaStream_t)stream>>>(a);
   return check_launch("glumb_mid_fwd");
 }
 
@@ -391,15 +439,22 @@ extern "C" int yat_glumb_mid_bwd(const void* u, const void* c, const void* w_dw,
   YAT_REQUIRE(aligned16(u) && aligned16(c) && aligned16(dmid) && aligned16(du), YAT_ERR_BAD_ARG,
               "yat_glumb_mid_bwd: tensors must be 16-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
-  GlumbParams p{};
-  p.u = (const __nv_bfloat16*)u; p.c = (__nv_bfloat16*)const_cast<void*>(c); p.w = (const __nv_bfloat16*)w_dw;
-  p.dmid = (const __nv_bfloat16*)dmid; p.du = (__nv_bfloat16*)du;
-  p.partial = (float*)workspace; p.B = B; p.H = H; p.W = W; p.Hd = Hd;
-  const int parts = B * bwd_ytiles(H);
-  glumb_bwd_kernel<<<dim3((Hd + 63) / 64, parts, 2), kThreads, 0, st>>>(p);
+  GlumbArgs a{};
+  if ((rc = image_tmap(&a.tm_u, u, B, H, W, 2 * (int64_t)Hd, kR)) != YAT_OK) return rc;
+  if ((rc = image_tmap(&a.tm_c, c, B, H, W, 2 * (int64_t)Hd, kIn)) != YAT_OK) return rc;
+  if ((rc = image_tmap(&a.tm_d, dmid, B, H, W, (int64_t)Hd, kIn)) != YAT_OK) return rc;
+  a.p.w = (const __nv_bfloat16*)w_dw; a.p.du = (__nv_bfloat16*)du;
+  a.p.partial = (float*)workspace; a.p.B = B; a.p.H = H; a.p.W = W; a.p.Hd = Hd;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(glumb_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem);
+    attr_set = true;
+  }
+  const int parts = B * ytiles_of(H);
+  glumb_bwd_kernel<<<dim3((Hd + 63) / 64, parts, 2), kThreads, kBwdSmem, st>>>(a);
   if ((rc = check_launch("glumb_bwd")) != YAT_OK) return rc;
   const int64_t n10 = (int64_t)2 * Hd * 10;
-  glumb_finish_kernel<<<(unsigned)((n10 + 255) / 256), 256, 0, st>>>(p.partial, parts, n10, (__nv_bfloat16*)dw,
+  glumb_finish_kernel<<<(unsigned)((n10 + 255) / 256), 256, 0, st>>>(a.p.partial, parts, n10, (__nv_bfloat16*)dw,
                                                                    (__nv_bfloat16*)db);
   return check_launch("glumb_finish");
 }

@@ -395,6 +395,27 @@ int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t N
   return YAT_OK;
 }
 
+// Plain (unswizzled) 4-D bf16 tensor map {d0, d1, d2, d3} (d0 contiguous) with box {b0, b1, b2, 1}; out-of-bounds
+// elements of a box (negative or past-the-end coordinates) read as zero.
+int make_tmap_4d_bf16_plain(CUtensorMap* out, const void* base, const uint64_t dims[4], const uint32_t box[4]) {
+  PFN_encodeTiled enc = get_encode_fn();
+  YAT_REQUIRE(enc != nullptr, YAT_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  const cuuint64_t d[4] = {dims[0], dims[1], dims[2], dims[3]};
+  const cuuint64_t strides[3] = {dims[0] * 2, dims[0] * dims[1] * 2, dims[0] * dims[1] * dims[2] * 2};
+  const cuuint32_t bx[4] = {box[0], box[1], box[2], box[3]};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = CUDA_ERROR_UNKNOWN;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), d, strides, bx, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_ERROR_INVALID_CONTEXT) break;
+    cudaFree(nullptr);  // first driver-API call on this thread (autograd worker): bind the primary context, retry
+  }
+  YAT_REQUIRE(r == CUDA_SUCCESS, YAT_ERR_CUDA, "cuTensorMapEncodeTiled (4d) failed with CUresult %d", (int)r);
+  return YAT_OK;
+}
+
 }  // namespace yat
 
 extern "C" int yat_linattn_fwd(const void* q, const void* k, const void* v, int B, int N, int H, int D, void* o,

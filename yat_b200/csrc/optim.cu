@@ -145,8 +145,10 @@ __global__ void __launch_bounds__(kThreads) grad_sumsq_kernel(const Tensor4* __r
   }
 }
 
-struct AdamArgs {
-  float lr, beta1, beta2, eps, weight_decay;
+struct AdamArgs {               // all derived on the host in double, then rounded once to fp32
+  float beta2, eps;
+  float omb1, omb2;     // 1 - beta1, 1 - beta2  (1.0f - 0.999f in fp32 would be off by 5e-5 relative)
+  float lr_wd;          // lr * weight_decay
   float step_size;      // lr / (1 - beta1^t)
   float bc2_sqrt;       // sqrt(1 - beta2^t)
 };
@@ -154,9 +156,9 @@ struct AdamArgs {
 template <typename T>
 __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, float coef, const AdamArgs& a) {
   g = Vec<T>::rnd(__fmul_rn(g, coef));
-  p = __fsub_rn(p, __fmul_rn(__fmul_rn(a.lr, a.weight_decay), p));
-  m = fmaf(1.0f - a.beta1, __fsub_rn(g, m), m);
-  v = fmaf(a.beta2, v, __fmul_rn(__fmul_rn(1.0f - a.beta2, g), g));
+  p = __fsub_rn(p, __fmul_rn(a.lr_wd, p));
+  m = fmaf(a.omb1, __fsub_rn(g, m), m);
+  v = fmaf(a.beta2, v, __fmul_rn(__fmul_rn(a.omb2, g), g));
   const float denom = __fadd_rn(Vec<T>::div(Vec<T>::sqrt(v), a.bc2_sqrt), a.eps);
   p = __fsub_rn(p, Vec<T>::div(__fmul_rn(a.step_size, m), denom));
 }
@@ -237,8 +239,8 @@ extern "C" int yat_grad_clip_coef(const int64_t* tensor_tab, const int64_t* grad
 }
 
 extern "C" int yat_adamw_step(const int64_t* tensor_tab, const int64_t* grad_ptrs, const int32_t* chunks, int n_chunks,
-                              int dtype, const float* clip_coef, float lr, float beta1, float beta2, float eps,
-                              float weight_decay, int64_t step, void* stream) {
+                              int dtype, const float* clip_coef, double lr, double beta1, double beta2, double eps,
+                              double weight_decay, int64_t step, void* stream) {
   using namespace yat;
   YAT_REQUIRE(tensor_tab && grad_ptrs && chunks, YAT_ERR_BAD_ARG, "yat_adamw_step: null pointer argument");
   YAT_REQUIRE(n_chunks > 0 && step > 0, YAT_ERR_BAD_ARG, "yat_adamw_step: n_chunks=%d step=%lld must be positive",
@@ -246,9 +248,11 @@ extern "C" int yat_adamw_step(const int64_t* tensor_tab, const int64_t* grad_ptr
   YAT_REQUIRE(dtype == YAT_DTYPE_BF16 || dtype == YAT_DTYPE_F32, YAT_ERR_UNSUPPORTED,
               "yat_adamw_step: dtype %d not supported", dtype);
   AdamArgs a;
-  a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.weight_decay = weight_decay;
-  const double bc1 = 1.0 - std::pow((double)beta1, (double)step), bc2 = 1.0 - std::pow((double)beta2, (double)step);
-  a.step_size = (float)((double)lr / bc1);
+  a.beta2 = (float)beta2; a.eps = (float)eps;
+  a.omb1 = (float)(1.0 - beta1); a.omb2 = (float)(1.0 - beta2);
+  a.lr_wd = (float)(lr * weight_decay);
+  const double bc1 = 1.0 - std::pow(beta1, (double)step), bc2 = 1.0 - std::pow(beta2, (double)step);
+  a.step_size = (float)(lr / bc1);
   a.bc2_sqrt = (float)std::sqrt(bc2);
   cudaStream_t st = (cudaStream_t)stream;
   const Tensor4* tab = (const Tensor4*)tensor_tab;
