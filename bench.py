@@ -312,15 +312,21 @@ def _standalone_kernels(device, pk):
     entry("ln_modulate_fwd", 4 * B * N * C, ms, [B, N, C])
     ms = timeit(lambda: gate_residual(q, k, gt.detach()))
     entry("gate_residual_fwd", 6 * B * N * C, ms, [B, N, C])
-    xg = q.clone().requires_grad_(True)
-    y1 = ln_modulate(xg, sc, sh)
-    ms = timeit(lambda: torch.autograd.grad(y1, (xg, mod), do, retain_graph=True))
-    entry("ln_modulate_bwd", 6 * B * N * C, ms, [B, N, C])
-    yg = k.clone().requires_grad_(True)
-    y2 = gate_residual(q, yg, gt)
-    ms = timeit(lambda: torch.autograd.grad(y2, (yg, mod), do, retain_graph=True))
-    entry("gate_residual_bwd", 6 * B * N * C, ms, [B, N, C])
-    del xg, yg, y1, y2, mod
+    # (the backward block ops are reported in situ only: stand-alone their ~50 us launches are shorter than the
+    #  host cost of torch.autograd.grad, so a back-to-back loop would time the CPU)
+    from yat_b200.glumb import glumb_mid
+    Hd = int(2.5 * C)
+    u = (torch.randn((B, N, 2 * Hd), device=device) * 1.2).to(torch.bfloat16).requires_grad_(True)
+    wdw = (torch.randn((2 * Hd, 1, 3, 3), device=device) * 0.3).to(torch.bfloat16).requires_grad_(True)
+    bdw = (torch.randn((2 * Hd,), device=device) * 0.2).to(torch.bfloat16).requires_grad_(True)
+    dmid = torch.randn((B, N, Hd), device=device).to(torch.bfloat16)
+    ms = timeit(lambda: glumb_mid(u, wdw, bdw, 32, 32))
+    entry("glumb_mid_fwd", 25 * B * N * C, ms, [B, 32, 32, 2 * Hd])
+    mid = glumb_mid(u, wdw, bdw, 32, 32)
+    ms = timeit(lambda: torch.autograd.grad(mid, (u, wdw, bdw), dmid, retain_graph=True))
+    entry("glumb_mid_bwd", 35 * B * N * C, ms, [B, 32, 32, 2 * Hd])
+    del u, wdw, bdw, dmid, mid
+    del mod
     ms = timeit(lambda: sana_linear_attention(q, k, v, H))
     entry("linattn_fwd_sm100", 8 * B * N * C, ms, [B, N, C], flops=4 * 32 * 33 * N * H * B)
     qg, kg, vg = [t.clone().requires_grad_(True) for t in (q, k, v)]

@@ -12,7 +12,8 @@ ps, gs = _make(dtype, 5, 1e-4)
 dev_ps = [torch.nn.Parameter(p.to(dev)) for p in ps]
 opt = FusedClipAdamW(dev_ps, lr=lr, weight_decay=wd)
 for step in range(1, 4):
-    grads = [(g * (1.0 + 0.25 * step)).to(dtype) for g in gs]
+    gen = torch.Generator().manual_seed(100 + step)
+    grads = [(torch.randn(g.shape, generator=gen) * 1e-4 * (1.0 + 0.25 * step)).to(dtype) for g in gs]
     for p, g in zip(dev_ps, grads):
         p.grad = g.to(dev)
     cur = [p.detach().cpu().clone() for p in dev_ps]
@@ -31,5 +32,5 @@ for step in range(1, 4):
             if int((d > 0).sum()):
                 print("  tensor", ti, name, "mismatch", int((d > 0).sum()), "bad", len(bad))
             for i in bad[:4]:
-                print("     ", i, "got", got[i].item(), "ref", ref[i].item(), "| p_in", p_in[ti].flatten()[i].item(), "g", grads[ti].flatten()[i].item(),
+                print("     ", i, "got", repr(got[i].item()), "ref", repr(ref[i].item()), "| p_in", p_in[ti].flatten()[i].item(), "g", grads[ti].flatten()[i].item(),
                       "m_in", m_in[ti].flatten()[i].item(), "v_in", v_in[ti].flatten()[i].item())

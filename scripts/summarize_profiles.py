@@ -110,7 +110,7 @@ def kernels(tag):
     with open(os.path.join(PROF, f"{tag}_kernels.md"), "w") as f:
         f.write(f"# {tag}: `ncu --set full --clock-control none --import-source on` of scripts/prof_kernels.py\n\n"
                 "Shapes: noise/loss `[4096,32,32,32]` bf16 (bulk slab > L2), REPA z `[64,1024,768]`, linear "
-                "attention `[16,1024,2240]` (SANA-1.6B layer).  Numbers taken under the profiler are evidence "
+                "attention / block ops `[16,1024,2240]`, GLUMB `[16,32,32,2x5600]` (SANA-1.6B layer), optimiser 321 M bf16 params.  Numbers taken under the profiler are evidence "
                 "for WHY, never bench values.\n\n")
         for rep in reps:
             r = subprocess.run(["ncu", "-i", os.path.join(OUT, rep), "--page", "raw", "--csv"], capture_output=True,
@@ -140,7 +140,10 @@ def kernels(tag):
                     wr = to_bytes(row[col["dram__bytes_write.sum"]], units[col["dram__bytes_write.sum"]])
                     key = {"noise_bf16_kernel": "noise_flowmatch", "loss_fused_kernel": "loss_fused",
                            "linattn_fwd_sm100_kernel": "linattn_fwd_sm100", "linattn_bwd_sm100_kernel": "linattn_bwd_sm100",
-                           "repa_pool_cos_kernel": "repa_cos"}.get(name, name)
+                           "repa_pool_cos_kernel": "repa_cos", "glumb_fwd_kernel": "glumb_mid_fwd",
+                           "glumb_bwd_kernel": "glumb_mid_bwd", "adamw_kernel": "adamw_step",
+                           "grad_sumsq_kernel": "grad_clip_coef", "ln_modulate_fwd_kernel": "ln_modulate_fwd",
+                           "gate_residual_fwd_kernel": "gate_residual_fwd"}.get(name, name)
                     traffic[key] = {"dram_bytes_per_launch": rd + wr, "read": rd, "write": wr, "capture": f"{tag}/{rep}"}
                 except (KeyError, ValueError):
                     pass
