@@ -105,6 +105,12 @@ class SanaModel(Model):
     def make_sampler(self):
         cfg = self.pipe.transformer.config
         s = cfg.sample_size
+        if getattr(self.params, "latent_cache", None):
+            # per-bucket bf16 slabs: every rank reads the same index, so all ranks step on the
+            # same bucket without the reference's barrier + all_gather per element (common/bucket_sampler.py:225-237)
+            from yat_b200.latent_cache import SlabBucketSampler, SlabReader
+            return SlabBucketSampler(SlabReader(self.params.latent_cache), self.params.batch_size,
+                                     rank=self.process_index, world=self.num_processes, seed=1234)
         return SyntheticBucketSampler(self.params.batch_size, (cfg.in_channels, s, s), cfg.caption_channels,
                                       ratio=1.0, seed=1234 + self.process_index, repa_tokens=self.params.use_repa)
 

@@ -19,6 +19,21 @@ def _pinned(nbytes):
     return buf
 
 
+def _is_packed_pinned(embeddings, lens, E, dtype):
+    base = getattr(embeddings[0], "_base", None)
+    if base is None or base.dtype != dtype or base.dim() != 2 or base.shape[1] != E or not base.is_contiguous() \
+            or not base.is_pinned():
+        return False
+    off = embeddings[0].storage_offset()
+    if off % E:
+        return False
+    for e, l in zip(embeddings, lens):
+        if e._base is not base or int(e.shape[0]) != l or e.storage_offset() != off or not e.is_contiguous():
+            return False
+        off += l * E
+    return True
+
+
 def pad_embeddings(embeddings, max_len, device, dtype=torch.bfloat16, trim_multiple=None):
     """embeddings: list of [L_i, E] tensors (host or device). Returns (padded [B,Lmax,E], mask int64 [B,Lmax]).
 
@@ -40,6 +55,12 @@ def pad_embeddings(embeddings, max_len, device, dtype=torch.bfloat16, trim_multi
     offsets[1:] = torch.tensor(lens, dtype=torch.int32).cumsum(0)
     if embeddings[0].is_cuda:
         packed = torch.cat([e[:l].to(dtype) for e, l in zip(embeddings, lens)], dim=0).contiguous()
+    elif _is_packed_pinned(embeddings, lens, E, dtype):
+        # slab cache (yat_b200/latent_cache.py): the list is consecutive views of ONE pinned packed buffer,
+        # already in the layout the kernel reads -> a single asynchronous H2D copy, no staging pass
+        base = embeddings[0]._base
+        r0 = embeddings[0].storage_offset() // E
+        packed = base[r0:r0 + total].to(device, non_blocking=True)
     else:
         stage = _pinned(total * E * 2).narrow(0, 0, total * E * 2).view(torch.bfloat16).view(total, E)
         o = 0

@@ -31,6 +31,7 @@ class TrainingParameters:
         self.lora_target_modules = None
         self.lora_rank = None
         self.lora_alpha = None
+        self.latent_cache = None         # directory of a slab cache (yat_b200/latent_cache.py); None = synthetic batches
         self.lora_dropout = None
         self.lora_algo = None
         self.lora_pretrained = None
@@ -101,6 +102,7 @@ class TrainingParameters:
             self.lora_algo = y["lora_algo"]
         self.low_vram = has("low_vram")
         self.use_repa = has("use_repa")
+        self.latent_cache = str(y["latent_cache"]) if has("latent_cache") else None
         if has("gradient_checkpointing"):
             v = y["gradient_checkpointing"]
             self.gradient_checkpointing = "auto" if str(v).lower() == "auto" else bool(v)
