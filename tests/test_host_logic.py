@@ -242,3 +242,98 @@ def test_optimizer_oracle_forms_agree_and_no_cpu_fallback():
     p.grad = torch.ones(4)
     with pytest.raises(ValueError):
         FusedClipAdamW([p]).step()
+
+
+@pytest.mark.parametrize("algo,rank", [("lora", 4), ("lokr", 2), ("lokr", 16)])
+def test_adapters_match_weight_space_form(algo, rank):
+    """LoRA / LoKr activation-space forward == x @ delta_weight^T evaluated in fp64 (the published formulas; peft is
+    absent so this is what pins the adapter maths), B / W2 zero at init, adapters_disabled restores the base."""
+    from yat_b200.adapters import ALGOS, adapter_state_dict, adapters_disabled, apply_adapters
+    torch.manual_seed(0)
+    ad = ALGOS[algo](48, 60, rank, 2 * rank, torch.float64, "cpu")
+    x = torch.randn(3, 7, 60, dtype=torch.float64)
+    assert torch.equal(ad(x), torch.zeros(3, 7, 48, dtype=torch.float64))          # zero-initialised second factor
+    for p in ad.parameters():
+        torch.nn.init.normal_(p, std=0.3)
+    dw = ad.delta_weight()
+    assert dw.shape == (48, 60)
+    assert torch.allclose(ad(x), x @ dw.T, rtol=1e-10, atol=1e-10)
+    if algo == "lokr":                                                              # explicit Kronecker product
+        assert torch.allclose(dw, ad.scale * torch.kron(ad.lokr_w1, ad._w2()), rtol=1e-12, atol=1e-12)
+        assert (ad.lokr_w2 is None) == (rank < max(ad.shape[1], ad.shape[3]) / 2)
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.to_q = torch.nn.Linear(60, 48)
+            self.conv = torch.nn.Conv2d(48, 24, 1)
+            self.conv_depth = torch.nn.Conv2d(24, 24, 3, padding=1, groups=24)
+
+        def forward(self, x):                                                       # x [B, 4, 4, 60]
+            return self.conv_depth(self.conv(self.to_q(x).permute(0, 3, 1, 2)))
+
+    net = Net().double()
+    xin = torch.randn(2, 4, 4, 60, dtype=torch.float64)
+    y0 = net(xin)
+    names = apply_adapters(net, algo, rank, rank, "to_q conv")
+    assert names == ["to_q", "conv"] and not any(p.requires_grad for n, p in net.named_parameters() if ".adapter." not in n)
+    assert all(p.requires_grad for n, p in net.named_parameters() if ".adapter." in n)
+    assert torch.equal(net(xin), y0)
+    for n, p in net.named_parameters():
+        if ".adapter." in n:
+            torch.nn.init.normal_(p, std=0.2)
+    y1 = net(xin)
+    merged = Net().double()
+    merged.load_state_dict({k: v for k, v in net.state_dict().items() if ".adapter." not in k})
+    with torch.no_grad():
+        merged.to_q.weight += net.to_q.adapter.delta_weight()
+        merged.conv.weight += net.conv.adapter.delta_weight()[:, :, None, None]
+    assert torch.allclose(y1, merged(xin), rtol=1e-9, atol=1e-9) and not torch.allclose(y1, y0, atol=1e-3)
+    with adapters_disabled(net):
+        assert torch.equal(net(xin), y0)
+    assert torch.equal(net(xin), y1)
+    assert set(adapter_state_dict(net)) == {n for n, _ in net.named_parameters() if ".adapter." in n}
+    with pytest.raises(ValueError):
+        apply_adapters(Net(), algo, rank, rank, "conv_depth")                       # README.md:16: no depthwise target
+    with pytest.raises(ValueError):
+        apply_adapters(Net(), "loha", rank, rank, "to_q")
+
+
+def test_adapters_on_sana_token_path_cpu():
+    """apply_adapters on the tiny SANA transformer: attention projections through the forward hook, GLUMBConv 1x1
+    convolutions through adapter_term on the token-major path; equals the same network with merged weights."""
+    from oracle.linear_attention import sana_linear_attention_core
+    from train_sana import SANA_CONFIGS
+    from yat_b200.adapters import adapters_disabled, apply_adapters
+    from yat_b200.sana_transformer import PatchedSanaTransformer2DModel
+
+    class OracleProc:
+        def __call__(self, attn, hs, encoder_hidden_states=None, attention_mask=None):
+            q, k, v = attn.to_q(hs), attn.to_k(hs), attn.to_v(hs)
+            return attn.to_out[1](attn.to_out[0](sana_linear_attention_core(q, k, v, attn.heads)))
+
+    torch.manual_seed(1)
+    m = PatchedSanaTransformer2DModel(**SANA_CONFIGS["sana_tiny"])
+    m.set_block_ops("torch")
+    for b in m.transformer_blocks:
+        b.attn1.set_processor(OracleProc())
+    x, enc, t = torch.randn(2, 32, 16, 16), torch.randn(2, 64, 64), torch.tensor([326.0, 811.0])
+    with torch.no_grad():
+        y0 = m(x, enc, t).sample
+    names = apply_adapters(m, "lokr", 16, 16, "to_q to_k to_v conv_inverted conv_point")
+    assert len(names) == 2 * (3 + 3 + 2)
+    with torch.no_grad():
+        assert torch.equal(m(x, enc, t).sample, y0)
+        for n, p in m.named_parameters():
+            if ".adapter." in n:
+                torch.nn.init.normal_(p, std=0.05)
+        y1 = m(x, enc, t).sample
+        with adapters_disabled(m):
+            assert torch.equal(m(x, enc, t).sample, y0)
+        for mod in m.modules():
+            if hasattr(mod, "adapter"):
+                dw = mod.adapter.delta_weight()
+                mod.weight += dw.view_as(mod.weight)
+                mod.adapter.enabled = False
+        y2 = m(x, enc, t).sample
+    assert not torch.allclose(y1, y0, atol=1e-3) and torch.allclose(y1, y2, rtol=1e-4, atol=1e-4)

@@ -144,6 +144,48 @@ def test_sana_model_hook_runs_and_learns(cuda, tmp_path, monkeypatch):
     assert torch.equal(l1.detach(), l2.detach())      # fresh generator -> same draws every step
 
 
+@pytest.mark.parametrize("algo,rank", [("lokr", 16), ("lora", 32)])
+def test_sana_adapter_step_k5(cuda, tmp_path, monkeypatch, algo, rank):
+    """BASELINE config K5 (REPA + use_preservation + LoKr r16) and the LoRA r32 wrap of K4 on the tiny SANA: only adapter
+    and REPA-projector tensors train, the base weights stay bit-identical, the frozen prediction of the preservation
+    term is the same network with adapters disabled (no second copy), the loss is finite and the adapters move."""
+    monkeypatch.chdir(tmp_path)
+    from train_sana import SanaModel
+    from yat_b200.adapters import adapters_disabled
+    from yat_b200.training_parameters_reader import TrainingParameters
+    params = TrainingParameters()
+    params.batch_size = 2
+    params.model_config = "sana_tiny"
+    params.learning_rate = 1e-2
+    params.use_repa = True
+    params.use_preservation = True
+    params.preservation_ratio = 0.5
+    params.lora_rank, params.lora_alpha, params.lora_algo = rank, rank, algo
+    params.lora_target_modules = "to_q to_k to_v to_out.0 conv_inverted conv_point"
+    tr = SanaModel(params)
+    tr.initialize()
+    assert getattr(tr, "frozen_model", None) is None and len(tr.adapted_modules) >= 2 * 10
+    base = {n: p.detach().clone() for n, p in tr.pipe.transformer.named_parameters() if ".adapter." not in n}
+    ad0 = {n: p.detach().clone() for n, p in tr.pipe.transformer.named_parameters() if ".adapter." in n}
+    assert not any(p.requires_grad for n, p in tr.pipe.transformer.named_parameters() if ".adapter." not in n)
+    it = iter(tr.sampler)
+    ls = [tr.train_step(next(it)).item() for _ in range(3)]
+    assert all(l == l and abs(l) < 1e3 for l in ls)
+    now = dict(tr.pipe.transformer.named_parameters())
+    assert all(torch.equal(base[n], now[n].detach()) for n in base)
+    assert sum(int(not torch.equal(ad0[n], now[n].detach())) for n in ad0) > len(ad0) // 2
+    # adapters disabled == the base network: same output as a copy with the adapters stripped
+    x = torch.randn(2, 32, 16, 16, device=cuda, dtype=torch.bfloat16)
+    enc = torch.randn(2, 64, tr.pipe.transformer.config.caption_channels, device=cuda, dtype=torch.bfloat16)
+    t = torch.tensor([100.0, 700.0], device=cuda)
+    with torch.no_grad():
+        y_on = tr.pipe.transformer(x, encoder_hidden_states=enc, timestep=t).sample
+        with adapters_disabled(tr.pipe.transformer):
+            y_off = tr.pipe.transformer(x, encoder_hidden_states=enc, timestep=t).sample
+            y_off2 = tr.pipe.transformer(x, encoder_hidden_states=enc, timestep=t).sample
+    assert torch.equal(y_off, y_off2) and not torch.equal(y_on, y_off)
+
+
 def test_trimmed_text_padding_matches_fixed_512(cuda):
     """pad_embeddings(trim_multiple=64) pads to the longest caption only; masked keys weigh exactly 0 in
     the cross-attention softmax, so the transformer output equals the reference's fixed 512-token padding

@@ -79,8 +79,9 @@ class SanaModel(Model):
             blk = f"transformer_blocks.{min(7, transformer.config.num_layers - 1)}"
             inner = transformer.config.num_attention_heads * transformer.config.attention_head_dim
             self.model = RepaModel(transformer, RepaConfig(target_modules=[blk], hidden_shape=[inner]))
-        if params.use_preservation:
+        if params.use_preservation and params.lora_rank is None:
             self.frozen_model = copy.deepcopy(transformer).requires_grad_(False).eval()
+        # with LoRA / LoKr the frozen prediction is the same network with its adapters disabled
 
     def _want_checkpointing(self, transformer, params):
         mode = getattr(params, "gradient_checkpointing", "auto")
@@ -169,6 +170,11 @@ class SanaModel(Model):
             with torch.no_grad():
                 pred_frozen = self.frozen_model(nz.x_t, encoder_hidden_states=embeddings, timestep=nz.timesteps,
                                                 encoder_attention_mask=attention_mask).sample
+        elif params.use_preservation and params.lora_rank is not None:
+            from yat_b200.adapters import adapters_disabled
+            with torch.no_grad(), adapters_disabled(self.pipe.transformer):
+                pred_frozen = self.pipe.transformer(nz.x_t, encoder_hidden_states=embeddings, timestep=nz.timesteps,
+                                                    encoder_attention_mask=attention_mask).sample
         loss = fused_denoise_loss(noise_pred, latents, nz.noise, pred_frozen=pred_frozen,
                                   rho=float(params.preservation_ratio or 0.0),
                                   gscale=1.0 / self.accelerator.gradient_accumulation_steps,

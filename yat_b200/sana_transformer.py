@@ -24,6 +24,7 @@ from torch.utils.checkpoint import checkpoint
 
 from .attention import Attention, AttnProcessor2_0, SanaLinearAttnProcessorB200
 from .block_ops import gate_residual, ln_modulate
+from .adapters import adapter_term
 from .glumb import glumb_mid
 
 
@@ -146,8 +147,13 @@ class GLUMBConv(nn.Module):
         GEMMs on the conv weights viewed as [out, in], the middle is one fused kernel."""
         w_inv, w_pt = self.conv_inverted.weight, self.conv_point.weight
         u = F.linear(hidden_states, w_inv.view(w_inv.shape[0], w_inv.shape[1]), self.conv_inverted.bias)
+        t = adapter_term(self.conv_inverted, hidden_states)                # LoRA / LoKr term, None without an adapter
+        if t is not None:
+            u = u + t
         mid = glumb_mid(u, self.conv_depth.weight, self.conv_depth.bias, height, width)
-        return F.linear(mid, w_pt.view(w_pt.shape[0], w_pt.shape[1]), self.conv_point.bias)
+        out = F.linear(mid, w_pt.view(w_pt.shape[0], w_pt.shape[1]), self.conv_point.bias)
+        t = adapter_term(self.conv_point, mid)
+        return out if t is None else out + t
 
 
 class SanaModulatedNorm(nn.Module):

@@ -116,6 +116,14 @@ class Model:
         if self.accelerator.is_main_process:
             os.makedirs("models", exist_ok=True)
         self.sampler = self.make_sampler()
+        if params.lora_rank is not None:                                   # PEFT wrap (common/trainer.py:212-241)
+            from .adapters import apply_adapters
+            if params.lora_pretrained is not None:
+                raise NotImplementedError("lora_pretrained: loading a saved PEFT adapter is outside the hot-path scope")
+            base = self.pipe.transformer if self.pipe is not None and getattr(self.pipe, "transformer", None) is not None \
+                else self.model
+            self.adapted_modules = apply_adapters(base, params.lora_algo or "lora", params.lora_rank, params.lora_alpha,
+                                                  params.lora_target_modules)
         trainable = [p for p in self.model.parameters() if p.requires_grad]
         if self.accelerator.device.type == "cuda":
             # clip_grad_norm_ + AdamW.step as two persistent kernels (common/trainer.py:245-248,347-348)
