@@ -47,6 +47,18 @@ constexpr int kBarBytes = kWarps * kStages * 8;
 constexpr int kFwdSmem = kWarps * kStages * kFwdSlotB + kBarBytes;
 constexpr int kBwdSmem = kWarps * kStages * kBwdSlotB1 + kBarBytes;
 
+// Packed fp32 pairs (Blackwell FFMA2 / FMUL2 / FADD2: one issue slot for the two channels a lane owns; each half is
+// an IEEE fp32 operation, so results equal the scalar form).  The kernels are issue-bound, not pipe-bound.
+struct f2 { unsigned long long v; };
+__device__ __forceinline__ f2 mk2(float lo, float hi) { f2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ f2 bc2(float x) { return mk2(x, x); }
+__device__ __forceinline__ void un2(f2 a, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.v)); }
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) { f2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v)); return r; }
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) { f2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
+__device__ __forceinline__ f2 add2(f2 a, f2 b) { f2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
+__device__ __forceinline__ f2 unpack2(uint32_t w) { return mk2(bf16_lo(w), bf16_hi(w)); }   // bf16x2 word -> fp32 pair
+__device__ __forceinline__ uint32_t pack2(f2 a) { float lo, hi; un2(a, lo, hi); return pack_bf16(lo, hi); }
+
 // silu through ONE special-function op:  sigmoid(x) = 0.5 + 0.5 tanh(x / 2)  =>  silu(x) = h + h tanh(h), h = x / 2.
 // tanh.approx.f32 has 2^-11 relative error, i.e. |error(silu)| <= 2.5e-4 |x|: below the bf16 rounding of the
 // activation for x > -2 and below 2e-3 absolute everywhere that matters (the reference rounds silu to bf16).
@@ -55,15 +67,20 @@ __device__ __forceinline__ float tanh_approx(float x) {
   asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-__device__ __forceinline__ float silu_f(float x) {
-  const float h = 0.5f * x;
-  return fmaf(h, tanh_approx(h), h);
+__device__ __forceinline__ f2 tanh2(f2 h) {
+  float a, b;
+  un2(h, a, b);
+  return mk2(tanh_approx(a), tanh_approx(b));
+}
+__device__ __forceinline__ f2 silu2(f2 x) {
+  const f2 h = mul2(x, bc2(0.5f));
+  return fma2(h, tanh2(h), h);
 }
 // s = silu(x), d = silu'(x) = sg (1 + x (1 - sg))
-__device__ __forceinline__ void silu_and_grad(float x, float& s, float& d) {
-  const float sg = fmaf(0.5f, tanh_approx(0.5f * x), 0.5f);
-  s = x * sg;
-  d = sg * fmaf(x, 1.0f - sg, 1.0f);
+__device__ __forceinline__ f2 sigmoid2(f2 x) { return fma2(bc2(0.5f), tanh2(mul2(x, bc2(0.5f))), bc2(0.5f)); }
+__device__ __forceinline__ f2 silu_grad_from_sigmoid2(f2 x, f2 sg) {
+  const f2 one = bc2(1.0f);
+  return mul2(sg, fma2(x, fma2(sg, bc2(-1.0f), one), one));
 }
 
 struct GlumbParams {
@@ -123,13 +140,15 @@ __global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const __grid_con
   for (int t = 0; t < kStages - 1; ++t)
     if (t <= W) issue(t);
 
-  float w[9][4], bias[4];
+  // [0] = the A channel pair (ca, ca+1), [1] = their gates (Hd+ca, Hd+ca+1)
+  f2 w[9][2], bias[2];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const int64_t ch = (j >> 1) * (int64_t)Hd + ca + (j & 1);
-    bias[j] = live ? __bfloat162float(p.bias[ch]) : 0.f;
+  for (int j = 0; j < 2; ++j) {
+    const int64_t ch = j * (int64_t)Hd + ca;
+    bias[j] = live ? mk2(__bfloat162float(p.bias[ch]), __bfloat162float(p.bias[ch + 1])) : bc2(0.f);
 #pragma unroll
-    for (int k = 0; k < 9; ++k) w[k][j] = live ? __bfloat162float(p.w[ch * 9 + k]) : 0.f;
+    for (int k = 0; k < 9; ++k)
+      w[k][j] = live ? mk2(__bfloat162float(p.w[ch * 9 + k]), __bfloat162float(p.w[(ch + 1) * 9 + k])) : bc2(0.f);
   }
 
   // outputs: running byte pointers advanced once per step; a row is one 32x32->64 multiply-add away
@@ -142,39 +161,39 @@ __global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const __grid_con
 #pragma unroll
   for (int r = 0; r < kR; ++r) omask |= (live && y0 + r < H) ? (1u << r) : 0u;
 
-  float acc0[kR][4], acc1[kR][4], acc2[kR][4];
+  f2 acc0[kR][2], acc1[kR][2], acc2[kR][2];
 #pragma unroll
   for (int r = 0; r < kR; ++r)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) acc0[r][j] = acc1[r][j] = acc2[r][j] = bias[j];
+    for (int j = 0; j < 2; ++j) acc0[r][j] = acc1[r][j] = acc2[r][j] = bias[j];
 
   // step x: input column x feeds the outputs at x-1 (tap kx = 2: aP, finished and written here), x (kx = 1: aC)
   // and x+1 (kx = 0: aN, started here from the bias).  x = W is the zero column right of the image.
-  auto step = [&](int x, float (&aP)[kR][4], float (&aC)[kR][4], float (&aN)[kR][4]) {
+  auto step = [&](int x, f2 (&aP)[kR][2], f2 (&aC)[kR][2], f2 (&aN)[kR][2]) {
     if (x + kStages - 1 <= W) issue(x + kStages - 1);             // into the slot read in step x-1
     const int s_idx = x & (kStages - 1);
     mbar_wait(bars + 8 * s_idx, (uint32_t)(x / kStages) & 1u);
     const uint32_t col = ring + s_idx * kFwdSlotB + lane * 4;
-    float s[kIn][4];
+    f2 s[kIn][2];
 #pragma unroll
     for (int i = 0; i < kIn; ++i) {
       uint32_t ra, rg;
       asm volatile("ld.shared.b32 %0, [%1];" : "=r"(ra) : "r"(col + i * kRowB));
       asm volatile("ld.shared.b32 %0, [%1];" : "=r"(rg) : "r"(col + (kIn + i) * kRowB));
-      s[i][0] = silu_f(bf16_lo(ra)); s[i][1] = silu_f(bf16_hi(ra));
-      s[i][2] = silu_f(bf16_lo(rg)); s[i][3] = silu_f(bf16_hi(rg));
+      s[i][0] = silu2(unpack2(ra));
+      s[i][1] = silu2(unpack2(rg));
     }
     __syncwarp();                                                 // every lane has read the slot: it may be refilled
 #pragma unroll
     for (int r = 0; r < kR; ++r)
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        float pa = aP[r][j], cc = aC[r][j], n = bias[j];
+      for (int j = 0; j < 2; ++j) {
+        f2 pa = aP[r][j], cc = aC[r][j], n = bias[j];
 #pragma unroll
         for (int ky = 0; ky < 3; ++ky) {
-          pa = fmaf(w[3 * ky + 2][j], s[r + ky][j], pa);
-          cc = fmaf(w[3 * ky + 1][j], s[r + ky][j], cc);
-          n = fmaf(w[3 * ky + 0][j], s[r + ky][j], n);
+          pa = fma2(w[3 * ky + 2][j], s[r + ky][j], pa);
+          cc = fma2(w[3 * ky + 1][j], s[r + ky][j], cc);
+          n = fma2(w[3 * ky + 0][j], s[r + ky][j], n);
         }
         aP[r][j] = pa; aC[r][j] = cc; aN[r][j] = n;
       }
@@ -183,13 +202,12 @@ __global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const __grid_con
       for (int r = 0; r < kR; ++r) {
         if ((omask >> r) & 1u) {
           // c is what the reference keeps as the bf16 conv output; the GLU uses the same rounded values
-          const uint32_t cxa = pack_bf16(aP[r][0], aP[r][1]), cg = pack_bf16(aP[r][2], aP[r][3]);
+          const uint32_t cxa = pack2(aP[r][0]), cg = pack2(aP[r][1]);
           if (out_a) {
             *reinterpret_cast<uint32_t*>(out_a + (uint64_t)row_b * (uint32_t)r) = cxa;
             *reinterpret_cast<uint32_t*>(out_g + (uint64_t)row_b * (uint32_t)r) = cg;
           }
-          *reinterpret_cast<uint32_t*>(out_m + (uint64_t)mid_row_b * (uint32_t)r) =
-              pack_bf16(bf16_lo(cxa) * silu_f(bf16_lo(cg)), bf16_hi(cxa) * silu_f(bf16_hi(cg)));
+          *reinterpret_cast<uint32_t*>(out_m + (uint64_t)mid_row_b * (uint32_t)r) = pack2(mul2(unpack2(cxa), silu2(unpack2(cg))));
         }
       }
       out_m += mcol_b;
@@ -228,13 +246,11 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbArgs& a, uint8_t* smem
   const int64_t C2 = 2 * (int64_t)Hd;
   const int64_t ch = (KIND ? Hd : 0) + cl;
 
-  float w[9][2];
-  float dw[9][2], db[2] = {0.f, 0.f};
+  f2 w[9], dw[9], db = bc2(0.f);
 #pragma unroll
   for (int k = 0; k < 9; ++k) {
-    dw[k][0] = dw[k][1] = 0.f;
-    w[k][0] = live ? __bfloat162float(p.w[ch * 9 + k]) : 0.f;
-    w[k][1] = live ? __bfloat162float(p.w[(ch + 1) * 9 + k]) : 0.f;
+    dw[k] = bc2(0.f);
+    w[k] = live ? mk2(__bfloat162float(p.w[ch * 9 + k]), __bfloat162float(p.w[(ch + 1) * 9 + k])) : bc2(0.f);
   }
 
   if (y0 < H) {                                                   // whole warp
@@ -268,13 +284,13 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbArgs& a, uint8_t* smem
 #pragma unroll
     for (int r = 0; r < kR; ++r) omask |= (live && y0 + r < H) ? (1u << r) : 0u;
 
-    float win0[kIn][2], win1[kIn][2], win2[kIn][2];
+    f2 win0[kIn], win1[kIn], win2[kIn];
 #pragma unroll
-    for (int i = 0; i < kIn; ++i) win0[i][0] = win0[i][1] = win1[i][0] = win1[i][1] = win2[i][0] = win2[i][1] = 0.f;
+    for (int i = 0; i < kIn; ++i) win0[i] = win1[i] = win2[i] = bc2(0.f);
 
     // step t: dc column t -> cP; outputs of column t-1 from (cM, cC, cP) = dc columns (t-2, t-1, t).
     // tap (ky, kx) pairs with dc at (y - ky + 1, x - kx + 1): window row r - ky + 2, column kx = 0 -> cP, 1 -> cC, 2 -> cM.
-    auto step = [&](int t, float (&cM)[kIn][2], float (&cC)[kIn][2], float (&cP)[kIn][2]) {
+    auto step = [&](int t, f2 (&cM)[kIn], f2 (&cC)[kIn], f2 (&cP)[kIn]) {
       if (t + kStages - 1 <= W) issue(t + kStages - 1);           // into the slot read in step t-1
       const int s_idx = t & (kStages - 1);
       mbar_wait(bars + 8 * s_idx, (uint32_t)(t / kStages) & 1u);
@@ -284,19 +300,13 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbArgs& a, uint8_t* smem
         uint32_t rg, rd;
         asm volatile("ld.shared.b32 %0, [%1];" : "=r"(rg) : "r"(col + i * kRowB));
         asm volatile("ld.shared.b32 %0, [%1];" : "=r"(rd) : "r"(col + (kIn + i) * kRowB));
-        const float g[2] = {bf16_lo(rg), bf16_hi(rg)}, dm[2] = {bf16_lo(rd), bf16_hi(rd)};
+        const f2 g = unpack2(rg), dm = unpack2(rd);
         if (KIND) {
           uint32_t rx;
           asm volatile("ld.shared.b32 %0, [%1];" : "=r"(rx) : "r"(col + (2 * kIn + kR + i) * kRowB));
-          const float xa[2] = {bf16_lo(rx), bf16_hi(rx)};
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            const float sg = fmaf(0.5f, tanh_approx(0.5f * g[e]), 0.5f);
-            cP[i][e] = (dm[e] * xa[e]) * (sg * fmaf(g[e], 1.0f - sg, 1.0f));   // dmid * xa * silu'(g)
-          }
+          cP[i] = mul2(mul2(dm, unpack2(rx)), silu_grad_from_sigmoid2(g, sigmoid2(g)));   // dmid * xa * silu'(g)
         } else {
-#pragma unroll
-          for (int e = 0; e < 2; ++e) cP[i][e] = dm[e] * silu_f(g[e]);          // dmid * silu(g)
+          cP[i] = mul2(dm, silu2(g));                                                    // dmid * silu(g)
         }
       }
       uint32_t ru[kR];
@@ -306,27 +316,22 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbArgs& a, uint8_t* smem
       if (t > 0) {
 #pragma unroll
         for (int r = 0; r < kR; ++r) {
-          const float uu[2] = {bf16_lo(ru[r]), bf16_hi(ru[r])};
-          float o[2];
+          const f2 uu = unpack2(ru[r]);
+          const f2 sg = sigmoid2(uu);
+          const f2 sv = mul2(uu, sg), d = silu_grad_from_sigmoid2(uu, sg);
+          f2 acc = bc2(0.f);
 #pragma unroll
-          for (int j = 0; j < 2; ++j) {
-            float s, d;
-            silu_and_grad(uu[j], s, d);
-            float acc = 0.f;
-#pragma unroll
-            for (int ky = 0; ky < 3; ++ky) {
-              const float d0 = cP[r - ky + 2][j], d1 = cC[r - ky + 2][j], d2 = cM[r - ky + 2][j];
-              acc = fmaf(w[3 * ky + 0][j], d0, acc);
-              acc = fmaf(w[3 * ky + 1][j], d1, acc);
-              acc = fmaf(w[3 * ky + 2][j], d2, acc);
-              dw[3 * ky + 0][j] = fmaf(s, d0, dw[3 * ky + 0][j]);
-              dw[3 * ky + 1][j] = fmaf(s, d1, dw[3 * ky + 1][j]);
-              dw[3 * ky + 2][j] = fmaf(s, d2, dw[3 * ky + 2][j]);
-            }
-            db[j] += cC[r + 1][j];
-            o[j] = acc * d;
+          for (int ky = 0; ky < 3; ++ky) {
+            const f2 d0 = cP[r - ky + 2], d1 = cC[r - ky + 2], d2 = cM[r - ky + 2];
+            acc = fma2(w[3 * ky + 0], d0, acc);
+            acc = fma2(w[3 * ky + 1], d1, acc);
+            acc = fma2(w[3 * ky + 2], d2, acc);
+            dw[3 * ky + 0] = fma2(sv, d0, dw[3 * ky + 0]);
+            dw[3 * ky + 1] = fma2(sv, d1, dw[3 * ky + 1]);
+            dw[3 * ky + 2] = fma2(sv, d2, dw[3 * ky + 2]);
           }
-          if ((omask >> r) & 1u) *reinterpret_cast<uint32_t*>(out_u + (uint64_t)row_b * (uint32_t)r) = pack_bf16(o[0], o[1]);
+          db = add2(db, cC[r + 1]);
+          if ((omask >> r) & 1u) *reinterpret_cast<uint32_t*>(out_u + (uint64_t)row_b * (uint32_t)r) = pack2(mul2(acc, d));
         }
         out_u += col_b;
       }
@@ -342,15 +347,12 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbArgs& a, uint8_t* smem
   // for and every slot read is done once all warps have passed the barrier.
   __syncthreads();
   float (*red)[20][32] = reinterpret_cast<float (*)[20][32]>(smem);
-  if (!live) {
-#pragma unroll
-    for (int k = 0; k < 9; ++k) dw[k][0] = dw[k][1] = 0.f;
-    db[0] = db[1] = 0.f;
-  }
 #pragma unroll
   for (int g = 0; g < 10; ++g) {
-    red[warp][2 * g + 0][lane] = g < 9 ? dw[g][0] : db[0];
-    red[warp][2 * g + 1][lane] = g < 9 ? dw[g][1] : db[1];
+    float lo, hi;
+    un2(g < 9 ? dw[g] : db, lo, hi);
+    red[warp][2 * g + 0][lane] = live ? lo : 0.f;
+    red[warp][2 * g + 1][lane] = live ? hi : 0.f;
   }
   __syncthreads();
   float* part = p.partial + ((int64_t)b * ytiles + yt) * C2 * 10;
