@@ -155,20 +155,29 @@ int yat_gate_residual_fwd(const void* res, const void* y, const void* gate, int6
 int yat_gate_residual_bwd(const void* dout, const void* y, const void* gate, int64_t mod_batch_stride,
                           int B, int N, int C, void* dy, void* dgate, void* workspace, void* stream);
 
+/* ---- (next, N1) bias gradient of a Linear layer: out[c] = sum_r a[r][c] ----------------------
+ * torch autograd's `grad_output.sum(0)` of every biased projection of the block (attention.to_out / attn2.to_q,k,v,
+ * diffusers Attention as used by utils/patch_sana_attention_layers.py:84-115).  a [rows, C] bf16 row-major,
+ * out [C] bf16, fp32 accumulation in a fixed order; workspace = yat_colsum_workspace_bytes(rows, C) bytes.
+ */
+int64_t yat_colsum_workspace_bytes(int64_t rows, int C);
+int yat_colsum_bf16(const void* a, int64_t rows, int C, void* out, void* workspace, void* stream);
+
 /* ---- (next, N1) fused middle of GLUMBConv ---------------------------------------------------
  * utils/patch_sana_attention_layers.py:106-111 -> GLUMBConv: SiLU, depthwise 3x3 (+bias, zero pad 1),
  * chunk, x * SiLU(gate).  Token-major (NHWC):
  *   u [B, H, W, 2*Hd] bf16 (conv_inverted output)   w_dw [2*Hd, 9] bf16   b_dw [2*Hd] bf16
  *   mid [B, H, W, Hd] bf16 (conv_point input);  Hd % 8 == 0 (any H, W: the image is cut into 4-row strips)
  * fwd optionally writes c [B, H, W, 2*Hd] bf16 = the depthwise-conv output (what autograd would keep);
- * bwd: (u, c, dmid) -> du [B,H,W,2*Hd], dw [2*Hd, 9] bf16, db [2*Hd] bf16;
+ * bwd: (u, c, dmid) -> du [B,H,W,2*Hd], dw [2*Hd, 9] bf16, db [2*Hd] bf16, and (du_colsum, may be NULL)
+ * sum over tokens of du [2*Hd] bf16 = the bias gradient of conv_inverted, formed from the fp32 values in the same pass;
  * workspace = yat_glumb_workspace_bytes(B, H, Hd) bytes (fixed-order partial sums).
  */
 int64_t yat_glumb_workspace_bytes(int B, int H, int Hd);
 int yat_glumb_mid_fwd(const void* u, const void* w_dw, const void* b_dw, int B, int H, int W, int Hd,
                       void* mid, void* c_out, void* stream);
 int yat_glumb_mid_bwd(const void* u, const void* c, const void* w_dw, const void* dmid,
-                      int B, int H, int W, int Hd, void* du, void* dw, void* db,
+                      int B, int H, int W, int Hd, void* du, void* dw, void* db, void* du_colsum,
                       void* workspace, void* stream);
 
 /* ---- (next) ragged text-embedding pad + mask -------------------------------------------

@@ -135,3 +135,35 @@ def test_fused_block_matches_reference_block(cuda):
     assert _rel(fused[0], truth[0]) < 2e-2
     for f, p, t in zip(fused, plain, truth):
         assert _rel(f, t) <= 1.25 * _rel(p, t) + 2e-3, (_rel(f, t), _rel(p, t))
+
+
+@pytest.mark.parametrize("rows,C", [(16384, 2240), (16 * 192, 2240), (1, 8), (33, 64), (100, 11200), (5000, 72)])
+def test_colsum_and_linear_bias_gradient(cuda, rows, C):
+    """yat_colsum_bf16 = grad_output.sum(0) of a biased Linear (fp32 accumulation, fixed order), and the Linear module
+    built on it: same forward, same dx / dW GEMMs, bias gradient at least as close to fp64 as torch's reduce."""
+    from yat_b200.linear import Linear, colsum
+    g = torch.Generator().manual_seed(rows + C)
+    a = torch.randn((rows, C), generator=g).to(torch.bfloat16).to(cuda)
+    s = colsum(a)
+    exact = a.double().sum(0)
+    assert s.shape == (C,) and s.dtype == torch.bfloat16
+    assert torch.equal(s, exact.to(torch.bfloat16)) or _rel(s, exact) < 4e-3
+    assert torch.equal(colsum(a), s)
+    if rows * C > 4_000_000 or C > 4096:
+        return
+    torch.manual_seed(0)
+    lin = Linear(C, 64).to(cuda).to(torch.bfloat16)
+    ref = torch.nn.Linear(C, 64).to(cuda).to(torch.bfloat16)
+    ref.load_state_dict(lin.state_dict())
+    x = a.view(1, rows, C).clone().requires_grad_(True)
+    xr = a.view(1, rows, C).clone().requires_grad_(True)
+    dy = torch.randn((1, rows, 64), generator=g).to(torch.bfloat16).to(cuda)
+    y, yr = lin(x), ref(xr)
+    assert torch.equal(y, yr)
+    y.backward(dy)
+    yr.backward(dy)
+    assert _rel(x.grad, xr.grad) < 1e-3 and _rel(lin.weight.grad, ref.weight.grad) < 1e-3
+    exact = dy.double().sum((0, 1))
+    assert _rel(lin.bias.grad, exact) <= _rel(ref.bias.grad, exact) + 3e-3
+    with pytest.raises(ValueError):
+        colsum(a.cpu())

@@ -111,3 +111,36 @@ def test_glumb_argument_errors(cuda):
         glumb_mid(torch.zeros((1, 16, 24), dtype=torch.bfloat16, device=cuda),
                   torch.zeros((24, 1, 3, 3), dtype=torch.bfloat16, device=cuda),
                   torch.zeros((24,), dtype=torch.bfloat16, device=cuda), 4, 4)
+
+
+@pytest.mark.parametrize("B,H,W,C,Hd", [(2, 16, 16, 128, 320), (1, 32, 32, 2240, 5600), (3, 5, 3, 40, 72)])
+def test_inverted_glumb_mid_bias_gradient_from_the_backward_kernel(cuda, B, H, W, C, Hd):
+    """conv_inverted + middle as one autograd node (inverted_glumb_mid): same forward and gradients as
+    F.linear -> glumb_mid, with conv_inverted's bias gradient = column sum of du formed inside glumb_bwd_kernel
+    (checked against the fp64 sum of the du the kernel wrote, and against the autograd chain)."""
+    from yat_b200.glumb import glumb_mid, inverted_glumb_mid
+    g = torch.Generator().manual_seed(B * 100 + C)
+    x = torch.randn((B, H * W, C), generator=g).to(torch.bfloat16).to(cuda)
+    wi = (torch.randn((2 * Hd, C), generator=g) * C ** -0.5).to(torch.bfloat16).to(cuda)
+    bi = (torch.randn((2 * Hd,), generator=g) * 0.2).to(torch.bfloat16).to(cuda)
+    w = (torch.randn((2 * Hd, 1, 3, 3), generator=g) * 0.3).to(torch.bfloat16).to(cuda)
+    b = (torch.randn((2 * Hd,), generator=g) * 0.2).to(torch.bfloat16).to(cuda)
+    dmid = torch.randn((B, H * W, Hd), generator=g).to(torch.bfloat16).to(cuda)
+
+    a = [t.clone().requires_grad_(True) for t in (x, wi, bi, w, b)]
+    mid = inverted_glumb_mid(*a, H, W)
+    mid.backward(dmid)
+    r = [t.clone().requires_grad_(True) for t in (x, wi, bi, w, b)]
+    u = F.linear(r[0], r[1], r[2])
+    u.retain_grad()
+    ref = glumb_mid(u, r[3], r[4], H, W)
+    ref.backward(dmid)
+    assert torch.equal(mid, ref)
+    assert torch.equal(a[3].grad, r[3].grad) and torch.equal(a[4].grad, r[4].grad)
+    assert _rel(a[0].grad, r[0].grad) < 1e-3 and _rel(a[1].grad, r[1].grad) < 1e-3      # same GEMMs
+    exact = u.grad.double().sum((0, 1))
+    assert _rel(a[2].grad, exact) < 6e-3          # fp32 sum of the unrounded du, one bf16 rounding
+    assert _rel(a[2].grad, exact) <= _rel(r[2].grad, exact) + 3e-3
+    a2 = [t.clone().requires_grad_(True) for t in (x, wi, bi, w, b)]
+    inverted_glumb_mid(*a2, H, W).backward(dmid)
+    assert torch.equal(a2[2].grad, a[2].grad)     # deterministic

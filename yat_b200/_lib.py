@@ -46,7 +46,9 @@ SIGNATURES = {
     "yat_glumb_mid_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                   c_void_p]),
     "yat_glumb_mid_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
-                                  c_void_p, c_void_p, c_void_p, c_void_p]),
+                                  c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "yat_colsum_workspace_bytes": (c_int64, [c_int64, c_int]),
+    "yat_colsum_bf16": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p]),
     "yat_optim_chunk_elems": (c_int, []),
     "yat_optim_workspace_bytes": (c_int64, [c_int]),
     "yat_grad_clip_coef": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p]),
@@ -65,7 +67,7 @@ LAUNCHING = ("yat_noise_flowmatch", "yat_noise_ddpm", "yat_loss_fused", "yat_rep
              "yat_linattn_bwd", "yat_linattn_fwd_simt", "yat_linattn_bwd_simt", "yat_pad_embeddings",
              "yat_philox_raw", "yat_ln_modulate_fwd", "yat_ln_modulate_bwd", "yat_gate_residual_fwd",
              "yat_gate_residual_bwd", "yat_glumb_mid_fwd", "yat_glumb_mid_bwd", "yat_grad_clip_coef",
-             "yat_adamw_step")
+             "yat_adamw_step", "yat_colsum_bf16")
 launch_counts = {name: 0 for name in LAUNCHING}
 
 

@@ -14,6 +14,7 @@ import torch
 import torch.nn.functional as F
 from torch import nn
 
+from .linear import Linear
 from .linear_attention import sana_linear_attention
 
 
@@ -84,10 +85,11 @@ class Attention(nn.Module):
         self.heads = heads
         self.norm_q = None
         self.norm_k = None
-        self.to_q = nn.Linear(query_dim, self.inner_dim, bias=bias)
-        self.to_k = nn.Linear(self.cross_attention_dim, self.inner_dim, bias=bias)
-        self.to_v = nn.Linear(self.cross_attention_dim, self.inner_dim, bias=bias)
-        self.to_out = nn.ModuleList([nn.Linear(self.inner_dim, query_dim, bias=out_bias), nn.Dropout(dropout)])
+        # nn.Linear parameters / keys; the bias gradient comes from yat_colsum_bf16 (linear.py)
+        self.to_q = Linear(query_dim, self.inner_dim, bias=bias)
+        self.to_k = Linear(self.cross_attention_dim, self.inner_dim, bias=bias)
+        self.to_v = Linear(self.cross_attention_dim, self.inner_dim, bias=bias)
+        self.to_out = nn.ModuleList([Linear(self.inner_dim, query_dim, bias=out_bias), nn.Dropout(dropout)])
         self.processor = processor if processor is not None else AttnProcessor2_0()
 
     def set_processor(self, processor) -> None:

@@ -153,6 +153,135 @@ __global__ void __launch_bounds__(kThreads) ln_modulate_bwd_dx_kernel(
 }
 
 // ------------------------------------------------------------------------------------------------
+// ln_modulate backward, ONE pass: dx (row part, as above) and the per-sample column sums
+//   dscale[b][c] = sum_n dy * xhat      dshift[b][c] = sum_n dy
+// from the same registers, so x and dy are read once (6·C B per token instead of 10·C).  CTA = (row split, sample),
+// 8 warps = 4 warp pairs, one row per pair at a time: the two warps of a pair own alternate 32-vector blocks of the
+// row (x and dy of their half live in registers, 2 * MAXH 128-bit loads in flight per lane) and exchange their two
+// partial row sums through shared memory with a 64-thread named barrier (slots alternate by row, so one barrier per
+// row).  Every pair owns a private fp32 accumulator image of the two [C] rows in shared memory, laid out as planes of
+// 16 bytes per 8-column vector so that lane-contiguous accesses are conflict-free, and touched only by the lane that
+// owns the vector.  Arithmetic on packed fp32 pairs (FFMA2).  Pairs are added in fixed order, splits by
+// column_finish_kernel -> bit-identical run to run.
+// ------------------------------------------------------------------------------------------------
+constexpr int kLnBwdPairs = 4;
+constexpr int kLnBwdThreads = kLnBwdPairs * 64;
+
+template <int MAXH>
+__global__ void __launch_bounds__(kLnBwdThreads, MAXH <= 5 ? 3 : 1) ln_modulate_bwd_fused_kernel(
+    const uint4* __restrict__ x, const uint4* __restrict__ dy, const uint4* __restrict__ scale,
+    int64_t mod_stride_vec, const float* __restrict__ mean_in, const float* __restrict__ rstd_in, int N, int nvec,
+    int rows_per_split, float inv_c, uint4* __restrict__ dx, float* __restrict__ part0, float* __restrict__ part1) {
+  extern __shared__ __align__(16) ulonglong2 acc_smem[];          // [pair][kind: dscale, dshift][plane][nvec] x 4 floats
+  __shared__ float xchg[kLnBwdPairs][2][2][2];                    // [pair][row parity][half][s1, s2]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int pair = warp >> 1, half = warp & 1;
+  const int split = blockIdx.x, b = blockIdx.y;
+  ulonglong2* acc = acc_smem + (size_t)pair * 4 * nvec;
+  for (int i = (half * 32 + lane); i < 4 * nvec; i += 64) acc[i] = make_ulonglong2(0ull, 0ull);   // fp32 +0.0 pairs
+  asm volatile("bar.sync %0, 64;" ::"r"(pair + 1) : "memory");
+  const int r0 = split * rows_per_split;
+  const int r1 = min(N, r0 + rows_per_split);
+  const uint4* sc = scale + (int64_t)b * mod_stride_vec;
+  const f2 one = bc2(1.0f);
+  int parity = 0;
+  for (int r = r0 + pair; r < r1; r += kLnBwdPairs, parity ^= 1) {
+    const int64_t row = (int64_t)b * N + r;
+    const uint4* xr = x + row * nvec;
+    const uint4* gr = dy + row * nvec;
+    if (lane == 0 && r + 2 * kLnBwdPairs < r1) {                   // pull the pair's row after next into L2: no registers held
+      const uint4* nxt = (half ? gr : xr) + (int64_t)2 * kLnBwdPairs * nvec;
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nxt), "r"(nvec * 16) : "memory");
+    }
+    uint4 xv[MAXH], gv[MAXH];
+#pragma unroll
+    for (int i = 0; i < MAXH; ++i) {
+      const int c = (2 * i + half) * 32 + lane;
+      if (c < nvec) {
+        xv[i] = ld_stream(xr + c);
+        gv[i] = ld_stream(gr + c);
+      }
+    }
+    const float mean = mean_in[row], rstd = rstd_in[row];
+    const f2 rs = bc2(rstd), nmr = bc2(-mean * rstd);              // xhat = x * rstd - mean * rstd
+    f2 s1 = bc2(0.f), s2 = bc2(0.f);
+#pragma unroll
+    for (int i = 0; i < MAXH; ++i) {
+      const int c = (2 * i + half) * 32 + lane;
+      if (c < nvec) {
+        const uint4 av = ld_cached(sc + c);
+        const uint32_t xw[4] = {xv[i].x, xv[i].y, xv[i].z, xv[i].w}, gw[4] = {gv[i].x, gv[i].y, gv[i].z, gv[i].w},
+                       aw[4] = {av.x, av.y, av.z, av.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const f2 gg = mul2(unpack2(gw[j]), add2(unpack2(aw[j]), one));
+          s1 = add2(s1, gg);
+          s2 = fma2(gg, fma2(unpack2(xw[j]), rs, nmr), s2);
+        }
+      }
+    }
+    float s1a, s1b, s2a, s2b;
+    un2(s1, s1a, s1b);
+    un2(s2, s2a, s2b);
+    const float h1 = warp_sum(s1a + s1b), h2 = warp_sum(s2a + s2b);
+    if (lane == 0) {
+      xchg[pair][parity][half][0] = h1;
+      xchg[pair][parity][half][1] = h2;
+    }
+    asm volatile("bar.sync %0, 64;" ::"r"(pair + 1) : "memory");
+    const float c1 = (xchg[pair][parity][0][0] + xchg[pair][parity][1][0]) * inv_c;
+    const float c2 = (xchg[pair][parity][0][1] + xchg[pair][parity][1][1]) * inv_c;
+    const f2 nc1r = bc2(-c1 * rstd), nc2r = bc2(-c2 * rstd);       // dx = gg * rstd - c1 * rstd - xhat * c2 * rstd
+    uint4* dr = dx + row * nvec;
+#pragma unroll
+    for (int i = 0; i < MAXH; ++i) {
+      const int c = (2 * i + half) * 32 + lane;
+      if (c < nvec) {
+        const uint4 av = ld_cached(sc + c);
+        const uint32_t xw[4] = {xv[i].x, xv[i].y, xv[i].z, xv[i].w}, gw[4] = {gv[i].x, gv[i].y, gv[i].z, gv[i].w},
+                       aw[4] = {av.x, av.y, av.z, av.w};
+        uint32_t ow[4];
+        f2 dsc[4], dsh[4];
+        {
+          const ulonglong2 t0 = acc[0 * nvec + c], t1 = acc[1 * nvec + c], t2 = acc[2 * nvec + c], t3 = acc[3 * nvec + c];
+          dsc[0].v = t0.x; dsc[1].v = t0.y; dsc[2].v = t1.x; dsc[3].v = t1.y;
+          dsh[0].v = t2.x; dsh[1].v = t2.y; dsh[2].v = t3.x; dsh[3].v = t3.y;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const f2 g = unpack2(gw[j]);
+          const f2 xh = fma2(unpack2(xw[j]), rs, nmr);
+          const f2 gg = mul2(g, add2(unpack2(aw[j]), one));
+          ow[j] = pack2(fma2(xh, nc2r, fma2(gg, rs, nc1r)));
+          dsc[j] = fma2(g, xh, dsc[j]);
+          dsh[j] = add2(dsh[j], g);
+        }
+        st_stream(dr + c, make_uint4(ow[0], ow[1], ow[2], ow[3]));
+        acc[0 * nvec + c] = make_ulonglong2(dsc[0].v, dsc[1].v);
+        acc[1 * nvec + c] = make_ulonglong2(dsc[2].v, dsc[3].v);
+        acc[2 * nvec + c] = make_ulonglong2(dsh[0].v, dsh[1].v);
+        acc[3 * nvec + c] = make_ulonglong2(dsh[2].v, dsh[3].v);
+      }
+    }
+  }
+  __syncthreads();
+  const float* af = reinterpret_cast<const float*>(acc_smem);
+  const int C = nvec * 8;
+  for (int col = threadIdx.x; col < C; col += kLnBwdThreads) {
+    const int c = col >> 3, plane = (col >> 2) & 1, j = col & 3;
+    float t0 = 0.f, t1 = 0.f;
+#pragma unroll
+    for (int w = 0; w < kLnBwdPairs; ++w) {
+      t0 += af[(((size_t)w * 4 + plane) * nvec + c) * 4 + j];
+      t1 += af[(((size_t)w * 4 + 2 + plane) * nvec + c) * 4 + j];
+    }
+    const int64_t o = ((int64_t)split * gridDim.y + b) * C + col;
+    part0[o] = t0;
+    part1[o] = t1;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Column pass: lanes run along C (coalesced 512 B per warp per row), warps stride over the rows of one
 // (sample, split); per-thread partial sums -> shared memory over the 8 warps -> partial[split][b][C] fp32.
 //   kColLn    sum_n dy * xhat  and  sum_n dy                     (gradients of scale and shift)
@@ -239,6 +368,63 @@ __global__ void __launch_bounds__(256) column_finish_kernel(const float* __restr
   if (part1) out1[i] = __float2bfloat16_rn(s1);
 }
 
+// ------------------------------------------------------------------------------------------------
+// colsum: out[c] = sum_r a[r][c] for a [rows, C] bf16 matrix = the bias gradient of a Linear layer (dy.sum(0) in
+// autograd: a strided torch reduce at ~2 TB/s).  Same lanes-along-C / warps-over-rows shape as the column pass,
+// 4 rows in flight per thread, fp32 partial per (split, column) -> column_finish_kernel (fixed order).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) colsum_kernel(const uint4* __restrict__ a, int64_t rows, int nvec,
+                                                          int rows_per_split, float* __restrict__ part) {
+  __shared__ float red[kWarpsPerBlock][32 * 8 + 8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_split;
+  const int64_t r1 = r0 + rows_per_split < rows ? r0 + rows_per_split : rows;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (c < nvec) {
+    const uint4* col = a + c;
+    int64_t r = r0 + warp;
+    for (; r + 3 * kWarpsPerBlock < r1; r += 4 * kWarpsPerBlock) {
+      uint4 v[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) v[i] = ld_stream(col + (r + i * kWarpsPerBlock) * nvec);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float f[8];
+        unpack8(v[i], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      }
+    }
+    for (; r < r1; r += kWarpsPerBlock) {
+      float f[8];
+      unpack8(ld_stream(col + r * nvec), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += f[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[warp][lane * 8 + j] = acc[j];
+  __syncthreads();
+  const int colx = blockIdx.x * 256 + threadIdx.x;
+  if (colx < nvec * 8) {
+    float s0 = 0.f;
+#pragma unroll
+    for (int w = 0; w < kWarpsPerBlock; ++w) s0 += red[w][threadIdx.x];
+    part[(int64_t)blockIdx.y * (nvec * 8) + colx] = s0;
+  }
+}
+
+inline int colsum_splits(int64_t rows, int C) {   // ~8 CTAs per SM, at least 32 rows per split
+  const int colblocks = (C / 8 + 31) / 32;
+  int64_t s = (kNumSMs * 8 + colblocks - 1) / colblocks;
+  const int64_t cap = (rows + 31) / 32;
+  if (s > cap) s = cap;
+  return (int)(s < 1 ? 1 : s);
+}
+
 // gate_residual forward: out = res + gate_b * y
 __global__ void __launch_bounds__(kThreads) gate_residual_fwd_kernel(
     const uint4* __restrict__ res, const uint4* __restrict__ y, const uint4* __restrict__ gate,
@@ -263,6 +449,17 @@ inline int split_count(int N) {  // rows per split >= 64, at most 16 splits
   return s < 1 ? 1 : (s > 16 ? 16 : s);
 }
 
+// fused ln_modulate backward: one wave of CTAs (B * splits <= SMs * resident CTAs), at least one row per warp pair
+inline int ln_bwd_smem(int C) { return kLnBwdPairs * 2 * C * (int)sizeof(float); }
+inline int ln_bwd_splits(int B, int N, int C) {
+  int per_sm = (227 * 1024) / (ln_bwd_smem(C) + 1024);
+  per_sm = per_sm < 1 ? 1 : (per_sm > 3 ? 3 : per_sm);
+  int s = (kNumSMs * per_sm) / B;
+  const int cap = (N + kLnBwdPairs - 1) / kLnBwdPairs;
+  if (s > cap) s = cap;
+  return s < 1 ? 1 : s;
+}
+
 // MAXV = 128-bit vectors per lane that cover one row: dispatch on ceil(nvec / 32)
 #define YAT_DISPATCH_MAXV(per_lane, ...)                      \
   do {                                                        \
@@ -284,8 +481,31 @@ int check_common(const char* what, int B, int N, int C, int64_t mod_stride) {
 }  // namespace
 }  // namespace yat
 
+extern "C" int64_t yat_colsum_workspace_bytes(int64_t rows, int C) {
+  return (int64_t)yat::colsum_splits(rows, C) * C * (int64_t)sizeof(float);
+}
+
+extern "C" int yat_colsum_bf16(const void* a, int64_t rows, int C, void* out, void* workspace, void* stream) {
+  using namespace yat;
+  YAT_REQUIRE(a && out && workspace, YAT_ERR_BAD_ARG, "yat_colsum_bf16: null pointer argument");
+  YAT_REQUIRE(rows > 0 && C > 0, YAT_ERR_BAD_ARG, "yat_colsum_bf16: rows=%lld C=%d must be positive", (long long)rows, C);
+  YAT_REQUIRE(C % 8 == 0, YAT_ERR_UNSUPPORTED, "yat_colsum_bf16: C=%d must be a multiple of 8", C);
+  YAT_REQUIRE(aligned16(a), YAT_ERR_BAD_ARG, "yat_colsum_bf16: the matrix must be 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nvec = C / 8, splits = colsum_splits(rows, C);
+  const int rows_per_split = (int)((rows + splits - 1) / splits);
+  colsum_kernel<<<dim3((nvec + 31) / 32, splits), kThreads, 0, st>>>((const uint4*)a, rows, nvec, rows_per_split,
+                                                                    (float*)workspace);
+  int rc = check_launch("colsum");
+  if (rc != YAT_OK) return rc;
+  column_finish_kernel<<<(unsigned)((C + 255) / 256), 256, 0, st>>>((const float*)workspace, nullptr, splits, C,
+                                                                   (__nv_bfloat16*)out, nullptr);
+  return check_launch("colsum_finish");
+}
+
 extern "C" int64_t yat_block_workspace_bytes(int B, int N, int C) {
-  return (int64_t)2 * yat::split_count(N) * B * C * (int64_t)sizeof(float);
+  const int a = yat::split_count(N), b = yat::ln_bwd_splits(B, N, C);
+  return (int64_t)2 * (a > b ? a : b) * B * C * (int64_t)sizeof(float);
 }
 
 extern "C" int yat_ln_modulate_fwd(const void* x, const void* scale, const void* shift, int64_t mod_batch_stride,
@@ -317,22 +537,34 @@ extern "C" int yat_ln_modulate_bwd(const void* x, const void* dy, const void* sc
               "yat_ln_modulate_bwd: tensors must be 16-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
   const int nvec = C / 8, rows = B * N;
-  const int grid = (rows + kWarpsPerBlock - 1) / kWarpsPerBlock;
-  YAT_DISPATCH_MAXV((nvec + 31) / 32, ln_modulate_bwd_dx_kernel<MAXV><<<grid, kThreads, 0, st>>>(
-      (const uint4*)x, (const uint4*)dy, (const uint4*)scale, mod_batch_stride / 8, mean, rstd, rows, N, nvec,
-      1.0f / C, (uint4*)dx));
-  rc = check_launch("ln_modulate_bwd_dx");
-  if (rc != YAT_OK) return rc;
-  const int splits = split_count(N), rows_per_split = (N + splits - 1) / splits;
+  (void)rows;
+  const int splits = ln_bwd_splits(B, N, C), rows_per_split = (N + splits - 1) / splits;
+  const int smem = ln_bwd_smem(C);
   float* part0 = (float*)workspace;
   float* part1 = part0 + (int64_t)splits * B * C;
-  const dim3 g((nvec + 31) / 32, splits, B);
-  column_pass_kernel<kColLn><<<g, kThreads, 0, st>>>((const uint4*)dy, (const uint4*)x, nullptr, 0, mean, rstd, N, nvec,
-                                                     rows_per_split, nullptr, part0, part1);
+#define YAT_LN_BWD_LAUNCH(MAXH)                                                                                       \
+  do {                                                                                                               \
+    static bool attr_set = false;                                                                                    \
+    if (!attr_set) {                                                                                                 \
+      cudaFuncSetAttribute(ln_modulate_bwd_fused_kernel<MAXH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024); \
+      attr_set = true;                                                                                               \
+    }                                                                                                                \
+    ln_modulate_bwd_fused_kernel<MAXH><<<dim3(splits, B), kLnBwdThreads, smem, st>>>(                                 \
+        (const uint4*)x, (const uint4*)dy, (const uint4*)scale, mod_batch_stride / 8, mean, rstd, N, nvec,           \
+        rows_per_split, 1.0f / C, (uint4*)dx, part0, part1);                                                         \
+  } while (0)
+  const int per_half = ((nvec + 31) / 32 + 1) / 2;                 // 32-vector blocks per warp of a pair
+  if (per_half <= 1)      YAT_LN_BWD_LAUNCH(1);
+  else if (per_half <= 2) YAT_LN_BWD_LAUNCH(2);
+  else if (per_half <= 5) YAT_LN_BWD_LAUNCH(5);
+  else                    YAT_LN_BWD_LAUNCH(8);
+#undef YAT_LN_BWD_LAUNCH
+  rc = check_launch("ln_modulate_bwd_fused");
+  if (rc != YAT_OK) return rc;
   const int64_t bc = (int64_t)B * C;
   column_finish_kernel<<<(unsigned)((bc + 255) / 256), 256, 0, st>>>(part0, part1, splits, bc, (__nv_bfloat16*)dscale,
                                                                     (__nv_bfloat16*)dshift);
-  return check_launch("ln_modulate_bwd_cols");
+  return check_launch("ln_modulate_bwd_finish");
 }
 
 extern "C" int yat_gate_residual_fwd(const void* res, const void* y, const void* gate, int64_t mod_batch_stride, int B,

@@ -38,6 +38,7 @@ constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;              // row strips per CTA (8 -> 32 rows)
 constexpr int kR = 4;                              // output rows per warp
 constexpr int kIn = kR + 2;                        // input rows per column (halo above and below)
+constexpr int kPart = 11;                         // backward partials per channel: dw[9], db, sum(du)
 constexpr int kStages = 4;                         // ring slots per warp: columns t .. t+3 resident / in flight
 constexpr int kRowB = 128;                         // bytes of one box row: 64 bf16 channels
 constexpr int kFwdSlotB = 2 * kIn * kRowB;                         // u: A rows | gate rows
@@ -46,18 +47,6 @@ constexpr int kBwdSlotB1 = (3 * kIn + kR) * kRowB;                 // half G:  g
 constexpr int kBarBytes = kWarps * kStages * 8;
 constexpr int kFwdSmem = kWarps * kStages * kFwdSlotB + kBarBytes;
 constexpr int kBwdSmem = kWarps * kStages * kBwdSlotB1 + kBarBytes;
-
-// Packed fp32 pairs (Blackwell FFMA2 / FMUL2 / FADD2: one issue slot for the two channels a lane owns; each half is
-// an IEEE fp32 operation, so results equal the scalar form).  The kernels are issue-bound, not pipe-bound.
-struct f2 { unsigned long long v; };
-__device__ __forceinline__ f2 mk2(float lo, float hi) { f2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(lo), "f"(hi)); return r; }
-__device__ __forceinline__ f2 bc2(float x) { return mk2(x, x); }
-__device__ __forceinline__ void un2(f2 a, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.v)); }
-__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) { f2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v)); return r; }
-__device__ __forceinline__ f2 mul2(f2 a, f2 b) { f2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
-__device__ __forceinline__ f2 add2(f2 a, f2 b) { f2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
-__device__ __forceinline__ f2 unpack2(uint32_t w) { return mk2(bf16_lo(w), bf16_hi(w)); }   // bf16x2 word -> fp32 pair
-__device__ __forceinline__ uint32_t pack2(f2 a) { float lo, hi; un2(a, lo, hi); return pack_bf16(lo, hi); }
 
 // silu through ONE special-function op:  sigmoid(x) = 0.5 + 0.5 tanh(x / 2)  =>  silu(x) = h + h tanh(h), h = x / 2.
 // tanh.approx.f32 has 2^-11 relative error, i.e. |error(silu)| <= 2.5e-4 |x|: below the bf16 rounding of the
@@ -89,7 +78,7 @@ struct GlumbParams {
   __nv_bfloat16* mid;         // [B, H, W, Hd]   (forward out)
   __nv_bfloat16* c;           // [B, H, W, 2*Hd] conv output (forward out, optional)
   __nv_bfloat16* du;          // [B, H, W, 2*Hd] (backward out)
-  float* partial;             // [B * y-tiles, 2*Hd, 10] (backward)
+  float* partial;             // [B * y-tiles, 2*Hd, kPart] (backward)
   int B, H, W, Hd;
 };
 struct alignas(64) GlumbArgs {
@@ -246,7 +235,7 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbArgs& a, uint8_t* smem
   const int64_t C2 = 2 * (int64_t)Hd;
   const int64_t ch = (KIND ? Hd : 0) + cl;
 
-  f2 w[9], dw[9], db = bc2(0.f);
+  f2 w[9], dw[9], db = bc2(0.f), dbu = bc2(0.f);
 #pragma unroll
   for (int k = 0; k < 9; ++k) {
     dw[k] = bc2(0.f);
@@ -331,7 +320,11 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbArgs& a, uint8_t* smem
             dw[3 * ky + 2] = fma2(sv, d2, dw[3 * ky + 2]);
           }
           db = add2(db, cC[r + 1]);
-          if ((omask >> r) & 1u) *reinterpret_cast<uint32_t*>(out_u + (uint64_t)row_b * (uint32_t)r) = pack2(mul2(acc, d));
+          if ((omask >> r) & 1u) {
+            const f2 o = mul2(acc, d);
+            dbu = add2(dbu, o);                                   // column sum of du = bias gradient of conv_inverted
+            *reinterpret_cast<uint32_t*>(out_u + (uint64_t)row_b * (uint32_t)r) = pack2(o);
+          }
         }
         out_u += col_b;
       }
@@ -346,23 +339,23 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbArgs& a, uint8_t* smem
   // per-CTA sums over the strips, fixed order.  The scratch aliases the rings: every TMA write has been waited
   // for and every slot read is done once all warps have passed the barrier.
   __syncthreads();
-  float (*red)[20][32] = reinterpret_cast<float (*)[20][32]>(smem);
+  float (*red)[2 * kPart][32] = reinterpret_cast<float (*)[2 * kPart][32]>(smem);
 #pragma unroll
-  for (int g = 0; g < 10; ++g) {
+  for (int g = 0; g < kPart; ++g) {
     float lo, hi;
-    un2(g < 9 ? dw[g] : db, lo, hi);
+    un2(g < 9 ? dw[g] : (g == 9 ? db : dbu), lo, hi);
     red[warp][2 * g + 0][lane] = live ? lo : 0.f;
     red[warp][2 * g + 1][lane] = live ? hi : 0.f;
   }
   __syncthreads();
-  float* part = p.partial + ((int64_t)b * ytiles + yt) * C2 * 10;
-  for (int i = tid; i < 2 * 10 * 32; i += kThreads) {              // (j, g, lane)
-    const int l = i & 31, g = (i >> 5) % 10, j = i / 320;
+  float* part = p.partial + ((int64_t)b * ytiles + yt) * C2 * kPart;
+  for (int i = tid; i < 2 * kPart * 32; i += kThreads) {           // (j, g, lane)
+    const int l = i & 31, g = (i >> 5) % kPart, j = i / (32 * kPart);
     float s = 0.f;
 #pragma unroll
     for (int st = 0; st < kWarps; ++st) s += red[st][2 * g + j][l];
     const int cq = c0 + 2 * l;
-    if (cq < Hd) part[((KIND ? Hd : 0) + cq + j) * 10 + g] = s;
+    if (cq < Hd) part[((KIND ? Hd : 0) + cq + j) * kPart + g] = s;
   }
 }
 
@@ -373,16 +366,18 @@ __global__ void __launch_bounds__(kThreads, 2) glumb_bwd_kernel(const __grid_con
   else            glumb_bwd_body<0>(a, smem);
 }
 
-__global__ void __launch_bounds__(256) glumb_finish_kernel(const float* __restrict__ partial, int parts, int64_t n10,
-                                                           __nv_bfloat16* __restrict__ dw, __nv_bfloat16* __restrict__ db) {
-  const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;   // over [2*Hd][10]
-  if (i >= n10) return;
+__global__ void __launch_bounds__(256) glumb_finish_kernel(const float* __restrict__ partial, int parts, int64_t n,
+                                                           __nv_bfloat16* __restrict__ dw, __nv_bfloat16* __restrict__ db,
+                                                           __nv_bfloat16* __restrict__ dbu) {
+  const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;   // over [2*Hd][kPart]
+  if (i >= n) return;
   float s = 0.f;
-  for (int b = 0; b < parts; ++b) s += partial[(int64_t)b * n10 + i];
-  const int64_t ch = i / 10;
-  const int k = (int)(i - ch * 10);
-  if (k < 9) dw[ch * 9 + k] = __float2bfloat16_rn(s);
-  else       db[ch] = __float2bfloat16_rn(s);
+  for (int b = 0; b < parts; ++b) s += partial[(int64_t)b * n + i];
+  const int64_t ch = i / kPart;
+  const int k = (int)(i - ch * kPart);
+  if (k < 9)        dw[ch * 9 + k] = __float2bfloat16_rn(s);
+  else if (k == 9)  db[ch] = __float2bfloat16_rn(s);
+  else if (dbu)     dbu[ch] = __float2bfloat16_rn(s);
 }
 
 inline bool aligned16(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; }
@@ -407,7 +402,7 @@ int image_tmap(CUtensorMap* out, const void* base, int B, int H, int W, int64_t 
 }  // namespace yat
 
 extern "C" int64_t yat_glumb_workspace_bytes(int B, int H, int Hd) {
-  return (int64_t)B * yat::ytiles_of(H) * 2 * Hd * 10 * (int64_t)sizeof(float);
+  return (int64_t)B * yat::ytiles_of(H) * 2 * Hd * yat::kPart * (int64_t)sizeof(float);
 }
 
 extern "C" int yat_glumb_mid_fwd(const void* u, const void* w_dw, const void* b_dw, int B, int H, int W, int Hd,
@@ -432,7 +427,7 @@ extern "C" int yat_glumb_mid_fwd(const void* u, const void* w_dw, const void* b_
 }
 
 extern "C" int yat_glumb_mid_bwd(const void* u, const void* c, const void* w_dw, const void* dmid, int B, int H, int W,
-                                 int Hd, void* du, void* dw, void* db, void* workspace, void* stream) {
+                                 int Hd, void* du, void* dw, void* db, void* du_colsum, void* workspace, void* stream) {
   using namespace yat;
   YAT_REQUIRE(u && c && w_dw && dmid && du && dw && db && workspace, YAT_ERR_BAD_ARG,
               "yat_glumb_mid_bwd: null pointer argument");
@@ -455,8 +450,8 @@ extern "C" int yat_glumb_mid_bwd(const void* u, const void* c, const void* w_dw,
   const int parts = B * ytiles_of(H);
   glumb_bwd_kernel<<<dim3((Hd + 63) / 64, parts, 2), kThreads, kBwdSmem, st>>>(a);
   if ((rc = check_launch("glumb_bwd")) != YAT_OK) return rc;
-  const int64_t n10 = (int64_t)2 * Hd * 10;
-  glumb_finish_kernel<<<(unsigned)((n10 + 255) / 256), 256, 0, st>>>(a.p.partial, parts, n10, (__nv_bfloat16*)dw,
-                                                                   (__nv_bfloat16*)db);
+  const int64_t n = (int64_t)2 * Hd * kPart;
+  glumb_finish_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a.p.partial, parts, n, (__nv_bfloat16*)dw,
+                                                                 (__nv_bfloat16*)db, (__nv_bfloat16*)du_colsum);
   return check_launch("glumb_finish");
 }

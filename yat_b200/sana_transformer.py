@@ -25,7 +25,7 @@ from torch.utils.checkpoint import checkpoint
 from .attention import Attention, AttnProcessor2_0, SanaLinearAttnProcessorB200
 from .block_ops import gate_residual, ln_modulate
 from .adapters import adapter_term
-from .glumb import glumb_mid
+from .glumb import glumb_mid, inverted_glumb_mid
 
 
 class Transformer2DModelOutput:
@@ -146,11 +146,15 @@ class GLUMBConv(nn.Module):
         """Same module on token-major data [B, H*W, C] (the product path): the 1x1 convolutions are
         GEMMs on the conv weights viewed as [out, in], the middle is one fused kernel."""
         w_inv, w_pt = self.conv_inverted.weight, self.conv_point.weight
-        u = F.linear(hidden_states, w_inv.view(w_inv.shape[0], w_inv.shape[1]), self.conv_inverted.bias)
         t = adapter_term(self.conv_inverted, hidden_states)                # LoRA / LoKr term, None without an adapter
-        if t is not None:
-            u = u + t
-        mid = glumb_mid(u, self.conv_depth.weight, self.conv_depth.bias, height, width)
+        if t is None and self.conv_inverted.bias is not None:
+            mid = inverted_glumb_mid(hidden_states, w_inv.view(w_inv.shape[0], w_inv.shape[1]), self.conv_inverted.bias,
+                                     self.conv_depth.weight, self.conv_depth.bias, height, width)
+        else:
+            u = F.linear(hidden_states, w_inv.view(w_inv.shape[0], w_inv.shape[1]), self.conv_inverted.bias)
+            if t is not None:
+                u = u + t
+            mid = glumb_mid(u, self.conv_depth.weight, self.conv_depth.bias, height, width)
         out = F.linear(mid, w_pt.view(w_pt.shape[0], w_pt.shape[1]), self.conv_point.bias)
         t = adapter_term(self.conv_point, mid)
         return out if t is None else out + t
