@@ -203,8 +203,8 @@ def test_world_size_2_gloo_bucket_rule_and_ddp():
 
 
 def test_pixart_and_sd35_hook_surface():
-    """The other two reference hook files exist with the reference's class / hook names and refuse to
-    build a pipeline without weights (no silent fallback)."""
+    """The other two reference hook files exist with the reference's class / hook names; SD3.5 refuses to build a
+    pipeline without a transformer module, PixArt-Sigma builds its restated transformer from ``model_config``."""
     import train_pixart_sigma
     import train_sd35
     from yat_b200.trainer import Model
@@ -213,8 +213,12 @@ def test_pixart_and_sd35_hook_surface():
         assert issubclass(cls, Model)
         for hook in ("extract_latents", "extract_embeddings", "optimize", "initialize", "validate"):
             assert callable(getattr(cls, hook))
-        with pytest.raises(NotImplementedError):
-            cls(TrainingParameters())
+    with pytest.raises(NotImplementedError):
+        train_sd35.SD35Trainer(TrainingParameters())
+    p = TrainingParameters()
+    p.model_config = "pixart_tiny"                     # random-init of a named size, like SanaModel
+    tr = train_pixart_sigma.PixartSigmaTrainer(p)
+    assert type(tr.pipe.transformer).__name__ == "PixArtTransformer2DModel" and tr.model.dtype == torch.bfloat16
     assert train_pixart_sigma.PixartSigmaTrainer.max_text_tokens == 300
 
 
@@ -337,3 +341,41 @@ def test_adapters_on_sana_token_path_cpu():
                 mod.adapter.enabled = False
         y2 = m(x, enc, t).sample
     assert not torch.allclose(y1, y0, atol=1e-3) and torch.allclose(y1, y2, rtol=1e-4, atol=1e-4)
+
+
+def test_pixart_sigma_transformer_matches_oracle_and_hf_layout():
+    """PixArt-Sigma restated: product module (op-by-op block ops on the CPU) == the independent
+    functional oracle on the same weights, square and non-square buckets; XL config has the published 610.9 M
+    parameters and the HF key layout."""
+    from oracle.pixart_model import pixart_forward, sincos_pos_embed
+    from yat_b200.pixart_transformer import PIXART_CONFIGS, PixArtTransformer2DModel, sincos_2d
+    torch.manual_seed(0)
+    m = PixArtTransformer2DModel(**PIXART_CONFIGS["pixart_tiny"])
+    enc, t = torch.randn(2, 20, 64), torch.tensor([10.0, 900.0])
+    mask = torch.zeros(2, 20, dtype=torch.long)
+    mask[0, :5] = 1
+    mask[1, :] = 1
+    with pytest.raises(ValueError):       # default block ops are the CUDA kernels: no CPU fallback
+        m(torch.randn(2, 4, 16, 16), enc, t)
+    m.set_block_ops("torch")
+    for shape in ((2, 4, 16, 16), (2, 4, 8, 24)):
+        x = torch.randn(shape)
+        with torch.no_grad():
+            y = m(x, enc, t, encoder_attention_mask=mask).sample
+            y_ref = pixart_forward(m.state_dict(), dict(vars(m.config)), x, enc, t, mask)
+        assert y.shape == (2, 8) + shape[2:] and torch.allclose(y, y_ref, atol=1e-5)
+    assert torch.allclose(sincos_2d(64, 5, 7, 8, 2.0), sincos_pos_embed(64, 5, 7, 8, 2.0), atol=1e-6)
+    pe = sincos_2d(64, 5, 7, 8, 1.0).view(5, 7, 64)
+    assert torch.equal(pe[0, :, 32:], pe[0, :1, 32:].expand(7, 32))   # second half of the channels encodes h
+    assert torch.equal(pe[:, 0, :32], pe[:1, 0, :32].expand(5, 32))   # first half encodes w
+    with torch.device("meta"):
+        big = PixArtTransformer2DModel(**PIXART_CONFIGS["pixart_sigma_xl_1024"])
+    assert sum(p.numel() for p in big.parameters()) == 610_856_096
+    keys = set(big.state_dict().keys())
+    for k in ("pos_embed.proj.weight", "adaln_single.emb.timestep_embedder.linear_1.weight", "adaln_single.linear.bias",
+              "caption_projection.linear_2.weight", "transformer_blocks.27.attn1.to_q.bias",
+              "transformer_blocks.0.attn2.to_out.0.weight", "transformer_blocks.0.ff.net.0.proj.weight",
+              "transformer_blocks.0.ff.net.2.bias", "transformer_blocks.0.scale_shift_table", "scale_shift_table",
+              "proj_out.bias"):
+        assert k in keys, k
+    assert not any("pos_embed.pos_embed" in k for k in keys)

@@ -6,9 +6,10 @@ train_pixart_sigma.py (``PixartSigmaTrainer(Model)``: ``extract_latents`` / ``ex
   pad/mask of the ragged T5 embeddings to 300 tokens              (:158-169 -> yat_pad_embeddings)
   noise + logit-normal index + alphas_cumprod lookup + add_noise   (:171-176 -> yat_noise_ddpm)
   eps target, first half of the 8 predicted channels, bf16 MSE     (:178-184 -> yat_loss_fused, EPS, lowp)
-The PixArt-Sigma XL transformer itself is a diffusers model this build does not restate (SURVEY.md
-§8(f) N4): pass any module with the ``PixArtTransformer2DModel`` forward signature as ``transformer``
-(``yat_b200.toy_models.ToyPixArtTransformer`` is the signature-compatible stand-in used by the tests).
+The PixArt-Sigma XL transformer is ``yat_b200.pixart_transformer.PixArtTransformer2DModel`` (the
+diffusers architecture restated with the HF key layout on the fused block ops; random-init of ``params.model_config``
+when no module is passed).  Any module with the same forward signature can be passed as ``transformer``
+(``yat_b200.toy_models.ToyPixArtTransformer`` is a small stand-in some tests use).
 """
 import argparse
 from types import SimpleNamespace
@@ -20,6 +21,7 @@ from yat_b200.bucket_sampler import SyntheticBucketSampler
 from yat_b200.embeddings import pad_embeddings
 from yat_b200.loss import EPS, fused_denoise_loss
 from yat_b200.noise import ddpm_noise
+from yat_b200.pixart_transformer import PIXART_CONFIGS, PixArtTransformer2DModel
 from yat_b200.schedulers import DDPMScheduler
 from yat_b200.trainer import Model
 from yat_b200.training_parameters_reader import TrainingParameters
@@ -33,9 +35,12 @@ class PixartSigmaTrainer(Model):
     def __init__(self, params: TrainingParameters, transformer=None):
         super().__init__(params)
         if transformer is None:
-            raise NotImplementedError(
-                "PixArtSigmaPipeline.from_pretrained needs diffusers + weights (out of this build's scope): "
-                "pass the transformer module (PixArtTransformer2DModel forward signature) as `transformer`")
+            # random-init PixArt-Sigma of the named size (BASELINE.json config 3; there are no weights offline).  A
+            # checkpoint of the reference's pipeline loads into it with load_state_dict (HF key layout).
+            cfg = params.model_config or "pixart_sigma_xl_1024"
+            cfg = PIXART_CONFIGS[cfg] if isinstance(cfg, str) else cfg
+            with torch.device(self.accelerator.device):
+                transformer = PixArtTransformer2DModel(**cfg)
         self.pipe = SimpleNamespace(transformer=transformer, vae=None, text_encoder=None, dtype=torch.bfloat16)
         self.scheduler = DDPMScheduler()                       # PixArt-Sigma: 1000 steps, linear betas 1e-4..0.02
         self.aspect_ratios = ASPECT_RATIO_1024_BIN
@@ -50,7 +55,7 @@ class PixartSigmaTrainer(Model):
 
     def make_sampler(self):
         cfg = getattr(self.pipe.transformer, "config", SimpleNamespace())
-        side = 1024 // self.vae_scale
+        side = getattr(cfg, "sample_size", None) or 1024 // self.vae_scale
         return SyntheticBucketSampler(self.params.batch_size, (self.latent_channels, side, side),
                                       getattr(cfg, "caption_channels", 4096), ratio=1.0,
                                       seed=1234 + self.process_index, max_len=self.max_text_tokens)
