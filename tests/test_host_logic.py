@@ -203,8 +203,8 @@ def test_world_size_2_gloo_bucket_rule_and_ddp():
 
 
 def test_pixart_and_sd35_hook_surface():
-    """The other two reference hook files exist with the reference's class / hook names; SD3.5 refuses to build a
-    pipeline without a transformer module, PixArt-Sigma builds its restated transformer from ``model_config``."""
+    """The other two reference hook files exist with the reference's class / hook names and build their restated
+    transformers (random-init of a named size, like SanaModel) from ``model_config``."""
     import train_pixart_sigma
     import train_sd35
     from yat_b200.trainer import Model
@@ -213,8 +213,10 @@ def test_pixart_and_sd35_hook_surface():
         assert issubclass(cls, Model)
         for hook in ("extract_latents", "extract_embeddings", "optimize", "initialize", "validate"):
             assert callable(getattr(cls, hook))
-    with pytest.raises(NotImplementedError):
-        train_sd35.SD35Trainer(TrainingParameters())
+    p = TrainingParameters()
+    p.model_config = "sd3_tiny"
+    tr = train_sd35.SD35Trainer(p)
+    assert type(tr.pipe.transformer).__name__ == "SD3Transformer2DModel" and tr.model.dtype == torch.bfloat16
     p = TrainingParameters()
     p.model_config = "pixart_tiny"                     # random-init of a named size, like SanaModel
     tr = train_pixart_sigma.PixartSigmaTrainer(p)
@@ -379,3 +381,36 @@ def test_pixart_sigma_transformer_matches_oracle_and_hf_layout():
               "proj_out.bias"):
         assert k in keys, k
     assert not any("pos_embed.pos_embed" in k for k in keys)
+
+
+def test_sd35_mmdit_matches_oracle_and_hf_layout():
+    """SD3.5 MMDiT restated: product module (op-by-op block ops on the CPU) == the independent
+    functional oracle on the same weights (dual-attention blocks, context_pre_only last block, cropped position
+    table, non-square bucket); the medium config has 2.24 G parameters and the HF key layout."""
+    from oracle.sd3_model import sd3_forward
+    from yat_b200.sd3_transformer import SD3_CONFIGS, SD3Transformer2DModel
+    torch.manual_seed(0)
+    m = SD3Transformer2DModel(**SD3_CONFIGS["sd3_tiny"])
+    enc, t, pooled = torch.randn(2, 20, 64), torch.tensor([10.0, 900.0]), torch.randn(2, 2048)
+    with pytest.raises(ValueError):       # default block ops are the CUDA kernels: no CPU fallback
+        m(torch.randn(2, 16, 16, 16), enc, t, pooled)
+    m.set_block_ops("torch")
+    for shape in ((2, 16, 16, 16), (2, 16, 8, 24)):
+        x = torch.randn(shape)
+        with torch.no_grad():
+            y = m(x, enc, t, pooled).sample
+            y_ref = sd3_forward(m.state_dict(), dict(vars(m.config)), x, enc, t, pooled)
+        assert y.shape == shape and torch.allclose(y, y_ref, atol=1e-5)
+    with torch.device("meta"):
+        big = SD3Transformer2DModel(**SD3_CONFIGS["sd35_medium"])
+    assert sum(p.numel() for p in big.parameters()) == 2_243_171_520
+    keys = set(big.state_dict().keys())
+    for k in ("pos_embed.pos_embed", "time_text_embed.text_embedder.linear_1.weight", "context_embedder.weight",
+              "transformer_blocks.0.norm1.linear.weight", "transformer_blocks.0.attn.add_q_proj.bias",
+              "transformer_blocks.0.attn.norm_added_k.weight", "transformer_blocks.0.attn.to_add_out.weight",
+              "transformer_blocks.12.attn2.to_out.0.weight", "transformer_blocks.5.ff_context.net.2.bias",
+              "transformer_blocks.23.norm1_context.linear.bias", "norm_out.linear.weight", "proj_out.bias"):
+        assert k in keys, k
+    assert "transformer_blocks.13.attn2.to_q.weight" not in keys and "transformer_blocks.23.attn.to_add_out.weight" not in keys
+    assert big.transformer_blocks[0].norm1.linear.weight.shape[0] == 9 * 1536
+    assert big.transformer_blocks[23].norm1_context.linear.weight.shape[0] == 2 * 1536

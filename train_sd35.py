@@ -4,11 +4,12 @@
 ``optimize`` is the flow-matching step of train_sd35.py:165-194 rebuilt on the fused ops:
   noise + logit-normal index + sigma lookup (shift 3.0) + scale_noise   (:180-185 -> yat_noise_flowmatch)
   velocity target noise - latents, bf16 MSE                              (:192-193 -> yat_loss_fused, lowp)
-A batch is ``(latents, embeddings, pooled_projections)`` (:177).  The SD3.5-medium MMDiT itself is a
-diffusers model this build does not restate: pass any module with the
-``SD3Transformer2DModel`` forward signature as ``transformer`` (``yat_b200.toy_models.ToySD3Transformer``
-is the signature-compatible stand-in used by the tests).  LoRA (rank 32 in BASELINE.json config 4) is a PEFT
-wrapper around that transformer and does not touch this path.
+A batch is ``(latents, embeddings, pooled_projections)`` (:177).  The SD3.5-medium MMDiT is
+``yat_b200.sd3_transformer.SD3Transformer2DModel`` (the diffusers architecture restated with the HF
+key layout on the fused block ops; random-init of ``params.model_config`` when no module is passed); any module with
+the same forward signature can be passed as ``transformer`` (``yat_b200.toy_models.ToySD3Transformer`` is a small
+stand-in some tests use).  LoRA (rank 32 in BASELINE.json config 4) is the adapter wrap of the base trainer
+(``yat_b200.adapters``, ``lora_rank`` / ``lora_target_modules``) around that transformer and does not touch this path.
 """
 import argparse
 from types import SimpleNamespace
@@ -20,6 +21,7 @@ from yat_b200.bucket_sampler import Batch, SyntheticBucketSampler
 from yat_b200.loss import VELOCITY, fused_denoise_loss
 from yat_b200.noise import flowmatch_noise
 from yat_b200.schedulers import FlowMatchEulerDiscreteScheduler
+from yat_b200.sd3_transformer import SD3_CONFIGS, SD3Transformer2DModel
 from yat_b200.trainer import Model
 from yat_b200.training_parameters_reader import TrainingParameters
 
@@ -43,9 +45,12 @@ class SD35Trainer(Model):
     def __init__(self, params: TrainingParameters, transformer=None):
         super().__init__(params)
         if transformer is None:
-            raise NotImplementedError(
-                "StableDiffusion3Pipeline.from_pretrained needs diffusers + weights (out of this build's scope): "
-                "pass the transformer module (SD3Transformer2DModel forward signature) as `transformer`")
+            # random-init SD3.5 MMDiT of the named size (BASELINE.json config 4; there are no weights offline).  A
+            # checkpoint of the reference's pipeline loads into it with load_state_dict (HF key layout).
+            cfg = params.model_config or "sd35_medium"
+            cfg = SD3_CONFIGS[cfg] if isinstance(cfg, str) else cfg
+            with torch.device(self.accelerator.device):
+                transformer = SD3Transformer2DModel(**cfg)
         self.pipe = SimpleNamespace(transformer=transformer, vae=None, text_encoder=None, text_encoder_2=None,
                                     text_encoder_3=None)
         shift = float(getattr(params, "flow_shift", 3.0) or 3.0)          # SD3.5 scheduler config: shift 3.0
@@ -62,7 +67,7 @@ class SD35Trainer(Model):
 
     def make_sampler(self):
         cfg = getattr(self.pipe.transformer, "config", SimpleNamespace())
-        side = 1024 // self.vae_scale
+        side = getattr(cfg, "sample_size", None) or 1024 // self.vae_scale
         return _SD35Sampler(self.params.batch_size, (self.latent_channels, side, side),
                             getattr(cfg, "caption_channels", 4096), 2048, 1234 + self.process_index)
 
