@@ -4,6 +4,7 @@ import torch
 sys.path.insert(0, ".")
 from yat_b200.block_ops import gate_residual, ln_modulate
 from yat_b200.glumb import glumb_mid
+from yat_b200.linear import colsum
 from yat_b200.linear_attention import sana_linear_attention
 from yat_b200.loss import fused_denoise_loss
 from yat_b200.noise import flowmatch_noise
@@ -43,6 +44,7 @@ for _ in range(reps):
     yg = k.clone().requires_grad_(True)
     torch.autograd.grad(gate_residual(q, yg, gt), (yg, mod), do)
     glumb_mid(u, wd, bd, 32, 32).backward(dm)
+    colsum(do.view(-1, C))
     opt.step(max_norm=1.0)
 torch.cuda.synchronize()
 print("ok")
