@@ -42,7 +42,9 @@ __device__ __forceinline__ void unpack8(const uint4& v, float f[8]) {
   f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
 }
 
-template <int VPL>  // 128-bit vectors of 8 channels per lane: E <= VPL*256
+// VPL = 128-bit vectors of 8 channels per lane: E <= VPL*256.  QUAD: every window is exactly 2x2 student tokens
+// (32x32 -> 16x16, the SANA 1024 px case): the four rows are fetched up front, 4 * VPL loads in flight per lane.
+template <int VPL, bool QUAD>
 __global__ void __launch_bounds__(kThreads) repa_pool_cos_kernel(const RepaParams p) {
   __shared__ float s_warp[kWarpsPerBlock];
   __shared__ bool s_last;
@@ -65,20 +67,42 @@ __global__ void __launch_bounds__(kThreads) repa_pool_cos_kernel(const RepaParam
     for (int j = 0; j < VPL; ++j)
 #pragma unroll
       for (int k = 0; k < 8; ++k) acc[j][k] = 0.f;
-    for (int r = r0; r < r1; ++r)
-      for (int c = c0; c < c1; ++c) {
-        const uint4* row = reinterpret_cast<const uint4*>(p.z + ((int64_t)b * p.gh * p.gw + (int64_t)r * p.gw + c) * p.E);
+    if (QUAD) {
+      uint4 q[4][VPL];
 #pragma unroll
-        for (int j = 0; j < VPL; ++j) {
-          const int v = lane + 32 * j;
-          if (v < nvec) {
+      for (int w = 0; w < 4; ++w) {
+        const uint4* row = reinterpret_cast<const uint4*>(
+            p.z + ((int64_t)b * p.gh * p.gw + (int64_t)(r0 + (w >> 1)) * p.gw + c0 + (w & 1)) * p.E);
+#pragma unroll
+        for (int j = 0; j < VPL; ++j)
+          if (lane + 32 * j < nvec) q[w][j] = ld_stream(row + lane + 32 * j);
+      }
+#pragma unroll
+      for (int w = 0; w < 4; ++w)                                  // same summation order as the generic loop
+#pragma unroll
+        for (int j = 0; j < VPL; ++j)
+          if (lane + 32 * j < nvec) {
             float f[8];
-            unpack8(ld_stream(row + v), f);
+            unpack8(q[w][j], f);
 #pragma unroll
             for (int k = 0; k < 8; ++k) acc[j][k] += f[k];
           }
+    } else {
+      for (int r = r0; r < r1; ++r)
+        for (int c = c0; c < c1; ++c) {
+          const uint4* row = reinterpret_cast<const uint4*>(p.z + ((int64_t)b * p.gh * p.gw + (int64_t)r * p.gw + c) * p.E);
+#pragma unroll
+          for (int j = 0; j < VPL; ++j) {
+            const int v = lane + 32 * j;
+            if (v < nvec) {
+              float f[8];
+              unpack8(ld_stream(row + v), f);
+#pragma unroll
+              for (int k = 0; k < 8; ++k) acc[j][k] += f[k];
+            }
+          }
         }
-      }
+    }
     float yv[VPL][8];
     float dot = 0.f, nz = 0.f, ny = 0.f;
     const int64_t yoff = ((int64_t)b * T + t) * p.E;
@@ -238,8 +262,11 @@ extern "C" int yat_repa_cos(const void* z, const void* y, int y_dtype, int B, in
   const int need = (p.total_warps + kWarpsPerBlock - 1) / kWarpsPerBlock;
   const int grid = need < kMaxBlocks ? need : kMaxBlocks;
   cudaStream_t st = (cudaStream_t)stream;
-  if (E <= 1024) repa_pool_cos_kernel<4><<<grid, kThreads, 0, st>>>(p);
-  else           repa_pool_cos_kernel<8><<<grid, kThreads, 0, st>>>(p);
+  const bool quad = gh == 2 * th && gw == 2 * tw;
+  if (E <= 768 && quad)  repa_pool_cos_kernel<3, true><<<grid, kThreads, 0, st>>>(p);
+  else if (E <= 768)     repa_pool_cos_kernel<3, false><<<grid, kThreads, 0, st>>>(p);
+  else if (E <= 1024)    repa_pool_cos_kernel<4, false><<<grid, kThreads, 0, st>>>(p);
+  else                   repa_pool_cos_kernel<8, false><<<grid, kThreads, 0, st>>>(p);
   int rc = check_launch("repa_pool_cos");
   if (rc != YAT_OK) return rc;
   if (dz && !p.direct) {
