@@ -209,3 +209,28 @@ def test_trimmed_text_padding_matches_fixed_512(cuda):
         y_trim = m(x, trim, t, encoder_attention_mask=mask_trim).sample
     rel = ((y_full.float() - y_trim.float()).norm() / y_full.float().norm()).item()
     assert rel < 4e-3, rel
+
+
+def test_lokr_dense_and_factored_forms_agree(cuda):
+    """LoKrAdapter on many tokens expands kron(W1, W2) and runs one GEMM; on few tokens it keeps the factored
+    W1 (X W2^T) form.  Same product: outputs and parameter gradients agree to bf16 GEMM noise."""
+    from yat_b200.adapters import LoKrAdapter
+    torch.manual_seed(0)
+    ad = LoKrAdapter(2240, 2240, 16, 16, torch.bfloat16, cuda)
+    with torch.no_grad():
+        for p in ad.parameters():
+            p.normal_(std=0.1)
+    x = torch.randn(2, 1024, 2240, device=cuda, dtype=torch.bfloat16)
+    dy = torch.randn(2, 1024, 2240, device=cuda, dtype=torch.bfloat16)
+    outs = []
+    for dense_tokens in (1, 1 << 30):
+        ad.dense_tokens = dense_tokens
+        ad.zero_grad()
+        xx = x.clone().requires_grad_(True)
+        y = ad(xx)
+        y.backward(dy)
+        outs.append((y.detach().float(), xx.grad.float(), [p.grad.float().clone() for p in ad.parameters()]))
+    rel = lambda a, b: ((a - b).norm() / b.norm()).item()
+    assert rel(outs[0][0], outs[1][0]) < 2e-2 and rel(outs[0][1], outs[1][1]) < 2e-2
+    for ga, gb in zip(outs[0][2], outs[1][2]):
+        assert rel(ga, gb) < 2e-2
