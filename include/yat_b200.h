@@ -187,6 +187,18 @@ int yat_glumb_mid_bwd(const void* u, const void* c, const void* w_dw, const void
 int yat_pad_embeddings(const void* packed, const int32_t* offsets, int B, int Lmax, int E,
                        void* padded, int64_t* mask, void* stream);
 
+/* ---- head padding for the cross-attention SDPA --------------------------------------------------
+ * The -10000 key-padding bias of the text cross-attention (utils/patched_sana_transformer.py:275-277 ->
+ * AttnProcessor2_0) is folded into one extra head column so the library SDPA runs without a mask tensor:
+ *   head_pad    x [rows, H*d] bf16 -> out [rows, H, da]: out[..,:d] = x, out[..,d] = tail_row[row] (if given) else
+ *               tail_const, rest 0;    head_unpad  xa [B, T, H, >=d] with element strides -> out [B*T, H*d].
+ * d, da and the strides are multiples of 8 elements.  Each is the other's backward.
+ */
+int yat_head_pad(const void* x, const void* tail_row, float tail_const, int64_t rows, int H, int d, int da,
+                 void* out, void* stream);
+int yat_head_unpad(const void* xa, int64_t stride_b, int64_t stride_t, int64_t stride_h, int B, int T, int H, int d,
+                   void* out, void* stream);
+
 /* ---- optimiser step: global-norm clip + AdamW (common/trainer.py:347-348) ---------------------
  * The parameters of one group are described by device tables built once by the caller:
  *   tensor_tab [T][4] int64 = {param ptr, exp_avg ptr, exp_avg_sq ptr, numel}

@@ -234,3 +234,42 @@ def test_lokr_dense_and_factored_forms_agree(cuda):
     assert rel(outs[0][0], outs[1][0]) < 2e-2 and rel(outs[0][1], outs[1][1]) < 2e-2
     for ga, gb in zip(outs[0][2], outs[1][2]):
         assert rel(ga, gb) < 2e-2
+
+
+@pytest.mark.parametrize("B,N,L,H,d", [(2, 256, 64, 2, 64), (3, 100, 192, 20, 112), (1, 33, 8, 4, 72)])
+def test_folded_key_mask_sdpa_matches_additive_mask(cuda, B, N, L, H, d):
+    """yat_head_pad / yat_head_unpad (bit-exact copies, each the other's backward) and the cross-attention with the
+    -10000 key-padding bias folded into an extra head column: same output and gradients as SDPA with the additive
+    mask tensor (masked keys weigh exactly 0 either way), <= 2e-2 relative by spec, asserted tighter."""
+    import torch.nn.functional as F
+    from yat_b200.attention import _HeadPad, _HeadUnpad, _sdpa_key_bias_folded
+    g = torch.Generator().manual_seed(B * 7 + d)
+    q, k, v = [torch.randn((B, T, H * d), generator=g).to(torch.bfloat16).to(cuda) for T in (N, L, L)]
+    do = torch.randn((B, N, H * d), generator=g).to(torch.bfloat16).to(cuda)
+    lens = torch.randint(1, L + 1, (B,), generator=g)
+    mask = (torch.arange(L)[None] < lens[:, None]).to(cuda)
+    bias = ((1 - mask.to(torch.bfloat16)) * -10000.0).view(B, 1, 1, L)
+    da = (d + 1 + 15) // 16 * 16
+    tail = torch.randn((B * L,), generator=g).to(torch.bfloat16).to(cuda)
+    ka = _HeadPad.apply(k, H, d, da, 0.0, tail)
+    assert ka.shape == (B, L, H, da) and torch.equal(ka[..., :d].reshape(B, L, H * d), k)
+    assert torch.equal(ka[..., d], tail.view(B, L, 1).expand(B, L, H)) and not ka[..., d + 1:].any()
+    qa = _HeadPad.apply(q, H, d, da, 1.0, None)
+    assert torch.equal(qa[..., d], torch.ones_like(qa[..., d])) and torch.equal(_HeadUnpad.apply(qa, d), q)
+    assert torch.equal(_HeadUnpad.apply(qa.transpose(1, 2).contiguous().transpose(1, 2), d), q)      # other strides
+
+    def heads(t):
+        return t.view(B, -1, H, d).transpose(1, 2)
+
+    a = [t.clone().requires_grad_(True) for t in (q, k, v)]
+    out = _sdpa_key_bias_folded(*a, bias, H, d)
+    out.backward(do)
+    r = [t.clone().requires_grad_(True) for t in (q, k, v)]
+    ref = F.scaled_dot_product_attention(heads(r[0]), heads(r[1]), heads(r[2]), attn_mask=bias)
+    ref = ref.transpose(1, 2).reshape(B, N, H * d)
+    ref.backward(do)
+    rel = lambda x, y: ((x.float() - y.float()).norm() / y.float().norm().clamp_min(1e-30)).item()
+    assert rel(out, ref) < 1e-2 and rel(a[0].grad, r[0].grad) < 1e-2
+    m3 = mask.view(B, L, 1)
+    assert rel(a[1].grad * m3, r[1].grad * m3) < 1e-2 and rel(a[2].grad * m3, r[2].grad * m3) < 1e-2
+    assert not (a[1].grad * ~m3).any() and not (a[2].grad * ~m3).float().abs().max() > 1e-30       # padded keys: zero grads
