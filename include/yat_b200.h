@@ -124,6 +124,13 @@ int yat_linattn_fwd(const void* q, const void* k, const void* v, int B, int N, i
                     void* o, void* stream);
 int yat_linattn_bwd(const void* q, const void* k, const void* v, const void* dout,
                     int B, int N, int H, int D, void* dq, void* dk, void* dv, void* stream);
+/* Same kernels on column slices of wider row-major buffers: q, k, v are [B, N, H*D] views with a row pitch of `ld`
+ * elements (the three thirds of ONE fused q|k|v projection output [B, N, 3*H*D]), dq, dk, dv likewise with `ld_grad`
+ * (so the backward writes straight into the gradient of that fused projection); o and dout stay dense. */
+int yat_linattn_fwd_ld(const void* q, const void* k, const void* v, int64_t ld, int B, int N, int H, int D,
+                       void* o, void* stream);
+int yat_linattn_bwd_ld(const void* q, const void* k, const void* v, int64_t ld, const void* dout, int B, int N, int H,
+                       int D, void* dq, void* dk, void* dv, int64_t ld_grad, void* stream);
 /* CUDA-core fp32 restatement of the same math; exists so the GPU tests can cross-check the
  * tensor-core kernels at full size, where the CPU oracle is too slow.  Not a product path. */
 int yat_linattn_fwd_simt(const void* q, const void* k, const void* v, int B, int N, int H, int D,

@@ -16,15 +16,26 @@ from torch import nn
 
 from . import _lib
 from .linear import Linear
-from .linear_attention import sana_linear_attention
+from .linear_attention import sana_linear_attention, sana_linear_attention_qkv
 
 
 class SanaLinearAttnProcessorB200:
     """Drop-in for diffusers ``SanaLinearAttnProcessor2_0``: projections stay ``attn.to_q/k/v``
     (possibly PEFT-wrapped), the ReLU linear-attention core runs as one tcgen05 kernel."""
 
-    def __init__(self, impl: str = "sm100"):
+    def __init__(self, impl: str = "sm100", fuse_qkv: bool = True):
         self.impl = impl
+        self.fuse_qkv = fuse_qkv
+
+    def _can_fuse_qkv(self, attn, hidden_states, encoder_hidden_states):
+        if not self.fuse_qkv or self.impl != "sm100" or encoder_hidden_states is not hidden_states:
+            return False
+        mods = (attn.to_q, attn.to_k, attn.to_v)
+        if any(hasattr(m, "adapter") or m._forward_hooks or m._forward_pre_hooks for m in mods):
+            return False                                   # LoRA / LoKr wraps and REPA-style hooks see the modules
+        if len({m.bias is None for m in mods}) != 1 or len({m.weight.shape for m in mods}) != 1:
+            return False
+        return hidden_states.is_cuda and hidden_states.dtype == torch.bfloat16 and attn.to_q.weight.dtype == torch.bfloat16
 
     def __call__(self, attn, hidden_states, encoder_hidden_states=None, attention_mask=None):
         original_dtype = hidden_states.dtype
@@ -33,6 +44,15 @@ class SanaLinearAttnProcessorB200:
         if attn.norm_q is not None or attn.norm_k is not None:
             raise ValueError("qk_norm is not supported by the B200 linear-attention kernel "
                              "(SANA-1.6B uses qk_norm=None, utils/patched_sana_transformer.py:109)")
+        if self._can_fuse_qkv(attn, hidden_states, encoder_hidden_states):
+            # ONE projection GEMM on the concatenated weights (parameters stay separate, HF layout): the kernels read
+            # q | k | v as column thirds of its output and write dq | dk | dv into its gradient, so the input gradient
+            # is a single GEMM over K = 3*C instead of three GEMMs and two accumulation passes
+            w = torch.cat([attn.to_q.weight, attn.to_k.weight, attn.to_v.weight], dim=0)
+            b = None if attn.to_q.bias is None else torch.cat([attn.to_q.bias, attn.to_k.bias, attn.to_v.bias], dim=0)
+            out = sana_linear_attention_qkv(F.linear(hidden_states, w, b), attn.heads)
+            out = attn.to_out[0](out.to(original_dtype))
+            return attn.to_out[1](out)
         query = attn.to_q(hidden_states)
         key = attn.to_k(encoder_hidden_states)
         value = attn.to_v(encoder_hidden_states)

@@ -628,7 +628,14 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
 
 extern "C" int yat_linattn_bwd(const void* q, const void* k, const void* v, const void* dout, int B, int N, int H,
                                int D, void* dq, void* dk, void* dv, void* stream) {
+  return yat_linattn_bwd_ld(q, k, v, (int64_t)H * D, dout, B, N, H, D, dq, dk, dv, (int64_t)H * D, stream);
+}
+
+extern "C" int yat_linattn_bwd_ld(const void* q, const void* k, const void* v, int64_t ld, const void* dout, int B,
+                                  int N, int H, int D, void* dq, void* dk, void* dv, int64_t ld_grad, void* stream) {
   using namespace yat;
+  YAT_REQUIRE(ld >= (int64_t)H * D && ld % 8 == 0 && ld_grad >= (int64_t)H * D && ld_grad % 8 == 0, YAT_ERR_BAD_ARG,
+              "yat_linattn_bwd: row pitches %lld / %lld must be >= H*D and multiples of 8", (long long)ld, (long long)ld_grad);
   YAT_REQUIRE(q && k && v && dout && dq && dk && dv, YAT_ERR_BAD_ARG, "yat_linattn_bwd: null pointer argument");
   YAT_REQUIRE(B > 0 && N > 0 && H > 0, YAT_ERR_BAD_ARG, "yat_linattn_bwd: non-positive dimension");
   YAT_REQUIRE(D == kD, YAT_ERR_UNSUPPORTED, "yat_linattn_bwd: head_dim %d not supported (SANA uses 32)", D);
@@ -640,7 +647,8 @@ extern "C" int yat_linattn_bwd(const void* q, const void* k, const void* v, cons
   const void* ptrs[7] = {q, k, v, dout, dq, dk, dv};
   CUtensorMap* tms[7] = {&maps.q, &maps.k, &maps.v, &maps.d_o, &maps.dq, &maps.dk, &maps.dv};
   for (int i = 0; i < 7; ++i) {
-    const int rc = make_tmap_3d_bf16(tms[i], ptrs[i], C, N, B, 64, kTile);
+    const uint64_t pitch = i < 3 ? (uint64_t)ld : (i == 3 ? C : (uint64_t)ld_grad);   // q k v | dO | dq dk dv
+    const int rc = make_tmap_3d_bf16(tms[i], ptrs[i], C, N, B, 64, kTile, pitch);
     if (rc != YAT_OK) return rc;
   }
   static bool attr_set = false;

@@ -374,11 +374,12 @@ static PFN_encodeTiled get_encode_fn() {
 }
 
 int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t N, uint64_t B, uint32_t box_c,
-                      uint32_t box_n) {
+                      uint32_t box_n, uint64_t ld) {
   PFN_encodeTiled enc = get_encode_fn();
   YAT_REQUIRE(enc != nullptr, YAT_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  if (ld == 0) ld = C;
   const cuuint64_t dims[3] = {C, N, B};
-  const cuuint64_t strides[2] = {C * 2, N * C * 2};
+  const cuuint64_t strides[2] = {ld * 2, N * ld * 2};
   const cuuint32_t box[3] = {box_c, box_n, 1};
   const cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
@@ -420,8 +421,15 @@ int make_tmap_4d_bf16_plain(CUtensorMap* out, const void* base, const uint64_t d
 
 extern "C" int yat_linattn_fwd(const void* q, const void* k, const void* v, int B, int N, int H, int D, void* o,
                                void* stream) {
+  return yat_linattn_fwd_ld(q, k, v, (int64_t)H * D, B, N, H, D, o, stream);
+}
+
+extern "C" int yat_linattn_fwd_ld(const void* q, const void* k, const void* v, int64_t ld, int B, int N, int H, int D,
+                                  void* o, void* stream) {
   using namespace yat;
   YAT_REQUIRE(q && k && v && o, YAT_ERR_BAD_ARG, "yat_linattn_fwd: null pointer argument");
+  YAT_REQUIRE(ld >= (int64_t)H * D && ld % 8 == 0, YAT_ERR_BAD_ARG, "yat_linattn_fwd: row pitch %lld must be >= H*D and a multiple of 8",
+              (long long)ld);
   YAT_REQUIRE(B > 0 && N > 0 && H > 0, YAT_ERR_BAD_ARG, "yat_linattn_fwd: non-positive dimension");
   YAT_REQUIRE(D == kD, YAT_ERR_UNSUPPORTED, "yat_linattn_fwd: head_dim %d not supported (SANA uses 32)", D);
   YAT_REQUIRE((((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o) & 15u) == 0, YAT_ERR_BAD_ARG,
@@ -429,9 +437,9 @@ extern "C" int yat_linattn_fwd(const void* q, const void* k, const void* v, int 
   CUtensorMap tq, tk, tv, to;
   const uint64_t C = (uint64_t)H * D;
   int rc;
-  if ((rc = make_tmap_3d_bf16(&tq, q, C, N, B, 64, kTile)) != YAT_OK) return rc;
-  if ((rc = make_tmap_3d_bf16(&tk, k, C, N, B, 64, kTile)) != YAT_OK) return rc;
-  if ((rc = make_tmap_3d_bf16(&tv, v, C, N, B, 64, kTile)) != YAT_OK) return rc;
+  if ((rc = make_tmap_3d_bf16(&tq, q, C, N, B, 64, kTile, (uint64_t)ld)) != YAT_OK) return rc;
+  if ((rc = make_tmap_3d_bf16(&tk, k, C, N, B, 64, kTile, (uint64_t)ld)) != YAT_OK) return rc;
+  if ((rc = make_tmap_3d_bf16(&tv, v, C, N, B, 64, kTile, (uint64_t)ld)) != YAT_OK) return rc;
   if ((rc = make_tmap_3d_bf16(&to, o, C, N, B, 64, kTile)) != YAT_OK) return rc;
   static bool attr_set = false;
   if (!attr_set) {

@@ -142,7 +142,7 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn_ma
 
 // host: encode a 3-D bf16 tensor map {C, N, B} with a {box_c, box_n, 1} box, 128B swizzle
 int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t N, uint64_t B, uint32_t box_c,
-                      uint32_t box_n);
+                      uint32_t box_n, uint64_t ld = 0 /* row pitch in elements, 0 = C (dense rows) */);
 
 // host: plain 4-D bf16 tensor map, zero fill out of bounds (GLUMB kernels)
 int make_tmap_4d_bf16_plain(CUtensorMap* out, const void* base, const uint64_t dims[4], const uint32_t box[4]);

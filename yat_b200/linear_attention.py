@@ -60,3 +60,46 @@ def sana_linear_attention(q, k, v, heads, impl="sm100"):
     if impl not in ("sm100", "simt"):
         raise ValueError(f"unknown impl {impl!r}")
     return _SanaLinearAttention.apply(q, k, v, heads, impl)
+
+
+class _SanaLinearAttentionQKV(torch.autograd.Function):
+    """Same kernels on the three column thirds of ONE fused projection output qkv [B, N, 3*C] (row pitch 3*C): no
+    q / k / v copies, and the backward writes dq | dk | dv straight into the gradient of that projection, so its
+    input gradient is a single GEMM over K = 3*C instead of three GEMMs and two accumulation passes."""
+
+    @staticmethod
+    def forward(ctx, qkv, heads):
+        if not qkv.is_cuda or qkv.dtype != torch.bfloat16 or qkv.dim() != 3 or qkv.shape[-1] % (3 * heads):
+            raise ValueError("fused linear attention expects a CUDA bf16 [B, N, 3*heads*D] tensor (no CPU fallback)")
+        qkv = qkv.contiguous()
+        B, N, C3 = qkv.shape
+        C = C3 // 3
+        o = torch.empty((B, N, C), dtype=qkv.dtype, device=qkv.device)
+        base = qkv.data_ptr()
+        with _lib.timed("linattn_fwd_sm100"):
+            rc = _lib.lib().yat_linattn_fwd_ld(base, base + 2 * C, base + 4 * C, C3, B, N, heads, C // heads,
+                                               _lib.ptr(o), _lib.current_stream())
+        _lib.check(rc, "yat_linattn_fwd_ld")
+        ctx.save_for_backward(qkv)
+        ctx.heads = heads
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        (qkv,) = ctx.saved_tensors
+        B, N, C3 = qkv.shape
+        C = C3 // 3
+        do = do.contiguous()
+        dqkv = torch.empty_like(qkv)
+        base, gbase = qkv.data_ptr(), dqkv.data_ptr()
+        with _lib.timed("linattn_bwd_sm100"):
+            rc = _lib.lib().yat_linattn_bwd_ld(base, base + 2 * C, base + 4 * C, C3, _lib.ptr(do), B, N, ctx.heads,
+                                               C // ctx.heads, gbase, gbase + 2 * C, gbase + 4 * C, C3,
+                                               _lib.current_stream())
+        _lib.check(rc, "yat_linattn_bwd_ld")
+        return dqkv, None
+
+
+def sana_linear_attention_qkv(qkv, heads):
+    """qkv [B, N, 3*heads*32] bf16 = [q | k | v] along the last axis (one fused projection) -> [B, N, heads*32]."""
+    return _SanaLinearAttentionQKV.apply(qkv, int(heads))
