@@ -253,7 +253,7 @@ def _algo_bytes(name, B, chw, N, C, P=0):
         "linattn_fwd_sm100": 8 * B * N * C,      # q,k,v in + o out, bf16
         "linattn_bwd_sm100": 14 * B * N * C,     # q,k,v,do in + dq,dk,dv out, bf16 (o is recomputed, not read)
         "ln_modulate_fwd": 4 * B * N * C,        # x in, y out
-        "ln_modulate_bwd": 6 * B * N * C,        # x, dy in, dx out (the column pass re-reads x, dy: counted as waste)
+        "ln_modulate_bwd": 6 * B * N * C,        # x, dy in, dx out (one pass: dx and the column sums from the same registers)
         "gate_residual_fwd": 6 * B * N * C,      # res, y in, out
         "gate_residual_bwd": 6 * B * N * C,      # dout, y in, dy out
         "glumb_mid_fwd": 25 * B * N * C,         # u in (10 C) + mid out (5 C) + c out (10 C, kept for the backward)

@@ -14,6 +14,6 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --csv --lo
     python bench.py --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_bench.log 2>&1
 echo "launch list rc=$?"; wc -l gpurun_out/launches.csv
 timeout 300 python scripts/prof_kernels.py 1 > gpurun_out/plain_prof.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:"linattn_.*sm100|noise_bf16|loss_fused|repa_|glumb_fwd|glumb_bwd|adamw|grad_sumsq|ln_modulate|gate_residual|column_pass|colsum_kernel" -c 17 \
-    -o gpurun_out/prof_r01e -f python scripts/prof_kernels.py 1 > gpurun_out/ncu_prof.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"linattn_.*sm100|noise_bf16|loss_fused|repa_|glumb_fwd|glumb_bwd|adamw|grad_sumsq|ln_modulate|gate_residual|column_pass|colsum_kernel|head_pad|head_unpad" -c 19 \
+    -o gpurun_out/prof_r01f -f python scripts/prof_kernels.py 1 > gpurun_out/ncu_prof.log 2>&1
 echo "full capture rc=$?"; ls -la gpurun_out/*.ncu-rep; tail -n 5 gpurun_out/ncu_prof.log

@@ -3,6 +3,7 @@ import sys
 import torch
 sys.path.insert(0, ".")
 from yat_b200.block_ops import gate_residual, ln_modulate
+from yat_b200.attention import _HeadPad, _HeadUnpad
 from yat_b200.glumb import glumb_mid
 from yat_b200.linear import colsum
 from yat_b200.linear_attention import sana_linear_attention
@@ -45,6 +46,7 @@ for _ in range(reps):
     torch.autograd.grad(gate_residual(q, yg, gt), (yg, mod), do)
     glumb_mid(u, wd, bd, 32, 32).backward(dm)
     colsum(do.view(-1, C))
+    _HeadUnpad.apply(_HeadPad.apply(q, 20, 112, 128, 1.0, None), 112)
     opt.step(max_norm=1.0)
 torch.cuda.synchronize()
 print("ok")
