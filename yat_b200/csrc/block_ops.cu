@@ -11,6 +11,8 @@
 // [16,1024,2240] forward and ~8 backward, most of them on the slow non-vectorised broadcast path;
 // here each direction is one pass (plus a column-sum pass for the per-sample gradients).
 // All arithmetic in fp32, one rounding to bf16 on the way out.  HBM-bound.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace yat {
@@ -278,6 +280,135 @@ __global__ void __launch_bounds__(kLnBwdThreads, MAXH <= 5 ? 3 : 1) ln_modulate_
     const int64_t o = ((int64_t)split * gridDim.y + b) * C + col;
     part0[o] = t0;
     part1[o] = t1;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// ln_modulate backward, column-ownership form (the one launched): a thread owns ONE 8-column vector for the whole CTA
+// = (row split, sample), so (1 + scale) is unpacked once into registers and the dscale / dshift column sums are plain
+// register accumulators written out at the end (no shared-memory image, no reduction over warps).  Rows go four at a
+// time: 8 x 128-bit loads in flight per thread, the 8 partial row sums (4 rows x {sum g, sum g*xhat}) are reduced in
+// the warp with a halving exchange (9 shuffles), across the warps through shared memory (every thread adds the warps
+// in the same order -> identical statistics everywhere, deterministic), ONE __syncthreads per 4 rows (the slot
+// alternates).  x and dy are read once; fp32 pairs (FFMA2).
+// ------------------------------------------------------------------------------------------------
+constexpr int kLnRows = 4;
+constexpr int kLnMaxWarps = 16;   // C <= 4096 -> nvec <= 512 threads
+
+template <int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB) ln_modulate_bwd_cols_kernel(
+    const uint4* __restrict__ x, const uint4* __restrict__ dy, const uint4* __restrict__ scale,
+    int64_t mod_stride_vec, const float* __restrict__ mean_in, const float* __restrict__ rstd_in, int N, int nvec,
+    int rows_per_split, float inv_c, uint4* __restrict__ dx, float* __restrict__ part0, float* __restrict__ part1) {
+  __shared__ float red[2][kLnMaxWarps][2 * kLnRows];
+  const int c = threadIdx.x, lane = c & 31, warp = c >> 5, nwarps = (blockDim.x + 31) >> 5;
+  const int split = blockIdx.x, b = blockIdx.y;
+  const bool live = c < nvec;
+  const int r0 = split * rows_per_split;
+  const int r1 = min(N, r0 + rows_per_split);
+  const f2 one = bc2(1.0f);
+  f2 a1[4], dsc[4], dsh[4];
+  {
+    const uint4 av = live ? ld_cached(scale + (int64_t)b * mod_stride_vec + c) : make_uint4(0u, 0u, 0u, 0u);
+    const uint32_t aw[4] = {av.x, av.y, av.z, av.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      a1[j] = add2(unpack2(aw[j]), one);
+      dsc[j] = bc2(0.f);
+      dsh[j] = bc2(0.f);
+    }
+  }
+  int slot = 0;
+  for (int rb = r0; rb < r1; rb += kLnRows, slot ^= 1) {
+    uint4 xv[kLnRows], gv[kLnRows];
+    float rs[kLnRows], nmr[kLnRows];
+#pragma unroll
+    for (int k = 0; k < kLnRows; ++k) {
+      const bool ok = live && rb + k < r1;
+      const int64_t row = (int64_t)b * N + min(rb + k, r1 - 1);
+      xv[k] = ok ? ld_stream(x + row * nvec + c) : make_uint4(0u, 0u, 0u, 0u);
+      gv[k] = ok ? ld_stream(dy + row * nvec + c) : make_uint4(0u, 0u, 0u, 0u);
+      rs[k] = rstd_in[row];
+      nmr[k] = -mean_in[row] * rs[k];
+    }
+    float v[2 * kLnRows];                                   // [k] = sum g, [kLnRows + k] = sum g * xhat
+#pragma unroll
+    for (int k = 0; k < kLnRows; ++k) {
+      const uint32_t xw[4] = {xv[k].x, xv[k].y, xv[k].z, xv[k].w}, gw[4] = {gv[k].x, gv[k].y, gv[k].z, gv[k].w};
+      const f2 rsk = bc2(rs[k]), nmk = bc2(nmr[k]);
+      f2 s1 = bc2(0.f), s2 = bc2(0.f);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const f2 gg = mul2(unpack2(gw[j]), a1[j]);
+        s1 = add2(s1, gg);
+        s2 = fma2(gg, fma2(unpack2(xw[j]), rsk, nmk), s2);
+      }
+      float lo, hi;
+      un2(s1, lo, hi);
+      v[k] = lo + hi;
+      un2(s2, lo, hi);
+      v[kLnRows + k] = lo + hi;
+    }
+    // warp reduction of 8 values with a halving exchange: 4 + 2 + 1 shuffles leave value (lane >> 2) & 7 ... then 2 more
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {                           // xor 16: keep 4 of 8
+      const bool up = lane & 16;
+      const float send = up ? v[i] : v[i + 4], keep = up ? v[i + 4] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {                           // xor 8: keep 2 of 4
+      const bool up = lane & 8;
+      const float send = up ? v[i] : v[i + 2], keep = up ? v[i + 2] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+    {
+      const bool up = lane & 4;                             // xor 4: keep 1 of 2
+      const float send = up ? v[0] : v[1], keep = up ? v[1] : v[0];
+      v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 2);
+    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+    // lane L now holds the warp total of value index ((L>>4)&1)*4 + ((L>>3)&1)*2 + ((L>>2)&1)
+    if ((lane & 3) == 0) red[slot][warp][((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1)] = v[0];
+    __syncthreads();
+    float tot[2 * kLnRows];
+#pragma unroll
+    for (int i = 0; i < 2 * kLnRows; ++i) tot[i] = 0.f;
+    for (int w = 0; w < nwarps; ++w) {
+      const float4 p0 = *reinterpret_cast<const float4*>(&red[slot][w][0]);
+      const float4 p1 = *reinterpret_cast<const float4*>(&red[slot][w][4]);
+      tot[0] += p0.x; tot[1] += p0.y; tot[2] += p0.z; tot[3] += p0.w;
+      tot[4] += p1.x; tot[5] += p1.y; tot[6] += p1.z; tot[7] += p1.w;
+    }
+#pragma unroll
+    for (int k = 0; k < kLnRows; ++k) {
+      if (!(live && rb + k < r1)) continue;
+      const int64_t row = (int64_t)b * N + rb + k;
+      const uint32_t xw[4] = {xv[k].x, xv[k].y, xv[k].z, xv[k].w}, gw[4] = {gv[k].x, gv[k].y, gv[k].z, gv[k].w};
+      const f2 rsk = bc2(rs[k]), nmk = bc2(nmr[k]);
+      const f2 nc1r = bc2(-tot[k] * inv_c * rs[k]), nc2r = bc2(-tot[kLnRows + k] * inv_c * rs[k]);
+      uint32_t ow[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const f2 g = unpack2(gw[j]);
+        const f2 xh = fma2(unpack2(xw[j]), rsk, nmk);
+        ow[j] = pack2(fma2(xh, nc2r, fma2(mul2(g, a1[j]), rsk, nc1r)));
+        dsc[j] = fma2(g, xh, dsc[j]);
+        dsh[j] = add2(dsh[j], g);
+      }
+      st_stream(dx + row * nvec + c, make_uint4(ow[0], ow[1], ow[2], ow[3]));
+    }
+  }
+  if (live) {
+    const int64_t o = ((int64_t)split * gridDim.y + b) * (nvec * 8) + c * 8;
+    float4 q0, q1;
+    un2(dsc[0], q0.x, q0.y); un2(dsc[1], q0.z, q0.w); un2(dsc[2], q1.x, q1.y); un2(dsc[3], q1.z, q1.w);
+    *reinterpret_cast<float4*>(part0 + o) = q0;
+    *reinterpret_cast<float4*>(part0 + o + 4) = q1;
+    un2(dsh[0], q0.x, q0.y); un2(dsh[1], q0.z, q0.w); un2(dsh[2], q1.x, q1.y); un2(dsh[3], q1.z, q1.w);
+    *reinterpret_cast<float4*>(part1 + o) = q0;
+    *reinterpret_cast<float4*>(part1 + o + 4) = q1;
   }
 }
 
@@ -571,6 +702,32 @@ extern "C" int yat_ln_modulate_bwd(const void* x, const void* dy, const void* sc
         (const uint4*)x, (const uint4*)dy, (const uint4*)scale, mod_batch_stride / 8, mean, rstd, N, nvec,           \
         rows_per_split, 1.0f / C, (uint4*)dx, part0, part1);                                                         \
   } while (0)
+  static const bool use_pairs = getenv("YAT_LN_BWD_PAIRS") != nullptr;   // development switch: the warp-pair kernel
+  if (!use_pairs) {
+    const int threads = (nvec + 31) / 32 * 32;
+    const int per_sm = threads <= 320 ? 2 : 1;                     // resident CTAs (launch bounds of the two instantiations)
+    int sp = (kNumSMs * per_sm) / B;
+    const int cap = (N + kLnRows - 1) / kLnRows;
+    sp = sp > cap ? cap : sp;
+    sp = sp > splits ? splits : sp;                                // the workspace is sized for `splits`
+    sp = sp < 1 ? 1 : sp;
+    const int rps = (N + sp - 1) / sp;
+    float* p1 = part0 + (int64_t)sp * B * C;
+    if (threads <= 320)
+      ln_modulate_bwd_cols_kernel<320, 2><<<dim3(sp, B), threads, 0, st>>>(
+          (const uint4*)x, (const uint4*)dy, (const uint4*)scale, mod_batch_stride / 8, mean, rstd, N, nvec, rps, 1.0f / C,
+          (uint4*)dx, part0, p1);
+    else
+      ln_modulate_bwd_cols_kernel<512, 1><<<dim3(sp, B), threads, 0, st>>>(
+          (const uint4*)x, (const uint4*)dy, (const uint4*)scale, mod_batch_stride / 8, mean, rstd, N, nvec, rps, 1.0f / C,
+          (uint4*)dx, part0, p1);
+    rc = check_launch("ln_modulate_bwd_cols");
+    if (rc != YAT_OK) return rc;
+    const int64_t bc2_ = (int64_t)B * C;
+    column_finish_kernel<<<(unsigned)((bc2_ + 255) / 256), 256, 0, st>>>(part0, p1, sp, bc2_, (__nv_bfloat16*)dscale,
+                                                                        (__nv_bfloat16*)dshift);
+    return check_launch("ln_modulate_bwd_finish");
+  }
   const int per_half = ((nvec + 31) / 32 + 1) / 2;                 // 32-vector blocks per warp of a pair
   if (per_half <= 1)      YAT_LN_BWD_LAUNCH(1);
   else if (per_half <= 2) YAT_LN_BWD_LAUNCH(2);
