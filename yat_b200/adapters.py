@@ -57,6 +57,26 @@ class LoRAAdapter(_Adapter):
         return self.scale * (self.lora_B @ self.lora_A)
 
 
+class _ScaledKron(torch.autograd.Function):
+    """scale * w1[a, b] * w2[c, d] as [a, c, b, d]; the backward contracts the dense gradient with the other factor as
+    two einsums (permute + matmul) - autograd's own path through the broadcast product reduces 5-25 M elements with
+    strided torch reductions per adapted module, which was ~10 % of the K5 step."""
+
+    @staticmethod
+    def forward(ctx, w1, w2, scale):
+        ctx.save_for_backward(w1, w2)
+        ctx.scale = scale
+        return scale * (w1[:, None, :, None] * w2[None, :, None, :])
+
+    @staticmethod
+    def backward(ctx, g):
+        w1, w2 = ctx.saved_tensors
+        g = g * ctx.scale if ctx.scale != 1.0 else g
+        dw1 = torch.einsum("acbd,cd->ab", g, w2) if ctx.needs_input_grad[0] else None
+        dw2 = torch.einsum("acbd,ab->cd", g, w1) if ctx.needs_input_grad[1] else None
+        return dw1, dw2, None
+
+
 class LoKrAdapter(_Adapter):
     def __init__(self, out_features, in_features, rank, alpha, dtype, device):
         super().__init__()
@@ -95,7 +115,7 @@ class LoKrAdapter(_Adapter):
     def delta_weight(self):
         ol, ok, im, in_ = self.shape
         # kron(w1, w2)[a * ok + c, b * in_ + d] = w1[a, b] * w2[c, d]
-        return self.scale * (self.lokr_w1[:, None, :, None] * self._w2()[None, :, None, :]).reshape(ol * ok, im * in_)
+        return _ScaledKron.apply(self.lokr_w1, self._w2(), self.scale).reshape(ol * ok, im * in_)
 
 
 ALGOS = {"lora": LoRAAdapter, "lokr": LoKrAdapter}
