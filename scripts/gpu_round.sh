@@ -15,5 +15,5 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --csv --lo
 echo "launch list rc=$?"; wc -l gpurun_out/launches.csv
 timeout 300 python scripts/prof_kernels.py 1 > gpurun_out/plain_prof.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:"linattn_.*sm100|noise_bf16|loss_fused|repa_|glumb_fwd|glumb_bwd|adamw|grad_sumsq|ln_modulate|gate_residual|column_pass|colsum_kernel|head_pad|head_unpad" -c 19 \
-    -o gpurun_out/prof_r01f -f python scripts/prof_kernels.py 1 > gpurun_out/ncu_prof.log 2>&1
+    -o gpurun_out/prof_r01h -f python scripts/prof_kernels.py 1 > gpurun_out/ncu_prof.log 2>&1
 echo "full capture rc=$?"; ls -la gpurun_out/*.ncu-rep; tail -n 5 gpurun_out/ncu_prof.log
