@@ -49,28 +49,34 @@ __global__ void __launch_bounds__(kThreads) ln_modulate_fwd_kernel(
     const int c = lane + 32 * i;
     if (c < nvec) v[i] = ld_stream(xr + c);
   }
-  float s = 0.f;
+  // packed fp32 pairs (FFMA2): the row statistics and the modulate take half the issue slots of the scalar form
+  f2 s2 = bc2(0.f);
 #pragma unroll
   for (int i = 0; i < MAXV; ++i) {
     if (lane + 32 * i < nvec) {
-      float f[8];
-      unpack8(v[i], f);
+      const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
 #pragma unroll
-      for (int j = 0; j < 8; ++j) s += f[j];
+      for (int j = 0; j < 4; ++j) s2 = add2(s2, unpack2(w[j]));
     }
   }
-  const float mean = warp_sum(s) * inv_c;
-  float q = 0.f;
+  float slo, shi;
+  un2(s2, slo, shi);
+  const float mean = warp_sum(slo + shi) * inv_c;
+  const f2 nmean = bc2(-mean);
+  f2 q2 = bc2(0.f);
 #pragma unroll
   for (int i = 0; i < MAXV; ++i) {
     if (lane + 32 * i < nvec) {
-      float f[8];
-      unpack8(v[i], f);
+      const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
 #pragma unroll
-      for (int j = 0; j < 8; ++j) q = fmaf(f[j] - mean, f[j] - mean, q);
+      for (int j = 0; j < 4; ++j) {
+        const f2 d = add2(unpack2(w[j]), nmean);
+        q2 = fma2(d, d, q2);
+      }
     }
   }
-  const float rstd = rsqrtf(warp_sum(q) * inv_c + eps);
+  un2(q2, slo, shi);
+  const float rstd = rsqrtf(warp_sum(slo + shi) * inv_c + eps);
   if (lane == 0 && mean_out) {
     mean_out[row] = mean;
     rstd_out[row] = rstd;
@@ -78,17 +84,19 @@ __global__ void __launch_bounds__(kThreads) ln_modulate_fwd_kernel(
   const uint4* sc = scale + (int64_t)b * mod_stride_vec;
   const uint4* sh = shift + (int64_t)b * mod_stride_vec;
   uint4* yr = y + (int64_t)row * nvec;
+  const f2 rs = bc2(rstd), one = bc2(1.0f);
 #pragma unroll
   for (int i = 0; i < MAXV; ++i) {
     const int c = lane + 32 * i;
     if (c < nvec) {
-      float f[8], a[8], d[8], o[8];
-      unpack8(v[i], f);
-      unpack8(ld_cached(sc + c), a);
-      unpack8(ld_cached(sh + c), d);
+      const uint4 av = ld_cached(sc + c), dv = ld_cached(sh + c);
+      const uint32_t w[4] = {v[i].x, v[i].y, v[i].z, v[i].w}, aw[4] = {av.x, av.y, av.z, av.w},
+                     dw[4] = {dv.x, dv.y, dv.z, dv.w};
+      uint32_t o[4];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] = fmaf((f[j] - mean) * rstd, 1.0f + a[j], d[j]);
-      st_stream(yr + c, pack8(o));
+      for (int j = 0; j < 4; ++j)      // ((x - mean) * rstd) * (1 + scale) + shift, same operation order as before
+        o[j] = pack2(fma2(mul2(add2(unpack2(w[j]), nmean), rs), add2(unpack2(aw[j]), one), unpack2(dw[j])));
+      st_stream(yr + c, make_uint4(o[0], o[1], o[2], o[3]));
     }
   }
 }
