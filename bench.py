@@ -137,6 +137,12 @@ def cpu_reference_steps(model_name, images_per_step, steps, warmup, budget_s):
     avail = psutil.virtual_memory().available
     if avail < need:
         return {"unavailable": f"host has {avail / 1e9:.0f} GB free, the fp32 oracle step needs ~{need / 1e9:.0f} GB"}
+    # all the host threads the run can use: torchrun exports OMP_NUM_THREADS=1 to every rank, which would time the
+    # reference arm on ONE core at N > 1 (measured: 4 min for 3 steps instead of 46 s for 4)
+    usable = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    want = int(os.environ.get("YAT_CPU_THREADS", "0")) or max(torch.get_num_threads(), min(16, usable))
+    if want != torch.get_num_threads():
+        torch.set_num_threads(want)
     threads = torch.get_num_threads()
     sd = ots.random_state_dict(meta, dtype=torch.float32)
     opt = torch.optim.AdamW(list(sd.values()), lr=1e-5, weight_decay=0.0)
