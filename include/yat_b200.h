@@ -228,6 +228,21 @@ int yat_adamw_step(const int64_t* tensor_tab, const int64_t* grad_ptrs, const in
                    int dtype, const float* clip_coef, double lr, double beta1, double beta2, double eps,
                    double weight_decay, int64_t step, void* stream);
 
+/* ---- EMA of the weights (common/trainer.py:264-268 EMAModel(decay=0.999), :350-351 ema_model.step every
+ * optimiser step).  diffusers' EMAModel.step is, per tensor, s.sub_(one_minus_decay * (s - p)) - three tensor ops,
+ * each rounded to the storage dtype - with p the value the optimiser just stored; the arithmetic here keeps those
+ * roundings.  one_minus_decay = 1 - get_decay(optimization_step) is formed by the caller (yat_b200/ema.py).
+ * yat_adamw_ema_step: yat_adamw_step + the shadow update in the SAME pass (+4 B/param instead of a separate
+ *   6 B/param pass); ema_ptrs [T] int64 = shadow pointer of each tensor of tensor_tab (NULL = plain AdamW).
+ * yat_ema_step: the update alone; tensor_tab rows = {param ptr, shadow ptr, unused, numel}.
+ */
+int yat_adamw_ema_step(const int64_t* tensor_tab, const int64_t* grad_ptrs, const int32_t* chunks, int n_chunks,
+                       int dtype, const float* clip_coef, double lr, double beta1, double beta2, double eps,
+                       double weight_decay, int64_t step, const int64_t* ema_ptrs, double ema_one_minus_decay,
+                       void* stream);
+int yat_ema_step(const int64_t* tensor_tab, const int32_t* chunks, int n_chunks, int dtype, double one_minus_decay,
+                 void* stream);
+
 /* ---- bucket assignment (host function; float64 compare, first-minimum wins) ---------------
  *   out[i] = argmin_j |keys[j] - ratios[i]| with strict '<' in table order, or -1 if nkeys==0.
  */

@@ -72,6 +72,30 @@ def glumbconv(x, sd, pre):
     return F.conv2d(x, sd[pre + "conv_point.weight"], None)
 
 
+def sana_block(sd, pre, x, temb, enc, bias, heads, xheads, ph, pw, eps=1e-6, softmax_self_attention=False):
+    """One SanaTransformerBlock, utils/patch_sana_attention_layers.py:82-115: x [B, N, C] tokens, temb [B, 6*C]
+    (AdaLayerNormSingle output), enc [B, L, C] projected + normed text, bias [B, 1, L] additive key mask or None.
+    ``pre`` = state-dict prefix ("transformer_blocks.<i>.")."""
+    B, _, C = x.shape
+    mod = (sd[pre + "scale_shift_table"][None] + temb.reshape(B, 6, -1)).chunk(6, dim=1)
+    shift_msa, scale_msa, gate_msa, shift_mlp, scale_mlp, gate_mlp = mod
+    n = F.layer_norm(x, (C,), None, None, eps)
+    n = (n * (1 + scale_msa) + shift_msa).to(x.dtype)
+    if softmax_self_attention:
+        a = softmax_attention(n, n, None, sd, pre + "attn1.", heads)
+    else:
+        a = linear_attention(n, sd, pre + "attn1.", heads)
+    x = x + gate_msa * a
+    a = softmax_attention(x, enc, bias, sd, pre + "attn2.", xheads)
+    x = a + x
+    n = F.layer_norm(x, (C,), None, None, eps)
+    n = n * (1 + scale_mlp) + shift_mlp
+    n = n.unflatten(1, (ph, pw)).permute(0, 3, 1, 2)
+    f = glumbconv(n, sd, pre + "ff.")
+    f = f.flatten(2, 3).permute(0, 2, 1)
+    return x + gate_mlp * f
+
+
 def sana_forward(sd, cfg, hidden_states, encoder_hidden_states, timestep, encoder_attention_mask=None,
                  gradient_checkpointing=False):
     """cfg: dict with num_attention_heads, attention_head_dim, num_layers, num_cross_attention_heads,
@@ -107,25 +131,10 @@ def sana_forward(sd, cfg, hidden_states, encoder_hidden_states, timestep, encode
     enc = rms_norm(enc, sd["caption_norm.weight"], 1e-5)
 
     C = x.shape[-1]
+
     def block(i, x, temb, enc):
-        pre = f"transformer_blocks.{i}."
-        mod = (sd[pre + "scale_shift_table"][None] + temb.reshape(B, 6, -1)).chunk(6, dim=1)
-        shift_msa, scale_msa, gate_msa, shift_mlp, scale_mlp, gate_mlp = mod
-        n = F.layer_norm(x, (C,), None, None, eps)
-        n = (n * (1 + scale_msa) + shift_msa).to(x.dtype)
-        if i in modified:
-            a = softmax_attention(n, n, None, sd, pre + "attn1.", heads)
-        else:
-            a = linear_attention(n, sd, pre + "attn1.", heads)
-        x = x + gate_msa * a
-        a = softmax_attention(x, enc, bias, sd, pre + "attn2.", xheads)
-        x = a + x
-        n = F.layer_norm(x, (C,), None, None, eps)
-        n = n * (1 + scale_mlp) + shift_mlp
-        n = n.unflatten(1, (ph, pw)).permute(0, 3, 1, 2)
-        f = glumbconv(n, sd, pre + "ff.")
-        f = f.flatten(2, 3).permute(0, 2, 1)
-        return x + gate_mlp * f
+        return sana_block(sd, f"transformer_blocks.{i}.", x, temb, enc, bias, heads, xheads, ph, pw, eps,
+                          softmax_self_attention=i in modified)
 
     for i in range(n_layers):
         if gradient_checkpointing and torch.is_grad_enabled():

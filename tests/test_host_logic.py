@@ -414,3 +414,94 @@ def test_sd35_mmdit_matches_oracle_and_hf_layout():
     assert "transformer_blocks.13.attn2.to_q.weight" not in keys and "transformer_blocks.23.attn.to_add_out.weight" not in keys
     assert big.transformer_blocks[0].norm1.linear.weight.shape[0] == 9 * 1536
     assert big.transformer_blocks[23].norm1_context.linear.weight.shape[0] == 2 * 1536
+
+
+def test_gradient_checkpointing_yaml_strings(tmp_path):
+    """BaseLoader leaves scalars as strings: "false" must not become True (bool("false"))."""
+    from yat_b200.training_parameters_reader import TrainingParameters
+    base = "batch_size: 1\nlearning_rate: 1e-5\nsteps: 1\n"
+    for text, want in [("false", False), ("0", False), ("no", False), ("off", False), ("never", False),
+                       ("true", True), ("1", True), ("yes", True), ("on", True), ("auto", "auto"), ("Auto", "auto")]:
+        cfg = tmp_path / "c.yaml"
+        cfg.write_text(base + f"gradient_checkpointing: {text}\n")
+        p = TrainingParameters()
+        p.read_yaml(str(cfg))
+        assert p.gradient_checkpointing == want and type(p.gradient_checkpointing) is type(want), text
+    (tmp_path / "c.yaml").write_text(base + "gradient_checkpointing: sometimes\n")
+    with pytest.raises(ValueError):
+        TrainingParameters().read_yaml(str(tmp_path / "c.yaml"))
+    (tmp_path / "c.yaml").write_text(base)
+    p = TrainingParameters()
+    p.read_yaml(str(tmp_path / "c.yaml"))
+    assert p.gradient_checkpointing == "auto"
+
+
+def test_ema_decay_schedule_and_oracle_restatement():
+    """EMAModel.get_decay (diffusers, restated): 0 on the first step, (1 + s) / (10 + s) warm-up capped at the
+    reference's decay = 0.999 (common/trainer.py:266); the product class and the oracle agree; the oracle's
+    update is the published s -= (1 - decay) (s - p)."""
+    from oracle.ema import EMAOracle, get_decay
+    from yat_b200.ema import EMAModel
+    assert get_decay(0) == 0.0 and get_decay(1) == 0.0
+    assert get_decay(2) == pytest.approx(2 / 11) and get_decay(3) == pytest.approx(3 / 12)
+    assert get_decay(10 ** 6) == 0.999
+    # crossover: (1 + s) / (10 + s) >= 0.999  <=>  s >= 8990
+    assert get_decay(8990) < 0.999 and get_decay(8992) == 0.999
+    e = EMAModel([torch.zeros(3)], decay=0.999)
+    for step in (1, 2, 3, 50, 9000, 20000):
+        assert e.get_decay(step) == get_decay(step)
+    p = torch.nn.Parameter(torch.tensor([1.0, 2.0]))
+    o = EMAOracle([p])
+    p.data += 1.0
+    assert o.step([p]) == 1.0 and torch.equal(o.shadow_params[0], p.data)          # decay 0: shadow = weights
+    p.data += 1.0
+    omd = o.step([p])
+    assert omd == pytest.approx(9 / 11)
+    assert torch.allclose(o.shadow_params[0], (p.data - 1.0) - omd * ((p.data - 1.0) - p.data))
+    # product class refuses CPU tensors (no CPU fallback)
+    with pytest.raises(ValueError):
+        e.step([torch.nn.Parameter(torch.zeros(3))])
+
+
+def test_trainer_refuses_silent_noops(tmp_path, monkeypatch):
+    """Config keys that would change the trained model must raise, not be dropped: the product trainer has no CPU
+    path; lora_dropout / DoRA / lora_pretrained / 8-bit optimiser are not built."""
+    monkeypatch.chdir(tmp_path)
+    from train_sana import SanaModel
+    from yat_b200.training_parameters_reader import TrainingParameters
+    params = TrainingParameters()
+    params.batch_size = 2
+    params.model_config = "sana_tiny"
+    params.learning_rate = 1e-4
+    tr = SanaModel(params)
+    if not torch.cuda.is_available():
+        with pytest.raises(RuntimeError, match="CUDA"):
+            tr.initialize()
+
+
+def test_adapter_checkpoint_is_adapter_only_and_reloads(tmp_path):
+    """save_adapters / load_adapters: peft-style adapter-only files (the full state dict with
+    '<module>.adapter.*' keys could not be reloaded by from_pretrained)."""
+    from train_sana import SANA_CONFIGS
+    from yat_b200.adapters import (ADAPTER_CONFIG_NAME, ADAPTER_WEIGHTS_NAME, adapter_state_dict, apply_adapters,
+                                   load_adapters, save_adapters)
+    from yat_b200.sana_transformer import PatchedSanaTransformer2DModel
+    from safetensors.torch import load_file
+    torch.manual_seed(2)
+    m = PatchedSanaTransformer2DModel(**SANA_CONFIGS["sana_tiny"])
+    base = {k: v.clone() for k, v in m.state_dict().items()}
+    apply_adapters(m, "lokr", 4, 4, "to_q to_k to_v to_out.0")
+    with torch.no_grad():
+        for n, p in m.named_parameters():
+            if ".adapter." in n:
+                torch.nn.init.normal_(p, std=0.05)
+    save_adapters(m, str(tmp_path / "ad"), "lokr", 4, 4, "to_q to_k to_v to_out.0")
+    files = sorted(f.name for f in (tmp_path / "ad").iterdir())
+    assert files == sorted([ADAPTER_CONFIG_NAME, ADAPTER_WEIGHTS_NAME])
+    sd = load_file(str(tmp_path / "ad" / ADAPTER_WEIGHTS_NAME))
+    assert set(sd) == set(adapter_state_dict(m)) and all(".adapter." in k for k in sd)
+    m2 = PatchedSanaTransformer2DModel(**SANA_CONFIGS["sana_tiny"])
+    m2.load_state_dict(base)                                     # a fresh base model loads strictly
+    load_adapters(m2, str(tmp_path / "ad"))
+    for (k1, v1), (k2, v2) in zip(sorted(m.state_dict().items()), sorted(m2.state_dict().items())):
+        assert k1 == k2 and torch.equal(v1, v2), k1

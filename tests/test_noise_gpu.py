@@ -177,3 +177,74 @@ def test_argument_errors(cuda):
         flowmatch_noise(lat.to(torch.float16), sch)
     with pytest.raises(ValueError):
         flowmatch_noise(lat, sch, u=torch.zeros(3, device=cuda))
+
+
+def test_generate_mode_noise_is_standard_normal_on_the_bf16_grid(cuda):
+    """The stream every real training step uses (generate mode, train_sana.py:183 draws eps ~ N(0,1) in bf16):
+    2^27 bf16 samples of the counter RNG against the bf16-ROUNDED standard normal (oracle/normal_grid.py: exact bin
+    masses from the float64 normal CDF).  Moments within 3.5 sampling standard errors, discrete
+    Kolmogorov-Smirnov distance below the alpha = 0.001 critical value, tail masses beyond 3, 4 and 4.5 sigma,
+    lag-1 and within-pair correlations (the two normals of a pair come from ONE Philox word), per-sample streams
+    uncorrelated.  Sampling errors: mean 1/sqrt(n), variance sqrt(2/n), skewness sqrt(6/n), kurtosis sqrt(24/n)."""
+    from oracle import normal_grid
+    from yat_b200.noise import flowmatch_noise
+    from yat_b200.schedulers import FlowMatchEulerDiscreteScheduler
+    B, chw = 4096, 32 * 32 * 32
+    n = B * chw
+    assert n == 1 << 27
+    lat = torch.zeros((B, chw), dtype=torch.bfloat16, device=cuda)
+    out = flowmatch_noise(lat, FlowMatchEulerDiscreteScheduler(), seed=20261104, offset=3, want_target=False,
+                          want_noise=True)
+    z = out.noise
+    del lat
+    # ---- histogram over the 65536 bf16 patterns (exact empirical distribution)
+    counts = torch.zeros(65536, dtype=torch.int64, device=cuda)
+    for part in z.view(torch.int16).reshape(-1).chunk(16):
+        counts += torch.bincount(part.to(torch.int32) & 0xFFFF, minlength=65536)
+    counts = counts.cpu().numpy()
+    assert counts.sum() == n
+    vals, bits, mass, cdf = normal_grid.bf16_normal_bins()
+    assert counts[~np.isin(np.arange(65536), np.concatenate([bits, [0x8000]]))].sum() == 0      # no inf / nan
+    d, _, at = normal_grid.discrete_ks(counts)
+    ks_crit = 1.95 / np.sqrt(n)                                # Kolmogorov, alpha = 0.001
+    assert d < ks_crit, (d, ks_crit, at)
+    # ---- moments of the rounded variable vs their exact expectations
+    c = counts.astype(np.float64).copy()
+    c[0] += c[0x8000]
+    p = c[bits] / n
+    m1 = float((p * vals).sum())
+    mu2 = float((p * (vals - m1) ** 2).sum())
+    skew = float((p * (vals - m1) ** 3).sum()) / mu2 ** 1.5
+    kurt = float((p * (vals - m1) ** 4).sum()) / mu2 ** 2 - 3.0
+    e1, e2, e3, e4 = normal_grid.rounded_normal_moments()
+    k = 3.5
+    assert abs(m1 - e1) < k / np.sqrt(n), m1
+    assert abs(mu2 - e2) < k * np.sqrt(2.0 / n), mu2
+    assert abs(skew - e3) < k * np.sqrt(6.0 / n), skew
+    assert abs(kurt - e4) < k * np.sqrt(24.0 / n), kurt
+    # ---- tail masses (two-sided) vs the rounded normal: binomial standard error
+    for t in (3.0, 4.0, 4.5):
+        exp = float(mass[np.abs(vals) >= t].sum())
+        got = float(p[np.abs(vals) >= t].sum())
+        se = np.sqrt(exp * (1 - exp) / n)
+        assert abs(got - exp) < 4 * se, (t, got, exp, se)
+    # the one-word Box-Muller stops at sqrt(40 ln 2) = 5.27 (torch's fp32 CPU randn at 5.77): the mass beyond is
+    # 1.4e-7, i.e. 18 of 2^27 samples
+    assert np.abs(vals[p > 0]).max() <= 5.3
+    # ---- correlations: lag 1 inside a sample (element 2j, 2j+1 share a Philox word; 2j+1, 2j+2 do not),
+    # across samples at the same element, squares (a shared-radius signature) - all ~ N(0, 1/sqrt(m))
+    zf = z[:512].float()                                       # 2^24 elements
+    m = zf.numel()
+    def corr(a, b):
+        a, b = a.reshape(-1).double(), b.reshape(-1).double()
+        return float(((a - a.mean()) * (b - b.mean())).mean() / (a.std() * b.std()))
+    pair = corr(zf[:, 0::2], zf[:, 1::2])
+    lag = corr(zf[:, 1:-1:2], zf[:, 2::2])
+    cross = corr(zf[:256], zf[256:])
+    sq_lag = corr(zf[:, 1:-1:2] ** 2, zf[:, 2::2] ** 2)
+    lim = 4.5 / np.sqrt(m / 2)
+    assert abs(pair) < lim and abs(lag) < lim and abs(cross) < lim and abs(sq_lag) < lim, (pair, lag, cross, sq_lag)
+    # the two normals of one word share the radius: their squares ARE correlated in any Box-Muller pair only if
+    # the angle were not uniform; with a uniform angle corr(z0^2, z1^2) = 0 exactly (chi-square_2 radius)
+    sq_pair = corr(zf[:, 0::2] ** 2, zf[:, 1::2] ** 2)
+    assert abs(sq_pair) < lim, sq_pair

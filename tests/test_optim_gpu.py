@@ -111,3 +111,112 @@ def test_deterministic_and_state_dict(cuda):
     assert set(sd["param_groups"][0]) >= {"lr", "betas", "eps", "weight_decay", "params"}
     assert set(sd["state"][0]) == {"step", "exp_avg", "exp_avg_sq"}
     ref.load_state_dict(sd)   # layout-compatible with torch.optim.AdamW
+
+
+# ---------------------------------------------------------------------------------------------------------
+# EMA (common/trainer.py:264-268,350-351): yat_ema_step / yat_adamw_ema_step vs oracle/ema.py (torch ops on CPU)
+# ---------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_ema_standalone_bit_exact_vs_oracle(cuda, dtype):
+    """EMAModel.step alone: the shadow tensors equal the reference's three torch ops bit for bit (the kernel keeps
+    the per-op rounding to the storage dtype), over the decay warm-up (1 - decay = 1, 9/11, 9/12, ...) and one
+    frozen tensor (copied)."""
+    from oracle.ema import EMAOracle, get_decay
+    from yat_b200.ema import EMAModel
+    ps, _ = _make(dtype, 11, 1.0)
+    cpu = [torch.nn.Parameter(p.clone()) for p in ps]
+    dev = [torch.nn.Parameter(p.to(cuda)) for p in ps]
+    cpu[3].requires_grad_(False), dev[3].requires_grad_(False)
+    ref, ema = EMAOracle(cpu, decay=0.999), EMAModel(dev, decay=0.999)
+    gen = torch.Generator().manual_seed(3)
+    for step in range(1, 7):
+        for a, b in zip(cpu, dev):                       # the weights move between EMA steps
+            d = (torch.randn(a.shape, generator=gen) * 0.05).to(dtype)
+            a.data.add_(d)
+            b.data.add_(d.to(cuda))
+        omd = ref.step(cpu)
+        ema.step(dev)
+        assert ema.optimization_step == step and abs((1 - ema.cur_decay_value) - omd) < 1e-15
+        assert ema.cur_decay_value == get_decay(step)
+        for s_ref, s in zip(ref.shadow_params, ema.shadow_params):
+            assert torch.equal(s.cpu(), s_ref), (step, s.shape)
+    assert ema.cur_decay_value == pytest.approx(6 / 15)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_ema_fused_into_adamw_equals_separate_steps(cuda, dtype):
+    """optimizer.clip_and_step(ema=...) == optimizer.clip_and_step(); ema.step(parameters): weights, moments and
+    shadows bit-identical (the fused kernel feeds the EMA the value it just stored), and the shadow matches the
+    oracle's torch ops applied to the device's own weights."""
+    from oracle.ema import EMAOracle
+    from yat_b200.ema import EMAModel
+    from yat_b200.optim import FusedClipAdamW
+    ps, gs = _make(dtype, 21, 1e-2)
+    a = [torch.nn.Parameter(p.to(cuda)) for p in ps]
+    b = [torch.nn.Parameter(p.to(cuda)) for p in ps]
+    oa, ob = FusedClipAdamW(a, lr=1e-2, weight_decay=0.05), FusedClipAdamW(b, lr=1e-2, weight_decay=0.05)
+    ea, eb = EMAModel(a, decay=0.999).bind(a), EMAModel(b, decay=0.999)
+    ref = EMAOracle([p.detach().cpu() for p in a], decay=0.999)
+    for step in range(1, 5):
+        gen = torch.Generator().manual_seed(50 + step)
+        for pa, pb, g in zip(a, b, gs):
+            gr = (torch.randn(g.shape, generator=gen) * 1e-2).to(dtype).to(cuda)
+            pa.grad, pb.grad = gr.clone(), gr.clone()
+        oa.clip_and_step(max_norm=1.0, ema=ea)
+        ob.clip_and_step(max_norm=1.0)
+        eb.step(b)
+        ref.step([p.detach().cpu().requires_grad_(True) for p in a])
+        for pa, pb in zip(a, b):
+            assert torch.equal(pa, pb)
+        for sa, sb, sr in zip(ea.shadow_params, eb.shadow_params, ref.shadow_params):
+            assert torch.equal(sa, sb)
+            assert torch.equal(sa.cpu(), sr)
+    assert ea.optimization_step == eb.optimization_step == 4
+
+
+def test_optimizer_state_dict_reload_uses_the_loaded_moments(cuda):
+    """step -> state_dict -> load_state_dict -> step: the device tables must follow the re-allocated moment
+    tensors (the table cache is keyed on parameter AND moment pointers), and the result equals an optimizer that
+    never went through the reload."""
+    from yat_b200.optim import FusedClipAdamW
+    ps, gs = _make(torch.bfloat16, 31, 1e-2)
+    a = [torch.nn.Parameter(p.to(cuda)) for p in ps]
+    b = [torch.nn.Parameter(p.to(cuda)) for p in ps]
+    oa, ob = FusedClipAdamW(a, lr=1e-2), FusedClipAdamW(b, lr=1e-2)
+
+    def grads(step):
+        gen = torch.Generator().manual_seed(70 + step)
+        return [(torch.randn(g.shape, generator=gen) * 1e-2).to(torch.bfloat16).to(cuda) for g in gs]
+
+    for step in (1, 2):
+        for pa, pb, g in zip(a, b, grads(step)):
+            pa.grad, pb.grad = g.clone(), g.clone()
+        oa.step(max_norm=1.0), ob.step(max_norm=1.0)
+    sd = ob.state_dict()
+    old = [ob.state[p]["exp_avg"] for p in b]
+    ob.load_state_dict(sd)                                  # replaces every state tensor
+    assert all(ob.state[p]["exp_avg"].data_ptr() != o.data_ptr() for p, o in zip(b, old))
+    for o in old:
+        o.fill_(float("nan"))                               # a stale table would read (and spread) these
+    del old
+    for step in (3, 4):
+        for pa, pb, g in zip(a, b, grads(step)):
+            pa.grad, pb.grad = g.clone(), g.clone()
+        oa.step(max_norm=1.0), ob.step(max_norm=1.0)
+    for pa, pb in zip(a, b):
+        assert torch.equal(pa, pb)
+        assert torch.equal(oa.state[pa]["exp_avg"], ob.state[pb]["exp_avg"])
+        assert torch.equal(oa.state[pa]["exp_avg_sq"], ob.state[pb]["exp_avg_sq"])
+
+
+def test_mixed_step_counts_in_one_group_are_refused(cuda):
+    from yat_b200.optim import FusedClipAdamW
+    a = torch.nn.Parameter(torch.zeros(64, device=cuda, dtype=torch.bfloat16))
+    b = torch.nn.Parameter(torch.zeros(64, device=cuda, dtype=torch.bfloat16))
+    opt = FusedClipAdamW([a, b], lr=1e-2)
+    a.grad, b.grad = torch.ones_like(a), torch.ones_like(b)
+    opt.step()
+    opt.state[b]["step"] += 5
+    a.grad, b.grad = torch.ones_like(a), torch.ones_like(b)
+    with pytest.raises(ValueError, match="different steps"):
+        opt.step()

@@ -54,6 +54,9 @@ SIGNATURES = {
     "yat_grad_clip_coef": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p]),
     "yat_adamw_step": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_double, c_double, c_double,
                                c_double, c_double, c_int64, c_void_p]),
+    "yat_adamw_ema_step": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_double, c_double, c_double,
+                                   c_double, c_double, c_int64, c_void_p, c_double, c_void_p]),
+    "yat_ema_step": (c_int, [c_void_p, c_void_p, c_int, c_int, c_double, c_void_p]),
     "yat_pad_embeddings": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "yat_linattn_fwd_ld": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "yat_linattn_bwd_ld": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
@@ -72,7 +75,7 @@ LAUNCHING = ("yat_noise_flowmatch", "yat_noise_ddpm", "yat_loss_fused", "yat_rep
              "yat_linattn_bwd", "yat_linattn_fwd_simt", "yat_linattn_bwd_simt", "yat_pad_embeddings",
              "yat_philox_raw", "yat_ln_modulate_fwd", "yat_ln_modulate_bwd", "yat_gate_residual_fwd",
              "yat_gate_residual_bwd", "yat_glumb_mid_fwd", "yat_glumb_mid_bwd", "yat_grad_clip_coef",
-             "yat_adamw_step", "yat_colsum_bf16", "yat_head_pad", "yat_head_unpad",
+             "yat_adamw_step", "yat_adamw_ema_step", "yat_ema_step", "yat_colsum_bf16", "yat_head_pad", "yat_head_unpad",
              "yat_linattn_fwd_ld", "yat_linattn_bwd_ld")
 launch_counts = {name: 0 for name in LAUNCHING}
 

@@ -13,6 +13,10 @@ updates away (a bf16 ulp of a 0.02-sized weight is 1e-4):
 The base weights stay frozen, ordinary ``weight`` tensors, so the hand-written kernels and the token-major GEMM
 path of GLUMBConv see the same layout as in a full fine-tune; modules reached as ``module(x)`` get the term from a
 forward hook, ``GLUMBConv.forward_tokens`` (which reads ``.weight`` directly) adds it through ``adapter_term``.
+Initialisation: LoRA as peft (A kaiming-uniform, B zero).  LoKr keeps ``w1`` kaiming-uniform and zero-initialises the
+``w2`` side; peft's ``LoKrLayer.reset_adapter_parameters`` zeroes ``w1`` and draws ``w2`` - either way the adapter starts at
+exactly 0, the two differ only in which factor receives the first non-zero gradient (stated deviation, unpinned:
+peft is not installed).
 ``adapters_disabled(model)`` runs the base weights only: the preservation term's frozen prediction
 (README.md:81-82; SURVEY.md §8 A7: "for LoRA/LoKr the same weights with adapters disabled") needs no second copy of
 the model.  Parity with peft is unpinned (the package is absent); the formulas are the published LoRA
@@ -196,3 +200,40 @@ def adapters_disabled(model):
 def adapter_state_dict(model):
     """Only the adapter tensors (what ``save_pretrained`` of a PeftModel stores)."""
     return {k: v for k, v in model.state_dict().items() if ".adapter." in k}
+
+
+ADAPTER_CONFIG_NAME = "adapter_config.json"
+ADAPTER_WEIGHTS_NAME = "adapter_model.safetensors"
+
+
+def save_adapters(model, path, algo, rank, alpha, target_modules):
+    """Adapter-only checkpoint in peft's file layout (``adapter_config.json`` + ``adapter_model.safetensors``):
+    what ``PeftModel.save_pretrained`` writes upstream (common/trainer.py:295-296 on a peft-wrapped model).  The
+    frozen base weights are not part of it, so the directory reloads with ``load_adapters`` on a fresh base model."""
+    import json
+    import os
+    from safetensors.torch import save_file
+    os.makedirs(path, exist_ok=True)
+    targets = target_modules.split() if isinstance(target_modules, str) else list(target_modules)
+    with open(os.path.join(path, ADAPTER_CONFIG_NAME), "w") as f:
+        json.dump({"peft_type": algo.upper(), "r": int(rank), "alpha": float(alpha if alpha is not None else rank),
+                   "target_modules": targets}, f, indent=2)
+    save_file({k: v.detach().contiguous().cpu() for k, v in adapter_state_dict(model).items()},
+              os.path.join(path, ADAPTER_WEIGHTS_NAME))
+
+
+def load_adapters(model, path):
+    """Attach adapters described by ``path/adapter_config.json`` to ``model`` and load their tensors."""
+    import json
+    import os
+    from safetensors.torch import load_file
+    with open(os.path.join(path, ADAPTER_CONFIG_NAME)) as f:
+        cfg = json.load(f)
+    names = apply_adapters(model, cfg["peft_type"].lower(), cfg["r"], cfg["alpha"], cfg["target_modules"])
+    sd = load_file(os.path.join(path, ADAPTER_WEIGHTS_NAME))
+    own = adapter_state_dict(model)
+    if set(sd) != set(own):
+        raise ValueError(f"adapter checkpoint keys do not match the model: {sorted(set(sd) ^ set(own))[:4]} ...")
+    for k, v in sd.items():
+        own[k].copy_(v.to(own[k].device, own[k].dtype))
+    return names

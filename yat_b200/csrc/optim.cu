@@ -163,12 +163,23 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
   p = __fsub_rn(p, Vec<T>::div(__fmul_rn(a.step_size, m), denom));
 }
 
-// ---- pass 2: AdamW over the same chunk list ---------------------------------------------------------
+// EMA of the weights, diffusers EMAModel.step (common/trainer.py:264-268,350-351):
+//   s_param.sub_(one_minus_decay * (s_param - param))
+// three tensor ops upstream, each rounded to the storage dtype; p is the value the optimiser just STORED.
 template <typename T>
+__device__ __forceinline__ float ema_one(float s, float p_stored, float omd) {
+  const float d = Vec<T>::rnd(__fsub_rn(s, p_stored));
+  const float t = Vec<T>::rnd(__fmul_rn(omd, d));
+  return __fsub_rn(s, t);     // rounded by the store
+}
+
+// ---- pass 2: AdamW over the same chunk list (+ the EMA shadow update in the same pass when kEma) ---------
+template <typename T, bool kEma>
 __global__ void __launch_bounds__(kThreads) adamw_kernel(const Tensor4* __restrict__ tab,
                                                          const int64_t* __restrict__ gtab,
                                                          const int2* __restrict__ chunks, int n_chunks,
-                                                         const float* __restrict__ coef_ptr, const AdamArgs a) {
+                                                         const float* __restrict__ coef_ptr, const AdamArgs a,
+                                                         const int64_t* __restrict__ etab, float ema_omd) {
   const float coef = coef_ptr ? __ldg(coef_ptr) : 1.0f;
   // walk the chunk list backwards: the norm pass ended on the last chunks, whose gradients are the
   // ones still resident in the 126 MB L2
@@ -181,20 +192,27 @@ __global__ void __launch_bounds__(kThreads) adamw_kernel(const Tensor4* __restri
     T* m = reinterpret_cast<T*>(t.m) + start;
     T* v = reinterpret_cast<T*>(t.v) + start;
     const T* g = reinterpret_cast<const T*>(gtab[ch.x]) + start;
+    T* s = kEma ? reinterpret_cast<T*>(etab[ch.x]) + start : nullptr;
     const bool vec = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v) |
-                       reinterpret_cast<uintptr_t>(g)) % Vec<T>::kBytes) == 0;
+                       reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(s)) % Vec<T>::kBytes) == 0;
     const int nv = vec ? len >> 3 : 0;
     for (int i = threadIdx.x; i < nv; i += kThreads) {
-      float fp[8], fg[8], fm[8], fv[8];
+      float fp[8], fg[8], fm[8], fv[8], fs[8];
       Vec<T>::load(p + 8 * i, fp);
       Vec<T>::load_stream(g + 8 * i, fg);
       Vec<T>::load(m + 8 * i, fm);
       Vec<T>::load(v + 8 * i, fv);
+      if (kEma) Vec<T>::load(s + 8 * i, fs);
 #pragma unroll
       for (int e = 0; e < 8; ++e) adam_one<T>(fp[e], fg[e], fm[e], fv[e], coef, a);
       Vec<T>::store(p + 8 * i, fp);
       Vec<T>::store(m + 8 * i, fm);
       Vec<T>::store(v + 8 * i, fv);
+      if (kEma) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) fs[e] = ema_one<T>(fs[e], Vec<T>::rnd(fp[e]), ema_omd);
+        Vec<T>::store(s + 8 * i, fs);
+      }
     }
     for (int i = 8 * nv + threadIdx.x; i < len; i += kThreads) {
       float fp = Vec<T>::get(p + i), fm = Vec<T>::get(m + i), fv = Vec<T>::get(v + i);
@@ -202,7 +220,34 @@ __global__ void __launch_bounds__(kThreads) adamw_kernel(const Tensor4* __restri
       Vec<T>::put(p + i, fp);
       Vec<T>::put(m + i, fm);
       Vec<T>::put(v + i, fv);
+      if (kEma) Vec<T>::put(s + i, ema_one<T>(Vec<T>::get(s + i), Vec<T>::rnd(fp), ema_omd));
     }
+  }
+}
+
+// ---- stand-alone EMA step over a chunk list: tab rows = {param ptr, shadow ptr, unused, numel} ----------
+template <typename T>
+__global__ void __launch_bounds__(kThreads) ema_kernel(const Tensor4* __restrict__ tab, const int2* __restrict__ chunks,
+                                                       int n_chunks, float omd) {
+  for (int c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+    const int2 ch = chunks[c];
+    const Tensor4 t = tab[ch.x];
+    const int64_t start = (int64_t)ch.y * kChunk;
+    const int len = (int)(t.n - start < kChunk ? t.n - start : kChunk);
+    const T* p = reinterpret_cast<const T*>(t.p) + start;
+    T* s = reinterpret_cast<T*>(t.m) + start;
+    const bool vec = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(s)) % Vec<T>::kBytes) == 0;
+    const int nv = vec ? len >> 3 : 0;
+    for (int i = threadIdx.x; i < nv; i += kThreads) {
+      float fp[8], fs[8];
+      Vec<T>::load_stream(p + 8 * i, fp);
+      Vec<T>::load(s + 8 * i, fs);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) fs[e] = ema_one<T>(fs[e], fp[e], omd);
+      Vec<T>::store(s + 8 * i, fs);
+    }
+    for (int i = 8 * nv + threadIdx.x; i < len; i += kThreads)
+      Vec<T>::put(s + i, ema_one<T>(Vec<T>::get(s + i), Vec<T>::get(p + i), omd));
   }
 }
 
@@ -241,7 +286,36 @@ extern "C" int yat_grad_clip_coef(const int64_t* tensor_tab, const int64_t* grad
 extern "C" int yat_adamw_step(const int64_t* tensor_tab, const int64_t* grad_ptrs, const int32_t* chunks, int n_chunks,
                               int dtype, const float* clip_coef, double lr, double beta1, double beta2, double eps,
                               double weight_decay, int64_t step, void* stream) {
+  return yat_adamw_ema_step(tensor_tab, grad_ptrs, chunks, n_chunks, dtype, clip_coef, lr, beta1, beta2, eps,
+                            weight_decay, step, nullptr, 0.0, stream);
+}
+
+extern "C" int yat_ema_step(const int64_t* tensor_tab, const int32_t* chunks, int n_chunks, int dtype,
+                            double one_minus_decay, void* stream) {
   using namespace yat;
+  YAT_REQUIRE(tensor_tab && chunks, YAT_ERR_BAD_ARG, "yat_ema_step: null pointer argument");
+  YAT_REQUIRE(n_chunks > 0, YAT_ERR_BAD_ARG, "yat_ema_step: n_chunks=%d must be positive", n_chunks);
+  YAT_REQUIRE(dtype == YAT_DTYPE_BF16 || dtype == YAT_DTYPE_F32, YAT_ERR_UNSUPPORTED,
+              "yat_ema_step: dtype %d not supported", dtype);
+  YAT_REQUIRE(one_minus_decay >= 0.0 && one_minus_decay <= 1.0, YAT_ERR_BAD_ARG,
+              "yat_ema_step: one_minus_decay=%g outside [0, 1]", one_minus_decay);
+  cudaStream_t st = (cudaStream_t)stream;
+  const Tensor4* tab = (const Tensor4*)tensor_tab;
+  const int2* ch = (const int2*)chunks;
+  if (dtype == YAT_DTYPE_BF16)
+    ema_kernel<__nv_bfloat16><<<grid_for(n_chunks), kThreads, 0, st>>>(tab, ch, n_chunks, (float)one_minus_decay);
+  else
+    ema_kernel<float><<<grid_for(n_chunks), kThreads, 0, st>>>(tab, ch, n_chunks, (float)one_minus_decay);
+  return check_launch("ema_step");
+}
+
+extern "C" int yat_adamw_ema_step(const int64_t* tensor_tab, const int64_t* grad_ptrs, const int32_t* chunks,
+                                  int n_chunks, int dtype, const float* clip_coef, double lr, double beta1,
+                                  double beta2, double eps, double weight_decay, int64_t step,
+                                  const int64_t* ema_ptrs, double ema_one_minus_decay, void* stream) {
+  using namespace yat;
+  YAT_REQUIRE(!ema_ptrs || (ema_one_minus_decay >= 0.0 && ema_one_minus_decay <= 1.0), YAT_ERR_BAD_ARG,
+              "yat_adamw_ema_step: one_minus_decay=%g outside [0, 1]", ema_one_minus_decay);
   YAT_REQUIRE(tensor_tab && grad_ptrs && chunks, YAT_ERR_BAD_ARG, "yat_adamw_step: null pointer argument");
   YAT_REQUIRE(n_chunks > 0 && step > 0, YAT_ERR_BAD_ARG, "yat_adamw_step: n_chunks=%d step=%lld must be positive",
               n_chunks, (long long)step);
@@ -257,9 +331,18 @@ extern "C" int yat_adamw_step(const int64_t* tensor_tab, const int64_t* grad_ptr
   cudaStream_t st = (cudaStream_t)stream;
   const Tensor4* tab = (const Tensor4*)tensor_tab;
   const int2* ch = (const int2*)chunks;
-  if (dtype == YAT_DTYPE_BF16)
-    adamw_kernel<__nv_bfloat16><<<grid_for(n_chunks), kThreads, 0, st>>>(tab, grad_ptrs, ch, n_chunks, clip_coef, a);
-  else
-    adamw_kernel<float><<<grid_for(n_chunks), kThreads, 0, st>>>(tab, grad_ptrs, ch, n_chunks, clip_coef, a);
+  const float omd = (float)ema_one_minus_decay;
+  const int grid = grid_for(n_chunks);
+  if (dtype == YAT_DTYPE_BF16) {
+    if (ema_ptrs)
+      adamw_kernel<__nv_bfloat16, true><<<grid, kThreads, 0, st>>>(tab, grad_ptrs, ch, n_chunks, clip_coef, a, ema_ptrs, omd);
+    else
+      adamw_kernel<__nv_bfloat16, false><<<grid, kThreads, 0, st>>>(tab, grad_ptrs, ch, n_chunks, clip_coef, a, nullptr, 0.f);
+  } else {
+    if (ema_ptrs)
+      adamw_kernel<float, true><<<grid, kThreads, 0, st>>>(tab, grad_ptrs, ch, n_chunks, clip_coef, a, ema_ptrs, omd);
+    else
+      adamw_kernel<float, false><<<grid, kThreads, 0, st>>>(tab, grad_ptrs, ch, n_chunks, clip_coef, a, nullptr, 0.f);
+  }
   return check_launch("adamw_step");
 }

@@ -142,14 +142,20 @@ __device__ __forceinline__ void box_muller_precise(uint32_t xa, uint32_t xb, flo
 // 8 normals of one 128-bit bf16 vector, and the transform is 4 MUFU ops per pair (lg2, sqrt, sin,
 // cos) with no integer->float conversion:
 //   f = 1 + (x>>12)*2^-20 in [1,2)       u1 = 2 - f in (0,1]  (exact)      r = sqrt(-2 ln u1)
-//   g = 1 + (x&0xfff)*2^-12 in [1,2)     theta = 2*pi*(g - 1.5) + pi/4096 in (-pi,pi)
+//   g = 1 + ((x&0xfff)*2^11 + ((x>>12)&0x7ff))*2^-23 in [1,2)
+//                                        theta = fl32(2*pi*g - 3*pi) in (-pi,pi)
 //   z0 = r cos(theta), z1 = r sin(theta)
-// 4096 angles are finer than the bf16 grid (2^-8 relative) the result is rounded to; the
-// half-step offset keeps the angle set symmetric.  Largest |z| = sqrt(40 ln 2) = 5.27 (the
-// reference's fp32 CPU randn stops at sqrt(48 ln 2) = 5.77).  |theta| < pi keeps sin.approx /
-// cos.approx at their 2^-21 absolute accuracy; the oracle (oracle/philox.py box_muller_word)
-// evaluates the same map in float64 and the test allows the ~1e-6 absolute difference before
-// rounding.  Element e of a sample lives in call (oct) e/8, word (e%8)/2, cos for even e.
+// The 12 angle bits alone would put every pair on a fixed lattice of 4096 rays; the rays next to the
+// axes then leave a dent in the distribution of r cos(theta) at |z| < 1e-3 (exact population count over all
+// 2^32 words: discrete Kolmogorov-Smirnov distance 8.3e-5 from the bf16-rounded normal, half the critical
+// value of a 2^27-sample test).  The LOW 11 radius bits therefore dither the lattice (they move r by < 2^-9
+// relative outside the far tail, and every sub-lattice is itself uniform): population KS distance 9.6e-6
+// (tests/test_oracle_golden.py checks a strided population count).  One extra instruction per word.
+// Largest |z| = sqrt(40 ln 2) = 5.27 (the reference's fp32 CPU randn stops at sqrt(48 ln 2) = 5.77).
+// |theta| < pi keeps sin.approx / cos.approx at their 2^-21 absolute accuracy; the oracle
+// (oracle/philox.py box_muller_word) evaluates the same map in float64 and the test allows the ~1e-6
+// absolute difference before rounding.  Element e of a sample lives in call (oct) e/8, word (e%8)/2,
+// cos for even e.
 __device__ __forceinline__ float mufu_lg2(float x) {
   float y;
   asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -163,12 +169,13 @@ __device__ __forceinline__ float mufu_sqrt(float x) {
 __device__ __forceinline__ void box_muller_word(uint32_t x, float& z0, float& z1) {
   // mantissa fields placed with one integer multiply-add each (written in PTX: the compiler
   // otherwise re-expands "shift, and, or" into three instructions per field)
-  uint32_t fb, gb;
+  uint32_t fb;
   asm("mad.lo.u32 %0, %1, 8, 0x3f800000;" : "=r"(fb) : "r"(x >> 12));
-  asm("mad.lo.u32 %0, %1, 2048, 0x3f800000;" : "=r"(gb) : "r"(x & 0xfffu));
+  // mantissa of g = [angle bits 0..11 | radius bits 12..22]: one funnel shift of {x : x << 9} by 11
+  const uint32_t gb = (__funnelshift_l(x << 9, x, 11) & 0x007fffffu) | 0x3f800000u;
   const float f = __uint_as_float(fb), g = __uint_as_float(gb);
   const float u1 = 2.0f - f;
-  const float theta = fmaf(g, 6.283185307179586f, -9.424010970375436f);  // -3 pi + pi/4096
+  const float theta = fmaf(g, 6.283185307179586f, -9.42477796076938f);  // fl32(-3 pi): the half-step offset pi/2^23 is below fp32 resolution here
   const float r = mufu_sqrt(-1.3862943611198906f * mufu_lg2(u1));       // -2 ln2 * log2(u1)
   z0 = r * __cosf(theta);
   z1 = r * __sinf(theta);

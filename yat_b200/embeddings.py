@@ -8,15 +8,30 @@ import torch
 
 from . import _lib
 
-_staging = {}
+_RING = 4          # staging buffers in flight: the step has no host sync, so the host runs ahead of the GPU
+_staging = {"bufs": [None] * _RING, "events": [None] * _RING, "slot": 0}
 
 
 def _pinned(nbytes):
-    buf = _staging.get("buf")
+    """Next pinned staging buffer of a ring.  A buffer is rewritten only after the H2D copy that last read it has
+    completed (CUDA event recorded after that copy); in steady state that copy finished several steps ago."""
+    k = _staging["slot"]
+    _staging["slot"] = (k + 1) % _RING
+    ev = _staging["events"][k]
+    if ev is not None:
+        ev.synchronize()
+        _staging["events"][k] = None
+    buf = _staging["bufs"][k]
     if buf is None or buf.numel() < nbytes:
         buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8).pin_memory()
-        _staging["buf"] = buf
-    return buf
+        _staging["bufs"][k] = buf
+    return buf, k
+
+
+def _copied(k):
+    ev = torch.cuda.Event()
+    ev.record()
+    _staging["events"][k] = ev
 
 
 def _is_packed_pinned(embeddings, lens, E, dtype):
@@ -62,12 +77,14 @@ def pad_embeddings(embeddings, max_len, device, dtype=torch.bfloat16, trim_multi
         r0 = embeddings[0].storage_offset() // E
         packed = base[r0:r0 + total].to(device, non_blocking=True)
     else:
-        stage = _pinned(total * E * 2).narrow(0, 0, total * E * 2).view(torch.bfloat16).view(total, E)
+        buf, slot = _pinned(total * E * 2)
+        stage = buf.narrow(0, 0, total * E * 2).view(torch.bfloat16).view(total, E)
         o = 0
         for e, l in zip(embeddings, lens):
             stage[o:o + l].copy_(e[:l])
             o += l
         packed = stage.to(device, non_blocking=True)
+        _copied(slot)
     offsets_d = offsets.to(device, non_blocking=True)
     padded = torch.empty((B, max_len, E), dtype=dtype, device=device)
     mask = torch.empty((B, max_len), dtype=torch.int64, device=device)

@@ -43,7 +43,24 @@ class _Group:
             st = state[p]
             rows.append([p.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(), p.numel()])
         self.tab = torch.tensor(rows, dtype=torch.int64).to(self.gtab.device)
-        self.tab_key = tuple(r[0] for r in rows)
+        self.tab_key = self.key_of(state)
+        self.etab = self.etab_key = None
+
+    def key_of(self, state):
+        """Every pointer the device table caches: Optimizer.load_state_dict() swaps the moment tensors while the
+        parameter pointers stay, so the parameters alone do not identify a valid table."""
+        return tuple((p.data_ptr(), state[p]["exp_avg"].data_ptr(), state[p]["exp_avg_sq"].data_ptr())
+                     for p in self.params)
+
+    def ema_table(self, shadows):
+        key = tuple(s.data_ptr() for s in shadows)
+        if self.etab is None or self.etab_key != key:
+            for p, s in zip(self.params, shadows):
+                if s.dtype != p.dtype or s.shape != p.shape or not s.is_contiguous() or s.device != p.device:
+                    raise ValueError("FusedClipAdamW: EMA shadow tensors must match their parameters (dtype, shape, device)")
+            self.etab = torch.tensor(key, dtype=torch.int64).to(self.gtab.device)
+            self.etab_key = key
+        return self.etab
 
     def upload_grads(self):
         """Gradient pointers of this step -> device (async from a pinned ring slot)."""
@@ -95,13 +112,23 @@ class FusedClipAdamW(torch.optim.Optimizer):
                         st["step"] = torch.zeros((), dtype=torch.float32)
                         st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
                         st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
-                if g.tab is None or g.tab_key != tuple(p.data_ptr() for p in ps):
+                if g.tab is None or g.tab_key != g.key_of(self.state):
                     g.build_table(self.state)
                 out.append((group, g))
         return out
 
+    def load_state_dict(self, state_dict):
+        super().load_state_dict(state_dict)
+        self._groups = {}          # the device tables point at the moment tensors that were just replaced
+
+    def __setstate__(self, state):
+        super().__setstate__(state)
+        self._groups = {}
+
     @torch.no_grad()
-    def step(self, closure=None, max_norm=None):
+    def step(self, closure=None, max_norm=None, ema=None):
+        """``ema``: a bound ``yat_b200.ema.EMAModel``; its shadow tensors are updated in the same pass as the
+        weights (common/trainer.py:350-351 ``ema_model.step(parameters)`` right after ``optimizer.step()``)."""
         loss = None
         if closure is not None:
             with torch.enable_grad():
@@ -125,18 +152,38 @@ class FusedClipAdamW(torch.optim.Optimizer):
             _lib.check(rc, "yat_grad_clip_coef")
             coef = g.norm_coef[1:]
             self.last_norm = g.norm_coef[0]
+        omd = ema.advance() if ema is not None else 0.0
         for group, g in sets:
+            steps = set()
             for p in g.params:
-                self.state[p]["step"] += 1
-            step = int(self.state[g.params[0]]["step"])
+                st = self.state[p]["step"]
+                st += 1
+                steps.add(int(st))
+            if len(steps) != 1:
+                # the bias corrections are launch constants: a tensor that first got a gradient later would be
+                # updated with the wrong 1 - beta^t
+                raise ValueError(f"FusedClipAdamW: parameters of one group are at different steps {sorted(steps)}; "
+                                 "give parameters that start receiving gradients later their own param group")
+            step = steps.pop()
             b1, b2 = group["betas"]
+            etab = g.ema_table(ema.shadow_of(g.params)) if ema is not None else None
             with _lib.timed("adamw_step"):
-                rc = lib.yat_adamw_step(_lib.ptr(g.tab), _lib.ptr(g.gtab), _lib.ptr(g.chunks), g.n_chunks,
-                                        _DTYPES[g.dtype], _lib.ptr(coef), float(group["lr"]), float(b1), float(b2),
-                                        float(group["eps"]), float(group["weight_decay"]), step, stream)
-            _lib.check(rc, "yat_adamw_step")
+                rc = lib.yat_adamw_ema_step(_lib.ptr(g.tab), _lib.ptr(g.gtab), _lib.ptr(g.chunks), g.n_chunks,
+                                            _DTYPES[g.dtype], _lib.ptr(coef), float(group["lr"]), float(b1), float(b2),
+                                            float(group["eps"]), float(group["weight_decay"]), step,
+                                            _lib.ptr(etab), float(omd), stream)
+            _lib.check(rc, "yat_adamw_ema_step")
+        if ema is not None:
+            done = {id(p) for _, g in sets for p in g.params}
+            rest = [(s, p) for s, p in zip(ema.shadow_params, ema._params()) if id(p) not in done]
+            for s, p in rest:
+                if not p.requires_grad:
+                    ema.copy_if_changed(s, p)                   # EMAModel.step: frozen tensors are copied
+                elif p.grad is None:
+                    raise ValueError("FusedClipAdamW: a trainable parameter tracked by the EMA received no gradient; "
+                                     "call EMAModel.step(parameters) instead of the fused path")
         return loss
 
-    def clip_and_step(self, max_norm=1.0):
-        """``accelerator.clip_grad_norm_(params, max_norm); optimizer.step()`` in two launches."""
-        return self.step(max_norm=max_norm)
+    def clip_and_step(self, max_norm=1.0, ema=None):
+        """``accelerator.clip_grad_norm_(params, max_norm); optimizer.step(); ema_model.step(params)`` in two launches."""
+        return self.step(max_norm=max_norm, ema=ema)

@@ -104,8 +104,17 @@ class TrainingParameters:
         self.use_repa = has("use_repa")
         self.latent_cache = str(y["latent_cache"]) if has("latent_cache") else None
         if has("gradient_checkpointing"):
-            v = y["gradient_checkpointing"]
-            self.gradient_checkpointing = "auto" if str(v).lower() == "auto" else bool(v)
+            # BaseLoader leaves every scalar a string: bool("false") would be True
+            v = str(y["gradient_checkpointing"]).strip().lower()
+            if v == "auto":
+                self.gradient_checkpointing = "auto"
+            elif v in ("1", "true", "yes", "on", ""):
+                self.gradient_checkpointing = True
+            elif v in ("0", "false", "no", "off", "never"):
+                self.gradient_checkpointing = False
+            else:
+                raise ValueError(f"gradient_checkpointing: {y['gradient_checkpointing']!r} is not one of "
+                                 "auto / true / false")
         self.repa_lambda = float(y["repa_lambda"]) if has("repa_lambda") else 0.05
         self.repa_pretrained_model = y.get("repa_pretrained_model")
         self.bucket_repeat = int(y["bucket_repeat"]) if has("bucket_repeat") else 1
