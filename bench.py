@@ -3,6 +3,10 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
+`--workload k3|k4|k5` runs another BASELINE config alone (same JSON schema); the default k2 line also carries a short
+run of each under `other_workloads`, and `account` = where the step's time goes (profiler pass: own / cuBLAS / cuDNN /
+ATen / NCCL kernel time per step, GPU-busy fraction).
+
 One "step" = one pass of the per-step training hot path over one bucket batch: pad/mask of the text
 embeddings, fused noising, SANA-1.6B forward (tcgen05 linear attention inside), fused loss, backward
 (gradient checkpointing only if the activations would not fit in HBM), DDP gradient all-reduce (N>1), grad-norm clip,
@@ -34,6 +38,54 @@ if ROOT not in sys.path:
 METRIC = "SANA-1.6B 1024px train img/s"
 UNIT = "img/s"
 WORKLOAD = "SANA-1.6B 1024px bf16 full finetune, 32x32x32 DC-AE latents, batch 16/GPU, text [16,512,2304]"
+# the product pads the text batch to its longest caption rounded up to 64 tokens (<= 320 with the synthetic
+# U{20..300} lengths) instead of always 512: masked keys weigh exactly 0, so the result is the reference's, but the
+# K/V projection and cross-attention work measured is that of the trimmed batch (config.text_padding says so)
+TEXT_PADDING = "trim64 (reference: fixed 512; masked keys weigh 0, tests/test_step_gpu.py::test_trimmed_text_padding_matches_fixed_512)"
+
+# BASELINE.json configs[1..4].  k2 is the metric's configuration (the bench line); k3 / k4 / k5 are the other
+# configs, timed briefly after the main run (`other_workloads`) or alone with --workload.
+WORKLOADS = {
+    "k2": {"workload": WORKLOAD, "batch": 16},
+    "k3": {"workload": "PixArt-Sigma XL 600M 1024px, 4-ch 128x128 latents, aspect-ratio buckets, bf16 (full finetune, batch 16/GPU, "
+                       "square bucket, text [16,300,4096])", "batch": 16},
+    "k4": {"workload": "SD3.5-medium MMDiT with logit-normal timestep weighting, LoRA rank 32, batch 8/GPU "
+                       "(16-ch 128x128 latents, text [8,333,4096])", "batch": 8},
+    "k5": {"workload": "SANA-1.6B with REPA alignment loss (DINOv2-shaped synthetic features) + use_preservation, LoKr rank 16 "
+                       "(batch 16/GPU, 32x32x32 latents)", "batch": 16},
+}
+
+
+def make_trainer(workload, batch, ckpt="auto", model=None):
+    """(trainer class, TrainingParameters) of a BASELINE config; scripts and tests build the same objects."""
+    from yat_b200.training_parameters_reader import TrainingParameters
+    p = TrainingParameters()
+    p.batch_size = batch
+    p.learning_rate = 1e-5
+    p.weight_decay = 0.0
+    p.gradient_checkpointing = {"auto": "auto", "on": True, "off": False}[ckpt]
+    if workload == "k2":
+        from train_sana import SanaModel as T
+        p.model_config = model or "sana_1600m_1024"
+    elif workload == "k3":
+        from train_pixart_sigma import PixartSigmaTrainer as T
+        p.model_config = model or "pixart_sigma_xl_1024"
+    elif workload == "k4":
+        from train_sd35 import SD35Trainer as T
+        p.model_config = model or "sd35_medium"
+        p.lora_rank, p.lora_alpha, p.lora_algo = 32, 32, "lora"
+        p.lora_target_modules = "to_q to_k to_v to_out.0 add_q_proj add_k_proj add_v_proj to_add_out"
+        p.learning_rate = 1e-4
+    elif workload == "k5":
+        from train_sana import SanaModel as T
+        p.model_config = model or "sana_1600m_1024"
+        p.use_repa, p.use_preservation, p.preservation_ratio = True, True, 0.5
+        p.lora_rank, p.lora_alpha, p.lora_algo = 16, 16, "lokr"
+        p.lora_target_modules = "to_q to_k to_v to_out.0 conv_inverted conv_point linear_1 linear_2 proj"  # README.md:78
+        p.learning_rate = 1e-4
+    else:
+        raise ValueError(workload)
+    return T, p
 
 
 def parse_args():
@@ -42,8 +94,12 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--model", default="sana_1600m_1024", help="debug only: sana_tiny runs the same code small")
-    ap.add_argument("--batch", type=int, default=16)
+    ap.add_argument("--model", default=None, help="debug only: sana_tiny runs the same code small")
+    ap.add_argument("--workload", default="k2", choices=sorted(WORKLOADS),
+                    help="k2 = the metric's configuration (default); k3 / k4 / k5 = the other BASELINE configs")
+    ap.add_argument("--batch", type=int, default=None)
+    ap.add_argument("--no-other-workloads", action="store_true", help="skip the short k3 / k4 / k5 runs after the k2 line")
+    ap.add_argument("--no-account", action="store_true", help="skip the profiler pass (GPU-busy / by-owner split)")
     ap.add_argument("--debug-linattn", default=None, choices=["simt"],
                     help="debug only: run linear attention on the CUDA-core restatement (flagged in config)")
     ap.add_argument("--ckpt", default="auto", choices=["auto", "on", "off"],
@@ -176,20 +232,27 @@ def cpu_reference_steps(model_name, images_per_step, steps, warmup, budget_s):
 
 def run_reference_arm(args):
     """`--impl reference`: the reference's CPU path = the oracle port (diffusers/accelerate are not
-    installed, so the upstream scripts cannot be imported).  Rank 0 only."""
+    installed, so the upstream scripts cannot be imported).  Rank 0 only.  `--warmup W` means
+    the same as in the own arm (W untimed steps first) but is capped at 1: a CPU step of this size takes ~10 s and
+    has no clock / cache state to settle; the cap is stated in the line (`warmup`, `warmup_cap`)."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
     import torch
-    r = cpu_reference_steps(args.model, 1, max(1, args.steps), max(0, min(args.warmup, 1)), budget_s=240.0)
+    if args.workload != "k2":
+        print(json.dumps({"impl": "reference", "unavailable": "the CPU reference arm exists for the k2 metric only"}), flush=True)
+        return
+    model = args.model or "sana_1600m_1024"
+    r = cpu_reference_steps(model, 1, max(1, args.steps), max(0, min(args.warmup, 1)), budget_s=240.0)
     line = {"impl": "reference", "metric": METRIC, "unit": UNIT, "n_gpus": args.gpus, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD if args.model == "sana_1600m_1024" else f"DEBUG {args.model}",
+            "config": {"workload": WORKLOAD if model == "sana_1600m_1024" else f"DEBUG {model}",
                        "global_batch": 16 * args.gpus, "parallelism": f"dp{args.gpus}",
+                       "text_padding": "fixed 512 (the reference's own padding, train_sana.py:167-179)",
                        "sample": "1 image per step on the host cores (bounded sample of the batch-16 workload)"}}
     if "unavailable" in r:
         line["unavailable"] = r["unavailable"]
     else:
-        line.update({"value": r["value"], "steps": r["steps"], "warmup": r["warmup"],
+        line.update({"value": r["value"], "steps": r["steps"], "warmup": r["warmup"], "warmup_cap": 1,
                      "ms_per_step": 1e3 * r["sec_per_step"],
                      "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
                                       "sample": r["sample"]},
@@ -203,13 +266,19 @@ def run_reference_arm(args):
 # ------------------------------------------------------------------------------------------------
 def _device_batch(trainer, batch, device):
     """Inputs of one step made resident in HBM ahead of the timed region: latents on the device and
-    the text embeddings already padded + masked (the optimize hook accepts that tuple)."""
+    the text embeddings already padded + masked (the optimize hooks accept that tuple)."""
     import torch
     from yat_b200.bucket_sampler import Batch
     b = Batch()
     b.ratio = batch.ratio
     b.vae_features = batch.vae_features.to(device, dtype=torch.bfloat16)
-    b.embeddings = trainer.pad_text(batch.embeddings)
+    if isinstance(batch.embeddings, tuple):                       # SD3.5: (joint text [B,333,4096], pooled [B,2048])
+        b.embeddings = tuple(t.to(device) for t in batch.embeddings)
+    elif hasattr(trainer, "pad_text"):
+        b.embeddings = trainer.pad_text(batch.embeddings)
+    else:
+        from yat_b200.embeddings import pad_embeddings
+        b.embeddings = pad_embeddings(batch.embeddings, trainer.max_text_tokens, device)
     b.repa_features = None if batch.repa_features is None else batch.repa_features.to(device)
     return b
 
@@ -217,7 +286,10 @@ def _device_batch(trainer, batch, device):
 def _batch_bytes(batch):
     n = batch.vae_features.numel() * batch.vae_features.element_size()
     n += sum(e.numel() * e.element_size() for e in batch.embeddings)
-    n += 4 * (len(batch.embeddings) + 1)     # int32 offsets
+    if not isinstance(batch.embeddings, tuple):
+        n += 4 * (len(batch.embeddings) + 1)     # int32 offsets
+    if batch.repa_features is not None:
+        n += batch.repa_features.numel() * batch.repa_features.element_size()
     return n
 
 
@@ -348,53 +420,106 @@ def _standalone_kernels(device, pk):
     return out
 
 
-def run_own_arm(args):
-    import torch
-    import torch.distributed as dist
-    from yat_b200 import _lib, build as _build
-    from train_sana import SanaModel
-    from yat_b200.training_parameters_reader import TrainingParameters
-
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device visible (yat_b200 has no CPU fallback)")
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    if rank == 0:
-        _build.build()
-    pk = peaks()
-    params = TrainingParameters()
-    params.batch_size = args.batch
-    params.model_config = args.model
-    params.learning_rate = 1e-5
-    params.weight_decay = 0.0
-    params.steps = args.steps
-    params.gradient_checkpointing = {"auto": "auto", "on": True, "off": False}[args.ckpt]
-    cwd = os.getcwd()
+def _build_trainer(workload, batch, ckpt, model, steps):
+    """Trainer of a BASELINE config, initialised in a scratch directory (initialize() creates ./models)."""
     import tempfile
+    T, params = make_trainer(workload, batch, ckpt, model)
+    params.steps = steps
+    cwd = os.getcwd()
     tmp = tempfile.mkdtemp(prefix="yat_bench_")
-    os.chdir(tmp)                      # initialize() creates ./models
+    os.chdir(tmp)
     try:
-        trainer = SanaModel(params)    # Accelerator inside: init_process_group(nccl) when WORLD_SIZE > 1
+        trainer = T(params)            # Accelerator inside: init_process_group(nccl) when WORLD_SIZE > 1
         trainer.initialize()
     finally:
         os.chdir(cwd)
+    return trainer
+
+
+OWNERS = (("own", ("yat::",)), ("nccl", ("nccl",)),
+          ("cublas", ("nvjet", "cublas", "gemm", "cutlass", "sm100_xmma", "sm90_xmma", "gemv", "splitK")),
+          ("cudnn", ("cudnn", "fmha", "flash", "sdpa")))
+
+
+def _owner(name):
+    low = name.lower()
+    for owner, keys in OWNERS:
+        if any(k.lower() in low for k in keys):
+            return owner
+    if low.startswith("memcpy") or low.startswith("memset"):
+        return "memcpy_memset"
+    return "aten"
+
+
+def _account(step_fn, n_steps, device, ms_per_step):
+    """Where one step's time goes: a torch.profiler (CUPTI) capture of `n_steps` resident steps.  Kernel
+    durations are summed by owner (own yat:: kernels / cuBLAS / cuDNN / ATen / NCCL / copies), `busy` is the union of
+    all device intervals over the span from the first to the last of them, `idle` the rest.  Durations under the
+    profiler are per-kernel device times (not cold-cache serialised like an ncu pass); launch gaps are slightly
+    wider than unprofiled, so `idle_frac_profiled` is an upper bound - `sum_ms_over_unprofiled_step` divides the same
+    kernel-time sum by the CUDA-event step time measured without the profiler."""
+    import torch
+    from torch.profiler import ProfilerActivity, profile
+    torch.cuda.synchronize(device)
+    with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+        for i in range(n_steps):
+            step_fn(i)
+        torch.cuda.synchronize(device)
+    iv, by_owner, by_name = [], {}, {}
+    for ev in prof.events():
+        if getattr(ev, "device_type", None) is None or "CUDA" not in str(ev.device_type).upper():
+            continue
+        t0, t1 = ev.time_range.start, ev.time_range.end
+        if t1 <= t0:
+            continue
+        iv.append((t0, t1))
+        dur = (t1 - t0) / 1e3 / n_steps                                  # ms per step
+        o = _owner(ev.name)
+        by_owner[o] = by_owner.get(o, 0.0) + dur
+        e = by_name.setdefault(ev.name[:96], [0.0, 0, o])
+        e[0] += dur
+        e[1] += 1
+    if not iv:
+        return {"unavailable": "the profiler returned no device events"}
+    iv.sort()
+    busy, cur0, cur1 = 0.0, iv[0][0], iv[0][1]
+    for t0, t1 in iv[1:]:
+        if t0 > cur1:
+            busy += cur1 - cur0
+            cur0, cur1 = t0, t1
+        else:
+            cur1 = max(cur1, t1)
+    busy += cur1 - cur0
+    span = iv[-1][1] - iv[0][0]
+    total = sum(by_owner.values())
+    top = sorted(by_name.items(), key=lambda kv: -kv[1][0])[:14]
+    return {"steps_profiled": n_steps, "launches_per_step": len(iv) / n_steps,
+            "span_ms_per_step": span / 1e3 / n_steps, "busy_ms_per_step": busy / 1e3 / n_steps,
+            "idle_frac_profiled": 1.0 - busy / span,
+            "sum_kernel_ms_per_step": total, "sum_ms_over_unprofiled_step": total / ms_per_step,
+            "by_owner_ms_per_step": {k: round(v, 3) for k, v in sorted(by_owner.items(), key=lambda kv: -kv[1])},
+            "by_owner_frac_of_kernel_time": {k: round(v / total, 4) for k, v in by_owner.items()},
+            "top_kernels": [{"name": n, "ms_per_step": round(v[0], 3), "launches_per_step": v[1] / n_steps,
+                             "owner": v[2]} for n, v in top]}
+
+
+def _measure(workload, args, steps, warmup, full):
+    """Timed resident steps (`value`) and timed plugin-call steps with host batches (`e2e`) of one workload.
+    `full` adds the in-situ kernel table (k2 line)."""
+    import torch
+    import torch.distributed as dist
+    from yat_b200 import _lib
+    batch = args.batch or WORKLOADS[workload]["batch"]
+    trainer = _build_trainer(workload, batch, args.ckpt, args.model if workload == args.workload else None, steps)
     device = trainer.accelerator.device
-    _lib.lib()
+    world = trainer.accelerator.num_processes
     if args.debug_linattn:
-        for proc in trainer.pipe.transformer.attn_processors.values():
+        for proc in getattr(trainer.pipe.transformer, "attn_processors", {}).values():
             if hasattr(proc, "impl"):
                 proc.impl = args.debug_linattn
     it = iter(trainer.sampler)
     host_batches = [next(it) for _ in range(4)]
     dev_batches = [_device_batch(trainer, b, device) for b in host_batches]
-    B = args.batch
-    cfg = trainer.pipe.transformer.config
-    chw = cfg.in_channels * cfg.sample_size * cfg.sample_size
-    N = (cfg.sample_size // cfg.patch_size) ** 2
-    C = cfg.num_attention_heads * cfg.attention_head_dim
-
-    n_params = sum(p.numel() for p in trainer.model.parameters() if p.requires_grad)
-
     losses = []
 
     def step_resident(i):
@@ -404,53 +529,113 @@ def run_own_arm(args):
         # the call a user makes: host Batch in pinned memory -> loss value back on the host
         losses.append(trainer.train_step(host_batches[i % len(host_batches)]).item())
 
-    # ---- warm-up (both paths), then `value`: K steps, inputs resident in HBM
-    for i in range(args.warmup):
+    for i in range(warmup):
         step_resident(i)
-    sink = []
+    sink = [] if full else None
     _lib.timing_sink = sink
     n0 = _lib.total_launches()
     with ClockSampler(trainer.accelerator.local_process_index) as clk:
-        ms_local = _timed_steps(step_resident, args.steps, dist, device)
+        ms_local = _timed_steps(step_resident, steps, dist, device)
     launches = _lib.total_launches() - n0
     _lib.timing_sink = None
     ms = _max_over_ranks(ms_local, dist, device)
-    value = world * B * args.steps / (ms * 1e-3)
+    for i in range(max(1, warmup // 2)):
+        step_e2e(i)
+    ms_e2e = _max_over_ranks(_timed_steps(step_e2e, steps, dist, device), dist, device)
+    res = {"trainer": trainer, "device": device, "world": world, "batch": batch, "ms": ms, "ms_local": ms_local,
+           "ms_e2e": ms_e2e, "launches": launches, "clocks": clk.summary(), "sink": sink, "losses": losses,
+           "h2d": _batch_bytes(host_batches[0]), "step_resident": step_resident,
+           "value": world * batch * steps / (ms * 1e-3), "e2e_value": world * batch * steps / (ms_e2e * 1e-3),
+           "mem_gib": torch.cuda.max_memory_allocated(device) / 2 ** 30}
+    return res
+
+
+def _other_workload(name, args):
+    """Short run of another BASELINE config after the k2 line (3 timed steps each way after 2 warm-ups)."""
+    import gc
+    import torch
+    try:
+        torch.cuda.reset_peak_memory_stats()
+        r = _measure(name, args, steps=3, warmup=2, full=False)
+        out = {"workload": WORKLOADS[name]["workload"], "batch": r["batch"], "steps": 3, "warmup": 2,
+               "ms_per_step": r["ms"] / 3, "value": r["value"], "unit": UNIT,
+               "e2e": {"value": r["e2e_value"], "ms_per_step": r["ms_e2e"] / 3, "h2d_bytes_per_step": r["h2d"],
+                       "d2h_bytes_per_step": 4},
+               "gpu_launches": r["launches"], "final_loss": float(r["losses"][-1]), "peak_mem_gib": round(r["mem_gib"], 1)}
+    except Exception as e:  # noqa: BLE001 — reported in the line, never hidden
+        out = {"workload": WORKLOADS[name]["workload"], "error": f"{type(e).__name__}: {str(e)[:300]}"}
+    r = None
+    gc.collect()
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_own_arm(args):
+    import gc
+    import torch
+    import torch.distributed as dist
+    from yat_b200 import _lib, build as _build
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device visible (yat_b200 has no CPU fallback)")
+    rank = int(os.environ.get("RANK", "0"))
+    if rank == 0:
+        _build.build()
+    pk = peaks()
+    _lib.lib()
+    wl = args.workload
+    r = _measure(wl, args, args.steps, args.warmup, full=True)
+    trainer, device, world, B = r["trainer"], r["device"], r["world"], r["batch"]
+    ms, ms_local, ms_e2e = r["ms"], r["ms_local"], r["ms_e2e"]
+    cfg = trainer.pipe.transformer.config
+    n_params = sum(p.numel() for p in trainer.model.parameters() if p.requires_grad)
 
     # ---- in-situ kernel durations from the events recorded inside the timed region
-    insitu = {}
-    for name, e0, e1 in sink:
-        insitu.setdefault(name, []).append(e0.elapsed_time(e1))
     kernels = {}
-    step_ms = ms_local / args.steps
-    for name, ts in insitu.items():
-        nbytes = _algo_bytes(name, B, chw, N, C, n_params)
-        avg = statistics.mean(ts)
-        k = {"timing": "in-situ", "launches_per_step": len(ts) / args.steps, "us": avg * 1e3,
-             "share_of_step": (sum(ts) / args.steps) / step_ms}
-        if nbytes:
-            k.update({"bound": "hbm", "achieved": nbytes / (avg * 1e-3) / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                      "bytes": nbytes})
-            k["frac"] = k["achieved"] / k["peak"]
-        kernels[name] = k
+    if wl == "k2":
+        chw = cfg.in_channels * cfg.sample_size * cfg.sample_size
+        N = (cfg.sample_size // cfg.patch_size) ** 2
+        C = cfg.num_attention_heads * cfg.attention_head_dim
+        insitu = {}
+        for name, e0, e1 in r["sink"]:
+            insitu.setdefault(name, []).append(e0.elapsed_time(e1))
+        step_ms = ms_local / args.steps
+        for name, ts in insitu.items():
+            nbytes = _algo_bytes(name, B, chw, N, C, n_params)
+            avg = statistics.mean(ts)
+            k = {"timing": "in-situ", "launches_per_step": len(ts) / args.steps, "us": avg * 1e3,
+                 "share_of_step": (sum(ts) / args.steps) / step_ms}
+            if nbytes:
+                k.update({"bound": "hbm", "achieved": nbytes / (avg * 1e-3) / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                          "bytes": nbytes})
+                k["frac"] = k["achieved"] / k["peak"]
+            kernels[name] = k
 
-    # ---- e2e: same K steps through the plugin call with host buffers
-    for i in range(max(1, args.warmup // 2)):
-        step_e2e(i)
-    ms_e2e = _max_over_ranks(_timed_steps(step_e2e, args.steps, dist, device), dist, device)
-    e2e_value = world * B * args.steps / (ms_e2e * 1e-3)
-    h2d = _batch_bytes(host_batches[0])
-
+    # ---- where the step's time goes (profiler pass, not timed)
+    account = None
+    if not args.no_account:            # every rank runs the profiled steps (they contain the DDP all-reduce); rank 0 reports
+        try:
+            account = _account(r["step_resident"], 2, device, ms / args.steps)
+        except Exception as e:  # noqa: BLE001
+            account = {"unavailable": f"{type(e).__name__}: {str(e)[:200]}"}
+    if dist.is_initialized():
+        dist.barrier()
+    final_loss = float(r["losses"][-1]) if r["losses"] else None
+    ckpt_on = bool(getattr(trainer.pipe.transformer, "gradient_checkpointing", False))
+    clocks, launches, h2d = r["clocks"], r["launches"], r["h2d"]
+    value, e2e_value = r["value"], r["e2e_value"]
     if rank != 0:
         return
-    # ---- rank 0 extras: stand-alone kernel roofline, CPU baseline
+    # ---- rank 0 extras: stand-alone kernel roofline, CPU baseline, the other BASELINE configs
+    r = trainer = None
+    gc.collect()
+    torch.cuda.empty_cache()
     standalone = {}
-    try:
-        del dev_batches
-        torch.cuda.empty_cache()
-        standalone = _standalone_kernels(device, pk)
-    except Exception as e:  # noqa: BLE001
-        standalone = {"error": str(e)[:300]}
+    if wl == "k2":
+        try:
+            standalone = _standalone_kernels(device, pk)
+        except Exception as e:  # noqa: BLE001
+            standalone = {"error": str(e)[:300]}
     dominant = max((n for n in kernels if "frac" in kernels[n]), key=lambda n: kernels[n]["share_of_step"], default=None)
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
@@ -465,31 +650,38 @@ def run_own_arm(args):
                     "timing": "in-situ CUDA events over the timed region", "us": d["us"],
                     "standalone": standalone.get(dominant)}
     cpu = None
-    if world == 1 and not args.no_cpu_baseline:
+    if world == 1 and wl == "k2" and not args.no_cpu_baseline:
         try:
-            r = cpu_reference_steps(args.model, 1, 2, 0, budget_s=args.cpu_budget_s)
-            cpu = ({"unavailable": r["unavailable"]} if "unavailable" in r else
-                   {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"],
-                    "sec_per_step": r["sec_per_step"]})
+            c = cpu_reference_steps(args.model or "sana_1600m_1024", 1, 2, 0, budget_s=args.cpu_budget_s)
+            cpu = ({"unavailable": c["unavailable"]} if "unavailable" in c else
+                   {"value": c["value"], "unit": UNIT, "cores": c["cores"], "kind": "port", "sample": c["sample"],
+                    "sec_per_step": c["sec_per_step"]})
         except Exception as e:  # noqa: BLE001
             cpu = {"unavailable": str(e)[:300]}
+    others = None
+    if world == 1 and wl == "k2" and not args.no_other_workloads and not args.model:
+        others = {name: _other_workload(name, args) for name in ("k3", "k4", "k5")}
+    debug = (f"DEBUG {args.model} " if args.model else "") + (f"DEBUG linattn={args.debug_linattn}" if args.debug_linattn else "")
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "metric": METRIC if wl == "k2" else f"{wl} train img/s", "value": value, "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": (WORKLOAD if args.model == "sana_1600m_1024" else f"DEBUG {args.model}")
-                   + (f" DEBUG linattn={args.debug_linattn}" if args.debug_linattn else ""),
+        "config": {"workload": (debug + WORKLOADS[wl]["workload"]).strip(),
                    "global_batch": world * B, "parallelism": f"dp{world}", "optimizer": "AdamW bf16, clip + update as 2 own kernels",
-                   "gradient_checkpointing": bool(trainer.pipe.transformer.gradient_checkpointing),
+                   "text_padding": TEXT_PADDING if wl in ("k2", "k5") else "fixed (hook default)",
+                   "gradient_checkpointing": ckpt_on,
                    "l2": "no explicit flush: one step streams ~3.2 GB of weights + >10 GB of activations (>> 126 MB L2)"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches,
-        "clocks": clk.summary(),
+        "clocks": clocks,
         "roofline": roofline,
+        "account": account,
         "kernels": {"in_situ": kernels, "standalone": standalone},
         "cpu_baseline": cpu,
-        "final_loss": float(losses[-1]) if losses else None,
+        "other_workloads": others,
+        "final_loss": final_loss,
         "torch": torch.__version__,
     }
     print(json.dumps(line), flush=True)

@@ -157,6 +157,16 @@ int yat_ln_modulate_fwd(const void* x, const void* scale, const void* shift, int
 int yat_ln_modulate_bwd(const void* x, const void* dy, const void* scale, int64_t mod_batch_stride,
                         const float* mean, const float* rstd, int B, int N, int C,
                         void* dx, void* dscale, void* dshift, void* workspace, void* stream);
+/* the same two ops with the neighbouring residual arithmetic folded in:
+ *   yat_add_ln_modulate_fwd  xsum = bf16(x + x2) (the attn2 residual add, :103), y = ln_modulate(xsum): one pass
+ *   yat_ln_modulate_bwd_res  dx = dres + d ln_modulate / dx: the gradient that reaches the same tensor through the
+ *                            residual branch is added in the same pass (dres may be NULL)                        */
+int yat_add_ln_modulate_fwd(const void* x, const void* x2, const void* scale, const void* shift,
+                            int64_t mod_batch_stride, int B, int N, int C, float eps, void* xsum, void* y,
+                            float* mean, float* rstd, void* stream);
+int yat_ln_modulate_bwd_res(const void* x, const void* dy, const void* dres, const void* scale,
+                            int64_t mod_batch_stride, const float* mean, const float* rstd, int B, int N, int C,
+                            void* dx, void* dscale, void* dshift, void* workspace, void* stream);
 int yat_gate_residual_fwd(const void* res, const void* y, const void* gate, int64_t mod_batch_stride,
                           int B, int N, int C, void* out, void* stream);
 int yat_gate_residual_bwd(const void* dout, const void* y, const void* gate, int64_t mod_batch_stride,

@@ -167,3 +167,48 @@ def test_colsum_and_linear_bias_gradient(cuda, rows, C):
     assert _rel(lin.bias.grad, exact) <= _rel(ref.bias.grad, exact) + 3e-3
     with pytest.raises(ValueError):
         colsum(a.cpu())
+
+
+@pytest.mark.parametrize("B,N,C", [(2, 256, 128), (16, 1024, 2240), (3, 100, 2240), (2, 33, 4096)])
+@pytest.mark.parametrize("with_add", [False, True])
+def test_ln_modulate_res_folds_the_residual_arithmetic(cuda, B, N, C, with_add):
+    """ln_modulate_res (yat_add_ln_modulate_fwd / yat_ln_modulate_bwd_res): h = x [+ x2] rounded to bf16 like the
+    reference's tensor add (utils/patch_sana_attention_layers.py:103), y = ln_modulate(h); the gradients reaching h
+    through the normalised branch and through the residual branch are combined inside the backward kernel.
+    Checked against fp64 torch for the same graph; h is bit-identical to torch's bf16 add."""
+    from yat_b200.block_ops import ln_modulate, ln_modulate_res
+    x, x2, mod, dy = _inputs(B, N, C, 7, cuda)
+    g = torch.Generator().manual_seed(9)
+    dh = torch.randn((B, N, C), generator=g).to(torch.bfloat16).to(cuda)
+    xg, ag = x.clone().requires_grad_(True), x2.clone().requires_grad_(True)
+    modg = mod.clone().requires_grad_(True)
+    sh, sc = modg.chunk(6, dim=1)[0], modg.chunk(6, dim=1)[1]
+    y, h = ln_modulate_res(xg, sc, sh, 1e-6, add=ag if with_add else None)
+    torch.autograd.backward([y, h], [dy, dh])
+    h_ref_bf16 = (x + x2) if with_add else x
+    assert torch.equal(h.detach(), h_ref_bf16)
+    # the normalised branch equals the stand-alone op on the same (rounded) h, bit for bit
+    assert torch.equal(y.detach(), ln_modulate(h_ref_bf16, mod.chunk(6, dim=1)[1], mod.chunk(6, dim=1)[0], 1e-6))
+    # fp64 reference of the same graph (the rounding of h is part of the function: straight-through for the add)
+    hr = h_ref_bf16.double().requires_grad_(True)
+    modr = mod.double().requires_grad_(True)
+    yr = _ref_ln_modulate(hr, modr.chunk(6, dim=1)[1], modr.chunk(6, dim=1)[0], 1e-6)
+    torch.autograd.backward([yr, hr * 1.0], [dy.double(), dh.double()])
+    assert _rel(xg.grad, hr.grad) < 5e-3
+    if with_add:
+        assert torch.equal(ag.grad, xg.grad)
+    else:
+        assert ag.grad is None
+    assert _rel(modg.grad[:, :2], modr.grad[:, :2]) < 5e-3
+    # one rounding instead of autograd's two (round dx_ln, then add dres in bf16): at least as close to fp64
+    x3 = h_ref_bf16.clone().requires_grad_(True)
+    y3 = ln_modulate(x3, mod.chunk(6, dim=1)[1], mod.chunk(6, dim=1)[0], 1e-6)
+    torch.autograd.backward([y3, x3 * 1.0], [dy, dh])
+    assert _rel(xg.grad, hr.grad) <= _rel(x3.grad, hr.grad) * 1.02
+    # only one of the two outputs used downstream
+    xg2 = x.clone().requires_grad_(True)
+    y2, h2 = ln_modulate_res(xg2, mod.chunk(6, dim=1)[1], mod.chunk(6, dim=1)[0], 1e-6)
+    y2.backward(dy)
+    x4 = x.clone().requires_grad_(True)
+    ln_modulate(x4, mod.chunk(6, dim=1)[1], mod.chunk(6, dim=1)[0], 1e-6).backward(dy)
+    assert torch.equal(xg2.grad, x4.grad)

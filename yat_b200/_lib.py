@@ -39,6 +39,10 @@ SIGNATURES = {
                                     c_void_p, c_void_p, c_void_p]),
     "yat_ln_modulate_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_int, c_int,
                                     c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "yat_add_ln_modulate_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_float,
+                                        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "yat_ln_modulate_bwd_res": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int,
+                                        c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "yat_gate_residual_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p]),
     "yat_gate_residual_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p,
                                       c_void_p, c_void_p]),
@@ -73,7 +77,8 @@ _lib = None
 # sum over its timed region as `gpu_launches`).
 LAUNCHING = ("yat_noise_flowmatch", "yat_noise_ddpm", "yat_loss_fused", "yat_repa_cos", "yat_linattn_fwd",
              "yat_linattn_bwd", "yat_linattn_fwd_simt", "yat_linattn_bwd_simt", "yat_pad_embeddings",
-             "yat_philox_raw", "yat_ln_modulate_fwd", "yat_ln_modulate_bwd", "yat_gate_residual_fwd",
+             "yat_philox_raw", "yat_ln_modulate_fwd", "yat_ln_modulate_bwd", "yat_add_ln_modulate_fwd",
+             "yat_ln_modulate_bwd_res", "yat_gate_residual_fwd",
              "yat_gate_residual_bwd", "yat_glumb_mid_fwd", "yat_glumb_mid_bwd", "yat_grad_clip_coef",
              "yat_adamw_step", "yat_adamw_ema_step", "yat_ema_step", "yat_colsum_bf16", "yat_head_pad", "yat_head_unpad",
              "yat_linattn_fwd_ld", "yat_linattn_bwd_ld")

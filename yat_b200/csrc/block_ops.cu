@@ -33,11 +33,14 @@ __device__ __forceinline__ uint4 ld_cached(const void* p) { return __ldg(reinter
 // ------------------------------------------------------------------------------------------------
 // ln_modulate forward: one warp per token row, the row lives in registers (MAXV 128-bit vectors per lane)
 // ------------------------------------------------------------------------------------------------
-template <int MAXV>
+// ADD: the row is first formed as bf16(x + x2) (the attn2 residual add `attn_output + hidden_states`,
+// utils/patch_sana_attention_layers.py:103, rounded to bf16 like the reference's tensor add), written to xsum, and
+// normalised from the rounded values: one pass (8 C bytes per token) instead of an add pass plus a norm pass (10 C).
+template <int MAXV, bool ADD>
 __global__ void __launch_bounds__(kThreads) ln_modulate_fwd_kernel(
-    const uint4* __restrict__ x, const uint4* __restrict__ scale, const uint4* __restrict__ shift,
-    int64_t mod_stride_vec, int rows, int N, int nvec, float inv_c, float eps, uint4* __restrict__ y,
-    float* __restrict__ mean_out, float* __restrict__ rstd_out) {
+    const uint4* __restrict__ x, const uint4* __restrict__ x2, const uint4* __restrict__ scale,
+    const uint4* __restrict__ shift, int64_t mod_stride_vec, int rows, int N, int nvec, float inv_c, float eps,
+    uint4* __restrict__ xsum, uint4* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out) {
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
   if (row >= rows) return;
@@ -48,6 +51,27 @@ __global__ void __launch_bounds__(kThreads) ln_modulate_fwd_kernel(
   for (int i = 0; i < MAXV; ++i) {
     const int c = lane + 32 * i;
     if (c < nvec) v[i] = ld_stream(xr + c);
+  }
+  if (ADD) {
+    const uint4* ar = x2 + (int64_t)row * nvec;
+    uint4* sr = xsum + (int64_t)row * nvec;
+    uint4 a[MAXV];
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nvec) a[i] = ld_stream(ar + c);
+    }
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nvec) {
+        v[i].x = pack2(add2(unpack2(v[i].x), unpack2(a[i].x)));
+        v[i].y = pack2(add2(unpack2(v[i].y), unpack2(a[i].y)));
+        v[i].z = pack2(add2(unpack2(v[i].z), unpack2(a[i].z)));
+        v[i].w = pack2(add2(unpack2(v[i].w), unpack2(a[i].w)));
+        sr[c] = v[i];                                   // re-read by the residual path: default caching
+      }
+    }
   }
   // packed fp32 pairs (FFMA2): the row statistics and the modulate take half the issue slots of the scalar form
   f2 s2 = bc2(0.f);
@@ -101,196 +125,6 @@ __global__ void __launch_bounds__(kThreads) ln_modulate_fwd_kernel(
   }
 }
 
-// ln_modulate backward, row part: dx = rstd * (g - mean(g) - xhat * mean(g * xhat)),  g = dy * (1 + scale)
-template <int MAXV>
-__global__ void __launch_bounds__(kThreads) ln_modulate_bwd_dx_kernel(
-    const uint4* __restrict__ x, const uint4* __restrict__ dy, const uint4* __restrict__ scale,
-    int64_t mod_stride_vec, const float* __restrict__ mean_in, const float* __restrict__ rstd_in, int rows, int N,
-    int nvec, float inv_c, uint4* __restrict__ dx) {
-  const int lane = threadIdx.x & 31;
-  const int row = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-  if (row >= rows) return;
-  const int b = row / N;
-  const uint4* xr = x + (int64_t)row * nvec;
-  const uint4* gr = dy + (int64_t)row * nvec;
-  const uint4* sc = scale + (int64_t)b * mod_stride_vec;
-  const float mean = mean_in[row], rstd = rstd_in[row];
-  uint4 xv[MAXV], gv[MAXV];
-#pragma unroll
-  for (int i = 0; i < MAXV; ++i) {
-    const int c = lane + 32 * i;
-    if (c < nvec) {
-      xv[i] = ld_stream(xr + c);
-      gv[i] = ld_stream(gr + c);
-    }
-  }
-  // pass 1: g (kept packed as bf16x2-free fp32 is too register hungry: recompute in pass 2), the two row means
-  float s1 = 0.f, s2 = 0.f;
-#pragma unroll
-  for (int i = 0; i < MAXV; ++i) {
-    const int c = lane + 32 * i;
-    if (c < nvec) {
-      float f[8], g[8], a[8];
-      unpack8(xv[i], f);
-      unpack8(gv[i], g);
-      unpack8(ld_cached(sc + c), a);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float gg = g[j] * (1.0f + a[j]);
-        s1 += gg;
-        s2 = fmaf(gg, (f[j] - mean) * rstd, s2);
-      }
-    }
-  }
-  const float c1 = warp_sum(s1) * inv_c, c2 = warp_sum(s2) * inv_c;
-  uint4* dr = dx + (int64_t)row * nvec;
-#pragma unroll
-  for (int i = 0; i < MAXV; ++i) {
-    const int c = lane + 32 * i;
-    if (c < nvec) {
-      float f[8], g[8], a[8], o[8];
-      unpack8(xv[i], f);
-      unpack8(gv[i], g);
-      unpack8(ld_cached(sc + c), a);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float xh = (f[j] - mean) * rstd;
-        o[j] = rstd * (g[j] * (1.0f + a[j]) - c1 - xh * c2);
-      }
-      st_stream(dr + c, pack8(o));
-    }
-  }
-}
-
-// ------------------------------------------------------------------------------------------------
-// ln_modulate backward, ONE pass: dx (row part, as above) and the per-sample column sums
-//   dscale[b][c] = sum_n dy * xhat      dshift[b][c] = sum_n dy
-// from the same registers, so x and dy are read once (6·C B per token instead of 10·C).  CTA = (row split, sample),
-// 8 warps = 4 warp pairs, one row per pair at a time: the two warps of a pair own alternate 32-vector blocks of the
-// row (x and dy of their half live in registers, 2 * MAXH 128-bit loads in flight per lane) and exchange their two
-// partial row sums through shared memory with a 64-thread named barrier (slots alternate by row, so one barrier per
-// row).  Every pair owns a private fp32 accumulator image of the two [C] rows in shared memory, laid out as planes of
-// 16 bytes per 8-column vector so that lane-contiguous accesses are conflict-free, and touched only by the lane that
-// owns the vector.  Arithmetic on packed fp32 pairs (FFMA2).  Pairs are added in fixed order, splits by
-// column_finish_kernel -> bit-identical run to run.
-// ------------------------------------------------------------------------------------------------
-constexpr int kLnBwdPairs = 4;
-constexpr int kLnBwdThreads = kLnBwdPairs * 64;
-
-template <int MAXH>
-__global__ void __launch_bounds__(kLnBwdThreads, MAXH <= 5 ? 3 : 1) ln_modulate_bwd_fused_kernel(
-    const uint4* __restrict__ x, const uint4* __restrict__ dy, const uint4* __restrict__ scale,
-    int64_t mod_stride_vec, const float* __restrict__ mean_in, const float* __restrict__ rstd_in, int N, int nvec,
-    int rows_per_split, float inv_c, uint4* __restrict__ dx, float* __restrict__ part0, float* __restrict__ part1) {
-  extern __shared__ __align__(16) ulonglong2 acc_smem[];          // [pair][kind: dscale, dshift][plane][nvec] x 4 floats
-  __shared__ float xchg[kLnBwdPairs][2][2][2];                    // [pair][row parity][half][s1, s2]
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int pair = warp >> 1, half = warp & 1;
-  const int split = blockIdx.x, b = blockIdx.y;
-  ulonglong2* acc = acc_smem + (size_t)pair * 4 * nvec;
-  for (int i = (half * 32 + lane); i < 4 * nvec; i += 64) acc[i] = make_ulonglong2(0ull, 0ull);   // fp32 +0.0 pairs
-  asm volatile("bar.sync %0, 64;" ::"r"(pair + 1) : "memory");
-  const int r0 = split * rows_per_split;
-  const int r1 = min(N, r0 + rows_per_split);
-  const uint4* sc = scale + (int64_t)b * mod_stride_vec;
-  const f2 one = bc2(1.0f);
-  int parity = 0;
-  for (int r = r0 + pair; r < r1; r += kLnBwdPairs, parity ^= 1) {
-    const int64_t row = (int64_t)b * N + r;
-    const uint4* xr = x + row * nvec;
-    const uint4* gr = dy + row * nvec;
-    if (lane == 0 && r + 2 * kLnBwdPairs < r1) {                   // pull the pair's row after next into L2: no registers held
-      const uint4* nxt = (half ? gr : xr) + (int64_t)2 * kLnBwdPairs * nvec;
-      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nxt), "r"(nvec * 16) : "memory");
-    }
-    uint4 xv[MAXH], gv[MAXH];
-#pragma unroll
-    for (int i = 0; i < MAXH; ++i) {
-      const int c = (2 * i + half) * 32 + lane;
-      if (c < nvec) {
-        xv[i] = ld_stream(xr + c);
-        gv[i] = ld_stream(gr + c);
-      }
-    }
-    const float mean = mean_in[row], rstd = rstd_in[row];
-    const f2 rs = bc2(rstd), nmr = bc2(-mean * rstd);              // xhat = x * rstd - mean * rstd
-    f2 s1 = bc2(0.f), s2 = bc2(0.f);
-#pragma unroll
-    for (int i = 0; i < MAXH; ++i) {
-      const int c = (2 * i + half) * 32 + lane;
-      if (c < nvec) {
-        const uint4 av = ld_cached(sc + c);
-        const uint32_t xw[4] = {xv[i].x, xv[i].y, xv[i].z, xv[i].w}, gw[4] = {gv[i].x, gv[i].y, gv[i].z, gv[i].w},
-                       aw[4] = {av.x, av.y, av.z, av.w};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const f2 gg = mul2(unpack2(gw[j]), add2(unpack2(aw[j]), one));
-          s1 = add2(s1, gg);
-          s2 = fma2(gg, fma2(unpack2(xw[j]), rs, nmr), s2);
-        }
-      }
-    }
-    float s1a, s1b, s2a, s2b;
-    un2(s1, s1a, s1b);
-    un2(s2, s2a, s2b);
-    const float h1 = warp_sum(s1a + s1b), h2 = warp_sum(s2a + s2b);
-    if (lane == 0) {
-      xchg[pair][parity][half][0] = h1;
-      xchg[pair][parity][half][1] = h2;
-    }
-    asm volatile("bar.sync %0, 64;" ::"r"(pair + 1) : "memory");
-    const float c1 = (xchg[pair][parity][0][0] + xchg[pair][parity][1][0]) * inv_c;
-    const float c2 = (xchg[pair][parity][0][1] + xchg[pair][parity][1][1]) * inv_c;
-    const f2 nc1r = bc2(-c1 * rstd), nc2r = bc2(-c2 * rstd);       // dx = gg * rstd - c1 * rstd - xhat * c2 * rstd
-    uint4* dr = dx + row * nvec;
-#pragma unroll
-    for (int i = 0; i < MAXH; ++i) {
-      const int c = (2 * i + half) * 32 + lane;
-      if (c < nvec) {
-        const uint4 av = ld_cached(sc + c);
-        const uint32_t xw[4] = {xv[i].x, xv[i].y, xv[i].z, xv[i].w}, gw[4] = {gv[i].x, gv[i].y, gv[i].z, gv[i].w},
-                       aw[4] = {av.x, av.y, av.z, av.w};
-        uint32_t ow[4];
-        f2 dsc[4], dsh[4];
-        {
-          const ulonglong2 t0 = acc[0 * nvec + c], t1 = acc[1 * nvec + c], t2 = acc[2 * nvec + c], t3 = acc[3 * nvec + c];
-          dsc[0].v = t0.x; dsc[1].v = t0.y; dsc[2].v = t1.x; dsc[3].v = t1.y;
-          dsh[0].v = t2.x; dsh[1].v = t2.y; dsh[2].v = t3.x; dsh[3].v = t3.y;
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const f2 g = unpack2(gw[j]);
-          const f2 xh = fma2(unpack2(xw[j]), rs, nmr);
-          const f2 gg = mul2(g, add2(unpack2(aw[j]), one));
-          ow[j] = pack2(fma2(xh, nc2r, fma2(gg, rs, nc1r)));
-          dsc[j] = fma2(g, xh, dsc[j]);
-          dsh[j] = add2(dsh[j], g);
-        }
-        st_stream(dr + c, make_uint4(ow[0], ow[1], ow[2], ow[3]));
-        acc[0 * nvec + c] = make_ulonglong2(dsc[0].v, dsc[1].v);
-        acc[1 * nvec + c] = make_ulonglong2(dsc[2].v, dsc[3].v);
-        acc[2 * nvec + c] = make_ulonglong2(dsh[0].v, dsh[1].v);
-        acc[3 * nvec + c] = make_ulonglong2(dsh[2].v, dsh[3].v);
-      }
-    }
-  }
-  __syncthreads();
-  const float* af = reinterpret_cast<const float*>(acc_smem);
-  const int C = nvec * 8;
-  for (int col = threadIdx.x; col < C; col += kLnBwdThreads) {
-    const int c = col >> 3, plane = (col >> 2) & 1, j = col & 3;
-    float t0 = 0.f, t1 = 0.f;
-#pragma unroll
-    for (int w = 0; w < kLnBwdPairs; ++w) {
-      t0 += af[(((size_t)w * 4 + plane) * nvec + c) * 4 + j];
-      t1 += af[(((size_t)w * 4 + 2 + plane) * nvec + c) * 4 + j];
-    }
-    const int64_t o = ((int64_t)split * gridDim.y + b) * C + col;
-    part0[o] = t0;
-    part1[o] = t1;
-  }
-}
-
 // ------------------------------------------------------------------------------------------------
 // ln_modulate backward, column-ownership form (the one launched): a thread owns ONE 8-column vector for the whole CTA
 // = (row split, sample), so (1 + scale) is unpacked once into registers and the dscale / dshift column sums are plain
@@ -303,11 +137,14 @@ __global__ void __launch_bounds__(kLnBwdThreads, MAXH <= 5 ? 3 : 1) ln_modulate_
 constexpr int kLnRows = 4;
 constexpr int kLnMaxWarps = 16;   // C <= 4096 -> nvec <= 512 threads
 
-template <int MAXT, int MINB>
-__global__ void __launch_bounds__(MAXT, MINB) ln_modulate_bwd_cols_kernel(
+template <int MAXREG>
+__global__ void __maxnreg__(MAXREG) ln_modulate_bwd_cols_kernel(
     const uint4* __restrict__ x, const uint4* __restrict__ dy, const uint4* __restrict__ scale,
     int64_t mod_stride_vec, const float* __restrict__ mean_in, const float* __restrict__ rstd_in, int N, int nvec,
-    int rows_per_split, float inv_c, uint4* __restrict__ dx, float* __restrict__ part0, float* __restrict__ part1) {
+    int rows_per_split, float inv_c, const uint4* __restrict__ dres, uint4* __restrict__ dx,
+    float* __restrict__ part0, float* __restrict__ part1) {
+  // dres (may be null): gradient arriving on the residual branch of the same tensor; dx = dres + dx_ln is formed in
+  // fp32 and rounded once (autograd would round dx_ln, then add in bf16 in a separate 6 C-byte pass)
   __shared__ float red[2][kLnMaxWarps][2 * kLnRows];
   const int c = threadIdx.x, lane = c & 31, warp = c >> 5, nwarps = (blockDim.x + 31) >> 5;
   const int split = blockIdx.x, b = blockIdx.y;
@@ -338,6 +175,7 @@ __global__ void __launch_bounds__(MAXT, MINB) ln_modulate_bwd_cols_kernel(
       gv[k] = ok ? ld_stream(dy + row * nvec + c) : make_uint4(0u, 0u, 0u, 0u);
       rs[k] = rstd_in[row];
       nmr[k] = -mean_in[row] * rs[k];
+      if (dres != nullptr && ok) asm volatile("prefetch.global.L2 [%0];" ::"l"(dres + row * nvec + c));
     }
     float v[2 * kLnRows];                                   // [k] = sum g, [kLnRows + k] = sum g * xhat
 #pragma unroll
@@ -396,12 +234,15 @@ __global__ void __launch_bounds__(MAXT, MINB) ln_modulate_bwd_cols_kernel(
       const uint32_t xw[4] = {xv[k].x, xv[k].y, xv[k].z, xv[k].w}, gw[4] = {gv[k].x, gv[k].y, gv[k].z, gv[k].w};
       const f2 rsk = bc2(rs[k]), nmk = bc2(nmr[k]);
       const f2 nc1r = bc2(-tot[k] * inv_c * rs[k]), nc2r = bc2(-tot[kLnRows + k] * inv_c * rs[k]);
+      uint4 rv = make_uint4(0u, 0u, 0u, 0u);                 // bf16 zeros: adding them leaves dx_ln unchanged
+      if (dres != nullptr) rv = ld_stream(dres + row * nvec + c);
+      const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
       uint32_t ow[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const f2 g = unpack2(gw[j]);
         const f2 xh = fma2(unpack2(xw[j]), rsk, nmk);
-        ow[j] = pack2(fma2(xh, nc2r, fma2(mul2(g, a1[j]), rsk, nc1r)));
+        ow[j] = pack2(add2(fma2(xh, nc2r, fma2(mul2(g, a1[j]), rsk, nc1r)), unpack2(rw[j])));
         dsc[j] = fma2(g, xh, dsc[j]);
         dsh[j] = add2(dsh[j], g);
       }
@@ -607,13 +448,11 @@ inline int split_count(int N) {  // rows per split >= 64, at most 16 splits
   return s < 1 ? 1 : (s > 16 ? 16 : s);
 }
 
-// fused ln_modulate backward: one wave of CTAs (B * splits <= SMs * resident CTAs), at least one row per warp pair
-inline int ln_bwd_smem(int C) { return kLnBwdPairs * 2 * C * (int)sizeof(float); }
+// ln_modulate backward: upper bound of the row splits per sample (sizes the partial-sum workspace)
 inline int ln_bwd_splits(int B, int N, int C) {
-  int per_sm = (227 * 1024) / (ln_bwd_smem(C) + 1024);
-  per_sm = per_sm < 1 ? 1 : (per_sm > 3 ? 3 : per_sm);
-  int s = (kNumSMs * per_sm) / B;
-  const int cap = (N + kLnBwdPairs - 1) / kLnBwdPairs;
+  (void)C;
+  int s = (kNumSMs * 3) / B;
+  const int cap = (N + 3) / 4;
   if (s > cap) s = cap;
   return s < 1 ? 1 : s;
 }
@@ -667,8 +506,17 @@ extern "C" int64_t yat_block_workspace_bytes(int B, int N, int C) {
 
 extern "C" int yat_ln_modulate_fwd(const void* x, const void* scale, const void* shift, int64_t mod_batch_stride,
                                    int B, int N, int C, float eps, void* y, float* mean, float* rstd, void* stream) {
+  return yat_add_ln_modulate_fwd(x, nullptr, scale, shift, mod_batch_stride, B, N, C, eps, nullptr, y, mean, rstd, stream);
+}
+
+extern "C" int yat_add_ln_modulate_fwd(const void* x, const void* x2, const void* scale, const void* shift,
+                                       int64_t mod_batch_stride, int B, int N, int C, float eps, void* xsum, void* y,
+                                       float* mean, float* rstd, void* stream) {
   using namespace yat;
   YAT_REQUIRE(x && scale && shift && y, YAT_ERR_BAD_ARG, "yat_ln_modulate_fwd: null pointer argument");
+  YAT_REQUIRE((x2 == nullptr) == (xsum == nullptr), YAT_ERR_BAD_ARG, "yat_add_ln_modulate_fwd: x2 and xsum go together");
+  YAT_REQUIRE(!x2 || (aligned16(x2) && aligned16(xsum)), YAT_ERR_BAD_ARG,
+              "yat_add_ln_modulate_fwd: tensors must be 16-byte aligned");
   YAT_REQUIRE((mean == nullptr) == (rstd == nullptr), YAT_ERR_BAD_ARG, "yat_ln_modulate_fwd: mean and rstd go together");
   int rc = check_common("yat_ln_modulate_fwd", B, N, C, mod_batch_stride);
   if (rc != YAT_OK) return rc;
@@ -676,16 +524,29 @@ extern "C" int yat_ln_modulate_fwd(const void* x, const void* scale, const void*
               "yat_ln_modulate_fwd: tensors must be 16-byte aligned");
   const int nvec = C / 8, rows = B * N;
   const int grid = (rows + kWarpsPerBlock - 1) / kWarpsPerBlock;
-  YAT_DISPATCH_MAXV((nvec + 31) / 32, ln_modulate_fwd_kernel<MAXV><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
-      (const uint4*)x, (const uint4*)scale, (const uint4*)shift, mod_batch_stride / 8, rows, N, nvec, 1.0f / C, eps,
-      (uint4*)y, mean, rstd));
+  if (x2)
+    YAT_DISPATCH_MAXV((nvec + 31) / 32, ln_modulate_fwd_kernel<MAXV, true><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+        (const uint4*)x, (const uint4*)x2, (const uint4*)scale, (const uint4*)shift, mod_batch_stride / 8, rows, N, nvec,
+        1.0f / C, eps, (uint4*)xsum, (uint4*)y, mean, rstd));
+  else
+    YAT_DISPATCH_MAXV((nvec + 31) / 32, ln_modulate_fwd_kernel<MAXV, false><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+        (const uint4*)x, nullptr, (const uint4*)scale, (const uint4*)shift, mod_batch_stride / 8, rows, N, nvec,
+        1.0f / C, eps, nullptr, (uint4*)y, mean, rstd));
   return check_launch("ln_modulate_fwd");
 }
 
 extern "C" int yat_ln_modulate_bwd(const void* x, const void* dy, const void* scale, int64_t mod_batch_stride,
                                    const float* mean, const float* rstd, int B, int N, int C, void* dx, void* dscale,
                                    void* dshift, void* workspace, void* stream) {
+  return yat_ln_modulate_bwd_res(x, dy, nullptr, scale, mod_batch_stride, mean, rstd, B, N, C, dx, dscale, dshift,
+                                 workspace, stream);
+}
+
+extern "C" int yat_ln_modulate_bwd_res(const void* x, const void* dy, const void* dres, const void* scale,
+                                       int64_t mod_batch_stride, const float* mean, const float* rstd, int B, int N,
+                                       int C, void* dx, void* dscale, void* dshift, void* workspace, void* stream) {
   using namespace yat;
+  YAT_REQUIRE(!dres || aligned16(dres), YAT_ERR_BAD_ARG, "yat_ln_modulate_bwd_res: dres must be 16-byte aligned");
   YAT_REQUIRE(x && dy && scale && mean && rstd && dx && dscale && dshift && workspace, YAT_ERR_BAD_ARG,
               "yat_ln_modulate_bwd: null pointer argument");
   int rc = check_common("yat_ln_modulate_bwd", B, N, C, mod_batch_stride);
@@ -695,23 +556,9 @@ extern "C" int yat_ln_modulate_bwd(const void* x, const void* dy, const void* sc
   cudaStream_t st = (cudaStream_t)stream;
   const int nvec = C / 8, rows = B * N;
   (void)rows;
-  const int splits = ln_bwd_splits(B, N, C), rows_per_split = (N + splits - 1) / splits;
-  const int smem = ln_bwd_smem(C);
+  const int splits = ln_bwd_splits(B, N, C);
   float* part0 = (float*)workspace;
-  float* part1 = part0 + (int64_t)splits * B * C;
-#define YAT_LN_BWD_LAUNCH(MAXH)                                                                                       \
-  do {                                                                                                               \
-    static bool attr_set = false;                                                                                    \
-    if (!attr_set) {                                                                                                 \
-      cudaFuncSetAttribute(ln_modulate_bwd_fused_kernel<MAXH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 144 * 1024); \
-      attr_set = true;                                                                                               \
-    }                                                                                                                \
-    ln_modulate_bwd_fused_kernel<MAXH><<<dim3(splits, B), kLnBwdThreads, smem, st>>>(                                 \
-        (const uint4*)x, (const uint4*)dy, (const uint4*)scale, mod_batch_stride / 8, mean, rstd, N, nvec,           \
-        rows_per_split, 1.0f / C, (uint4*)dx, part0, part1);                                                         \
-  } while (0)
-  static const bool use_pairs = getenv("YAT_LN_BWD_PAIRS") != nullptr;   // development switch: the warp-pair kernel
-  if (!use_pairs) {
+  {
     const int threads = (nvec + 31) / 32 * 32;
     const int per_sm = threads <= 320 ? 2 : 1;                     // resident CTAs (launch bounds of the two instantiations)
     int sp = (kNumSMs * per_sm) / B;
@@ -721,14 +568,18 @@ extern "C" int yat_ln_modulate_bwd(const void* x, const void* dy, const void* sc
     sp = sp < 1 ? 1 : sp;
     const int rps = (N + sp - 1) / sp;
     float* p1 = part0 + (int64_t)sp * B * C;
-    if (threads <= 320)
-      ln_modulate_bwd_cols_kernel<320, 2><<<dim3(sp, B), threads, 0, st>>>(
+    if (threads <= 288)     // SANA-1.6B: C = 2240 -> 280 vectors; 2 x 288 threads leave 112 registers per thread (no spills)
+      ln_modulate_bwd_cols_kernel<112><<<dim3(sp, B), threads, 0, st>>>(
           (const uint4*)x, (const uint4*)dy, (const uint4*)scale, mod_batch_stride / 8, mean, rstd, N, nvec, rps, 1.0f / C,
-          (uint4*)dx, part0, p1);
+          (const uint4*)dres, (uint4*)dx, part0, p1);
+    else if (threads <= 320)
+      ln_modulate_bwd_cols_kernel<96><<<dim3(sp, B), threads, 0, st>>>(
+          (const uint4*)x, (const uint4*)dy, (const uint4*)scale, mod_batch_stride / 8, mean, rstd, N, nvec, rps, 1.0f / C,
+          (const uint4*)dres, (uint4*)dx, part0, p1);
     else
-      ln_modulate_bwd_cols_kernel<512, 1><<<dim3(sp, B), threads, 0, st>>>(
+      ln_modulate_bwd_cols_kernel<128><<<dim3(sp, B), threads, 0, st>>>(
           (const uint4*)x, (const uint4*)dy, (const uint4*)scale, mod_batch_stride / 8, mean, rstd, N, nvec, rps, 1.0f / C,
-          (uint4*)dx, part0, p1);
+          (const uint4*)dres, (uint4*)dx, part0, p1);
     rc = check_launch("ln_modulate_bwd_cols");
     if (rc != YAT_OK) return rc;
     const int64_t bc2_ = (int64_t)B * C;
@@ -736,18 +587,6 @@ extern "C" int yat_ln_modulate_bwd(const void* x, const void* dy, const void* sc
                                                                         (__nv_bfloat16*)dshift);
     return check_launch("ln_modulate_bwd_finish");
   }
-  const int per_half = ((nvec + 31) / 32 + 1) / 2;                 // 32-vector blocks per warp of a pair
-  if (per_half <= 1)      YAT_LN_BWD_LAUNCH(1);
-  else if (per_half <= 2) YAT_LN_BWD_LAUNCH(2);
-  else if (per_half <= 5) YAT_LN_BWD_LAUNCH(5);
-  else                    YAT_LN_BWD_LAUNCH(8);
-#undef YAT_LN_BWD_LAUNCH
-  rc = check_launch("ln_modulate_bwd_fused");
-  if (rc != YAT_OK) return rc;
-  const int64_t bc = (int64_t)B * C;
-  column_finish_kernel<<<(unsigned)((bc + 255) / 256), 256, 0, st>>>(part0, part1, splits, bc, (__nv_bfloat16*)dscale,
-                                                                    (__nv_bfloat16*)dshift);
-  return check_launch("ln_modulate_bwd_finish");
 }
 
 extern "C" int yat_gate_residual_fwd(const void* res, const void* y, const void* gate, int64_t mod_batch_stride, int B,

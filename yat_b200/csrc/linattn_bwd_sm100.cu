@@ -112,8 +112,7 @@ struct BwdMaps {
 };
 
 __global__ void __launch_bounds__(kThreads, 1)
-linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int groups, int dbg) {
-  const int max_pass = dbg & 3 ? (dbg & 3) : 3;  // debug: run only the first passes
+linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int groups) {
   extern __shared__ uint8_t smem_raw[];
   BwdSmem& S = *reinterpret_cast<BwdSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -157,7 +156,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
       uint32_t it = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const int b = item / groups, c0 = (item % groups) * (kHeadsPerItem * kD);
-        for (int pass = 0; pass < max_pass; ++pass) {
+        for (int pass = 0; pass < 3; ++pass) {
           for (int t = 0; t < n_tiles; ++t) {
 #pragma unroll
             for (int w = 0; w < 2; ++w, ++it) {
@@ -230,7 +229,6 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         tc_commit(smem_u32(&S.kv_full));
         mbar_wait(smem_u32(&S.b_ready), item_iter & 1);
         tc_fence_after();
-        if (max_pass < 2) continue;
         // ---- pass B
         for (int t = 0; t < n_tiles; ++t, it += 2, ++bt) {
           const uint32_t sq = it % kStages, sd = (it + 1) % kStages;
@@ -238,14 +236,13 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           wait_ready(sq);                                        // relu(Q) in place, den written
           mbar_wait(smem_u32(&S.num_empty), (bt & 1) ^ 1);
           tc_fence_after();
-          if (!(dbg & 128)) small_mmas(kColNum, qa, false);      // num = relu(Q) KV
+          small_mmas(kColNum, qa, false);           // num = relu(Q) KV
           tc_commit(smem_u32(&S.num_full));
           wait_ready(sd);                                        // Q~ hi (Q slot) / lo written, dO landed
           mbar_wait(smem_u32(&S.dq_empty), (bt & 1) ^ 1);
           tc_fence_after();
-          if (!(dbg & 4)) small_mmas(kColDQ, da_, true);         // dQ~ = dO KV^T
+          small_mmas(kColDQ, da_, true);             // dQ~ = dO KV^T
           tc_commit(smem_u32(&S.dq_full));
-          if (!(dbg & 256))
 #pragma unroll
           for (int part = 0; part < 2; ++part) {                 // D_dKV += (Q~hi + Q~lo)^T dO
             const uint32_t aa = part ? la : qa;
@@ -261,7 +258,6 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         tc_commit(smem_u32(&S.dkv_full));
         mbar_wait(smem_u32(&S.b2_ready), item_iter & 1);
         tc_fence_after();
-        if (max_pass < 3) continue;
         // ---- pass C: dV = relu(K) dKV, dK~ = V dKV^T
         for (int t = 0; t < n_tiles; ++t, it += 2, ++ct) {
           const uint32_t sk = it % kStages, sv = (it + 1) % kStages, pv = ((it + 1) / kStages) & 1;
@@ -270,7 +266,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           mbar_wait(smem_u32(&S.c_empty), (ct & 1) ^ 1);
           tc_fence_after();
           small_mmas(kColDV, smem_u32(&S.slots[sk][0]), false);
-          if (!(dbg & 4)) small_mmas(kColDK, smem_u32(&S.slots[sv][0]), true);
+          small_mmas(kColDK, smem_u32(&S.slots[sv][0]), true);
           tc_commit(smem_u32(&S.c_full));
         }
       }
@@ -291,24 +287,22 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const int b = item / groups, c0 = (item % groups) * (kHeadsPerItem * kD);
         it += 2 * n_tiles;  // pass A: slots are released by the issuer's commits
-        if (max_pass < 2) continue;
         for (int t = 0; t < n_tiles; ++t, it += 2) {
           const uint32_t sq = it % kStages, sd = (it + 1) % kStages;
           wait_out(sd);                                  // dQ sits in the dO slot; nobody reads the Q slot any more
           mbar_arrive(smem_u32(&S.empty[sq]));
-          if (!(dbg & 8)) store(&M.dq, sd, c0, t * kTile, b);
+          store(&M.dq, sd, c0, t * kTile, b);
           tma_store_commit();
           tma_store_wait_read<0>();
           mbar_arrive(smem_u32(&S.empty[sd]));
         }
-        if (max_pass < 3) continue;
         for (int t = 0; t < n_tiles; ++t, it += 2) {
           const uint32_t sk = it % kStages, sv = (it + 1) % kStages;
           wait_out(sk);
-          if (!(dbg & 8)) store(&M.dk, sk, c0, t * kTile, b);
+          store(&M.dk, sk, c0, t * kTile, b);
           tma_store_commit();
           wait_out(sv);
-          if (!(dbg & 8)) store(&M.dv, sv, c0, t * kTile, b);
+          store(&M.dv, sv, c0, t * kTile, b);
           tma_store_commit();
           tma_store_wait_read<1>();
           mbar_arrive(smem_u32(&S.empty[sk]));
@@ -397,8 +391,6 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
       float ksr[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) ksr[j] = S.ks[cc * 8 + j];
-
-      if (max_pass < 2) continue;
       // ---------------- pass B ----------------
       float dcs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
       for (int t = 0; t < n_tiles; ++t, it += 2, ++bt) {
@@ -437,7 +429,6 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         uint8_t* lrow = &S.lo[row_off];
         const uint8_t* drow = &S.slots[sd][row_off];
         rr[0] = rr[1] = dd[0] = dd[1] = 0.f;
-        if (!(dbg & 16))
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {
           const int h = colhalf * 2 + hh;
@@ -486,7 +477,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         named_bar_sync(1, kEpiThreads);         // wrow and Q~ visible in the transform mapping
 
         // E3a: dKs += sum_n Q~_n (dDen_n / r_n)
-        if (!(dbg & 32)) {
+        {
           const uint8_t* bh = &S.slots[sq][half * kHalfBytes];
           const uint8_t* bl = &S.lo[half * kHalfBytes];
 #pragma unroll
@@ -509,7 +500,6 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         for (int hh = 0; hh < 2; ++hh)
 #pragma unroll
           for (int g = 0; g < 4; ++g) outv[hh][g] = make_uint4(0, 0, 0, 0);
-        if (!(dbg & 64))
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {
           const int h = colhalf * 2 + hh;
@@ -547,8 +537,6 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
       tc_fence_after();
       build_bmat(kColDKV);                      // barrier inside: dks visible, D_dKV drained, bmat rewritten
       if (lane == 0) mbar_arrive(smem_u32(&S.b2_ready));
-
-      if (max_pass < 3) continue;
       // ---------------- pass C ----------------
       for (int t = 0; t < n_tiles; ++t, it += 2, ++ct) {
         const uint32_t sk = it % kStages, pk = (it / kStages) & 1;
@@ -662,8 +650,6 @@ extern "C" int yat_linattn_bwd_ld(const void* q, const void* k, const void* v, i
   const int groups = (H + kHeadsPerItem - 1) / kHeadsPerItem;
   const int items = B * groups;
   const int grid = items < kNumSMs ? items : kNumSMs;
-  const char* dbg_env = getenv("YAT_BWD_DEBUG");  // development aid: bits 0-1 = passes to run, 4 = no transposed MMAs, 8 = no stores
-  const int dbg = dbg_env ? atoi(dbg_env) : 0;
-  linattn_bwd_sm100_kernel<<<grid, kThreads, kBwdSmemBytes, (cudaStream_t)stream>>>(maps, B, N, groups, dbg);
+  linattn_bwd_sm100_kernel<<<grid, kThreads, kBwdSmemBytes, (cudaStream_t)stream>>>(maps, B, N, groups);
   return check_launch("linattn_bwd_sm100");
 }

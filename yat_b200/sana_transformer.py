@@ -23,7 +23,7 @@ from torch import nn
 from torch.utils.checkpoint import checkpoint
 
 from .attention import Attention, AttnProcessor2_0, SanaLinearAttnProcessorB200
-from .block_ops import gate_residual, ln_modulate
+from .block_ops import gate_residual, ln_modulate, ln_modulate_res
 from .adapters import adapter_term
 from .glumb import glumb_mid, inverted_glumb_mid
 
@@ -230,14 +230,18 @@ class SanaTransformerBlock(nn.Module):
                        shift_msa, scale_msa, gate_msa, shift_mlp, scale_mlp, gate_mlp):
         """Same block with the modulate / gate / residual arithmetic as fused kernels
         (yat_b200/csrc/block_ops.cu); everything stays token-major [B, N, C]."""
-        norm_hidden_states = ln_modulate(hidden_states, scale_msa, shift_msa, self.norm1.eps)
+        # ln_modulate_res returns the residual-branch tensor from the same autograd node as the normalised one: the
+        # two gradients of every residual-stream tensor are then added inside the LN backward kernel, and the attn2
+        # residual add (:103) is formed inside the norm2 forward kernel - no torch elementwise pass is left here
+        norm_hidden_states, hidden_states = ln_modulate_res(hidden_states, scale_msa, shift_msa, self.norm1.eps)
         attn_output = self.attn1(norm_hidden_states)
         hidden_states = gate_residual(hidden_states, attn_output, gate_msa)
+        attn_output = None
         if self.attn2 is not None:
             attn_output = self.attn2(hidden_states, encoder_hidden_states=encoder_hidden_states,
                                      attention_mask=encoder_attention_mask)
-            hidden_states = attn_output + hidden_states
-        norm_hidden_states = ln_modulate(hidden_states, scale_mlp, shift_mlp, self.norm2.eps)
+        norm_hidden_states, hidden_states = ln_modulate_res(hidden_states, scale_mlp, shift_mlp, self.norm2.eps,
+                                                            add=attn_output)
         ff_output = self.ff.forward_tokens(norm_hidden_states, height, width)
         return gate_residual(hidden_states, ff_output, gate_mlp)
 
