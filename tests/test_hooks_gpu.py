@@ -4,6 +4,8 @@ stand-in transformer weights).  Bit-exact: timestep indices / timesteps / x_t; <
 and gradients (north star).  Shapes are BASELINE.json configs 3 and 4 scaled down."""
 import copy
 
+import os
+
 import pytest
 import torch
 
@@ -19,6 +21,28 @@ def _params(batch):
     p.learning_rate = 1e-3
     p.weight_decay = 0.0
     return p
+
+
+def _assert_grads_within_bf16_noise(named_params, g32, g16, skip, min_checked, report=None):
+    """North star: bf16 gradients <= 2e-2 relative.  The product runs in bf16 like the reference; the oracle is
+    evaluated in fp32 (the function both approximate) and in bf16 (the reference's own dtype).  Per tensor: within
+    2e-2 of the fp32 oracle, or at least as close to it as the bf16 oracle is (x1.25 for sampling noise)."""
+    rows, bad = {}, {}
+    for n, p in named_params:
+        gref = g32.get(n)
+        if gref is None or gref.norm() == 0 or any(n.endswith(sfx) for sfx in skip):
+            continue
+        a, b = _rel(p.grad, gref), _rel(g16[n], gref)
+        rows[n] = (a, b)
+        if not (a < 2e-2 or a <= 1.25 * b):
+            bad[n] = (a, b)
+    assert not bad, bad
+    assert len(rows) > min_checked
+    d = os.environ.get("YAT_REPORT_DIR")
+    if report and d and os.path.isdir(d):
+        import json
+        with open(os.path.join(d, f"parity_{report}.json"), "w") as f:
+            json.dump({k: {"product_vs_fp32": v[0], "bf16_oracle_vs_fp32": v[1]} for k, v in rows.items()}, f, indent=1)
 
 
 def _rel(a, b):
@@ -147,18 +171,18 @@ def test_pixart_sigma_real_transformer_step_vs_oracle(cuda, tmp_path, monkeypatc
     npred, tgt = losses.pixart_crop(pred, noise.float())
     loss_ref = torch.nn.functional.mse_loss(npred, tgt)
     loss_ref.backward()
+    # the same step in the reference's own dtype (train_pixart_sigma.py runs the model and the MSE in bf16)
+    sd16 = {k: v.detach().to(torch.bfloat16).requires_grad_(True) for k, v in sd.items()}
+    pred16 = pixart_forward(sd16, cfg, x_t, padded, t, mask)
+    npred16, tgt16 = losses.pixart_crop(pred16, noise)
+    torch.nn.functional.mse_loss(npred16, tgt16).backward()
 
     loss = tr.optimize(1.67, lat, embs, None, torch.Generator())
     loss.backward()
     assert abs(loss.item() - loss_ref.item()) <= 2e-2 * abs(loss_ref.item())
-    checked = 0
-    for n, p in tr.model.named_parameters():
-        gref = sd[n].grad
-        if gref is None or gref.norm() == 0 or n.endswith("to_k.bias"):
-            continue                      # softmax is invariant to a key bias: exact gradient 0
-        assert _rel(p.grad, gref) < 6e-2, (n, _rel(p.grad, gref))
-        checked += 1
-    assert checked > 40
+    # softmax is invariant to a key bias: exact gradient 0 -> skipped
+    _assert_grads_within_bf16_noise(tr.model.named_parameters(), {k: v.grad for k, v in sd.items()},
+                                    {k: v.grad for k, v in sd16.items()}, ("to_k.bias",), 40, "k3_tiny_step")
 
 
 def test_pixart_sigma_trains_from_model_config(cuda, tmp_path, monkeypatch):
@@ -201,18 +225,18 @@ def test_sd35_real_mmdit_step_vs_oracle(cuda, tmp_path, monkeypatch):
     pred = sd3_forward(sd, cfg, x_t.float(), emb.float(), t, pooled.float())
     loss_ref = torch.nn.functional.mse_loss(pred, target.float())
     loss_ref.backward()
+    # the same step in the reference's own dtype (train_sd35.py:187-193: bf16 model, bf16 MSE)
+    sd16 = {k: (v.detach().to(torch.bfloat16).requires_grad_(True) if v.is_floating_point() else v) for k, v in sd.items()}
+    torch.nn.functional.mse_loss(sd3_forward(sd16, cfg, x_t, emb, t, pooled), target).backward()
 
     loss = tr.optimize(1.0, lat, (emb, pooled), None, torch.Generator())
     loss.backward()
     assert abs(loss.item() - loss_ref.item()) <= 2e-2 * abs(loss_ref.item())
-    checked = 0
-    for n, p in tr.model.named_parameters():
-        gref = sd[n].grad
-        if gref is None or gref.norm() == 0 or n.endswith("to_k.bias") or n.endswith("add_k_proj.bias"):
-            continue                      # a key bias only enters through the RMS-normed key: near-zero exact gradient
-        assert _rel(p.grad, gref) < 8e-2, (n, _rel(p.grad, gref))
-        checked += 1
-    assert checked > 60
+    # a key bias only enters through the RMS-normed key: near-zero exact gradient -> skipped
+    _assert_grads_within_bf16_noise(tr.model.named_parameters(),
+                                    {k: v.grad for k, v in sd.items() if v.is_floating_point()},
+                                    {k: v.grad for k, v in sd16.items() if v.is_floating_point()},
+                                    ("to_k.bias", "add_k_proj.bias"), 60, "k4_tiny_step")
 
 
 @pytest.mark.parametrize("lora", [False, True])
