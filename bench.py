@@ -405,6 +405,23 @@ def _standalone_kernels(device, pk):
     entry("glumb_mid_bwd", 35 * B * N * C, ms, [B, 32, 32, 2 * Hd])
     del u, wdw, bdw, dmid, mid
     del mod
+    # the fused q|k|v projection of one SANA-1.6B layer: own tcgen05 GEMM vs the library call it replaces (A/B)
+    try:
+        from yat_b200.gemm import gemm_bf16_tn
+        xa = q.view(B * N, C)
+        wq = (torch.randn((3 * C, C), device=device) / C ** 0.5).to(torch.bfloat16)
+        fl = 2.0 * B * N * C * 3 * C
+        for name, fn in (("gemm_qkv_own_tcgen05", lambda: gemm_bf16_tn(xa, wq)),
+                         ("gemm_qkv_cublas", lambda: torch.nn.functional.linear(xa, wq))):
+            ms = timeit(fn, iters=30, warm=5)
+            out[name] = {"bound": "tensor", "achieved": fl / (ms * 1e-3) / 1e12, "peak": pk["bf16_tflops"],
+                         "unit": "TFLOP/s", "us": ms * 1e3, "flops": fl, "shape": [B * N, 3 * C, C],
+                         "peak_source": pk["source"] + " (bf16_tflops, burst: kernel timed alone)", "timing": "stand-alone"}
+            out[name]["frac"] = out[name]["achieved"] / out[name]["peak"]
+        out["gemm_qkv_own_tcgen05"]["vs_cublas_time"] = out["gemm_qkv_cublas"]["us"] / out["gemm_qkv_own_tcgen05"]["us"]
+        del wq
+    except Exception as e:  # noqa: BLE001 — reported, not hidden
+        out["gemm_qkv_own_tcgen05"] = {"error": str(e)[:200]}
     ms = timeit(lambda: sana_linear_attention(q, k, v, H))
     entry("linattn_fwd_sm100", 8 * B * N * C, ms, [B, N, C], flops=4 * 32 * 33 * N * H * B)
     qg, kg, vg = [t.clone().requires_grad_(True) for t in (q, k, v)]
@@ -469,6 +486,8 @@ def _account(step_fn, n_steps, device, ms_per_step):
     for ev in prof.events():
         if getattr(ev, "device_type", None) is None or "CUDA" not in str(ev.device_type).upper():
             continue
+        if getattr(ev, "is_user_annotation", False) or ev.name.startswith(("Optimizer.", "ProfilerStep", "## ")):
+            continue                                                     # record_function ranges mirrored on the device
         t0, t1 = ev.time_range.start, ev.time_range.end
         if t1 <= t0:
             continue

@@ -253,6 +253,17 @@ int yat_adamw_ema_step(const int64_t* tensor_tab, const int64_t* grad_ptrs, cons
 int yat_ema_step(const int64_t* tensor_tab, const int32_t* chunks, int n_chunks, int dtype, double one_minus_decay,
                  void* stream);
 
+/* ---- (next, N1) projection GEMM on tcgen05:  c[M, N] = a[M, K] . w[N, K]^T (+ bias[N]) -----------------------
+ * The `x @ W^T` form of torch F.linear, i.e. every projection of the SANA block (diffusers Attention to_q / to_k /
+ * to_v / to_out and the token-major 1x1 convolutions of GLUMBConv, utils/patch_sana_attention_layers.py:84-113).
+ * a [M, K] and w [N, K] bf16 row-major with row pitches lda / ldw (elements, multiples of 8), bias bf16 [N] or NULL
+ * (added in fp32 before the single rounding), c [M, N] bf16 with pitch ldc (multiple of 16, c 32-byte aligned).
+ * fp32 accumulation in TMEM, cta_group::2 (two CTAs per 256 x tile_n tile), TMA operand staging, persistent grid.
+ * tile_n: 256, 224 or 128; 0 = pick (224 when N is a multiple of 224 but not of 256: all SANA-1.6B widths).
+ */
+int yat_gemm_bf16_tn(const void* a, const void* w, const void* bias, void* c, int64_t M, int N, int K,
+                     int64_t lda, int64_t ldw, int64_t ldc, int tile_n, void* stream);
+
 /* ---- bucket assignment (host function; float64 compare, first-minimum wins) ---------------
  *   out[i] = argmin_j |keys[j] - ratios[i]| with strict '<' in table order, or -1 if nkeys==0.
  */

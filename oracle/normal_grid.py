@@ -51,6 +51,7 @@ def discrete_ks(counts_by_bits, n=None):
     # +0 and -0 are the same value: fold the -0 pattern into +0
     c = c.copy()
     c[0x0000] += c[0x8000]
+    c[0x8000] = 0.0
     n = float(c.sum()) if n is None else float(n)
     emp = np.cumsum(c[bits]) / n
     d = np.abs(emp - cdf)

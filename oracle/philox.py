@@ -54,13 +54,13 @@ def box_muller(xa, xb):
 
 def box_muller_word(x):
     """Latent-noise stream (stream 0): ONE 32-bit word per pair, 20 radius bits + 12 angle bits, the angle lattice
-    dithered by the low 11 radius bits (philox.cuh box_muller_word): u1 = 1 - (x>>12)*2^-20 in (0,1],
-    g = 1 + ((x&0xfff)*2^11 + ((x>>12)&0x7ff))*2^-23, theta = fl32(fma(g, fl32(2 pi), fl32(-3 pi)))
+    dithered by the low 8 radius bits (philox.cuh box_muller_word): u1 = 1 - (x>>12)*2^-20 in (0,1],
+    g = 1 + ((x&0xfff)*2^11 + ((x>>12)&0xff)*2^3)*2^-23, theta = fl32(fma(g, fl32(2 pi), fl32(-3 pi)))
     in (-pi,pi).  The device evaluates lg2/sqrt/sin/cos on the special-function unit, so its fp32 normals sit
     within ~1e-6 absolute of this float64 evaluation before rounding to the latent dtype."""
     x = np.asarray(x, dtype=np.uint32)
     u1 = 1.0 - (x >> np.uint32(12)).astype(np.float64) * 2.0 ** -20
-    mant = (x & np.uint32(0xFFF)).astype(np.uint64) * np.uint64(2048) + ((x >> np.uint32(12)) & np.uint32(0x7FF)).astype(np.uint64)
+    mant = (x & np.uint32(0xFFF)).astype(np.uint64) * np.uint64(2048) + ((x >> np.uint32(12)) & np.uint32(0xFF)).astype(np.uint64) * np.uint64(8)
     g = 1.0 + mant.astype(np.float64) * 2.0 ** -23
     two_pi = np.float64(np.float32(6.283185307179586))
     c = np.float64(np.float32(-9.42477796076938))

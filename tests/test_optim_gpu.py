@@ -192,7 +192,11 @@ def test_optimizer_state_dict_reload_uses_the_loaded_moments(cuda):
         for pa, pb, g in zip(a, b, grads(step)):
             pa.grad, pb.grad = g.clone(), g.clone()
         oa.step(max_norm=1.0), ob.step(max_norm=1.0)
-    sd = ob.state_dict()
+    import io
+    buf = io.BytesIO()
+    torch.save(ob.state_dict(), buf)                        # a checkpoint: the reload allocates every state tensor anew
+    buf.seek(0)
+    sd = torch.load(buf, map_location="cpu")
     old = [ob.state[p]["exp_avg"] for p in b]
     ob.load_state_dict(sd)                                  # replaces every state tensor
     assert all(ob.state[p]["exp_avg"].data_ptr() != o.data_ptr() for p, o in zip(b, old))

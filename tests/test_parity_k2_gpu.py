@@ -100,8 +100,8 @@ def test_k2_block_forward_backward_vs_oracle(cuda):
     bias = ((1 - mask.float()) * -10000.0).unsqueeze(1)                       # patched_sana_transformer.py:275-277
 
     def oracle(dtype):
-        sdd = {k: v.to(dtype).requires_grad_(True) for k, v in sd.items()}
-        xi, ti, ei = [t.to(dtype).requires_grad_(True) for t in (x, temb, enc)]
+        sdd = {k: v.detach().clone().to(dtype).requires_grad_(True) for k, v in sd.items()}
+        xi, ti, ei = [t.detach().clone().to(dtype).requires_grad_(True) for t in (x, temb, enc)]
         y = sana_block(sdd, "b.", xi, ti, ei, bias.to(dtype), 70, 20, hw, hw, 1e-6)
         y.backward(dout.to(dtype))
         grads = {k[2:]: p.grad for k, p in sdd.items()}
@@ -172,11 +172,11 @@ def test_k1_step_vs_bf16_and_fp32_oracle(cuda):
     x_t, target, t_ref, _ = noising.flow_noise_sana(lat, noise, idx, tt, ss)
 
     def oracle(dtype):
-        sd = {k: v.to(dtype).requires_grad_(v.dtype.is_floating_point) for k, v in base.items()}
+        sd = {k: v.detach().clone().to(dtype).requires_grad_(v.dtype.is_floating_point) for k, v in base.items()}
         pred = sana_forward(sd, cfg, x_t.to(dtype), enc_ref.to(dtype), t_ref, mask_ref)
         loss = losses.mse_fp32(pred, target)                                 # train_sana.py:218
         loss.backward()
-        return float(loss), {k: p.grad for k, p in sd.items() if p.grad is not None}
+        return float(loss.detach()), {k: p.grad for k, p in sd.items() if p.grad is not None}
 
     l32, g32 = oracle(torch.float32)
     l16, g16 = oracle(torch.bfloat16)

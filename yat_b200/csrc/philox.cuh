@@ -142,15 +142,16 @@ __device__ __forceinline__ void box_muller_precise(uint32_t xa, uint32_t xb, flo
 // 8 normals of one 128-bit bf16 vector, and the transform is 4 MUFU ops per pair (lg2, sqrt, sin,
 // cos) with no integer->float conversion:
 //   f = 1 + (x>>12)*2^-20 in [1,2)       u1 = 2 - f in (0,1]  (exact)      r = sqrt(-2 ln u1)
-//   g = 1 + ((x&0xfff)*2^11 + ((x>>12)&0x7ff))*2^-23 in [1,2)
+//   g = 1 + ((x&0xfff)*2^11 + ((x>>12)&0xff)*2^3)*2^-23 in [1,2)
 //                                        theta = fl32(2*pi*g - 3*pi) in (-pi,pi)
 //   z0 = r cos(theta), z1 = r sin(theta)
 // The 12 angle bits alone would put every pair on a fixed lattice of 4096 rays; the rays next to the
 // axes then leave a dent in the distribution of r cos(theta) at |z| < 1e-3 (exact population count over all
 // 2^32 words: discrete Kolmogorov-Smirnov distance 8.3e-5 from the bf16-rounded normal, half the critical
-// value of a 2^27-sample test).  The LOW 11 radius bits therefore dither the lattice (they move r by < 2^-9
-// relative outside the far tail, and every sub-lattice is itself uniform): population KS distance 9.6e-6
-// (tests/test_oracle_golden.py checks a strided population count).  One extra instruction per word.
+// value of a 2^27-sample test).  The LOW 8 radius bits therefore dither the lattice (they move r by < 2^-12
+// relative outside the far tail, and every sub-lattice is itself uniform): population KS distance ~1e-5
+// (tests/test_oracle_golden.py checks a strided population count).  The mantissa of g is one bit-select of (x << 11)
+// and the radius word f, which already carries the exponent and those 8 bits at [3, 11).
 // Largest |z| = sqrt(40 ln 2) = 5.27 (the reference's fp32 CPU randn stops at sqrt(48 ln 2) = 5.77).
 // |theta| < pi keeps sin.approx / cos.approx at their 2^-21 absolute accuracy; the oracle
 // (oracle/philox.py box_muller_word) evaluates the same map in float64 and the test allows the ~1e-6
@@ -171,8 +172,8 @@ __device__ __forceinline__ void box_muller_word(uint32_t x, float& z0, float& z1
   // otherwise re-expands "shift, and, or" into three instructions per field)
   uint32_t fb;
   asm("mad.lo.u32 %0, %1, 8, 0x3f800000;" : "=r"(fb) : "r"(x >> 12));
-  // mantissa of g = [angle bits 0..11 | radius bits 12..22]: one funnel shift of {x : x << 9} by 11
-  const uint32_t gb = (__funnelshift_l(x << 9, x, 11) & 0x007fffffu) | 0x3f800000u;
+  // g = [exponent of f | angle bits 0..11 at [11, 23) | low 8 radius bits at [3, 11)]: bits [11, 23) from x << 11, rest from f
+  const uint32_t gb = ((x << 11) & 0x007ff800u) | (fb & 0xff8007ffu);
   const float f = __uint_as_float(fb), g = __uint_as_float(gb);
   const float u1 = 2.0f - f;
   const float theta = fmaf(g, 6.283185307179586f, -9.42477796076938f);  // fl32(-3 pi): the half-step offset pi/2^23 is below fp32 resolution here
