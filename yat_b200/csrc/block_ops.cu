@@ -14,9 +14,11 @@
 #include <cstdlib>
 
 #include "common.cuh"
+#include "sm100.cuh"
 
 namespace yat {
 namespace {
+using namespace sm100;
 
 constexpr int kWarpsPerBlock = 8;
 constexpr int kThreads = kWarpsPerBlock * 32;
@@ -126,69 +128,128 @@ __global__ void __launch_bounds__(kThreads) ln_modulate_fwd_kernel(
 }
 
 // ------------------------------------------------------------------------------------------------
-// ln_modulate backward, column-ownership form (the one launched): a thread owns ONE 8-column vector for the whole CTA
-// = (row split, sample), so (1 + scale) is unpacked once into registers and the dscale / dshift column sums are plain
-// register accumulators written out at the end (no shared-memory image, no reduction over warps).  Rows go four at a
-// time: 8 x 128-bit loads in flight per thread, the 8 partial row sums (4 rows x {sum g, sum g*xhat}) are reduced in
-// the warp with a halving exchange (9 shuffles), across the warps through shared memory (every thread adds the warps
-// in the same order -> identical statistics everywhere, deterministic), ONE __syncthreads per 4 rows (the slot
-// alternates).  x and dy are read once; fp32 pairs (FFMA2).
+// ln_modulate backward, column-ownership form over a shared-memory row ring (the one launched).
+//
+// A CTA = (row split, sample), one CTA per SM.  Its rows arrive four at a time through bulk asynchronous copies
+// (cp.async.bulk global -> shared, completion counted on an mbarrier): the four rows of x, of dy and of the residual
+// gradient are each ONE contiguous 4 * 2 C-byte copy issued by a single thread, so the bytes in flight per SM
+// (two to three 12 C-row groups, 107-161 KB at C = 2240) do not depend on registers or on how many warps are waiting.
+// A thread owns ONE 4-column vector (8 bytes) for the whole CTA, so (1 + scale) is unpacked once into registers and
+// the dscale / dshift column sums are plain register accumulators written out at the end (no shared-memory image).
+// The 8 partial row sums (4 rows x {sum g, sum g*xhat}) are reduced in the warp with a halving exchange (9 shuffles),
+// across the warps through shared memory (lane i of every warp adds value i over the warps in index order, then the
+// eight totals are broadcast by shuffle -> identical statistics everywhere, deterministic), ONE barrier per 4 rows.
+// A thread copies its 12 vectors of the group from the ring into registers BEFORE that barrier, so the barrier also
+// proves that the CTA is done with the slot: it is refilled at once with the group kSlots iterations ahead.
+// x, dy and dres are read once; fp32 pairs (FFMA2).
 // ------------------------------------------------------------------------------------------------
 constexpr int kLnRows = 4;
-constexpr int kLnMaxWarps = 16;   // C <= 4096 -> nvec <= 512 threads
+constexpr int kLnMaxWarps = 32;   // C <= 4096 -> C / 4 <= 1024 threads
+constexpr int kLnMaxSlots = 4;
 
-template <int MAXREG>
-__global__ void __maxnreg__(MAXREG) ln_modulate_bwd_cols_kernel(
-    const uint4* __restrict__ x, const uint4* __restrict__ dy, const uint4* __restrict__ scale,
-    int64_t mod_stride_vec, const float* __restrict__ mean_in, const float* __restrict__ rstd_in, int N, int nvec,
-    int rows_per_split, float inv_c, const uint4* __restrict__ dres, uint4* __restrict__ dx,
+__device__ __forceinline__ void bulk_load(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_dst),
+               "l"(gsrc), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float lds32f(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+
+// shared memory: ring [slots][3 tensors][kLnRows rows][C] bf16 | red [2][warps][8] fp32 | barriers
+inline int ln_bwd_slots(int C) {
+  const int64_t slot = 3ll * kLnRows * C * 2;
+  int s = (int)((232448 - 128 - 2 * kLnMaxWarps * 2 * kLnRows * 4 - kLnMaxSlots * 8) / slot);
+  return s > kLnMaxSlots ? kLnMaxSlots : s;
+}
+inline int64_t ln_bwd_smem_bytes(int slots, int C) {
+  return 128 + (int64_t)slots * 3 * kLnRows * C * 2 + 2 * kLnMaxWarps * 2 * kLnRows * 4 + kLnMaxSlots * 8;
+}
+
+template <int MAXT>
+__global__ void __launch_bounds__(MAXT, 1) ln_modulate_bwd_ring_kernel(
+    const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ scale,
+    int64_t mod_stride, const float* __restrict__ mean_in, const float* __restrict__ rstd_in, int N, int C, int slots,
+    int rows_per_split, float inv_c, const __nv_bfloat16* __restrict__ dres, __nv_bfloat16* __restrict__ dx,
     float* __restrict__ part0, float* __restrict__ part1) {
   // dres (may be null): gradient arriving on the residual branch of the same tensor; dx = dres + dx_ln is formed in
   // fp32 and rounded once (autograd would round dx_ln, then add in bf16 in a separate 6 C-byte pass)
-  __shared__ float red[2][kLnMaxWarps][2 * kLnRows];
-  const int c = threadIdx.x, lane = c & 31, warp = c >> 5, nwarps = (blockDim.x + 31) >> 5;
+  extern __shared__ uint8_t ln_smem_raw[];
+  const uint32_t row_bytes = (uint32_t)C * 2u, tensor_bytes = kLnRows * row_bytes, slot_bytes = 3u * tensor_bytes;
+  const uint32_t ring0 = (smem_u32(ln_smem_raw) + 127u) & ~127u;
+  const uint32_t red0 = ring0 + slots * slot_bytes;
+  const uint32_t bar0 = red0 + 2 * kLnMaxWarps * 2 * kLnRows * 4;
+  const int c = threadIdx.x, lane = c & 31, warp = c >> 5, nwarps = blockDim.x >> 5;
   const int split = blockIdx.x, b = blockIdx.y;
-  const bool live = c < nvec;
+  const bool live = 4 * c < C;
   const int r0 = split * rows_per_split;
   const int r1 = min(N, r0 + rows_per_split);
+  const int n_groups = (r1 - r0 + kLnRows - 1) / kLnRows;
+
+  if (c == 0) {
+    for (int i = 0; i < slots; ++i) mbar_init(bar0 + i * 8, 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+
+  auto issue = [&](int g, int slot) {                        // row group g of this CTA -> ring slot (one thread)
+    const int rb = r0 + g * kLnRows;
+    const uint32_t bytes = (uint32_t)min(kLnRows, r1 - rb) * row_bytes;
+    const int64_t off = ((int64_t)b * N + rb) * C;
+    const uint32_t dst = ring0 + slot * slot_bytes, bar = bar0 + slot * 8;
+    mbar_arrive_expect_tx(bar, dres != nullptr ? 3u * bytes : 2u * bytes);
+    bulk_load(dst, x + off, bytes, bar);
+    bulk_load(dst + tensor_bytes, dy + off, bytes, bar);
+    if (dres != nullptr) bulk_load(dst + 2u * tensor_bytes, dres + off, bytes, bar);
+  };
+  if (c == 0)
+    for (int s = 0; s < slots && s < n_groups; ++s) issue(s, s);
+
   const f2 one = bc2(1.0f);
-  f2 a1[4], dsc[4], dsh[4];
+  f2 a1[2], dsc[2], dsh[2];
   {
-    const uint4 av = live ? ld_cached(scale + (int64_t)b * mod_stride_vec + c) : make_uint4(0u, 0u, 0u, 0u);
-    const uint32_t aw[4] = {av.x, av.y, av.z, av.w};
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      a1[j] = add2(unpack2(aw[j]), one);
-      dsc[j] = bc2(0.f);
-      dsh[j] = bc2(0.f);
-    }
+    uint2 av = make_uint2(0u, 0u);
+    if (live) av = __ldg(reinterpret_cast<const uint2*>(scale + (int64_t)b * mod_stride) + c);
+    a1[0] = add2(unpack2(av.x), one);
+    a1[1] = add2(unpack2(av.y), one);
+    dsc[0] = dsc[1] = dsh[0] = dsh[1] = bc2(0.f);
   }
   int slot = 0;
-  for (int rb = r0; rb < r1; rb += kLnRows, slot ^= 1) {
-    uint4 xv[kLnRows], gv[kLnRows];
+  uint32_t phase = 0;
+  for (int g = 0; g < n_groups; ++g) {
+    const int rb = r0 + g * kLnRows;
+    const uint32_t src = ring0 + slot * slot_bytes + (uint32_t)c * 8u;
     float rs[kLnRows], nmr[kLnRows];
 #pragma unroll
     for (int k = 0; k < kLnRows; ++k) {
-      const bool ok = live && rb + k < r1;
       const int64_t row = (int64_t)b * N + min(rb + k, r1 - 1);
-      xv[k] = ok ? ld_stream(x + row * nvec + c) : make_uint4(0u, 0u, 0u, 0u);
-      gv[k] = ok ? ld_stream(dy + row * nvec + c) : make_uint4(0u, 0u, 0u, 0u);
       rs[k] = rstd_in[row];
       nmr[k] = -mean_in[row] * rs[k];
-      if (dres != nullptr && ok) asm volatile("prefetch.global.L2 [%0];" ::"l"(dres + row * nvec + c));
+    }
+    mbar_wait(bar0 + slot * 8, phase);
+    uint2 xv[kLnRows], gv[kLnRows], rv[kLnRows];
+#pragma unroll
+    for (int k = 0; k < kLnRows; ++k) {
+      const bool ok = live && rb + k < r1;
+      xv[k] = ok ? lds64(src + k * row_bytes) : make_uint2(0u, 0u);
+      gv[k] = ok ? lds64(src + tensor_bytes + k * row_bytes) : make_uint2(0u, 0u);
+      // bf16 zeros without a residual gradient: adding them leaves dx_ln unchanged
+      rv[k] = ok && dres != nullptr ? lds64(src + 2u * tensor_bytes + k * row_bytes) : make_uint2(0u, 0u);
     }
     float v[2 * kLnRows];                                   // [k] = sum g, [kLnRows + k] = sum g * xhat
 #pragma unroll
     for (int k = 0; k < kLnRows; ++k) {
-      const uint32_t xw[4] = {xv[k].x, xv[k].y, xv[k].z, xv[k].w}, gw[4] = {gv[k].x, gv[k].y, gv[k].z, gv[k].w};
       const f2 rsk = bc2(rs[k]), nmk = bc2(nmr[k]);
-      f2 s1 = bc2(0.f), s2 = bc2(0.f);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const f2 gg = mul2(unpack2(gw[j]), a1[j]);
-        s1 = add2(s1, gg);
-        s2 = fma2(gg, fma2(unpack2(xw[j]), rsk, nmk), s2);
-      }
+      const f2 g0 = mul2(unpack2(gv[k].x), a1[0]), g1 = mul2(unpack2(gv[k].y), a1[1]);
+      const f2 s1 = add2(g0, g1);
+      const f2 s2 = fma2(g1, fma2(unpack2(xv[k].y), rsk, nmk), mul2(g0, fma2(unpack2(xv[k].x), rsk, nmk)));
       float lo, hi;
       un2(s1, lo, hi);
       v[k] = lo + hi;
@@ -216,48 +277,44 @@ __global__ void __maxnreg__(MAXREG) ln_modulate_bwd_cols_kernel(
     v[0] += __shfl_xor_sync(0xffffffffu, v[0], 2);
     v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
     // lane L now holds the warp total of value index ((L>>4)&1)*4 + ((L>>3)&1)*2 + ((L>>2)&1)
-    if ((lane & 3) == 0) red[slot][warp][((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1)] = v[0];
-    __syncthreads();
-    float tot[2 * kLnRows];
-#pragma unroll
-    for (int i = 0; i < 2 * kLnRows; ++i) tot[i] = 0.f;
-    for (int w = 0; w < nwarps; ++w) {
-      const float4 p0 = *reinterpret_cast<const float4*>(&red[slot][w][0]);
-      const float4 p1 = *reinterpret_cast<const float4*>(&red[slot][w][4]);
-      tot[0] += p0.x; tot[1] += p0.y; tot[2] += p0.z; tot[3] += p0.w;
-      tot[4] += p1.x; tot[5] += p1.y; tot[6] += p1.z; tot[7] += p1.w;
+    const uint32_t red_slot = red0 + (g & 1) * (kLnMaxWarps * 2 * kLnRows * 4);
+    if ((lane & 3) == 0) {
+      const int vi = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+      asm volatile("st.shared.f32 [%0], %1;" ::"r"(red_slot + (warp * 2 * kLnRows + vi) * 4), "f"(v[0]) : "memory");
     }
+    __syncthreads();
+    // every thread has copied this group out of the ring: refill the slot with the group `slots` ahead
+    if (c == 0 && g + slots < n_groups) issue(g + slots, slot);
+    float mine = 0.f;                                        // lane i < 8: total of value i over the warps, in order
+    for (int w = 0; w < nwarps; ++w) mine += lds32f(red_slot + (w * 2 * kLnRows + (lane & 7)) * 4);
 #pragma unroll
     for (int k = 0; k < kLnRows; ++k) {
+      const float t1 = __shfl_sync(0xffffffffu, mine, k), t2 = __shfl_sync(0xffffffffu, mine, kLnRows + k);
       if (!(live && rb + k < r1)) continue;
       const int64_t row = (int64_t)b * N + rb + k;
-      const uint32_t xw[4] = {xv[k].x, xv[k].y, xv[k].z, xv[k].w}, gw[4] = {gv[k].x, gv[k].y, gv[k].z, gv[k].w};
       const f2 rsk = bc2(rs[k]), nmk = bc2(nmr[k]);
-      const f2 nc1r = bc2(-tot[k] * inv_c * rs[k]), nc2r = bc2(-tot[kLnRows + k] * inv_c * rs[k]);
-      uint4 rv = make_uint4(0u, 0u, 0u, 0u);                 // bf16 zeros: adding them leaves dx_ln unchanged
-      if (dres != nullptr) rv = ld_stream(dres + row * nvec + c);
-      const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
-      uint32_t ow[4];
+      const f2 nc1r = bc2(-t1 * inv_c * rs[k]), nc2r = bc2(-t2 * inv_c * rs[k]);
+      const uint32_t xw[2] = {xv[k].x, xv[k].y}, gw[2] = {gv[k].x, gv[k].y}, rw[2] = {rv[k].x, rv[k].y};
+      uint32_t ow[2];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const f2 g = unpack2(gw[j]);
+      for (int j = 0; j < 2; ++j) {
+        const f2 g2 = unpack2(gw[j]);
         const f2 xh = fma2(unpack2(xw[j]), rsk, nmk);
-        ow[j] = pack2(add2(fma2(xh, nc2r, fma2(mul2(g, a1[j]), rsk, nc1r)), unpack2(rw[j])));
-        dsc[j] = fma2(g, xh, dsc[j]);
-        dsh[j] = add2(dsh[j], g);
+        ow[j] = pack2(add2(fma2(xh, nc2r, fma2(mul2(g2, a1[j]), rsk, nc1r)), unpack2(rw[j])));
+        dsc[j] = fma2(g2, xh, dsc[j]);
+        dsh[j] = add2(dsh[j], g2);
       }
-      st_stream(dx + row * nvec + c, make_uint4(ow[0], ow[1], ow[2], ow[3]));
+      asm volatile("st.global.cs.v2.u32 [%0], {%1, %2};" ::"l"(dx + row * C + 4 * c), "r"(ow[0]), "r"(ow[1]) : "memory");
     }
+    if (++slot == slots) { slot = 0; phase ^= 1u; }
   }
-  if (live) {
-    const int64_t o = ((int64_t)split * gridDim.y + b) * (nvec * 8) + c * 8;
-    float4 q0, q1;
-    un2(dsc[0], q0.x, q0.y); un2(dsc[1], q0.z, q0.w); un2(dsc[2], q1.x, q1.y); un2(dsc[3], q1.z, q1.w);
-    *reinterpret_cast<float4*>(part0 + o) = q0;
-    *reinterpret_cast<float4*>(part0 + o + 4) = q1;
-    un2(dsh[0], q0.x, q0.y); un2(dsh[1], q0.z, q0.w); un2(dsh[2], q1.x, q1.y); un2(dsh[3], q1.z, q1.w);
-    *reinterpret_cast<float4*>(part1 + o) = q0;
-    *reinterpret_cast<float4*>(part1 + o + 4) = q1;
+  if (live) {   // partial of this split: the finish kernel adds gridDim.x partials in index order
+    const int64_t o = ((int64_t)split * gridDim.y + b) * C + c * 4;
+    float4 q;
+    un2(dsc[0], q.x, q.y); un2(dsc[1], q.z, q.w);
+    *reinterpret_cast<float4*>(part0 + o) = q;
+    un2(dsh[0], q.x, q.y); un2(dsh[1], q.z, q.w);
+    *reinterpret_cast<float4*>(part1 + o) = q;
   }
 }
 
@@ -559,27 +616,36 @@ extern "C" int yat_ln_modulate_bwd_res(const void* x, const void* dy, const void
   const int splits = ln_bwd_splits(B, N, C);
   float* part0 = (float*)workspace;
   {
-    const int threads = (nvec + 31) / 32 * 32;
-    const int per_sm = threads <= 320 ? 2 : 1;                     // resident CTAs (launch bounds of the two instantiations)
-    int sp = (kNumSMs * per_sm) / B;
+    const int threads = (C / 4 + 31) / 32 * 32;
+    const int slots = ln_bwd_slots(C);
+    YAT_REQUIRE(slots >= 2 && threads <= 1024, YAT_ERR_UNSUPPORTED,
+                "yat_ln_modulate_bwd: C=%d does not fit the shared-memory row ring", C);
+    const int64_t smem = ln_bwd_smem_bytes(slots, C);
+    int sp = kNumSMs / B;                                          // one CTA per SM
     const int cap = (N + kLnRows - 1) / kLnRows;
     sp = sp > cap ? cap : sp;
-    sp = sp > splits ? splits : sp;                                // the workspace is sized for `splits`
+    sp = sp > splits ? splits : sp;                                // the workspace is sized for `splits` partials
     sp = sp < 1 ? 1 : sp;
     const int rps = (N + sp - 1) / sp;
     float* p1 = part0 + (int64_t)sp * B * C;
-    if (threads <= 288)     // SANA-1.6B: C = 2240 -> 280 vectors; 2 x 288 threads leave 112 registers per thread (no spills)
-      ln_modulate_bwd_cols_kernel<112><<<dim3(sp, B), threads, 0, st>>>(
-          (const uint4*)x, (const uint4*)dy, (const uint4*)scale, mod_batch_stride / 8, mean, rstd, N, nvec, rps, 1.0f / C,
-          (const uint4*)dres, (uint4*)dx, part0, p1);
-    else if (threads <= 320)
-      ln_modulate_bwd_cols_kernel<96><<<dim3(sp, B), threads, 0, st>>>(
-          (const uint4*)x, (const uint4*)dy, (const uint4*)scale, mod_batch_stride / 8, mean, rstd, N, nvec, rps, 1.0f / C,
-          (const uint4*)dres, (uint4*)dx, part0, p1);
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaError_t e =
+          cudaFuncSetAttribute(ln_modulate_bwd_ring_kernel<640>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+      if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(ln_modulate_bwd_ring_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+      YAT_REQUIRE(e == cudaSuccess, YAT_ERR_CUDA, "yat_ln_modulate_bwd: shared memory opt-in failed (%s)",
+                  cudaGetErrorString(e));
+      attr_set = true;
+    }
+    if (threads <= 640)    // SANA-1.6B: C = 2240 -> 560 columns-of-4, 576 threads, no register spills
+      ln_modulate_bwd_ring_kernel<640><<<dim3(sp, B), threads, smem, st>>>(
+          (const __nv_bfloat16*)x, (const __nv_bfloat16*)dy, (const __nv_bfloat16*)scale, mod_batch_stride, mean, rstd, N,
+          C, slots, rps, 1.0f / C, (const __nv_bfloat16*)dres, (__nv_bfloat16*)dx, part0, p1);
     else
-      ln_modulate_bwd_cols_kernel<128><<<dim3(sp, B), threads, 0, st>>>(
-          (const uint4*)x, (const uint4*)dy, (const uint4*)scale, mod_batch_stride / 8, mean, rstd, N, nvec, rps, 1.0f / C,
-          (const uint4*)dres, (uint4*)dx, part0, p1);
+      ln_modulate_bwd_ring_kernel<1024><<<dim3(sp, B), threads, smem, st>>>(
+          (const __nv_bfloat16*)x, (const __nv_bfloat16*)dy, (const __nv_bfloat16*)scale, mod_batch_stride, mean, rstd, N,
+          C, slots, rps, 1.0f / C, (const __nv_bfloat16*)dres, (__nv_bfloat16*)dx, part0, p1);
     rc = check_launch("ln_modulate_bwd_cols");
     if (rc != YAT_OK) return rc;
     const int64_t bc2_ = (int64_t)B * C;

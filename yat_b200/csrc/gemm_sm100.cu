@@ -33,18 +33,20 @@ constexpr int kBK = 64;                  // K elements per stage = one 128-byte 
 constexpr int kABytes = kBM * kBK * 2;   // 16 KB
 constexpr int kWSlot = 128 * kBK * 2;    // 16 KB slot for up to 128 W rows (BN / 2)
 constexpr int kStageBytes = kABytes + kWSlot;
-constexpr int kGemmStages = 6;
+constexpr int kMaxGemmStages = 7;
 constexpr int kGemmThreads = 256;
 constexpr int kAccStride = 256;          // TMEM columns between the two accumulators
 
+template <int STAGES>
 struct GemmSmem {
-  uint8_t stage[kGemmStages][kStageBytes];       // 1024-aligned
-  uint64_t full[kGemmStages], empty[kGemmStages];
+  uint8_t stage[STAGES][kStageBytes];            // 1024-aligned
+  uint64_t full[STAGES], empty[STAGES];
   uint64_t tmem_full[2], tmem_empty[2];
   uint32_t tmem_base;
 };
-constexpr int kGemmSmemBytes = (int)sizeof(GemmSmem) + 1024;
-static_assert(kGemmSmemBytes <= 232448, "GEMM shared memory exceeds the 227 KB per-CTA limit");
+template <int STAGES>
+constexpr int gemm_smem_bytes() { return (int)sizeof(GemmSmem<STAGES>) + 1024; }
+static_assert(gemm_smem_bytes<kMaxGemmStages>() <= 232448, "GEMM shared memory exceeds the 227 KB per-CTA limit");
 
 // ---- cluster / cta_group::2 primitives (the cta_group::1 ones live in sm100.cuh) ----
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -108,7 +110,7 @@ struct GemmMaps {
 };
 
 // BN: tile width (multiple of 32, <= 256; BN / 2 W rows per CTA)
-template <int BN>
+template <int BN, int kGemmStages>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_tn_sm100_kernel(const __grid_constant__ GemmMaps maps, const __nv_bfloat16* __restrict__ bias,
                           __nv_bfloat16* __restrict__ c, int M, int N, int K, int64_t ldc) {
@@ -118,7 +120,8 @@ gemm_bf16_tn_sm100_kernel(const __grid_constant__ GemmMaps maps, const __nv_bflo
   constexpr uint32_t kTxBytes = 2u * (kABytes + kHalfN * kBK * 2);     // both CTAs' loads of one stage
 
   extern __shared__ uint8_t smem_raw[];
-  GemmSmem& S = *reinterpret_cast<GemmSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  using Smem = GemmSmem<kGemmStages>;
+  Smem& S = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const bool leader = rank == 0;
@@ -287,20 +290,20 @@ static int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t cols, 
   return YAT_OK;
 }
 
-template <int BN>
+template <int BN, int STAGES>
 static int launch_gemm(const GemmMaps& maps, const void* bias, void* c, int M, int N, int K, int64_t ldc,
                        cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    const cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tn_sm100_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                               kGemmSmemBytes);
+    const cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tn_sm100_kernel<BN, STAGES>,
+                                               cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_bytes<STAGES>());
     YAT_REQUIRE(e == cudaSuccess, YAT_ERR_CUDA, "yat_gemm_bf16_tn: cannot reserve %d B of shared memory (%s)",
-                kGemmSmemBytes, cudaGetErrorString(e));
+                gemm_smem_bytes<STAGES>(), cudaGetErrorString(e));
     attr_set = true;
   }
   const int tiles = ((M + 255) / 256) * ((N + BN - 1) / BN);
   const int clusters = tiles < kNumSMs / 2 ? tiles : kNumSMs / 2;
-  gemm_bf16_tn_sm100_kernel<BN><<<2 * clusters, kGemmThreads, kGemmSmemBytes, st>>>(
+  gemm_bf16_tn_sm100_kernel<BN, STAGES><<<2 * clusters, kGemmThreads, gemm_smem_bytes<STAGES>(), st>>>(
       maps, (const __nv_bfloat16*)bias, (__nv_bfloat16*)c, M, N, K, ldc);
   return check_launch("gemm_bf16_tn_sm100");
 }
@@ -319,7 +322,10 @@ extern "C" int yat_gemm_bf16_tn(const void* a, const void* w, const void* bias, 
   YAT_REQUIRE((((uintptr_t)a | (uintptr_t)w) & 15u) == 0 && ((uintptr_t)c & 31u) == 0 &&
                   (bias == nullptr || ((uintptr_t)bias & 3u) == 0),
               YAT_ERR_BAD_ARG, "yat_gemm_bf16_tn: a / w must be 16-byte aligned, c 32-byte, bias 4-byte");
-  if (tile_n == 0) tile_n = (N % 224 == 0 && N % 256 != 0) ? 224 : 256;     // SANA widths are multiples of 224 = 7 x 32
+  int stages = 6;
+  if (tile_n >= 1000) { stages = tile_n / 1000; tile_n %= 1000; }           // development: tile_n + 1000 * stages
+  if (tile_n == 0) tile_n = 256;     // measured: 256 beats 224 even where 224 divides N (profiles/r02_gemm_ab.json)
+  YAT_REQUIRE(stages >= 4 && stages <= 7, YAT_ERR_UNSUPPORTED, "yat_gemm_bf16_tn: %d stages not supported", stages);
   YAT_REQUIRE(tile_n == 256 || tile_n == 224 || tile_n == 128, YAT_ERR_UNSUPPORTED,
               "yat_gemm_bf16_tn: tile_n %d not supported (256, 224, 128)", tile_n);
   GemmMaps maps;
@@ -327,7 +333,10 @@ extern "C" int yat_gemm_bf16_tn(const void* a, const void* w, const void* bias, 
   if ((rc = make_tmap_2d_bf16(&maps.a, a, (uint64_t)K, (uint64_t)M, (uint64_t)lda, kBM)) != YAT_OK) return rc;
   if ((rc = make_tmap_2d_bf16(&maps.w, w, (uint64_t)K, (uint64_t)N, (uint64_t)ldw, (uint32_t)tile_n / 2)) != YAT_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  if (tile_n == 256) return launch_gemm<256>(maps, bias, c, (int)M, N, K, ldc, st);
-  if (tile_n == 224) return launch_gemm<224>(maps, bias, c, (int)M, N, K, ldc, st);
-  return launch_gemm<128>(maps, bias, c, (int)M, N, K, ldc, st);
+#define YAT_GEMM_CASE(BN, ST) if (tile_n == BN && stages == ST) return launch_gemm<BN, ST>(maps, bias, c, (int)M, N, K, ldc, st)
+  YAT_GEMM_CASE(256, 6); YAT_GEMM_CASE(224, 6); YAT_GEMM_CASE(128, 6);
+  YAT_GEMM_CASE(256, 7); YAT_GEMM_CASE(224, 7); YAT_GEMM_CASE(256, 5); YAT_GEMM_CASE(224, 5); YAT_GEMM_CASE(224, 4);
+#undef YAT_GEMM_CASE
+  YAT_REQUIRE(false, YAT_ERR_UNSUPPORTED, "yat_gemm_bf16_tn: tile_n %d with %d stages is not built", tile_n, stages);
+  return YAT_ERR_UNSUPPORTED;
 }
