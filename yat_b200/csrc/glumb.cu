@@ -76,6 +76,16 @@ __device__ __forceinline__ f2 silu_grad_from_sigmoid2(f2 x, f2 sg) {
   const f2 one = bc2(1.0f);
   return mul2(sg, fma2(x, fma2(sg, bc2(-1.0f), one), one));
 }
+// With h = x / 2, th = tanh(h):  silu(x) = h + h th  and  2 silu'(x) = 1 + r,  r = th + h (1 - th^2).  The backward
+// works from nh = -h (one multiply by -0.5; the special-function op takes the negated source for free), so that no
+// operand ever needs a separate negation:  -silu(x) = nh + nh th,  r = th + nh (th^2 - 1).  Signs and the factors
+// 1/2 are carried in the conv weights and in the final scale of dw / db (powers of two: exact).
+__device__ __forceinline__ f2 tanh2_neg(f2 nh) {                 // tanh(-nh)
+  float a, b;
+  un2(nh, a, b);
+  return mk2(tanh_approx(-a), tanh_approx(-b));
+}
+__device__ __forceinline__ f2 silu_grad_r(f2 nh, f2 th) { return fma2(nh, fma2(th, th, bc2(-1.0f)), th); }
 __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
   uint32_t r;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(r) : "r"(addr));
@@ -203,28 +213,31 @@ __global__ void __launch_bounds__(kThreads, 2) glumb_fwd_kernel(const __grid_con
     const int s_idx = 3 * (m & 1) + j;
     mbar_wait(ring.full + 8 * s_idx, (uint32_t)(m >> 1) & 1u);
     const uint32_t col = my_rows + s_idx * kFwdSlotB;
-    f2 s[kIn][2];
+    uint32_t raw[2][kIn];
 #pragma unroll
     for (int i = 0; i < kIn; ++i) {
-      const uint32_t ra = lds32(col + i * kRowB), rg = lds32(col + (kInCta + i) * kRowB);
-      s[i][0] = silu2(unpack2(ra));
-      s[i][1] = silu2(unpack2(rg));
+      raw[0][i] = lds32(col + i * kRowB);
+      raw[1][i] = lds32(col + (kInCta + i) * kRowB);
     }
     __syncwarp();                                                 // every lane has read the slot
     if (lane == 0) mbar_arrive(ring.empty + 8 * s_idx);
 #pragma unroll
-    for (int r = 0; r < kR; ++r)
+    for (int j = 0; j < 2; ++j) {                                 // A channels, then their gates: 6 activations live at a time
+      f2 s[kIn];
 #pragma unroll
-      for (int j = 0; j < 2; ++j) {
+      for (int i = 0; i < kIn; ++i) s[i] = silu2(unpack2(raw[j][i]));
+#pragma unroll
+      for (int r = 0; r < kR; ++r) {
         f2 pa = aP[r][j], cc = aC[r][j], n = bias[j];
 #pragma unroll
         for (int ky = 0; ky < 3; ++ky) {
-          pa = fma2(w[3 * ky + 2][j], s[r + ky][j], pa);
-          cc = fma2(w[3 * ky + 1][j], s[r + ky][j], cc);
-          n = fma2(w[3 * ky + 0][j], s[r + ky][j], n);
+          pa = fma2(w[3 * ky + 2][j], s[r + ky], pa);
+          cc = fma2(w[3 * ky + 1][j], s[r + ky], cc);
+          n = fma2(w[3 * ky + 0][j], s[r + ky], n);
         }
         aP[r][j] = pa; aC[r][j] = cc; aN[r][j] = n;
       }
+    }
     if (x > 0) {
 #pragma unroll
       for (int r = 0; r < kR; ++r) {
@@ -289,7 +302,8 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbArgs& a, uint8_t* smem
     f2 w[9];
 #pragma unroll
     for (int k = 0; k < 9; ++k)
-      w[k] = live ? mk2(__bfloat162float(p.w[ch * 9 + k]), __bfloat162float(p.w[(ch + 1) * 9 + k])) : bc2(0.f);
+      w[k] = live ? mul2(bc2(KIND ? 0.25f : -0.5f), mk2(__bfloat162float(p.w[ch * 9 + k]), __bfloat162float(p.w[(ch + 1) * 9 + k])))
+                  : bc2(0.f);         // x 1/2: silu'(u) = (1 + r) / 2;  A half carries -dc (x -1), gate half 2 dc (x 1/2)
 
     const uint32_t col_b = (uint32_t)C2 * 2u, row_b = (uint32_t)W * col_b;
     char* out_u = reinterpret_cast<char*>(p.du + (((int64_t)b * H + y0) * W) * C2 + ch);
@@ -333,11 +347,12 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbArgs& a, uint8_t* smem
 #pragma unroll
       for (int i = 0; i < kIn; ++i) {
         const f2 g = unpack2(lds32(col + i * kRowB)), dm = unpack2(lds32(col + (kInCta + i) * kRowB));
+        const f2 nh = mul2(g, bc2(-0.5f)), th = tanh2_neg(nh);
         if (KIND) {
-          const f2 xa = unpack2(lds32(col + (2 * kInCta + kRowsCta + i) * kRowB));
-          cP[i] = mul2(mul2(dm, xa), silu_grad_from_sigmoid2(g, sigmoid2(g)));           // dmid * xa * silu'(g)
+          const f2 dmxa = mul2(dm, unpack2(lds32(col + (2 * kInCta + kRowsCta + i) * kRowB)));
+          cP[i] = fma2(dmxa, silu_grad_r(nh, th), dmxa);                                 // 2 dmid * xa * silu'(g)
         } else {
-          cP[i] = mul2(dm, silu2(g));                                                    // dmid * silu(g)
+          cP[i] = mul2(dm, fma2(nh, th, nh));                                            // -dmid * silu(g)
         }
       }
       uint32_t ru[kR];
@@ -349,21 +364,22 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbArgs& a, uint8_t* smem
         uint32_t o[kR];
 #pragma unroll
         for (int r = 0; r < kR; ++r) {
-          const f2 uu = unpack2(ru[r]);
-          const f2 sg = sigmoid2(uu);
-          const f2 sv = mul2(uu, sg), d = silu_grad_from_sigmoid2(uu, sg);
-          // three independent partial sums (one per kernel row) keep the dependent chain at 3 FMAs
-          f2 ak[3];
+          const f2 nh = mul2(unpack2(ru[r]), bc2(-0.5f)), th = tanh2_neg(nh);
+          const f2 sv = fma2(nh, th, nh), rr = silu_grad_r(nh, th);   // -silu(u); 2 silu'(u) - 1
+          f2 acc;                                                 // the four rows' chains interleave (one basic block)
 #pragma unroll
           for (int ky = 0; ky < 3; ++ky) {
             const f2 d0 = cP[r - ky + 2], d1 = cC[r - ky + 2], d2 = cM[r - ky + 2];
-            ak[ky] = fma2(w[3 * ky + 2], d2, fma2(w[3 * ky + 1], d1, mul2(w[3 * ky + 0], d0)));
+            acc = ky ? fma2(w[3 * ky + 0], d0, acc) : mul2(w[0], d0);
+            acc = fma2(w[3 * ky + 1], d1, acc);
+            acc = fma2(w[3 * ky + 2], d2, acc);
             dw[3 * ky + 0] = fma2(sv, d0, dw[3 * ky + 0]);
             dw[3 * ky + 1] = fma2(sv, d1, dw[3 * ky + 1]);
             dw[3 * ky + 2] = fma2(sv, d2, dw[3 * ky + 2]);
           }
           db = add2(db, cC[r + 1]);
-          const f2 ov = mul2(add2(add2(ak[0], ak[1]), ak[2]), d);
+          const f2 ov = fma2(acc, rr, acc);                       // (w/2 (*) dc) (1 + r) = ds * silu'(u)
+          // dw accumulates (-silu(u)) * (-dc) (A half) or (-silu(u)) * (2 dc) (gate half, final scale -1/2)
           if ((omask >> r) & 1u) dbu = add2(dbu, ov);             // column sum of du = bias gradient of conv_inverted
                                                                   // (a row below the image still sees dc of the last row)
           o[r] = pack2(ov);
@@ -390,6 +406,8 @@ __device__ __forceinline__ void glumb_bwd_body(const GlumbArgs& a, uint8_t* smem
     for (int g = 0; g < kPart; ++g) {
       float lo, hi;
       un2(g < 9 ? dw[g] : (g == 9 ? db : dbu), lo, hi);
+      const float fs = KIND ? (g < 9 ? -0.5f : (g == 9 ? 0.5f : 1.f)) : (g == 9 ? -1.f : 1.f);   // see the sign / scale notes above
+      lo *= fs; hi *= fs;
       red[warp][2 * g + 0][lane] = live ? lo : 0.f;
       red[warp][2 * g + 1][lane] = live ? hi : 0.f;
     }
