@@ -21,7 +21,10 @@
 // reference's `.float()` matmuls.
 //
 // Roles (352 threads): warp 0 TMA producer, warp 1 tcgen05 issuer, warps 2..9 transform/epilogue,
-// warp 10 TMA-store + slot release.  Parity waits follow one rule: every waiter observes every phase of
+// warp 10 TMA-store + slot release.  Passes B and C are software-pipelined by one tile: the epilogue warps
+// transform tile t+1 (relu, den) before they finish tile t, the issuer orders the tensor pipe dQ~(t), num(t+1),
+// dKV(t), and pass C double-buffers its dV / dK accumulators in TMEM - the MMA + mbarrier round trips that used
+// to sit between E1 -> E2 -> E3 of one tile now overlap the neighbouring tile's CUDA-core work.  Parity waits follow one rule: every waiter observes every phase of
 // the barriers it waits on, in order.
 #include <cstdio>
 #include <cstdlib>
@@ -49,21 +52,23 @@ constexpr uint32_t kColKV = 0;     // pass A accumulator; pass C: dV
 constexpr uint32_t kColDKV = 128;  // pass B accumulator
 constexpr uint32_t kColNum = 256;  // pass B: num, pass C: dK
 constexpr uint32_t kColDQ = 384;   // pass B: dQ~
-constexpr uint32_t kColDK = 256;
+// pass C accumulators, double-buffered by tile parity: dV at 0 / 128, dK at 256 / 384 (dKV and dQ~ are dead by then)
 constexpr uint32_t kColDV = 0;
+constexpr uint32_t kColDK = 256;
+constexpr uint32_t kColBuf = 128;
 
 struct BwdSmem {
   uint8_t slots[kStages][kSlotBytes];           // 1024-aligned
   uint8_t lo[kSlotBytes];                       // low halves of Q~ = r * relu(Q)
   uint8_t bmat[kHeadsPerItem][2][kBmatBytes];   // [head][hi|lo] 32x32: KV in pass B, dKV in pass C
-  float den[kTile][kHeadsPerItem];
-  float wrow[kTile][kHeadsPerItem];             // dDen / r per row and head (weights of the dKs sum)
+  float den[2][kTile][kHeadsPerItem];           // by tile parity: E1 of tile t+1 runs before E2 of tile t
+  float wrow[2][kTile][kHeadsPerItem];          // dDen / r per row and head (weights of the dKs sum)
   float ks[kHeadsPerItem * kD];
   float dks[kHeadsPerItem * kD];
   float red[kEpiWarps][kHeadsPerItem * kD];
   uint64_t full[kStages], empty[kStages], ready[kStages], out_ready[kStages];
   uint64_t kv_full, b_ready, dkv_full, b2_ready;
-  uint64_t num_full, num_empty, dq_full, dq_empty, pair_done, c_full, c_empty;
+  uint64_t num_full, num_empty, dq_full, dq_empty, pair_done, c_full[2], c_empty[2];
   uint32_t tmem_base;
 };
 constexpr int kBwdSmemBytes = (int)sizeof(BwdSmem) + 1024;
@@ -135,8 +140,10 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
     mbar_init(smem_u32(&S.dq_full), 1);
     mbar_init(smem_u32(&S.dq_empty), kEpiWarps);
     mbar_init(smem_u32(&S.pair_done), 1);
-    mbar_init(smem_u32(&S.c_full), 1);
-    mbar_init(smem_u32(&S.c_empty), kEpiWarps);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(smem_u32(&S.c_full[i]), 1);
+      mbar_init(smem_u32(&S.c_empty[i]), kEpiWarps);
+    }
     fence_barrier_init();
     tma_prefetch_desc(&M.q); tma_prefetch_desc(&M.k); tma_prefetch_desc(&M.v); tma_prefetch_desc(&M.d_o);
     tma_prefetch_desc(&M.dq); tma_prefetch_desc(&M.dk); tma_prefetch_desc(&M.dv);
@@ -208,8 +215,8 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         }
       };
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++item_iter) {
-        // TMEM columns [0,128) were dV of the previous item's last tile: wait until it has been read
-        mbar_wait(smem_u32(&S.c_empty), (ct & 1) ^ 1);
+        // TMEM columns [0,128) held dV of the previous item: its epilogue has run, because the first MMA below waits for
+        // ready[] of THIS item's pass A, which every epilogue warp signals only after finishing the previous item.
         // ---- pass A: D_KV += relu(K)^T V
         for (int t = 0; t < n_tiles; ++t, it += 2) {
           const uint32_t sk = it % kStages, sv = (it + 1) % kStages, pv = ((it + 1) / kStages) & 1;
@@ -229,20 +236,32 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         tc_commit(smem_u32(&S.kv_full));
         mbar_wait(smem_u32(&S.b_ready), item_iter & 1);
         tc_fence_after();
-        // ---- pass B
+        // ---- pass B.  Tensor-pipe order per tile: dQ~(t), num(t+1), dKV(t) - the epilogue warps transform tile t+1
+        // (E1) before they finish tile t, so num(t+1) is in TMEM by the time E2(t+1) wants it.
+        {
+          const uint32_t sq0 = it % kStages;
+          wait_ready(sq0);                                       // relu(Q) in place, den written
+          mbar_wait(smem_u32(&S.num_empty), (bt & 1) ^ 1);
+          tc_fence_after();
+          small_mmas(kColNum, smem_u32(&S.slots[sq0][0]), false);   // num = relu(Q) KV
+          tc_commit(smem_u32(&S.num_full));
+        }
         for (int t = 0; t < n_tiles; ++t, it += 2, ++bt) {
           const uint32_t sq = it % kStages, sd = (it + 1) % kStages;
           const uint32_t qa = smem_u32(&S.slots[sq][0]), da_ = smem_u32(&S.slots[sd][0]), la = smem_u32(&S.lo[0]);
-          wait_ready(sq);                                        // relu(Q) in place, den written
-          mbar_wait(smem_u32(&S.num_empty), (bt & 1) ^ 1);
-          tc_fence_after();
-          small_mmas(kColNum, qa, false);           // num = relu(Q) KV
-          tc_commit(smem_u32(&S.num_full));
           wait_ready(sd);                                        // Q~ hi (Q slot) / lo written, dO landed
           mbar_wait(smem_u32(&S.dq_empty), (bt & 1) ^ 1);
           tc_fence_after();
           small_mmas(kColDQ, da_, true);             // dQ~ = dO KV^T
           tc_commit(smem_u32(&S.dq_full));
+          if (t + 1 < n_tiles) {
+            const uint32_t sq1 = (it + 2) % kStages;
+            wait_ready(sq1);
+            mbar_wait(smem_u32(&S.num_empty), ((bt + 1) & 1) ^ 1);
+            tc_fence_after();
+            small_mmas(kColNum, smem_u32(&S.slots[sq1][0]), false);
+            tc_commit(smem_u32(&S.num_full));
+          }
 #pragma unroll
           for (int part = 0; part < 2; ++part) {                 // D_dKV += (Q~hi + Q~lo)^T dO
             const uint32_t aa = part ? la : qa;
@@ -261,13 +280,14 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         // ---- pass C: dV = relu(K) dKV, dK~ = V dKV^T
         for (int t = 0; t < n_tiles; ++t, it += 2, ++ct) {
           const uint32_t sk = it % kStages, sv = (it + 1) % kStages, pv = ((it + 1) / kStages) & 1;
+          const uint32_t buf = ct & 1;
           wait_ready(sk);
           mbar_wait(smem_u32(&S.full[sv]), pv);
-          mbar_wait(smem_u32(&S.c_empty), (ct & 1) ^ 1);
+          mbar_wait(smem_u32(&S.c_empty[buf]), ((ct >> 1) & 1) ^ 1);
           tc_fence_after();
-          small_mmas(kColDV, smem_u32(&S.slots[sk][0]), false);
-          small_mmas(kColDK, smem_u32(&S.slots[sv][0]), true);
-          tc_commit(smem_u32(&S.c_full));
+          small_mmas(kColDV + buf * kColBuf, smem_u32(&S.slots[sk][0]), false);
+          small_mmas(kColDK + buf * kColBuf, smem_u32(&S.slots[sv][0]), true);
+          tc_commit(smem_u32(&S.c_full[buf]));
         }
       }
     }
@@ -301,11 +321,11 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           wait_out(sk);
           store(&M.dk, sk, c0, t * kTile, b);
           tma_store_commit();
+          tma_store_wait_read<0>();                      // dV's epilogue is still running: release the K slot now
+          mbar_arrive(smem_u32(&S.empty[sk]));
           wait_out(sv);
           store(&M.dv, sv, c0, t * kTile, b);
           tma_store_commit();
-          tma_store_wait_read<1>();
-          mbar_arrive(smem_u32(&S.empty[sk]));
           tma_store_wait_read<0>();
           mbar_arrive(smem_u32(&S.empty[sv]));
         }
@@ -392,33 +412,40 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
 #pragma unroll
       for (int j = 0; j < 8; ++j) ksr[j] = S.ks[cc * 8 + j];
       // ---------------- pass B ----------------
+      // Software-pipelined by one tile: E1(t+1) (relu(Q), den) runs BEFORE E2(t) / E3(t), so the num MMA of tile t+1
+      // and its mbarrier round trip overlap this tile's epilogue instead of sitting on the critical path.
       float dcs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-      for (int t = 0; t < n_tiles; ++t, it += 2, ++bt) {
-        const uint32_t sq = it % kStages, pq = (it / kStages) & 1;
-        const uint32_t sd = (it + 1) % kStages, pd = ((it + 1) / kStages) & 1;
-        // E1: relu(Q) in place, den = relu(Q).Ks
+      // E1: relu(Q) in place, den = relu(Q).Ks  (tile with ring index `jt`, den buffer `db`)
+      auto e1 = [&](uint32_t jt, int db) {
+        const uint32_t sq = jt % kStages, pq = (jt / kStages) & 1;
         mbar_wait(smem_u32(&S.full[sq]), pq);
-        {
-          uint8_t* base = &S.slots[sq][half * kHalfBytes];
+        uint8_t* base = &S.slots[sq][half * kHalfBytes];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int r = rbase + 16 * i;
-            uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
-            const uint4 v = relu8(*p);
-            *p = v;
-            float f[8], d = 0.f;
-            unpack8f(v, f);
+        for (int i = 0; i < 8; ++i) {
+          const int r = rbase + 16 * i;
+          uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
+          const uint4 v = relu8(*p);
+          *p = v;
+          float f[8], d = 0.f;
+          unpack8f(v, f);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) d = fmaf(f[j], ksr[j], d);
-            d += __shfl_xor_sync(0xffffffffu, d, 1);
-            d += __shfl_xor_sync(0xffffffffu, d, 2);
-            if ((cc & 3) == 0) S.den[r][hsel] = d;
-          }
+          for (int j = 0; j < 8; ++j) d = fmaf(f[j], ksr[j], d);
+          d += __shfl_xor_sync(0xffffffffu, d, 1);
+          d += __shfl_xor_sync(0xffffffffu, d, 2);
+          if ((cc & 3) == 0) S.den[db][r][hsel] = d;
         }
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&S.ready[sq]));
-        named_bar_sync(1, kEpiThreads);         // den visible in the row mapping
+      };
+      e1(it, bt & 1);
+      for (int t = 0; t < n_tiles; ++t, it += 2, ++bt) {
+        const uint32_t sq = it % kStages;
+        const uint32_t sd = (it + 1) % kStages, pd = ((it + 1) / kStages) & 1;
+        const int db = bt & 1;
+        if (t + 1 < n_tiles) e1(it + 2, db ^ 1);
+        // den(t) visible in the row mapping; every warp is past E3a(t-1), so S.lo may be rewritten below
+        named_bar_sync(1, kEpiThreads);
 
         // E2: num -> r, dDen; Q~ = r * relu(Q) as bf16 hi (in place) + lo
         mbar_wait(smem_u32(&S.full[sd]), pd);
@@ -443,10 +470,10 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
 #pragma unroll
             for (int j = 0; j < 8; ++j) s = fmaf(f[j], __uint_as_float(acc[g * 8 + j]), s);
           }
-          const float r = 1.0f / (S.den[row][h] + 1e-15f);
+          const float r = 1.0f / (S.den[db][row][h] + 1e-15f);
           rr[hh] = r;
           dd[hh] = -s * r * r;
-          S.wrow[row][h] = -s * r;
+          S.wrow[db][row][h] = -s * r;
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             const int o = ((hh * 4 + g) ^ (row & 7)) << 4;
@@ -487,7 +514,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
             float fh[8], fl[8];
             unpack8f(*reinterpret_cast<const uint4*>(bh + o), fh);
             unpack8f(*reinterpret_cast<const uint4*>(bl + o), fl);
-            const float w = S.wrow[r][hsel];
+            const float w = S.wrow[db][r][hsel];
 #pragma unroll
             for (int j = 0; j < 8; ++j) dcs[j] = fmaf(fh[j] + fl[j], w, dcs[j]);
           }
@@ -538,24 +565,29 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
       build_bmat(kColDKV);                      // barrier inside: dks visible, D_dKV drained, bmat rewritten
       if (lane == 0) mbar_arrive(smem_u32(&S.b2_ready));
       // ---------------- pass C ----------------
-      for (int t = 0; t < n_tiles; ++t, it += 2, ++ct) {
-        const uint32_t sk = it % kStages, pk = (it / kStages) & 1;
-        const uint32_t sv = (it + 1) % kStages, pv = ((it + 1) / kStages) & 1;
+      // Same skew: relu(K) of tile t+1 is done before the epilogue of tile t, and the dV / dK accumulators are
+      // double-buffered in TMEM (tile parity), so the issuer runs the MMAs of tile t+1 during this tile's epilogue.
+      auto relu_k = [&](uint32_t jt) {
+        const uint32_t sk = jt % kStages, pk = (jt / kStages) & 1;
         mbar_wait(smem_u32(&S.full[sk]), pk);
-        {
-          uint8_t* base = &S.slots[sk][half * kHalfBytes];
+        uint8_t* base = &S.slots[sk][half * kHalfBytes];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int r = rbase + 16 * i;
-            uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
-            *p = relu8(*p);
-          }
+        for (int i = 0; i < 8; ++i) {
+          const int r = rbase + 16 * i;
+          uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
+          *p = relu8(*p);
         }
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&S.ready[sk]));
-        mbar_wait(smem_u32(&S.full[sv]), pv);       // observe the V phase
-        mbar_wait(smem_u32(&S.c_full), ct & 1);     // both MMAs done: K and V tiles may be overwritten
+      };
+      relu_k(it);
+      for (int t = 0; t < n_tiles; ++t, it += 2, ++ct) {
+        const uint32_t sk = it % kStages, sv = (it + 1) % kStages;
+        const uint32_t buf = ct & 1;
+        if (t + 1 < n_tiles) relu_k(it + 2);
+        mbar_wait(smem_u32(&S.full[sv]), ((it + 1) / kStages) & 1);   // observe the V phase (complete: the MMA read it)
+        mbar_wait(smem_u32(&S.c_full[buf]), (ct >> 1) & 1);   // both MMAs done: K and V tiles may be overwritten
         tc_fence_after();
         // dK = (V dKV^T + dKs) * [k > 0]  -> K slot
         uint8_t* krow = &S.slots[sk][row_off];
@@ -563,7 +595,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         for (int hh = 0; hh < 2; ++hh) {
           const int h = colhalf * 2 + hh;
           uint32_t acc[32];
-          tmem_ld32(tmem + lane_addr + kColDK + h * kD, acc);
+          tmem_ld32(tmem + lane_addr + kColDK + buf * kColBuf + h * kD, acc);
           tmem_ld_wait();
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
@@ -585,7 +617,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         for (int hh = 0; hh < 2; ++hh) {
           const int h = colhalf * 2 + hh;
           uint32_t acc[32];
-          tmem_ld32(tmem + lane_addr + kColDV + h * kD, acc);
+          tmem_ld32(tmem + lane_addr + kColDV + buf * kColBuf + h * kD, acc);
           tmem_ld_wait();
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
@@ -599,7 +631,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) {
-          mbar_arrive(smem_u32(&S.c_empty));
+          mbar_arrive(smem_u32(&S.c_empty[buf]));
           mbar_arrive(smem_u32(&S.out_ready[sv]));
         }
       }
