@@ -41,6 +41,9 @@ def build(force=False, verbose=False):
     tmp = f"{OUT}.{os.getpid()}.tmp"          # link to a private name, then rename: readers never see a partial file
     cmd = [_nvcc(), *ARCH, "-O3", "-std=c++17", "-lineinfo", "-shared", "-Xcompiler", "-fPIC",
            "--threads", "0", "-o", tmp, *srcs]
+    extra = os.environ.get("YAT_NVCC_FLAGS")     # experiments only (e.g. -DYAT_BWD_PROBE); the release build sets nothing
+    if extra:
+        cmd[1:1] = extra.split()
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")

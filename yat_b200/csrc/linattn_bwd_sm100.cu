@@ -13,15 +13,19 @@
 // Work item = (batch, 4 heads) = a 128-column stripe, streamed in 128-token tiles through a ring of 32 KB
 // shared-memory slots ([2 halves][128 tokens][64 cols], SWIZZLE_128B), exactly like the forward kernel:
 //   pass A   K V  pairs -> D_KV [128x128] += relu(K)^T V (diagonal 32x32 blocks = per-head KV), Ks
-//   pass B   Q dO pairs -> num = Q KV -> r, dDen; Q~ = r Q split into bf16 hi (in place) + lo;
-//            dQ~ = dO KV^T (raw dO, exact) ; D_dKV += (Q~hi + Q~lo)^T dO ; dQ leaves from the dO slot
+//   pass B   Q dO pairs -> num = Q KV -> r, dDen; Q~ = bf16(r Q) in place;
+//            dQ~ = dO KV^T (raw dO, exact) ; D_dKV += Q~^T dO ; dQ leaves from the dO slot
 //   pass C   K V  pairs -> dV = relu(K) dKV, dK = V dKV^T + dKs ; both leave from their own slots
-// Every per-row scale is applied in fp32 (in the epilogue or through a hi/lo bf16 split), and the 32x32
-// KV / dKV operands are split hi/lo as well, so all five contractions keep ~fp32 accuracy like the
-// reference's `.float()` matmuls.
+// The 32x32 KV / dKV operands are split into bf16 hi + lo and the per-row scales of dQ are applied in the fp32
+// epilogue, so the contractions whose operand is an ACCUMULATED quantity keep ~fp32 accuracy like the reference's
+// `.float()` matmuls.  Q~ = r Q is rounded to bf16 once: its rounding errors are independent
+// per token and average out over the N-token sum of dKV / dKs (measured: dq, dk, dv at 1.66e-3 of the fp64
+// oracle at the SANA-1.6B size with or without a lo half, i.e. the bf16 rounding of the outputs themselves), and
+// the 32 KB the lo half occupied is the sixth ring slot (165 -> 154 us).
 //
-// Roles (352 threads): warp 0 TMA producer, warp 1 tcgen05 issuer, warps 2..9 transform/epilogue,
-// warp 10 TMA-store + slot release.  Passes B and C are software-pipelined by one tile: the epilogue warps
+// Roles (608 threads): warp 0 TMA producer, warp 1 tcgen05 issuer, warps 2..17 transform/epilogue (16 warps: the
+// CUDA-core work between the MMAs is what bounds the kernel, and 8 warps left the schedulers idle 70 % of the
+// time), warp 18 TMA-store + slot release.  Passes B and C are software-pipelined by one tile: the epilogue warps
 // transform tile t+1 (relu, den) before they finish tile t, the issuer orders the tensor pipe dQ~(t), num(t+1),
 // dKV(t), and pass C double-buffers its dV / dK accumulators in TMEM - the MMA + mbarrier round trips that used
 // to sit between E1 -> E2 -> E3 of one tile now overlap the neighbouring tile's CUDA-core work.  Parity waits follow one rule: every waiter observes every phase of
@@ -41,8 +45,11 @@ constexpr int kHeadsPerItem = 4;
 constexpr int kTile = 128;
 constexpr int kHalfBytes = kTile * 128;
 constexpr int kSlotBytes = 2 * kHalfBytes;
-constexpr int kStages = 5;
-constexpr int kEpiWarps = 8;
+constexpr int kStages = 6;
+constexpr int kEpiWarps = 16;                     // 4 per TMEM lane quadrant: one head each in the row mapping
+constexpr int kHH = 4 * kHeadsPerItem / kEpiWarps; // heads per thread in the row mapping (1)
+constexpr int kTRows = 16 * kTile / (kEpiWarps * 32); // rows per thread in the transform mapping (4)
+constexpr int kTStep = kTile / kTRows;             // row stride of the transform mapping (32)
 constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kThreads = 64 + kEpiThreads + 32;
 constexpr int kTmemCols = 512;
@@ -59,7 +66,6 @@ constexpr uint32_t kColBuf = 128;
 
 struct BwdSmem {
   uint8_t slots[kStages][kSlotBytes];           // 1024-aligned
-  uint8_t lo[kSlotBytes];                       // low halves of Q~ = r * relu(Q)
   uint8_t bmat[kHeadsPerItem][2][kBmatBytes];   // [head][hi|lo] 32x32: KV in pass B, dKV in pass C
   float den[2][kTile][kHeadsPerItem];           // by tile parity: E1 of tile t+1 runs before E2 of tile t
   float wrow[2][kTile][kHeadsPerItem];          // dDen / r per row and head (weights of the dKs sum)
@@ -117,12 +123,23 @@ struct BwdMaps {
 };
 
 __global__ void __launch_bounds__(kThreads, 1)
+#ifdef YAT_BWD_PROBE   // timing experiment build only (scripts/linattn_bwd_probe.py); never defined for the product library
+linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int groups, int probe_mask) {
+#else
 linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int groups) {
+#endif
   extern __shared__ uint8_t smem_raw[];
   BwdSmem& S = *reinterpret_cast<BwdSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_tiles = (N + kTile - 1) / kTile;
   const int n_items = B * groups;
+#ifdef YAT_BWD_PROBE   // timing experiment only (results are wrong): run a subset of the three passes
+  const int nA = (probe_mask & 1) ? n_tiles : 0, nB = (probe_mask & 2) ? n_tiles : 0, nC = (probe_mask & 4) ? n_tiles : 0;
+#define PROBE_SKIP(bit) (probe_mask & (bit))
+#else
+#define PROBE_SKIP(bit) false
+  const int nA = n_tiles, nB = n_tiles, nC = n_tiles;
+#endif
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -159,12 +176,15 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
 
   if (warp == 0) {
     // ======================= TMA producer =======================
+    // (An L2 prefetch of every tile pair 4 pairs ahead of its ring load - cp.async.bulk.prefetch.tensor - was measured
+    // and made every pass SLOWER, 165 -> 188 us: the prefetches queue in the same TMA unit as the loads.)
     if (lane == 0) {
       uint32_t it = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const int b = item / groups, c0 = (item % groups) * (kHeadsPerItem * kD);
         for (int pass = 0; pass < 3; ++pass) {
-          for (int t = 0; t < n_tiles; ++t) {
+          const int np = pass == 0 ? nA : (pass == 1 ? nB : nC);
+          for (int t = 0; t < np; ++t) {
 #pragma unroll
             for (int w = 0; w < 2; ++w, ++it) {
               const CUtensorMap* tm = pass == 1 ? (w ? &M.d_o : &M.q) : (w ? &M.v : &M.k);
@@ -218,7 +238,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         // TMEM columns [0,128) held dV of the previous item: its epilogue has run, because the first MMA below waits for
         // ready[] of THIS item's pass A, which every epilogue warp signals only after finishing the previous item.
         // ---- pass A: D_KV += relu(K)^T V
-        for (int t = 0; t < n_tiles; ++t, it += 2) {
+        for (int t = 0; t < nA; ++t, it += 2) {
           const uint32_t sk = it % kStages, sv = (it + 1) % kStages, pv = ((it + 1) / kStages) & 1;
           wait_ready(sk);
           mbar_wait(smem_u32(&S.full[sv]), pv);
@@ -238,7 +258,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         tc_fence_after();
         // ---- pass B.  Tensor-pipe order per tile: dQ~(t), num(t+1), dKV(t) - the epilogue warps transform tile t+1
         // (E1) before they finish tile t, so num(t+1) is in TMEM by the time E2(t+1) wants it.
-        {
+        if (nB > 0) {
           const uint32_t sq0 = it % kStages;
           wait_ready(sq0);                                       // relu(Q) in place, den written
           mbar_wait(smem_u32(&S.num_empty), (bt & 1) ^ 1);
@@ -246,15 +266,15 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           small_mmas(kColNum, smem_u32(&S.slots[sq0][0]), false);   // num = relu(Q) KV
           tc_commit(smem_u32(&S.num_full));
         }
-        for (int t = 0; t < n_tiles; ++t, it += 2, ++bt) {
+        for (int t = 0; t < nB; ++t, it += 2, ++bt) {
           const uint32_t sq = it % kStages, sd = (it + 1) % kStages;
-          const uint32_t qa = smem_u32(&S.slots[sq][0]), da_ = smem_u32(&S.slots[sd][0]), la = smem_u32(&S.lo[0]);
+          const uint32_t qa = smem_u32(&S.slots[sq][0]), da_ = smem_u32(&S.slots[sd][0]);
           wait_ready(sd);                                        // Q~ hi (Q slot) / lo written, dO landed
           mbar_wait(smem_u32(&S.dq_empty), (bt & 1) ^ 1);
           tc_fence_after();
           small_mmas(kColDQ, da_, true);             // dQ~ = dO KV^T
           tc_commit(smem_u32(&S.dq_full));
-          if (t + 1 < n_tiles) {
+          if (t + 1 < nB) {
             const uint32_t sq1 = (it + 2) % kStages;
             wait_ready(sq1);
             mbar_wait(smem_u32(&S.num_empty), ((bt + 1) & 1) ^ 1);
@@ -263,14 +283,10 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
             tc_commit(smem_u32(&S.num_full));
           }
 #pragma unroll
-          for (int part = 0; part < 2; ++part) {                 // D_dKV += (Q~hi + Q~lo)^T dO
-            const uint32_t aa = part ? la : qa;
-#pragma unroll
-            for (int ks = 0; ks < kTile / 16; ++ks) {
-              const uint64_t da = make_smem_desc(aa + ks * 2048, kHalfBytes, 1024, kLayoutSw128);
-              const uint64_t db = make_smem_desc(da_ + ks * 2048, kHalfBytes, 1024, kLayoutSw128);
-              umma_bf16(tmem + kColDKV, da, db, kIdescTT, (t | part | ks) != 0);
-            }
+          for (int ks = 0; ks < kTile / 16; ++ks) {              // D_dKV += Q~^T dO
+            const uint64_t da = make_smem_desc(qa + ks * 2048, kHalfBytes, 1024, kLayoutSw128);
+            const uint64_t db = make_smem_desc(da_ + ks * 2048, kHalfBytes, 1024, kLayoutSw128);
+            umma_bf16(tmem + kColDKV, da, db, kIdescTT, (t | ks) != 0);
           }
           tc_commit(smem_u32(&S.pair_done));
         }
@@ -278,7 +294,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         mbar_wait(smem_u32(&S.b2_ready), item_iter & 1);
         tc_fence_after();
         // ---- pass C: dV = relu(K) dKV, dK~ = V dKV^T
-        for (int t = 0; t < n_tiles; ++t, it += 2, ++ct) {
+        for (int t = 0; t < nC; ++t, it += 2, ++ct) {
           const uint32_t sk = it % kStages, sv = (it + 1) % kStages, pv = ((it + 1) / kStages) & 1;
           const uint32_t buf = ct & 1;
           wait_ready(sk);
@@ -291,7 +307,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         }
       }
     }
-  } else if (warp == 10) {
+  } else if (warp == 2 + kEpiWarps) {
     // ======================= TMA store + slot release =======================
     if (lane == 0) {
       uint32_t it = 0, out_ph = 0;
@@ -306,8 +322,8 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
       };
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const int b = item / groups, c0 = (item % groups) * (kHeadsPerItem * kD);
-        it += 2 * n_tiles;  // pass A: slots are released by the issuer's commits
-        for (int t = 0; t < n_tiles; ++t, it += 2) {
+        it += 2 * nA;  // pass A: slots are released by the issuer's commits
+        for (int t = 0; t < nB; ++t, it += 2) {
           const uint32_t sq = it % kStages, sd = (it + 1) % kStages;
           wait_out(sd);                                  // dQ sits in the dO slot; nobody reads the Q slot any more
           mbar_arrive(smem_u32(&S.empty[sq]));
@@ -316,7 +332,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           tma_store_wait_read<0>();
           mbar_arrive(smem_u32(&S.empty[sd]));
         }
-        for (int t = 0; t < n_tiles; ++t, it += 2) {
+        for (int t = 0; t < nC; ++t, it += 2) {
           const uint32_t sk = it % kStages, sv = (it + 1) % kStages;
           wait_out(sk);
           store(&M.dk, sk, c0, t * kTile, b);
@@ -334,10 +350,10 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
     }
   } else {
     // ======================= transform + epilogue warps (2..9) =======================
-    const int te = threadIdx.x - 64;          // 0..255
-    const int we = te >> 5;                   // 0..7
+    const int te = threadIdx.x - 64;          // 0..kEpiThreads-1
+    const int we = te >> 5;                   // 0..kEpiWarps-1
     const int cc = te & 15;                   // transform mapping: 16-byte chunk column of the 256-byte item row
-    const int rbase = te >> 4;                //                    rows rbase + 16 i
+    const int rbase = te >> 4;                //                    rows rbase + kTStep i
     const int half = cc >> 3, chunk = cc & 7;
     // Head (0..3) owning this thread's chunk column.  Kept opaque to the optimiser: nvcc 12.9 otherwise folds
     // `[r][cc >> 2]` into `base + 16 r + cc` (valid only under the `(cc & 3) == 0` predicate of the den store)
@@ -345,10 +361,13 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
     int hsel = cc >> 2;
     asm volatile("" : "+r"(hsel));
     const int quad = warp & 3;                // TMEM lane quadrant this warp may access
-    const int colhalf = we >> 2;              // row mapping: which 64-column half (2 heads) this warp finishes
+    const int colsel = we >> 2;               // row mapping: heads colsel * kHH .. + kHH - 1 are finished by this warp
     const int row = quad * 32 + lane;         //              token row in the tile (TMEM lane)
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
-    const int row_off = colhalf * kHalfBytes + row * 128;
+    // head h of the row: 64-column half h >> 1, 16-byte chunks (h & 1) * 4 + g (swizzled by the row)
+    const int h0 = colsel * kHH;
+    const int row_off = (h0 >> 1) * kHalfBytes + row * 128;
+    const int ch0 = (h0 & 1) * 4;
     uint32_t it = 0, bt = 0, ct = 0, item_iter = 0;
 
     // column sums held per thread (transform mapping) -> dst[128] through S.red; all epilogue threads call it
@@ -383,13 +402,13 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++item_iter) {
       // ---------------- pass A: relu(K) in place, Ks ----------------
       float csum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-      for (int t = 0; t < n_tiles; ++t, it += 2) {
+      for (int t = 0; t < nA; ++t, it += 2) {
         const uint32_t sk = it % kStages, pk = (it / kStages) & 1;
         mbar_wait(smem_u32(&S.full[sk]), pk);
         uint8_t* base = &S.slots[sk][half * kHalfBytes];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int r = rbase + 16 * i;
+        for (int i = 0; i < kTRows; ++i) {
+          const int r = rbase + kTStep * i;
           uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
           const uint4 v = relu8(*p);
           *p = v;
@@ -421,8 +440,8 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         mbar_wait(smem_u32(&S.full[sq]), pq);
         uint8_t* base = &S.slots[sq][half * kHalfBytes];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int r = rbase + 16 * i;
+        for (int i = 0; i < kTRows; ++i) {
+          const int r = rbase + kTStep * i;
           uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
           const uint4 v = relu8(*p);
           *p = v;
@@ -438,12 +457,12 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&S.ready[sq]));
       };
-      e1(it, bt & 1);
-      for (int t = 0; t < n_tiles; ++t, it += 2, ++bt) {
+      if (nB > 0) e1(it, bt & 1);
+      for (int t = 0; t < nB; ++t, it += 2, ++bt) {
         const uint32_t sq = it % kStages;
         const uint32_t sd = (it + 1) % kStages, pd = ((it + 1) / kStages) & 1;
         const int db = bt & 1;
-        if (t + 1 < n_tiles) e1(it + 2, db ^ 1);
+        if (t + 1 < nB) e1(it + 2, db ^ 1);
         // den(t) visible in the row mapping; every warp is past E3a(t-1), so S.lo may be rewritten below
         named_bar_sync(1, kEpiThreads);
 
@@ -451,14 +470,15 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         mbar_wait(smem_u32(&S.full[sd]), pd);
         mbar_wait(smem_u32(&S.num_full), bt & 1);
         tc_fence_after();
-        float rr[2], dd[2];
+        float rr[kHH], dd[kHH];
         uint8_t* qrow = &S.slots[sq][row_off];
-        uint8_t* lrow = &S.lo[row_off];
         const uint8_t* drow = &S.slots[sd][row_off];
-        rr[0] = rr[1] = dd[0] = dd[1] = 0.f;
+        #pragma unroll
+        for (int hh = 0; hh < kHH; ++hh) rr[hh] = dd[hh] = 0.f;
+        if (!PROBE_SKIP(16))
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-          const int h = colhalf * 2 + hh;
+        for (int hh = 0; hh < kHH; ++hh) {
+          const int h = h0 + hh;
           uint32_t acc[32];
           tmem_ld32(tmem + lane_addr + kColNum + h * kD, acc);
           tmem_ld_wait();
@@ -466,7 +486,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             float f[8];
-            unpack8f(*reinterpret_cast<const uint4*>(drow + (((hh * 4 + g) ^ (row & 7)) << 4)), f);
+            unpack8f(*reinterpret_cast<const uint4*>(drow + (((ch0 + hh * 4 + g) ^ (row & 7)) << 4)), f);
 #pragma unroll
             for (int j = 0; j < 8; ++j) s = fmaf(f[j], __uint_as_float(acc[g * 8 + j]), s);
           }
@@ -476,22 +496,12 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           S.wrow[db][row][h] = -s * r;
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
-            const int o = ((hh * 4 + g) ^ (row & 7)) << 4;
-            float f[8], hi[8], lo[8];
+            const int o = ((ch0 + hh * 4 + g) ^ (row & 7)) << 4;
+            float f[8];
             unpack8f(*reinterpret_cast<const uint4*>(qrow + o), f);
-            uint4 hv;
-            uint32_t* hw = reinterpret_cast<uint32_t*>(&hv);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const float a0 = f[2 * j] * r, a1 = f[2 * j + 1] * r;
-              hw[j] = pack_bf16(a0, a1);
-              hi[2 * j] = bf16_lo(hw[j]);
-              hi[2 * j + 1] = bf16_hi(hw[j]);
-              lo[2 * j] = a0 - hi[2 * j];
-              lo[2 * j + 1] = a1 - hi[2 * j + 1];
-            }
-            *reinterpret_cast<uint4*>(qrow + o) = hv;
-            *reinterpret_cast<uint4*>(lrow + o) = pack8(lo);
+            for (int j = 0; j < 8; ++j) f[j] *= r;
+            *reinterpret_cast<uint4*>(qrow + o) = pack8(f);
           }
         }
         tc_fence_before();
@@ -504,39 +514,38 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         named_bar_sync(1, kEpiThreads);         // wrow and Q~ visible in the transform mapping
 
         // E3a: dKs += sum_n Q~_n (dDen_n / r_n)
-        {
+        if (!PROBE_SKIP(8)) {
           const uint8_t* bh = &S.slots[sq][half * kHalfBytes];
-          const uint8_t* bl = &S.lo[half * kHalfBytes];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int r = rbase + 16 * i;
+          for (int i = 0; i < kTRows; ++i) {
+            const int r = rbase + kTStep * i;
             const int o = r * 128 + ((chunk ^ (r & 7)) << 4);
-            float fh[8], fl[8];
+            float fh[8];
             unpack8f(*reinterpret_cast<const uint4*>(bh + o), fh);
-            unpack8f(*reinterpret_cast<const uint4*>(bl + o), fl);
             const float w = S.wrow[db][r][hsel];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) dcs[j] = fmaf(fh[j] + fl[j], w, dcs[j]);
+            for (int j = 0; j < 8; ++j) dcs[j] = fmaf(fh[j], w, dcs[j]);
           }
         }
         // E3b: dQ = (r * dQ~ + dDen * Ks) * [q > 0]
         mbar_wait(smem_u32(&S.dq_full), bt & 1);
         tc_fence_after();
-        uint4 outv[2][4];
+        uint4 outv[kHH][4];
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh)
+        for (int hh = 0; hh < kHH; ++hh)
 #pragma unroll
           for (int g = 0; g < 4; ++g) outv[hh][g] = make_uint4(0, 0, 0, 0);
+        if (!PROBE_SKIP(32))
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-          const int h = colhalf * 2 + hh;
+        for (int hh = 0; hh < kHH; ++hh) {
+          const int h = h0 + hh;
           uint32_t acc[32];
           tmem_ld32(tmem + lane_addr + kColDQ + h * kD, acc);
           tmem_ld_wait();
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             float m[8], o8[8];
-            unpack8f(*reinterpret_cast<const uint4*>(qrow + (((hh * 4 + g) ^ (row & 7)) << 4)), m);
+            unpack8f(*reinterpret_cast<const uint4*>(qrow + (((ch0 + hh * 4 + g) ^ (row & 7)) << 4)), m);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               const float val = fmaf(rr[hh], __uint_as_float(acc[g * 8 + j]), dd[hh] * S.ks[h * kD + g * 8 + j]);
@@ -551,10 +560,10 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         mbar_wait(smem_u32(&S.pair_done), bt & 1);   // the MMAs have finished reading the dO / Q~ tiles
         uint8_t* orow = &S.slots[sd][row_off];
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh)
+        for (int hh = 0; hh < kHH; ++hh)
 #pragma unroll
           for (int g = 0; g < 4; ++g)
-            *reinterpret_cast<uint4*>(orow + (((hh * 4 + g) ^ (row & 7)) << 4)) = outv[hh][g];
+            *reinterpret_cast<uint4*>(orow + (((ch0 + hh * 4 + g) ^ (row & 7)) << 4)) = outv[hh][g];
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&S.out_ready[sd]));
@@ -572,8 +581,8 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         mbar_wait(smem_u32(&S.full[sk]), pk);
         uint8_t* base = &S.slots[sk][half * kHalfBytes];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int r = rbase + 16 * i;
+        for (int i = 0; i < kTRows; ++i) {
+          const int r = rbase + kTStep * i;
           uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
           *p = relu8(*p);
         }
@@ -581,25 +590,25 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&S.ready[sk]));
       };
-      relu_k(it);
-      for (int t = 0; t < n_tiles; ++t, it += 2, ++ct) {
+      if (nC > 0) relu_k(it);
+      for (int t = 0; t < nC; ++t, it += 2, ++ct) {
         const uint32_t sk = it % kStages, sv = (it + 1) % kStages;
         const uint32_t buf = ct & 1;
-        if (t + 1 < n_tiles) relu_k(it + 2);
+        if (t + 1 < nC) relu_k(it + 2);
         mbar_wait(smem_u32(&S.full[sv]), ((it + 1) / kStages) & 1);   // observe the V phase (complete: the MMA read it)
         mbar_wait(smem_u32(&S.c_full[buf]), (ct >> 1) & 1);   // both MMAs done: K and V tiles may be overwritten
         tc_fence_after();
         // dK = (V dKV^T + dKs) * [k > 0]  -> K slot
         uint8_t* krow = &S.slots[sk][row_off];
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-          const int h = colhalf * 2 + hh;
+        for (int hh = 0; hh < kHH; ++hh) {
+          const int h = h0 + hh;
           uint32_t acc[32];
           tmem_ld32(tmem + lane_addr + kColDK + buf * kColBuf + h * kD, acc);
           tmem_ld_wait();
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
-            uint4* p = reinterpret_cast<uint4*>(krow + (((hh * 4 + g) ^ (row & 7)) << 4));
+            uint4* p = reinterpret_cast<uint4*>(krow + (((ch0 + hh * 4 + g) ^ (row & 7)) << 4));
             float m[8], o8[8];
             unpack8f(*p, m);
 #pragma unroll
@@ -614,8 +623,8 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         // dV = relu(K) dKV -> V slot
         uint8_t* vrow = &S.slots[sv][row_off];
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-          const int h = colhalf * 2 + hh;
+        for (int hh = 0; hh < kHH; ++hh) {
+          const int h = h0 + hh;
           uint32_t acc[32];
           tmem_ld32(tmem + lane_addr + kColDV + buf * kColBuf + h * kD, acc);
           tmem_ld_wait();
@@ -624,7 +633,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
             float o8[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) o8[j] = __uint_as_float(acc[g * 8 + j]);
-            *reinterpret_cast<uint4*>(vrow + (((hh * 4 + g) ^ (row & 7)) << 4)) = pack8(o8);
+            *reinterpret_cast<uint4*>(vrow + (((ch0 + hh * 4 + g) ^ (row & 7)) << 4)) = pack8(o8);
           }
         }
         tc_fence_before();
@@ -682,6 +691,12 @@ extern "C" int yat_linattn_bwd_ld(const void* q, const void* k, const void* v, i
   const int groups = (H + kHeadsPerItem - 1) / kHeadsPerItem;
   const int items = B * groups;
   const int grid = items < kNumSMs ? items : kNumSMs;
+#ifdef YAT_BWD_PROBE
+  int probe_mask = 7;
+  if (const char* e = getenv("YAT_BWD_MASK")) probe_mask = atoi(e);
+  linattn_bwd_sm100_kernel<<<grid, kThreads, kBwdSmemBytes, (cudaStream_t)stream>>>(maps, B, N, groups, probe_mask);
+#else
   linattn_bwd_sm100_kernel<<<grid, kThreads, kBwdSmemBytes, (cudaStream_t)stream>>>(maps, B, N, groups);
+#endif
   return check_launch("linattn_bwd_sm100");
 }
