@@ -264,6 +264,21 @@ int yat_ema_step(const int64_t* tensor_tab, const int32_t* chunks, int n_chunks,
 int yat_gemm_bf16_tn(const void* a, const void* w, const void* bias, void* c, int64_t M, int N, int K,
                      int64_t lda, int64_t ldw, int64_t ldc, int tile_n, void* stream);
 
+/* ---- (next, N1) to_q | to_k | to_v projection with the linear attention's phase 1 as its epilogue ----------------
+ * Replaces `attn.to_q / to_k / to_v` + the first half of diffusers' SanaLinearAttnProcessor2_0 (reached from
+ * utils/patch_sana_attention_layers.py:94) by ONE tcgen05 kernel:
+ *   qkv   [B, N, 3*H*32] bf16 = x [B, N, Cin] . w_qkv[3*H*32, Cin]^T      (q | k | v thirds; what the backward reads)
+ *   state [B, 2*ceil(N/256), H, 33, 32] fp32: per 128-token tile and head, rows 0..31 = relu(k)^T v, row 32 = sum relu(k)
+ * yat_qkv_linattn_state_bytes gives the size of `state`.  yat_linattn_fwd_state is the attention forward that consumes
+ * it: it streams only q (row pitch ld elements) and sums the tile partials in fixed order -> o [B, N, H*32] bf16.
+ * No bias (SANA's attention_bias is False); head_dim 32 only.
+ */
+int64_t yat_qkv_linattn_state_bytes(int B, int N, int H);
+int yat_qkv_linattn_fwd(const void* x, const void* w_qkv, int B, int N, int H, int D, int Cin, void* qkv, void* state,
+                        void* stream);
+int yat_linattn_fwd_state(const void* q, int64_t ld, const void* state, int B, int N, int H, int D, void* o,
+                          void* stream);
+
 /* ---- bucket assignment (host function; float64 compare, first-minimum wins) ---------------
  *   out[i] = argmin_j |keys[j] - ratios[i]| with strict '<' in table order, or -1 if nkeys==0.
  */

@@ -1,0 +1,116 @@
+"""yat_qkv_linattn_fwd + yat_linattn_fwd_state: the to_q | to_k | to_v projection on the repo's own
+tcgen05 GEMM with the linear attention's phase 1 (relu(k)^T v, sum relu(k)) as its epilogue, against
+  * the fp64 product of the same bf16 operands (projection) and torch's bf16 GEMM,
+  * the CPU oracle of diffusers' SanaLinearAttnProcessor2_0 (oracle/linear_attention.py) on the bf16-rounded q, k, v,
+  * the unfused product path (F.linear -> yat_linattn_fwd_ld), forward and backward.
+Tolerances: projection = bf16 rounding of the fp32-accumulated result (4e-3, as tests/test_gemm_gpu.py); attention
+output <= 2e-2 by spec (north star), asserted at 4e-3 like tests/test_linattn_gpu.py; state partials are fp32 sums of
+exact bf16 products (1e-5 relative)."""
+import pytest
+import torch
+
+from oracle import linear_attention as ola
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    a, b = a.double(), b.double()
+    return ((a - b).norm() / b.norm().clamp_min(1e-300)).item()
+
+
+def _inputs(B, N, H, Cin, cuda, seed=0):
+    g = torch.Generator(device=cuda).manual_seed(seed)
+    x = torch.randn((B, N, Cin), device=cuda, generator=g).to(torch.bfloat16)
+    w = (torch.randn((3 * H * 32, Cin), device=cuda, generator=g) / Cin ** 0.5).to(torch.bfloat16)
+    return x, w
+
+
+# (B, N, H, Cin): SANA-1.6B width at reduced batch, ragged token counts (TMA zero-fill / masked rows), head counts that are
+# not a multiple of the 3-head k/v tiles or the 6-head q tiles, a single head, K tails
+SHAPES = [(2, 1024, 70, 2240), (1, 924, 70, 2240), (3, 256, 6, 192), (2, 130, 4, 128), (1, 100, 1, 72), (2, 512, 7, 264),
+          (5, 300, 3, 64)]
+
+
+@pytest.mark.parametrize("B,N,H,Cin", SHAPES)
+def test_projection_state_and_attention(cuda, B, N, H, Cin):
+    from yat_b200 import _lib
+    x, w = _inputs(B, N, H, Cin, cuda, seed=B * 1000 + N + H)
+    C = H * 32
+    L = _lib.lib()
+    qkv = torch.full((B, N, 3 * C), float("nan"), dtype=torch.bfloat16, device=cuda)
+    nstate = L.yat_qkv_linattn_state_bytes(B, N, H) // 4
+    state = torch.full((nstate,), float("nan"), dtype=torch.float32, device=cuda)
+    st = torch.cuda.current_stream().cuda_stream
+    _lib.check(L.yat_qkv_linattn_fwd(x.data_ptr(), w.data_ptr(), B, N, H, 32, Cin, qkv.data_ptr(), state.data_ptr(), st),
+               "yat_qkv_linattn_fwd")
+    # --- projection: every element written, equals the rounded fp32-accumulated product
+    ref = x.double() @ w.double().t()
+    lib = torch.nn.functional.linear(x, w)
+    assert not torch.isnan(qkv.float()).any()
+    e_own, e_lib = _rel(qkv, ref), _rel(lib, ref)
+    assert e_own < 4e-3 and e_own <= 1.05 * e_lib + 1e-5, (e_own, e_lib)
+    # --- state: sum of the tile partials == relu(k)^T v, sum relu(k) of the bf16 k, v the kernel wrote
+    n_part = 2 * ((N + 255) // 256)
+    part = state.view(B, n_part, H, 33, 32)
+    assert not torch.isnan(part).any()
+    q, k, v = [t.reshape(B, N, H, 32).double() for t in qkv.split(C, dim=-1)]
+    kr = k.clamp_min(0)
+    kv_ref = torch.einsum("bnhi,bnhj->bhij", kr, v)
+    ks_ref = kr.sum(1)
+    tot = part.double().sum(1)
+    assert _rel(tot[:, :, :32, :], kv_ref) < 1e-5
+    assert _rel(tot[:, :, 32, :], ks_ref) < 1e-5
+    # per-tile partials cover exactly their 128 tokens
+    for t in range(n_part):
+        sl = slice(128 * t, min(128 * (t + 1), N))
+        ref_t = torch.einsum("bnhi,bnhj->bhij", kr[:, sl], v[:, sl]) if sl.start < N else torch.zeros_like(kv_ref)
+        assert (part[:, t, :, :32, :].double() - ref_t).abs().max() <= 1e-5 * ref_t.abs().max().clamp_min(1.0)
+    # --- attention forward from (q, state) vs the oracle on the same bf16 q, k, v
+    o = torch.empty((B, N, C), dtype=torch.bfloat16, device=cuda)
+    _lib.check(L.yat_linattn_fwd_state(qkv.data_ptr(), 3 * C, state.data_ptr(), B, N, H, 32, o.data_ptr(), st),
+               "yat_linattn_fwd_state")
+    qc, kc, vc = [t.contiguous().cpu() for t in qkv.split(C, dim=-1)]
+    o_ref = ola.sana_linear_attention_textbook(qc, kc, vc, H, dtype=torch.float64)
+    assert _rel(o.cpu(), o_ref) < 4e-3
+    # and vs the unfused kernel on the same qkv buffer: same algorithm, only the fp32 summation order of KV differs
+    o2 = torch.empty_like(o)
+    base = qkv.data_ptr()
+    _lib.check(L.yat_linattn_fwd_ld(base, base + 2 * C, base + 4 * C, 3 * C, B, N, H, 32, o2.data_ptr(), st), "fwd_ld")
+    assert _rel(o, o2) < 2e-3
+    # run-to-run identical (fixed-order partial sums, no atomics)
+    qkv_b, state_b, o_b = torch.empty_like(qkv), torch.empty_like(state), torch.empty_like(o)
+    L.yat_qkv_linattn_fwd(x.data_ptr(), w.data_ptr(), B, N, H, 32, Cin, qkv_b.data_ptr(), state_b.data_ptr(), st)
+    L.yat_linattn_fwd_state(qkv_b.data_ptr(), 3 * C, state_b.data_ptr(), B, N, H, 32, o_b.data_ptr(), st)
+    assert torch.equal(qkv, qkv_b) and torch.equal(state, state_b) and torch.equal(o, o_b)
+
+
+@pytest.mark.parametrize("B,N,H,Cin", [(2, 512, 8, 256), (1, 300, 5, 160)])
+def test_autograd_function_matches_unfused_path(cuda, B, N, H, Cin):
+    """sana_linear_attention_proj(x, Wqkv) == F.linear -> sana_linear_attention_qkv, forward and backward."""
+    from yat_b200.linear_attention import sana_linear_attention_proj, sana_linear_attention_qkv
+    x, w = _inputs(B, N, H, Cin, cuda, seed=11)
+    do = torch.randn((B, N, H * 32), device=cuda, generator=torch.Generator(device=cuda).manual_seed(3)).to(torch.bfloat16)
+    xa, wa = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    xb, wb = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    oa = sana_linear_attention_proj(xa, wa, H)
+    ob = sana_linear_attention_qkv(torch.nn.functional.linear(xb, wb), H)
+    oa.backward(do)
+    ob.backward(do)
+    assert _rel(oa, ob) < 3e-3
+    assert _rel(xa.grad, xb.grad) < 6e-3 and _rel(wa.grad, wb.grad) < 6e-3
+
+
+def test_k2_layer_size(cuda):
+    """SANA-1.6B layer size [16, 1024, 2240] -> 70 heads: fused vs unfused output, and the CPU oracle on two samples."""
+    from yat_b200.linear_attention import sana_linear_attention_proj, sana_linear_attention_qkv
+    B, N, H, Cin = 16, 1024, 70, 2240
+    x, w = _inputs(B, N, H, Cin, cuda, seed=2)
+    with torch.no_grad():
+        o = sana_linear_attention_proj(x, w, H)
+        qkv = torch.nn.functional.linear(x, w)
+        o2 = sana_linear_attention_qkv(qkv, H)
+    assert _rel(o, o2) < 4e-3
+    qc, kc, vc = [t[:2].contiguous().cpu() for t in qkv.split(H * 32, dim=-1)]
+    o_ref = ola.sana_linear_attention_textbook(qc, kc, vc, H, dtype=torch.float64)
+    assert _rel(o[:2].cpu(), o_ref) < 6e-3      # includes the projection's own bf16 rounding differences (own GEMM vs cuBLAS)

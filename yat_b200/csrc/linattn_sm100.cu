@@ -77,10 +77,13 @@ __device__ __forceinline__ void unpack8f(const uint4& v, float f[8]) {
   f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
 }
 
+// kState: phase 1 has already been done by the projection kernel (qkv_linattn_sm100.cu): KV_h / Ks_h arrive as fp32
+// partials state[b][tile][head][33][32] (n_part tiles per sample, summed here in fixed order) and only q is streamed.
+template <bool kState>
 __global__ void __launch_bounds__(kThreads, 1)
 linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                          const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_o,
-                         int B, int N, int groups) {
+                         int B, int N, int groups, const float* __restrict__ state, int n_part, int H) {
   extern __shared__ uint8_t smem_raw[];
   FwdSmem& S = *reinterpret_cast<FwdSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -122,7 +125,7 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
       uint32_t it = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const int b = item / groups, c0 = (item % groups) * (kHeadsPerItem * kD);
-        for (int j = 0; j < 3 * n_tiles; ++j, ++it) {
+        for (int j = kState ? 2 * n_tiles : 0; j < 3 * n_tiles; ++j, ++it) {
           const CUtensorMap* tm;
           int tile;
           if (j < 2 * n_tiles) { tm = (j & 1) ? &tm_v : &tm_k; tile = j >> 1; }
@@ -145,7 +148,7 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
       uint32_t d2_use[kGroups] = {0, 0};
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++item_iter) {
         // ---- phase 1: D1 += relu(K)^T V over all token tiles
-        for (int t = 0; t < n_tiles; ++t, it += 2) {
+        for (int t = 0; t < (kState ? 0 : n_tiles); ++t, it += 2) {
           const uint32_t sk = it % kStages;
           const uint32_t sv = (it + 1) % kStages, pv = ((it + 1) / kStages) & 1;
           mbar_wait(smem_u32(&S.ready[sk]), (ready_ph >> sk) & 1);
@@ -163,7 +166,7 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
           tc_commit(smem_u32(&S.empty[sk]));
           tc_commit(smem_u32(&S.empty[sv]));
         }
-        tc_commit(smem_u32(&S.d1_full));
+        if (!kState) tc_commit(smem_u32(&S.d1_full));
         mbar_wait(smem_u32(&S.b_ready), item_iter & 1);
         tc_fence_after();
         // ---- phase 2: D2[group] = relu(Q_h) ([KV_h|Ks_h] hi + lo), per head
@@ -196,6 +199,7 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
           }
           tc_commit(smem_u32(&S.d2_full[g]));
         }
+        if (kState) tc_commit(smem_u32(&S.d1_full));   // every MMA of this item has read bmat: it may be rebuilt
       }
     }
   } else if (warp == kStoreWarp) {
@@ -204,7 +208,7 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
       uint32_t it = 0, o_ph = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const int b = item / groups, c0 = (item % groups) * (kHeadsPerItem * kD);
-        it += 2 * n_tiles;
+        if (!kState) it += 2 * n_tiles;
         for (int t = 0; t < n_tiles; ++t, ++it) {
           const uint32_t sq = it % kStages;
           mbar_wait(smem_u32(&S.o_ready[sq]), (o_ph >> sq) & 1);
@@ -258,7 +262,7 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
       // groups (a parity wait is only sound if the waiter sees every phase of the barrier); only the
       // owner touches the tile.  V needs no transform: the issuer waits on its `full`.
       float csum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-      for (int t = 0; t < n_tiles; ++t, it += 2) {
+      for (int t = 0; t < (kState ? 0 : n_tiles); ++t, it += 2) {
         const uint32_t sk = it % kStages, pk = (it / kStages) & 1;
         mbar_wait(smem_u32(&S.full[sk]), pk);
         if ((t & 1) == grp) relu_tile(sk, csum);
@@ -275,13 +279,36 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
       if (grp == 0) {
         // ---- build the B operands of phase 2: head `quad`, k row `lane`
         float ksum = 0.f;
-#pragma unroll
-        for (int w = 0; w < kEpiWarps; ++w) ksum += S.red[w][quad * kD + lane];
-        mbar_wait(smem_u32(&S.d1_full), item_iter & 1);
-        tc_fence_after();
         uint32_t r[32];
-        tmem_ld32(tmem + lane_base + quad * kD, r);  // KV_head[dk = lane][dv = 0..31]
-        tmem_ld_wait();
+        if (kState) {
+          // the previous item's phase-2 MMAs read bmat: the issuer commits d1_full after the last of them (kState only)
+          if (item_iter > 0) mbar_wait(smem_u32(&S.d1_full), (item_iter - 1) & 1);
+          const int head = (item % groups) * kHeadsPerItem + quad;
+          float accv[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) accv[j] = 0.f;
+          if (head < H) {
+            const float* sp = state + (((int64_t)(item / groups) * n_part) * H + head) * (33 * 32);
+            for (int p = 0; p < n_part; ++p, sp += (int64_t)H * (33 * 32)) {
+              const float4* row4 = reinterpret_cast<const float4*>(sp + lane * 32);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float4 v = __ldg(row4 + j);
+                accv[4 * j] += v.x; accv[4 * j + 1] += v.y; accv[4 * j + 2] += v.z; accv[4 * j + 3] += v.w;
+              }
+              ksum += __ldg(sp + 32 * 32 + lane);
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(accv[j]);
+        } else {
+#pragma unroll
+          for (int w = 0; w < kEpiWarps; ++w) ksum += S.red[w][quad * kD + lane];
+          mbar_wait(smem_u32(&S.d1_full), item_iter & 1);
+          tc_fence_after();
+          tmem_ld32(tmem + lane_base + quad * kD, r);  // KV_head[dk = lane][dv = 0..31]
+          tmem_ld_wait();
+        }
         uint8_t* bh = &S.bmat[quad][0][0];
         uint8_t* bl = &S.bmat[quad][1][0];
         const int off = (lane >> 3) * 128 + (lane & 7) * 16;
@@ -424,15 +451,15 @@ extern "C" int yat_linattn_fwd(const void* q, const void* k, const void* v, int 
   return yat_linattn_fwd_ld(q, k, v, (int64_t)H * D, B, N, H, D, o, stream);
 }
 
-extern "C" int yat_linattn_fwd_ld(const void* q, const void* k, const void* v, int64_t ld, int B, int N, int H, int D,
-                                  void* o, void* stream) {
+static int linattn_fwd_launch(const void* q, const void* k, const void* v, int64_t ld, int B, int N, int H, int D, void* o,
+                              const float* state, int n_part, void* stream) {
   using namespace yat;
   YAT_REQUIRE(q && k && v && o, YAT_ERR_BAD_ARG, "yat_linattn_fwd: null pointer argument");
   YAT_REQUIRE(ld >= (int64_t)H * D && ld % 8 == 0, YAT_ERR_BAD_ARG, "yat_linattn_fwd: row pitch %lld must be >= H*D and a multiple of 8",
               (long long)ld);
   YAT_REQUIRE(B > 0 && N > 0 && H > 0, YAT_ERR_BAD_ARG, "yat_linattn_fwd: non-positive dimension");
   YAT_REQUIRE(D == kD, YAT_ERR_UNSUPPORTED, "yat_linattn_fwd: head_dim %d not supported (SANA uses 32)", D);
-  YAT_REQUIRE((((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o) & 15u) == 0, YAT_ERR_BAD_ARG,
+  YAT_REQUIRE((((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o | (uintptr_t)state) & 15u) == 0, YAT_ERR_BAD_ARG,
               "yat_linattn_fwd: tensors must be 16-byte aligned");
   CUtensorMap tq, tk, tv, to;
   const uint64_t C = (uint64_t)H * D;
@@ -443,8 +470,9 @@ extern "C" int yat_linattn_fwd_ld(const void* q, const void* k, const void* v, i
   if ((rc = make_tmap_3d_bf16(&to, o, C, N, B, 64, kTile)) != YAT_OK) return rc;
   static bool attr_set = false;
   if (!attr_set) {
-    const cudaError_t e =
-        cudaFuncSetAttribute(linattn_fwd_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(linattn_fwd_sm100_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(linattn_fwd_sm100_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes);
     YAT_REQUIRE(e == cudaSuccess, YAT_ERR_CUDA, "yat_linattn_fwd: cannot reserve %d B of shared memory (%s)",
                 kFwdSmemBytes, cudaGetErrorString(e));
     attr_set = true;
@@ -452,6 +480,22 @@ extern "C" int yat_linattn_fwd_ld(const void* q, const void* k, const void* v, i
   const int groups = (H + kHeadsPerItem - 1) / kHeadsPerItem;
   const int items = B * groups;
   const int grid = items < kNumSMs ? items : kNumSMs;
-  linattn_fwd_sm100_kernel<<<grid, kThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(tq, tk, tv, to, B, N, groups);
+  if (state)
+    linattn_fwd_sm100_kernel<true><<<grid, kThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(tq, tk, tv, to, B, N, groups, state, n_part, H);
+  else
+    linattn_fwd_sm100_kernel<false><<<grid, kThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(tq, tk, tv, to, B, N, groups, nullptr, 0, H);
   return check_launch("linattn_fwd_sm100");
+}
+
+extern "C" int yat_linattn_fwd_ld(const void* q, const void* k, const void* v, int64_t ld, int B, int N, int H, int D,
+                                  void* o, void* stream) {
+  return linattn_fwd_launch(q, k, v, ld, B, N, H, D, o, nullptr, 0, stream);
+}
+
+// Phase 2 only: q [B, N, H*32] (row pitch ld) and the state partials written by yat_qkv_linattn_fwd
+// (state[b][tile][head][33][32] fp32, 2 * ceil(N / 256) tiles per sample) -> o [B, N, H*32].
+extern "C" int yat_linattn_fwd_state(const void* q, int64_t ld, const void* state, int B, int N, int H, int D, void* o,
+                                     void* stream) {
+  YAT_REQUIRE(state != nullptr, YAT_ERR_BAD_ARG, "yat_linattn_fwd_state: null state");
+  return linattn_fwd_launch(q, q, q, ld, B, N, H, D, o, (const float*)state, 2 * ((N + 255) / 256), stream);
 }

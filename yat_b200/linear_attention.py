@@ -103,3 +103,58 @@ class _SanaLinearAttentionQKV(torch.autograd.Function):
 def sana_linear_attention_qkv(qkv, heads):
     """qkv [B, N, 3*heads*32] bf16 = [q | k | v] along the last axis (one fused projection) -> [B, N, heads*32]."""
     return _SanaLinearAttentionQKV.apply(qkv, int(heads))
+
+
+class _SanaLinearAttentionProj(torch.autograd.Function):
+    """x -> to_q | to_k | to_v -> ReLU linear attention, with the projection on the repo's own tcgen05 GEMM and the
+    attention's phase 1 (relu(k)^T v, sum relu(k)) as that GEMM's epilogue (``yat_qkv_linattn_fwd``); the attention
+    forward then streams only q and the 33 x 32 per-head state (``yat_linattn_fwd_state``).  SURVEY.md §8(f) N1.
+    Backward: the same tcgen05 backward kernel on the saved qkv, then the two projection-gradient GEMMs."""
+
+    @staticmethod
+    def forward(ctx, x, w_qkv, heads):
+        if not (x.is_cuda and w_qkv.is_cuda) or x.dtype != torch.bfloat16 or w_qkv.dtype != torch.bfloat16:
+            raise ValueError("fused projection + linear attention expects CUDA bf16 tensors (no CPU fallback)")
+        if x.dim() != 3 or w_qkv.dim() != 2 or w_qkv.shape[1] != x.shape[-1] or w_qkv.shape[0] % (3 * heads):
+            raise ValueError(f"bad shapes x {tuple(x.shape)} w_qkv {tuple(w_qkv.shape)} for {heads} heads")
+        x, w_qkv = x.contiguous(), w_qkv.contiguous()
+        B, N, Cin = x.shape
+        C = w_qkv.shape[0] // 3
+        L = _lib.lib()
+        qkv = torch.empty((B, N, 3 * C), dtype=torch.bfloat16, device=x.device)
+        state = torch.empty(L.yat_qkv_linattn_state_bytes(B, N, heads) // 4, dtype=torch.float32, device=x.device)
+        o = torch.empty((B, N, C), dtype=torch.bfloat16, device=x.device)
+        with _lib.timed("qkv_linattn_fwd"):
+            rc = L.yat_qkv_linattn_fwd(_lib.ptr(x), _lib.ptr(w_qkv), B, N, heads, C // heads, Cin, _lib.ptr(qkv),
+                                       _lib.ptr(state), _lib.current_stream())
+        _lib.check(rc, "yat_qkv_linattn_fwd")
+        with _lib.timed("linattn_fwd_state"):
+            rc = L.yat_linattn_fwd_state(_lib.ptr(qkv), 3 * C, _lib.ptr(state), B, N, heads, C // heads, _lib.ptr(o),
+                                         _lib.current_stream())
+        _lib.check(rc, "yat_linattn_fwd_state")
+        ctx.save_for_backward(x, w_qkv, qkv)
+        ctx.heads = heads
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        x, w_qkv, qkv = ctx.saved_tensors
+        B, N, C3 = qkv.shape
+        C = C3 // 3
+        do = do.contiguous()
+        dqkv = torch.empty_like(qkv)
+        base, gbase = qkv.data_ptr(), dqkv.data_ptr()
+        with _lib.timed("linattn_bwd_sm100"):
+            rc = _lib.lib().yat_linattn_bwd_ld(base, base + 2 * C, base + 4 * C, C3, _lib.ptr(do), B, N, ctx.heads,
+                                               C // ctx.heads, gbase, gbase + 2 * C, gbase + 4 * C, C3,
+                                               _lib.current_stream())
+        _lib.check(rc, "yat_linattn_bwd_ld")
+        g2 = dqkv.view(B * N, C3)
+        dx = (g2 @ w_qkv).view_as(x) if ctx.needs_input_grad[0] else None
+        dw = g2.t() @ x.view(B * N, -1) if ctx.needs_input_grad[1] else None
+        return dx, dw, None
+
+
+def sana_linear_attention_proj(x, w_qkv, heads):
+    """x [B, N, Cin] bf16, w_qkv [3*heads*32, Cin] bf16 (to_q | to_k | to_v weights stacked) -> [B, N, heads*32]."""
+    return _SanaLinearAttentionProj.apply(x, w_qkv, int(heads))
