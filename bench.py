@@ -419,16 +419,43 @@ def _standalone_kernels(device, pk):
                          "peak_source": pk["source"] + " (bf16_tflops, burst: kernel timed alone)", "timing": "stand-alone"}
             out[name]["frac"] = out[name]["achieved"] / out[name]["peak"]
         out["gemm_qkv_own_tcgen05"]["vs_cublas_time"] = out["gemm_qkv_cublas"]["us"] / out["gemm_qkv_own_tcgen05"]["us"]
-        del wq
+        # projection + linear attention forward, fused (phase 1 = the GEMM's epilogue; the attention streams only q)
+        # vs the path the step runs today (library GEMM -> yat_linattn_fwd_ld).  FLOP = projection + attention.
+        from yat_b200 import _lib as _L
+        from yat_b200.linear_attention import sana_linear_attention_proj, sana_linear_attention_qkv
+        x3 = q.view(B, N, C)
+        fl_att = 4.0 * 32 * 33 * N * H * B
+        with torch.no_grad():
+            ms_f = timeit(lambda: sana_linear_attention_proj(x3, wq, H), iters=30, warm=5)
+            ms_u = timeit(lambda: sana_linear_attention_qkv(torch.nn.functional.linear(x3, wq), H), iters=30, warm=5)
+            L = _L.lib()
+            qkv_buf = torch.empty((B, N, 3 * C), dtype=torch.bfloat16, device=device)
+            st_buf = torch.empty(L.yat_qkv_linattn_state_bytes(B, N, H) // 4, dtype=torch.float32, device=device)
+            o_buf = torch.empty((B, N, C), dtype=torch.bfloat16, device=device)
+            cs = torch.cuda.current_stream().cuda_stream
+            ms_g = timeit(lambda: L.yat_qkv_linattn_fwd(x3.data_ptr(), wq.data_ptr(), B, N, H, 32, C, qkv_buf.data_ptr(),
+                                                        st_buf.data_ptr(), cs), iters=30, warm=5)
+            ms_s = timeit(lambda: L.yat_linattn_fwd_state(qkv_buf.data_ptr(), 3 * C, st_buf.data_ptr(), B, N, H, 32,
+                                                          o_buf.data_ptr(), cs), iters=30, warm=5)
+        out["qkv_linattn_fused_gemm"] = {
+            "bound": "tensor", "achieved": (fl + fl_att / 2) / (ms_g * 1e-3) / 1e12, "peak": pk["bf16_tflops"],
+            "unit": "TFLOP/s", "us": ms_g * 1e3, "flops": fl + fl_att / 2, "shape": [B, N, C, 3 * C],
+            "peak_source": pk["source"] + " (bf16_tflops, burst: kernel timed alone)", "timing": "stand-alone",
+            "what": "yat_qkv_linattn_fwd: q|k|v projection + relu(k)^T v, sum relu(k) in its epilogue"}
+        out["qkv_linattn_fused_gemm"]["frac"] = out["qkv_linattn_fused_gemm"]["achieved"] / pk["bf16_tflops"]
+        entry("linattn_fwd_state", 4 * B * N * C, ms_s, [B, N, C], flops=fl_att / 2)
+        out["qkv_linattn_fwd_path"] = {"fused_us": ms_f * 1e3, "unfused_us": ms_u * 1e3, "fused_over_unfused_time": ms_f / ms_u,
+                                       "what": "projection + attention forward: (own fused GEMM + state kernel) vs "
+                                               "(library GEMM + yat_linattn_fwd_ld)"}
+        del wq, qkv_buf, st_buf, o_buf
     except Exception as e:  # noqa: BLE001 — reported, not hidden
         out["gemm_qkv_own_tcgen05"] = {"error": str(e)[:200]}
     ms = timeit(lambda: sana_linear_attention(q, k, v, H))
     entry("linattn_fwd_sm100", 8 * B * N * C, ms, [B, N, C], flops=4 * 32 * 33 * N * H * B)
-    qg, kg, vg = [t.clone().requires_grad_(True) for t in (q, k, v)]
-    o = sana_linear_attention(qg, kg, vg, H)
+    from yat_b200.linear_attention import _launch_bwd
 
-    def bwd():
-        torch.autograd.grad(o, (qg, kg, vg), do, retain_graph=True)
+    def bwd():     # the C-ABI call itself: at ~150 us the kernel is shorter than the host cost of torch.autograd.grad
+        _launch_bwd(q, k, v, do, H, "sm100")
     try:
         ms = timeit(bwd)
         entry("linattn_bwd_sm100", 14 * B * N * C, ms, [B, N, C], flops=int(2.5 * 4 * 32 * 33 * N * H * B))

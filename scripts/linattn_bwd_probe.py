@@ -25,7 +25,13 @@ if len(sys.argv) > 1:
         e0.record(); run(); e1.record(); torch.cuda.synchronize()
         ts.append(e0.elapsed_time(e1) * 1e3)
     ts.sort()
-    print(f"mask {os.environ.get('YAT_BWD_MASK', '7')}: median {ts[len(ts) // 2]:.1f} us  best {ts[0]:.1f} us")
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(20):
+        run()
+    e1.record(); torch.cuda.synchronize()
+    print(f"mask {os.environ.get('YAT_BWD_MASK', '7')}: median {ts[len(ts) // 2]:.1f} us  best {ts[0]:.1f} us  "
+          f"(L2 flushed between launches);  back to back {e0.elapsed_time(e1) * 1e3 / 20:.1f} us")
 else:
     for m in [int(x) for x in os.environ.get('YAT_PROBE_MASKS', '7,1,2,4,3,6').split(',')]:
         env = dict(os.environ, YAT_BWD_MASK=str(m))

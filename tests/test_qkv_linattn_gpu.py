@@ -114,3 +114,26 @@ def test_k2_layer_size(cuda):
     qc, kc, vc = [t[:2].contiguous().cpu() for t in qkv.split(H * 32, dim=-1)]
     o_ref = ola.sana_linear_attention_textbook(qc, kc, vc, H, dtype=torch.float64)
     assert _rel(o[:2].cpu(), o_ref) < 6e-3      # includes the projection's own bf16 rounding differences (own GEMM vs cuBLAS)
+
+
+def test_processor_flag_routes_through_the_fused_kernel(cuda):
+    """SanaLinearAttnProcessorB200(fuse_projection=True) == the default processor (library GEMM + attention kernel):
+    output and every parameter gradient, in the diffusers processor protocol (utils/patch_sana_attention_layers.py:94)."""
+    from yat_b200 import _lib
+    from yat_b200.attention import Attention, SanaLinearAttnProcessorB200
+    torch.manual_seed(0)
+    a1 = Attention(query_dim=192, heads=6, dim_head=32, bias=False, processor=SanaLinearAttnProcessorB200())
+    a1 = a1.to(cuda).to(torch.bfloat16)
+    a2 = Attention(query_dim=192, heads=6, dim_head=32, bias=False, processor=SanaLinearAttnProcessorB200(fuse_projection=True))
+    a2 = a2.to(cuda).to(torch.bfloat16)
+    a2.load_state_dict(a1.state_dict())
+    x = torch.randn((2, 300, 192), device=cuda, dtype=torch.bfloat16)
+    before = _lib.launch_counts["yat_qkv_linattn_fwd"]
+    y1, y2 = a1(x), a2(x)
+    assert _lib.launch_counts["yat_qkv_linattn_fwd"] == before + 1
+    g = torch.randn_like(y1)
+    y1.backward(g)
+    y2.backward(g)
+    assert _rel(y2, y1) < 4e-3
+    for (n1, p1), (_, p2) in zip(a1.named_parameters(), a2.named_parameters()):
+        assert _rel(p2.grad, p1.grad) < 8e-3, n1

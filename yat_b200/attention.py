@@ -16,16 +16,21 @@ from torch import nn
 
 from . import _lib
 from .linear import Linear
-from .linear_attention import sana_linear_attention, sana_linear_attention_qkv
+from .linear_attention import sana_linear_attention, sana_linear_attention_proj, sana_linear_attention_qkv
 
 
 class SanaLinearAttnProcessorB200:
     """Drop-in for diffusers ``SanaLinearAttnProcessor2_0``: projections stay ``attn.to_q/k/v``
     (possibly PEFT-wrapped), the ReLU linear-attention core runs as one tcgen05 kernel."""
 
-    def __init__(self, impl: str = "sm100", fuse_qkv: bool = True):
+    def __init__(self, impl: str = "sm100", fuse_qkv: bool = True, fuse_projection: bool = False):
         self.impl = impl
         self.fuse_qkv = fuse_qkv
+        # fuse_projection: run to_q | to_k | to_v on the repo's own tcgen05 GEMM with the attention's phase 1 as its
+        # epilogue (yat_qkv_linattn_fwd, SURVEY.md §8(f) N1).  Off by default: measured on B200 at the SANA-1.6B layer
+        # size the pair (fused GEMM 400 us + state attention 55 us) is 17 % slower than (library GEMM 337 us +
+        # attention 61 us) - the operand staging of the epilogue costs the GEMM its sixth pipeline stage (DESIGN.md §5.7).
+        self.fuse_projection = fuse_projection
 
     def _can_fuse_qkv(self, attn, hidden_states, encoder_hidden_states):
         if not self.fuse_qkv or self.impl != "sm100" or encoder_hidden_states is not hidden_states:
@@ -50,7 +55,10 @@ class SanaLinearAttnProcessorB200:
             # is a single GEMM over K = 3*C instead of three GEMMs and two accumulation passes
             w = torch.cat([attn.to_q.weight, attn.to_k.weight, attn.to_v.weight], dim=0)
             b = None if attn.to_q.bias is None else torch.cat([attn.to_q.bias, attn.to_k.bias, attn.to_v.bias], dim=0)
-            out = sana_linear_attention_qkv(F.linear(hidden_states, w, b), attn.heads)
+            if self.fuse_projection and b is None and hidden_states.dim() == 3:
+                out = sana_linear_attention_proj(hidden_states, w, attn.heads)
+            else:
+                out = sana_linear_attention_qkv(F.linear(hidden_states, w, b), attn.heads)
             out = attn.to_out[0](out.to(original_dtype))
             return attn.to_out[1](out)
         query = attn.to_q(hidden_states)

@@ -427,9 +427,6 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
       tc_fence_after();
       build_bmat(kColKV);                       // barrier inside: ks visible, D_KV drained, bmat written
       if (lane == 0) mbar_arrive(smem_u32(&S.b_ready));
-      float ksr[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) ksr[j] = S.ks[cc * 8 + j];
       // ---------------- pass B ----------------
       // Software-pipelined by one tile: E1(t+1) (relu(Q), den) runs BEFORE E2(t) / E3(t), so the num MMA of tile t+1
       // and its mbarrier round trip overlap this tile's epilogue instead of sitting on the critical path.
@@ -439,6 +436,11 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         const uint32_t sq = jt % kStages, pq = (jt / kStages) & 1;
         mbar_wait(smem_u32(&S.full[sq]), pq);
         uint8_t* base = &S.slots[sq][half * kHalfBytes];
+        float ksr[8];                               // re-read per tile (two 128-bit loads): 8 fewer registers live across the pass
+        {
+          const float4 k0 = *reinterpret_cast<const float4*>(&S.ks[cc * 8]), k1 = *reinterpret_cast<const float4*>(&S.ks[cc * 8 + 4]);
+          ksr[0] = k0.x; ksr[1] = k0.y; ksr[2] = k0.z; ksr[3] = k0.w; ksr[4] = k1.x; ksr[5] = k1.y; ksr[6] = k1.z; ksr[7] = k1.w;
+        }
 #pragma unroll
         for (int i = 0; i < kTRows; ++i) {
           const int r = rbase + kTStep * i;
