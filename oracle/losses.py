@@ -53,3 +53,17 @@ def denoise_loss(pred, x0, noise, mode="velocity", pred_frozen=None, rho=0.0, we
         l_pres = torch.nn.MSELoss()(p.float(), pred_frozen[:, :C].float())
         total = l_noise + rho * l_pres.to(l_noise.dtype)
     return total, l_noise, l_pres
+
+
+def sd3_loss_weighting(weighting_scheme, sigmas):
+    """diffusers.training_utils.compute_loss_weighting_for_sd3 restated (the SD3 / SANA trainers of diffusers weight the
+    per-sample flow-matching MSE by it; the YAT hooks train_sd35.py:179-193 / train_sana.py:217-218 use no weighting,
+    i.e. ``none``): sigma_sqrt -> sigma^-2, cosmap -> 2 / (pi (1 - 2 sigma + 2 sigma^2)), anything else -> 1."""
+    import math
+    import torch
+    sigmas = sigmas.float()
+    if weighting_scheme == "sigma_sqrt":
+        return sigmas ** -2.0
+    if weighting_scheme == "cosmap":
+        return 2.0 / (math.pi * (1.0 - 2.0 * sigmas + 2.0 * sigmas ** 2))
+    return torch.ones_like(sigmas)

@@ -6,7 +6,8 @@ from yat_b200.block_ops import gate_residual, ln_modulate
 from yat_b200.attention import _HeadPad, _HeadUnpad
 from yat_b200.glumb import glumb_mid
 from yat_b200.linear import colsum
-from yat_b200.linear_attention import sana_linear_attention
+from yat_b200.linear_attention import sana_linear_attention, sana_linear_attention_proj
+from yat_b200.gemm import gemm_bf16_tn
 from yat_b200.loss import fused_denoise_loss
 from yat_b200.noise import flowmatch_noise
 from yat_b200.optim import FusedClipAdamW
@@ -34,7 +35,11 @@ params = [torch.nn.Parameter(torch.randn(2240 * 2240, device=dev, dtype=torch.bf
 opt = FusedClipAdamW(params, lr=1e-5, weight_decay=0.0)
 for p in params:
     p.grad = torch.randn_like(p) * 1e-3
+wq = (torch.randn((3 * C, C), device=dev) / C ** 0.5).to(torch.bfloat16)
 for _ in range(reps):
+    with torch.no_grad():
+        sana_linear_attention_proj(q, wq, H)          # fused projection + phase 1, then the state-mode attention forward
+        gemm_bf16_tn(q.view(B * N, C), wq)            # the plain own GEMM of the same projection
     flowmatch_noise(x0, sch, seed=1, offset=2, want_target=False)
     fused_denoise_loss(pred, x0, None, seed=1, offset=2)
     o = sana_linear_attention(qg, kg, vg, H)

@@ -505,3 +505,31 @@ def test_adapter_checkpoint_is_adapter_only_and_reloads(tmp_path):
     load_adapters(m2, str(tmp_path / "ad"))
     for (k1, v1), (k2, v2) in zip(sorted(m.state_dict().items()), sorted(m2.state_dict().items())):
         assert k1 == k2 and torch.equal(v1, v2), k1
+
+
+def test_sd3_weighting_scheme_key_and_formulas(tmp_path):
+    """`weighting_scheme` (none | sigma_sqrt | cosmap) is parsed, rejected when unknown, and the product's weight formula
+    equals the oracle restatement of diffusers' compute_loss_weighting_for_sd3; `none` keeps the reference's w = 1."""
+    import math
+    from oracle import losses as ol
+    from yat_b200.loss import sd3_loss_weights
+    from yat_b200.training_parameters_reader import TrainingParameters
+    for scheme in ("none", "sigma_sqrt", "cosmap"):
+        f = tmp_path / f"{scheme}.yaml"
+        f.write_text(f"batch_size: 2\nlearning_rate: 1e-5\nsteps: 10\nnum_steps_per_validation: 100\nvalidation_prompts: [a]\nweighting_scheme: {scheme}\n")
+        p = TrainingParameters()
+        p.read_yaml(str(f))
+        assert p.weighting_scheme == scheme
+    f = tmp_path / "bad.yaml"
+    f.write_text("batch_size: 2\nlearning_rate: 1e-5\nsteps: 10\nnum_steps_per_validation: 100\nvalidation_prompts: [a]\nweighting_scheme: lognorm\n")
+    with pytest.raises(ValueError):
+        TrainingParameters().read_yaml(str(f))
+    assert TrainingParameters().weighting_scheme == "none"
+    sig = torch.tensor([0.05, 0.326, 0.5, 0.811, 0.95])
+    assert sd3_loss_weights("none", sig) is None
+    for scheme in ("sigma_sqrt", "cosmap"):
+        assert torch.allclose(sd3_loss_weights(scheme, sig), ol.sd3_loss_weighting(scheme, sig), rtol=1e-6)
+    assert abs(ol.sd3_loss_weighting("cosmap", torch.tensor([0.5]))[0].item() - 4.0 / math.pi) < 1e-6
+    assert torch.equal(ol.sd3_loss_weighting("none", sig), torch.ones_like(sig))
+    with pytest.raises(ValueError):
+        sd3_loss_weights("lognorm", sig)

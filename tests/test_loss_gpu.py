@@ -150,3 +150,29 @@ def test_argument_errors(cuda):
         fused_denoise_loss(z, z, z)
     with pytest.raises(ValueError):
         fused_denoise_loss(z.float(), z, z)
+
+
+@pytest.mark.parametrize("scheme", ["sigma_sqrt", "cosmap", "none"])
+def test_sd3_weighting_scheme_through_the_hook_path(cuda, scheme):
+    """weighting_scheme (config key) -> per-sample weights from the device sigmas -> yat_loss_fused(weights=), against the
+    oracle restatement of diffusers' compute_loss_weighting_for_sd3 + the weighted per-sample MSE (oracle/losses.py)."""
+    from oracle import losses as ol
+    from yat_b200.loss import VELOCITY, fused_denoise_loss, sd3_loss_weights
+    g = torch.Generator().manual_seed(7)
+    B = 6
+    x0, noise = [torch.randn((B, 16, 24, 24), generator=g).to(torch.bfloat16) for _ in range(2)]
+    pred = torch.randn((B, 16, 24, 24), generator=g).to(torch.bfloat16)
+    sig = torch.rand((B,), generator=g) * 0.9 + 0.05
+    w_ref = ol.sd3_loss_weighting(scheme, sig)
+    pr = pred.clone().float().requires_grad_(True)
+    loss_ref = ol.denoise_loss(pr, x0, noise, mode="velocity", weights=w_ref)
+    loss_ref = loss_ref[0] if isinstance(loss_ref, tuple) else loss_ref
+    loss_ref.backward()
+    w = sd3_loss_weights(scheme, sig.to(cuda))
+    assert (w is None) == (scheme == "none")
+    pc = pred.to(cuda).requires_grad_(True)
+    loss = fused_denoise_loss(pc, x0.to(cuda), noise.to(cuda), weights=w, target_mode=VELOCITY, lowp=False)
+    loss.backward()
+    assert abs(loss.item() - loss_ref.item()) <= 1e-5 * abs(loss_ref.item())
+    num = (pc.grad.float().cpu() - pr.grad).norm() / pr.grad.norm()
+    assert num < 2e-2

@@ -24,7 +24,7 @@ from yat_b200.aspect_ratios import (ASPECT_RATIO_256_BIN, ASPECT_RATIO_512_BIN, 
                                     ASPECT_RATIO_2048_BIN)
 from yat_b200.bucket_sampler import SyntheticBucketSampler
 from yat_b200.embeddings import pad_embeddings
-from yat_b200.loss import VELOCITY, fused_denoise_loss
+from yat_b200.loss import VELOCITY, fused_denoise_loss, sd3_loss_weights
 from yat_b200.noise import flowmatch_noise
 from yat_b200.repa import RepaConfig, RepaModel
 from yat_b200.sana_transformer import SanaTransformer2DModel
@@ -176,6 +176,7 @@ class SanaModel(Model):
                 pred_frozen = self.pipe.transformer(nz.x_t, encoder_hidden_states=embeddings, timestep=nz.timesteps,
                                                     encoder_attention_mask=attention_mask).sample
         loss = fused_denoise_loss(noise_pred, latents, nz.noise, pred_frozen=pred_frozen,
+                                  weights=sd3_loss_weights(getattr(params, "weighting_scheme", "none"), nz.sigmas),
                                   rho=float(params.preservation_ratio or 0.0),
                                   gscale=1.0 / self.accelerator.gradient_accumulation_steps,
                                   target_mode=VELOCITY, lowp=False, seed=seed, offset=offset,

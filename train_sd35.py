@@ -18,7 +18,7 @@ import torch
 
 from yat_b200.aspect_ratios import ASPECT_RATIO_1024_BIN
 from yat_b200.bucket_sampler import Batch, SyntheticBucketSampler
-from yat_b200.loss import VELOCITY, fused_denoise_loss
+from yat_b200.loss import VELOCITY, fused_denoise_loss, sd3_loss_weights
 from yat_b200.noise import flowmatch_noise
 from yat_b200.schedulers import FlowMatchEulerDiscreteScheduler
 from yat_b200.sd3_transformer import SD3_CONFIGS, SD3Transformer2DModel
@@ -106,6 +106,7 @@ class SD35Trainer(Model):
         pred = self.model(nz.x_t, encoder_hidden_states=embeddings, timestep=nz.timesteps,
                           pooled_projections=pooled).sample
         return fused_denoise_loss(pred.to(torch.bfloat16), latents, nz.noise,
+                                  weights=sd3_loss_weights(getattr(self.params, "weighting_scheme", "none"), nz.sigmas),
                                   gscale=1.0 / self.accelerator.gradient_accumulation_steps, target_mode=VELOCITY,
                                   lowp=True, seed=seed, offset=offset, trust_gscale=self._trust_gscale)
 

@@ -80,3 +80,17 @@ def fused_denoise_loss(pred, x0, noise=None, *, pred_frozen=None, weights=None, 
     loss, terms = _FusedDenoiseLoss.apply(pred, x0, noise, pred_frozen, weights, rho, gscale, target_mode, lowp,
                                           seed, offset, trust_gscale)
     return (loss, terms) if return_terms else loss
+
+
+def sd3_loss_weights(weighting_scheme, sigmas):
+    """Per-sample loss weights w_b of the SD3 weighting schemes from the sigmas the noising kernel left on the device
+    (no host sync): ``sigma_sqrt`` -> sigma^-2, ``cosmap`` -> 2 / (pi (1 - 2 sigma + 2 sigma^2)); ``none`` / None -> None
+    (w = 1: what train_sd35.py:179-193 and train_sana.py:217-218 compute).  Feeds ``fused_denoise_loss(weights=)``."""
+    if weighting_scheme in (None, "none", "logit_normal"):
+        return None
+    sigmas = sigmas.float().reshape(-1)
+    if weighting_scheme == "sigma_sqrt":
+        return sigmas ** -2.0
+    if weighting_scheme == "cosmap":
+        return 2.0 / (3.141592653589793 * (1.0 - 2.0 * sigmas + 2.0 * sigmas * sigmas))
+    raise ValueError(f"unknown weighting_scheme {weighting_scheme!r} (none, sigma_sqrt, cosmap)")

@@ -1,11 +1,10 @@
-"""Signature-compatible stand-in denoisers for the PixArt-Sigma and SD3.5 hooks.
+"""Small signature-compatible stand-in denoisers for the PixArt-Sigma and SD3.5 hooks (TEST FIXTURES).
 
-The PixArt-Sigma XL and SD3.5-medium MMDiT transformers themselves are diffusers models that this
-build does not restate; the hot path of their training step — noising, loss —
-is model-agnostic.  These small modules have the same ``forward`` signatures and output shapes as
-``PixArtTransformer2DModel`` (8 output channels = eps + learned sigma, train_pixart_sigma.py:178-182)
-and ``SD3Transformer2DModel`` (``pooled_projections``, train_sd35.py:187-191), so the hooks can be
-exercised, tested and timed end to end; a real transformer is passed to the trainer the same way.
+The real transformers are restated in ``pixart_transformer.py`` (PixArt-Sigma XL) and ``sd3_transformer.py``
+(SD3.5-medium MMDiT-X) and are what the hooks build from ``params.model_config``.  These few-layer modules have the
+same ``forward`` signatures and output shapes as ``PixArtTransformer2DModel`` (8 output channels = eps + learned
+sigma, train_pixart_sigma.py:178-182) and ``SD3Transformer2DModel`` (``pooled_projections``, train_sd35.py:187-191):
+the hook tests use them where the CPU oracle has to finish in seconds.
 """
 from types import SimpleNamespace
 

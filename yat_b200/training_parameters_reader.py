@@ -25,6 +25,7 @@ class TrainingParameters:
         self.preservation_ratio = None
         self.use_adamw_8bit = False
         self.weight_decay = 0.0
+        self.weighting_scheme = "none"          # SD3 loss weighting (none | sigma_sqrt | cosmap); the reference hooks use none
         self.warmup_steps = None
         self.use_ema = False
         self.train_unconditional_prob = 0.0
@@ -85,6 +86,9 @@ class TrainingParameters:
             self.timesteps = y["timesteps"]
         self.cache_size = int(y["cache_size"]) if has("cache_size") else 1000
         self.weight_decay = float(y["weight_decay"]) if has("weight_decay") else 0.0
+        self.weighting_scheme = str(y["weighting_scheme"]) if has("weighting_scheme") else "none"
+        if self.weighting_scheme not in ("none", "sigma_sqrt", "cosmap"):
+            raise ValueError(f"weighting_scheme {self.weighting_scheme!r}: expected none, sigma_sqrt or cosmap")
         self.bfloat16 = has("bfloat16")
         self.gradient_accumulation_steps = int(y["gradient_accumulation_steps"]) if has("gradient_accumulation_steps") else 1
         self.use_ema = has("use_ema")
