@@ -122,6 +122,23 @@ struct BwdMaps {
   CUtensorMap q, k, v, d_o, dq, dk, dv;
 };
 
+#ifdef YAT_BWD_PROBE   // experiment build only: per-role (code, clock64) event trace of CTA 0
+__device__ long long g_tr[4][4096];
+__device__ int g_trn[4];
+#define TRACE(role, code)                                                                          \
+  do {                                                                                             \
+    if (blockIdx.x == 0) {                                                                         \
+      const int i_ = g_trn[role];                                                                  \
+      if (i_ < 4096) {                                                                             \
+        g_tr[role][i_] = ((long long)(code) << 48) | (clock64() & 0xffffffffffffll);               \
+        g_trn[role] = i_ + 1;                                                                      \
+      }                                                                                            \
+    }                                                                                              \
+  } while (0)
+#else
+#define TRACE(role, code) do { } while (0)
+#endif
+
 __global__ void __launch_bounds__(kThreads, 1)
 #ifdef YAT_BWD_PROBE   // timing experiment build only (scripts/linattn_bwd_probe.py); never defined for the product library
 linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int groups, int probe_mask) {
@@ -172,7 +189,11 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem = S.tmem_base;
+  // One CTA per SM allocating all 512 columns: the only possible base is column 0.  Treating it as the constant it is
+  // keeps every TMEM address in the issuer's MMA loop a compile-time immediate (a register-held base costs an
+  // ELECT / R2UR.BROADCAST waterfall per tcgen05.mma: ~100 cycles per issue from a single thread).
+  if (S.tmem_base != 0) __trap();
+  constexpr uint32_t tmem = 0;
 
   if (warp == 0) {
     // ======================= TMA producer =======================
@@ -189,7 +210,9 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
             for (int w = 0; w < 2; ++w, ++it) {
               const CUtensorMap* tm = pass == 1 ? (w ? &M.d_o : &M.q) : (w ? &M.v : &M.k);
               const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+              TRACE(3, 50 + pass);
               mbar_wait(smem_u32(&S.empty[s]), ph ^ 1);
+              TRACE(3, 55 + pass);
               const uint32_t full = smem_u32(&S.full[s]);
               mbar_arrive_expect_tx(full, kSlotBytes);
               const uint32_t dst = smem_u32(&S.slots[s][0]);
@@ -209,30 +232,41 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         mbar_wait(smem_u32(&S.ready[s]), (ready_ph >> s) & 1);
         ready_ph ^= 1u << s;
       };
-      // rows x (32x32 operand): 4 heads x (hi, lo) x 2 K-steps into 32-column accumulators
+      // rows x (32x32 operand): 4 heads x (hi, lo) x 2 K-steps into 32-column accumulators.  A descriptor is its base
+      // plus (byte offset >> 4) as long as the address field does not overflow (shared memory < 256 KB): one 64-bit add
+      // of an immediate per MMA instead of re-encoding.
+      const uint64_t bmat_mn = make_smem_desc(smem_u32(&S.bmat[0][0][0]), 128, 512, kLayoutNone);   // operand [k][n] as stored
+      const uint64_t bmat_k = make_smem_desc(smem_u32(&S.bmat[0][0][0]), 512, 128, kLayoutNone);    // same bytes as the transpose
       auto small_mmas = [&](uint32_t acc_col, uint32_t a_slot, bool transposed) {
+        const uint64_t a0 = make_smem_desc(a_slot, 16, 1024, kLayoutSw128);
 #pragma unroll
         for (int h = 0; h < kHeadsPerItem; ++h) {
           const uint32_t d = tmem + acc_col + h * kD;
-          const uint32_t ah = a_slot + (h >> 1) * kHalfBytes + (h & 1) * 64;  // 32 columns = 64 B inside the 128 B row
+          const uint32_t aoff = (h >> 1) * kHalfBytes + (h & 1) * 64;  // 32 columns = 64 B inside the 128 B row
 #pragma unroll
-          for (int hl = 0; hl < 2; ++hl) {
-            const uint32_t ba = smem_u32(&S.bmat[h][hl][0]);
+          for (int hl = 0; hl < (PROBE_SKIP(64) ? 1 : 2); ++hl) {
+            const uint32_t boff = (h * 2 + hl) * kBmatBytes;
 #pragma unroll
             for (int ks = 0; ks < 2; ++ks) {
-              const uint64_t da = make_smem_desc(ah + ks * 32, 16, 1024, kLayoutSw128);
+              const uint64_t da = a0 + ((aoff + ks * 32) >> 4);
               if (!transposed) {
-                // operand [k][n] as stored: MN-major, 8-k group stride (LBO) 128 B, 8-n group stride (SBO) 512 B
-                const uint64_t db = make_smem_desc(ba + ks * 256, 128, 512, kLayoutNone);
-                umma_bf16(d, da, db, kIdescMN, (hl | ks) != 0);
+                // MN-major: 8-k group stride (LBO) 128 B, 8-n group stride (SBO) 512 B; K step of 16 = 256 B
+                umma_bf16(d, da, bmat_mn + ((boff + ks * 256) >> 4), kIdescMN, (hl | ks) != 0);
               } else {
-                // same bytes read as the transpose: K-major, 8-k chunk stride (LBO) 512 B, 8-n group stride (SBO) 128 B
-                const uint64_t db = make_smem_desc(ba + ks * 1024, 512, 128, kLayoutNone);
-                umma_bf16(d, da, db, kIdescK, (hl | ks) != 0);
+                // K-major view: 8-k chunk stride (LBO) 512 B, 8-n group stride (SBO) 128 B; K step of 16 = 1024 B
+                umma_bf16(d, da, bmat_k + ((boff + ks * 1024) >> 4), kIdescK, (hl | ks) != 0);
               }
             }
           }
         }
+      };
+      // [128 x 128] += X^T Y over the 128 tokens of a tile pair (8 K-steps of 16 tokens = 2048 B each)
+      auto big_mmas = [&](uint32_t acc_col, uint32_t x_slot, uint32_t y_slot, bool first) {
+        const uint64_t x0 = make_smem_desc(x_slot, kHalfBytes, 1024, kLayoutSw128);
+        const uint64_t y0 = make_smem_desc(y_slot, kHalfBytes, 1024, kLayoutSw128);
+#pragma unroll
+        for (int ks = 0; ks < kTile / 16; ++ks)
+          umma_bf16(tmem + acc_col, x0 + ((ks * 2048) >> 4), y0 + ((ks * 2048) >> 4), kIdescTT, !(first && ks == 0));
       };
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++item_iter) {
         // TMEM columns [0,128) held dV of the previous item: its epilogue has run, because the first MMA below waits for
@@ -243,13 +277,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           wait_ready(sk);
           mbar_wait(smem_u32(&S.full[sv]), pv);
           tc_fence_after();
-          const uint32_t ka = smem_u32(&S.slots[sk][0]), va = smem_u32(&S.slots[sv][0]);
-#pragma unroll
-          for (int ks = 0; ks < kTile / 16; ++ks) {
-            const uint64_t da = make_smem_desc(ka + ks * 2048, kHalfBytes, 1024, kLayoutSw128);
-            const uint64_t db = make_smem_desc(va + ks * 2048, kHalfBytes, 1024, kLayoutSw128);
-            umma_bf16(tmem + kColKV, da, db, kIdescTT, (t | ks) != 0);
-          }
+          big_mmas(kColKV, smem_u32(&S.slots[sk][0]), smem_u32(&S.slots[sv][0]), t == 0);
           tc_commit(smem_u32(&S.empty[sk]));
           tc_commit(smem_u32(&S.empty[sv]));
         }
@@ -269,11 +297,19 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         for (int t = 0; t < nB; ++t, it += 2, ++bt) {
           const uint32_t sq = it % kStages, sd = (it + 1) % kStages;
           const uint32_t qa = smem_u32(&S.slots[sq][0]), da_ = smem_u32(&S.slots[sd][0]);
-          wait_ready(sd);                                        // Q~ hi (Q slot) / lo written, dO landed
+          TRACE(1, 30);
+          // dQ~ = dO KV^T needs only the raw dO tile and a drained dQ accumulator: it is issued while the epilogue warps
+          // are still in E2 of this tile, so dq_full is up by the time E3b asks for it
+          mbar_wait(smem_u32(&S.full[sd]), ((it + 1) / kStages) & 1);
           mbar_wait(smem_u32(&S.dq_empty), (bt & 1) ^ 1);
           tc_fence_after();
-          small_mmas(kColDQ, da_, true);             // dQ~ = dO KV^T
+          TRACE(1, 31);
+          small_mmas(kColDQ, da_, true);
           tc_commit(smem_u32(&S.dq_full));
+          TRACE(1, 32);
+          wait_ready(sd);                                        // Q~ written in place (Q slot)
+          tc_fence_after();
+          TRACE(1, 33);
           if (t + 1 < nB) {
             const uint32_t sq1 = (it + 2) % kStages;
             wait_ready(sq1);
@@ -282,13 +318,9 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
             small_mmas(kColNum, smem_u32(&S.slots[sq1][0]), false);
             tc_commit(smem_u32(&S.num_full));
           }
-#pragma unroll
-          for (int ks = 0; ks < kTile / 16; ++ks) {              // D_dKV += Q~^T dO
-            const uint64_t da = make_smem_desc(qa + ks * 2048, kHalfBytes, 1024, kLayoutSw128);
-            const uint64_t db = make_smem_desc(da_ + ks * 2048, kHalfBytes, 1024, kLayoutSw128);
-            umma_bf16(tmem + kColDKV, da, db, kIdescTT, (t | ks) != 0);
-          }
+          big_mmas(kColDKV, qa, da_, t == 0);                    // D_dKV += Q~^T dO
           tc_commit(smem_u32(&S.pair_done));
+          TRACE(1, 34);
         }
         tc_commit(smem_u32(&S.dkv_full));
         mbar_wait(smem_u32(&S.b2_ready), item_iter & 1);
@@ -325,12 +357,15 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         it += 2 * nA;  // pass A: slots are released by the issuer's commits
         for (int t = 0; t < nB; ++t, it += 2) {
           const uint32_t sq = it % kStages, sd = (it + 1) % kStages;
+          TRACE(2, 40);
           wait_out(sd);                                  // dQ sits in the dO slot; nobody reads the Q slot any more
+          TRACE(2, 41);
           mbar_arrive(smem_u32(&S.empty[sq]));
           store(&M.dq, sd, c0, t * kTile, b);
           tma_store_commit();
           tma_store_wait_read<0>();
           mbar_arrive(smem_u32(&S.empty[sd]));
+          TRACE(2, 42);
         }
         for (int t = 0; t < nC; ++t, it += 2) {
           const uint32_t sk = it % kStages, sv = (it + 1) % kStages;
@@ -464,14 +499,19 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         const uint32_t sq = it % kStages;
         const uint32_t sd = (it + 1) % kStages, pd = ((it + 1) / kStages) & 1;
         const int db = bt & 1;
+        if (te == 0) TRACE(0, 10);
         if (t + 1 < nB) e1(it + 2, db ^ 1);
+        if (te == 0) TRACE(0, 11);
         // den(t) visible in the row mapping; every warp is past E3a(t-1), so S.lo may be rewritten below
         named_bar_sync(1, kEpiThreads);
+        if (te == 0) TRACE(0, 12);
 
-        // E2: num -> r, dDen; Q~ = r * relu(Q) as bf16 hi (in place) + lo
+        // E2: num -> r, dDen; Q~ = bf16(r * relu(Q)) in place
         mbar_wait(smem_u32(&S.full[sd]), pd);
+        if (te == 0) TRACE(0, 13);
         mbar_wait(smem_u32(&S.num_full), bt & 1);
         tc_fence_after();
+        if (te == 0) TRACE(0, 14);
         float rr[kHH], dd[kHH];
         uint8_t* qrow = &S.slots[sq][row_off];
         const uint8_t* drow = &S.slots[sd][row_off];
@@ -513,7 +553,9 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           mbar_arrive(smem_u32(&S.num_empty));
           mbar_arrive(smem_u32(&S.ready[sd]));
         }
+        if (te == 0) TRACE(0, 15);
         named_bar_sync(1, kEpiThreads);         // wrow and Q~ visible in the transform mapping
+        if (te == 0) TRACE(0, 16);
 
         // E3a: dKs += sum_n Q~_n (dDen_n / r_n)
         if (!PROBE_SKIP(8)) {
@@ -530,8 +572,10 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           }
         }
         // E3b: dQ = (r * dQ~ + dDen * Ks) * [q > 0]
+        if (te == 0) TRACE(0, 17);
         mbar_wait(smem_u32(&S.dq_full), bt & 1);
         tc_fence_after();
+        if (te == 0) TRACE(0, 18);
         uint4 outv[kHH][4];
 #pragma unroll
         for (int hh = 0; hh < kHH; ++hh)
@@ -548,9 +592,12 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           for (int g = 0; g < 4; ++g) {
             float m[8], o8[8];
             unpack8f(*reinterpret_cast<const uint4*>(qrow + (((ch0 + hh * 4 + g) ^ (row & 7)) << 4)), m);
+            const float4 k0 = *reinterpret_cast<const float4*>(&S.ks[h * kD + g * 8]);       // broadcast 128-bit loads
+            const float4 k1 = *reinterpret_cast<const float4*>(&S.ks[h * kD + g * 8 + 4]);
+            const float kk[8] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w};
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              const float val = fmaf(rr[hh], __uint_as_float(acc[g * 8 + j]), dd[hh] * S.ks[h * kD + g * 8 + j]);
+              const float val = fmaf(rr[hh], __uint_as_float(acc[g * 8 + j]), dd[hh] * kk[j]);
               o8[j] = m[j] > 0.f ? val : 0.f;
             }
             outv[hh][g] = pack8(o8);
@@ -559,7 +606,9 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&S.dq_empty));
+        if (te == 0) TRACE(0, 19);
         mbar_wait(smem_u32(&S.pair_done), bt & 1);   // the MMAs have finished reading the dO / Q~ tiles
+        if (te == 0) TRACE(0, 20);
         uint8_t* orow = &S.slots[sd][row_off];
 #pragma unroll
         for (int hh = 0; hh < kHH; ++hh)
@@ -656,6 +705,20 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
 
 }  // namespace
 }  // namespace yat
+
+#ifdef YAT_BWD_PROBE
+extern "C" int yat_bwd_probe_reset() {
+  int z[4] = {0, 0, 0, 0};
+  return (int)cudaMemcpyToSymbol(yat::g_trn, z, sizeof(z));
+}
+extern "C" int yat_bwd_probe_read(int role, long long* out, int max_n) {
+  int n[4];
+  if (cudaMemcpyFromSymbol(n, yat::g_trn, sizeof(n)) != cudaSuccess) return -1;
+  const int m = n[role] < max_n ? n[role] : max_n;
+  if (cudaMemcpyFromSymbol(out, yat::g_tr, (size_t)m * sizeof(long long), (size_t)role * 4096 * sizeof(long long)) != cudaSuccess) return -1;
+  return m;
+}
+#endif
 
 extern "C" int yat_linattn_bwd(const void* q, const void* k, const void* v, const void* dout, int B, int N, int H,
                                int D, void* dq, void* dk, void* dv, void* stream) {
