@@ -6,15 +6,18 @@
 //   dQ_n  = (r_n (dO_n KV^T) + dDen_n Ks) * [q_n > 0]
 //   dKV   = sum_n (r_n Q_n)^T dO_n          dKs = sum_n Q_n dDen_n
 //   dK_n  = (V_n dKV^T + dKs) * [k_n > 0]    dV_n = K_n dKV
+// Every reduction over tokens or over a head's 32 columns runs on the tensor core (the column sums Ks and dKs as
+// 16-column MMAs against a ones / per-row-weight operand, den as a 33rd column of the KV operand): the CUDA cores only
+// do elementwise work on their own rows, so pass B has no cross-thread shared-memory traffic and no CTA-wide barrier.
 // Nothing but q, k, v, dO is read (O is recomputed: it is what gradient checkpointing would do anyway),
 // so the algorithmic traffic is 7 tensors; k and v are streamed twice (pass A and pass C), the second time
 // mostly out of L2.
 //
 // Work item = (batch, 4 heads) = a 128-column stripe, streamed in 128-token tiles through a ring of 32 KB
 // shared-memory slots ([2 halves][128 tokens][64 cols], SWIZZLE_128B), exactly like the forward kernel:
-//   pass A   K V  pairs -> D_KV [128x128] += relu(K)^T V (diagonal 32x32 blocks = per-head KV), Ks
-//   pass B   Q dO pairs -> num = Q KV -> r, dDen; Q~ = bf16(r Q) in place;
-//            dQ~ = dO KV^T (raw dO, exact) ; D_dKV += Q~^T dO ; dQ leaves from the dO slot
+//   pass A   K V  pairs -> D_KV [128x128] += relu(K)^T V (diagonal 32x32 blocks = per-head KV), Ks = relu(K)^T 1
+//   pass B   Q dO pairs -> [num | den] = Q [KV | Ks] -> r, dDen; Q~ = bf16(r Q) in place;
+//            dQ~ = dO KV^T (raw dO, exact) ; D_dKV += Q~^T dO ; D_dKs += Q~^T (dDen / r) ; dQ leaves from the dO slot
 //   pass C   K V  pairs -> dV = relu(K) dKV, dK = V dKV^T + dKs ; both leave from their own slots
 // The 32x32 KV / dKV operands are split into bf16 hi + lo and the per-row scales of dQ are applied in the fp32
 // epilogue, so the contractions whose operand is an ACCUMULATED quantity keep ~fp32 accuracy like the reference's
@@ -26,8 +29,8 @@
 // Roles (608 threads): warp 0 TMA producer, warp 1 tcgen05 issuer, warps 2..17 transform/epilogue (16 warps: the
 // CUDA-core work between the MMAs is what bounds the kernel, and 8 warps left the schedulers idle 70 % of the
 // time), warp 18 TMA-store + slot release.  Passes B and C are software-pipelined by one tile: the epilogue warps
-// transform tile t+1 (relu, den) before they finish tile t, the issuer orders the tensor pipe dQ~(t), num(t+1),
-// dKV(t), and pass C double-buffers its dV / dK accumulators in TMEM - the MMA + mbarrier round trips that used
+// transform tile t+1 (relu) before they finish tile t, the issuer orders the tensor pipe dQ~(t), dKV(t) + dKs(t),
+// num(t+1), and pass C double-buffers its dV / dK accumulators in TMEM - the MMA + mbarrier round trips that used
 // to sit between E1 -> E2 -> E3 of one tile now overlap the neighbouring tile's CUDA-core work.  Parity waits follow one rule: every waiter observes every phase of
 // the barriers it waits on, in order.
 #include <cstdio>
@@ -53,12 +56,16 @@ constexpr int kTStep = kTile / kTRows;             // row stride of the transfor
 constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kThreads = 64 + kEpiThreads + 32;
 constexpr int kTmemCols = 512;
-constexpr int kBmatBytes = 2048;
+constexpr int kNB = 48;                            // N of the num MMA: 32 KV columns + Ks (-> den) + padding to 16
+constexpr int kBmatBytes = kD * kNB * 2;           // one [32 x 48] bf16 operand: columns 0..31 = X_head, column 32 = Ks_head
+constexpr int kVecBytes = kTile * 16 * 2;          // a [128 tokens x 16] MN-major operand (ones / per-row weights)
 // TMEM columns
-constexpr uint32_t kColKV = 0;     // pass A accumulator; pass C: dV
+constexpr uint32_t kColKV = 0;     // pass A accumulator (dead once the operands are built); pass B: dQ~
+constexpr uint32_t kColDQ = 0;
 constexpr uint32_t kColDKV = 128;  // pass B accumulator
-constexpr uint32_t kColNum = 256;  // pass B: num, pass C: dK
-constexpr uint32_t kColDQ = 384;   // pass B: dQ~
+constexpr uint32_t kColNum = 256;  // pass B: [num | den] per head, 4 x 48 columns
+constexpr uint32_t kColDks = 448;  // pass B: Q~^T [w_hi | w_lo] (16 columns)
+constexpr uint32_t kColKs = 464;   // pass A: relu(K)^T 1 (16 columns, column 0 = Ks)
 // pass C accumulators, double-buffered by tile parity: dV at 0 / 128, dK at 256 / 384 (dKV and dQ~ are dead by then)
 constexpr uint32_t kColDV = 0;
 constexpr uint32_t kColDK = 256;
@@ -66,12 +73,11 @@ constexpr uint32_t kColBuf = 128;
 
 struct BwdSmem {
   uint8_t slots[kStages][kSlotBytes];           // 1024-aligned
-  uint8_t bmat[kHeadsPerItem][2][kBmatBytes];   // [head][hi|lo] 32x32: KV in pass B, dKV in pass C
-  float den[2][kTile][kHeadsPerItem];           // by tile parity: E1 of tile t+1 runs before E2 of tile t
-  float wrow[2][kTile][kHeadsPerItem];          // dDen / r per row and head (weights of the dKs sum)
+  uint8_t bmat[kHeadsPerItem][2][kBmatBytes];   // [head][hi|lo] [32 x 48]: [KV | Ks] in pass B, dKV in pass C
+  uint8_t ones[kVecBytes];                      // [128 tokens x 16] MN-major, column 0 = 1: relu(K)^T ones = Ks on the tensor core
+  uint8_t wm[kVecBytes];                        // same layout, columns h / 4 + h = hi / lo of (dDen / r) of head h: Q~^T wm = dKs
   float ks[kHeadsPerItem * kD];
   float dks[kHeadsPerItem * kD];
-  float red[kEpiWarps][kHeadsPerItem * kD];
   uint64_t full[kStages], empty[kStages], ready[kStages], out_ready[kStages];
   uint64_t kv_full, b_ready, dkv_full, b2_ready;
   uint64_t num_full, num_empty, dq_full, dq_empty, pair_done, c_full[2], c_empty[2];
@@ -82,6 +88,8 @@ static_assert(kBwdSmemBytes <= 232448, "backward kernel exceeds the 227 KB share
 
 constexpr uint32_t kIdescTT = make_idesc_bf16(128, 128, 1, 1);  // X^T Y over tokens: A, B MN-major
 constexpr uint32_t kIdescMN = make_idesc_bf16(128, 32, 0, 1);   // rows x 32x32 operand read as [k][n]
+constexpr uint32_t kIdescNum = make_idesc_bf16(128, kNB, 0, 1); // rows x [32 x 48] operand: numerator and den in one MMA
+constexpr uint32_t kIdescVec = make_idesc_bf16(128, 16, 1, 1);  // X^T [tokens x 16] over tokens: column sums on the tensor core
 constexpr uint32_t kIdescK = make_idesc_bf16(128, 32, 0, 0);    // rows x transposed 32x32 operand
 
 __device__ __forceinline__ uint4 relu8(uint4 v) {
@@ -182,6 +190,13 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
     tma_prefetch_desc(&M.q); tma_prefetch_desc(&M.k); tma_prefetch_desc(&M.v); tma_prefetch_desc(&M.d_o);
     tma_prefetch_desc(&M.dq); tma_prefetch_desc(&M.dk); tma_prefetch_desc(&M.dv);
   }
+  // operand padding stays zero for the whole kernel: bmat columns 33..47, wm / ones columns 8..15; ones column 0 = 1
+  for (int i = threadIdx.x; i < (int)(sizeof(S.bmat) + sizeof(S.ones) + sizeof(S.wm)) / 16; i += kThreads)
+    reinterpret_cast<uint4*>(&S.bmat[0][0][0])[i] = make_uint4(0, 0, 0, 0);
+  __syncthreads();
+  if (threadIdx.x < kTile)   // element [token][n] of a vector operand at (n/8)*2048 + (token/8)*128 + (token%8)*16 + (n%8)*2
+    *reinterpret_cast<uint32_t*>(&S.ones[(threadIdx.x >> 3) * 128 + (threadIdx.x & 7) * 16]) = 0x00003f80u;   // bf16 1.0
+  fence_proxy_async();
   if (warp == 1) {
     tmem_alloc(smem_u32(&S.tmem_base), kTmemCols);
     tmem_relinquish();
@@ -237,11 +252,12 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
       // of an immediate per MMA instead of re-encoding.
       const uint64_t bmat_mn = make_smem_desc(smem_u32(&S.bmat[0][0][0]), 128, 512, kLayoutNone);   // operand [k][n] as stored
       const uint64_t bmat_k = make_smem_desc(smem_u32(&S.bmat[0][0][0]), 512, 128, kLayoutNone);    // same bytes as the transpose
-      auto small_mmas = [&](uint32_t acc_col, uint32_t a_slot, bool transposed) {
+      auto small_mmas = [&](uint32_t acc_col, uint32_t a_slot, bool transposed, uint32_t idesc_mn = kIdescMN,
+                            uint32_t head_cols = kD) {
         const uint64_t a0 = make_smem_desc(a_slot, 16, 1024, kLayoutSw128);
 #pragma unroll
         for (int h = 0; h < kHeadsPerItem; ++h) {
-          const uint32_t d = tmem + acc_col + h * kD;
+          const uint32_t d = tmem + acc_col + h * head_cols;
           const uint32_t aoff = (h >> 1) * kHalfBytes + (h & 1) * 64;  // 32 columns = 64 B inside the 128 B row
 #pragma unroll
           for (int hl = 0; hl < (PROBE_SKIP(64) ? 1 : 2); ++hl) {
@@ -251,7 +267,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
               const uint64_t da = a0 + ((aoff + ks * 32) >> 4);
               if (!transposed) {
                 // MN-major: 8-k group stride (LBO) 128 B, 8-n group stride (SBO) 512 B; K step of 16 = 256 B
-                umma_bf16(d, da, bmat_mn + ((boff + ks * 256) >> 4), kIdescMN, (hl | ks) != 0);
+                umma_bf16(d, da, bmat_mn + ((boff + ks * 256) >> 4), idesc_mn, (hl | ks) != 0);
               } else {
                 // K-major view: 8-k chunk stride (LBO) 512 B, 8-n group stride (SBO) 128 B; K step of 16 = 1024 B
                 umma_bf16(d, da, bmat_k + ((boff + ks * 1024) >> 4), kIdescK, (hl | ks) != 0);
@@ -259,6 +275,15 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
             }
           }
         }
+      };
+      // [128 x 16] += X^T vec over the 128 tokens: column sums / weighted column sums of a tile on the tensor core
+      // (vec: MN-major no-swizzle [tokens][16], 8-token group stride 128 B, 8-column group stride 2048 B)
+      auto vec_mmas = [&](uint32_t acc_col, uint32_t x_slot, uint32_t vec_addr, bool first) {
+        const uint64_t x0 = make_smem_desc(x_slot, kHalfBytes, 1024, kLayoutSw128);
+        const uint64_t v0 = make_smem_desc(vec_addr, 128, 2048, kLayoutNone);
+#pragma unroll
+        for (int ks = 0; ks < kTile / 16; ++ks)
+          umma_bf16(tmem + acc_col, x0 + ((ks * 2048) >> 4), v0 + ((ks * 256) >> 4), kIdescVec, !(first && ks == 0));
       };
       // [128 x 128] += X^T Y over the 128 tokens of a tile pair (8 K-steps of 16 tokens = 2048 B each)
       auto big_mmas = [&](uint32_t acc_col, uint32_t x_slot, uint32_t y_slot, bool first) {
@@ -278,6 +303,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           mbar_wait(smem_u32(&S.full[sv]), pv);
           tc_fence_after();
           big_mmas(kColKV, smem_u32(&S.slots[sk][0]), smem_u32(&S.slots[sv][0]), t == 0);
+          vec_mmas(kColKs, smem_u32(&S.slots[sk][0]), smem_u32(&S.ones[0]), t == 0);      // Ks = relu(K)^T 1
           tc_commit(smem_u32(&S.empty[sk]));
           tc_commit(smem_u32(&S.empty[sv]));
         }
@@ -291,7 +317,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           wait_ready(sq0);                                       // relu(Q) in place, den written
           mbar_wait(smem_u32(&S.num_empty), (bt & 1) ^ 1);
           tc_fence_after();
-          small_mmas(kColNum, smem_u32(&S.slots[sq0][0]), false);   // num = relu(Q) KV
+          small_mmas(kColNum, smem_u32(&S.slots[sq0][0]), false, kIdescNum, kNB);   // [num | den] = relu(Q) [KV | Ks]
           tc_commit(smem_u32(&S.num_full));
         }
         for (int t = 0; t < nB; ++t, it += 2, ++bt) {
@@ -310,16 +336,19 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           wait_ready(sd);                                        // Q~ written in place (Q slot)
           tc_fence_after();
           TRACE(1, 33);
+          // the tile's token-axis contractions first (pair_done frees the dO / Q~ slots and lets E3b write dQ), then the
+          // numerator of the next tile: E2(t+1) is a whole epilogue away, E3b(t) is waiting now
+          big_mmas(kColDKV, qa, da_, t == 0);                    // D_dKV += Q~^T dO
+          vec_mmas(kColDks, qa, smem_u32(&S.wm[0]), t == 0);     // D_dKs += Q~^T [w_hi | w_lo]
+          tc_commit(smem_u32(&S.pair_done));
           if (t + 1 < nB) {
             const uint32_t sq1 = (it + 2) % kStages;
             wait_ready(sq1);
             mbar_wait(smem_u32(&S.num_empty), ((bt + 1) & 1) ^ 1);
             tc_fence_after();
-            small_mmas(kColNum, smem_u32(&S.slots[sq1][0]), false);
+            small_mmas(kColNum, smem_u32(&S.slots[sq1][0]), false, kIdescNum, kNB);
             tc_commit(smem_u32(&S.num_full));
           }
-          big_mmas(kColDKV, qa, da_, t == 0);                    // D_dKV += Q~^T dO
-          tc_commit(smem_u32(&S.pair_done));
           TRACE(1, 34);
         }
         tc_commit(smem_u32(&S.dkv_full));
@@ -329,13 +358,17 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         for (int t = 0; t < nC; ++t, it += 2, ++ct) {
           const uint32_t sk = it % kStages, sv = (it + 1) % kStages, pv = ((it + 1) / kStages) & 1;
           const uint32_t buf = ct & 1;
+          TRACE(1, 70);
           wait_ready(sk);
           mbar_wait(smem_u32(&S.full[sv]), pv);
+          TRACE(1, 71);
           mbar_wait(smem_u32(&S.c_empty[buf]), ((ct >> 1) & 1) ^ 1);
           tc_fence_after();
+          TRACE(1, 72);
           small_mmas(kColDV + buf * kColBuf, smem_u32(&S.slots[sk][0]), false);
           small_mmas(kColDK + buf * kColBuf, smem_u32(&S.slots[sv][0]), true);
           tc_commit(smem_u32(&S.c_full[buf]));
+          TRACE(1, 73);
         }
       }
     }
@@ -369,7 +402,9 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         }
         for (int t = 0; t < nC; ++t, it += 2) {
           const uint32_t sk = it % kStages, sv = (it + 1) % kStages;
+          TRACE(2, 80);
           wait_out(sk);
+          TRACE(2, 81);
           store(&M.dk, sk, c0, t * kTile, b);
           tma_store_commit();
           tma_store_wait_read<0>();                      // dV's epilogue is still running: release the K slot now
@@ -379,6 +414,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           tma_store_commit();
           tma_store_wait_read<0>();
           mbar_arrive(smem_u32(&S.empty[sv]));
+          TRACE(2, 82);
         }
       }
       tma_store_wait_all<0>();
@@ -390,11 +426,6 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
     const int cc = te & 15;                   // transform mapping: 16-byte chunk column of the 256-byte item row
     const int rbase = te >> 4;                //                    rows rbase + kTStep i
     const int half = cc >> 3, chunk = cc & 7;
-    // Head (0..3) owning this thread's chunk column.  Kept opaque to the optimiser: nvcc 12.9 otherwise folds
-    // `[r][cc >> 2]` into `base + 16 r + cc` (valid only under the `(cc & 3) == 0` predicate of the den store)
-    // and reuses that address for the unpredicated wrow load, which then faults as a misaligned access.
-    int hsel = cc >> 2;
-    asm volatile("" : "+r"(hsel));
     const int quad = warp & 3;                // TMEM lane quadrant this warp may access
     const int colsel = we >> 2;               // row mapping: heads colsel * kHH .. + kHH - 1 are finished by this warp
     const int row = quad * 32 + lane;         //              token row in the tile (TMEM lane)
@@ -405,29 +436,35 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
     const int ch0 = (h0 & 1) * 4;
     uint32_t it = 0, bt = 0, ct = 0, item_iter = 0;
 
-    // column sums held per thread (transform mapping) -> dst[128] through S.red; all epilogue threads call it
-    auto reduce_columns = [&](float (&cs)[8], float* dst) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], 16);
-      if (lane < 16) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) S.red[we][cc * 8 + j] = cs[j];
-      }
-      named_bar_sync(1, kEpiThreads);
-      if (te < kHeadsPerItem * kD) {
-        float s = 0.f;
-#pragma unroll
-        for (int w = 0; w < kEpiWarps; ++w) s += S.red[w][te];
-        dst[te] = s;
-      }
-    };
     // diagonal 32x32 blocks of a [128x128] accumulator -> hi/lo operands in S.bmat (warps with we < 4: head = quad)
-    auto build_bmat = [&](uint32_t col) {
+    // The column sums that go with it come off the tensor core too (this thread's TMEM lane = column quad*32 + lane):
+    // with_ks: Ks = relu(K)^T 1 -> S.ks and column 32 of the operand (so the num MMA also yields den);
+    // else:    dKs = Q~^T [w_hi | w_lo] -> S.dks.
+    auto build_bmat = [&](uint32_t col, bool with_ks) {
       if (we < 4) {
         uint32_t r[32];
         tmem_ld32(tmem + lane_addr + col + quad * kD, r);   // X_head[k = lane][n = 0..31]
+        uint32_t v8[8];
+        tmem_ld8(tmem + lane_addr + (with_ks ? kColKs : kColDks), v8);
         tmem_ld_wait();
         store_bmat_hilo(&S.bmat[quad][0][0], &S.bmat[quad][1][0], lane, r);
+        if (with_ks) {
+          const float ks = __uint_as_float(v8[0]);
+          S.ks[quad * kD + lane] = ks;
+          const uint32_t khi = pack_bf16(ks, 0.f);
+          const uint32_t klo = pack_bf16(ks - bf16_lo(khi), 0.f);
+          const int off = 4 * 512 + (lane >> 3) * 128 + (lane & 7) * 16;   // [k = lane][n = 32]
+          *reinterpret_cast<uint4*>(&S.bmat[quad][0][off]) = make_uint4(khi, 0, 0, 0);
+          *reinterpret_cast<uint4*>(&S.bmat[quad][1][off]) = make_uint4(klo, 0, 0, 0);
+        } else {
+          float hi = 0.f, lo = 0.f;
+#pragma unroll
+          for (int j = 0; j < kHeadsPerItem; ++j) {                        // select column `quad` without dynamic indexing
+            hi = j == quad ? __uint_as_float(v8[j]) : hi;
+            lo = j == quad ? __uint_as_float(v8[kHeadsPerItem + j]) : lo;
+          }
+          S.dks[quad * kD + lane] = hi + lo;
+        }
         fence_proxy_async();
       }
       tc_fence_before();
@@ -436,7 +473,6 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
 
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++item_iter) {
       // ---------------- pass A: relu(K) in place, Ks ----------------
-      float csum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
       for (int t = 0; t < nA; ++t, it += 2) {
         const uint32_t sk = it % kStages, pk = (it / kStages) & 1;
         mbar_wait(smem_u32(&S.full[sk]), pk);
@@ -445,66 +481,44 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         for (int i = 0; i < kTRows; ++i) {
           const int r = rbase + kTStep * i;
           uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
-          const uint4 v = relu8(*p);
-          *p = v;
-          float f[8];
-          unpack8f(v, f);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) csum[j] += f[j];
+          *p = relu8(*p);
         }
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&S.ready[sk]));
         mbar_wait(smem_u32(&S.full[(it + 1) % kStages]), ((it + 1) / kStages) & 1);  // observe the V phase too
       }
-      reduce_columns(csum, S.ks);
       mbar_wait(smem_u32(&S.kv_full), item_iter & 1);
       tc_fence_after();
-      build_bmat(kColKV);                       // barrier inside: ks visible, D_KV drained, bmat written
+      build_bmat(kColKV, true);                 // barrier inside: S.ks visible, D_KV drained, [KV | Ks] operands written
       if (lane == 0) mbar_arrive(smem_u32(&S.b_ready));
       // ---------------- pass B ----------------
       // Software-pipelined by one tile: E1(t+1) (relu(Q), den) runs BEFORE E2(t) / E3(t), so the num MMA of tile t+1
       // and its mbarrier round trip overlap this tile's epilogue instead of sitting on the critical path.
-      float dcs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-      // E1: relu(Q) in place, den = relu(Q).Ks  (tile with ring index `jt`, den buffer `db`)
-      auto e1 = [&](uint32_t jt, int db) {
+      // E1: relu(Q) in place.  den = relu(Q).Ks comes out of the num MMA (column 32 of the [KV | Ks] operand) and
+      // dKs = sum_n Q~_n (dDen_n / r_n) out of a 16-column MMA on the weights E2 leaves in S.wm: no CUDA-core dot
+      // products, no cross-thread traffic through shared memory and no CTA-wide barrier are left in this pass.
+      auto e1 = [&](uint32_t jt) {
         const uint32_t sq = jt % kStages, pq = (jt / kStages) & 1;
         mbar_wait(smem_u32(&S.full[sq]), pq);
         uint8_t* base = &S.slots[sq][half * kHalfBytes];
-        float ksr[8];                               // re-read per tile (two 128-bit loads): 8 fewer registers live across the pass
-        {
-          const float4 k0 = *reinterpret_cast<const float4*>(&S.ks[cc * 8]), k1 = *reinterpret_cast<const float4*>(&S.ks[cc * 8 + 4]);
-          ksr[0] = k0.x; ksr[1] = k0.y; ksr[2] = k0.z; ksr[3] = k0.w; ksr[4] = k1.x; ksr[5] = k1.y; ksr[6] = k1.z; ksr[7] = k1.w;
-        }
 #pragma unroll
         for (int i = 0; i < kTRows; ++i) {
           const int r = rbase + kTStep * i;
           uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
-          const uint4 v = relu8(*p);
-          *p = v;
-          float f[8], d = 0.f;
-          unpack8f(v, f);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) d = fmaf(f[j], ksr[j], d);
-          d += __shfl_xor_sync(0xffffffffu, d, 1);
-          d += __shfl_xor_sync(0xffffffffu, d, 2);
-          if ((cc & 3) == 0) S.den[db][r][hsel] = d;
+          *p = relu8(*p);
         }
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&S.ready[sq]));
       };
-      if (nB > 0) e1(it, bt & 1);
+      if (nB > 0) e1(it);
       for (int t = 0; t < nB; ++t, it += 2, ++bt) {
         const uint32_t sq = it % kStages;
         const uint32_t sd = (it + 1) % kStages, pd = ((it + 1) / kStages) & 1;
-        const int db = bt & 1;
         if (te == 0) TRACE(0, 10);
-        if (t + 1 < nB) e1(it + 2, db ^ 1);
+        if (t + 1 < nB) e1(it + 2);
         if (te == 0) TRACE(0, 11);
-        // den(t) visible in the row mapping; every warp is past E3a(t-1), so S.lo may be rewritten below
-        named_bar_sync(1, kEpiThreads);
-        if (te == 0) TRACE(0, 12);
 
         // E2: num -> r, dDen; Q~ = bf16(r * relu(Q)) in place
         mbar_wait(smem_u32(&S.full[sd]), pd);
@@ -521,8 +535,9 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
 #pragma unroll
         for (int hh = 0; hh < kHH; ++hh) {
           const int h = h0 + hh;
-          uint32_t acc[32];
-          tmem_ld32(tmem + lane_addr + kColNum + h * kD, acc);
+          uint32_t acc[32], dn;
+          tmem_ld32(tmem + lane_addr + kColNum + h * kNB, acc);
+          tmem_ld1(tmem + lane_addr + kColNum + h * kNB + kD, dn);       // den = relu(Q_n).Ks
           tmem_ld_wait();
           float s = 0.f;
 #pragma unroll
@@ -532,10 +547,17 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
 #pragma unroll
             for (int j = 0; j < 8; ++j) s = fmaf(f[j], __uint_as_float(acc[g * 8 + j]), s);
           }
-          const float r = 1.0f / (S.den[db][row][h] + 1e-15f);
+          const float r = 1.0f / (__uint_as_float(dn) + 1e-15f);
           rr[hh] = r;
           dd[hh] = -s * r * r;
-          S.wrow[db][row][h] = -s * r;
+          {  // dDen / r as bf16 hi + lo, columns h and 4 + h of the [tokens x 16] operand of the dKs MMA
+            const float w = -s * r;
+            const __nv_bfloat16 whi = __float2bfloat16_rn(w);
+            const __nv_bfloat16 wlo = __float2bfloat16_rn(w - __bfloat162float(whi));
+            __nv_bfloat16* wr = reinterpret_cast<__nv_bfloat16*>(&S.wm[(row >> 3) * 128 + (row & 7) * 16]);
+            wr[h] = whi;
+            wr[kHeadsPerItem + h] = wlo;
+          }
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             const int o = ((ch0 + hh * 4 + g) ^ (row & 7)) << 4;
@@ -554,23 +576,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           mbar_arrive(smem_u32(&S.ready[sd]));
         }
         if (te == 0) TRACE(0, 15);
-        named_bar_sync(1, kEpiThreads);         // wrow and Q~ visible in the transform mapping
-        if (te == 0) TRACE(0, 16);
 
-        // E3a: dKs += sum_n Q~_n (dDen_n / r_n)
-        if (!PROBE_SKIP(8)) {
-          const uint8_t* bh = &S.slots[sq][half * kHalfBytes];
-#pragma unroll
-          for (int i = 0; i < kTRows; ++i) {
-            const int r = rbase + kTStep * i;
-            const int o = r * 128 + ((chunk ^ (r & 7)) << 4);
-            float fh[8];
-            unpack8f(*reinterpret_cast<const uint4*>(bh + o), fh);
-            const float w = S.wrow[db][r][hsel];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) dcs[j] = fmaf(fh[j], w, dcs[j]);
-          }
-        }
         // E3b: dQ = (r * dQ~ + dDen * Ks) * [q > 0]
         if (te == 0) TRACE(0, 17);
         mbar_wait(smem_u32(&S.dq_full), bt & 1);
@@ -619,10 +625,9 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&S.out_ready[sd]));
       }
-      reduce_columns(dcs, S.dks);
       mbar_wait(smem_u32(&S.dkv_full), item_iter & 1);
       tc_fence_after();
-      build_bmat(kColDKV);                      // barrier inside: dks visible, D_dKV drained, bmat rewritten
+      build_bmat(kColDKV, false);               // barrier inside: S.dks visible, D_dKV / D_dKs drained, operands rewritten
       if (lane == 0) mbar_arrive(smem_u32(&S.b2_ready));
       // ---------------- pass C ----------------
       // Same skew: relu(K) of tile t+1 is done before the epilogue of tile t, and the dV / dK accumulators are
@@ -645,10 +650,13 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
       for (int t = 0; t < nC; ++t, it += 2, ++ct) {
         const uint32_t sk = it % kStages, sv = (it + 1) % kStages;
         const uint32_t buf = ct & 1;
+        if (te == 0) TRACE(0, 60);
         if (t + 1 < nC) relu_k(it + 2);
+        if (te == 0) TRACE(0, 61);
         mbar_wait(smem_u32(&S.full[sv]), ((it + 1) / kStages) & 1);   // observe the V phase (complete: the MMA read it)
         mbar_wait(smem_u32(&S.c_full[buf]), (ct >> 1) & 1);   // both MMAs done: K and V tiles may be overwritten
         tc_fence_after();
+        if (te == 0) TRACE(0, 62);
         // dK = (V dKV^T + dKs) * [k > 0]  -> K slot
         uint8_t* krow = &S.slots[sk][row_off];
 #pragma unroll
@@ -662,15 +670,18 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
             uint4* p = reinterpret_cast<uint4*>(krow + (((ch0 + hh * 4 + g) ^ (row & 7)) << 4));
             float m[8], o8[8];
             unpack8f(*p, m);
+            const float4 k0 = *reinterpret_cast<const float4*>(&S.dks[h * kD + g * 8]);      // broadcast 128-bit loads
+            const float4 k1 = *reinterpret_cast<const float4*>(&S.dks[h * kD + g * 8 + 4]);
+            const float kk[8] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w};
 #pragma unroll
-            for (int j = 0; j < 8; ++j)
-              o8[j] = m[j] > 0.f ? __uint_as_float(acc[g * 8 + j]) + S.dks[h * kD + g * 8 + j] : 0.f;
+            for (int j = 0; j < 8; ++j) o8[j] = m[j] > 0.f ? __uint_as_float(acc[g * 8 + j]) + kk[j] : 0.f;
             *p = pack8(o8);
           }
         }
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&S.out_ready[sk]));
+        if (te == 0) TRACE(0, 63);
         // dV = relu(K) dKV -> V slot
         uint8_t* vrow = &S.slots[sv][row_off];
 #pragma unroll
@@ -694,6 +705,7 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           mbar_arrive(smem_u32(&S.c_empty[buf]));
           mbar_arrive(smem_u32(&S.out_ready[sv]));
         }
+        if (te == 0) TRACE(0, 64);
       }
     }
   }
