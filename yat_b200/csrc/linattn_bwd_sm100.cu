@@ -99,12 +99,19 @@ __device__ __forceinline__ uint4 relu8(uint4 v) {
   for (int i = 0; i < 4; ++i) h[i] = __hmax2_nan(h[i], z);
   return v;
 }
-__device__ __forceinline__ void unpack8f(const uint4& v, float f[8]) {
-  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
-  f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
-}
 __device__ __forceinline__ uint4 pack8(const float f[8]) {
   return make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+}
+
+// packed-pair helpers for the row epilogues (FFMA2 / FMUL2: one issue slot per two columns; common.cuh)
+__device__ __forceinline__ f2 acc2(const uint32_t (&r)[32], int i) {      // columns 2i, 2i+1 of a tcgen05.ld row
+  return mk2(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
+}
+__device__ __forceinline__ uint32_t word(const uint4& v, int i) { return i == 0 ? v.x : (i == 1 ? v.y : (i == 2 ? v.z : v.w)); }
+// keep the halves of a packed bf16 pair whose mask half is > 0 (the ReLU mask of a gradient: q > 0 / k > 0), zero the rest
+__device__ __forceinline__ uint32_t mask_pos(uint32_t val, uint32_t m) {
+  const __nv_bfloat162 keep = __hgt2(as_bf162(m), __float2bfloat162_rn(0.f));   // 1.0 / 0.0 per half
+  return as_u32(__hmul2(as_bf162(val), keep));
 }
 
 // 32x32 fp32 block held as one row (32 values) per lane -> bf16 hi + lo, MN-major no-swizzle core matrices:
@@ -539,14 +546,16 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           tmem_ld32(tmem + lane_addr + kColNum + h * kNB, acc);
           tmem_ld1(tmem + lane_addr + kColNum + h * kNB + kD, dn);       // den = relu(Q_n).Ks
           tmem_ld_wait();
-          float s = 0.f;
+          f2 s2 = bc2(0.f);
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
-            float f[8];
-            unpack8f(*reinterpret_cast<const uint4*>(drow + (((ch0 + hh * 4 + g) ^ (row & 7)) << 4)), f);
+            const uint4 dv = *reinterpret_cast<const uint4*>(drow + (((ch0 + hh * 4 + g) ^ (row & 7)) << 4));
 #pragma unroll
-            for (int j = 0; j < 8; ++j) s = fmaf(f[j], __uint_as_float(acc[g * 8 + j]), s);
+            for (int j = 0; j < 4; ++j) s2 = fma2(unpack2(word(dv, j)), acc2(acc, g * 4 + j), s2);
           }
+          float s, s_hi;
+          un2(s2, s, s_hi);
+          s += s_hi;
           const float r = 1.0f / (__uint_as_float(dn) + 1e-15f);
           rr[hh] = r;
           dd[hh] = -s * r * r;
@@ -561,11 +570,11 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             const int o = ((ch0 + hh * 4 + g) ^ (row & 7)) << 4;
-            float f[8];
-            unpack8f(*reinterpret_cast<const uint4*>(qrow + o), f);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) f[j] *= r;
-            *reinterpret_cast<uint4*>(qrow + o) = pack8(f);
+            const uint4 qv = *reinterpret_cast<const uint4*>(qrow + o);
+            const f2 r2 = bc2(r);
+            *reinterpret_cast<uint4*>(qrow + o) =
+                make_uint4(pack2(mul2(unpack2(qv.x), r2)), pack2(mul2(unpack2(qv.y), r2)), pack2(mul2(unpack2(qv.z), r2)),
+                           pack2(mul2(unpack2(qv.w), r2)));
           }
         }
         tc_fence_before();
@@ -594,19 +603,18 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
           uint32_t acc[32];
           tmem_ld32(tmem + lane_addr + kColDQ + h * kD, acc);
           tmem_ld_wait();
+          const f2 r2 = bc2(rr[hh]), d2 = bc2(dd[hh]);
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
-            float m[8], o8[8];
-            unpack8f(*reinterpret_cast<const uint4*>(qrow + (((ch0 + hh * 4 + g) ^ (row & 7)) << 4)), m);
+            const uint4 mv = *reinterpret_cast<const uint4*>(qrow + (((ch0 + hh * 4 + g) ^ (row & 7)) << 4));   // Q~ >= 0: the mask
             const float4 k0 = *reinterpret_cast<const float4*>(&S.ks[h * kD + g * 8]);       // broadcast 128-bit loads
             const float4 k1 = *reinterpret_cast<const float4*>(&S.ks[h * kD + g * 8 + 4]);
-            const float kk[8] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w};
+            const f2 kk[4] = {mk2(k0.x, k0.y), mk2(k0.z, k0.w), mk2(k1.x, k1.y), mk2(k1.z, k1.w)};
+            uint32_t w4[4];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float val = fmaf(rr[hh], __uint_as_float(acc[g * 8 + j]), dd[hh] * kk[j]);
-              o8[j] = m[j] > 0.f ? val : 0.f;
-            }
-            outv[hh][g] = pack8(o8);
+            for (int j = 0; j < 4; ++j)
+              w4[j] = mask_pos(pack2(fma2(r2, acc2(acc, g * 4 + j), mul2(d2, kk[j]))), word(mv, j));
+            outv[hh][g] = make_uint4(w4[0], w4[1], w4[2], w4[3]);
           }
         }
         tc_fence_before();
@@ -668,14 +676,14 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             uint4* p = reinterpret_cast<uint4*>(krow + (((ch0 + hh * 4 + g) ^ (row & 7)) << 4));
-            float m[8], o8[8];
-            unpack8f(*p, m);
+            const uint4 mv = *p;                                                             // relu(k) >= 0: the mask
             const float4 k0 = *reinterpret_cast<const float4*>(&S.dks[h * kD + g * 8]);      // broadcast 128-bit loads
             const float4 k1 = *reinterpret_cast<const float4*>(&S.dks[h * kD + g * 8 + 4]);
-            const float kk[8] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w};
+            const f2 kk[4] = {mk2(k0.x, k0.y), mk2(k0.z, k0.w), mk2(k1.x, k1.y), mk2(k1.z, k1.w)};
+            uint32_t w4[4];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) o8[j] = m[j] > 0.f ? __uint_as_float(acc[g * 8 + j]) + kk[j] : 0.f;
-            *p = pack8(o8);
+            for (int j = 0; j < 4; ++j) w4[j] = mask_pos(pack2(add2(acc2(acc, g * 4 + j), kk[j])), word(mv, j));
+            *p = make_uint4(w4[0], w4[1], w4[2], w4[3]);
           }
         }
         fence_proxy_async();
