@@ -137,22 +137,6 @@ struct BwdMaps {
   CUtensorMap q, k, v, d_o, dq, dk, dv;
 };
 
-#ifdef YAT_BWD_PROBE   // experiment build only: per-role (code, clock64) event trace of CTA 0
-__device__ long long g_tr[4][4096];
-__device__ int g_trn[4];
-#define TRACE(role, code)                                                                          \
-  do {                                                                                             \
-    if (blockIdx.x == 0) {                                                                         \
-      const int i_ = g_trn[role];                                                                  \
-      if (i_ < 4096) {                                                                             \
-        g_tr[role][i_] = ((long long)(code) << 48) | (clock64() & 0xffffffffffffll);               \
-        g_trn[role] = i_ + 1;                                                                      \
-      }                                                                                            \
-    }                                                                                              \
-  } while (0)
-#else
-#define TRACE(role, code) do { } while (0)
-#endif
 
 __global__ void __launch_bounds__(kThreads, 1)
 #ifdef YAT_BWD_PROBE   // timing experiment build only (scripts/linattn_bwd_probe.py); never defined for the product library
@@ -726,19 +710,8 @@ linattn_bwd_sm100_kernel(const __grid_constant__ BwdMaps M, int B, int N, int gr
 }  // namespace
 }  // namespace yat
 
-#ifdef YAT_BWD_PROBE
-extern "C" int yat_bwd_probe_reset() {
-  int z[4] = {0, 0, 0, 0};
-  return (int)cudaMemcpyToSymbol(yat::g_trn, z, sizeof(z));
-}
-extern "C" int yat_bwd_probe_read(int role, long long* out, int max_n) {
-  int n[4];
-  if (cudaMemcpyFromSymbol(n, yat::g_trn, sizeof(n)) != cudaSuccess) return -1;
-  const int m = n[role] < max_n ? n[role] : max_n;
-  if (cudaMemcpyFromSymbol(out, yat::g_tr, (size_t)m * sizeof(long long), (size_t)role * 4096 * sizeof(long long)) != cudaSuccess) return -1;
-  return m;
-}
-#endif
+
+YAT_DEFINE_TRACE_API(yat_bwd)
 
 extern "C" int yat_linattn_bwd(const void* q, const void* k, const void* v, const void* dout, int B, int N, int H,
                                int D, void* dq, void* dk, void* dv, void* stream) {

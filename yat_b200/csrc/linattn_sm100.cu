@@ -151,10 +151,13 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
         for (int t = 0; t < (kState ? 0 : n_tiles); ++t, it += 2) {
           const uint32_t sk = it % kStages;
           const uint32_t sv = (it + 1) % kStages, pv = ((it + 1) / kStages) & 1;
+          TRACE(1, 50);
           mbar_wait(smem_u32(&S.ready[sk]), (ready_ph >> sk) & 1);
           ready_ph ^= 1u << sk;
+          TRACE(1, 51);
           mbar_wait(smem_u32(&S.full[sv]), pv);  // V is consumed as loaded
           tc_fence_after();
+          TRACE(1, 52);
           const uint32_t ka = smem_u32(&S.slots[sk][0]), va = smem_u32(&S.slots[sv][0]);
 #pragma unroll
           for (int ks = 0; ks < kTile / 16; ++ks) {
@@ -165,6 +168,7 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
           }
           tc_commit(smem_u32(&S.empty[sk]));
           tc_commit(smem_u32(&S.empty[sv]));
+          TRACE(1, 53);
         }
         if (!kState) tc_commit(smem_u32(&S.d1_full));
         mbar_wait(smem_u32(&S.b_ready), item_iter & 1);
@@ -174,10 +178,13 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
           const uint32_t sq = it % kStages;
           const uint32_t g = t & 1, pb = d2_use[g] & 1;
           ++d2_use[g];
+          TRACE(1, 30);
           mbar_wait(smem_u32(&S.ready[sq]), (ready_ph >> sq) & 1);
           ready_ph ^= 1u << sq;
+          TRACE(1, 31);
           mbar_wait(smem_u32(&S.d2_empty[g]), pb ^ 1);
           tc_fence_after();
+          TRACE(1, 32);
           const uint32_t qa = smem_u32(&S.slots[sq][0]);
 #pragma unroll
           for (int h = 0; h < kHeadsPerItem; ++h) {
@@ -198,6 +205,7 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
             }
           }
           tc_commit(smem_u32(&S.d2_full[g]));
+          TRACE(1, 33);
         }
         if (kState) tc_commit(smem_u32(&S.d1_full));   // every MMA of this item has read bmat: it may be rebuilt
       }
@@ -211,14 +219,17 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
         if (!kState) it += 2 * n_tiles;
         for (int t = 0; t < n_tiles; ++t, ++it) {
           const uint32_t sq = it % kStages;
+          TRACE(2, 40);
           mbar_wait(smem_u32(&S.o_ready[sq]), (o_ph >> sq) & 1);
           o_ph ^= 1u << sq;
+          TRACE(2, 41);
           const uint32_t src = smem_u32(&S.slots[sq][0]);
           tma_store_3d(&tm_o, src, c0, t * kTile, b);
           tma_store_3d(&tm_o, src + kHalfBytes, c0 + 64, t * kTile, b);
           tma_store_commit();
           tma_store_wait_read<0>();                       // smem has been read: the slot can be refilled
           mbar_arrive(smem_u32(&S.empty[sq]));
+          TRACE(2, 42);
         }
       }
       tma_store_wait_all<0>();
@@ -264,9 +275,13 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
       float csum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
       for (int t = 0; t < (kState ? 0 : n_tiles); ++t, it += 2) {
         const uint32_t sk = it % kStages, pk = (it / kStages) & 1;
+        if (tg == 0) TRACE(grp ? 3 : 0, 20);
         mbar_wait(smem_u32(&S.full[sk]), pk);
+        if (tg == 0) TRACE(grp ? 3 : 0, 21);
         if ((t & 1) == grp) relu_tile(sk, csum);
+        if (tg == 0) TRACE(grp ? 3 : 0, 22);
         mbar_wait(smem_u32(&S.full[(it + 1) % kStages]), ((it + 1) / kStages) & 1);
+        if (tg == 0) TRACE(grp ? 3 : 0, 23);
       }
       // Ks partials: lanes l and l^16 share the chunk column
 #pragma unroll
@@ -339,13 +354,17 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
       // ---- phase 2
       for (int t = 0; t < n_tiles; ++t, ++it) {
         const uint32_t sq = it % kStages, pq = (it / kStages) & 1;
+        if (tg == 0) TRACE(grp ? 3 : 0, 9);
         mbar_wait(smem_u32(&S.full[sq]), pq);
         if ((t & 1) != grp) continue;
+        if (tg == 0) TRACE(grp ? 3 : 0, 10);
         relu_tile(sq, nullptr);
+        if (tg == 0) TRACE(grp ? 3 : 0, 11);
 
         mbar_wait(smem_u32(&S.d2_full[grp]), d2_use & 1);
         ++d2_use;
         tc_fence_after();
+        if (tg == 0) TRACE(grp ? 3 : 0, 12);
         const uint32_t d2 = tmem + lane_base + 128 + grp * kD2Cols;
 #pragma unroll
         for (int h = 0; h < kHeadsPerItem; ++h) {
@@ -372,6 +391,7 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
           mbar_arrive(smem_u32(&S.d2_empty[grp]));
           mbar_arrive(smem_u32(&S.o_ready[sq]));
         }
+        if (tg == 0) TRACE(grp ? 3 : 0, 13);
       }
     }
   }
@@ -445,6 +465,8 @@ int make_tmap_4d_bf16_plain(CUtensorMap* out, const void* base, const uint64_t d
 }
 
 }  // namespace yat
+
+YAT_DEFINE_TRACE_API(yat_fwd)
 
 extern "C" int yat_linattn_fwd(const void* q, const void* k, const void* v, int B, int N, int H, int D, void* o,
                                void* stream) {

@@ -147,6 +147,42 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn_ma
 
 }  // namespace sm100
 
+// ---------------------------------------------------------------- experiment builds only: event trace of CTA 0
+// -DYAT_BWD_PROBE (scripts/linattn_bwd_trace.py): TRACE(role, code) appends (code, clock64) to a per-role device log;
+// called by ONE designated thread per role.  Never defined for the product library (the macro expands to nothing).
+#ifdef YAT_BWD_PROBE
+static __device__ long long g_tr[4][4096];   // one log per translation unit (no relocatable device code in this build)
+static __device__ int g_trn[4];
+#define TRACE(role, code)                                                                          \
+  do {                                                                                             \
+    if (blockIdx.x == 0) {                                                                         \
+      const int i_ = ::yat::g_trn[role];                                                           \
+      if (i_ < 4096) {                                                                             \
+        ::yat::g_tr[role][i_] = ((long long)(code) << 48) | (clock64() & 0xffffffffffffll);        \
+        ::yat::g_trn[role] = i_ + 1;                                                               \
+      }                                                                                            \
+    }                                                                                              \
+  } while (0)
+// host accessors of this translation unit's log: <prefix>_probe_reset(), <prefix>_probe_read(role, out, max_n)
+#define YAT_DEFINE_TRACE_API(prefix)                                                               \
+  extern "C" int prefix##_probe_reset() {                                                          \
+    int z[4] = {0, 0, 0, 0};                                                                       \
+    return (int)cudaMemcpyToSymbol(::yat::g_trn, z, sizeof(z));                                    \
+  }                                                                                                \
+  extern "C" int prefix##_probe_read(int role, long long* out, int max_n) {                        \
+    int n[4];                                                                                      \
+    if (cudaMemcpyFromSymbol(n, ::yat::g_trn, sizeof(n)) != cudaSuccess) return -1;                \
+    const int m = n[role] < max_n ? n[role] : max_n;                                               \
+    if (cudaMemcpyFromSymbol(out, ::yat::g_tr, (size_t)m * sizeof(long long),                      \
+                             (size_t)role * 4096 * sizeof(long long)) != cudaSuccess)              \
+      return -1;                                                                                   \
+    return m;                                                                                      \
+  }
+#else
+#define TRACE(role, code) do { } while (0)
+#define YAT_DEFINE_TRACE_API(prefix)
+#endif
+
 // host: encode a 3-D bf16 tensor map {C, N, B} with a {box_c, box_n, 1} box, 128B swizzle
 int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t N, uint64_t B, uint32_t box_c,
                       uint32_t box_n, uint64_t ld = 0 /* row pitch in elements, 0 = C (dense rows) */);
