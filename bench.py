@@ -450,7 +450,8 @@ def _standalone_kernels(device, pk):
         del wq, qkv_buf, st_buf, o_buf
     except Exception as e:  # noqa: BLE001 — reported, not hidden
         out["gemm_qkv_own_tcgen05"] = {"error": str(e)[:200]}
-    ms = timeit(lambda: sana_linear_attention(q, k, v, H))
+    from yat_b200.linear_attention import _launch_fwd
+    ms = timeit(lambda: _launch_fwd(q, k, v, H, "sm100"))      # the C-ABI call (as for the backward below)
     entry("linattn_fwd_sm100", 8 * B * N * C, ms, [B, N, C], flops=4 * 32 * 33 * N * H * B)
     from yat_b200.linear_attention import _launch_bwd
 

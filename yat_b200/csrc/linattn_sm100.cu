@@ -11,14 +11,16 @@
 //   K0 V0 K1 V1 ... | Q0 Q1 ...         (3 * ceil(N/128) tiles per item; O tiles leave from the Q slot)
 // The grid is persistent (one CTA per SM, loads run ahead across items).
 //
-// Roles (352 threads):
-//   warp 0      TMA producer
-//   warp 1      tcgen05 issuer (one thread)
-//   warps 2-5   transform/epilogue group 0   } the two groups own alternate tiles, so the ReLU pass of
-//   warps 6-9   transform/epilogue group 1   } tile t+1 overlaps the MMA + epilogue of tile t
-//   warp 10     TMA-store warp: O tile out, then the slot goes back to the producer
+// Roles (608 threads):
+//   warp 0       TMA producer
+//   warp 1       tcgen05 issuer (one thread)
+//   warps 2-9    transform/epilogue group 0   } phase 2: the two groups own alternate tiles, so the ReLU pass of
+//   warps 10-17  transform/epilogue group 1   } tile t+1 overlaps the MMA + epilogue of tile t (2 heads per thread)
+//   warp 18      TMA-store warp: O tile out, then the slot goes back to the producer
+// In phase 1 all sixteen warps ReLU every K tile together, and Ks = relu(K)^T 1 is a 16-column MMA against a ones
+// operand (round 2: the CUDA-core column sums + their CTA barrier made the K transform the longest stage of the ring).
 //
-//   phase 1  transform: relu(K) in place (+ fp32 column sums -> Ks)     MMA1: D1[128x128] += relu(K)^T V
+//   phase 1  transform: relu(K) in place     MMA1: D1[128x128] += relu(K)^T V,  Ks[128x16] += relu(K)^T ones
 //            (A and B both MN-major straight from the TMA tiles; the four 32x32 diagonal blocks of D1
 //             are the per-head K^T V, the off-diagonal blocks are discarded — the kernel is HBM-bound)
 //   build    (group 0) D1 diagonal -> registers -> bf16 hi + bf16 lo split -> smem B operand
@@ -41,21 +43,23 @@ constexpr int kTile = 128;                       // tokens per tile
 constexpr int kHalfBytes = kTile * 128;          // [128 tokens][64 cols] bf16
 constexpr int kSlotBytes = 2 * kHalfBytes;       // 32 KB
 constexpr int kStages = 6;
-constexpr int kGroups = 2, kGroupWarps = 4;
+constexpr int kGroups = 2, kGroupWarps = 8;       // two groups of 8 warps: 2 warps per TMEM lane quadrant, 2 heads each
 constexpr int kEpiWarps = kGroups * kGroupWarps;
-constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kStoreWarp = 2 + kEpiWarps;
 constexpr int kThreads = 32 * (kStoreWarp + 1);
 constexpr int kNB = 48;                          // N of the phase-2 MMA: 32 KV columns + Ks + padding to 16
 constexpr int kD2Cols = kHeadsPerItem * kNB;     // 192 TMEM columns per D2 buffer
 constexpr int kTmemCols = 512;                   // D1 [0,128) + D2[group] [128 + 192 g, +192)
 constexpr int kBmatBytes = kD * kNB * 2;         // one [32 x 48] bf16 B operand
+constexpr int kVecBytes = kTile * 16 * 2;        // [128 tokens x 16] MN-major ones operand: relu(K)^T 1 = Ks on the tensor core
+constexpr uint32_t kColD2 = 128;                 // D2[group] at kColD2 + group * kD2Cols
+constexpr uint32_t kColKs = kColD2;              // phase 1: the Ks accumulator borrows the first 16 columns of D2[0]
 
 struct FwdSmem {
   uint8_t slots[kStages][kSlotBytes];                       // 1024-aligned
   uint8_t bmat[kHeadsPerItem][2][kBmatBytes];               // [head][hi|lo], MN-major no-swizzle
-  float red[kEpiWarps][kHeadsPerItem * kD];
-  uint64_t full[kStages], ready[kStages], empty[kStages], o_ready[kStages];
+  uint8_t ones[kVecBytes];
+  uint64_t full[kStages], ready[kStages], ready_k[kStages], empty[kStages], o_ready[kStages];
   uint64_t d1_full, b_ready, d2_full[kGroups], d2_empty[kGroups];
   uint32_t tmem_base;
 };
@@ -64,6 +68,7 @@ static_assert(kFwdSmemBytes <= 232448, "forward shared memory exceeds the 227 KB
 
 constexpr uint32_t kIdesc1 = make_idesc_bf16(128, 128, 1, 1);  // relu(K)^T V : A, B MN-major
 constexpr uint32_t kIdesc2 = make_idesc_bf16(128, kNB, 0, 1);  // relu(Q) [KV|Ks] : A K-major, B MN-major
+constexpr uint32_t kIdescVec = make_idesc_bf16(128, 16, 1, 1); // relu(K)^T ones over tokens
 
 __device__ __forceinline__ uint4 relu8(uint4 v) {
   const __nv_bfloat162 z = __float2bfloat162_rn(0.f);
@@ -71,10 +76,6 @@ __device__ __forceinline__ uint4 relu8(uint4 v) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) h[i] = __hmax2_nan(h[i], z);
   return v;
-}
-__device__ __forceinline__ void unpack8f(const uint4& v, float f[8]) {
-  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
-  f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
 }
 
 // kState: phase 1 has already been done by the projection kernel (qkv_linattn_sm100.cu): KV_h / Ks_h arrive as fp32
@@ -93,12 +94,13 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
       mbar_init(smem_u32(&S.full[s]), 1);
-      mbar_init(smem_u32(&S.ready[s]), kGroupWarps);
+      mbar_init(smem_u32(&S.ready[s]), kGroupWarps);      // phase 2: the owning group's warps
+      mbar_init(smem_u32(&S.ready_k[s]), kEpiWarps);      // phase 1: every epilogue warp works on every K tile
       mbar_init(smem_u32(&S.empty[s]), 1);
       mbar_init(smem_u32(&S.o_ready[s]), kGroupWarps);
     }
     mbar_init(smem_u32(&S.d1_full), 1);
-    mbar_init(smem_u32(&S.b_ready), kGroupWarps);
+    mbar_init(smem_u32(&S.b_ready), 4);                   // the four warps (one per head) that build the operands
     for (int i = 0; i < kGroups; ++i) {
       mbar_init(smem_u32(&S.d2_full[i]), 1);
       mbar_init(smem_u32(&S.d2_empty[i]), kGroupWarps);
@@ -106,9 +108,12 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
     fence_barrier_init();
     tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v); tma_prefetch_desc(&tm_o);
   }
-  // the padding columns of the B operands stay zero for the whole kernel
-  for (int i = threadIdx.x; i < (int)sizeof(S.bmat) / 16; i += kThreads)
+  // the padding columns of the B operands stay zero for the whole kernel; ones operand: column 0 = 1
+  for (int i = threadIdx.x; i < (int)(sizeof(S.bmat) + sizeof(S.ones)) / 16; i += kThreads)
     reinterpret_cast<uint4*>(&S.bmat[0][0][0])[i] = make_uint4(0, 0, 0, 0);
+  __syncthreads();
+  if (threadIdx.x < kTile)   // element [token][n] at (n/8)*2048 + (token/8)*128 + (token%8)*16 + (n%8)*2
+    *reinterpret_cast<uint32_t*>(&S.ones[(threadIdx.x >> 3) * 128 + (threadIdx.x & 7) * 16]) = 0x00003f80u;   // bf16 1.0
   fence_proxy_async();
   if (warp == 1) {
     tmem_alloc(smem_u32(&S.tmem_base), kTmemCols);
@@ -117,7 +122,9 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem = S.tmem_base;
+  // one CTA per SM allocating all 512 columns: the base is column 0 (immediates in the issuer's MMA loop, see the backward)
+  if (S.tmem_base != 0) __trap();
+  constexpr uint32_t tmem = 0;
 
   if (warp == 0) {
     // ======================= TMA producer =======================
@@ -144,28 +151,34 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
     // ======================= tcgen05 issuer =======================
     if (lane == 0) {
       uint32_t it = 0, item_iter = 0;
-      uint32_t ready_ph = 0;        // per-slot parity of `ready` (only K and Q uses of a slot complete a phase)
+      uint32_t ready_ph = 0, ready_k_ph = 0;   // per-slot parities of `ready` (Q uses) / `ready_k` (K uses)
       uint32_t d2_use[kGroups] = {0, 0};
+      const uint64_t ones0 = make_smem_desc(smem_u32(&S.ones[0]), 128, 2048, kLayoutNone);
+      const uint64_t bmat0 = make_smem_desc(smem_u32(&S.bmat[0][0][0]), 128, 512, kLayoutNone);
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++item_iter) {
         // ---- phase 1: D1 += relu(K)^T V over all token tiles
         for (int t = 0; t < (kState ? 0 : n_tiles); ++t, it += 2) {
           const uint32_t sk = it % kStages;
           const uint32_t sv = (it + 1) % kStages, pv = ((it + 1) / kStages) & 1;
           TRACE(1, 50);
-          mbar_wait(smem_u32(&S.ready[sk]), (ready_ph >> sk) & 1);
-          ready_ph ^= 1u << sk;
+          mbar_wait(smem_u32(&S.ready_k[sk]), (ready_k_ph >> sk) & 1);
+          ready_k_ph ^= 1u << sk;
           TRACE(1, 51);
           mbar_wait(smem_u32(&S.full[sv]), pv);  // V is consumed as loaded
+          // the Ks accumulator borrows the first columns of D2[0]: the previous item's last group-0 tile must be drained
+          if (t == 0) mbar_wait(smem_u32(&S.d2_empty[0]), (d2_use[0] & 1) ^ 1);
           tc_fence_after();
           TRACE(1, 52);
-          const uint32_t ka = smem_u32(&S.slots[sk][0]), va = smem_u32(&S.slots[sv][0]);
+          // MN-major SW128: LBO = stride between the two 64-column halves, SBO = 8-token group (1 KB); a descriptor is
+          // its base + (byte offset >> 4)
+          const uint64_t ka0 = make_smem_desc(smem_u32(&S.slots[sk][0]), kHalfBytes, 1024, kLayoutSw128);
+          const uint64_t va0 = make_smem_desc(smem_u32(&S.slots[sv][0]), kHalfBytes, 1024, kLayoutSw128);
 #pragma unroll
-          for (int ks = 0; ks < kTile / 16; ++ks) {
-            // MN-major SW128: LBO = stride between the two 64-column halves, SBO = 8-token group (1 KB)
-            const uint64_t da = make_smem_desc(ka + ks * 2048, kHalfBytes, 1024, kLayoutSw128);
-            const uint64_t db = make_smem_desc(va + ks * 2048, kHalfBytes, 1024, kLayoutSw128);
-            umma_bf16(tmem, da, db, kIdesc1, (t | ks) != 0);
-          }
+          for (int ks = 0; ks < kTile / 16; ++ks)
+            umma_bf16(tmem, ka0 + ((ks * 2048) >> 4), va0 + ((ks * 2048) >> 4), kIdesc1, (t | ks) != 0);
+#pragma unroll
+          for (int ks = 0; ks < kTile / 16; ++ks)    // Ks = relu(K)^T 1 (column 0 of a 16-column accumulator)
+            umma_bf16(tmem + kColKs, ka0 + ((ks * 2048) >> 4), ones0 + ((ks * 256) >> 4), kIdescVec, (t | ks) != 0);
           tc_commit(smem_u32(&S.empty[sk]));
           tc_commit(smem_u32(&S.empty[sv]));
           TRACE(1, 53);
@@ -185,23 +198,20 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
           mbar_wait(smem_u32(&S.d2_empty[g]), pb ^ 1);
           tc_fence_after();
           TRACE(1, 32);
-          const uint32_t qa = smem_u32(&S.slots[sq][0]);
+          // A: K-major SW128, 8-row groups 1 KB apart; head h = 64 B inside the 128 B row of half h >> 1; K step = 32 B
+          const uint64_t qa0 = make_smem_desc(smem_u32(&S.slots[sq][0]), 16, 1024, kLayoutSw128);
 #pragma unroll
           for (int h = 0; h < kHeadsPerItem; ++h) {
-            const uint32_t d2 = tmem + 128 + g * kD2Cols + h * kNB;
-            const uint32_t qh = qa + (h >> 1) * kHalfBytes + (h & 1) * 64;  // 32 columns = 64 B inside the 128 B row
+            const uint32_t d2 = tmem + kColD2 + g * kD2Cols + h * kNB;
+            const uint32_t aoff = (h >> 1) * kHalfBytes + (h & 1) * 64;
 #pragma unroll
             for (int hl = 0; hl < 2; ++hl) {
-              const uint32_t ba = smem_u32(&S.bmat[h][hl][0]);
+              const uint32_t boff = (h * 2 + hl) * kBmatBytes;
 #pragma unroll
-              for (int ks = 0; ks < 2; ++ks) {
-                // A: K-major SW128, 8-row groups 1 KB apart; K step of 16 columns = 32 B
-                const uint64_t da = make_smem_desc(qh + ks * 32, 16, 1024, kLayoutSw128);
+              for (int ks = 0; ks < 2; ++ks)
                 // B: MN-major no-swizzle, core matrix = 8 k-rows x 16 B; k-group stride (LBO) 128 B,
                 //    mn-group stride (SBO) 512 B; K step of 16 = 2 k-groups = 256 B
-                const uint64_t db = make_smem_desc(ba + ks * 256, 128, 512, kLayoutNone);
-                umma_bf16(d2, da, db, kIdesc2, (hl | ks) != 0);
-              }
+                umma_bf16(d2, qa0 + ((aoff + ks * 32) >> 4), bmat0 + ((boff + ks * 256) >> 4), kIdesc2, (hl | ks) != 0);
             }
           }
           tc_commit(smem_u32(&S.d2_full[g]));
@@ -236,62 +246,48 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
     }
   } else {
     // ======================= transform + epilogue groups =======================
-    const int we = warp - 2;                  // 0..7
-    const int grp = we >> 2;                  // tiles with (t & 1) == grp belong to this group
-    const int tg = threadIdx.x - 64 - grp * 128;   // 0..127 inside the group
-    const int cc = tg & 15;                   // logical 16-byte chunk column of the 256-byte item row
-    const int rbase = tg >> 4;                // 0..7; rows rbase + 8 i
+    const int te = threadIdx.x - 64;          // 0..511
+    const int we = warp - 2;                  // 0..15
+    const int grp = we >> 3;                  // phase 2: tiles with (t & 1) == grp belong to this group
+    const int tg = te - grp * (kGroupWarps * 32);  // 0..255 inside the group
+    const int cc = te & 15;                   // logical 16-byte chunk column of the 256-byte item row (te and tg agree mod 16)
     const int half = cc >> 3, chunk = cc & 7;
     const int quad = warp & 3;                // TMEM lane quadrant this warp may access
+    const int hp = (we >> 2) & 1;             // phase-2 epilogue: heads 2 hp, 2 hp + 1 of this thread's row
     const int row = quad * 32 + lane;         // token row in the tile (TMEM lane)
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
     uint32_t it = 0, item_iter = 0, d2_use = 0;
 
-    // relu in place over this group's share of a [2][128][64] tile; returns nothing, adds column sums
-    auto relu_tile = [&](uint32_t slot, float* csum) {
+    // relu in place: rows r0, r0 + step, ... (n rows per thread) of a [2][128][64] tile, then one arrival per warp
+    auto relu_rows = [&](uint32_t slot, int r0, int step, int n, uint64_t* bar) {
       uint8_t* base = &S.slots[slot][half * kHalfBytes];
-#pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int r = rbase + 8 * i;
+#pragma unroll 8
+      for (int i = 0; i < n; ++i) {
+        const int r = r0 + step * i;
         uint4* p = reinterpret_cast<uint4*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
-        const uint4 v = relu8(*p);
-        *p = v;
-        if (csum) {
-          float f[8];
-          unpack8f(v, f);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) csum[j] += f[j];
-        }
+        *p = relu8(*p);
       }
       fence_proxy_async();
       __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&S.ready[slot]));
+      if (lane == 0) mbar_arrive(smem_u32(bar));
     };
 
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++item_iter) {
-      // ---- phase 1: relu(K) in place, column sums.  Every `full` phase is observed in order by both
-      // groups (a parity wait is only sound if the waiter sees every phase of the barrier); only the
-      // owner touches the tile.  V needs no transform: the issuer waits on its `full`.
-      float csum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      // ---- phase 1: relu(K) in place by ALL sixteen warps (4 rows per thread); the column sums Ks come off the tensor
+      // core (relu(K)^T ones), so there is no CUDA-core reduction and no CTA-wide barrier here.  Every `full` phase is
+      // observed in order (a parity wait is only sound if the waiter sees every phase of the barrier).  V needs no
+      // transform: the issuer waits on its `full`.
       for (int t = 0; t < (kState ? 0 : n_tiles); ++t, it += 2) {
         const uint32_t sk = it % kStages, pk = (it / kStages) & 1;
         if (tg == 0) TRACE(grp ? 3 : 0, 20);
         mbar_wait(smem_u32(&S.full[sk]), pk);
         if (tg == 0) TRACE(grp ? 3 : 0, 21);
-        if ((t & 1) == grp) relu_tile(sk, csum);
+        relu_rows(sk, te >> 4, 32, 4, &S.ready_k[sk]);
         if (tg == 0) TRACE(grp ? 3 : 0, 22);
         mbar_wait(smem_u32(&S.full[(it + 1) % kStages]), ((it + 1) / kStages) & 1);
         if (tg == 0) TRACE(grp ? 3 : 0, 23);
       }
-      // Ks partials: lanes l and l^16 share the chunk column
-#pragma unroll
-      for (int j = 0; j < 8; ++j) csum[j] += __shfl_xor_sync(0xffffffffu, csum[j], 16);
-      if (lane < 16) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) S.red[we][cc * 8 + j] = csum[j];
-      }
-      named_bar_sync(1, kEpiThreads);
-      if (grp == 0) {
+      if (we < 4) {
         // ---- build the B operands of phase 2: head `quad`, k row `lane`
         float ksum = 0.f;
         uint32_t r[32];
@@ -317,12 +313,13 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
 #pragma unroll
           for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(accv[j]);
         } else {
-#pragma unroll
-          for (int w = 0; w < kEpiWarps; ++w) ksum += S.red[w][quad * kD + lane];
           mbar_wait(smem_u32(&S.d1_full), item_iter & 1);
           tc_fence_after();
+          uint32_t k1;
           tmem_ld32(tmem + lane_base + quad * kD, r);  // KV_head[dk = lane][dv = 0..31]
+          tmem_ld1(tmem + lane_base + kColKs, k1);     // Ks[column quad * 32 + lane]
           tmem_ld_wait();
+          ksum = __uint_as_float(k1);
         }
         uint8_t* bh = &S.bmat[quad][0][0];
         uint8_t* bl = &S.bmat[quad][1][0];
@@ -358,16 +355,16 @@ linattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
         mbar_wait(smem_u32(&S.full[sq]), pq);
         if ((t & 1) != grp) continue;
         if (tg == 0) TRACE(grp ? 3 : 0, 10);
-        relu_tile(sq, nullptr);
+        relu_rows(sq, tg >> 4, 16, 8, &S.ready[sq]);
         if (tg == 0) TRACE(grp ? 3 : 0, 11);
 
         mbar_wait(smem_u32(&S.d2_full[grp]), d2_use & 1);
         ++d2_use;
         tc_fence_after();
         if (tg == 0) TRACE(grp ? 3 : 0, 12);
-        const uint32_t d2 = tmem + lane_base + 128 + grp * kD2Cols;
+        const uint32_t d2 = tmem + lane_base + kColD2 + grp * kD2Cols;
 #pragma unroll
-        for (int h = 0; h < kHeadsPerItem; ++h) {
+        for (int h = 2 * hp; h < 2 * hp + 2; ++h) {
           uint32_t acc[32], dn;
           tmem_ld32(d2 + h * kNB, acc);
           tmem_ld1(d2 + h * kNB + kD, dn);
