@@ -13,5 +13,5 @@ timeout 600 python bench.py --kernels-only > gpurun_out/kernels_only.log 2>&1; e
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file gpurun_out/launches.csv python bench.py --steps 1 --warmup 1 --no-other-workloads --no-account --no-cpu-baseline > gpurun_out/ncu.log 2>&1; echo "launch list rc=$?"
 timeout 300 python scripts/prof_kernels.py 1 > gpurun_out/plain_prof.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:"linattn_.*sm100|qkv_linattn|gemm_bf16|noise_bf16|loss_fused|repa_|glumb_fwd|glumb_bwd|adamw|grad_sumsq|ln_modulate|gate_residual|column_pass|colsum_kernel|head_pad|head_unpad" -c 24 \
-    -o gpurun_out/prof_r02c -f python scripts/prof_kernels.py 1 > gpurun_out/ncu_prof.log 2>&1
+    -o gpurun_out/prof_r02d -f python scripts/prof_kernels.py 1 > gpurun_out/ncu_prof.log 2>&1
 echo "full capture rc=$?"; ls -la gpurun_out/*.ncu-rep | tail -2
