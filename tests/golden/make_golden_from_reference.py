@@ -1,0 +1,305 @@
+"""Golden vectors produced by EXECUTING THE REFERENCE'S OWN SOURCE (run in the build container, where /root/reference exists).
+
+The reference cannot be imported as a package (diffusers / accelerate / peft / webdataset are not installed, SURVEY.md
+F4), but its hot-path functions are plain Python + torch.  This script pulls them out of the reference files with `ast`
+(function objects compiled from the reference's own text - nothing is copied into this repository) and runs them with
+the two diffusers helpers they call replaced by the restatements SURVEY.md §8(c)(i)-(iii) records:
+
+  train_sana.py        SanaModel.optimize            pad / mask loop, draw order (noise then u), index -> timestep,
+                                                     get_sigmas float-equality lookup, x_t with its bf16 rounding chain,
+                                                     velocity target, fp32 MSE                          (rows A1-A6, A12)
+  train_sd35.py        SD35Trainer.optimize          global-RNG draw order, velocity target, bf16 MSE   (rows A1, A2, A5, A6)
+  train_pixart_sigma.py PixartSigmaTrainer.optimize  pad to 300, eps target cropped to pred[:, :C], bf16 MSE (A5, A6, A12)
+  common/trainer.py    Model.find_closest_ratio      first-minimum bucket rule                          (row A9)
+  common/bucket_sampler.py  find_closest_key, BucketSamplerExtractFeatures.find_closest_ratio            (row A9)
+  common/repa.py       RepaMLP                       projector Linear-ReLU-Linear                       (row A8, projector)
+  common/training_parameters_reader.py  TrainingParameters.read_yaml  (imported as is: it only needs yaml)   (boundary)
+
+What stays restated (not reference-owned): diffusers' `randn_tensor`, `compute_density_for_timestep_sampling` and the
+FlowMatchEuler tables (oracle/schedule.py), `scheduler.scale_noise` / `DDPMScheduler.add_noise` (restated in this file
+from SURVEY.md §8(c)(iii)-(iv)), and the transformer behind `self.model` (a recorded stub here).
+
+    python tests/golden/make_golden_from_reference.py      ->  tests/golden/reference_*.{json,pt}
+"""
+import ast
+import hashlib
+import importlib.util
+import json
+import os
+import sys
+import types
+
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+REF = "/root/reference"
+
+from oracle import schedule  # noqa: E402  (restated scheduler tables: the only non-reference numerics below)
+from yat_b200.aspect_ratios import ASPECT_RATIO_1024_BIN  # noqa: E402  (the table is data passed in by the hook)
+
+
+def extract(path, func, cls=None):
+    """The function object `func` (of class `cls`) compiled from the reference file's own source text."""
+    full = os.path.join(REF, path)
+    tree = ast.parse(open(full).read())
+    body = tree.body
+    if cls is not None:
+        body = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == cls).body
+    node = next(n for n in body if isinstance(n, ast.FunctionDef) and n.name == func)
+    node.decorator_list = []
+    code = compile(ast.fix_missing_locations(ast.Module(body=[node], type_ignores=[])), full, "exec")
+    return code, node.lineno
+
+
+def extract_class(path, cls, glb):
+    full = os.path.join(REF, path)
+    tree = ast.parse(open(full).read())
+    node = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == cls)
+    exec(compile(ast.fix_missing_locations(ast.Module(body=[node], type_ignores=[])), full, "exec"), glb)
+    return glb[cls], node.lineno
+
+
+# ---- diffusers helpers, restated -------------------------------------------------------
+def randn_tensor(shape, generator=None, device=None, dtype=None, layout=None):
+    """CPU generator + any target device: draw on the CPU in `dtype`, then move."""
+    return torch.randn(shape, generator=generator, device="cpu", dtype=dtype).to(device)
+
+
+def compute_density_for_timestep_sampling(weighting_scheme, batch_size, logit_mean=None, logit_std=None,
+                                          mode_scale=None, device="cpu", generator=None):
+    assert weighting_scheme == "logit_normal"
+    u = torch.normal(mean=logit_mean, std=logit_std, size=(batch_size,), device=device, generator=generator)
+    return torch.nn.functional.sigmoid(u)
+
+
+def sha(t):
+    return hashlib.sha256(t.contiguous().view(torch.uint8).numpy().tobytes()).hexdigest()
+
+
+class RecordingModel:
+    """Stands in for the transformer: records what the reference's optimize() feeds it, returns a fixed prediction."""
+
+    def __init__(self, pred):
+        self.pred, self.seen = pred, None
+
+    def __call__(self, x, **kw):
+        self.seen = dict(kw, x=x)
+        return types.SimpleNamespace(sample=self.pred)
+
+
+def run_sana_optimize(shape, emb_lens, emb_dim, shift, seed):
+    code, line = extract("train_sana.py", "optimize", cls="SanaModel")
+    glb = {"torch": torch, "randn_tensor": randn_tensor,
+           "compute_density_for_timestep_sampling": compute_density_for_timestep_sampling}
+    exec(code, glb)
+    optimize = glb["optimize"]
+    tt, ss = schedule.flow_match_tables(1000, shift)
+    g = torch.Generator().manual_seed(seed)
+    latents = torch.randn(shape, generator=g).to(torch.bfloat16)
+    pred = torch.randn(shape, generator=g).to(torch.bfloat16)
+    embeddings = [(0.5 * torch.randn((L, emb_dim), generator=g)).to(torch.bfloat16) for L in emb_lens]
+    model = RecordingModel(pred)
+    self = types.SimpleNamespace(
+        params=types.SimpleNamespace(batch_size=shape[0]),
+        accelerator=types.SimpleNamespace(device=torch.device("cpu")),
+        scheduler=types.SimpleNamespace(config=types.SimpleNamespace(num_train_timesteps=1000), timesteps=tt, sigmas=ss),
+        model=model)
+    # the reference creates a fresh, unseeded torch.Generator() every step (common/trainer.py:325)
+    loss = optimize(self, "1.0", latents, embeddings, None, torch.Generator())
+    seen = model.seen
+    return {"line": line, "latents": latents, "pred": pred, "embeddings": embeddings, "x_t": seen["x"],
+            "timesteps": seen["timestep"], "padded": seen["encoder_hidden_states"],
+            "mask": seen["encoder_attention_mask"], "loss": loss}
+
+
+# ---- diffusers scheduler methods the SD3.5 / PixArt hooks call, restated ---------------
+class FlowScheduler:
+    def __init__(self, shift):
+        self.timesteps, self.sigmas = schedule.flow_match_tables(1000, shift)
+        self.config = types.SimpleNamespace(num_train_timesteps=1000)
+
+    def scale_noise(self, sample, timestep, noise):
+        sigmas = self.sigmas.to(device=sample.device, dtype=sample.dtype)
+        idx = []
+        for t in timestep:
+            hits = (self.timesteps == t).nonzero()
+            idx.append(hits[1 if len(hits) > 1 else 0].item())
+        sigma = sigmas[idx].flatten()
+        while len(sigma.shape) < len(sample.shape):
+            sigma = sigma.unsqueeze(-1)
+        return sigma * noise + (1.0 - sigma) * sample
+
+
+class DdpmScheduler:
+    def __init__(self):
+        betas = torch.linspace(1e-4, 0.02, 1000, dtype=torch.float32)
+        self.alphas_cumprod = torch.cumprod(1.0 - betas, dim=0)
+        self.timesteps = torch.arange(0, 1000).flip(0)
+        self.config = types.SimpleNamespace(num_train_timesteps=1000)
+
+    def add_noise(self, original_samples, noise, timesteps):
+        ac = self.alphas_cumprod.to(dtype=original_samples.dtype)
+        a = ac[timesteps] ** 0.5
+        a = a.flatten()
+        while len(a.shape) < len(original_samples.shape):
+            a = a.unsqueeze(-1)
+        b = (1 - ac[timesteps]) ** 0.5
+        b = b.flatten()
+        while len(b.shape) < len(original_samples.shape):
+            b = b.unsqueeze(-1)
+        return a * original_samples + b * noise
+
+
+class Movable:
+    """pipe.vae / text encoders / transformer handles: .cpu() and .to() return self."""
+    dtype = torch.bfloat16
+
+    def cpu(self):
+        return self
+
+    def to(self, *a, **k):
+        return self
+
+
+class RecordingTransformer(Movable):
+    def __init__(self, pred):
+        self.pred, self.seen = pred, None
+
+    def __call__(self, x, **kw):
+        self.seen = dict(kw, x=x)
+        return types.SimpleNamespace(sample=self.pred)
+
+
+def run_sd35_optimize(shape, seed):
+    """train_sd35.py SD35Trainer.optimize(model, batch): global-RNG draws, scale_noise, velocity target, bf16 MSE."""
+    code, line = extract("train_sd35.py", "optimize", cls="SD35Trainer")
+    glb = {"torch": torch, "randn_tensor": randn_tensor,
+           "compute_density_for_timestep_sampling": compute_density_for_timestep_sampling}
+    exec(code, glb)
+    g = torch.Generator().manual_seed(seed)
+    latents = torch.randn(shape, generator=g).to(torch.bfloat16)
+    pred = torch.randn(shape, generator=g).to(torch.bfloat16)
+    emb = torch.randn((shape[0], 12, 32), generator=g).to(torch.bfloat16)
+    pooled = torch.randn((shape[0], 16), generator=g).to(torch.bfloat16)
+    model = RecordingTransformer(pred)
+    self = types.SimpleNamespace(
+        params=types.SimpleNamespace(batch_size=shape[0]), accelerator=types.SimpleNamespace(device=torch.device("cpu")),
+        scheduler=FlowScheduler(3.0),
+        pipe=types.SimpleNamespace(text_encoder=Movable(), text_encoder_2=Movable(), text_encoder_3=Movable(), vae=Movable(),
+                                   transformer=Movable()))
+    torch.manual_seed(seed + 100)              # the hook draws from the global generator
+    loss = glb["optimize"](self, model, (latents, emb, pooled))
+    return {"line": line, "latents": latents, "pred": pred, "x_t": model.seen["x"], "timesteps": model.seen["timestep"],
+            "loss": loss, "global_seed": seed + 100}
+
+
+def run_pixart_optimize(shape, emb_lens, seed):
+    """train_pixart_sigma.py PixartSigmaTrainer.optimize(latents, embeddings): pad to 300, DDPM add_noise, eps target cropped
+    to the first half of the 2C-channel prediction, bf16 MSE."""
+    code, line = extract("train_pixart_sigma.py", "optimize", cls="PixartSigmaTrainer")
+    glb = {"torch": torch, "randn_tensor": randn_tensor,
+           "compute_density_for_timestep_sampling": compute_density_for_timestep_sampling}
+    exec(code, glb)
+    g = torch.Generator().manual_seed(seed)
+    latents = torch.randn(shape, generator=g).to(torch.bfloat16)
+    pred = torch.randn((shape[0], 2 * shape[1], shape[2], shape[3]), generator=g).to(torch.bfloat16)
+    embeddings = [(0.5 * torch.randn((L, 48), generator=g)).to(torch.bfloat16) for L in emb_lens]
+    model = RecordingTransformer(pred)
+    self = types.SimpleNamespace(
+        params=types.SimpleNamespace(batch_size=shape[0]), accelerator=types.SimpleNamespace(device=torch.device("cpu")),
+        scheduler=DdpmScheduler(), model=model,
+        pipe=types.SimpleNamespace(vae=Movable(), text_encoder=Movable(), dtype=torch.bfloat16))
+    torch.manual_seed(seed + 100)
+    loss = glb["optimize"](self, latents, embeddings)
+    seen = model.seen
+    return {"line": line, "latents": latents, "pred": pred, "embeddings": embeddings, "x_t": seen["x"],
+            "timesteps": seen["timestep"], "padded": seen["encoder_hidden_states"], "mask": seen["encoder_attention_mask"],
+            "loss": loss, "global_seed": seed + 100}
+
+
+def main():
+    meta = {"generated_by": "tests/golden/make_golden_from_reference.py", "torch": torch.__version__,
+            "reference_functions": {}}
+
+    # ---- SD35Trainer.optimize / PixartSigmaTrainer.optimize on small shapes (tensors kept)
+    sd = run_sd35_optimize((2, 16, 16, 16), seed=31)
+    meta["reference_functions"]["train_sd35.py::SD35Trainer.optimize"] = sd.pop("line")
+    px = run_pixart_optimize((3, 4, 16, 16), [5, 300, 120], seed=32)
+    meta["reference_functions"]["train_pixart_sigma.py::PixartSigmaTrainer.optimize"] = px.pop("line")
+    torch.save({"sd35": sd, "pixart": px}, os.path.join(HERE, "reference_sd35_pixart_optimize.pt"))
+
+    # ---- SanaModel.optimize, K1 shape (tensors kept) and K2 shape (hashes kept)
+    k1 = run_sana_optimize((2, 32, 16, 16), [7, 300], 64, 1.0, seed=11)
+    meta["reference_functions"]["train_sana.py::SanaModel.optimize"] = k1.pop("line")
+    k1s3 = run_sana_optimize((2, 32, 16, 16), [512, 1], 64, 3.0, seed=12)
+    k1s3.pop("line")
+    torch.save({"shift1": k1, "shift3": k1s3}, os.path.join(HERE, "reference_sana_optimize_k1.pt"))
+    lens = [int(x) for x in torch.randint(20, 301, (16,), generator=torch.Generator().manual_seed(5))]
+    k2 = run_sana_optimize((16, 32, 32, 32), lens, 2304, 1.0, seed=13)
+    meta["sana_optimize_k2"] = {
+        "shape": [16, 32, 32, 32], "emb_lens": lens, "emb_dim": 2304, "shift": 1.0, "seed": 13,
+        "timesteps": [float(t) for t in k2["timesteps"]],
+        "x_t_sha256": sha(k2["x_t"]), "padded_sha256": sha(k2["padded"]), "mask_sha256": sha(k2["mask"]),
+        "mask_row_sums": [int(s) for s in k2["mask"].sum(1)], "loss": float(k2["loss"]),
+        "loss_bits": int(k2["loss"].detach().view(torch.int32)), "x_t_first": [float(v) for v in k2["x_t"].flatten()[:8].float()]}
+
+    # ---- bucket assignment: three reference functions on one set of ratios
+    ratios = sorted({h / w for h in range(256, 2049, 64) for w in range(256, 2049, 64)})
+    ratios += [0.25, 4.0, 0.1, 9.0, 0.265, 0.485, 0.985, 1.035, 1.0, 0.6, 3.75, (0.94 + 1.0) / 2, (0.5 + 0.52) / 2, (1.0 + 1.07) / 2]
+    code, line = extract("common/trainer.py", "find_closest_ratio", cls="Model")
+    glb = {}
+    exec(code, glb)
+    meta["reference_functions"]["common/trainer.py::Model.find_closest_ratio"] = line
+    trainer_self = types.SimpleNamespace(aspect_ratios=ASPECT_RATIO_1024_BIN)
+    keys_trainer = [glb["find_closest_ratio"](trainer_self, r) for r in ratios]
+    code, line = extract("common/bucket_sampler.py", "find_closest_ratio", cls="BucketSamplerExtractFeatures")
+    glb = {}
+    exec(code, glb)
+    meta["reference_functions"]["common/bucket_sampler.py::BucketSamplerExtractFeatures.find_closest_ratio"] = line
+    sampler_self = types.SimpleNamespace(model=trainer_self)
+    keys_sampler = [glb["find_closest_ratio"](sampler_self, r) for r in ratios]
+    code, line = extract("common/bucket_sampler.py", "find_closest_key", cls="BucketSampler")
+    glb = {}
+    exec(code, glb)
+    meta["reference_functions"]["common/bucket_sampler.py::BucketSampler.find_closest_key"] = line
+    bucket_self = types.SimpleNamespace(buckets={float(k): [] for k in ASPECT_RATIO_1024_BIN})
+    keys_bucket = [glb["find_closest_key"](bucket_self, r) for r in ratios + [-1.0]]
+    meta["buckets"] = {"table": "ASPECT_RATIO_1024_BIN", "ratios": ratios, "trainer_keys": keys_trainer,
+                       "sampler_keys": keys_sampler, "bucket_keys": keys_bucket}
+
+    # ---- REPA projector (common/repa.py RepaMLP): class body executed from the reference source
+    RepaMLP, line = extract_class("common/repa.py", "RepaMLP", {"torch": torch, "nn": torch.nn})
+    meta["reference_functions"]["common/repa.py::RepaMLP"] = line
+    torch.manual_seed(21)
+    mlp = RepaMLP(96, 64, 48) if RepaMLP.__init__.__code__.co_argcount == 4 else None
+    if mlp is None:
+        raise SystemExit("RepaMLP signature changed: inspect common/repa.py:43-57")
+    x = torch.randn((3, 10, 96))
+    torch.save({"state_dict": mlp.state_dict(), "x": x, "y": mlp(x).detach(), "ctor": [96, 64, 48]},
+               os.path.join(HERE, "reference_repa_mlp.pt"))
+
+    # ---- config reader: the reference module itself (it only imports json / yaml / huggingface_hub)
+    spec = importlib.util.spec_from_file_location("ref_tpr", os.path.join(REF, "common/training_parameters_reader.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    yaml_text = ("urls: [shard-000.tar]\nbatch_size: 16\nlearning_rate: 1e-5\nsteps: 1000\nnum_steps_per_validation: 100\n"
+                 "validation_prompts: [a cat, a dog]\nbfloat16:\nuse_repa:\nrepa_lambda: 0.1\nexploration_steps: 2\n"
+                 "gradient_accumulation_steps: 4\ntrain_unconditional_prob: 0.1\nwarmup_steps: 5\ntimesteps: [1, 2]\n"
+                 "lora_rank: 16\nlora_alpha: 8\nlora_algo: lokr\nlora_target_modules: [to_q, to_k, to_v, to_out.0]\nuse_ema:\n"
+                 "weight_decay: 0.01\n")
+    path = os.path.join(HERE, "reference_config.yaml")
+    open(path, "w").write(yaml_text)
+    p = mod.TrainingParameters()
+    p.read_yaml(path)
+    attrs = {k: v for k, v in vars(p).items() if isinstance(v, (int, float, str, bool, list, type(None)))}
+    meta["config"] = {"yaml": "reference_config.yaml", "attributes": attrs,
+                      "defaults": {k: v for k, v in vars(mod.TrainingParameters()).items()
+                                   if isinstance(v, (int, float, str, bool, list, type(None)))}}
+    json.dump(meta, open(os.path.join(HERE, "reference_golden.json"), "w"), indent=1, sort_keys=True)
+    print("wrote reference_golden.json, reference_sana_optimize_k1.pt, reference_repa_mlp.pt, reference_config.yaml")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,151 @@
+"""Parity against golden vectors produced by EXECUTING THE REFERENCE'S OWN SOURCE (tests/golden/make_golden_from_reference.py:
+`SanaModel.optimize` of train_sana.py:163-219, the three bucket functions, `RepaMLP`, the YAML reader - compiled from the
+reference files with `ast` / imported, with only diffusers' `randn_tensor`, `compute_density_for_timestep_sampling` and the
+scheduler tables restated).  These pin, for rows A1-A6, A9, A12 and the projector / config surface, what the oracle and the
+product must reproduce: bit-exact timestep values, masks, padded embeddings and x_t; fp32 loss <= 1e-5 relative (north star)."""
+import hashlib
+import json
+import os
+
+import pytest
+import torch
+
+from oracle import buckets as obuckets
+from oracle import losses, noising, sampling, schedule
+from oracle.train_step import pad_embeddings_reference
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+META = json.load(open(os.path.join(GOLD, "reference_golden.json")))
+
+
+def _sha(t):
+    return hashlib.sha256(t.contiguous().view(torch.uint8).numpy().tobytes()).hexdigest()
+
+
+def _k2_inputs():
+    """Same seeded inputs as make_golden_from_reference.run_sana_optimize((16,32,32,32), lens, 2304, 1.0, seed=13)."""
+    m = META["sana_optimize_k2"]
+    g = torch.Generator().manual_seed(m["seed"])
+    shape = tuple(m["shape"])
+    latents = torch.randn(shape, generator=g).to(torch.bfloat16)
+    pred = torch.randn(shape, generator=g).to(torch.bfloat16)
+    embeddings = [(0.5 * torch.randn((L, m["emb_dim"]), generator=g)).to(torch.bfloat16) for L in m["emb_lens"]]
+    return m, latents, pred, embeddings
+
+
+# ------------------------------------------------------------------------------------------- CPU: oracle + host logic
+@pytest.mark.parametrize("case,shift", [("shift1", 1.0), ("shift3", 3.0)])
+def test_oracle_reproduces_reference_optimize_k1(case, shift):
+    ref = torch.load(os.path.join(GOLD, "reference_sana_optimize_k1.pt"))[case]
+    lat, pred = ref["latents"], ref["pred"]
+    noise, u, idx = sampling.sana_step_draws(tuple(lat.shape), lat.shape[0], torch.bfloat16, torch.Generator())
+    tt, ss = schedule.flow_match_tables(1000, shift)
+    x_t, target, t, _ = noising.flow_noise_sana(lat, noise, idx, tt, ss)
+    assert torch.equal(t, ref["timesteps"])
+    assert torch.equal(x_t, ref["x_t"])                                   # bit-exact incl. the bf16 rounding chain
+    padded, mask = pad_embeddings_reference(ref["embeddings"], 512)
+    assert torch.equal(mask, ref["mask"]) and torch.equal(padded.to(torch.bfloat16), ref["padded"])
+    loss = losses.mse_fp32(pred, target)
+    assert abs(loss.item() - ref["loss"].item()) <= 1e-6 * abs(ref["loss"].item())
+
+
+def test_oracle_reproduces_reference_optimize_k2():
+    m, lat, pred, embeddings = _k2_inputs()
+    noise, u, idx = sampling.sana_step_draws(tuple(lat.shape), lat.shape[0], torch.bfloat16, torch.Generator())
+    tt, ss = schedule.flow_match_tables(1000, m["shift"])
+    x_t, target, t, _ = noising.flow_noise_sana(lat, noise, idx, tt, ss)
+    assert [float(v) for v in t] == m["timesteps"]
+    assert _sha(x_t) == m["x_t_sha256"]
+    padded, mask = pad_embeddings_reference(embeddings, 512)
+    assert _sha(mask) == m["mask_sha256"] and _sha(padded.to(torch.bfloat16)) == m["padded_sha256"]
+    assert abs(losses.mse_fp32(pred, target).item() - m["loss"]) <= 1e-6 * abs(m["loss"])
+
+
+def test_bucket_functions_match_the_reference_source():
+    from yat_b200.aspect_ratios import ASPECT_RATIO_1024_BIN
+    from yat_b200.bucket_sampler import find_closest_ratio
+    b = META["buckets"]
+    for r, k_tr, k_sa in zip(b["ratios"], b["trainer_keys"], b["sampler_keys"]):
+        assert obuckets.find_closest_ratio_trainer(ASPECT_RATIO_1024_BIN, r) == k_tr
+        assert obuckets.find_closest_ratio_sampler(ASPECT_RATIO_1024_BIN, r) == k_sa
+        assert find_closest_ratio(ASPECT_RATIO_1024_BIN, r) == k_tr       # product: yat_bucket_assign (host C function)
+    keys = [float(k) for k in ASPECT_RATIO_1024_BIN]
+    for r, k in zip(b["ratios"] + [-1.0], b["bucket_keys"]):
+        assert obuckets.find_closest_key(keys, r) == k
+
+
+def test_repa_projector_matches_the_reference_class():
+    from oracle import repa as orepa
+    from yat_b200.repa import RepaMLP
+    ref = torch.load(os.path.join(GOLD, "reference_repa_mlp.pt"))
+    mlp = RepaMLP(*ref["ctor"])
+    mlp.load_state_dict(ref["state_dict"])                                # same parameter names as common/repa.py:43-57
+    assert torch.allclose(mlp(ref["x"]), ref["y"], rtol=1e-6, atol=1e-6)
+    sd = ref["state_dict"]
+    y = orepa.repa_mlp(ref["x"], sd["fc1.weight"], sd["fc1.bias"], sd["fc2.weight"], sd["fc2.bias"])
+    assert torch.allclose(y, ref["y"], rtol=1e-6, atol=1e-6)
+
+
+def test_config_reader_matches_the_reference_reader():
+    """Every attribute the reference's reader sets from the YAML that this build's reader also defines has the same
+    value (the reference keeps `gradient_accumulation_steps` as the YAML string; the product casts it to int)."""
+    from yat_b200.training_parameters_reader import TrainingParameters
+    p = TrainingParameters()
+    p.read_yaml(os.path.join(GOLD, META["config"]["yaml"]))
+    ref = META["config"]["attributes"]
+    checked = 0
+    for name in ("batch_size", "learning_rate", "steps", "num_steps_per_validation", "validation_prompts", "bfloat16",
+                 "use_repa", "repa_lambda", "exploration_steps", "train_unconditional_prob", "warmup_steps", "timesteps",
+                 "lora_rank", "lora_alpha", "lora_algo", "lora_target_modules", "lora_dropout", "lora_use_dora", "use_ema",
+                 "weight_decay", "use_adamw_8bit", "cache_size", "dual_gpu", "low_vram"):
+        if name in ref and hasattr(p, name):
+            assert getattr(p, name) == ref[name], (name, getattr(p, name), ref[name])
+            checked += 1
+    assert int(p.gradient_accumulation_steps) == int(ref["gradient_accumulation_steps"])
+    assert checked >= 18
+    d = META["config"]["defaults"]
+    q = TrainingParameters()
+    for name in ("repa_lambda", "use_preservation", "preservation_ratio"):
+        if name in d:
+            assert getattr(q, name) == d[name], name
+
+
+# ------------------------------------------------------------------------------------------- GPU: the product path
+@pytest.mark.gpu
+@pytest.mark.parametrize("case,shift", [("shift1", 1.0), ("shift3", 3.0)])
+def test_product_reproduces_reference_optimize_k1(cuda, case, shift):
+    from yat_b200.embeddings import pad_embeddings
+    from yat_b200.loss import fused_denoise_loss
+    from yat_b200.noise import flowmatch_noise
+    from yat_b200.schedulers import FlowMatchEulerDiscreteScheduler
+    ref = torch.load(os.path.join(GOLD, "reference_sana_optimize_k1.pt"))[case]
+    lat, pred = ref["latents"], ref["pred"]
+    g = torch.Generator()                                                 # the reference's fresh generator, its draw order
+    noise = torch.randn(tuple(lat.shape), generator=g, dtype=torch.bfloat16)
+    u = torch.sigmoid(torch.normal(mean=0.0, std=1.0, size=(lat.shape[0],), generator=g))
+    nz = flowmatch_noise(lat.to(cuda), FlowMatchEulerDiscreteScheduler(shift=shift), noise=noise.to(cuda), u=u.to(cuda))
+    assert torch.equal(nz.timesteps.cpu(), ref["timesteps"])
+    assert torch.equal(nz.x_t.cpu(), ref["x_t"])
+    padded, mask = pad_embeddings(ref["embeddings"], 512, cuda)
+    assert torch.equal(mask.cpu(), ref["mask"]) and torch.equal(padded.cpu(), ref["padded"])
+    loss = fused_denoise_loss(pred.to(cuda), lat.to(cuda), noise.to(cuda))
+    assert abs(loss.item() - ref["loss"].item()) <= 1e-5 * abs(ref["loss"].item())
+
+
+@pytest.mark.gpu
+def test_product_reproduces_reference_optimize_k2(cuda):
+    from yat_b200.embeddings import pad_embeddings
+    from yat_b200.loss import fused_denoise_loss
+    from yat_b200.noise import flowmatch_noise
+    from yat_b200.schedulers import FlowMatchEulerDiscreteScheduler
+    m, lat, pred, embeddings = _k2_inputs()
+    g = torch.Generator()
+    noise = torch.randn(tuple(lat.shape), generator=g, dtype=torch.bfloat16)
+    u = torch.sigmoid(torch.normal(mean=0.0, std=1.0, size=(lat.shape[0],), generator=g))
+    nz = flowmatch_noise(lat.to(cuda), FlowMatchEulerDiscreteScheduler(shift=m["shift"]), noise=noise.to(cuda), u=u.to(cuda))
+    assert [float(v) for v in nz.timesteps.cpu()] == m["timesteps"]
+    assert _sha(nz.x_t.cpu()) == m["x_t_sha256"]
+    padded, mask = pad_embeddings(embeddings, 512, cuda)
+    assert _sha(mask.cpu()) == m["mask_sha256"] and _sha(padded.cpu()) == m["padded_sha256"]
+    loss = fused_denoise_loss(pred.to(cuda), lat.to(cuda), noise.to(cuda))
+    assert abs(loss.item() - m["loss"]) <= 1e-5 * abs(m["loss"])
