@@ -9,15 +9,22 @@ What it is: a plain-torch (CPU) restatement of the arithmetic the reference gets
 torch + diffusers on its hot path, function by function, each citing the reference
 ``file:line`` it follows (paths relative to the upstream tree).
 
-Pinning status (see DESIGN.md §Oracle):
-  * The reference has no tests, fixtures or golden vectors for this path and cannot be
-    imported here (diffusers / accelerate / peft are not installed), so there is no
-    reference-owned vector to pin against: **parity unpinned by the reference**.
-  * What *is* pinned: every op the reference calls is a stock ATen CPU op, and the oracle
-    calls the very same ATen ops in the same order and dtype (bf16 rounding chain
-    included).  The known-answer vectors in ``tests/golden/`` (generated by
-    ``tests/golden/make_golden.py`` from torch itself: fresh-``torch.Generator`` draws,
-    scheduler tables, bucket keys, linear-attention identities) freeze that behaviour.
+Pinning status (see DESIGN.md §2):
+  * PINNED by outputs of the reference itself: the reference cannot be imported as a package
+    here (diffusers / accelerate / peft are not installed) and ships no tests or vectors, but
+    its hot-path functions are plain Python + torch.  ``tests/golden/make_golden_from_reference.py``
+    compiles them from the reference files with ``ast`` and EXECUTES them - ``SanaModel.optimize``
+    (train_sana.py:163-219), ``SD35Trainer.optimize`` (train_sd35.py:165-194),
+    ``PixartSigmaTrainer.optimize`` (train_pixart_sigma.py:151-185), the three bucket functions,
+    ``RepaMLP``, the YAML reader - and commits what they produce (``tests/golden/reference_*``).
+    ``tests/test_reference_golden.py`` holds this oracle (and the product, on the GPU) to those
+    vectors: timesteps, pad / mask, x_t bit-exact, losses to 1e-6.
+  * NOT pinned (restated from SURVEY.md §8(c), no diffusers on either box): the two diffusers
+    helpers those functions call (``randn_tensor``, ``compute_density_for_timestep_sampling``),
+    the scheduler tables and ``scale_noise`` / ``add_noise``, the transformer bodies
+    (SANA / PixArt / SD3 models, ``SanaLinearAttnProcessor2_0``): **unpinned by the reference**.
+  * Also frozen: the ATen behaviour the reference relies on (``tests/golden/make_golden.py``:
+    fresh-``torch.Generator`` draws, scheduler tables, bucket keys, linear-attention identities).
   * ``use_preservation`` and the REPA cosine term are not implemented by the reference
     (README prose / commented-out code only); their oracle is our own stated formula.
 """
