@@ -15,7 +15,8 @@ Pinning status:
     its hot-path functions are plain Python + torch.  ``tests/golden/make_golden_from_reference.py``
     compiles them from the reference files with ``ast`` and EXECUTES them - ``SanaModel.optimize``
     (train_sana.py:163-219), ``SD35Trainer.optimize`` (train_sd35.py:165-194),
-    ``PixartSigmaTrainer.optimize`` (train_pixart_sigma.py:151-185), the three bucket functions,
+    ``PixartSigmaTrainer.optimize`` (train_pixart_sigma.py:151-185), ``PatchedSanaTransformerBlock.forward``
+    (utils/patch_sana_attention_layers.py:72-115, linear stand-ins for attn1 / attn2 / ff), the three bucket functions,
     ``RepaMLP``, the YAML reader - and commits what they produce (``tests/golden/reference_*``).
     ``tests/test_reference_golden.py`` holds this oracle (and the product, on the GPU) to those
     vectors: timesteps, pad / mask, x_t bit-exact, losses to 1e-6.

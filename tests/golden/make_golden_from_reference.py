@@ -10,6 +10,8 @@ the two diffusers helpers they call replaced by the restatements SURVEY.md §8(c
                                                      velocity target, fp32 MSE                          (rows A1-A6, A12)
   train_sd35.py        SD35Trainer.optimize          global-RNG draw order, velocity target, bf16 MSE   (rows A1, A2, A5, A6)
   train_pixart_sigma.py PixartSigmaTrainer.optimize  pad to 300, eps target cropped to pred[:, :C], bf16 MSE (A5, A6, A12)
+  utils/patch_sana_attention_layers.py  PatchedSanaTransformerBlock.forward   adaLN-single modulate / gate / residual
+                                                     around linear stand-ins for attn1 / attn2 / ff     (row A11)
   common/trainer.py    Model.find_closest_ratio      first-minimum bucket rule                          (row A9)
   common/bucket_sampler.py  find_closest_key, BucketSamplerExtractFeatures.find_closest_ratio            (row A9)
   common/repa.py       RepaMLP                       projector Linear-ReLU-Linear                       (row A8, projector)
@@ -219,9 +221,38 @@ def run_pixart_optimize(shape, emb_lens, seed):
             "loss": loss, "global_seed": seed + 100}
 
 
+def run_sana_block(seed, dtype):
+    """utils/patch_sana_attention_layers.py PatchedSanaTransformerBlock.forward (:72-115) with real torch LayerNorms and the
+    linear stand-ins of block_stubs.py for attn1 / attn2 / ff: the adaLN-single modulate, gate and residual arithmetic and
+    its rounding order in `dtype` (row A11)."""
+    sys.path.insert(0, HERE)
+    from block_stubs import StubCrossAttn, StubFF, StubSelfAttn
+    code, line = extract("utils/patch_sana_attention_layers.py", "forward", cls="PatchedSanaTransformerBlock")
+    glb = {"torch": torch, "Optional": __import__("typing").Optional}
+    exec(code, glb)
+    B, Hh, Ww, C, L = 2, 8, 8, 64, 12
+    g = torch.Generator().manual_seed(seed)
+    rnd = lambda *s, k=1.0: (k * torch.randn(s, generator=g)).to(dtype)  # noqa: E731
+    w1, w2, we, wf = rnd(C, C, k=C ** -0.5), rnd(C, C, k=C ** -0.5), rnd(C, C, k=C ** -0.5), rnd(C, C, k=C ** -0.5)
+    table = rnd(6, C, k=C ** -0.5)
+    hidden, enc, temb = rnd(B, Hh * Ww, C), rnd(B, L, C), rnd(B, 6 * C, k=0.5)
+    self = types.SimpleNamespace(
+        norm1=torch.nn.LayerNorm(C, elementwise_affine=False, eps=1e-6), norm2=torch.nn.LayerNorm(C, elementwise_affine=False, eps=1e-6),
+        attn1=StubSelfAttn(w1), attn2=StubCrossAttn(w2, we), ff=StubFF(wf), scale_shift_table=table)
+    out = glb["forward"](self, hidden, None, enc, None, temb, Hh, Ww)
+    return {"line": line, "w1": w1, "w2": w2, "we": we, "wf": wf, "table": table, "hidden": hidden, "enc": enc, "temb": temb,
+            "height": Hh, "width": Ww, "out": out}
+
+
 def main():
     meta = {"generated_by": "tests/golden/make_golden_from_reference.py", "torch": torch.__version__,
             "reference_functions": {}}
+
+    # ---- the SANA block wrapper (row A11) in bf16 (the training dtype) and fp32
+    blk = {"bf16": run_sana_block(41, torch.bfloat16), "fp32": run_sana_block(41, torch.float32)}
+    meta["reference_functions"]["utils/patch_sana_attention_layers.py::PatchedSanaTransformerBlock.forward"] = blk["bf16"].pop("line")
+    blk["fp32"].pop("line")
+    torch.save(blk, os.path.join(HERE, "reference_sana_block.pt"))
 
     # ---- SD35Trainer.optimize / PixartSigmaTrainer.optimize on small shapes (tensors kept)
     sd = run_sd35_optimize((2, 16, 16, 16), seed=31)
