@@ -16,10 +16,12 @@ Pinning status:
     compiles them from the reference files with ``ast`` and EXECUTES them - ``SanaModel.optimize``
     (train_sana.py:163-219), ``SD35Trainer.optimize`` (train_sd35.py:165-194),
     ``PixartSigmaTrainer.optimize`` (train_pixart_sigma.py:151-185), ``PatchedSanaTransformerBlock.forward``
-    (utils/patch_sana_attention_layers.py:72-115, linear stand-ins for attn1 / attn2 / ff), the three bucket functions,
+    (utils/patch_sana_attention_layers.py:72-115, linear stand-ins for attn1 / attn2 / ff), the step loop ``Model.run``
+    (common/trainer.py:298-403, a tiny denoiser, accelerate's accumulate / backward restated), the three bucket functions,
     ``RepaMLP``, the YAML reader - and commits what they produce (``tests/golden/reference_*``).
     ``tests/test_reference_golden.py`` holds this oracle (and the product, on the GPU) to those
-    vectors: timesteps, pad / mask, x_t bit-exact, losses to 1e-6.
+    vectors: timesteps, pad / mask, x_t bit-exact, losses to 1e-6; ``oracle/step_loop.py`` equals the
+    reference loop bit for bit (logged losses, learning rates, final parameters).
   * NOT pinned (restated from SURVEY.md §8(c), no diffusers on either box): the two diffusers
     helpers those functions call (``randn_tensor``, ``compute_density_for_timestep_sampling``),
     the scheduler tables and ``scale_noise`` / ``add_noise``, the transformer bodies

@@ -36,3 +36,42 @@ class StubFF(torch.nn.Module):
 
     def forward_tokens(self, x, height, width):             # [B, N, C]
         return torch.nn.functional.linear(x, self.w.to(x.device))
+
+
+class TinyDenoiser(torch.nn.Module):
+    """A few-parameter denoiser with the SanaTransformer2DModel call signature (x_t, encoder_hidden_states, timestep,
+    encoder_attention_mask) -> .sample, fp32 parameters, bf16 in / out.  The text enters through a MASKED mean, so the
+    result does not depend on how far the captions are padded (512 in the reference, trimmed in this build)."""
+
+    def __init__(self, channels, emb_dim, seed=0):
+        super().__init__()
+        g = torch.Generator().manual_seed(seed)
+        self.mix = torch.nn.Parameter(torch.randn((channels, channels, 1, 1), generator=g) * channels ** -0.5)
+        self.txt = torch.nn.Parameter(torch.randn((channels, emb_dim), generator=g) * emb_dim ** -0.5)
+        self.tsc = torch.nn.Parameter(torch.randn((channels,), generator=g) * 0.1)
+
+    def forward(self, x, encoder_hidden_states=None, timestep=None, encoder_attention_mask=None, **kw):
+        import types
+        m = encoder_attention_mask.to(torch.float32)
+        if m.dim() == 3:                               # additive bias form [B, 1, L]: 0 on real tokens
+            m = (m.squeeze(1) == 0).to(torch.float32)
+        ctx = (encoder_hidden_states.float() * m.unsqueeze(-1)).sum(1) / m.sum(1, keepdim=True).clamp_min(1.0)
+        h = torch.einsum("oc,bchw->bohw", self.mix[:, :, 0, 0], x.float())    # fp32 matmul (no TF32 conv path)
+        h = h + torch.nn.functional.linear(ctx, self.txt)[:, :, None, None]
+        h = h + (self.tsc[None] * (timestep.float() / 1000.0)[:, None])[:, :, None, None]
+        return types.SimpleNamespace(sample=h.to(x.dtype))
+
+
+def loop_batches(n_micro, batch_size, channels, hw, emb_dim, seed):
+    """The micro-batches the step-loop golden feeds (fresh objects every call: the reference's CFG dropout writes into the
+    embeddings list it is handed, common/trainer.py:321-323)."""
+    import types
+    g = torch.Generator().manual_seed(seed)
+    out = []
+    for _ in range(n_micro):
+        lens = [int(v) for v in torch.randint(3, 40, (batch_size,), generator=g)]
+        out.append(types.SimpleNamespace(
+            ratio="1.0", repa_features=None,
+            vae_features=torch.randn((batch_size, channels, hw, hw), generator=g).to(torch.bfloat16),
+            embeddings=[(0.5 * torch.randn((L, emb_dim), generator=g)).to(torch.bfloat16) for L in lens]))
+    return out

@@ -244,6 +244,102 @@ def run_sana_block(seed, dtype):
             "height": Hh, "width": Ww, "out": out}
 
 
+# ---- the step loop: common/trainer.py Model.run (:298-403) driving SanaModel.optimize, both from the reference source ----
+class AccelerateStub:
+    """The slice of accelerate.Accelerator the loop touches, restated (accelerate is not installed):
+    accumulate() counts micro-steps and raises sync_gradients on every G-th; backward() divides the loss by G;
+    clip_grad_norm_ is torch's; gather() on one process is the identity."""
+
+    def __init__(self, accum):
+        self.device, self.is_main_process, self.accum = torch.device("cpu"), True, int(accum)
+        self.sync_gradients, self.step = True, 0
+
+    def accumulate(self, model):
+        import contextlib
+
+        @contextlib.contextmanager
+        def ctx():
+            self.step += 1
+            self.sync_gradients = self.step % self.accum == 0
+            yield
+        return ctx()
+
+    def backward(self, loss):
+        (loss / self.accum).backward()
+
+    def clip_grad_norm_(self, parameters, max_norm):
+        return torch.nn.utils.clip_grad_norm_(parameters, max_norm)
+
+    def gather(self, t):
+        return t
+
+    def wait_for_everyone(self):
+        pass
+
+    def unwrap_model(self, m):
+        return m
+
+
+LOOP = dict(steps=4, accum=2, batch_size=2, channels=8, hw=8, emb_dim=16, exploration_steps=2, uncond_prob=0.4,
+            warmup_steps=2, lr=1e-2, weight_decay=1e-2, shift=3.0, model_seed=3, data_seed=17, random_seed=7)
+
+
+def run_trainer_loop(cfg=LOOP):
+    """Model.run executed from the reference file with SanaModel.optimize as its hook, a TinyDenoiser as the transformer,
+    torch.optim.AdamW / LambdaLR built the way Model.initialize builds them (:245-262), seeded `random` for the CFG-dropout
+    draw (:319) and a list sampler.  Records every logged train/loss, train/lr and the final parameters (row A13)."""
+    import random
+    sys.path.insert(0, HERE)
+    from block_stubs import TinyDenoiser, loop_batches
+    from torch.optim.lr_scheduler import LambdaLR
+    run_code, line = extract("common/trainer.py", "run", cls="Model")
+    opt_code, _ = extract("train_sana.py", "optimize", cls="SanaModel")
+    tqdm_stub = types.SimpleNamespace(tqdm=lambda **kw: types.SimpleNamespace(update=lambda n: None))
+    glb = {"torch": torch, "tqdm": tqdm_stub, "random": random, "rescale_adapter_scale": lambda m, s: None,
+           "randn_tensor": randn_tensor, "compute_density_for_timestep_sampling": compute_density_for_timestep_sampling}
+    exec(run_code, glb)
+    exec(opt_code, glb)
+    log, calls = [], []
+    tt, ss = schedule.flow_match_tables(1000, cfg["shift"])
+    empty = (0.5 * torch.randn((1, cfg["emb_dim"]), generator=torch.Generator().manual_seed(99))).to(torch.bfloat16)
+    warm = cfg["warmup_steps"]
+
+    class RefTrainer:
+        run, optimize = glb["run"], glb["optimize"]
+
+        def __init__(self):
+            self.params = types.SimpleNamespace(
+                steps=cfg["steps"], batch_size=cfg["batch_size"], exploration_steps=cfg["exploration_steps"],
+                train_unconditional_prob=cfg["uncond_prob"], num_steps_per_validation=1000, dual_gpu=False, use_repa=False)
+            self.accelerator = AccelerateStub(cfg["accum"])
+            self.scheduler = types.SimpleNamespace(config=types.SimpleNamespace(num_train_timesteps=1000), timesteps=tt, sigmas=ss)
+            self.model = TinyDenoiser(cfg["channels"], cfg["emb_dim"], seed=cfg["model_seed"])
+            self.global_step, self.timesteps, self.ema_model = 0, [], None
+            self.logger = types.SimpleNamespace(add_scalar=lambda k, v, s: log.append((k, float(v), int(s))))
+
+        def initialize(self):                                        # the optimiser half of Model.initialize (:245-262)
+            self.optimizer = torch.optim.AdamW(self.model.parameters(), lr=cfg["lr"], weight_decay=cfg["weight_decay"])
+            self.lr_scheduler = LambdaLR(self.optimizer, lr_lambda=lambda s: float(s) / float(max(1, warm)) if s < warm else 1.0)
+            self.sampler = loop_batches(cfg["steps"] * cfg["accum"], cfg["batch_size"], cfg["channels"], cfg["hw"],
+                                        cfg["emb_dim"], cfg["data_seed"])
+
+        def extract_embeddings(self, captions):
+            return [empty]
+
+        def validate(self):
+            calls.append(("validate", self.global_step))
+
+        def save_model(self):
+            calls.append(("save_model", self.global_step))
+
+    random.seed(cfg["random_seed"])
+    t = RefTrainer()
+    t.run()
+    return {"line": line, "cfg": dict(cfg), "log": log, "calls": calls, "empty": empty,
+            "params": {k: v.detach().clone() for k, v in t.model.state_dict().items()},
+            "exp_avg": {k: t.optimizer.state[p]["exp_avg"].clone() for k, p in t.model.named_parameters()}}
+
+
 def main():
     meta = {"generated_by": "tests/golden/make_golden_from_reference.py", "torch": torch.__version__,
             "reference_functions": {}}
@@ -253,6 +349,11 @@ def main():
     meta["reference_functions"]["utils/patch_sana_attention_layers.py::PatchedSanaTransformerBlock.forward"] = blk["bf16"].pop("line")
     blk["fp32"].pop("line")
     torch.save(blk, os.path.join(HERE, "reference_sana_block.pt"))
+
+    # ---- the step loop (row A13)
+    loop = run_trainer_loop()
+    meta["reference_functions"]["common/trainer.py::Model.run"] = loop.pop("line")
+    torch.save(loop, os.path.join(HERE, "reference_trainer_loop.pt"))
 
     # ---- SD35Trainer.optimize / PixartSigmaTrainer.optimize on small shapes (tensors kept)
     sd = run_sd35_optimize((2, 16, 16, 16), seed=31)

@@ -255,3 +255,80 @@ def test_block_wrapper_fused_kernels_vs_the_reference_block(cuda):
     assert e_fused < 2e-2 and e_fused <= 1.25 * e_ref_bf16 + 1e-3, (e_fused, e_ref_bf16)
     e_pair = ((out.cpu().double() - r["out"].double()).norm() / r["out"].double().norm()).item()
     assert e_pair < 2e-2, e_pair
+
+
+# ------------------------------------------------------------------- the step loop (row A13)
+def _loop_fixture():
+    import sys
+    sys.path.insert(0, GOLD)
+    from block_stubs import TinyDenoiser, loop_batches
+    r = torch.load(os.path.join(GOLD, "reference_trainer_loop.pt"))
+    c = r["cfg"]
+    model = TinyDenoiser(c["channels"], c["emb_dim"], seed=c["model_seed"])
+    batches = loop_batches(c["steps"] * c["accum"], c["batch_size"], c["channels"], c["hw"], c["emb_dim"], c["data_seed"])
+    ref_loss = [v for k, v, _ in r["log"] if k == "train/loss"]
+    ref_lr = [v for k, v, _ in r["log"] if k == "train/lr"]
+    return r, c, model, batches, ref_loss, ref_lr
+
+
+def test_oracle_step_loop_equals_the_reference_run_loop():
+    """Model.run + SanaModel.optimize executed from the reference source (accumulation over 2 micro-steps, CFG dropout,
+    2 exploration trials, clip, AdamW, warm-up) against oracle/step_loop.py: same ATen ops on the CPU -> every logged
+    loss, learning rate and final parameter bit-exact."""
+    from oracle import step_loop
+    r, c, model, batches, ref_loss, ref_lr = _loop_fixture()
+    assert [s for k, _, s in r["log"] if k == "train/loss"] == list(range(c["steps"]))
+    logged, lrs = step_loop.run(model, batches, r["empty"], c["steps"], c["accum"], c["batch_size"], c["exploration_steps"],
+                                c["uncond_prob"], c["warmup_steps"], c["lr"], c["weight_decay"], c["shift"], c["random_seed"])
+    assert logged == ref_loss and lrs == ref_lr
+    for k, v in model.state_dict().items():
+        assert torch.equal(v, r["params"][k]), k
+
+
+@pytest.mark.gpu
+def test_product_step_loop_follows_the_reference_run_loop(cuda):
+    """yat_b200.trainer.Model.run with train_sana.SanaModel.optimize as its hook (pad kernel, noising kernel, fused loss,
+    FusedClipAdamW) on the same TinyDenoiser, batches, `random` seed and per-step torch.Generator as the reference loop:
+    logged losses <= 1e-5 relative, final parameters within 2e-3 of the distance the run moved them."""
+    import random
+    from train_sana import SanaModel
+    from yat_b200.schedulers import FlowMatchEulerDiscreteScheduler
+    from yat_b200.trainer import Model
+    from yat_b200.training_parameters_reader import TrainingParameters
+    r, c, model, batches, ref_loss, ref_lr = _loop_fixture()
+    start = {k: v.clone() for k, v in model.state_dict().items()}
+
+    class Loop(SanaModel):
+        def __init__(self, params):
+            Model.__init__(self, params)
+            self.model = model.to(cuda)
+            self.pipe = __import__("types").SimpleNamespace(transformer=self.model)
+            self.scheduler = FlowMatchEulerDiscreteScheduler(shift=c["shift"])
+            self.frozen_model, self.patch_size, self._trust_gscale = None, 1, False
+            self.empty_embeddings = [r["empty"]]
+
+        def make_sampler(self):
+            return batches
+
+        def _generator(self):
+            return torch.Generator()          # the reference's per-step generator (common/trainer.py:325)
+
+        def save_model(self):
+            pass
+
+    p = TrainingParameters()
+    p.batch_size, p.steps, p.gradient_accumulation_steps = c["batch_size"], c["steps"], c["accum"]
+    p.exploration_steps, p.train_unconditional_prob, p.warmup_steps = c["exploration_steps"], c["uncond_prob"], c["warmup_steps"]
+    p.learning_rate, p.weight_decay, p.num_steps_per_validation = c["lr"], c["weight_decay"], 1000
+    random.seed(c["random_seed"])
+    t = Loop(p)
+    t.run()
+    got = [float(v) for v in t.losses]
+    assert len(got) == c["steps"]
+    for a, b in zip(got, ref_loss):
+        assert abs(a - b) <= 1e-5 * abs(b), (got, ref_loss)
+    assert abs(t.lr_scheduler.get_last_lr()[0] - ref_lr[-1]) < 1e-12
+    for k, v in t.model.state_dict().items():
+        moved = (r["params"][k] - start[k]).norm().item()
+        assert moved > 0
+        assert (v.cpu() - r["params"][k]).norm().item() <= 2e-3 * moved, k
