@@ -340,6 +340,66 @@ def run_trainer_loop(cfg=LOOP):
             "exp_avg": {k: t.optimizer.state[p]["exp_avg"].clone() for k, p in t.model.named_parameters()}}
 
 
+# ---- the cache record (row A14): the writer's sample dict and the reader's decoder, both from the reference source -------
+def run_cache_record(path, seed=23):
+    """common/features_extractor.py: the nested `tensor_to_bytes` (:61-64) and the `sample = {...}` literal (:78-83) are
+    evaluated from the reference text; webdataset's TarWriter (absent) is restated as what it does with such a dict: one tar
+    member `<__key__>.<field>` per field, str values utf-8 encoded.  The shard is then read back the way
+    common/bucket_sampler.py does: members regrouped by key (webdataset's base_plus_ext, restated), each field through the
+    reference's `pt_decoder` (:138-146), each record through `process_element` / `add_bucket` (:148-156)."""
+    import io
+    import tarfile
+    from collections import deque
+    full = os.path.join(REF, "common/features_extractor.py")
+    tree = ast.parse(open(full).read())
+    t2b = next(n for n in ast.walk(tree) if isinstance(n, ast.FunctionDef) and n.name == "tensor_to_bytes")
+    lit = next(n for n in ast.walk(tree) if isinstance(n, ast.Assign) and getattr(n.targets[0], "id", None) == "sample"
+               and isinstance(n.value, ast.Dict))
+    glb = {"io": io, "torch": torch}
+    exec(compile(ast.fix_missing_locations(ast.Module(body=[t2b], type_ignores=[])), full, "exec"), glb)
+    sample_expr = compile(ast.fix_missing_locations(ast.Expression(body=lit.value)), full, "eval")
+    g = torch.Generator().manual_seed(seed)
+    groups = [("1.0", (8, 4, 4), [5, 9]), ("0.57", (8, 3, 5), [12, 1, 7])]          # (ratio key, latent shape, caption lengths)
+    current_element, written = 0, []
+    with tarfile.open(path, "w") as tar:
+        for ratio, shape, lens in groups:
+            latents = torch.randn((len(lens),) + shape, generator=g).to(torch.bfloat16)
+            embeddings = [torch.randn((L, 16), generator=g).to(torch.bfloat16) for L in lens]
+            for i in range(len(lens)):
+                sample = eval(sample_expr, dict(glb, current_element=current_element, ratio=ratio, latents=latents,
+                                                embeddings=embeddings, i=i))
+                for field, v in sample.items():                     # wds.TarWriter.write, restated
+                    if field == "__key__":
+                        continue
+                    data = v.encode("utf-8") if isinstance(v, str) else v
+                    info = tarfile.TarInfo(sample["__key__"] + "." + field)
+                    info.size = len(data)
+                    tar.addfile(info, io.BytesIO(data))
+                written.append({"__key__": sample["__key__"], "ratio": ratio, "latent": latents[i].clone(), "emb": embeddings[i]})
+                current_element += 1
+    # ---- read back with the reference's decoder + bucket regrouping
+    glb2 = {"torch": torch, "io": io, "deque": deque}
+    for fn in ("pt_decoder", "process_element", "add_bucket"):
+        code, line = extract("common/bucket_sampler.py", fn, cls="BucketSampler")
+        exec(code, glb2)
+    sampler = types.SimpleNamespace(buckets={}, batch_size=8)
+    sampler.add_bucket = lambda r: glb2["add_bucket"](sampler, r)
+    order = []
+    with tarfile.open(path, "r") as tar:
+        cur_key, cur = None, {}
+        for m in tar:
+            key, _, field = m.name.partition(".")                   # webdataset base_plus_ext, restated
+            if key != cur_key and cur:
+                glb2["process_element"](sampler, cur)
+                cur = {}
+            cur_key = key
+            cur[field] = glb2["pt_decoder"](sampler, field, tar.extractfile(m).read())
+            order.append(m.name)
+        glb2["process_element"](sampler, cur)
+    return {"line": t2b.lineno, "written": written, "members": order,
+            "buckets": {k: [(lat, emb) for lat, emb in v] for k, v in sampler.buckets.items()}}
+
+
 def main():
     meta = {"generated_by": "tests/golden/make_golden_from_reference.py", "torch": torch.__version__,
             "reference_functions": {}}
@@ -349,6 +409,11 @@ def main():
     meta["reference_functions"]["utils/patch_sana_attention_layers.py::PatchedSanaTransformerBlock.forward"] = blk["bf16"].pop("line")
     blk["fp32"].pop("line")
     torch.save(blk, os.path.join(HERE, "reference_sana_block.pt"))
+
+    # ---- the cache record (row A14): a 5-sample shard written and read back by the reference's own lines
+    rec = run_cache_record(os.path.join(HERE, "reference_shard.tar"))
+    meta["reference_functions"]["common/features_extractor.py::tensor_to_bytes"] = rec.pop("line")
+    torch.save(rec, os.path.join(HERE, "reference_shard_decoded.pt"))
 
     # ---- the step loop (row A13)
     loop = run_trainer_loop()

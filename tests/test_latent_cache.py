@@ -154,3 +154,48 @@ def test_trainer_steps_from_a_slab_cache(cuda, tmp_path, monkeypatch):
         losses.append(tr.train_step(b).item())
     assert len(shapes) == 2 and all(l == l and abs(l) < 1e3 for l in losses)
     assert sum(int(not torch.equal(before[n], p.detach())) for n, p in tr.model.named_parameters() if n in before) > 10
+
+
+# ------------------------------------------------------------------ the record as the reference's own lines write / read it
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def test_reader_decodes_a_shard_written_by_the_reference_lines():
+    """tests/golden/reference_shard.tar was written by evaluating the reference's `sample = {...}` literal and
+    `tensor_to_bytes` (common/features_extractor.py:61-64,78-83) and decoded by its `pt_decoder` / `process_element`
+    (common/bucket_sampler.py:138-156), all from the reference source (make_golden_from_reference.run_cache_record).
+    read_reference_shard must yield the same records: key order, float bucket key, tensors bit for bit."""
+    ref = torch.load(os.path.join(GOLD, "reference_shard_decoded.pt"))
+    back = list(read_reference_shard(os.path.join(GOLD, "reference_shard.tar")))
+    assert [r["__key__"] for r in back] == [w["__key__"] for w in ref["written"]]
+    regroup = {}
+    for r, w in zip(back, ref["written"]):
+        assert r["ratio"] == float(w["ratio"])
+        assert r["latent.pt"].dtype == torch.bfloat16 and torch.equal(r["latent.pt"], w["latent"])
+        assert torch.equal(r["emb.pt"], w["emb"])
+        regroup.setdefault(r["ratio"], []).append((r["latent.pt"], r["emb.pt"]))
+    assert list(regroup) == list(ref["buckets"])                           # the reference's per-ratio deques, same order
+    for k, items in ref["buckets"].items():
+        assert len(items) == len(regroup[k])
+        for (la, ea), (lb, eb) in zip(items, regroup[k]):
+            assert torch.equal(la, lb) and torch.equal(ea, eb)
+
+
+def test_writer_produces_the_member_layout_of_the_reference_shard(tmp_path):
+    """write_reference_shard on the same samples: same tar member names in the same order, same `ratio` payload bytes,
+    `.pt` payloads that torch.load to the same tensors (and, with the torch that made the fixture, the same bytes)."""
+    import tarfile
+    ref = torch.load(os.path.join(GOLD, "reference_shard_decoded.pt"))
+    path = os.path.join(tmp_path, "shard-000000.tar")
+    write_reference_shard(path, [{"__key__": w["__key__"], "ratio": w["ratio"], "latent.pt": w["latent"], "emb.pt": w["emb"]}
+                                 for w in ref["written"]])
+    with tarfile.open(path) as mine, tarfile.open(os.path.join(GOLD, "reference_shard.tar")) as gold:
+        a, b = mine.getmembers(), gold.getmembers()
+        assert [m.name for m in a] == [m.name for m in b] == ref["members"]
+        for ma, mb in zip(a, b):
+            da, db = mine.extractfile(ma).read(), gold.extractfile(mb).read()
+            if ma.name.endswith(".ratio"):
+                assert da == db
+            else:
+                import io
+                assert torch.equal(torch.load(io.BytesIO(da)), torch.load(io.BytesIO(db)))
