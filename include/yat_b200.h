@@ -279,6 +279,17 @@ int yat_qkv_linattn_fwd(const void* x, const void* w_qkv, int B, int N, int H, i
 int yat_linattn_fwd_state(const void* q, int64_t ld, const void* state, int B, int N, int H, int D, void* o,
                           void* stream);
 
+/* ---- cross-attention of the block (attn2): softmax(scale q k^T + bias) v, few keys ------------------------------------
+ * Replaces F.scaled_dot_product_attention inside diffusers' AttnProcessor2_0 for `self.attn2(...)` of the SANA / PixArt
+ * block (utils/patch_sana_attention_layers.py:100-106; the mask argument is diffusers' additive bias, 0 on caption tokens
+ * and -10000 on padding).  q, o [B, Nq, H*d] bf16 (q row pitch ldq elements, o dense), k, v [B, L, H*d] bf16 (row pitch
+ * ldkv), bias fp32 [B, L] or NULL, lse fp32 [B, H, Nq] or NULL (ln sum_j exp(scale q.k_j + bias_j), what the backward
+ * reads).  d a multiple of 8, <= 128; L <= yat_xattn_max_keys() (384: a whole row of scores lives in tensor memory).
+ */
+int yat_xattn_max_keys(void);
+int yat_xattn_fwd(const void* q, const void* k, const void* v, const void* bias, int B, int H, int Nq, int L, int d,
+                  int64_t ldq, int64_t ldkv, float scale, void* o, void* lse, void* stream);
+
 /* ---- bucket assignment (host function; float64 compare, first-minimum wins) ---------------
  *   out[i] = argmin_j |keys[j] - ratios[i]| with strict '<' in table order, or -1 if nkeys==0.
  */

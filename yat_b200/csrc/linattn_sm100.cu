@@ -440,6 +440,26 @@ int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t N
   return YAT_OK;
 }
 
+int make_tmap_heads_bf16(CUtensorMap* out, const void* base, uint64_t d, uint64_t H, uint64_t rows, uint64_t B, uint64_t ld,
+                         uint32_t box_rows) {
+  PFN_encodeTiled enc = get_encode_fn();
+  YAT_REQUIRE(enc != nullptr, YAT_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  const cuuint64_t dims[4] = {d, H, rows, B};
+  const cuuint64_t strides[3] = {d * 2, ld * 2, rows * ld * 2};
+  const cuuint32_t box[4] = {64, 1, box_rows, 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = CUDA_ERROR_UNKNOWN;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_ERROR_INVALID_CONTEXT) break;
+    cudaFree(nullptr);  // first driver-API call on this thread (autograd worker): bind the primary context, retry
+  }
+  YAT_REQUIRE(r == CUDA_SUCCESS, YAT_ERR_CUDA, "cuTensorMapEncodeTiled (heads) failed with CUresult %d", (int)r);
+  return YAT_OK;
+}
+
 // Plain (unswizzled) 4-D bf16 tensor map {d0, d1, d2, d3} (d0 contiguous) with box {b0, b1, b2, 1}; out-of-bounds
 // elements of a box (negative or past-the-end coordinates) read as zero.
 int make_tmap_4d_bf16_plain(CUtensorMap* out, const void* base, const uint64_t dims[4], const uint32_t box[4]) {

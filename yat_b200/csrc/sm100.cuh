@@ -67,6 +67,11 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, uint32_t smem
                "r"(c0), "r"(c1), "r"(c2)
                : "memory");
 }
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, uint32_t smem_src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(m), "r"(smem_src),
+               "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void tma_store_wait_read() {
@@ -186,6 +191,11 @@ static __device__ int g_trn[4];
 // host: encode a 3-D bf16 tensor map {C, N, B} with a {box_c, box_n, 1} box, 128B swizzle
 int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t N, uint64_t B, uint32_t box_c,
                       uint32_t box_n, uint64_t ld = 0 /* row pitch in elements, 0 = C (dense rows) */);
+
+// host: head-split 4-D bf16 tensor map {d, H, rows, B} over a token-major [B, rows, H*d] tensor (row pitch ld elements) with a
+// {64, 1, box_rows, 1} box, 128B swizzle: columns past d of a box read as zero and are clipped on store (cross-attention)
+int make_tmap_heads_bf16(CUtensorMap* out, const void* base, uint64_t d, uint64_t H, uint64_t rows, uint64_t B, uint64_t ld,
+                         uint32_t box_rows);
 
 // host: plain 4-D bf16 tensor map, zero fill out of bounds (GLUMB kernels)
 int make_tmap_4d_bf16_plain(CUtensorMap* out, const void* base, const uint64_t dims[4], const uint32_t box[4]);
