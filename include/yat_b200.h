@@ -180,6 +180,21 @@ int yat_gate_residual_bwd(const void* dout, const void* y, const void* gate, int
 int64_t yat_colsum_workspace_bytes(int64_t rows, int C);
 int yat_colsum_bf16(const void* a, int64_t rows, int C, void* out, void* workspace, void* stream);
 
+/* yat_colsum_bf16_static: the same two kernels with the split partials in a file-scope device array inside the library
+ * instead of a caller workspace, for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  NO COUNTERPART IN THE REFERENCE.
+ * It allocates nothing (no cudaMalloc / cudaFree / allocating library call); the array is yat_colsum_static_max_bytes()
+ * = 2 MiB per GPU that loads the library, held until exit.  Shapes whose partials do not fit (splits * C * 4 B, the
+ * figure yat_colsum_workspace_bytes reports) are rejected with YAT_ERR_UNSUPPORTED and a message naming both sizes;
+ * every SANA / PixArt / SD3.5 width of this build fits (C <= 11200 at any row count).  All calls share the array:
+ * nothing has to start at zero (each call overwrites what it reads), but two calls that OVERLAP on the GPU (different
+ * streams, or graphs replayed concurrently) race - serialise them.  The address is resolved once per device on the
+ * first call with that device current (cudaGetSymbolAddress): make that first call outside stream capture.
+ * Result: bit-identical to yat_colsum_bf16.
+ */
+int64_t yat_colsum_static_max_bytes(void);
+int yat_colsum_bf16_static(const void* a, int64_t rows, int C, void* out, void* stream);
+
 /* ---- (next, N1) fused middle of GLUMBConv ---------------------------------------------------
  * utils/patch_sana_attention_layers.py:106-111 -> GLUMBConv: SiLU, depthwise 3x3 (+bias, zero pad 1),
  * chunk, x * SiLU(gate).  Token-major (NHWC):

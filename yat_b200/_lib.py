@@ -53,6 +53,8 @@ SIGNATURES = {
                                   c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "yat_colsum_workspace_bytes": (c_int64, [c_int64, c_int]),
     "yat_colsum_bf16": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p]),
+    "yat_colsum_static_max_bytes": (c_int64, []),
+    "yat_colsum_bf16_static": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p]),
     "yat_optim_chunk_elems": (c_int, []),
     "yat_optim_workspace_bytes": (c_int64, [c_int]),
     "yat_grad_clip_coef": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p]),
@@ -88,7 +90,7 @@ LAUNCHING = ("yat_noise_flowmatch", "yat_noise_ddpm", "yat_loss_fused", "yat_rep
              "yat_philox_raw", "yat_ln_modulate_fwd", "yat_ln_modulate_bwd", "yat_add_ln_modulate_fwd",
              "yat_ln_modulate_bwd_res", "yat_gate_residual_fwd",
              "yat_gate_residual_bwd", "yat_glumb_mid_fwd", "yat_glumb_mid_bwd", "yat_grad_clip_coef",
-             "yat_adamw_step", "yat_adamw_ema_step", "yat_ema_step", "yat_colsum_bf16", "yat_head_pad", "yat_head_unpad",
+             "yat_adamw_step", "yat_adamw_ema_step", "yat_ema_step", "yat_colsum_bf16", "yat_colsum_bf16_static", "yat_head_pad", "yat_head_unpad",
              "yat_linattn_fwd_ld", "yat_linattn_bwd_ld", "yat_gemm_bf16_tn", "yat_qkv_linattn_fwd",
              "yat_linattn_fwd_state", "yat_xattn_fwd")
 launch_counts = {name: 0 for name in LAUNCHING}

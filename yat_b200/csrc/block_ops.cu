@@ -556,6 +556,59 @@ extern "C" int yat_colsum_bf16(const void* a, int64_t rows, int C, void* out, vo
   return check_launch("colsum_finish");
 }
 
+// ---- colsum without any allocation: the split partials live in a file-scope device array ------------------------------
+// For callers that cannot call cudaMalloc (CUDA graph capture, serving loops, harnesses that forbid it).  No counterpart in
+// the reference.  2 MiB per GPU that loads the library, held until exit.
+// Every partial the finish kernel reads is written by the first kernel of the same call, so stale contents are harmless
+// and nothing needs clearing; but ALL calls share the array: two calls that overlap on the GPU (different streams) race.
+constexpr int64_t kColsumStaticFloats = 512 * 1024;
+static __device__ __align__(256) float g_colsum_scratch[kColsumStaticFloats];
+
+// In host code `g_colsum_scratch` is a host-side stand-in, not a device address: resolve it once per device, with that
+// device current, and hand the kernels the resolved pointer.
+static int colsum_static_ptr(float** out) {
+  constexpr int kMaxDevices = 64;
+  static float* ptrs[kMaxDevices] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  YAT_REQUIRE(e == cudaSuccess && dev >= 0 && dev < kMaxDevices, YAT_ERR_CUDA, "yat_colsum_bf16_static: cudaGetDevice failed (%s)",
+              cudaGetErrorString(e));
+  float* p = __atomic_load_n(&ptrs[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    e = cudaGetSymbolAddress((void**)&p, g_colsum_scratch);
+    YAT_REQUIRE(e == cudaSuccess && p != nullptr, YAT_ERR_CUDA, "yat_colsum_bf16_static: cudaGetSymbolAddress failed (%s)",
+                cudaGetErrorString(e));
+    __atomic_store_n(&ptrs[dev], p, __ATOMIC_RELEASE);   // racing threads resolve the same address
+  }
+  *out = p;
+  return YAT_OK;
+}
+
+extern "C" int64_t yat_colsum_static_max_bytes(void) { return kColsumStaticFloats * (int64_t)sizeof(float); }
+
+extern "C" int yat_colsum_bf16_static(const void* a, int64_t rows, int C, void* out, void* stream) {
+  using namespace yat;
+  YAT_REQUIRE(a && out, YAT_ERR_BAD_ARG, "yat_colsum_bf16_static: null pointer argument");
+  YAT_REQUIRE(rows > 0 && C > 0, YAT_ERR_BAD_ARG, "yat_colsum_bf16_static: rows=%lld C=%d must be positive", (long long)rows, C);
+  YAT_REQUIRE(C % 8 == 0, YAT_ERR_UNSUPPORTED, "yat_colsum_bf16_static: C=%d must be a multiple of 8", C);
+  YAT_REQUIRE(aligned16(a), YAT_ERR_BAD_ARG, "yat_colsum_bf16_static: the matrix must be 16-byte aligned");
+  const int nvec = C / 8, splits = colsum_splits(rows, C);
+  YAT_REQUIRE((int64_t)splits * C <= kColsumStaticFloats, YAT_ERR_UNSUPPORTED,
+              "yat_colsum_bf16_static: rows=%lld C=%d needs %lld B of scratch, the built-in array holds %lld B; use "
+              "yat_colsum_bf16 with a caller-owned workspace", (long long)rows, C,
+              (long long)((int64_t)splits * C * sizeof(float)), (long long)(kColsumStaticFloats * sizeof(float)));
+  float* scratch = nullptr;
+  int rc = colsum_static_ptr(&scratch);
+  if (rc != YAT_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int rows_per_split = (int)((rows + splits - 1) / splits);
+  colsum_kernel<<<dim3((nvec + 31) / 32, splits), kThreads, 0, st>>>((const uint4*)a, rows, nvec, rows_per_split, scratch);
+  rc = check_launch("colsum (static scratch)");
+  if (rc != YAT_OK) return rc;
+  colsum_finish_kernel<<<(unsigned)((C + 31) / 32), 256, 0, st>>>(scratch, splits, C, (__nv_bfloat16*)out);
+  return check_launch("colsum_finish (static scratch)");
+}
+
 extern "C" int64_t yat_block_workspace_bytes(int B, int N, int C) {
   const int a = yat::split_count(N), b = yat::ln_bwd_splits(B, N, C);
   return (int64_t)2 * (a > b ? a : b) * B * C * (int64_t)sizeof(float);
