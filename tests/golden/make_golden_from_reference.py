@@ -400,6 +400,83 @@ def run_cache_record(path, seed=23):
             "buckets": {k: [(lat, emb) for lat, emb in v] for k, v in sampler.buckets.items()}}
 
 
+# ---- the legacy one-file-per-item cache (row A14 "legacy", row A9 extract_features_sana.find_closest_ratio) --------------
+def run_legacy_cache(out_tar, seed=29):
+    """Writes cache/<idx>.npy items with the reference's own writer lines, executed from source in a scratch directory:
+      utils/extract_features_sana.py  find_closest_ratio (:52-63) + cache_latents_embeddings (:65-88)  -> items 0, 1
+      common/cache.py                 CacheLoadFeatures.run, main-process branch (:59-86)               -> items 2, 3
+    (VAE / text encoder / Resize replaced by recorded stand-ins; the tuple layouts, squeezes, the 300-token pad + mask and
+    the torch.save calls are the reference's).  The items travel as one .tar.gz; what they must decode to is returned."""
+    import tarfile
+    import tempfile
+    g = torch.Generator().manual_seed(seed)
+    expect = []
+    cwd = os.getcwd()
+    tmp = tempfile.mkdtemp()
+    os.makedirs(os.path.join(tmp, "cache"))
+    os.chdir(tmp)
+    try:
+        # -- writer 1
+        glb = {"torch": torch, "Resize": lambda size: (lambda img: img), "pipe": None,
+               "accelerator": types.SimpleNamespace(device=torch.device("cpu"))}
+        made = {}
+
+        def extract_latents(img, pipe, accelerator):
+            lat = torch.randn((1, 8, img.shape[-2] // 4, img.shape[-1] // 4), generator=g).to(torch.bfloat16)   # h / 32 of the real image
+            made["latent"] = lat
+            return lat
+
+        def extract_embeddings(caption, pipe, accelerator):
+            emb = [(0.5 * torch.randn((len(caption), 2304), generator=g)).to(torch.bfloat16)]
+            made["emb"] = emb[0]
+            return emb
+
+        glb.update(extract_latents=extract_latents, extract_embeddings=extract_embeddings)
+        code, line1 = extract("utils/extract_features_sana.py", "find_closest_ratio")
+        exec(code, glb)
+        code, _ = extract("utils/extract_features_sana.py", "cache_latents_embeddings")
+        exec(code, glb)
+        ratios = sorted({h / w for h in range(256, 2049, 64) for w in range(256, 2049, 64)}) + [0.25, 4.0, 0.1, 9.0, 0.97, 1.035]
+        keys_extract = [glb["find_closest_ratio"](r, ASPECT_RATIO_1024_BIN) for r in ratios]
+        for idx, (hh, ww, cap) in enumerate([(1024, 1024, "a cat"), (704, 1408, "two dogs on a hill")]):
+            # the image is only measured (h / w) and handed to the stand-ins: a [1, 3, h/8, w/8] tensor keeps the ratio
+            img = torch.zeros((1, 3, hh // 8, ww // 8))
+            glb["cache_latents_embeddings"](img, cap, idx, ASPECT_RATIO_1024_BIN, 0)
+            key = glb["find_closest_ratio"](hh / ww, ASPECT_RATIO_1024_BIN)
+            expect.append({"ratio": key, "latent": made["latent"][0].clone(), "emb": made["emb"].clone()})
+        # -- writer 2
+        code, line2 = extract("common/cache.py", "run", cls="CacheLoadFeatures")
+        glb2 = {"torch": torch, "tqdm": types.SimpleNamespace(tqdm=lambda it, **kw: it)}
+        exec(code, glb2)
+        items = []
+        for key, L in (("1.0", 7), ("0.5", 3)):
+            H, W = ASPECT_RATIO_1024_BIN[key]
+            lat = torch.randn((1, 8, int(H) // 32, int(W) // 32), generator=g).to(torch.bfloat16)
+            rows = [torch.randn((1, 2304), generator=g) for _ in range(L)]          # a batch-of-1 collate of L token rows
+            items.append([(key, lat, rows)])
+            expect.append({"ratio": key, "latent": lat[0].clone(), "emb": torch.cat(rows).clone()})
+
+        class Shifted:                       # the loop writes cache/<cache_idx>.npy from 0: move them behind writer 1's
+            pass
+        trainer = types.SimpleNamespace(
+            model=types.SimpleNamespace(cpu=lambda: None), data_extractor_iter=iter(items),
+            params=types.SimpleNamespace(cache_size=2),
+            accelerator=types.SimpleNamespace(is_main_process=True, num_processes=1, process_index=0))
+        os.rename("cache", "cache_w1")
+        os.makedirs("cache")
+        glb2["run"](None, trainer)
+        for i in range(2):
+            os.rename(f"cache/{i}.npy", f"cache_w1/{i + 2}.npy")
+        os.rmdir("cache")
+        os.rename("cache_w1", "cache")
+        with tarfile.open(out_tar, "w:gz") as tar:
+            for i in range(4):
+                tar.add(f"cache/{i}.npy", arcname=f"cache/{i}.npy")
+    finally:
+        os.chdir(cwd)
+    return {"lines": (line1, line2), "expect": expect, "ratios": ratios, "keys_extract": keys_extract}
+
+
 def main():
     meta = {"generated_by": "tests/golden/make_golden_from_reference.py", "torch": torch.__version__,
             "reference_functions": {}}
@@ -414,6 +491,13 @@ def main():
     rec = run_cache_record(os.path.join(HERE, "reference_shard.tar"))
     meta["reference_functions"]["common/features_extractor.py::tensor_to_bytes"] = rec.pop("line")
     torch.save(rec, os.path.join(HERE, "reference_shard_decoded.pt"))
+
+    # ---- the legacy per-item cache (row A14) + the extractor's bucket function (row A9)
+    leg = run_legacy_cache(os.path.join(HERE, "reference_legacy_cache.tar.gz"))
+    meta["reference_functions"]["utils/extract_features_sana.py::find_closest_ratio"] = leg["lines"][0]
+    meta["reference_functions"]["common/cache.py::CacheLoadFeatures.run"] = leg["lines"][1]
+    meta["buckets_extract_features"] = {"ratios": leg["ratios"], "keys": leg["keys_extract"]}
+    torch.save({"expect": leg["expect"]}, os.path.join(HERE, "reference_legacy_cache_decoded.pt"))
 
     # ---- the step loop (row A13)
     loop = run_trainer_loop()

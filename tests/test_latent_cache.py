@@ -199,3 +199,47 @@ def test_writer_produces_the_member_layout_of_the_reference_shard(tmp_path):
             else:
                 import io
                 assert torch.equal(torch.load(io.BytesIO(da)), torch.load(io.BytesIO(db)))
+
+
+def test_legacy_per_item_cache_written_by_the_reference_lines(tmp_path):
+    """cache/<idx>.npy items written by the reference's own writer code executed from source (utils/extract_features_sana.py
+    cache_latents_embeddings -> items 0, 1; common/cache.py CacheLoadFeatures.run -> items 2, 3: text zero-padded to 300 with
+    a float mask) decode to the recorded (bucket key, latent, real tokens), and convert to slabs holding the same bytes."""
+    import tarfile
+    from yat_b200.latent_cache import convert_legacy_cache, read_legacy_cache_record
+    ref = torch.load(os.path.join(GOLD, "reference_legacy_cache_decoded.pt"))["expect"]
+    with tarfile.open(os.path.join(GOLD, "reference_legacy_cache.tar.gz")) as tar:
+        tar.extractall(tmp_path, filter="data")
+    cache = os.path.join(tmp_path, "cache")
+    for i, e in enumerate(ref):
+        ratio, latent, emb = read_legacy_cache_record(os.path.join(cache, f"{i}.npy"))
+        assert str(ratio) == e["ratio"]
+        assert latent.shape == e["latent"].shape and torch.equal(latent, e["latent"])
+        assert emb.shape == e["emb"].shape and torch.equal(emb.float(), e["emb"].float())
+    # the 4-tuple the legacy reader unpacks (common/bucket_sampler_cache.py:102): (ratio, image, latent, embedding)
+    torch.save(("1.0", None, ref[0]["latent"][None], ref[0]["emb"]), os.path.join(tmp_path, "four.npy"))
+    r4 = read_legacy_cache_record(os.path.join(tmp_path, "four.npy"))
+    assert r4[0] == "1.0" and torch.equal(r4[1], ref[0]["latent"]) and torch.equal(r4[2], ref[0]["emb"])
+    with pytest.raises(ValueError):
+        torch.save({"not": "a tuple"}, os.path.join(tmp_path, "bad.npy"))
+        read_legacy_cache_record(os.path.join(tmp_path, "bad.npy"))
+    index = convert_legacy_cache(cache, os.path.join(tmp_path, "slabs"), ASPECT_RATIO_1024_BIN)
+    rd = SlabReader(os.path.join(tmp_path, "slabs"))
+    assert sum(b["n"] for b in index["buckets"].values()) == len(ref)
+    for key in rd.keys():
+        mine = [e for e in ref if e["ratio"] == key]
+        b = rd.batch(key, 0, len(mine), pin=False)
+        assert torch.equal(b.vae_features, torch.stack([e["latent"] for e in mine]))
+        assert all(torch.equal(x, e["emb"].to(torch.bfloat16)) for x, e in zip(b.embeddings, mine))
+
+
+def test_extractor_bucket_function_matches_the_trainer_rule():
+    """utils/extract_features_sana.py:52-63 find_closest_ratio (executed from the reference source on 581 ratios) picks the
+    keys the product's yat_bucket_assign picks: the same first-minimum rule as common/trainer.py:109-120."""
+    import json
+    from yat_b200.bucket_sampler import find_closest_ratio
+    meta = json.load(open(os.path.join(GOLD, "reference_golden.json")))["buckets_extract_features"]
+    assert len(meta["ratios"]) > 500
+    for r, k in zip(meta["ratios"], meta["keys"]):
+        assert find_closest_ratio(ASPECT_RATIO_1024_BIN, r) == k
+        assert buckets.find_closest_ratio_trainer(ASPECT_RATIO_1024_BIN, r) == k

@@ -10,6 +10,8 @@ one WebDataset tar member group per sample,
 
 decoded by ``torch.load`` per sample on the host (pickle) and regrouped into per-ratio deques.
 ``read_reference_shard`` / ``write_reference_shard`` speak that format with ``tarfile`` (no webdataset).
+``read_legacy_cache_record`` / ``convert_legacy_cache`` read the older one-file-per-item cache (common/cache.py,
+utils/extract_features_sana.py:84-88).
 
 B200 layout (``SlabWriter`` / ``SlabReader``): one directory per cache, per bucket key three raw files
 
@@ -154,6 +156,50 @@ def convert_shards(shard_paths, root, aspect_ratios, latent_div=32):
     for path in shard_paths:
         for rec in read_reference_shard(path):
             w.add(rec["ratio"], rec["latent.pt"], rec["emb.pt"])
+    return w.close()
+
+
+# ------------------------------------------------------------------------------------------------
+# legacy per-item cache (cache/<idx>.npy)
+# ------------------------------------------------------------------------------------------------
+def read_legacy_cache_record(path):
+    """One item of the reference's older per-file cache -> (ratio, latent [C, h, w], emb [L, E]).  Three writers exist
+    upstream, all ``torch.save`` of a tuple (despite the .npy suffix); the layout is told apart by shape:
+      (ratio, latent, [emb])                utils/extract_features_sana.py:84-88   ratio = table key (str), list of 1 tensor
+      (ratio, latent, (emb_300, mask_300))  common/cache.py:70-85                  text zero-padded to 300 + float mask
+      (ratio, image, latent, emb)           read at common/bucket_sampler_cache.py:102 (image may be None)
+    Leading singleton batch axes are squeezed as the readers do (cache.py:83, bucket_sampler_cache.py:122-125); a padded
+    text comes back trimmed to its mask."""
+    item = torch.load(path, map_location="cpu")
+    if not isinstance(item, (tuple, list)) or len(item) not in (3, 4):
+        raise ValueError(f"{path}: not a legacy cache item (tuple of 3 or 4 expected, got {type(item).__name__})")
+    ratio, latent, emb = (item[0], item[2], item[3]) if len(item) == 4 else item
+    mask = None
+    if isinstance(emb, (tuple, list)) and len(emb) == 2 and torch.is_tensor(emb[1]) and emb[1].dim() == 1 \
+            and torch.is_tensor(emb[0]) and emb[0].dim() == 2 and emb[0].shape[0] == emb[1].shape[0]:
+        emb, mask = emb
+    elif isinstance(emb, (tuple, list)):
+        if len(emb) != 1:
+            raise ValueError(f"{path}: {len(emb)} embeddings in one item")
+        emb = emb[0]
+    while emb.dim() > 2 and emb.shape[0] == 1:
+        emb = emb[0]
+    while latent.dim() > 3 and latent.shape[0] == 1:
+        latent = latent[0]
+    if mask is not None:
+        emb = emb[: int(mask.sum().item())]
+    if emb.dim() != 2 or latent.dim() != 3:
+        raise ValueError(f"{path}: latent {tuple(latent.shape)} / embedding {tuple(emb.shape)} are not [C,h,w] / [L,E]")
+    return ratio, latent, emb
+
+
+def convert_legacy_cache(cache_dir, root, aspect_ratios, latent_div=32):
+    """cache/0.npy, cache/1.npy, ... (index order, as common/bucket_sampler_cache.py:101-102 walks them) -> slabs."""
+    names = sorted((n for n in os.listdir(cache_dir) if n.endswith(".npy") and n[:-4].isdigit()), key=lambda n: int(n[:-4]))
+    w = SlabWriter(root, aspect_ratios, latent_div)
+    for n in names:
+        ratio, latent, emb = read_legacy_cache_record(os.path.join(cache_dir, n))
+        w.add(ratio, latent.to(torch.bfloat16), emb.to(torch.bfloat16))
     return w.close()
 
 
