@@ -75,3 +75,24 @@ def loop_batches(n_micro, batch_size, channels, hw, emb_dim, seed):
             vae_features=torch.randn((batch_size, channels, hw, hw), generator=g).to(torch.bfloat16),
             embeddings=[(0.5 * torch.randn((L, emb_dim), generator=g)).to(torch.bfloat16) for L in lens]))
     return out
+
+
+MODEL_CFG = dict(in_channels=4, out_channels=4, num_attention_heads=2, attention_head_dim=32, num_layers=2,
+                 num_cross_attention_heads=2, cross_attention_head_dim=32, cross_attention_dim=64, caption_channels=16,
+                 sample_size=8)
+
+
+def stub_model(seed, cfg=MODEL_CFG):
+    """The product's SANA model (fp32, CPU) with every block's attn1 / attn2 / ff replaced by the linear stand-ins of
+    block_stubs.py and the op-by-op (torch) block path: what is left is the glue the forward owns."""
+    from yat_b200.sana_transformer import SanaTransformer2DModel
+    torch.manual_seed(seed)
+    model = SanaTransformer2DModel(**cfg)
+    C = cfg["num_attention_heads"] * cfg["attention_head_dim"]
+    g = torch.Generator().manual_seed(seed + 1)
+    w = lambda: torch.randn((C, C), generator=g) * C ** -0.5  # noqa: E731
+    for blk in model.transformer_blocks:
+        blk.attn1, blk.attn2, blk.ff = StubSelfAttn(w()), StubCrossAttn(w(), w()), StubFF(w())
+        blk.block_ops = "torch"
+    model.norm_out.block_ops = "torch"
+    return model.eval()

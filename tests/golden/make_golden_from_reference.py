@@ -477,6 +477,66 @@ def run_legacy_cache(out_tar, seed=29):
     return {"lines": (line1, line2), "expect": expect, "ratios": ratios, "keys_extract": keys_extract}
 
 
+# ---- the model forward around the blocks (row A11, utils/patched_sana_transformer.py:228-350) -----------------------------
+def run_sana_model_forward(seed=51):
+    """PatchedSanaTransformer2DModel.forward executed from the reference file with the product model instance as `self`
+    (same attribute names: patch_embed, time_embed, caption_projection, caption_norm, transformer_blocks, norm_out, proj_out,
+    scale_shift_table, config.patch_size): mask -> additive bias, patchify, block call order and arguments, modulated output
+    norm, unpatchify.  diffusers' PEFT scaling helpers are no-ops here (USE_PEFT_BACKEND False)."""
+    import typing
+    from yat_b200.sana_transformer import Transformer2DModelOutput
+    sys.path.insert(0, HERE)
+    from block_stubs import stub_model
+    code, line = extract("utils/patched_sana_transformer.py", "forward", cls="PatchedSanaTransformer2DModel")
+    glb = {"torch": torch, "Optional": typing.Optional, "Dict": typing.Dict, "Any": typing.Any, "Tuple": typing.Tuple,
+           "Union": typing.Union, "Transformer2DModelOutput": Transformer2DModelOutput, "USE_PEFT_BACKEND": False,
+           "logger": types.SimpleNamespace(warning=lambda *a, **k: None),
+           "scale_lora_layers": lambda *a: None, "unscale_lora_layers": lambda *a: None}
+    exec(code, glb)
+    model = stub_model(seed)
+    model.gradient_checkpointing = False
+    g = torch.Generator().manual_seed(seed + 2)
+    x = torch.randn((3, 4, 8, 6), generator=g)                       # non-square latent grid
+    enc = torch.randn((3, 10, 16), generator=g)
+    t = torch.tensor([999.0, 500.5, 1.0])
+    mask = torch.ones((3, 10), dtype=torch.long)
+    mask[1, 4:] = 0
+    mask[2, 1:] = 0
+    seen = []
+    hook = model.transformer_blocks[0].register_forward_pre_hook(lambda m, a: seen.append(a))
+    with torch.no_grad():
+        out = glb["forward"](model, x, enc, t, encoder_attention_mask=mask)
+        out_nomask = glb["forward"](model, x, enc, t, return_dict=False)
+    hook.remove()
+    a = seen[0]
+    return {"line": line, "seed": seed, "x": x, "enc": enc, "t": t, "mask": mask, "out": out.sample, "out_nomask": out_nomask[0],
+            "block0_hidden": a[0], "block0_enc": a[2], "block0_enc_bias": a[3], "block0_temb": a[4], "block0_hw": (a[5], a[6]),
+            "state_dict": {k: v.clone() for k, v in model.state_dict().items()}}
+
+
+def run_patch_helpers():
+    """unfreeze_sana_blocks / patch_sana_attention_layers (utils/patch_sana_attention_layers.py:117-137) executed from the
+    reference source on the product model: which parameters train, which processors the listed blocks get, what lands in
+    config.modified_blocks."""
+    from yat_b200.attention import AttnProcessor2_0
+    from yat_b200.sana_transformer import SanaTransformer2DModel
+    sys.path.insert(0, HERE)
+    from block_stubs import MODEL_CFG
+    glb = {"AttnProcessor2_0": AttnProcessor2_0, "list": list}
+    code, line = extract("utils/patch_sana_attention_layers.py", "unfreeze_sana_blocks")
+    exec(code, glb)
+    code, _ = extract("utils/patch_sana_attention_layers.py", "patch_sana_attention_layers")
+    exec(code, glb)
+    m = SanaTransformer2DModel(**dict(MODEL_CFG, num_layers=3))
+    m.register_to_config(modified_blocks=[2])
+    glb["unfreeze_sana_blocks"](m, [1])
+    trainable = sorted(n for n, p_ in m.named_parameters() if p_.requires_grad)
+    out = glb["patch_sana_attention_layers"](m, [0, 2])
+    procs = [[type(b.attn1.processor).__name__, type(b.attn2.processor).__name__] for b in m.transformer_blocks]
+    return {"line": line, "trainable": trainable, "processors": procs, "modified_blocks": list(m.config.modified_blocks),
+            "returns_transformer": out is m}
+
+
 def main():
     meta = {"generated_by": "tests/golden/make_golden_from_reference.py", "torch": torch.__version__,
             "reference_functions": {}}
@@ -498,6 +558,16 @@ def main():
     meta["reference_functions"]["common/cache.py::CacheLoadFeatures.run"] = leg["lines"][1]
     meta["buckets_extract_features"] = {"ratios": leg["ratios"], "keys": leg["keys_extract"]}
     torch.save({"expect": leg["expect"]}, os.path.join(HERE, "reference_legacy_cache_decoded.pt"))
+
+    # ---- unfreeze_sana_blocks / patch_sana_attention_layers (row A10 swap-out)
+    ph = run_patch_helpers()
+    meta["reference_functions"]["utils/patch_sana_attention_layers.py::unfreeze_sana_blocks"] = ph.pop("line")
+    meta["patch_helpers"] = ph
+
+    # ---- the model forward around the blocks (row A11)
+    mf = run_sana_model_forward()
+    meta["reference_functions"]["utils/patched_sana_transformer.py::PatchedSanaTransformer2DModel.forward"] = mf.pop("line")
+    torch.save(mf, os.path.join(HERE, "reference_sana_model_forward.pt"))
 
     # ---- the step loop (row A13)
     loop = run_trainer_loop()

@@ -332,3 +332,47 @@ def test_product_step_loop_follows_the_reference_run_loop(cuda):
         moved = (r["params"][k] - start[k]).norm().item()
         assert moved > 0
         assert (v.cpu() - r["params"][k]).norm().item() <= 2e-3 * moved, k
+
+
+# ------------------------------------------------------------------- the model forward around the blocks (row A11)
+def test_model_forward_glue_equals_the_reference_forward():
+    """PatchedSanaTransformer2DModel.forward (utils/patched_sana_transformer.py:228-350) was executed from the reference file
+    with the product model as `self` (blocks on linear stand-ins, fp32, CPU).  The product's own forward on the same weights
+    and inputs: same mask -> bias values, same arguments into block 0, same output, bit for bit, with and without a mask."""
+    import sys
+    sys.path.insert(0, GOLD)
+    from block_stubs import stub_model
+    r = torch.load(os.path.join(GOLD, "reference_sana_model_forward.pt"))
+    model = stub_model(r["seed"])
+    model.load_state_dict(r["state_dict"])
+    seen = []
+    model.transformer_blocks[0].register_forward_pre_hook(lambda m, a: seen.append(a))
+    with torch.no_grad():
+        out = model(r["x"], r["enc"], r["t"], encoder_attention_mask=r["mask"]).sample
+        out_nomask = model(r["x"], r["enc"], r["t"], return_dict=False)[0]
+    a = seen[0]
+    assert torch.equal(a[0], r["block0_hidden"]) and torch.equal(a[2], r["block0_enc"]) and torch.equal(a[4], r["block0_temb"])
+    assert torch.equal(a[3], r["block0_enc_bias"]) and a[3].shape == (3, 1, 10)
+    assert set(a[3].unique().tolist()) == {0.0, -10000.0}
+    assert (a[5], a[6]) == tuple(r["block0_hw"]) == (8, 6)
+    assert out.shape == (3, 4, 8, 6) and torch.equal(out, r["out"])
+    assert torch.equal(out_nomask, r["out_nomask"])          # (the cross-attention stand-in ignores the bias: same values)
+
+
+def test_patch_helpers_equal_the_reference_functions():
+    """unfreeze_sana_blocks / patch_sana_attention_layers of utils/patch_sana_attention_layers.py:117-137, executed from
+    the reference source on the product model, against the product's own two functions."""
+    import sys
+    sys.path.insert(0, GOLD)
+    from block_stubs import MODEL_CFG
+    from yat_b200.sana_transformer import SanaTransformer2DModel, patch_sana_attention_layers, unfreeze_sana_blocks
+    ref = META["patch_helpers"]
+    m = SanaTransformer2DModel(**dict(MODEL_CFG, num_layers=3))
+    m.register_to_config(modified_blocks=[2])
+    unfreeze_sana_blocks(m, [1])
+    assert sorted(n for n, p in m.named_parameters() if p.requires_grad) == ref["trainable"]
+    assert all(n.startswith("transformer_blocks.1.") for n in ref["trainable"]) and len(ref["trainable"]) > 0
+    out = patch_sana_attention_layers(m, [0, 2])
+    assert (out is m) == ref["returns_transformer"]
+    assert [[type(b.attn1.processor).__name__, type(b.attn2.processor).__name__] for b in m.transformer_blocks] == ref["processors"]
+    assert list(m.config.modified_blocks) == ref["modified_blocks"]
