@@ -537,6 +537,54 @@ def run_patch_helpers():
             "returns_transformer": out is m}
 
 
+class TinyBackbone(torch.nn.Module):
+    """Three named blocks (Linear + tanh); REPA taps the output of `blocks.1`."""
+
+    def __init__(self, dim=24, seed=61):
+        super().__init__()
+        torch.manual_seed(seed)
+        self.blocks = torch.nn.ModuleList([torch.nn.Linear(dim, dim) for _ in range(3)])
+        self.config = types.SimpleNamespace(dim=dim)
+
+    def forward(self, x):
+        for b in self.blocks:
+            x = torch.tanh(b(x))
+        return x
+
+
+def run_repa_model(seed=62):
+    """RepaModule / RepaModel (common/repa.py:59-154) executed from the reference source (diffusers' ModelMixin replaced by
+    torch.nn.Module + the two properties calculate_loss reads): the wrapper's parameter names, the projected tokens it
+    stashes on the target module, the base-model output, its no-grad token-mean MSE placeholder, and get_base_model()."""
+    glb = {"torch": torch, "nn": torch.nn}
+    extract_class("common/repa.py", "RepaMLP", glb)
+    extract_class("common/repa.py", "RepaModule", glb)
+
+    class ModelMixin(torch.nn.Module):
+        device = property(lambda self: next(self.parameters()).device)
+        dtype = property(lambda self: next(self.parameters()).dtype)
+
+    glb.update(ModelMixin=ModelMixin, PreTrainedModel=object, RepaConfig=types.SimpleNamespace, os=os, json=json)
+    RepaModel, line = extract_class("common/repa.py", "RepaModel", glb)
+    base = TinyBackbone()
+    torch.manual_seed(seed)
+    cfg = types.SimpleNamespace(target_modules=["blocks.1"], target_shape=16, hidden_shape=[24])
+    wrapped = RepaModel(base, cfg)
+    g = torch.Generator().manual_seed(seed + 1)
+    x = torch.randn((2, 9, 24), generator=g)
+    feats = torch.randn((2, 16), generator=g)
+    with torch.no_grad():
+        y = wrapped(x)
+        zs = wrapped.model.get_submodule("blocks.1").zs.clone()
+        placeholder = wrapped.calculate_loss(feats)
+    sd = {k: v.clone() for k, v in wrapped.state_dict().items()}
+    cleared = wrapped.model.get_submodule("blocks.1").zs is None
+    restored = wrapped.get_base_model()
+    return {"line": line, "x": x, "features": feats, "y": y, "zs": zs, "placeholder_loss": placeholder, "state_dict": sd,
+            "zs_cleared": cleared, "restored_keys": sorted(restored.state_dict().keys()),
+            "restored_is_linear": type(restored.blocks[1]).__name__}
+
+
 def main():
     meta = {"generated_by": "tests/golden/make_golden_from_reference.py", "torch": torch.__version__,
             "reference_functions": {}}
@@ -563,6 +611,11 @@ def main():
     ph = run_patch_helpers()
     meta["reference_functions"]["utils/patch_sana_attention_layers.py::unfreeze_sana_blocks"] = ph.pop("line")
     meta["patch_helpers"] = ph
+
+    # ---- RepaModule / RepaModel wrapper (row A8)
+    rm = run_repa_model()
+    meta["reference_functions"]["common/repa.py::RepaModel"] = rm.pop("line")
+    torch.save(rm, os.path.join(HERE, "reference_repa_model.pt"))
 
     # ---- the model forward around the blocks (row A11)
     mf = run_sana_model_forward()

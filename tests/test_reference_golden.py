@@ -376,3 +376,38 @@ def test_patch_helpers_equal_the_reference_functions():
     assert (out is m) == ref["returns_transformer"]
     assert [[type(b.attn1.processor).__name__, type(b.attn2.processor).__name__] for b in m.transformer_blocks] == ref["processors"]
     assert list(m.config.modified_blocks) == ref["modified_blocks"]
+
+
+# ------------------------------------------------------------------- the REPA wrapper (row A8)
+def test_repa_wrapper_equals_the_reference_classes():
+    """RepaModule / RepaModel of common/repa.py:59-154, executed from the reference source around a three-block backbone:
+    the product wrapper has the same parameter names, returns the same base output, stashes the same projected tokens on
+    the target module, and unwraps to the same base model; the oracle restates the reference's no-grad token-mean MSE
+    placeholder (the product's calculate_loss is the REPA cosine term instead - DESIGN.md)."""
+    import types
+    from oracle import repa as orepa
+    from yat_b200.repa import RepaConfig, RepaModel
+    r = torch.load(os.path.join(GOLD, "reference_repa_model.pt"))
+
+    class TinyBackbone(torch.nn.Module):
+        def __init__(self, dim=24):
+            super().__init__()
+            self.blocks = torch.nn.ModuleList([torch.nn.Linear(dim, dim) for _ in range(3)])
+            self.config = types.SimpleNamespace(dim=dim)
+
+        def forward(self, x):
+            for b in self.blocks:
+                x = torch.tanh(b(x))
+            return x
+
+    wrapped = RepaModel(TinyBackbone(), RepaConfig(target_modules=["blocks.1"], target_shape=16, hidden_shape=[24]))
+    assert list(wrapped.state_dict().keys()) == list(r["state_dict"].keys())
+    wrapped.load_state_dict(r["state_dict"])
+    with torch.no_grad():
+        y = wrapped(r["x"])
+    zs = wrapped.model.get_submodule("blocks.1").zs
+    assert torch.equal(y, r["y"]) and torch.equal(zs, r["zs"])
+    ref_loss = orepa.reference_calculate_loss([zs], r["features"])
+    assert torch.allclose(ref_loss.reshape(-1), r["placeholder_loss"].reshape(-1), rtol=1e-6, atol=0)
+    base = wrapped.get_base_model()
+    assert sorted(base.state_dict().keys()) == r["restored_keys"] and type(base.blocks[1]).__name__ == r["restored_is_linear"]
