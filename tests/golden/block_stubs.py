@@ -96,3 +96,36 @@ def stub_model(seed, cfg=MODEL_CFG):
         blk.block_ops = "torch"
     model.norm_out.block_ops = "torch"
     return model.eval()
+
+
+class StubPixArtBlock(torch.nn.Module):
+    """Stand-in for a PixArt block that takes the reference's keyword call (hidden_states, attention_mask=, encoder_hidden_states=,
+    encoder_attention_mask=, timestep=, ...) and the product's positional one (x, enc, mask, timestep) alike."""
+
+    def __init__(self, w):
+        super().__init__()
+        self.w = w
+
+    def forward(self, hidden_states, *args, **kw):
+        enc = kw["encoder_hidden_states"] if "encoder_hidden_states" in kw else args[0]
+        temb = kw["timestep"] if "timestep" in kw else args[2]
+        D = hidden_states.shape[-1]
+        y = torch.tanh(torch.nn.functional.linear(hidden_states, self.w.to(hidden_states.dtype)))
+        return y + 0.1 * enc.mean(dim=1, keepdim=True) + 0.1 * temb[:, None, :D]
+
+
+PIXART_REPA_CFG = dict(num_attention_heads=2, attention_head_dim=32, in_channels=4, out_channels=8, num_layers=3,
+                       cross_attention_dim=64, caption_channels=16, sample_size=8, patch_size=2, interpolation_scale=1,
+                       repa_depth=1, repa_encoder_hidden_size=24, repa_projector_dim=40)
+
+
+def stub_pixart_repa_model(seed, cfg=PIXART_REPA_CFG):
+    from yat_b200.pixart_transformer import REPAPixArtTransformerModel
+    torch.manual_seed(seed)
+    model = REPAPixArtTransformerModel(**cfg)
+    D = cfg["num_attention_heads"] * cfg["attention_head_dim"]
+    g = torch.Generator().manual_seed(seed + 1)
+    model.transformer_blocks = torch.nn.ModuleList(
+        [StubPixArtBlock(torch.randn((D, D), generator=g) * D ** -0.5) for _ in range(cfg["num_layers"])])
+    model.set_block_ops("torch")
+    return model.eval()

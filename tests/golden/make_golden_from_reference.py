@@ -585,6 +585,46 @@ def run_repa_model(seed=62):
             "restored_is_linear": type(restored.blocks[1]).__name__}
 
 
+def run_pixart_repa(seed=71):
+    """utils/patch_pixart_sigma_transformer.py: ThreeLayerMLP (:10-22, class executed from source) and
+    REPAPixArtTransformerModel.forward (:88-198, executed from source on a namespace holding the product model's own pos_embed /
+    adaln_single / caption_projection / norm_out / proj_out / repa_mlps and stand-in blocks): where the REPA projection is taken
+    (after block index repa_depth), what it is, and the forward's output."""
+    import typing
+    sys.path.insert(0, HERE)
+    from block_stubs import PIXART_REPA_CFG, stub_pixart_repa_model
+    from yat_b200.sana_transformer import Transformer2DModelOutput
+    glb = {"torch": torch, "nn": torch.nn}
+    MLP, line = extract_class("utils/patch_pixart_sigma_transformer.py", "ThreeLayerMLP", glb)
+    torch.manual_seed(seed)
+    mlp = MLP(20, 28, 12)
+    g = torch.Generator().manual_seed(seed + 5)
+    mx = torch.randn((7, 20), generator=g)
+    out = {"line": line, "mlp_state": mlp.state_dict(), "mlp_x": mx, "mlp_y": mlp(mx).detach(), "mlp_ctor": [20, 28, 12]}
+
+    code, _ = extract("utils/patch_pixart_sigma_transformer.py", "forward", cls="REPAPixArtTransformerModel")
+    glb = {"torch": torch, "Optional": typing.Optional, "Dict": typing.Dict, "Any": typing.Any,
+           "Transformer2DModelOutput": Transformer2DModelOutput}
+    exec(code, glb)
+    model = stub_pixart_repa_model(seed)
+    self = types.SimpleNamespace(
+        use_additional_conditions=False, config=model.config, pos_embed=model.pos_embed,
+        adaln_single=lambda t, added, batch_size, hidden_dtype: model.adaln_single(t, batch_size=batch_size, hidden_dtype=hidden_dtype),
+        caption_projection=model.caption_projection, transformer_blocks=model.transformer_blocks, gradient_checkpointing=False,
+        repa_depth=model.repa_depth, repa_mlps=model.repa_mlps, repa_proj=None, scale_shift_table=model.scale_shift_table,
+        norm_out=model.norm_out, proj_out=model.proj_out, out_channels=PIXART_REPA_CFG["out_channels"])
+    x = torch.randn((2, 4, 8, 12), generator=g)
+    enc = torch.randn((2, 9, 16), generator=g)
+    t = torch.tensor([999, 3])
+    mask = torch.ones((2, 9))
+    mask[1, 2:] = 0
+    with torch.no_grad():
+        y = glb["forward"](self, x, enc, t, encoder_attention_mask=mask)
+    out.update(seed=seed, x=x, enc=enc, t=t, mask=mask, out=y.sample, repa_proj=self.repa_proj,
+               state_dict={k: v.clone() for k, v in model.state_dict().items()})
+    return out
+
+
 def main():
     meta = {"generated_by": "tests/golden/make_golden_from_reference.py", "torch": torch.__version__,
             "reference_functions": {}}
@@ -616,6 +656,11 @@ def main():
     rm = run_repa_model()
     meta["reference_functions"]["common/repa.py::RepaModel"] = rm.pop("line")
     torch.save(rm, os.path.join(HERE, "reference_repa_model.pt"))
+
+    # ---- PixArt REPA variant (row A8)
+    pr = run_pixart_repa()
+    meta["reference_functions"]["utils/patch_pixart_sigma_transformer.py::ThreeLayerMLP"] = pr.pop("line")
+    torch.save(pr, os.path.join(HERE, "reference_pixart_repa.pt"))
 
     # ---- the model forward around the blocks (row A11)
     mf = run_sana_model_forward()

@@ -260,3 +260,48 @@ def test_sd35_trains_from_model_config(cuda, tmp_path, monkeypatch, lora):
     assert all(torch.isfinite(l).item() for l in ls)
     now = dict(tr.model.named_parameters())
     assert sum(int(not torch.equal(v, now[n].detach())) for n, v in train.items()) > len(train) // 3
+
+
+def test_pixart_sigma_repa_variant_adds_the_cosine_term(cuda, tmp_path, monkeypatch):
+    """use_repa: the hook builds REPAPixArtTransformerModel (train_pixart_sigma.py:28-32), the projection taken after block
+    `repa_depth` enters the loss as repa_lambda * (-mean cos) against the teacher tokens (oracle/repa.py formula), and the
+    projector trains.  Upstream stops at the stash: the loss term is this build's, as for SANA's RepaModel."""
+    monkeypatch.chdir(tmp_path)
+    from oracle import repa as orepa
+    from train_pixart_sigma import PixartSigmaTrainer
+    from yat_b200.pixart_transformer import PIXART_CONFIGS, REPAPixArtTransformerModel
+    p = _params(2)
+    p.model_config = dict(PIXART_CONFIGS["pixart_tiny"], sample_size=64, repa_depth=1, repa_projector_dim=96,
+                          repa_encoder_hidden_size=768)
+    p.use_repa, p.repa_lambda = True, 0.5
+    tr = PixartSigmaTrainer(p)
+    tr.initialize()
+    assert isinstance(tr.model, REPAPixArtTransformerModel)
+    batch = next(iter(tr.sampler))
+    assert batch.repa_features is not None and batch.vae_features.shape[-1] == 64
+    stash = {}
+    orig = tr.model.calculate_loss
+
+    def spy(features, grid_hw, teacher_hw=(16, 16)):
+        stash["z"], stash["grid"] = tr.model.repa_proj.detach().clone(), grid_hw
+        return orig(features, grid_hw, teacher_hw)
+
+    monkeypatch.setattr(tr.model, "calculate_loss", spy)
+    gen = lambda: torch.Generator().manual_seed(5)  # noqa: E731
+    with torch.no_grad():
+        base = tr.optimize(batch.ratio, batch.vae_features, batch.embeddings, None, gen())
+    total = tr.optimize(batch.ratio, batch.vae_features, batch.embeddings, batch.repa_features, gen())
+    assert stash["grid"] == (32, 32) and stash["z"].shape == (2, 1024, 768)
+    cos = orepa.repa_cosine_loss(stash["z"].to(torch.bfloat16).cpu(), batch.repa_features.cpu(), (32, 32))
+    want = base.float().item() + 0.5 * float(cos)
+    assert abs(total.float().item() - want) <= 2e-2 * abs(want) + 1e-3, (total.item(), want)
+    total.backward()
+    grads = [q.grad for q in tr.model.repa_mlps.parameters()]
+    assert all(g is not None and torch.isfinite(g).all() and g.abs().sum() > 0 for g in grads)
+    assert tr.model.repa_proj is None                                   # cleared after use
+    tr.optimizer.zero_grad(set_to_none=True)
+    before = [q.detach().clone() for q in tr.model.repa_mlps.parameters()]
+    it = iter(tr.sampler)
+    ls = [tr.train_step(next(it)) for _ in range(2)]
+    assert all(torch.isfinite(l).item() for l in ls)
+    assert all(not torch.equal(a, b.detach()) for a, b in zip(before, tr.model.repa_mlps.parameters()))

@@ -411,3 +411,30 @@ def test_repa_wrapper_equals_the_reference_classes():
     assert torch.allclose(ref_loss.reshape(-1), r["placeholder_loss"].reshape(-1), rtol=1e-6, atol=0)
     base = wrapped.get_base_model()
     assert sorted(base.state_dict().keys()) == r["restored_keys"] and type(base.blocks[1]).__name__ == r["restored_is_linear"]
+
+
+# ------------------------------------------------------------------- PixArt REPA variant (row A8)
+def test_pixart_repa_variant_equals_the_reference_forward():
+    """utils/patch_pixart_sigma_transformer.py executed from source: ThreeLayerMLP (same parameter names, same output) and the
+    REPAPixArtTransformerModel forward (projection taken after block index repa_depth; output) against the product's
+    REPAPixArtTransformerModel on the same weights and stand-in blocks - bit for bit (fp32, CPU)."""
+    import sys
+    sys.path.insert(0, GOLD)
+    from block_stubs import stub_pixart_repa_model
+    from yat_b200.pixart_transformer import ThreeLayerMLP
+    r = torch.load(os.path.join(GOLD, "reference_pixart_repa.pt"))
+    mlp = ThreeLayerMLP(*r["mlp_ctor"])
+    assert list(mlp.state_dict().keys()) == list(r["mlp_state"].keys())
+    mlp.load_state_dict(r["mlp_state"])
+    assert torch.equal(mlp(r["mlp_x"]), r["mlp_y"])
+    model = stub_pixart_repa_model(r["seed"])
+    model.load_state_dict(r["state_dict"])
+    with torch.no_grad():
+        out = model(r["x"], encoder_hidden_states=r["enc"], timestep=r["t"], encoder_attention_mask=r["mask"]).sample
+    assert torch.equal(model.repa_proj, r["repa_proj"]) and model.repa_proj.shape == (2, 24, 24)
+    assert torch.equal(out, r["out"])
+    # the tap really is block index repa_depth: moving it changes the projection
+    model.repa_depth = 0
+    with torch.no_grad():
+        model(r["x"], encoder_hidden_states=r["enc"], timestep=r["t"], encoder_attention_mask=r["mask"])
+    assert not torch.equal(model.repa_proj, r["repa_proj"])

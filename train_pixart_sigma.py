@@ -21,7 +21,7 @@ from yat_b200.bucket_sampler import SyntheticBucketSampler
 from yat_b200.embeddings import pad_embeddings
 from yat_b200.loss import EPS, fused_denoise_loss
 from yat_b200.noise import ddpm_noise
-from yat_b200.pixart_transformer import PIXART_CONFIGS, PixArtTransformer2DModel
+from yat_b200.pixart_transformer import PIXART_CONFIGS, PixArtTransformer2DModel, REPAPixArtTransformerModel
 from yat_b200.schedulers import DDPMScheduler
 from yat_b200.trainer import Model
 from yat_b200.training_parameters_reader import TrainingParameters
@@ -40,7 +40,8 @@ class PixartSigmaTrainer(Model):
             cfg = params.model_config or "pixart_sigma_xl_1024"
             cfg = PIXART_CONFIGS[cfg] if isinstance(cfg, str) else cfg
             with torch.device(self.accelerator.device):
-                transformer = PixArtTransformer2DModel(**cfg)
+                # train_pixart_sigma.py:28-32: with use_repa the transformer is the REPA variant (projection head)
+                transformer = REPAPixArtTransformerModel(**cfg) if params.use_repa else PixArtTransformer2DModel(**cfg)
         self.pipe = SimpleNamespace(transformer=transformer, vae=None, text_encoder=None, dtype=torch.bfloat16)
         self.scheduler = DDPMScheduler()                       # PixArt-Sigma: 1000 steps, linear betas 1e-4..0.02
         self.aspect_ratios = ASPECT_RATIO_1024_BIN
@@ -58,7 +59,8 @@ class PixartSigmaTrainer(Model):
         side = getattr(cfg, "sample_size", None) or 1024 // self.vae_scale
         return SyntheticBucketSampler(self.params.batch_size, (self.latent_channels, side, side),
                                       getattr(cfg, "caption_channels", 4096), ratio=1.0,
-                                      seed=1234 + self.process_index, max_len=self.max_text_tokens)
+                                      seed=1234 + self.process_index, max_len=self.max_text_tokens,
+                                      repa_tokens=bool(self.params.use_repa))
 
     def extract_latents(self, images):
         raise NotImplementedError("SDXL-VAE encoding needs the PixArt pipeline weights (out of scope); feed cached latents")
@@ -96,9 +98,15 @@ class PixartSigmaTrainer(Model):
         pred = self.model(nz.x_t, encoder_hidden_states=embeddings, timestep=nz.timesteps,
                           encoder_attention_mask=attention_mask.to(torch.bfloat16)).sample
         # learned-sigma models predict 2C channels; the loss reads the first C (chunk(2, 1)[0], :182)
-        return fused_denoise_loss(pred.to(torch.bfloat16), latents, nz.noise,
+        loss = fused_denoise_loss(pred.to(torch.bfloat16), latents, nz.noise,
                                   gscale=1.0 / self.accelerator.gradient_accumulation_steps, target_mode=EPS,
                                   lowp=True, seed=seed, offset=offset, trust_gscale=self._trust_gscale)
+        base = self.accelerator.unwrap_model(self.model)
+        if self.params.use_repa and repa_tokens is not None and hasattr(base, "calculate_loss"):
+            p = base.config.patch_size
+            grid = (latents.shape[-2] // p, latents.shape[-1] // p)
+            loss = loss + self.params.repa_lambda * base.calculate_loss(repa_tokens.to(device, non_blocking=True), grid)
+        return loss
 
 
 if __name__ == "__main__":

@@ -179,6 +179,9 @@ class PixArtTransformer2DModel(nn.Module):
             if hasattr(m, "block_ops"):
                 m.block_ops = impl
 
+    def _after_block(self, index, hidden_states):
+        """Tap for subclasses (REPAPixArtTransformerModel projects the tokens that leave one block)."""
+
     def forward(self, hidden_states, encoder_hidden_states=None, timestep=None, added_cond_kwargs=None,
                 encoder_attention_mask=None, return_dict=True, **kw):
         if encoder_attention_mask is not None and encoder_attention_mask.ndim == 2:
@@ -190,11 +193,12 @@ class PixArtTransformer2DModel(nn.Module):
         timestep, embedded_timestep = self.adaln_single(timestep, batch_size=B, hidden_dtype=x.dtype)
         enc = self.caption_projection(encoder_hidden_states).view(B, -1, x.shape[-1])
         use_ckpt = torch.is_grad_enabled() and self.gradient_checkpointing
-        for block in self.transformer_blocks:
+        for index, block in enumerate(self.transformer_blocks):
             if use_ckpt:
                 x = checkpoint(block, x, enc, encoder_attention_mask, timestep, use_reentrant=False)
             else:
                 x = block(x, enc, encoder_attention_mask, timestep)
+            self._after_block(index, x)
         shift, scale = (self.scale_shift_table[None] + embedded_timestep[:, None]).chunk(2, dim=1)
         if self.block_ops == "sm100":
             x = ln_modulate(x, scale, shift, self.norm_out.eps)
@@ -204,3 +208,49 @@ class PixArtTransformer2DModel(nn.Module):
         x = x.reshape(B, h, w, p, p, -1).permute(0, 5, 1, 3, 2, 4)          # "nhwpqc->nchpwq"
         out = x.reshape(B, -1, h * p, w * p)
         return Transformer2DModelOutput(sample=out) if return_dict else (out,)
+
+
+class ThreeLayerMLP(nn.Module):
+    """REPA projector of the PixArt variant (utils/patch_pixart_sigma_transformer.py:10-22): Linear-SiLU-Linear-SiLU-Linear,
+    parameters under ``fc.0 / fc.2 / fc.4``."""
+
+    def __init__(self, input_size, projector_size, output_size):
+        super().__init__()
+        self.fc = nn.Sequential(nn.Linear(input_size, projector_size), nn.SiLU(),
+                                nn.Linear(projector_size, projector_size), nn.SiLU(),
+                                nn.Linear(projector_size, output_size))
+
+    def forward(self, x):
+        return self.fc(x)
+
+
+class REPAPixArtTransformerModel(PixArtTransformer2DModel):
+    """PixArt-Sigma with a REPA projection head (utils/patch_pixart_sigma_transformer.py:24-198; arXiv 2410.06940): the
+    tokens that leave block ``repa_depth`` (0-based: the reference compares its block counter AFTER the block ran, :165)
+    go through ``repa_mlps`` and stay on ``self.repa_proj`` [B, T, repa_encoder_hidden_size] until the next forward.
+    Upstream nothing reads ``repa_proj`` (REPA is unfinished there); here ``calculate_loss`` turns it into the
+    cosine alignment with the teacher tokens (``yat_repa_cos``, the same term as ``yat_b200.repa.RepaModel``)."""
+
+    def __init__(self, *args, repa_depth=4, repa_encoder_hidden_size=768, repa_projector_dim=2048, **kwargs):
+        super().__init__(*args, **kwargs)
+        self.repa_depth = repa_depth
+        self.repa_projector_dim = repa_projector_dim
+        self.repa_encoder_hidden_size = repa_encoder_hidden_size
+        self.config.repa_depth, self.config.repa_projector_dim = repa_depth, repa_projector_dim
+        self.config.repa_encoder_hidden_size = repa_encoder_hidden_size
+        self.repa_mlps = ThreeLayerMLP(self.config.cross_attention_dim, repa_projector_dim, repa_encoder_hidden_size)
+        self.repa_proj = None
+
+    def _after_block(self, index, hidden_states):
+        if index == self.repa_depth:
+            N, T, D = hidden_states.shape
+            self.repa_proj = self.repa_mlps(hidden_states.reshape(-1, D)).reshape(N, T, -1)
+
+    def calculate_loss(self, features, grid_hw, teacher_hw=(16, 16)):
+        """-mean cos(avgpool(repa_proj), features); clears the stash (common/repa.py:150-152 does the same)."""
+        from .repa import repa_cosine_loss
+        if self.repa_proj is None:
+            raise RuntimeError("calculate_loss needs a forward pass first (repa_proj is empty)")
+        loss = repa_cosine_loss(self.repa_proj.to(torch.bfloat16), features, grid_hw, teacher_hw)
+        self.repa_proj = None
+        return loss
