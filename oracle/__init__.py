@@ -17,7 +17,9 @@ Pinning status:
     (train_sana.py:163-219), ``SD35Trainer.optimize`` (train_sd35.py:165-194),
     ``PixartSigmaTrainer.optimize`` (train_pixart_sigma.py:151-185), ``PatchedSanaTransformerBlock.forward``
     (utils/patch_sana_attention_layers.py:72-115, linear stand-ins for attn1 / attn2 / ff), the step loop ``Model.run``
-    (common/trainer.py:298-403, a tiny denoiser, accelerate's accumulate / backward restated), the three bucket functions,
+    (common/trainer.py:298-403, a tiny denoiser, accelerate's accumulate / backward restated), ``Model.get_timesteps`` and its
+    list override, ``BucketSampler.__iter__`` (the readiness loop), ``RepaModule`` / ``RepaModel``, the PixArt REPA forward and
+    ``ThreeLayerMLP``, the SANA model forward glue, the cache writers (shard and legacy items), the bucket functions,
     ``RepaMLP``, the YAML reader - and commits what they produce (``tests/golden/reference_*``).
     ``tests/test_reference_golden.py`` holds this oracle (and the product, on the GPU) to those
     vectors: timesteps, pad / mask, x_t bit-exact, losses to 1e-6; ``oracle/step_loop.py`` equals the

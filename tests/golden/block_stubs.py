@@ -129,3 +129,17 @@ def stub_pixart_repa_model(seed, cfg=PIXART_REPA_CFG):
         [StubPixArtBlock(torch.randn((D, D), generator=g) * D ** -0.5) for _ in range(cfg["num_layers"])])
     model.set_block_ops("torch")
     return model.eval()
+
+
+def bucket_stream(seed=81, n=63):
+    """The decoded shard elements both the reference loop and the product accumulator are fed (two shards)."""
+    g = torch.Generator().manual_seed(seed)
+    keys = ["1.0", "0.5", "2.0"]
+    shapes = {"1.0": (4, 4), "0.5": (3, 6), "2.0": (6, 3)}
+    out = []
+    for i in range(n):
+        k = keys[int(torch.randint(0, 3, (1,), generator=g))]
+        L = int(torch.randint(1, 9, (1,), generator=g))
+        out.append({"__key__": f"{i:07d}", "ratio": k, "latent.pt": torch.randn((2,) + shapes[k], generator=g).to(torch.bfloat16),
+                    "emb.pt": torch.randn((L, 8), generator=g).to(torch.bfloat16)})
+    return [out[: n // 2], out[n // 2:]]

@@ -625,6 +625,119 @@ def run_pixart_repa(seed=71):
     return out
 
 
+def run_bucket_sampler_iter(batch_size=4, use_repa=False):
+    """BucketSampler.__iter__ (common/bucket_sampler.py:202-276) executed from the reference source, with its own
+    process_element / add_bucket / get_ratio_from_key / get_local_shard_path / remove_shard and Batch class; webdataset, the
+    download process and accelerate are stand-ins (a shard = a list of decoded elements; one rank).  extract_features is the
+    subclass contract (three values) without encoders: (stack(latents), embeddings, None)."""
+    from collections import deque
+
+    class Done(Exception):
+        pass
+
+    class Queue:
+        def __init__(self):
+            self.items = []
+
+        def get(self):
+            if not self.items:
+                raise Done
+            return self.items.pop(0)
+
+        def put(self, x):
+            self.items.append(x)
+
+    sys.path.insert(0, HERE)
+    from block_stubs import bucket_stream
+    shards = bucket_stream()
+    queues = []
+
+    def make_queue():
+        q = Queue()
+        queues.append(q)
+        return q
+
+    class Dataset:
+        def __init__(self, path, **kw):
+            self.elems = shards[path]
+
+        def shuffle(self, n):
+            return self
+
+        def decode(self, fn):
+            return self
+
+        def __iter__(self):
+            return iter([dict(e) for e in self.elems])
+
+    started = []
+    glb = {"torch": torch, "gc": __import__("gc"), "deque": deque,
+           "mp": types.SimpleNamespace(Queue=make_queue, Process=lambda target, args: types.SimpleNamespace(start=lambda: started.append(args[0]))),
+           "wds": types.SimpleNamespace(WebDataset=Dataset)}
+    Batch, _ = extract_class("common/bucket_sampler.py", "Batch", glb)
+    names = ["__iter__", "process_element", "add_bucket", "get_ratio_from_key", "get_local_shard_path", "remove_shard"]
+    ns = {}
+    line = None
+    for fn in names:
+        code, ln = extract("common/bucket_sampler.py", fn, cls="BucketSampler")
+        exec(code, glb)
+        ns[fn] = glb[fn]
+        line = ln if fn == "__iter__" else line
+    ns["extract_features"] = lambda self, batch, ratio: (torch.stack(batch[0]), batch[1], None)
+    ns["pt_decoder"] = lambda self, k, v: v
+    Sampler = type("RefBucketSampler", (), ns)
+    s = Sampler()
+    s.buckets, s.batch_size, s.use_repa, s.process_index = {}, batch_size, use_repa, 0
+    s.download_shard_proc = None
+    s.accelerator = types.SimpleNamespace(device=torch.device("cpu"), wait_for_everyone=lambda: None, gather=lambda t: t.reshape(1))
+    it = iter(s)
+    # the download process would have queued the shard paths: the first queue made is to_train
+    batches = []
+    try:
+        first = True
+        while True:
+            if first:
+                # run up to the Queue construction, then fill it (generators start lazily: prime with the queue hook)
+                first = False
+                orig = glb["mp"].Queue
+
+                def primed():
+                    q = orig()
+                    if len(queues) == 1:
+                        q.items = [0, 1]
+                    return q
+                glb["mp"].Queue = primed
+            b = next(it)
+            batches.append({"ratio": b.ratio, "vae_features": b.vae_features.clone(), "embeddings": [e.clone() for e in b.embeddings],
+                            "repa_features": b.repa_features})
+    except Done:
+        pass
+    return {"line": line, "batch_size": batch_size, "batches": batches, "removed": queues[1].items,
+            "left": {k: len(v) for k, v in s.buckets.items()}}
+
+
+def run_get_timesteps():
+    """Model.get_timesteps (common/trainer.py:96-101) and the fixed-list override nested in Model.__init__ (:53-62), both from
+    the reference source: global-RNG logit-normal draw -> index -> scheduler.timesteps; random.choice over params.timesteps."""
+    import random
+    tree = ast.parse(open(os.path.join(REF, "common/trainer.py")).read())
+    nested = next(n for n in ast.walk(tree) if isinstance(n, ast.FunctionDef) and n.name == "get_timesteps_from_list")
+    tt, _ = schedule.flow_match_tables(1000, 3.0)
+    self = types.SimpleNamespace(timesteps=[0, 250, 999], accelerator=types.SimpleNamespace(device=torch.device("cpu")),
+                                 scheduler=types.SimpleNamespace(timesteps=tt, config=types.SimpleNamespace(num_train_timesteps=1000)))
+    glb = {"random": random, "self": self, "torch": torch,
+           "compute_density_for_timestep_sampling": compute_density_for_timestep_sampling}
+    exec(compile(ast.fix_missing_locations(ast.Module(body=[nested], type_ignores=[])), "trainer.py", "exec"), glb)
+    random.seed(91)
+    from_list = glb["get_timesteps_from_list"](12)
+    code, line = extract("common/trainer.py", "get_timesteps", cls="Model")
+    exec(code, glb)
+    torch.manual_seed(92)
+    drawn = glb["get_timesteps"](self, 16)
+    return {"line": line, "list": self.timesteps, "shift": 3.0, "random_seed": 91, "from_list": [float(v) for v in from_list],
+            "torch_seed": 92, "drawn": [float(v) for v in drawn]}
+
+
 def main():
     meta = {"generated_by": "tests/golden/make_golden_from_reference.py", "torch": torch.__version__,
             "reference_functions": {}}
@@ -656,6 +769,16 @@ def main():
     rm = run_repa_model()
     meta["reference_functions"]["common/repa.py::RepaModel"] = rm.pop("line")
     torch.save(rm, os.path.join(HERE, "reference_repa_model.pt"))
+
+    # ---- the bucket sampler loop (row A9 readiness rule, Batch)
+    bi = run_bucket_sampler_iter()
+    meta["reference_functions"]["common/bucket_sampler.py::BucketSampler.__iter__"] = bi.pop("line")
+    torch.save(bi, os.path.join(HERE, "reference_bucket_iter.pt"))
+
+    # ---- get_timesteps + the fixed-list override (row A1)
+    gt = run_get_timesteps()
+    meta["reference_functions"]["common/trainer.py::Model.get_timesteps"] = gt.pop("line")
+    meta["get_timesteps"] = gt
 
     # ---- PixArt REPA variant (row A8)
     pr = run_pixart_repa()

@@ -438,3 +438,55 @@ def test_pixart_repa_variant_equals_the_reference_forward():
     with torch.no_grad():
         model(r["x"], encoder_hidden_states=r["enc"], timestep=r["t"], encoder_attention_mask=r["mask"])
     assert not torch.equal(model.repa_proj, r["repa_proj"])
+
+
+# ------------------------------------------------------------------- the bucket sampler loop (row A9)
+def test_bucket_accumulator_yields_the_reference_loop_batches():
+    """BucketSampler.__iter__ (common/bucket_sampler.py:202-276) executed from the reference source over two decoded shards
+    (webdataset / download process / accelerate stood in, one rank): the product's BucketAccumulator, fed the same elements
+    and polled after each one in bucket-creation order, yields the same batches in the same order - ratio key, stacked
+    latents, embedding lists - and keeps the same leftovers."""
+    import sys
+    sys.path.insert(0, GOLD)
+    from block_stubs import bucket_stream
+    from yat_b200.bucket_sampler import BucketAccumulator
+    r = torch.load(os.path.join(GOLD, "reference_bucket_iter.pt"))
+    acc = BucketAccumulator(r["batch_size"])
+    got = []
+    for shard in bucket_stream():
+        for e in shard:
+            acc.add(e["ratio"], e["latent.pt"], e["emb.pt"])
+            for key in acc.ready_keys(list(acc.buckets.keys())):
+                got.append(acc.pop_batch(key))
+    assert len(got) == len(r["batches"]) > 10
+    for b, ref in zip(got, r["batches"]):
+        assert b.ratio == ref["ratio"] and isinstance(b.ratio, float)
+        assert torch.equal(b.vae_features, ref["vae_features"])
+        assert len(b.embeddings) == len(ref["embeddings"]) and all(torch.equal(x, y) for x, y in zip(b.embeddings, ref["embeddings"]))
+        assert b.repa_features is None and ref["repa_features"] is None
+    assert {k: len(v) for k, v in acc.buckets.items()} == r["left"] and sum(r["left"].values()) > 0
+
+
+# ------------------------------------------------------------------- get_timesteps (row A1)
+def test_timestep_draws_equal_the_reference_functions():
+    """Model.get_timesteps (common/trainer.py:96-101) and the fixed-list override (:53-62) executed from the reference
+    source: the oracle's index rule on the same global-RNG draw gives the same timesteps; the product trainer's list
+    override (same `random.choice` order) returns the same values."""
+    import random
+    import types
+    from yat_b200.schedulers import FlowMatchEulerDiscreteScheduler
+    from yat_b200.trainer import Model
+    from yat_b200.training_parameters_reader import TrainingParameters
+    m = META["get_timesteps"]
+    tt, _ = schedule.flow_match_tables(1000, m["shift"])
+    torch.manual_seed(m["torch_seed"])
+    u = torch.sigmoid(torch.normal(mean=0.0, std=1.0, size=(16,)))
+    assert [float(v) for v in tt[sampling.timestep_indices(u, 1000)]] == m["drawn"]
+    p = TrainingParameters()
+    p.timesteps = m["list"]
+    tr = Model(p)
+    tr.scheduler = FlowMatchEulerDiscreteScheduler(shift=m["shift"])
+    tr.accelerator = types.SimpleNamespace(device=torch.device("cpu"))
+    random.seed(m["random_seed"])
+    assert [float(v) for v in tr.get_timesteps(12)] == m["from_list"]
+    assert set(m["from_list"]) <= {float(tt[i]) for i in m["list"]}
