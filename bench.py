@@ -450,6 +450,37 @@ def _standalone_kernels(device, pk):
         del wq, qkv_buf, st_buf, o_buf
     except Exception as e:  # noqa: BLE001 — reported, not hidden
         out["gemm_qkv_own_tcgen05"] = {"error": str(e)[:200]}
+    # cross-attention forward of one SANA-1.6B layer (attn2: 20 heads x 112, 320 keys): own tcgen05 kernel vs the path the
+    # step runs (yat_head_pad x 2 + cuDNN SDPA with the key bias folded into an extra head column).  Not on the training path:
+    # there is no own backward, so the step keeps the library call.
+    try:
+        from yat_b200 import _lib as _L
+        from yat_b200.attention import _sdpa_key_bias_folded
+        xh, xd, xl = 20, 112, 320
+        xq = torch.randn((B, N, xh * xd), device=device).to(torch.bfloat16)
+        xk = torch.randn((B, xl, xh * xd), device=device).to(torch.bfloat16)
+        xv = torch.randn((B, xl, xh * xd), device=device).to(torch.bfloat16)
+        xb = torch.zeros((B, xl), device=device)
+        for b_, n_ in enumerate(torch.randint(20, 301, (B,), generator=torch.Generator().manual_seed(1)).tolist()):
+            xb[b_, n_:] = -10000.0
+        xo = torch.empty_like(xq)
+        xlse = torch.empty((B, xh, N), dtype=torch.float32, device=device)
+        cs = torch.cuda.current_stream().cuda_stream
+        L = _L.lib()
+        ms_o = timeit(lambda: L.yat_xattn_fwd(xq.data_ptr(), xk.data_ptr(), xv.data_ptr(), xb.data_ptr(), B, xh, N, xl, xd,
+                                              xh * xd, xh * xd, xd ** -0.5, xo.data_ptr(), xlse.data_ptr(), cs), iters=30, warm=5)
+        xb4 = xb.view(B, 1, 1, xl).to(torch.bfloat16)
+        with torch.no_grad():
+            ms_l = timeit(lambda: _sdpa_key_bias_folded(xq, xk, xv, xb4, xh, xd), iters=30, warm=5)
+        fl_x = 4.0 * B * xh * N * xl * xd
+        out["xattn_fwd_own_tcgen05"] = {"bound": "tensor", "achieved": fl_x / (ms_o * 1e-3) / 1e12, "peak": pk["bf16_tflops"],
+                                        "unit": "TFLOP/s", "us": ms_o * 1e3, "flops": fl_x, "shape": [B, xh, N, xl, xd],
+                                        "library_path_us": ms_l * 1e3, "vs_library_time": ms_l / ms_o,
+                                        "timing": "stand-alone", "what": "yat_xattn_fwd vs head_pad + cuDNN SDPA (folded key bias)"}
+        out["xattn_fwd_own_tcgen05"]["frac"] = out["xattn_fwd_own_tcgen05"]["achieved"] / pk["bf16_tflops"]
+        del xq, xk, xv, xo, xlse
+    except Exception as e:  # noqa: BLE001 — reported, not hidden
+        out["xattn_fwd_own_tcgen05"] = {"error": str(e)[:200]}
     from yat_b200.linear_attention import _launch_fwd
     ms = timeit(lambda: _launch_fwd(q, k, v, H, "sm100"))      # the C-ABI call (as for the backward below)
     entry("linattn_fwd_sm100", 8 * B * N * C, ms, [B, N, C], flops=4 * 32 * 33 * N * H * B)
