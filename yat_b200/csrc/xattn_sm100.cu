@@ -11,13 +11,17 @@
 // rescaling.  Q, K, V and O stay token-major [B, rows, H*d]: a 4-D tensor map {d, H, rows, B} addresses one head, and the
 // columns d..127 of a 64-wide box come back as zeros (and are clipped on store), so d = 112 costs no padded copies.
 //
-// Work item = (batch, head, 128-query tile); persistent grid, one CTA per SM.  Per item:
-//   producer   Q tile (2 x [128 x 64] SW128 boxes), then the K chunks and the V chunks ([64 keys x 128] each) through a ring
-//   issuer     S[:, 64c..] = Q K_c^T (K-major A and B)  ->  s_full;   O += P_c V_c (A = P_c written by the softmax warps,
-//              B = V_c MN-major straight from its TMA tile), chunk by chunk as P arrives  ->  o_full
+// Work item = (batch, head, 128-query tile); persistent grid, one CTA per SM.  The probabilities never touch shared
+// memory: the softmax threads write P (bf16 pairs) back into the tensor-memory columns of the scores they came from, and
+// P_c V_c reads its A operand from tensor memory.
+//   producer   Q tile (2 x [128 x 64] SW128 boxes); K and V chunks ([64 keys x 128]) through one ring, in the order the issuer
+//              consumes them: K_0.. of the CTA's first item, then per item i and chunk c: V_c(i), K_c(i+1)
+//   issuer     O += P_c V_c (A = P_c in tensor memory, B = V_c MN-major straight from its TMA tile) and, right behind it,
+//              S'[:, 64c..] = Q' K'_c^T of the NEXT item into the score columns pass 2 has just finished with: the next
+//              item's scores are complete when this item's pass 2 ends
 //   softmax    8 warps = 2 per TMEM lane quadrant (thread = query row x half of each chunk's columns): pass 1 row max of
-//              s*c + bias2, pass 2 p = 2^(s*c + bias2 - m) -> bf16 -> swizzled K-major P chunk in shared memory, row sum;
-//              epilogue O / l -> bf16 -> the item's Q buffer -> TMA store; lse = ln sum_j exp(...) for the backward
+//              s*c + bias2, pass 2 p = 2^(s*c + bias2 - m) -> bf16 pairs -> tcgen05.st over the thread's own score columns,
+//              row sum; epilogue O / l -> bf16 -> the item's Q buffer -> TMA store; lse = ln sum_j exp(...) for a backward
 // c = scale * log2(e), bias2 = bias * log2(e) (keys past L: -inf).
 #include "common.cuh"
 #include "sm100.cuh"
@@ -33,8 +37,8 @@ constexpr int kQHalf = kQT * 128;            // [128 rows][64 cols] bf16
 constexpr int kQBytes = 2 * kQHalf;          // 32 KB
 constexpr int kCHalf = kKC * 128;            // [64 keys][64 cols] bf16
 constexpr int kCBytes = 2 * kCHalf;          // 16 KB
-constexpr int kPBytes = kQT * 128;           // [128 rows][64 keys] bf16
-constexpr int kStages = 6;
+constexpr int kStages = 7;
+constexpr int kQBufs = 3;                    // Q(i+1) lands while O(i-1) is still leaving from its own buffer
 constexpr int kSoftWarps = 8, kSoftThreads = 32 * kSoftWarps;
 constexpr int kStoreWarp = 2 + kSoftWarps;
 constexpr int kThreads = 32 * (kStoreWarp + 1);
@@ -42,25 +46,29 @@ constexpr uint32_t kColO = 64 * kMaxChunks;
 constexpr int kTmemCols = 512;
 
 struct XfSmem {
-  uint8_t q[2][kQBytes];                     // 1024-aligned; the O tile leaves from the item's Q buffer
+  uint8_t q[kQBufs][kQBytes];                // 1024-aligned; the O tile leaves from the item's Q buffer
   uint8_t kv[kStages][kCBytes];
-  uint8_t p[2][kPBytes];
   float bias2[2][kMaxChunks * kKC];
   float xm[2][kQT], xl[2][kQT];              // row max / row sum halves exchanged between the two warps of a row
-  uint64_t q_full[2], q_empty[2], kv_full[kStages], kv_empty[kStages], p_ready[2], p_empty[2];
-  uint64_t s_full, s_empty, o_full, o_empty, o_staged;
+  uint64_t q_full[kQBufs], q_empty[kQBufs], kv_full[kStages], kv_empty[kStages], p_ready[kMaxChunks];
+  uint64_t s_full, o_full, o_empty, o_staged;
   uint32_t tmem_base;
 };
 constexpr int kXfSmemBytes = (int)sizeof(XfSmem) + 1024;
 static_assert(kXfSmemBytes <= 232448, "cross-attention forward shared memory exceeds the 227 KB per-CTA limit");
 
 constexpr uint32_t kIdescS = make_idesc_bf16(128, kKC, 0, 0);    // Q K_c^T : A, B K-major
-constexpr uint32_t kIdescPV = make_idesc_bf16(128, 128, 0, 1);   // P_c V_c : A K-major, B MN-major
+constexpr uint32_t kIdescPV = make_idesc_bf16(128, 128, 0, 1);   // P_c V_c : A K-major (tensor memory), B MN-major
 
 __device__ __forceinline__ float ex2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+  float r;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
 }
 
 struct Item { int b, h, q0; };
@@ -87,18 +95,16 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
   const int nK = (d + 15) / 16;                // K steps of the score MMA (columns d.. of Q and K are zero-filled)
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < kQBufs; ++i) {
       mbar_init(smem_u32(&S.q_full[i]), 1);
       mbar_init(smem_u32(&S.q_empty[i]), 1);
-      mbar_init(smem_u32(&S.p_ready[i]), kSoftWarps);
-      mbar_init(smem_u32(&S.p_empty[i]), 1);
     }
     for (int s = 0; s < kStages; ++s) {
       mbar_init(smem_u32(&S.kv_full[s]), 1);
       mbar_init(smem_u32(&S.kv_empty[s]), 1);
     }
+    for (int c = 0; c < kMaxChunks; ++c) mbar_init(smem_u32(&S.p_ready[c]), kSoftWarps);
     mbar_init(smem_u32(&S.s_full), 1);
-    mbar_init(smem_u32(&S.s_empty), kSoftWarps);
     mbar_init(smem_u32(&S.o_full), 1);
     mbar_init(smem_u32(&S.o_empty), kSoftWarps);
     mbar_init(smem_u32(&S.o_staged), kSoftWarps);
@@ -119,65 +125,106 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
     // ======================= TMA producer =======================
     if (lane == 0) {
       uint32_t it = 0, qi = 0;
-      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi) {
-        const Item w = decode(item, n_qt, H);
-        const uint32_t qb = qi & 1;
-        mbar_wait(smem_u32(&S.q_empty[qb]), ((qi >> 1) & 1) ^ 1);
+      auto load_q = [&](const Item& w, uint32_t n) {
+        const uint32_t qb = n % kQBufs;
+        mbar_wait(smem_u32(&S.q_empty[qb]), ((n / kQBufs) & 1) ^ 1);
         const uint32_t qf = smem_u32(&S.q_full[qb]);
         mbar_arrive_expect_tx(qf, kQBytes);
         tma_load_4d(smem_u32(&S.q[qb][0]), &tm_q, qf, 0, w.h, w.q0, w.b);
         tma_load_4d(smem_u32(&S.q[qb][kQHalf]), &tm_q, qf, 64, w.h, w.q0, w.b);
-        for (int j = 0; j < 2 * nC; ++j, ++it) {
-          const CUtensorMap* tm = j < nC ? &tm_k : &tm_v;
-          const int c = j < nC ? j : j - nC;
-          const uint32_t s = it % kStages, ph = (it / kStages) & 1;
-          mbar_wait(smem_u32(&S.kv_empty[s]), ph ^ 1);
-          const uint32_t full = smem_u32(&S.kv_full[s]);
-          mbar_arrive_expect_tx(full, kCBytes);
-          tma_load_4d(smem_u32(&S.kv[s][0]), tm, full, 0, w.h, c * kKC, w.b);
-          tma_load_4d(smem_u32(&S.kv[s][kCHalf]), tm, full, 64, w.h, c * kKC, w.b);
+      };
+      auto load_chunk = [&](const CUtensorMap* tm, const Item& w, int c) {
+        const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+        TRACE(3, 30);
+        mbar_wait(smem_u32(&S.kv_empty[s]), ph ^ 1);
+        TRACE(3, 31);
+        const uint32_t full = smem_u32(&S.kv_full[s]);
+        mbar_arrive_expect_tx(full, kCBytes);
+        tma_load_4d(smem_u32(&S.kv[s][0]), tm, full, 0, w.h, c * kKC, w.b);
+        tma_load_4d(smem_u32(&S.kv[s][kCHalf]), tm, full, 64, w.h, c * kKC, w.b);
+        TRACE(3, 32);
+        ++it;
+      };
+      if ((int)blockIdx.x < n_items) {
+        const Item w0 = decode(blockIdx.x, n_qt, H);
+        load_q(w0, 0);
+        for (int c = 0; c < nC; ++c) load_chunk(&tm_k, w0, c);
+      }
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi) {
+        const Item w = decode(item, n_qt, H);
+        const bool has_next = item + (int)gridDim.x < n_items;
+        Item wn = w;
+        if (has_next) {
+          wn = decode(item + gridDim.x, n_qt, H);
+          load_q(wn, qi + 1);
+        }
+        for (int c = 0; c < nC; ++c) {
+          load_chunk(&tm_v, w, c);
+          if (has_next) load_chunk(&tm_k, wn, c);
         }
       }
     }
   } else if (warp == 1) {
     // ======================= tcgen05 issuer =======================
-    if (lane == 0) {
-      uint32_t it = 0, qi = 0, p_use = 0;
-      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi) {
-        const uint32_t qb = qi & 1;
-        mbar_wait(smem_u32(&S.q_full[qb]), (qi >> 1) & 1);
-        mbar_wait(smem_u32(&S.s_empty), (qi & 1) ^ 1);       // the previous item's scores have been read
+    if (lane == 0 && (int)blockIdx.x < n_items) {
+      uint32_t it = 0, qi = 0;
+      // scores of chunk c of the item in Q buffer qb: K-major SW128 operands (8-row groups 1 KB apart, K step of 16 = 32 B
+      // inside the 128 B row, 64-column halves)
+      auto score_mma = [&](uint32_t qb, int c) {
+        const uint32_t s = it % kStages;
+        mbar_wait(smem_u32(&S.kv_full[s]), (it / kStages) & 1);
         tc_fence_after();
-        // K-major SW128 operands: 8-row groups 1 KB apart, K step of 16 = 32 B inside the 128 B row, 64-column halves
         const uint64_t qa0 = make_smem_desc(smem_u32(&S.q[qb][0]), 16, 1024, kLayoutSw128);
-        for (int c = 0; c < nC; ++c, ++it) {
-          const uint32_t s = it % kStages;
-          mbar_wait(smem_u32(&S.kv_full[s]), (it / kStages) & 1);
-          tc_fence_after();
-          const uint64_t kb0 = make_smem_desc(smem_u32(&S.kv[s][0]), 16, 1024, kLayoutSw128);
-          for (int ks = 0; ks < nK; ++ks)
+        const uint64_t kb0 = make_smem_desc(smem_u32(&S.kv[s][0]), 16, 1024, kLayoutSw128);
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          if (ks < nK)
             umma_bf16(tmem + c * kKC, qa0 + (((ks >> 2) * kQHalf + (ks & 3) * 32) >> 4),
                       kb0 + (((ks >> 2) * kCHalf + (ks & 3) * 32) >> 4), kIdescS, ks != 0);
-          tc_commit(smem_u32(&S.kv_empty[s]));
-        }
-        tc_commit(smem_u32(&S.s_full));
-        for (int c = 0; c < nC; ++c, ++it, ++p_use) {
-          const uint32_t s = it % kStages, pb = p_use & 1;
-          mbar_wait(smem_u32(&S.kv_full[s]), (it / kStages) & 1);
-          mbar_wait(smem_u32(&S.p_ready[pb]), (p_use >> 1) & 1);
-          if (c == 0) mbar_wait(smem_u32(&S.o_empty), (qi & 1) ^ 1);   // the previous item's O has left TMEM
+        tc_commit(smem_u32(&S.kv_empty[s]));
+        ++it;
+      };
+      mbar_wait(smem_u32(&S.q_full[0]), 0);
+      for (int c = 0; c < nC; ++c) score_mma(0, c);
+      tc_commit(smem_u32(&S.s_full));
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi) {
+        const bool has_next = item + (int)gridDim.x < n_items;
+#ifdef YAT_BWD_PROBE
+        long long t_v = 0, t_p = 0, t_pv = 0, t_s = 0;   // cycles: waiting for V, for P, issuing P V, issuing the next scores
+#define XT(acc, ...) do { const long long t0_ = clock64(); __VA_ARGS__; acc += clock64() - t0_; } while (0)
+#else
+#define XT(acc, ...) do { __VA_ARGS__; } while (0)
+#endif
+        for (int c = 0; c < nC; ++c) {
+          const uint32_t s = it % kStages;
+          XT(t_v, mbar_wait(smem_u32(&S.kv_full[s]), (it / kStages) & 1));
+          XT(t_p, mbar_wait(smem_u32(&S.p_ready[c]), qi & 1);                  // every softmax warp has written P_c over S_c
+             if (c == 0) mbar_wait(smem_u32(&S.o_empty), (qi & 1) ^ 1));      // the previous item's O has left TMEM
           tc_fence_after();
-          const uint64_t pa0 = make_smem_desc(smem_u32(&S.p[pb][0]), 16, 1024, kLayoutSw128);
           // V_c as the B operand, MN-major SW128: LBO = stride between the two 64-column halves, SBO = 8-key group (1 KB),
-          // K step of 16 keys = 2 KB
+          // K step of 16 keys = 2 KB.  A = P_c in tensor memory: keys 0..31 of the chunk as bf16 pairs in columns
+          // [64c, 64c+16), keys 32..63 in [64c+32, 64c+48) (each softmax thread wrote over its own score columns)
           const uint64_t vb0 = make_smem_desc(smem_u32(&S.kv[s][0]), kCHalf, 1024, kLayoutSw128);
+          auto pv_mma = [&]() {
 #pragma unroll
-          for (int ks = 0; ks < kKC / 16; ++ks)
-            umma_bf16(tmem + kColO, pa0 + ((ks * 32) >> 4), vb0 + ((ks * 2048) >> 4), kIdescPV, (c | ks) != 0);
-          tc_commit(smem_u32(&S.kv_empty[s]));
-          tc_commit(smem_u32(&S.p_empty[pb]));
+            for (int ks = 0; ks < kKC / 16; ++ks)
+              umma_bf16_ts(tmem + kColO, tmem + c * kKC + (ks >> 1) * 32 + (ks & 1) * 8, vb0 + ((ks * 2048) >> 4), kIdescPV,
+                           (c | ks) != 0);
+            tc_commit(smem_u32(&S.kv_empty[s]));
+            ++it;
+            if (c == nC - 1) tc_commit(smem_u32(&S.o_full));
+          };
+          XT(t_pv, pv_mma());
+          if (has_next) {
+            XT(t_s,
+            if (c == 0) mbar_wait(smem_u32(&S.q_full[(qi + 1) % kQBufs]), ((qi + 1) / kQBufs) & 1);
+            score_mma((qi + 1) % kQBufs, c));   // in order behind P_c V_c on the tensor pipe: the columns of chunk c are free
+          }
         }
-        tc_commit(smem_u32(&S.o_full));
+#ifdef YAT_BWD_PROBE
+        TRACE(1, 1000 + (int)(t_v >> 4)); TRACE(1, 2000 + (int)(t_p >> 4)); TRACE(1, 3000 + (int)(t_pv >> 4)); TRACE(1, 4000 + (int)(t_s >> 4));
+#endif
+        if (has_next) tc_commit(smem_u32(&S.s_full));
       }
     }
   } else if (warp == kStoreWarp) {
@@ -186,7 +233,7 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
       uint32_t qi = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi) {
         const Item w = decode(item, n_qt, H);
-        const uint32_t qb = qi & 1;
+        const uint32_t qb = qi % kQBufs;
         mbar_wait(smem_u32(&S.o_staged), qi & 1);
         tma_store_4d(&tm_o, smem_u32(&S.q[qb][0]), 0, w.h, w.q0, w.b);
         if (d > 64) tma_store_4d(&tm_o, smem_u32(&S.q[qb][kQHalf]), 64, w.h, w.q0, w.b);
@@ -203,23 +250,34 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
     const int quad = warp & 3;                    // TMEM lane quadrant this warp may access
     const int row = quad * 32 + lane;             // query row in the tile (TMEM lane)
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    const uint32_t s_addr = tmem + lane_base + wg * 32;   // this thread's 32 score columns of chunk 0 (P goes to the first 16)
     const f2 cs2 = bc2(scale_log2);
-    uint32_t qi = 0, p_use = 0;
+    constexpr float kLog2e = 1.4426950408889634f;
+    uint32_t qi = 0;
+    if ((int)blockIdx.x < n_items) {
+      const Item w0 = decode(blockIdx.x, n_qt, H);
+      for (int j = te; j < nC * kKC; j += kSoftThreads)
+        S.bias2[0][j] = j < L ? (bias ? __ldg(bias + (int64_t)w0.b * L + j) * kLog2e : 0.f) : -INFINITY;
+      named_bar_sync(1, kSoftThreads);
+    }
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi) {
       const Item w = decode(item, n_qt, H);
-      const uint32_t qb = qi & 1;
-      float* bs = S.bias2[qi & 1];
-      for (int j = te; j < nC * kKC; j += kSoftThreads)
-        bs[j] = j < L ? (bias ? __ldg(bias + (int64_t)w.b * L + j) * 1.4426950408889634f : 0.f) : -INFINITY;
-      named_bar_sync(1, kSoftThreads);
+      const bool has_next = item + (int)gridDim.x < n_items;
+      const uint32_t qb = qi % kQBufs;
+      const float* bs = S.bias2[qi & 1];
+      float nb0 = 0.f, nb1 = 0.f;                 // the next item's bias row: in flight during pass 1
+      if (has_next && bias != nullptr) {
+        const float* bn = bias + (int64_t)decode(item + gridDim.x, n_qt, H).b * L;
+        if (te < L) nb0 = __ldg(bn + te);
+        if (te + kSoftThreads < L) nb1 = __ldg(bn + te + kSoftThreads);
+      }
+      if (te == 0) TRACE(0, 10);
       mbar_wait(smem_u32(&S.s_full), qi & 1);
       tc_fence_after();
-      // ---- pass 1: row max of s * c + bias2 over this thread's half of every chunk
+      if (te == 0) TRACE(0, 11);
+      // ---- pass 1: row max of s * c + bias2 over this thread's half of every chunk (the load of chunk c+1 is in flight)
       float mx = -INFINITY;
-      for (int c = 0; c < nC; ++c) {
-        uint32_t r[32];
-        tmem_ld32(tmem + lane_base + c * kKC + wg * 32, r);
-        tmem_ld_wait();
+      auto max_chunk = [&](const uint32_t (&r)[32], int c) {
         const float4* b4 = reinterpret_cast<const float4*>(bs + c * kKC + wg * 32);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -227,76 +285,105 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
           float a0, a1, a2, a3;
           un2(fma2(mk2(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1])), cs2, mk2(bb.x, bb.y)), a0, a1);
           un2(fma2(mk2(__uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3])), cs2, mk2(bb.z, bb.w)), a2, a3);
-          mx = fmaxf(fmaxf(mx, fmaxf(a0, a1)), fmaxf(a2, a3));
+          mx = max3(max3(mx, a0, a1), a2, a3);
+        }
+      };
+      {
+        uint32_t ra[32], rb[32];
+        tmem_ld32(s_addr, ra);
+        for (int c = 0; c < nC; c += 2) {
+          tmem_ld_wait();
+          if (c + 1 < nC) tmem_ld32(s_addr + (c + 1) * kKC, rb);
+          max_chunk(ra, c);
+          if (c + 1 < nC) {
+            tmem_ld_wait();
+            if (c + 2 < nC) tmem_ld32(s_addr + (c + 2) * kKC, ra);
+            max_chunk(rb, c + 1);
+          }
         }
       }
+      if (te == 0) TRACE(0, 12);
       S.xm[wg][row] = mx;
+      if (has_next) {      // next item's bias2 (that buffer was last read in the previous item's pass 2: two barriers ago)
+        float* bn = S.bias2[(qi + 1) & 1];
+        if (te < nC * kKC) bn[te] = te < L ? nb0 * kLog2e : -INFINITY;
+        if (te + kSoftThreads < nC * kKC) bn[te + kSoftThreads] = te + kSoftThreads < L ? nb1 * kLog2e : -INFINITY;
+      }
       named_bar_sync(1, kSoftThreads);
+      if (te == 0) TRACE(0, 13);
       mx = fmaxf(mx, S.xm[wg ^ 1][row]);
-      // ---- pass 2: p = 2^(s c + bias2 - m) -> bf16 P chunk (K-major SW128: row = 128 B, 16 B chunks XOR-swizzled)
+      // ---- pass 2: p = 2^(s c + bias2 - m) -> bf16 pairs -> back into the first 16 of this thread's 32 score columns
       const f2 nm = bc2(-mx);
       float sum = 0.f;
-      for (int c = 0; c < nC; ++c, ++p_use) {
-        const uint32_t pb = p_use & 1;
-        uint32_t r[32];
-        tmem_ld32(tmem + lane_base + c * kKC + wg * 32, r);
-        mbar_wait(smem_u32(&S.p_empty[pb]), ((p_use >> 1) & 1) ^ 1);
-        tmem_ld_wait();
+      auto exp_chunk = [&](const uint32_t (&r)[32], int c) {
         const float4* b4 = reinterpret_cast<const float4*>(bs + c * kKC + wg * 32);
-        uint8_t* prow = &S.p[pb][row * 128];
+        uint32_t pk[16];
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          uint32_t wv[4];
-#pragma unroll
-          for (int jj = 0; jj < 2; ++jj) {
-            const int j = 2 * g + jj;
-            const float4 bb = b4[j];
-            float a0, a1, a2, a3;
-            un2(add2(fma2(mk2(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1])), cs2, mk2(bb.x, bb.y)), nm), a0, a1);
-            un2(add2(fma2(mk2(__uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3])), cs2, mk2(bb.z, bb.w)), nm), a2, a3);
-            const float p0 = ex2(a0), p1 = ex2(a1), p2 = ex2(a2), p3 = ex2(a3);
-            sum += (p0 + p1) + (p2 + p3);
-            wv[2 * jj] = pack_bf16(p0, p1);
-            wv[2 * jj + 1] = pack_bf16(p2, p3);
-          }
-          *reinterpret_cast<uint4*>(prow + (((wg * 4 + g) ^ (row & 7)) << 4)) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+        for (int j = 0; j < 8; ++j) {
+          const float4 bb = b4[j];
+          float a0, a1, a2, a3;
+          un2(add2(fma2(mk2(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1])), cs2, mk2(bb.x, bb.y)), nm), a0, a1);
+          un2(add2(fma2(mk2(__uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3])), cs2, mk2(bb.z, bb.w)), nm), a2, a3);
+          const float p0 = ex2(a0), p1 = ex2(a1), p2 = ex2(a2), p3 = ex2(a3);
+          sum += (p0 + p1) + (p2 + p3);
+          pk[2 * j] = pack_bf16(p0, p1);
+          pk[2 * j + 1] = pack_bf16(p2, p3);
         }
-        fence_proxy_async();
+        tmem_st16(s_addr + c * kKC, pk);
+        tmem_st_wait();
+        tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&S.p_ready[pb]));
+        if (lane == 0) mbar_arrive(smem_u32(&S.p_ready[c]));
+      };
+      {
+        uint32_t ra[32], rb[32];
+        tmem_ld32(s_addr, ra);
+        for (int c = 0; c < nC; c += 2) {
+          tmem_ld_wait();
+          if (c + 1 < nC) tmem_ld32(s_addr + (c + 1) * kKC, rb);
+          exp_chunk(ra, c);
+          if (c + 1 < nC) {
+            tmem_ld_wait();
+            if (c + 2 < nC) tmem_ld32(s_addr + (c + 2) * kKC, ra);
+            exp_chunk(rb, c + 1);
+          }
+        }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&S.s_empty));
+      if (te == 0) TRACE(0, 14);
       S.xl[wg][row] = sum;
       named_bar_sync(1, kSoftThreads);
       sum += S.xl[wg ^ 1][row];
       // ---- epilogue: O / l -> bf16 -> this item's Q buffer (half wg) -> store warp
+      if (te == 0) TRACE(0, 15);
       mbar_wait(smem_u32(&S.o_full), qi & 1);
       tc_fence_after();
+      if (te == 0) TRACE(0, 16);
       const float rinv = __frcp_rn(sum);
       uint8_t* orow = &S.q[qb][wg * kQHalf + row * 128];
-#pragma unroll
-      for (int hh = 0; hh < 2; ++hh) {
-        uint32_t r[32];
-        tmem_ld32(tmem + lane_base + kColO + wg * 64 + hh * 32, r);
+      {
+        uint32_t ra[32], rb[32];
+        tmem_ld32(tmem + lane_base + kColO + wg * 64, ra);
+        tmem_ld32(tmem + lane_base + kColO + wg * 64 + 32, rb);
         tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&S.o_empty));     // O is in registers: the next item's P V may start
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
-          uint32_t wv[4];
+          uint32_t wa[4], wb[4];
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
-            wv[j] = pack_bf16(__uint_as_float(r[g * 8 + 2 * j]) * rinv, __uint_as_float(r[g * 8 + 2 * j + 1]) * rinv);
-          *reinterpret_cast<uint4*>(orow + (((hh * 4 + g) ^ (row & 7)) << 4)) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+          for (int j = 0; j < 4; ++j) {
+            wa[j] = pack_bf16(__uint_as_float(ra[g * 8 + 2 * j]) * rinv, __uint_as_float(ra[g * 8 + 2 * j + 1]) * rinv);
+            wb[j] = pack_bf16(__uint_as_float(rb[g * 8 + 2 * j]) * rinv, __uint_as_float(rb[g * 8 + 2 * j + 1]) * rinv);
+          }
+          *reinterpret_cast<uint4*>(orow + ((g ^ (row & 7)) << 4)) = make_uint4(wa[0], wa[1], wa[2], wa[3]);
+          *reinterpret_cast<uint4*>(orow + (((4 + g) ^ (row & 7)) << 4)) = make_uint4(wb[0], wb[1], wb[2], wb[3]);
         }
       }
-      tc_fence_before();
       fence_proxy_async();
       __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(smem_u32(&S.o_empty));
-        mbar_arrive(smem_u32(&S.o_staged));
-      }
+      if (lane == 0) mbar_arrive(smem_u32(&S.o_staged));
+      if (te == 0) TRACE(0, 17);
       if (wg == 0 && lse != nullptr && w.q0 + row < Nq)
         lse[((int64_t)w.b * H + w.h) * Nq + w.q0 + row] = 0.6931471805599453f * (mx + log2f(sum));
     }
@@ -311,6 +398,8 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
 }  // namespace yat
 
 // ------------------------------------------------------------------ host side
+YAT_DEFINE_TRACE_API(yat_xattn)
+
 extern "C" int yat_xattn_max_keys() { return yat::kMaxChunks * yat::kKC; }
 
 extern "C" int yat_xattn_fwd(const void* q, const void* k, const void* v, const void* bias, int B, int H, int Nq, int L, int d,
