@@ -14,11 +14,12 @@
 // Work item = (batch, head, 128-query tile); persistent grid, one CTA per SM.  The probabilities never touch shared
 // memory: the softmax threads write P (bf16 pairs) back into the tensor-memory columns of the scores they came from, and
 // P_c V_c reads its A operand from tensor memory.
-//   producer   Q tile (2 x [128 x 64] SW128 boxes); K and V chunks ([64 keys x 128]) through one ring, in the order the issuer
+//   producer   Q tile (2 x [128 x 64] SW128 boxes); K and V chunks ([128 keys x 128]) through one ring, in the order the issuer
 //              consumes them: K_0.. of the CTA's first item, then per item i and chunk c: V_c(i), K_c(i+1)
-//   issuer     O += P_c V_c (A = P_c in tensor memory, B = V_c MN-major straight from its TMA tile) and, right behind it,
-//              S'[:, 64c..] = Q' K'_c^T of the NEXT item into the score columns pass 2 has just finished with: the next
-//              item's scores are complete when this item's pass 2 ends
+//   issuer     O += P_j V_j per 64-key sub-chunk (A = P_j in tensor memory, B = V MN-major straight from its TMA tile) and,
+//              behind the second sub-chunk of a ring chunk, S'[:, 128c..] = Q' K'_c^T of the NEXT item (N = 128: a 64-key
+//              score MMA is bound by its shared-memory operand reads) into the score columns pass 2 has just finished with:
+//              the next item's scores are complete when this item's pass 2 ends
 //   softmax    8 warps = 2 per TMEM lane quadrant (thread = query row x half of each chunk's columns): pass 1 row max of
 //              s*c + bias2, pass 2 p = 2^(s*c + bias2 - m) -> bf16 pairs -> tcgen05.st over the thread's own score columns,
 //              row sum; epilogue O / l -> bf16 -> the item's Q buffer -> TMA store; lse = ln sum_j exp(...) for a backward
@@ -31,14 +32,15 @@ namespace {
 using namespace sm100;
 
 constexpr int kQT = 128;                     // queries per tile
-constexpr int kKC = 64;                      // keys per chunk
+constexpr int kKC = 64;                      // keys per softmax sub-chunk (one p_ready barrier, 4 P V MMAs)
+constexpr int kKR = 128;                     // keys per ring chunk (one TMA pair, one N = 128 score MMA per K step)
 constexpr int kMaxChunks = 6;                // L <= 384: S occupies TMEM columns [0, 384), O [384, 512)
 constexpr int kQHalf = kQT * 128;            // [128 rows][64 cols] bf16
 constexpr int kQBytes = 2 * kQHalf;          // 32 KB
-constexpr int kCHalf = kKC * 128;            // [64 keys][64 cols] bf16
-constexpr int kCBytes = 2 * kCHalf;          // 16 KB
-constexpr int kStages = 7;
-constexpr int kQBufs = 3;                    // Q(i+1) lands while O(i-1) is still leaving from its own buffer
+constexpr int kCHalf = kKR * 128;            // [128 keys][64 cols] bf16
+constexpr int kCBytes = 2 * kCHalf;          // 32 KB
+constexpr int kStages = 4;
+constexpr int kQBufs = 2;
 constexpr int kSoftWarps = 8, kSoftThreads = 32 * kSoftWarps;
 constexpr int kStoreWarp = 2 + kSoftWarps;
 constexpr int kThreads = 32 * (kStoreWarp + 1);
@@ -50,15 +52,16 @@ struct XfSmem {
   uint8_t kv[kStages][kCBytes];
   float bias2[2][kMaxChunks * kKC];
   float xm[2][kQT], xl[2][kQT];              // row max / row sum halves exchanged between the two warps of a row
-  uint64_t q_full[kQBufs], q_empty[kQBufs], kv_full[kStages], kv_empty[kStages], p_ready[kMaxChunks];
+  uint64_t q_full[kQBufs], kv_full[kStages], kv_empty[kStages], p_ready[kMaxChunks];
   uint64_t s_full, o_full, o_empty, o_staged;
   uint32_t tmem_base;
 };
 constexpr int kXfSmemBytes = (int)sizeof(XfSmem) + 1024;
 static_assert(kXfSmemBytes <= 232448, "cross-attention forward shared memory exceeds the 227 KB per-CTA limit");
 
-constexpr uint32_t kIdescS = make_idesc_bf16(128, kKC, 0, 0);    // Q K_c^T : A, B K-major
-constexpr uint32_t kIdescPV = make_idesc_bf16(128, 128, 0, 1);   // P_c V_c : A K-major (tensor memory), B MN-major
+constexpr uint32_t kIdescS128 = make_idesc_bf16(128, 128, 0, 0);  // Q K_c^T over 128 keys: A, B K-major
+constexpr uint32_t kIdescS64 = make_idesc_bf16(128, 64, 0, 0);    // last chunk with <= 64 keys
+constexpr uint32_t kIdescPV = make_idesc_bf16(128, 128, 0, 1);    // P_j V_j : A K-major (tensor memory), B MN-major
 
 __device__ __forceinline__ float ex2(float x) {
   float y;
@@ -91,13 +94,13 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_qt = (Nq + kQT - 1) / kQT;
   const int n_items = B * H * n_qt;
-  const int nC = (L + kKC - 1) / kKC;          // key chunks
+  const int nC = (L + kKC - 1) / kKC;          // 64-key sub-chunks
+  const int nR = (L + kKR - 1) / kKR;          // 128-key ring chunks
   const int nK = (d + 15) / 16;                // K steps of the score MMA (columns d.. of Q and K are zero-filled)
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < kQBufs; ++i) {
       mbar_init(smem_u32(&S.q_full[i]), 1);
-      mbar_init(smem_u32(&S.q_empty[i]), 1);
     }
     for (int s = 0; s < kStages; ++s) {
       mbar_init(smem_u32(&S.kv_full[s]), 1);
@@ -125,40 +128,25 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
     // ======================= TMA producer =======================
     if (lane == 0) {
       uint32_t it = 0, qi = 0;
-      auto load_q = [&](const Item& w, uint32_t n) {
-        const uint32_t qb = n % kQBufs;
-        mbar_wait(smem_u32(&S.q_empty[qb]), ((n / kQBufs) & 1) ^ 1);
-        const uint32_t qf = smem_u32(&S.q_full[qb]);
-        mbar_arrive_expect_tx(qf, kQBytes);
-        tma_load_4d(smem_u32(&S.q[qb][0]), &tm_q, qf, 0, w.h, w.q0, w.b);
-        tma_load_4d(smem_u32(&S.q[qb][kQHalf]), &tm_q, qf, 64, w.h, w.q0, w.b);
-      };
       auto load_chunk = [&](const CUtensorMap* tm, const Item& w, int c) {
         const uint32_t s = it % kStages, ph = (it / kStages) & 1;
-        TRACE(3, 30);
         mbar_wait(smem_u32(&S.kv_empty[s]), ph ^ 1);
-        TRACE(3, 31);
         const uint32_t full = smem_u32(&S.kv_full[s]);
         mbar_arrive_expect_tx(full, kCBytes);
-        tma_load_4d(smem_u32(&S.kv[s][0]), tm, full, 0, w.h, c * kKC, w.b);
-        tma_load_4d(smem_u32(&S.kv[s][kCHalf]), tm, full, 64, w.h, c * kKC, w.b);
-        TRACE(3, 32);
+        tma_load_4d(smem_u32(&S.kv[s][0]), tm, full, 0, w.h, c * kKR, w.b);
+        tma_load_4d(smem_u32(&S.kv[s][kCHalf]), tm, full, 64, w.h, c * kKR, w.b);
         ++it;
       };
       if ((int)blockIdx.x < n_items) {
         const Item w0 = decode(blockIdx.x, n_qt, H);
-        load_q(w0, 0);
-        for (int c = 0; c < nC; ++c) load_chunk(&tm_k, w0, c);
+        for (int c = 0; c < nR; ++c) load_chunk(&tm_k, w0, c);
       }
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi) {
         const Item w = decode(item, n_qt, H);
         const bool has_next = item + (int)gridDim.x < n_items;
         Item wn = w;
-        if (has_next) {
-          wn = decode(item + gridDim.x, n_qt, H);
-          load_q(wn, qi + 1);
-        }
-        for (int c = 0; c < nC; ++c) {
+        if (has_next) wn = decode(item + gridDim.x, n_qt, H);
+        for (int c = 0; c < nR; ++c) {
           load_chunk(&tm_v, w, c);
           if (has_next) load_chunk(&tm_k, wn, c);
         }
@@ -168,24 +156,25 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
     // ======================= tcgen05 issuer =======================
     if (lane == 0 && (int)blockIdx.x < n_items) {
       uint32_t it = 0, qi = 0;
-      // scores of chunk c of the item in Q buffer qb: K-major SW128 operands (8-row groups 1 KB apart, K step of 16 = 32 B
-      // inside the 128 B row, 64-column halves)
+      // scores of ring chunk c (128 keys, or 64 when no more are left) of the item in Q buffer qb: K-major SW128 operands
+      // (8-row groups 1 KB apart, K step of 16 = 32 B inside the 128 B row, 64-column halves)
       auto score_mma = [&](uint32_t qb, int c) {
         const uint32_t s = it % kStages;
         mbar_wait(smem_u32(&S.kv_full[s]), (it / kStages) & 1);
         tc_fence_after();
+        const uint32_t idesc = (nC - 2 * c >= 2) ? kIdescS128 : kIdescS64;
         const uint64_t qa0 = make_smem_desc(smem_u32(&S.q[qb][0]), 16, 1024, kLayoutSw128);
         const uint64_t kb0 = make_smem_desc(smem_u32(&S.kv[s][0]), 16, 1024, kLayoutSw128);
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks)
           if (ks < nK)
-            umma_bf16(tmem + c * kKC, qa0 + (((ks >> 2) * kQHalf + (ks & 3) * 32) >> 4),
-                      kb0 + (((ks >> 2) * kCHalf + (ks & 3) * 32) >> 4), kIdescS, ks != 0);
+            umma_bf16(tmem + c * kKR, qa0 + (((ks >> 2) * kQHalf + (ks & 3) * 32) >> 4),
+                      kb0 + (((ks >> 2) * kCHalf + (ks & 3) * 32) >> 4), idesc, ks != 0);
         tc_commit(smem_u32(&S.kv_empty[s]));
         ++it;
       };
       mbar_wait(smem_u32(&S.q_full[0]), 0);
-      for (int c = 0; c < nC; ++c) score_mma(0, c);
+      for (int c = 0; c < nR; ++c) score_mma(0, c);
       tc_commit(smem_u32(&S.s_full));
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi) {
         const bool has_next = item + (int)gridDim.x < n_items;
@@ -195,30 +184,32 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
 #else
 #define XT(acc, ...) do { __VA_ARGS__; } while (0)
 #endif
-        for (int c = 0; c < nC; ++c) {
+        for (int j = 0; j < nC; ++j) {
+          const int c = j >> 1;
           const uint32_t s = it % kStages;
-          XT(t_v, mbar_wait(smem_u32(&S.kv_full[s]), (it / kStages) & 1));
-          XT(t_p, mbar_wait(smem_u32(&S.p_ready[c]), qi & 1);                  // every softmax warp has written P_c over S_c
-             if (c == 0) mbar_wait(smem_u32(&S.o_empty), (qi & 1) ^ 1));      // the previous item's O has left TMEM
+          if ((j & 1) == 0) XT(t_v, mbar_wait(smem_u32(&S.kv_full[s]), (it / kStages) & 1));
+          XT(t_p, mbar_wait(smem_u32(&S.p_ready[j]), qi & 1);                  // every softmax warp has written P_j over S_j
+             if (j == 0) mbar_wait(smem_u32(&S.o_empty), (qi & 1) ^ 1));      // the previous item's O has left TMEM
           tc_fence_after();
-          // V_c as the B operand, MN-major SW128: LBO = stride between the two 64-column halves, SBO = 8-key group (1 KB),
-          // K step of 16 keys = 2 KB.  A = P_c in tensor memory: keys 0..31 of the chunk as bf16 pairs in columns
-          // [64c, 64c+16), keys 32..63 in [64c+32, 64c+48) (each softmax thread wrote over its own score columns)
+          // V as the B operand, MN-major SW128: LBO = stride between the two 64-column halves, SBO = 8-key group (1 KB),
+          // K step of 16 keys = 2 KB.  A = P_j in tensor memory: keys 0..31 of the sub-chunk as bf16 pairs in columns
+          // [64j, 64j+16), keys 32..63 in [64j+32, 64j+48) (each softmax thread wrote over its own score columns)
           const uint64_t vb0 = make_smem_desc(smem_u32(&S.kv[s][0]), kCHalf, 1024, kLayoutSw128);
+          const bool last_of_chunk = (j & 1) == 1 || j == nC - 1;
           auto pv_mma = [&]() {
 #pragma unroll
             for (int ks = 0; ks < kKC / 16; ++ks)
-              umma_bf16_ts(tmem + kColO, tmem + c * kKC + (ks >> 1) * 32 + (ks & 1) * 8, vb0 + ((ks * 2048) >> 4), kIdescPV,
-                           (c | ks) != 0);
-            tc_commit(smem_u32(&S.kv_empty[s]));
-            ++it;
-            if (c == nC - 1) tc_commit(smem_u32(&S.o_full));
+              umma_bf16_ts(tmem + kColO, tmem + j * kKC + (ks >> 1) * 32 + (ks & 1) * 8,
+                           vb0 + ((((j & 1) * 4 + ks) * 2048) >> 4), kIdescPV, (j | ks) != 0);
+            if (last_of_chunk) { tc_commit(smem_u32(&S.kv_empty[s])); ++it; }
+            if (j == nC - 1) tc_commit(smem_u32(&S.o_full));
           };
           XT(t_pv, pv_mma());
-          if (has_next) {
+          if (has_next && last_of_chunk) {
+            const uint32_t qn = (qi + 1) & 1;
             XT(t_s,
-            if (c == 0) mbar_wait(smem_u32(&S.q_full[(qi + 1) % kQBufs]), ((qi + 1) / kQBufs) & 1);
-            score_mma((qi + 1) % kQBufs, c));   // in order behind P_c V_c on the tensor pipe: the columns of chunk c are free
+            if (c == 0) mbar_wait(smem_u32(&S.q_full[qn]), ((qi + 1) >> 1) & 1);
+            score_mma(qn, c));                // in order behind the P V of both sub-chunks: the 128 columns of chunk c are free
           }
         }
 #ifdef YAT_BWD_PROBE
@@ -228,18 +219,27 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
       }
     }
   } else if (warp == kStoreWarp) {
-    // ======================= TMA-store warp =======================
+    // ======================= Q loads + O stores (one thread: a Q buffer is refilled right after its O tile has left) ==========
     if (lane == 0) {
+      auto load_q = [&](int item, uint32_t qb) {
+        const Item w = decode(item, n_qt, H);
+        const uint32_t qf = smem_u32(&S.q_full[qb]);
+        mbar_arrive_expect_tx(qf, kQBytes);
+        tma_load_4d(smem_u32(&S.q[qb][0]), &tm_q, qf, 0, w.h, w.q0, w.b);
+        tma_load_4d(smem_u32(&S.q[qb][kQHalf]), &tm_q, qf, 64, w.h, w.q0, w.b);
+      };
+      if ((int)blockIdx.x < n_items) load_q(blockIdx.x, 0);
+      if ((int)(blockIdx.x + gridDim.x) < n_items) load_q(blockIdx.x + gridDim.x, 1);
       uint32_t qi = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi) {
         const Item w = decode(item, n_qt, H);
-        const uint32_t qb = qi % kQBufs;
+        const uint32_t qb = qi & 1;
         mbar_wait(smem_u32(&S.o_staged), qi & 1);
         tma_store_4d(&tm_o, smem_u32(&S.q[qb][0]), 0, w.h, w.q0, w.b);
         if (d > 64) tma_store_4d(&tm_o, smem_u32(&S.q[qb][kQHalf]), 64, w.h, w.q0, w.b);
         tma_store_commit();
-        tma_store_wait_read<0>();                 // shared memory has been read: the Q buffer can be refilled
-        mbar_arrive(smem_u32(&S.q_empty[qb]));
+        tma_store_wait_read<0>();                 // shared memory has been read: the buffer takes the Q tile two items ahead
+        if (item + 2 * (int)gridDim.x < n_items) load_q(item + 2 * gridDim.x, qb);
       }
       tma_store_wait_all<0>();
     }
@@ -263,7 +263,6 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi) {
       const Item w = decode(item, n_qt, H);
       const bool has_next = item + (int)gridDim.x < n_items;
-      const uint32_t qb = qi % kQBufs;
       const float* bs = S.bias2[qi & 1];
       float nb0 = 0.f, nb1 = 0.f;                 // the next item's bias row: in flight during pass 1
       if (has_next && bias != nullptr) {
@@ -353,13 +352,12 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
       S.xl[wg][row] = sum;
       named_bar_sync(1, kSoftThreads);
       sum += S.xl[wg ^ 1][row];
-      // ---- epilogue: O / l -> bf16 -> this item's Q buffer (half wg) -> store warp
+      // ---- epilogue: O / l -> bf16 -> this item's Q buffer (half wg) -> store thread
       if (te == 0) TRACE(0, 15);
       mbar_wait(smem_u32(&S.o_full), qi & 1);
       tc_fence_after();
       if (te == 0) TRACE(0, 16);
       const float rinv = __frcp_rn(sum);
-      uint8_t* orow = &S.q[qb][wg * kQHalf + row * 128];
       {
         uint32_t ra[32], rb[32];
         tmem_ld32(tmem + lane_base + kColO + wg * 64, ra);
@@ -368,6 +366,7 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&S.o_empty));     // O is in registers: the next item's P V may start
+        uint8_t* orow = &S.q[qi & 1][wg * kQHalf + row * 128];
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           uint32_t wa[4], wb[4];
@@ -417,8 +416,8 @@ extern "C" int yat_xattn_fwd(const void* q, const void* k, const void* v, const 
   CUtensorMap tq, tk, tv, to;
   int rc;
   if ((rc = make_tmap_heads_bf16(&tq, q, d, H, Nq, B, (uint64_t)ldq, kQT)) != YAT_OK) return rc;
-  if ((rc = make_tmap_heads_bf16(&tk, k, d, H, L, B, (uint64_t)ldkv, kKC)) != YAT_OK) return rc;
-  if ((rc = make_tmap_heads_bf16(&tv, v, d, H, L, B, (uint64_t)ldkv, kKC)) != YAT_OK) return rc;
+  if ((rc = make_tmap_heads_bf16(&tk, k, d, H, L, B, (uint64_t)ldkv, kKR)) != YAT_OK) return rc;
+  if ((rc = make_tmap_heads_bf16(&tv, v, d, H, L, B, (uint64_t)ldkv, kKR)) != YAT_OK) return rc;
   if ((rc = make_tmap_heads_bf16(&to, o, d, H, Nq, B, (uint64_t)H * d, kQT)) != YAT_OK) return rc;
   static bool attr_set = false;
   if (!attr_set) {
