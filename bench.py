@@ -451,8 +451,8 @@ def _standalone_kernels(device, pk):
     except Exception as e:  # noqa: BLE001 — reported, not hidden
         out["gemm_qkv_own_tcgen05"] = {"error": str(e)[:200]}
     # cross-attention forward of one SANA-1.6B layer (attn2: 20 heads x 112, 320 keys): own tcgen05 kernel vs the path the
-    # step runs (yat_head_pad x 2 + cuDNN SDPA with the key bias folded into an extra head column).  Not on the training path:
-    # there is no own backward, so the step keeps the library call.
+    # step runs (yat_head_pad x 2 + cuDNN SDPA with the key bias folded into an extra head column).  Used by gradient-free
+    # forwards only: there is no own backward, so the training forward keeps the library call.
     try:
         from yat_b200 import _lib as _L
         from yat_b200.attention import _sdpa_key_bias_folded

@@ -104,3 +104,33 @@ def test_argument_errors(cuda):
     with pytest.raises(Exception):
         _run(q, k, v, None, 2)                       # 500 keys > yat_xattn_max_keys()
     assert _lib.lib().yat_xattn_max_keys() == 384
+
+
+def test_processor_uses_the_own_forward_when_no_gradient_is_needed(cuda):
+    """AttnProcessor2_0 (the block's attn2): under no_grad (exploration trials, the frozen preservation pass, sampling) the
+    cross-attention runs on yat_xattn_fwd; with a gradient it stays on the library path (there is no own backward).
+    Same module, same inputs: the two outputs agree to bf16 rounding."""
+    from yat_b200 import _lib
+    from yat_b200.attention import Attention, AttnProcessor2_0
+    torch.manual_seed(0)
+    attn = Attention(query_dim=224, cross_attention_dim=224, heads=2, dim_head=112, bias=True, processor=AttnProcessor2_0())
+    attn = attn.to(cuda).to(torch.bfloat16)
+    x = torch.randn((3, 200, 224), device=cuda, dtype=torch.bfloat16)
+    enc = torch.randn((3, 77, 224), device=cuda, dtype=torch.bfloat16)
+    mask = torch.zeros((3, 1, 77), device=cuda, dtype=torch.bfloat16)
+    mask[1, :, 30:] = -10000.0
+    mask[2, :, 1:] = -10000.0
+    before = _lib.launch_counts["yat_xattn_fwd"]
+    with torch.no_grad():
+        y_own = attn(x, encoder_hidden_states=enc, attention_mask=mask)
+    assert _lib.launch_counts["yat_xattn_fwd"] == before + 1
+    xg = x.clone().requires_grad_(True)
+    y_lib = attn(xg, encoder_hidden_states=enc, attention_mask=mask)
+    assert _lib.launch_counts["yat_xattn_fwd"] == before + 1          # the training path did not take it
+    y_lib.sum().backward()
+    assert xg.grad is not None and torch.isfinite(xg.grad).all()
+    assert _rel(y_own, y_lib.detach()) < 6e-3
+    attn.processor.own_forward = False
+    with torch.no_grad():
+        y_off = attn(x, encoder_hidden_states=enc, attention_mask=mask)
+    assert _lib.launch_counts["yat_xattn_fwd"] == before + 1 and torch.equal(y_off, y_lib.detach())

@@ -154,9 +154,45 @@ def _sdpa_key_bias_folded(q, k, v, bias, H, d):
     return out.transpose(1, 2).reshape(B, -1, H * d)
 
 
+_bias_f32_cache = {}
+
+
+def _xattn_own_forward(q, k, v, bias, H, d):
+    """Forward-only cross-attention on the own tcgen05 kernel (``yat_xattn_fwd``, csrc/xattn_sm100.cu): no padded copies, the
+    key bias read as it is.  q [B, N, H*d], k / v [B, L, H*d] bf16 token-major (row-pitched views allowed), bias [B, L]-shaped
+    additive mask or None.  There is no own backward, so the caller uses this only when no gradient is needed."""
+    B, N, _ = q.shape
+    L = k.shape[1]
+    bias_f = None
+    if bias is not None:
+        key = (bias.data_ptr(), bias._version, bias.numel())
+        hit = _bias_f32_cache.get("b")
+        if hit is not None and hit[0] == key:
+            bias_f = hit[2]
+        else:
+            bias_f = bias.reshape(B, L).float().contiguous()
+            _bias_f32_cache["b"] = (key, bias, bias_f)      # holding `bias` keeps its storage (and the pointer) alive
+    out = torch.empty((B, N, H * d), dtype=torch.bfloat16, device=q.device)
+    with _lib.timed("xattn_fwd"):
+        rc = _lib.lib().yat_xattn_fwd(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(bias_f), B, H, N, L, d, q.stride(1),
+                                      k.stride(1), float(d) ** -0.5, _lib.ptr(out), None, _lib.current_stream())
+    _lib.check(rc, "yat_xattn_fwd")
+    return out
+
+
+def _xattn_own_ok(q, k, v, d):
+    return (not (torch.is_grad_enabled() and (q.requires_grad or k.requires_grad or v.requires_grad))
+            and k.shape[1] <= _lib.lib().yat_xattn_max_keys() and d <= 128
+            and q.stride(2) == 1 and k.stride(2) == 1 and v.stride(2) == 1 and k.stride(1) == v.stride(1)
+            and q.stride(0) == q.shape[1] * q.stride(1) and k.stride(0) == k.shape[1] * k.stride(1)
+            and v.stride(0) == v.shape[1] * v.stride(1) and q.stride(1) % 8 == 0 and k.stride(1) % 8 == 0
+            and q.data_ptr() % 16 == 0 and k.data_ptr() % 16 == 0 and v.data_ptr() % 16 == 0)
+
+
 class AttnProcessor2_0:
     """Softmax scaled-dot-product attention (diffusers ``AttnProcessor2_0`` semantics)."""
     fold_key_mask = True
+    own_forward = True          # no-grad forwards (exploration trials, the frozen preservation pass, sampling): yat_xattn_fwd
 
     def __call__(self, attn, hidden_states, encoder_hidden_states=None, attention_mask=None):
         B = hidden_states.shape[0]
@@ -169,8 +205,11 @@ class AttnProcessor2_0:
         if (attention_mask is not None and self.fold_key_mask and query.is_cuda and query.dtype == torch.bfloat16
                 and attn.norm_q is None and attn.norm_k is None and d % 8 == 0
                 and attention_mask.numel() == B * attention_mask.shape[-1]):
-            out = _sdpa_key_bias_folded(query, key, value, attention_mask.view(B, 1, 1, -1).to(query.dtype),
-                                        attn.heads, d)
+            if self.own_forward and _xattn_own_ok(query, key, value, d):
+                out = _xattn_own_forward(query, key, value, attention_mask, attn.heads, d)
+            else:
+                out = _sdpa_key_bias_folded(query, key, value, attention_mask.view(B, 1, 1, -1).to(query.dtype),
+                                            attn.heads, d)
             out = attn.to_out[0](out)
             return attn.to_out[1](out)
         query = query.view(B, -1, attn.heads, d).transpose(1, 2)

@@ -15,7 +15,8 @@
 // memory: the softmax threads write P (bf16 pairs) back into the tensor-memory columns of the scores they came from, and
 // P_c V_c reads its A operand from tensor memory.
 //   producer   Q tile (2 x [128 x 64] SW128 boxes); K and V chunks ([128 keys x 128]) through one ring, in the order the issuer
-//              consumes them: K_0.. of the CTA's first item, then per item i and chunk c: V_c(i), K_c(i+1)
+//              consumes them: K_0.. of the CTA's first item, then per item i: V_c(i) with the early K_c(i+1) behind them, the
+//              last two K chunks of item i+1 at the end
 //   issuer     O += P_j V_j per 64-key sub-chunk (A = P_j in tensor memory, B = V MN-major straight from its TMA tile) and,
 //              behind the second sub-chunk of a ring chunk, S'[:, 128c..] = Q' K'_c^T of the NEXT item (N = 128: a 64-key
 //              score MMA is bound by its shared-memory operand reads) into the score columns pass 2 has just finished with:
@@ -61,7 +62,8 @@ static_assert(kXfSmemBytes <= 232448, "cross-attention forward shared memory exc
 
 constexpr uint32_t kIdescS128 = make_idesc_bf16(128, 128, 0, 0);  // Q K_c^T over 128 keys: A, B K-major
 constexpr uint32_t kIdescS64 = make_idesc_bf16(128, 64, 0, 0);    // last chunk with <= 64 keys
-constexpr uint32_t kIdescPV = make_idesc_bf16(128, 128, 0, 1);    // P_j V_j : A K-major (tensor memory), B MN-major
+// P_j V_j : A K-major (tensor memory), B MN-major; N = head dim rounded up to 16 (112 for SANA-1.6B: an eighth less work)
+__device__ __forceinline__ uint32_t idesc_pv(int n) { return make_idesc_bf16(128, n, 0, 1); }
 
 __device__ __forceinline__ float ex2(float x) {
   float y;
@@ -146,16 +148,19 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
         const bool has_next = item + (int)gridDim.x < n_items;
         Item wn = w;
         if (has_next) wn = decode(item + gridDim.x, n_qt, H);
-        for (int c = 0; c < nR; ++c) {
+        for (int c = 0; c < nR; ++c) {               // the order the issuer consumes them in (see there)
           load_chunk(&tm_v, w, c);
-          if (has_next) load_chunk(&tm_k, wn, c);
+          if (has_next && c < nR - 2) load_chunk(&tm_k, wn, c);
         }
+        if (has_next)
+          for (int c = max(0, nR - 2); c < nR; ++c) load_chunk(&tm_k, wn, c);
       }
     }
   } else if (warp == 1) {
     // ======================= tcgen05 issuer =======================
     if (lane == 0 && (int)blockIdx.x < n_items) {
       uint32_t it = 0, qi = 0;
+      const uint32_t idesc_o = idesc_pv((d + 15) & ~15);
       // scores of ring chunk c (128 keys, or 64 when no more are left) of the item in Q buffer qb: K-major SW128 operands
       // (8-row groups 1 KB apart, K step of 16 = 32 B inside the 128 B row, 64-column halves)
       auto score_mma = [&](uint32_t qb, int c) {
@@ -200,16 +205,22 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
 #pragma unroll
             for (int ks = 0; ks < kKC / 16; ++ks)
               umma_bf16_ts(tmem + kColO, tmem + j * kKC + (ks >> 1) * 32 + (ks & 1) * 8,
-                           vb0 + ((((j & 1) * 4 + ks) * 2048) >> 4), kIdescPV, (j | ks) != 0);
+                           vb0 + ((((j & 1) * 4 + ks) * 2048) >> 4), idesc_o, (j | ks) != 0);
             if (last_of_chunk) { tc_commit(smem_u32(&S.kv_empty[s])); ++it; }
             if (j == nC - 1) tc_commit(smem_u32(&S.o_full));
           };
           XT(t_pv, pv_mma());
+          // the next item's scores go into the columns of ring chunks whose P V has been issued (the tensor pipe runs in
+          // order).  Early chunks are issued right away; the last two wait until the final P V is in the pipe, so that
+          // nothing sits between the end of pass 2 and o_full - they run under the epilogue instead.
           if (has_next && last_of_chunk) {
             const uint32_t qn = (qi + 1) & 1;
+            const int c_lo = (j == nC - 1) ? max(0, min(c, nR - 2)) : c, c_hi = (j == nC - 1 || c < nR - 2) ? c : c_lo - 1;
             XT(t_s,
-            if (c == 0) mbar_wait(smem_u32(&S.q_full[qn]), ((qi + 1) >> 1) & 1);
-            score_mma(qn, c));                // in order behind the P V of both sub-chunks: the 128 columns of chunk c are free
+            for (int cc = c_lo; cc <= c_hi; ++cc) {
+              if (cc == 0) mbar_wait(smem_u32(&S.q_full[qn]), ((qi + 1) >> 1) & 1);
+              score_mma(qn, cc);
+            });
           }
         }
 #ifdef YAT_BWD_PROBE
@@ -260,15 +271,19 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
         S.bias2[0][j] = j < L ? (bias ? __ldg(bias + (int64_t)w0.b * L + j) * kLog2e : 0.f) : -INFINITY;
       named_bar_sync(1, kSoftThreads);
     }
+    Item w_next = decode(blockIdx.x, n_qt, H);
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi) {
-      const Item w = decode(item, n_qt, H);
+      const Item w = w_next;
       const bool has_next = item + (int)gridDim.x < n_items;
       const float* bs = S.bias2[qi & 1];
       float nb0 = 0.f, nb1 = 0.f;                 // the next item's bias row: in flight during pass 1
-      if (has_next && bias != nullptr) {
-        const float* bn = bias + (int64_t)decode(item + gridDim.x, n_qt, H).b * L;
-        if (te < L) nb0 = __ldg(bn + te);
-        if (te + kSoftThreads < L) nb1 = __ldg(bn + te + kSoftThreads);
+      if (has_next) {
+        w_next = decode(item + gridDim.x, n_qt, H);
+        if (bias != nullptr) {
+          const float* bn = bias + (int64_t)w_next.b * L;
+          if (te < L) nb0 = __ldg(bn + te);
+          if (te + kSoftThreads < L) nb1 = __ldg(bn + te + kSoftThreads);
+        }
       }
       if (te == 0) TRACE(0, 10);
       mbar_wait(smem_u32(&S.s_full), qi & 1);
@@ -352,6 +367,8 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
       S.xl[wg][row] = sum;
       named_bar_sync(1, kSoftThreads);
       sum += S.xl[wg ^ 1][row];
+      if (wg == 0 && lse != nullptr && w.q0 + row < Nq)      // (under the wait for the last P V)
+        lse[((int64_t)w.b * H + w.h) * Nq + w.q0 + row] = 0.6931471805599453f * (mx + log2f(sum));
       // ---- epilogue: O / l -> bf16 -> this item's Q buffer (half wg) -> store thread
       if (te == 0) TRACE(0, 15);
       mbar_wait(smem_u32(&S.o_full), qi & 1);
@@ -383,8 +400,6 @@ xattn_fwd_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&S.o_staged));
       if (te == 0) TRACE(0, 17);
-      if (wg == 0 && lse != nullptr && w.q0 + row < Nq)
-        lse[((int64_t)w.b * H + w.h) * Nq + w.q0 + row] = 0.6931471805599453f * (mx + log2f(sum));
     }
   }
 
