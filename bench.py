@@ -467,11 +467,14 @@ def _standalone_kernels(device, pk):
         xlse = torch.empty((B, xh, N), dtype=torch.float32, device=device)
         cs = torch.cuda.current_stream().cuda_stream
         L = _L.lib()
-        ms_o = timeit(lambda: L.yat_xattn_fwd(xq.data_ptr(), xk.data_ptr(), xv.data_ptr(), xb.data_ptr(), B, xh, N, xl, xd,
-                                              xh * xd, xh * xd, xd ** -0.5, xo.data_ptr(), xlse.data_ptr(), cs), iters=30, warm=5)
         xb4 = xb.view(B, 1, 1, xl).to(torch.bfloat16)
-        with torch.no_grad():
-            ms_l = timeit(lambda: _sdpa_key_bias_folded(xq, xk, xv, xb4, xh, xd), iters=30, warm=5)
+        own = lambda: L.yat_xattn_fwd(xq.data_ptr(), xk.data_ptr(), xv.data_ptr(), xb.data_ptr(), B, xh, N, xl, xd,  # noqa: E731
+                                      xh * xd, xh * xd, xd ** -0.5, xo.data_ptr(), xlse.data_ptr(), cs)
+        ms_o = ms_l = float("inf")
+        with torch.no_grad():   # both arms are clock-sensitive and the GEMM A/B above leaves the board at its power cap:
+            for _ in range(3):  # alternate the arms and keep each one's best
+                ms_l = min(ms_l, timeit(lambda: _sdpa_key_bias_folded(xq, xk, xv, xb4, xh, xd), iters=30, warm=5))
+                ms_o = min(ms_o, timeit(own, iters=30, warm=5))
         fl_x = 4.0 * B * xh * N * xl * xd
         out["xattn_fwd_own_tcgen05"] = {"bound": "tensor", "achieved": fl_x / (ms_o * 1e-3) / 1e12, "peak": pk["bf16_tflops"],
                                         "unit": "TFLOP/s", "us": ms_o * 1e3, "flops": fl_x, "shape": [B, xh, N, xl, xd],

@@ -84,3 +84,53 @@ if hasattr(raw, "yat_xattn_probe_read"):
         for key in sorted(delta):
             dd = delta[key]
             print(f"   {key[0]:3d} -> {key[1]:3d}: n={len(dd):4d} mean {sum(dd) / len(dd):8.0f}  min {min(dd):7d}  max {max(dd):7d}")
+
+# host cost of one C-ABI call (tensor-map encodes + launch), and the back-to-back device time bench.py reports
+import time  # noqa: E402
+torch.cuda.synchronize()
+t0 = time.perf_counter()
+for _ in range(200):
+    run(True)
+host_us = (time.perf_counter() - t0) / 200 * 1e6
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(50):
+    run(True)
+e1.record()
+torch.cuda.synchronize()
+print(f"host {host_us:.1f} us per call (queueing only); back to back {e0.elapsed_time(e1) * 20:.1f} us per call")
+
+# the same comparison at the power-capped clock the training step runs at: a GEMM burn before each arm, SM clock sampled by NVML
+import pynvml  # noqa: E402
+pynvml.nvmlInit()
+hnd = pynvml.nvmlDeviceGetHandleByIndex(0)
+ga = torch.randn((8192, 8192), device=dev).to(torch.bfloat16)
+gb = torch.randn((8192, 8192), device=dev).to(torch.bfloat16)
+
+
+def burn(seconds):
+    t0 = time.time()
+    while time.time() - t0 < seconds:
+        for _ in range(20):
+            ga @ gb
+        torch.cuda.synchronize()
+
+
+def capped(fn, n=150):
+    burn(2.0)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n):
+        fn()
+    e1.record()
+    mhz = pynvml.nvmlDeviceGetClockInfo(hnd, pynvml.NVML_CLOCK_SM)
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n * 1e3, mhz
+
+
+with torch.no_grad():
+    for rep in range(2):
+        a_us, a_mhz = capped(lambda: run(True))
+        b_us, b_mhz = capped(lambda: _sdpa_key_bias_folded(q, k, v, bias4, H, d))
+        print(f"after a GEMM burn: own {a_us:.1f} us @ {a_mhz} MHz, library path {b_us:.1f} us @ {b_mhz} MHz")
