@@ -305,6 +305,16 @@ int yat_xattn_max_keys(void);
 int yat_xattn_fwd(const void* q, const void* k, const void* v, const void* bias, int B, int H, int Nq, int L, int d,
                   int64_t ldq, int64_t ldkv, float scale, void* o, void* lse, void* stream);
 
+/* yat_xattn_bwd: the backward of the same attention (the autograd of F.scaled_dot_product_attention for `self.attn2(...)`,
+ * utils/patch_sana_attention_layers.py:100-106).  o, lse: what yat_xattn_fwd returned; d_o [B, Nq, H*d] dense bf16;
+ * dq [B, Nq, H*d], dk, dv [B, L, H*d] dense bf16 (dk and dv may both be NULL: only dq is formed);
+ * workspace = yat_xattn_bwd_workspace_bytes(B, H, Nq) bytes (D = rowsum(dO * O), fp32).
+ */
+int64_t yat_xattn_bwd_workspace_bytes(int B, int H, int Nq);
+int yat_xattn_bwd(const void* q, const void* k, const void* v, const void* bias, const void* o, const void* lse,
+                  const void* d_o, int B, int H, int Nq, int L, int d, int64_t ldq, int64_t ldkv, float scale,
+                  void* dq, void* dk, void* dv, void* workspace, void* stream);
+
 /* ---- bucket assignment (host function; float64 compare, first-minimum wins) ---------------
  *   out[i] = argmin_j |keys[j] - ratios[i]| with strict '<' in table order, or -1 if nkeys==0.
  */

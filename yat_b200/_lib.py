@@ -77,6 +77,9 @@ SIGNATURES = {
     "yat_xattn_max_keys": (c_int, []),
     "yat_xattn_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int64, c_int64,
                               c_float, c_void_p, c_void_p, c_void_p]),
+    "yat_xattn_bwd_workspace_bytes": (c_int64, [c_int, c_int, c_int]),
+    "yat_xattn_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
+                              c_int, c_int64, c_int64, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "yat_bucket_assign": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p]),
     "yat_philox_raw": (c_int, [c_uint64, c_uint64, c_uint32, c_uint32, c_int, c_void_p, c_void_p]),
 }
@@ -92,7 +95,7 @@ LAUNCHING = ("yat_noise_flowmatch", "yat_noise_ddpm", "yat_loss_fused", "yat_rep
              "yat_gate_residual_bwd", "yat_glumb_mid_fwd", "yat_glumb_mid_bwd", "yat_grad_clip_coef",
              "yat_adamw_step", "yat_adamw_ema_step", "yat_ema_step", "yat_colsum_bf16", "yat_colsum_bf16_static", "yat_head_pad", "yat_head_unpad",
              "yat_linattn_fwd_ld", "yat_linattn_bwd_ld", "yat_gemm_bf16_tn", "yat_qkv_linattn_fwd",
-             "yat_linattn_fwd_state", "yat_xattn_fwd")
+             "yat_linattn_fwd_state", "yat_xattn_fwd", "yat_xattn_bwd")
 launch_counts = {name: 0 for name in LAUNCHING}
 
 

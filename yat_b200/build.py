@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libyat_b200.so")
 SOURCES = ["api.cu", "noise.cu", "loss.cu", "repa.cu", "pad.cu", "linattn_simt.cu", "linattn_sm100.cu",
-           "linattn_bwd_sm100.cu", "block_ops.cu", "glumb.cu", "optim.cu", "gemm_sm100.cu", "qkv_linattn_sm100.cu", "xattn_sm100.cu"]
+           "linattn_bwd_sm100.cu", "block_ops.cu", "glumb.cu", "optim.cu", "gemm_sm100.cu", "qkv_linattn_sm100.cu", "xattn_sm100.cu", "xattn_bwd_sm100.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 

@@ -1,0 +1,364 @@
+// Cross-attention of the SANA / PixArt blocks (attn2), backward, on the 5th-gen tensor cores (tcgen05 + TMEM + TMA).
+//
+// With s_ij = scale q_i.k_j + bias_j, p_ij = exp(s_ij - lse_i) (lse from the forward, yat_xattn_fwd) and D_i = dO_i . O_i:
+//   dP_ij = dO_i . v_j        dS_ij = p_ij (dP_ij - D_i)
+//   dQ_i = scale sum_j dS_ij k_j        dK_j = scale sum_i dS_ij q_i        dV_j = sum_i p_ij dO_i
+// (the backward of F.scaled_dot_product_attention inside diffusers' AttnProcessor2_0, reached from
+// utils/patch_sana_attention_layers.py:100-106).  Three kernels:
+//   prep   D[b, h, i] = sum_c dO . O                                   (one warp per token row and head; HBM-bound)
+//   dq     item = (batch, head, 128-query tile): S_j = Q K_j^T and dP_j = dO V_j^T per 64-key sub-chunk into one of two
+//          tensor-memory buffers, dS_j written back over S_j by the threads that own the rows (bf16 pairs), dQ += dS_j K_j
+//          with its A operand read from tensor memory - the same feedback as the forward's P V
+//   dkv    item = (batch, head, 128-key block), K and V blocks resident, looping over the query tiles: S^T = K Q_t^T and
+//          dP^T = V dO_t^T (keys along the lanes), P^T and dS^T written back over them, dV += P^T dO_t, dK += dS^T Q_t
+// No probability ever touches shared memory; every reduction over keys or queries is an MMA.
+#include "common.cuh"
+#include "sm100.cuh"
+
+namespace yat {
+namespace {
+using namespace sm100;
+
+constexpr int kQT = 128;                     // queries per tile
+constexpr int kKC = 64;                      // keys per sub-chunk (dq kernel)
+constexpr int kMaxKeys = 384;
+constexpr int kTHalf = kQT * 128;            // [128 rows][64 cols] bf16
+constexpr int kTBytes = 2 * kTHalf;          // 32 KB
+constexpr int kCHalf = kKC * 128;            // [64 keys][64 cols] bf16
+constexpr int kCBytes = 2 * kCHalf;          // 16 KB
+constexpr int kSoftWarps = 8, kSoftThreads = 32 * kSoftWarps;
+constexpr int kStoreWarp = 2 + kSoftWarps;
+constexpr int kThreads = 32 * (kStoreWarp + 1);
+constexpr int kTmemCols = 512;
+constexpr float kLog2e = 1.4426950408889634f;
+
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// ------------------------------------------------------------------------------------------------ prep: D = rowsum(dO * O)
+__global__ void __launch_bounds__(256) xattn_prep_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
+                                                         float* __restrict__ D, int64_t rows, int H, int d, int Nq) {
+  const int lane = threadIdx.x & 31;
+  const int64_t wid = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);      // (token row, head)
+  if (wid >= rows * H) return;
+  const int64_t r = wid / H;
+  const int h = (int)(wid - r * H);
+  const uint4* po = reinterpret_cast<const uint4*>(o + (r * H + h) * d);
+  const uint4* pd = reinterpret_cast<const uint4*>(d_o + (r * H + h) * d);
+  float acc = 0.f;
+  if (lane < d / 8) {
+    const uint4 a = ld_stream(po + lane), b = ld_stream(pd + lane);
+    const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) acc += bf16_lo(aw[i]) * bf16_lo(bw[i]) + bf16_hi(aw[i]) * bf16_hi(bw[i]);
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) D[((r / Nq) * H + h) * Nq + (r % Nq)] = acc;             // [B, H, Nq] like lse
+}
+
+struct Item { int b, h, q0; };
+__device__ __forceinline__ Item decode(int item, int n_qt, int H) {
+  Item r;
+  r.q0 = (item % n_qt) * kQT;
+  const int bh = item / n_qt;
+  r.h = bh % H;
+  r.b = bh / H;
+  return r;
+}
+
+// ------------------------------------------------------------------------------------------------ dq kernel
+constexpr int kDqStages = 5;
+constexpr uint32_t kColDQ = 256;
+
+struct DqSmem {
+  uint8_t qd[2][2][kTBytes];                 // [item buffer][Q | dO]; the dQ tile leaves from the Q half
+  uint8_t kv[kDqStages][kCBytes];            // ring: V_0 K_0 V_1 K_1 ... (V_j is free after dP_j, K_j after dQ += dS_j K_j)
+  float bias2[2][kMaxKeys];
+  uint64_t qd_full[2], kv_full[kDqStages], kv_empty[kDqStages], sd_full[2], ds_ready[2];
+  uint64_t dq_full, dq_empty, dq_staged;
+  uint32_t tmem_base;
+};
+constexpr int kDqSmemBytes = (int)sizeof(DqSmem) + 1024;
+static_assert(kDqSmemBytes <= 232448, "xattn dq kernel exceeds the 227 KB shared-memory limit");
+
+constexpr uint32_t kIdescSd = make_idesc_bf16(128, kKC, 0, 0);   // Q K_j^T, dO V_j^T : A, B K-major
+
+__global__ void __launch_bounds__(kThreads, 1)
+xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_do,
+                      const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v,
+                      const __grid_constant__ CUtensorMap tm_dq, const float* __restrict__ bias,
+                      const float* __restrict__ lse, const float* __restrict__ D, int B, int H, int Nq, int L, int d,
+                      float scale) {
+  extern __shared__ uint8_t smem_raw[];
+  DqSmem& S = *reinterpret_cast<DqSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_qt = (Nq + kQT - 1) / kQT;
+  const int n_items = B * H * n_qt;
+  const int nC = (L + kKC - 1) / kKC;
+  const int nK = (d + 15) / 16;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(smem_u32(&S.qd_full[i]), 1);
+      mbar_init(smem_u32(&S.sd_full[i]), 1);
+      mbar_init(smem_u32(&S.ds_ready[i]), kSoftWarps);
+    }
+    for (int s = 0; s < kDqStages; ++s) {
+      mbar_init(smem_u32(&S.kv_full[s]), 1);
+      mbar_init(smem_u32(&S.kv_empty[s]), 1);
+    }
+    mbar_init(smem_u32(&S.dq_full), 1);
+    mbar_init(smem_u32(&S.dq_empty), kSoftWarps);
+    mbar_init(smem_u32(&S.dq_staged), kSoftWarps);
+    fence_barrier_init();
+    tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_do); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v);
+    tma_prefetch_desc(&tm_dq);
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(&S.tmem_base), kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (S.tmem_base != 0) __trap();
+  constexpr uint32_t tmem = 0;
+
+  if (warp == 0) {
+    // ======================= TMA producer: the key ring =======================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const Item w = decode(item, n_qt, H);
+        for (int n = 0; n < 2 * nC; ++n, ++it) {
+          const CUtensorMap* tm = (n & 1) ? &tm_k : &tm_v;
+          const uint32_t s = it % kDqStages, ph = (it / kDqStages) & 1;
+          mbar_wait(smem_u32(&S.kv_empty[s]), ph ^ 1);
+          const uint32_t full = smem_u32(&S.kv_full[s]);
+          mbar_arrive_expect_tx(full, kCBytes);
+          tma_load_4d(smem_u32(&S.kv[s][0]), tm, full, 0, w.h, (n >> 1) * kKC, w.b);
+          tma_load_4d(smem_u32(&S.kv[s][kCHalf]), tm, full, 64, w.h, (n >> 1) * kKC, w.b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ======================= tcgen05 issuer =======================
+    if (lane == 0) {
+      uint32_t it0 = 0, qi = 0, sd_use[2] = {0, 0}, ds_use[2] = {0, 0};
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi, it0 += 2 * nC) {
+        const uint32_t buf = qi & 1;
+        mbar_wait(smem_u32(&S.qd_full[buf]), (qi >> 1) & 1);
+        tc_fence_after();
+        const uint64_t qa0 = make_smem_desc(smem_u32(&S.qd[buf][0][0]), 16, 1024, kLayoutSw128);
+        const uint64_t da0 = make_smem_desc(smem_u32(&S.qd[buf][1][0]), 16, 1024, kLayoutSw128);
+        // S_j = Q K_j^T and dP_j = dO V_j^T into buffer j & 1 (columns 128 (j & 1) + {0, 64})
+        auto issue_sd = [&](int j) {
+          const uint32_t iv = it0 + 2 * j, ik = iv + 1, sv = iv % kDqStages, sk = ik % kDqStages, b = j & 1;
+          mbar_wait(smem_u32(&S.kv_full[sv]), (iv / kDqStages) & 1);
+          mbar_wait(smem_u32(&S.kv_full[sk]), (ik / kDqStages) & 1);
+          tc_fence_after();
+          const uint64_t kb0 = make_smem_desc(smem_u32(&S.kv[sk][0]), 16, 1024, kLayoutSw128);
+          const uint64_t vb0 = make_smem_desc(smem_u32(&S.kv[sv][0]), 16, 1024, kLayoutSw128);
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            if (ks < nK)
+              umma_bf16(tmem + b * 128, qa0 + (((ks >> 2) * kTHalf + (ks & 3) * 32) >> 4),
+                        kb0 + (((ks >> 2) * kCHalf + (ks & 3) * 32) >> 4), kIdescSd, ks != 0);
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            if (ks < nK)
+              umma_bf16(tmem + b * 128 + 64, da0 + (((ks >> 2) * kTHalf + (ks & 3) * 32) >> 4),
+                        vb0 + (((ks >> 2) * kCHalf + (ks & 3) * 32) >> 4), kIdescSd, ks != 0);
+          tc_commit(smem_u32(&S.kv_empty[sv]));        // V_j is done; K_j stays for dQ
+          tc_commit(smem_u32(&S.sd_full[b]));
+          ++sd_use[b];
+        };
+        // dQ += dS_j K_j: A = dS_j in tensor memory (bf16 pairs over the score columns, see the softmax warps), B = K_j
+        // MN-major (LBO = stride between the two 64-column halves, SBO = 8-key group, K step of 16 keys = 2 KB)
+        const uint32_t idesc_dq = make_idesc_bf16(128, (d + 15) & ~15, 0, 1);
+        auto issue_dq = [&](int j) {
+          const uint32_t ik = it0 + 2 * j + 1, sk = ik % kDqStages, b = j & 1;
+          mbar_wait(smem_u32(&S.ds_ready[b]), ds_use[b] & 1);
+          ++ds_use[b];
+          if (j == 0) mbar_wait(smem_u32(&S.dq_empty), (qi & 1) ^ 1);
+          tc_fence_after();
+          const uint64_t kb0 = make_smem_desc(smem_u32(&S.kv[sk][0]), kCHalf, 1024, kLayoutSw128);
+#pragma unroll
+          for (int ks = 0; ks < kKC / 16; ++ks)
+            umma_bf16_ts(tmem + kColDQ, tmem + b * 128 + (ks >> 1) * 32 + (ks & 1) * 8, kb0 + ((ks * 2048) >> 4), idesc_dq,
+                         (j | ks) != 0);
+          tc_commit(smem_u32(&S.kv_empty[sk]));
+          if (j == nC - 1) tc_commit(smem_u32(&S.dq_full));
+        };
+        issue_sd(0);
+        if (nC > 1) issue_sd(1);
+        for (int j = 0; j < nC; ++j) {
+          issue_dq(j);
+          if (j + 2 < nC) issue_sd(j + 2);     // in order behind dQ_j: buffer j & 1 is free
+        }
+      }
+    }
+  } else if (warp == kStoreWarp) {
+    // ======================= Q / dO loads + dQ stores (one thread) =======================
+    if (lane == 0) {
+      auto load_qd = [&](int item, uint32_t buf) {
+        const Item w = decode(item, n_qt, H);
+        const uint32_t f = smem_u32(&S.qd_full[buf]);
+        mbar_arrive_expect_tx(f, 2 * kTBytes);
+        tma_load_4d(smem_u32(&S.qd[buf][0][0]), &tm_q, f, 0, w.h, w.q0, w.b);
+        tma_load_4d(smem_u32(&S.qd[buf][0][kTHalf]), &tm_q, f, 64, w.h, w.q0, w.b);
+        tma_load_4d(smem_u32(&S.qd[buf][1][0]), &tm_do, f, 0, w.h, w.q0, w.b);
+        tma_load_4d(smem_u32(&S.qd[buf][1][kTHalf]), &tm_do, f, 64, w.h, w.q0, w.b);
+      };
+      if ((int)blockIdx.x < n_items) load_qd(blockIdx.x, 0);
+      if ((int)(blockIdx.x + gridDim.x) < n_items) load_qd(blockIdx.x + gridDim.x, 1);
+      uint32_t qi = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi) {
+        const Item w = decode(item, n_qt, H);
+        const uint32_t buf = qi & 1;
+        mbar_wait(smem_u32(&S.dq_staged), qi & 1);
+        tma_store_4d(&tm_dq, smem_u32(&S.qd[buf][0][0]), 0, w.h, w.q0, w.b);
+        if (d > 64) tma_store_4d(&tm_dq, smem_u32(&S.qd[buf][0][kTHalf]), 64, w.h, w.q0, w.b);
+        tma_store_commit();
+        tma_store_wait_read<0>();
+        if (item + 2 * (int)gridDim.x < n_items) load_qd(item + 2 * gridDim.x, buf);
+      }
+      tma_store_wait_all<0>();
+    }
+  } else {
+    // ======================= dS + epilogue warps =======================
+    const int te = threadIdx.x - 64;              // 0..255
+    const int wg = te >> 7;                       // which 32 of a sub-chunk's 64 keys / which half of dQ
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;
+    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    const f2 cs2 = bc2(scale * kLog2e);
+    uint32_t qi = 0, sd_use[2] = {0, 0};
+    int bias_b = -1;
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi) {
+      const Item w = decode(item, n_qt, H);
+      const bool valid = w.q0 + row < Nq;
+      const int64_t vi = ((int64_t)w.b * H + w.h) * Nq + w.q0 + row;
+      const float lse2 = valid ? __ldg(lse + vi) * kLog2e : 0.f;
+      const f2 nd2 = bc2(valid ? -__ldg(D + vi) : 0.f);
+      if (w.b != bias_b) {                        // the bias row of this sample (items of a CTA change sample rarely)
+        named_bar_sync(1, kSoftThreads);          // nobody still reads the old row
+        for (int j = te; j < nC * kKC; j += kSoftThreads)
+          S.bias2[0][j] = j < L ? (bias ? __ldg(bias + (int64_t)w.b * L + j) * kLog2e : 0.f) : -INFINITY;
+        named_bar_sync(1, kSoftThreads);
+        bias_b = w.b;
+      }
+      for (int j = 0; j < nC; ++j) {
+        const uint32_t b = j & 1;
+        mbar_wait(smem_u32(&S.sd_full[b]), sd_use[b] & 1);
+        ++sd_use[b];
+        tc_fence_after();
+        uint32_t rs[32], rp[32];
+        const uint32_t base = tmem + lane_base + b * 128 + wg * 32;
+        tmem_ld32(base, rs);
+        tmem_ld32(base + 64, rp);
+        tmem_ld_wait();
+        const float4* b4 = reinterpret_cast<const float4*>(&S.bias2[0][j * kKC + wg * 32]);
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float4 bb = b4[i];
+          float a0, a1, a2, a3;
+          un2(fma2(mk2(__uint_as_float(rs[4 * i]), __uint_as_float(rs[4 * i + 1])), cs2, mk2(bb.x - lse2, bb.y - lse2)), a0, a1);
+          un2(fma2(mk2(__uint_as_float(rs[4 * i + 2]), __uint_as_float(rs[4 * i + 3])), cs2, mk2(bb.z - lse2, bb.w - lse2)), a2, a3);
+          const f2 p01 = mk2(ex2(a0), ex2(a1)), p23 = mk2(ex2(a2), ex2(a3));
+          const f2 s01 = mul2(p01, add2(mk2(__uint_as_float(rp[4 * i]), __uint_as_float(rp[4 * i + 1])), nd2));
+          const f2 s23 = mul2(p23, add2(mk2(__uint_as_float(rp[4 * i + 2]), __uint_as_float(rp[4 * i + 3])), nd2));
+          pk[2 * i] = pack2(s01);
+          pk[2 * i + 1] = pack2(s23);
+        }
+        tmem_st16(base, pk);
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&S.ds_ready[b]));
+      }
+      // ---- epilogue: scale dQ -> bf16 -> the item's Q buffer -> store thread
+      mbar_wait(smem_u32(&S.dq_full), qi & 1);
+      tc_fence_after();
+      {
+        uint32_t ra[32], rb[32];
+        tmem_ld32(tmem + lane_base + kColDQ + wg * 64, ra);
+        tmem_ld32(tmem + lane_base + kColDQ + wg * 64 + 32, rb);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&S.dq_empty));
+        uint8_t* orow = &S.qd[qi & 1][0][wg * kTHalf + row * 128];
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint32_t wa[4], wb[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            wa[i] = pack_bf16(__uint_as_float(ra[g * 8 + 2 * i]) * scale, __uint_as_float(ra[g * 8 + 2 * i + 1]) * scale);
+            wb[i] = pack_bf16(__uint_as_float(rb[g * 8 + 2 * i]) * scale, __uint_as_float(rb[g * 8 + 2 * i + 1]) * scale);
+          }
+          *reinterpret_cast<uint4*>(orow + ((g ^ (row & 7)) << 4)) = make_uint4(wa[0], wa[1], wa[2], wa[3]);
+          *reinterpret_cast<uint4*>(orow + (((4 + g) ^ (row & 7)) << 4)) = make_uint4(wb[0], wb[1], wb[2], wb[3]);
+        }
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&S.dq_staged));
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, kTmemCols);
+}
+
+}  // namespace
+}  // namespace yat
+
+// ------------------------------------------------------------------ host side
+extern "C" int64_t yat_xattn_bwd_workspace_bytes(int B, int H, int Nq) { return (int64_t)B * H * Nq * (int64_t)sizeof(float); }
+
+extern "C" int yat_xattn_bwd(const void* q, const void* k, const void* v, const void* bias, const void* o, const void* lse,
+                             const void* d_o, int B, int H, int Nq, int L, int d, int64_t ldq, int64_t ldkv, float scale,
+                             void* dq, void* dk, void* dv, void* workspace, void* stream) {
+  using namespace yat;
+  YAT_REQUIRE(q && k && v && o && lse && d_o && dq && workspace, YAT_ERR_BAD_ARG, "yat_xattn_bwd: null pointer argument");
+  YAT_REQUIRE((dk == nullptr) == (dv == nullptr), YAT_ERR_BAD_ARG, "yat_xattn_bwd: dk and dv go together");
+  YAT_REQUIRE(B > 0 && H > 0 && Nq > 0 && L > 0, YAT_ERR_BAD_ARG, "yat_xattn_bwd: non-positive dimension");
+  YAT_REQUIRE(d >= 8 && d <= 128 && d % 8 == 0, YAT_ERR_UNSUPPORTED, "yat_xattn_bwd: head_dim %d not supported (8..128, multiple of 8)", d);
+  YAT_REQUIRE(L <= kMaxKeys, YAT_ERR_UNSUPPORTED, "yat_xattn_bwd: %d keys exceed the %d supported", L, kMaxKeys);
+  YAT_REQUIRE(ldq >= (int64_t)H * d && ldq % 8 == 0 && ldkv >= (int64_t)H * d && ldkv % 8 == 0, YAT_ERR_BAD_ARG,
+              "yat_xattn_bwd: row pitches %lld / %lld must be >= H*d and multiples of 8", (long long)ldq, (long long)ldkv);
+  YAT_REQUIRE((((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o | (uintptr_t)d_o | (uintptr_t)dq | (uintptr_t)dk |
+                (uintptr_t)dv) & 15u) == 0, YAT_ERR_BAD_ARG, "yat_xattn_bwd: tensors must be 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t rows = (int64_t)B * Nq;
+  float* D = (float*)workspace;
+  xattn_prep_kernel<<<(unsigned)((rows * H + 7) / 8), 256, 0, st>>>((const __nv_bfloat16*)o, (const __nv_bfloat16*)d_o, D, rows, H, d, Nq);
+  int rc = check_launch("xattn_prep");
+  if (rc != YAT_OK) return rc;
+  const uint64_t C = (uint64_t)H * d;
+  CUtensorMap tq, tdo, tk, tv, tdq;
+  if ((rc = make_tmap_heads_bf16(&tq, q, d, H, Nq, B, (uint64_t)ldq, kQT)) != YAT_OK) return rc;
+  if ((rc = make_tmap_heads_bf16(&tdo, d_o, d, H, Nq, B, C, kQT)) != YAT_OK) return rc;
+  if ((rc = make_tmap_heads_bf16(&tk, k, d, H, L, B, (uint64_t)ldkv, kKC)) != YAT_OK) return rc;
+  if ((rc = make_tmap_heads_bf16(&tv, v, d, H, L, B, (uint64_t)ldkv, kKC)) != YAT_OK) return rc;
+  if ((rc = make_tmap_heads_bf16(&tdq, dq, d, H, Nq, B, C, kQT)) != YAT_OK) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(xattn_dq_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDqSmemBytes);
+    YAT_REQUIRE(e == cudaSuccess, YAT_ERR_CUDA, "yat_xattn_bwd: cannot reserve %d B of shared memory (%s)", kDqSmemBytes,
+                cudaGetErrorString(e));
+    attr_set = true;
+  }
+  const int items = B * H * ((Nq + kQT - 1) / kQT);
+  xattn_dq_sm100_kernel<<<items < kNumSMs ? items : kNumSMs, kThreads, kDqSmemBytes, st>>>(
+      tq, tdo, tk, tv, tdq, (const float*)bias, (const float*)lse, D, B, H, Nq, L, d, scale);
+  rc = check_launch("xattn_dq_sm100");
+  if (rc != YAT_OK) return rc;
+  return YAT_OK;
+}
