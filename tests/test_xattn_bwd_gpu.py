@@ -74,3 +74,31 @@ def test_dq_against_fp64_autograd(cuda, B, H, Nq, L, d, lens):
     dq_ref, _, _ = _oracle(q, k, v, do, bias, H)
     assert not torch.isnan(dq.float()).any()
     assert _rel(dq.cpu(), dq_ref) < 8e-3
+
+
+@pytest.mark.parametrize("B,H,Nq,L,d,lens", CASES)
+def test_dq_dk_dv_against_fp64_autograd(cuda, B, H, Nq, L, d, lens):
+    q, k, v, do, bias = _problem(B, H, Nq, L, d, cuda, seed=B * 10 + L + d + 1, lens=lens)
+    dq, dk, dv = _own(q, k, v, do, bias, H)
+    dq_ref, dk_ref, dv_ref = _oracle(q, k, v, do, bias, H)
+    for name, a, b in (("dq", dq, dq_ref), ("dk", dk, dk_ref), ("dv", dv, dv_ref)):
+        assert not torch.isnan(a.float()).any(), name
+        assert _rel(a.cpu(), b) < 8e-3, (name, _rel(a.cpu(), b))
+    if lens is not None:                       # padded keys receive exactly zero gradient
+        for b, n in enumerate(lens):
+            if n < L:
+                assert dk[b, n:].abs().max().item() == 0 and dv[b, n:].abs().max().item() == 0
+
+
+def test_backward_is_deterministic_and_matches_sdpa_autograd(cuda):
+    B, H, Nq, L, d = 2, 20, 1024, 320, 112
+    q, k, v, do, bias = _problem(B, H, Nq, L, d, cuda, seed=5, lens=[250, 320])
+    a = _own(q, k, v, do, bias, H)
+    b = _own(q, k, v, do, bias, H)
+    assert all(torch.equal(x, y) for x, y in zip(a, b))
+    qg, kg, vg = [t.float().requires_grad_(True) for t in (q, k, v)]
+    sp = lambda t, T: t.view(B, T, H, d).transpose(1, 2)  # noqa: E731
+    out = torch.nn.functional.scaled_dot_product_attention(sp(qg, Nq), sp(kg, L), sp(vg, L), attn_mask=bias.view(B, 1, 1, L))
+    out.transpose(1, 2).reshape(B, Nq, H * d).backward(do.float())
+    for x, g in zip(a, (qg.grad, kg.grad, vg.grad)):
+        assert _rel(x, g) < 8e-3

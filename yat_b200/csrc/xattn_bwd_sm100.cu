@@ -316,6 +316,274 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   if (warp == 1) tmem_dealloc(tmem, kTmemCols);
 }
 
+
+// ------------------------------------------------------------------------------------------------ dkv kernel
+constexpr int kKB = 128;                      // keys per block (the lanes of S^T, dP^T, dV, dK)
+constexpr int kQdStages = 2;
+constexpr uint32_t kColST = 0, kColDPT = 128, kColDV = 256, kColDK = 384;
+
+struct DkvSmem {
+  uint8_t kvb[2][kTBytes];                    // K block | V block ([2 halves][128 keys][64]); dK | dV leave from here
+  uint8_t qd[kQdStages][2][kTBytes];          // ring of query tiles: Q_t | dO_t
+  float lq[kQdStages][kQT], dd[kQdStages][kQT];   // per query of the tile: lse * log2(e), D
+  uint64_t kvb_full, kvb_empty, qd_full[kQdStages], qd_empty[kQdStages], st_full, pds_ready, dkv_full, dkv_empty, dkv_staged;
+  uint32_t tmem_base;
+};
+constexpr int kDkvSmemBytes = (int)sizeof(DkvSmem) + 1024;
+static_assert(kDkvSmemBytes <= 232448, "xattn dkv kernel exceeds the 227 KB shared-memory limit");
+
+constexpr uint32_t kIdescTT = make_idesc_bf16(128, 128, 0, 0);   // K Q_t^T, V dO_t^T : A, B K-major
+
+struct KItem { int b, h, kb; };
+__device__ __forceinline__ KItem kdecode(int item, int n_kb, int H) {
+  KItem r;
+  r.kb = item % n_kb;
+  const int bh = item / n_kb;
+  r.h = bh % H;
+  r.b = bh / H;
+  return r;
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+xattn_dkv_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_do,
+                       const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v,
+                       const __grid_constant__ CUtensorMap tm_dk, const __grid_constant__ CUtensorMap tm_dv,
+                       const float* __restrict__ bias, const float* __restrict__ lse, const float* __restrict__ D, int B, int H,
+                       int Nq, int L, int d, float scale) {
+  extern __shared__ uint8_t smem_raw[];
+  DkvSmem& S = *reinterpret_cast<DkvSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_kb = (L + kKB - 1) / kKB, nT = (Nq + kQT - 1) / kQT;
+  const int n_items = B * H * n_kb;
+  const int nK = (d + 15) / 16;
+
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&S.kvb_full), 1);
+    mbar_init(smem_u32(&S.kvb_empty), 1);
+    for (int s = 0; s < kQdStages; ++s) {
+      mbar_init(smem_u32(&S.qd_full[s]), 1);
+      mbar_init(smem_u32(&S.qd_empty[s]), 1);
+    }
+    mbar_init(smem_u32(&S.st_full), 1);
+    mbar_init(smem_u32(&S.pds_ready), kSoftWarps);
+    mbar_init(smem_u32(&S.dkv_full), 1);
+    mbar_init(smem_u32(&S.dkv_empty), kSoftWarps);
+    mbar_init(smem_u32(&S.dkv_staged), kSoftWarps);
+    fence_barrier_init();
+    tma_prefetch_desc(&tm_q); tma_prefetch_desc(&tm_do); tma_prefetch_desc(&tm_k); tma_prefetch_desc(&tm_v);
+    tma_prefetch_desc(&tm_dk); tma_prefetch_desc(&tm_dv);
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(&S.tmem_base), kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (S.tmem_base != 0) __trap();
+  constexpr uint32_t tmem = 0;
+
+  if (warp == 0) {
+    // ======================= TMA producer =======================
+    if (lane == 0) {
+      uint32_t tt = 0, ii = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++ii) {
+        const KItem w = kdecode(item, n_kb, H);
+        mbar_wait(smem_u32(&S.kvb_empty), (ii & 1) ^ 1);
+        const uint32_t f = smem_u32(&S.kvb_full);
+        mbar_arrive_expect_tx(f, 2 * kTBytes);
+        tma_load_4d(smem_u32(&S.kvb[0][0]), &tm_k, f, 0, w.h, w.kb * kKB, w.b);
+        tma_load_4d(smem_u32(&S.kvb[0][kTHalf]), &tm_k, f, 64, w.h, w.kb * kKB, w.b);
+        tma_load_4d(smem_u32(&S.kvb[1][0]), &tm_v, f, 0, w.h, w.kb * kKB, w.b);
+        tma_load_4d(smem_u32(&S.kvb[1][kTHalf]), &tm_v, f, 64, w.h, w.kb * kKB, w.b);
+        for (int t = 0; t < nT; ++t, ++tt) {
+          const uint32_t s = tt % kQdStages, ph = (tt / kQdStages) & 1;
+          mbar_wait(smem_u32(&S.qd_empty[s]), ph ^ 1);
+          const uint32_t qf = smem_u32(&S.qd_full[s]);
+          mbar_arrive_expect_tx(qf, 2 * kTBytes);
+          tma_load_4d(smem_u32(&S.qd[s][0][0]), &tm_q, qf, 0, w.h, t * kQT, w.b);
+          tma_load_4d(smem_u32(&S.qd[s][0][kTHalf]), &tm_q, qf, 64, w.h, t * kQT, w.b);
+          tma_load_4d(smem_u32(&S.qd[s][1][0]), &tm_do, qf, 0, w.h, t * kQT, w.b);
+          tma_load_4d(smem_u32(&S.qd[s][1][kTHalf]), &tm_do, qf, 64, w.h, t * kQT, w.b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ======================= tcgen05 issuer =======================
+    if (lane == 0) {
+      uint32_t tt = 0, ii = 0;
+      const uint32_t idesc_acc = make_idesc_bf16(128, (d + 15) & ~15, 0, 1);
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++ii) {
+        mbar_wait(smem_u32(&S.kvb_full), ii & 1);
+        tc_fence_after();
+        const uint64_t ka0 = make_smem_desc(smem_u32(&S.kvb[0][0]), 16, 1024, kLayoutSw128);
+        const uint64_t va0 = make_smem_desc(smem_u32(&S.kvb[1][0]), 16, 1024, kLayoutSw128);
+        for (int t = 0; t < nT; ++t, ++tt) {
+          const uint32_t s = tt % kQdStages;
+          mbar_wait(smem_u32(&S.qd_full[s]), (tt / kQdStages) & 1);
+          tc_fence_after();
+          // S^T = K Q_t^T, dP^T = V dO_t^T (keys along the lanes, the tile's queries along the columns); in order behind
+          // the dV / dK MMAs of the previous tile, which read P^T / dS^T from the same columns
+          const uint64_t qb0 = make_smem_desc(smem_u32(&S.qd[s][0][0]), 16, 1024, kLayoutSw128);
+          const uint64_t db0 = make_smem_desc(smem_u32(&S.qd[s][1][0]), 16, 1024, kLayoutSw128);
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            if (ks < nK) {
+              const uint32_t off = ((ks >> 2) * kTHalf + (ks & 3) * 32) >> 4;
+              umma_bf16(tmem + kColST, ka0 + off, qb0 + off, kIdescTT, ks != 0);
+            }
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            if (ks < nK) {
+              const uint32_t off = ((ks >> 2) * kTHalf + (ks & 3) * 32) >> 4;
+              umma_bf16(tmem + kColDPT, va0 + off, db0 + off, kIdescTT, ks != 0);
+            }
+          tc_commit(smem_u32(&S.st_full));
+          mbar_wait(smem_u32(&S.pds_ready), tt & 1);
+          if (t == 0) mbar_wait(smem_u32(&S.dkv_empty), (ii & 1) ^ 1);    // the previous item's dV / dK have left TMEM
+          tc_fence_after();
+          // dV += P^T dO_t, dK += dS^T Q_t: A from tensor memory (16 queries of K step ks as 8 packed columns at
+          // 64 (ks >> 2) + 32 ((ks >> 1) & 1) + 8 (ks & 1)), B = the tile MN-major (K step of 16 query rows = 2 KB)
+          const uint64_t dob = make_smem_desc(smem_u32(&S.qd[s][1][0]), kTHalf, 1024, kLayoutSw128);
+          const uint64_t qmb = make_smem_desc(smem_u32(&S.qd[s][0][0]), kTHalf, 1024, kLayoutSw128);
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint32_t acol = 64 * (ks >> 2) + 32 * ((ks >> 1) & 1) + 8 * (ks & 1);
+            umma_bf16_ts(tmem + kColDV, tmem + kColST + acol, dob + ((ks * 2048) >> 4), idesc_acc, (t | ks) != 0);
+          }
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint32_t acol = 64 * (ks >> 2) + 32 * ((ks >> 1) & 1) + 8 * (ks & 1);
+            umma_bf16_ts(tmem + kColDK, tmem + kColDPT + acol, qmb + ((ks * 2048) >> 4), idesc_acc, (t | ks) != 0);
+          }
+          tc_commit(smem_u32(&S.qd_empty[s]));
+          if (t == nT - 1) tc_commit(smem_u32(&S.dkv_full));
+        }
+      }
+    }
+  } else if (warp == kStoreWarp) {
+    // ======================= dK / dV stores =======================
+    if (lane == 0) {
+      uint32_t ii = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++ii) {
+        const KItem w = kdecode(item, n_kb, H);
+        mbar_wait(smem_u32(&S.dkv_staged), ii & 1);
+        tma_store_4d(&tm_dk, smem_u32(&S.kvb[0][0]), 0, w.h, w.kb * kKB, w.b);
+        tma_store_4d(&tm_dv, smem_u32(&S.kvb[1][0]), 0, w.h, w.kb * kKB, w.b);
+        if (d > 64) {
+          tma_store_4d(&tm_dk, smem_u32(&S.kvb[0][kTHalf]), 64, w.h, w.kb * kKB, w.b);
+          tma_store_4d(&tm_dv, smem_u32(&S.kvb[1][kTHalf]), 64, w.h, w.kb * kKB, w.b);
+        }
+        tma_store_commit();
+        tma_store_wait_read<0>();
+        mbar_arrive(smem_u32(&S.kvb_empty));        // the next item's K / V blocks may land
+      }
+      tma_store_wait_all<0>();
+    }
+  } else {
+    // ======================= P^T / dS^T + epilogue warps =======================
+    const int te = threadIdx.x - 64;              // 0..255
+    const int wg = te >> 7;                       // which 64 of the tile's 128 queries / which half of dV, dK
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;             // key row of the block (TMEM lane)
+    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    const f2 cs2 = bc2(scale * kLog2e);
+    uint32_t tt = 0, ii = 0;
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++ii) {
+      const KItem w = kdecode(item, n_kb, H);
+      const int key = w.kb * kKB + row;
+      const float bk = key < L ? (bias ? __ldg(bias + (int64_t)w.b * L + key) * kLog2e : 0.f) : -INFINITY;
+      const float* lrow = lse + ((int64_t)w.b * H + w.h) * Nq;
+      const float* drow = D + ((int64_t)w.b * H + w.h) * Nq;
+      // per-query vectors of tile 0 (the vectors of tile t + 1 are fetched while tile t is processed)
+      {
+        const int qq = te & 127;
+        const float x = qq < Nq ? (te < 128 ? __ldg(lrow + qq) * kLog2e : __ldg(drow + qq)) : 0.f;
+        (te < 128 ? S.lq : S.dd)[tt % kQdStages][qq] = x;
+        named_bar_sync(1, kSoftThreads);
+      }
+      for (int t = 0; t < nT; ++t, ++tt) {
+        const uint32_t s = tt % kQdStages;
+        float nxt = 0.f;
+        if (t + 1 < nT) {
+          const int qq = (t + 1) * kQT + (te & 127);
+          if (qq < Nq) nxt = te < 128 ? __ldg(lrow + qq) * kLog2e : __ldg(drow + qq);
+        }
+        mbar_wait(smem_u32(&S.st_full), tt & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          uint32_t rs[32], rp[32];
+          const uint32_t col = wg * 64 + hh * 32;
+          tmem_ld32(tmem + lane_base + kColST + col, rs);
+          tmem_ld32(tmem + lane_base + kColDPT + col, rp);
+          tmem_ld_wait();
+          const float4* l4 = reinterpret_cast<const float4*>(&S.lq[s][col]);
+          const float4* d4 = reinterpret_cast<const float4*>(&S.dd[s][col]);
+          uint32_t pp[16], ps[16];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 ll = l4[i], dv4 = d4[i];
+            float a0, a1, a2, a3;
+            un2(fma2(mk2(__uint_as_float(rs[4 * i]), __uint_as_float(rs[4 * i + 1])), cs2, mk2(bk - ll.x, bk - ll.y)), a0, a1);
+            un2(fma2(mk2(__uint_as_float(rs[4 * i + 2]), __uint_as_float(rs[4 * i + 3])), cs2, mk2(bk - ll.z, bk - ll.w)), a2, a3);
+            const f2 p01 = mk2(ex2(a0), ex2(a1)), p23 = mk2(ex2(a2), ex2(a3));
+            pp[2 * i] = pack2(p01);
+            pp[2 * i + 1] = pack2(p23);
+            ps[2 * i] = pack2(mul2(p01, add2(mk2(__uint_as_float(rp[4 * i]), __uint_as_float(rp[4 * i + 1])), mk2(-dv4.x, -dv4.y))));
+            ps[2 * i + 1] = pack2(mul2(p23, add2(mk2(__uint_as_float(rp[4 * i + 2]), __uint_as_float(rp[4 * i + 3])), mk2(-dv4.z, -dv4.w))));
+          }
+          tmem_st16(tmem + lane_base + kColST + col, pp);
+          tmem_st16(tmem + lane_base + kColDPT + col, ps);
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&S.pds_ready));
+        if (t + 1 < nT) {                       // the other stage's vectors were last read two tiles ago
+          (te < 128 ? S.lq : S.dd)[(tt + 1) % kQdStages][te & 127] = nxt;
+          named_bar_sync(1, kSoftThreads);
+        }
+      }
+      // ---- epilogue: dV, scale dK -> bf16 -> the K / V block buffers -> store warp
+      mbar_wait(smem_u32(&S.dkv_full), ii & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int which = 0; which < 2; ++which) {   // 0: dK (scaled) into kvb[0]; 1: dV into kvb[1]
+        uint32_t ra[32], rb[32];
+        const uint32_t col = (which ? kColDV : kColDK) + wg * 64;
+        tmem_ld32(tmem + lane_base + col, ra);
+        tmem_ld32(tmem + lane_base + col + 32, rb);
+        tmem_ld_wait();
+        const float f = which ? 1.f : scale;
+        uint8_t* orow = &S.kvb[which][wg * kTHalf + row * 128];
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint32_t wa[4], wb[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            wa[i] = pack_bf16(__uint_as_float(ra[g * 8 + 2 * i]) * f, __uint_as_float(ra[g * 8 + 2 * i + 1]) * f);
+            wb[i] = pack_bf16(__uint_as_float(rb[g * 8 + 2 * i]) * f, __uint_as_float(rb[g * 8 + 2 * i + 1]) * f);
+          }
+          *reinterpret_cast<uint4*>(orow + ((g ^ (row & 7)) << 4)) = make_uint4(wa[0], wa[1], wa[2], wa[3]);
+          *reinterpret_cast<uint4*>(orow + (((4 + g) ^ (row & 7)) << 4)) = make_uint4(wb[0], wb[1], wb[2], wb[3]);
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(smem_u32(&S.dkv_empty));
+        mbar_arrive(smem_u32(&S.dkv_staged));
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, kTmemCols);
+}
+
 }  // namespace
 }  // namespace yat
 
@@ -360,5 +628,23 @@ extern "C" int yat_xattn_bwd(const void* q, const void* k, const void* v, const 
       tq, tdo, tk, tv, tdq, (const float*)bias, (const float*)lse, D, B, H, Nq, L, d, scale);
   rc = check_launch("xattn_dq_sm100");
   if (rc != YAT_OK) return rc;
-  return YAT_OK;
+  if (dk == nullptr) return YAT_OK;
+  CUtensorMap tq2, tdo2, tk2, tv2, tdk, tdv;      // the dkv kernel reads 128-row boxes of everything
+  if ((rc = make_tmap_heads_bf16(&tq2, q, d, H, Nq, B, (uint64_t)ldq, kQT)) != YAT_OK) return rc;
+  if ((rc = make_tmap_heads_bf16(&tdo2, d_o, d, H, Nq, B, C, kQT)) != YAT_OK) return rc;
+  if ((rc = make_tmap_heads_bf16(&tk2, k, d, H, L, B, (uint64_t)ldkv, kKB)) != YAT_OK) return rc;
+  if ((rc = make_tmap_heads_bf16(&tv2, v, d, H, L, B, (uint64_t)ldkv, kKB)) != YAT_OK) return rc;
+  if ((rc = make_tmap_heads_bf16(&tdk, dk, d, H, L, B, C, kKB)) != YAT_OK) return rc;
+  if ((rc = make_tmap_heads_bf16(&tdv, dv, d, H, L, B, C, kKB)) != YAT_OK) return rc;
+  static bool attr2_set = false;
+  if (!attr2_set) {
+    cudaError_t e = cudaFuncSetAttribute(xattn_dkv_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDkvSmemBytes);
+    YAT_REQUIRE(e == cudaSuccess, YAT_ERR_CUDA, "yat_xattn_bwd: cannot reserve %d B of shared memory (%s)", kDkvSmemBytes,
+                cudaGetErrorString(e));
+    attr2_set = true;
+  }
+  const int kitems = B * H * ((L + kKB - 1) / kKB);
+  xattn_dkv_sm100_kernel<<<kitems < kNumSMs ? kitems : kNumSMs, kThreads, kDkvSmemBytes, st>>>(
+      tq2, tdo2, tk2, tv2, tdk, tdv, (const float*)bias, (const float*)lse, D, B, H, Nq, L, d, scale);
+  return check_launch("xattn_dkv_sm100");
 }
