@@ -102,3 +102,37 @@ def test_backward_is_deterministic_and_matches_sdpa_autograd(cuda):
     out.transpose(1, 2).reshape(B, Nq, H * d).backward(do.float())
     for x, g in zip(a, (qg.grad, kg.grad, vg.grad)):
         assert _rel(x, g) < 8e-3
+
+
+def test_processor_opt_in_own_backward_matches_the_library_path(cuda):
+    """AttnProcessor2_0(own_backward=True): forward and every gradient of the attn2 module on the own kernels against the
+    default training path (cuDNN SDPA with the folded key bias)."""
+    from yat_b200 import _lib
+    from yat_b200.attention import Attention, AttnProcessor2_0
+    torch.manual_seed(0)
+    a1 = Attention(query_dim=224, cross_attention_dim=224, heads=2, dim_head=112, bias=True, processor=AttnProcessor2_0())
+    a1 = a1.to(cuda).to(torch.bfloat16)
+    p2 = AttnProcessor2_0()
+    p2.own_backward = True
+    a2 = Attention(query_dim=224, cross_attention_dim=224, heads=2, dim_head=112, bias=True, processor=p2).to(cuda).to(torch.bfloat16)
+    a2.load_state_dict(a1.state_dict())
+    x = torch.randn((3, 300, 224), device=cuda, dtype=torch.bfloat16)
+    enc = torch.randn((3, 77, 224), device=cuda, dtype=torch.bfloat16)
+    mask = torch.zeros((3, 1, 77), device=cuda, dtype=torch.bfloat16)
+    mask[1, :, 30:] = -10000.0
+    x1, x2 = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    e1, e2 = enc.clone().requires_grad_(True), enc.clone().requires_grad_(True)
+    before = _lib.launch_counts["yat_xattn_bwd"]
+    y1 = a1(x1, encoder_hidden_states=e1, attention_mask=mask)
+    y2 = a2(x2, encoder_hidden_states=e2, attention_mask=mask)
+    g = torch.randn_like(y1)
+    y1.backward(g)
+    y2.backward(g)
+    assert _lib.launch_counts["yat_xattn_bwd"] == before + 1
+    assert _rel(y2, y1) < 6e-3 and _rel(x2.grad, x1.grad) < 1e-2 and _rel(e2.grad, e1.grad) < 1e-2
+    ref_scale = a1.to_v.bias.grad.float().abs().max().item()
+    for (n1, q1), (_, q2) in zip(a1.named_parameters(), a2.named_parameters()):
+        if n1 == "to_k.bias":      # exactly zero in exact arithmetic (sum_j dS_ij = 0: softmax is shift-invariant): rounding noise
+            assert q1.grad.float().abs().max().item() < 0.05 * ref_scale and q2.grad.float().abs().max().item() < 0.05 * ref_scale
+            continue
+        assert _rel(q2.grad, q1.grad) < 1e-2, n1

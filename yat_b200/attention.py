@@ -180,6 +180,52 @@ def _xattn_own_forward(q, k, v, bias, H, d):
     return out
 
 
+class _XAttnOwn(torch.autograd.Function):
+    """Cross-attention with both directions on the own tcgen05 kernels (yat_xattn_fwd / yat_xattn_bwd).  Opt-in
+    (``AttnProcessor2_0.own_backward``): measured slower than the library backward."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, bias_f, H):
+        B, N, C = q.shape
+        L, d = k.shape[1], C // H
+        out = torch.empty((B, N, C), dtype=torch.bfloat16, device=q.device)
+        lse = torch.empty((B, H, N), dtype=torch.float32, device=q.device)
+        with _lib.timed("xattn_fwd"):
+            rc = _lib.lib().yat_xattn_fwd(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(bias_f), B, H, N, L, d, q.stride(1),
+                                          k.stride(1), float(d) ** -0.5, _lib.ptr(out), _lib.ptr(lse), _lib.current_stream())
+        _lib.check(rc, "yat_xattn_fwd")
+        ctx.save_for_backward(q, k, v, bias_f, out, lse)
+        ctx.H = H
+        return out
+
+    @staticmethod
+    def backward(ctx, do):
+        q, k, v, bias_f, out, lse = ctx.saved_tensors
+        H = ctx.H
+        B, N, C = q.shape
+        L, d = k.shape[1], C // H
+        do = do.contiguous()
+        dq = torch.empty((B, N, C), dtype=torch.bfloat16, device=q.device)
+        dk = torch.empty((B, L, C), dtype=torch.bfloat16, device=q.device)
+        dv = torch.empty((B, L, C), dtype=torch.bfloat16, device=q.device)
+        lib = _lib.lib()
+        ws = torch.empty(lib.yat_xattn_bwd_workspace_bytes(B, H, N), dtype=torch.uint8, device=q.device)
+        with _lib.timed("xattn_bwd"):
+            rc = lib.yat_xattn_bwd(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(bias_f), _lib.ptr(out), _lib.ptr(lse),
+                                   _lib.ptr(do), B, H, N, L, d, q.stride(1), k.stride(1), float(d) ** -0.5, _lib.ptr(dq),
+                                   _lib.ptr(dk), _lib.ptr(dv), _lib.ptr(ws), _lib.current_stream())
+        _lib.check(rc, "yat_xattn_bwd")
+        return dq, dk, dv, None, None
+
+
+def _xattn_layout_ok(q, k, v, d):
+    return (k.shape[1] <= _lib.lib().yat_xattn_max_keys() and d <= 128
+            and q.stride(2) == 1 and k.stride(2) == 1 and v.stride(2) == 1 and k.stride(1) == v.stride(1)
+            and q.stride(0) == q.shape[1] * q.stride(1) and k.stride(0) == k.shape[1] * k.stride(1)
+            and v.stride(0) == v.shape[1] * v.stride(1) and q.stride(1) % 8 == 0 and k.stride(1) % 8 == 0
+            and q.data_ptr() % 16 == 0 and k.data_ptr() % 16 == 0 and v.data_ptr() % 16 == 0)
+
+
 def _xattn_own_ok(q, k, v, d):
     return (not (torch.is_grad_enabled() and (q.requires_grad or k.requires_grad or v.requires_grad))
             and k.shape[1] <= _lib.lib().yat_xattn_max_keys() and d <= 128
@@ -193,6 +239,7 @@ class AttnProcessor2_0:
     """Softmax scaled-dot-product attention (diffusers ``AttnProcessor2_0`` semantics)."""
     fold_key_mask = True
     own_forward = True          # no-grad forwards (exploration trials, the frozen preservation pass, sampling): yat_xattn_fwd
+    own_backward = False        # training forward + backward on yat_xattn_fwd / yat_xattn_bwd (opt-in: slower than cuDNN's)
 
     def __call__(self, attn, hidden_states, encoder_hidden_states=None, attention_mask=None):
         B = hidden_states.shape[0]
@@ -205,7 +252,10 @@ class AttnProcessor2_0:
         if (attention_mask is not None and self.fold_key_mask and query.is_cuda and query.dtype == torch.bfloat16
                 and attn.norm_q is None and attn.norm_k is None and d % 8 == 0
                 and attention_mask.numel() == B * attention_mask.shape[-1]):
-            if self.own_forward and _xattn_own_ok(query, key, value, d):
+            if self.own_backward and torch.is_grad_enabled() and _xattn_layout_ok(query, key, value, d):
+                bias_f = attention_mask.reshape(B, -1).float().contiguous()
+                out = _XAttnOwn.apply(query, key, value, bias_f, attn.heads)
+            elif self.own_forward and _xattn_own_ok(query, key, value, d):
                 out = _xattn_own_forward(query, key, value, attention_mask, attn.heads, d)
             else:
                 out = _sdpa_key_bias_folded(query, key, value, attention_mask.view(B, 1, 1, -1).to(query.dtype),

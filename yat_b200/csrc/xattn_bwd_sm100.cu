@@ -237,20 +237,36 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
     const f2 cs2 = bc2(scale * kLog2e);
     uint32_t qi = 0, sd_use[2] = {0, 0};
-    int bias_b = -1;
-    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi) {
+    // per-item scalars and the sample's bias row are fetched one item ahead (registers), so no global latency sits between
+    // two items; the bias row alternates between two shared-memory buffers
+    auto fetch = [&](int item, float& l2, float& dn, float& b0, float& b1) {
       const Item w = decode(item, n_qt, H);
       const bool valid = w.q0 + row < Nq;
       const int64_t vi = ((int64_t)w.b * H + w.h) * Nq + w.q0 + row;
-      const float lse2 = valid ? __ldg(lse + vi) * kLog2e : 0.f;
-      const f2 nd2 = bc2(valid ? -__ldg(D + vi) : 0.f);
-      if (w.b != bias_b) {                        // the bias row of this sample (items of a CTA change sample rarely)
-        named_bar_sync(1, kSoftThreads);          // nobody still reads the old row
-        for (int j = te; j < nC * kKC; j += kSoftThreads)
-          S.bias2[0][j] = j < L ? (bias ? __ldg(bias + (int64_t)w.b * L + j) * kLog2e : 0.f) : -INFINITY;
-        named_bar_sync(1, kSoftThreads);
-        bias_b = w.b;
+      l2 = valid ? __ldg(lse + vi) * kLog2e : 0.f;
+      dn = valid ? -__ldg(D + vi) : 0.f;
+      b0 = b1 = 0.f;
+      if (bias != nullptr) {
+        if (te < L) b0 = __ldg(bias + (int64_t)w.b * L + te);
+        if (te + kSoftThreads < L) b1 = __ldg(bias + (int64_t)w.b * L + te + kSoftThreads);
       }
+    };
+    auto put_bias = [&](uint32_t n, float b0, float b1) {
+      if (te < nC * kKC) S.bias2[n & 1][te] = te < L ? b0 * kLog2e : -INFINITY;
+      if (te + kSoftThreads < nC * kKC) S.bias2[n & 1][te + kSoftThreads] = te + kSoftThreads < L ? b1 * kLog2e : -INFINITY;
+    };
+    float n_l2 = 0.f, n_dn = 0.f, n_b0 = 0.f, n_b1 = 0.f;
+    if ((int)blockIdx.x < n_items) {
+      fetch(blockIdx.x, n_l2, n_dn, n_b0, n_b1);
+      put_bias(0, n_b0, n_b1);
+      named_bar_sync(1, kSoftThreads);
+    }
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi) {
+      const float lse2 = n_l2;
+      const f2 nd2 = bc2(n_dn);
+      const float* bs = S.bias2[qi & 1];
+      const bool has_next = item + (int)gridDim.x < n_items;
+      if (has_next) fetch(item + gridDim.x, n_l2, n_dn, n_b0, n_b1);
       for (int j = 0; j < nC; ++j) {
         const uint32_t b = j & 1;
         mbar_wait(smem_u32(&S.sd_full[b]), sd_use[b] & 1);
@@ -261,7 +277,7 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         tmem_ld32(base, rs);
         tmem_ld32(base + 64, rp);
         tmem_ld_wait();
-        const float4* b4 = reinterpret_cast<const float4*>(&S.bias2[0][j * kKC + wg * 32]);
+        const float4* b4 = reinterpret_cast<const float4*>(bs + j * kKC + wg * 32);
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -281,6 +297,8 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&S.ds_ready[b]));
       }
+      if (has_next) put_bias(qi + 1, n_b0, n_b1);     // that buffer was last read in the previous item (a barrier ago)
+      named_bar_sync(1, kSoftThreads);
       // ---- epilogue: scale dQ -> bf16 -> the item's Q buffer -> store thread
       mbar_wait(smem_u32(&S.dq_full), qi & 1);
       tc_fence_after();
