@@ -101,6 +101,34 @@ e1.record()
 torch.cuda.synchronize()
 print(f"host {host_us:.1f} us per call (queueing only); back to back {e0.elapsed_time(e1) * 20:.1f} us per call")
 
+# backward: own (prep + dq + dkv) against the library path's backward (fwd + bwd of the folded SDPA minus its fwd)
+do = torch.randn_like(q)
+dq_, dk_, dv_ = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+ws = torch.empty(L.yat_xattn_bwd_workspace_bytes(B, H, Nq), dtype=torch.uint8, device=dev)
+run(True)
+
+
+def run_bwd(with_dkv=True):
+    rc = L.yat_xattn_bwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), bias.data_ptr(), o.data_ptr(), lse.data_ptr(), do.data_ptr(), B, H,
+                         Nq, Lk, d, C, C, d ** -0.5, dq_.data_ptr(), dk_.data_ptr() if with_dkv else None,
+                         dv_.data_ptr() if with_dkv else None, ws.data_ptr(), st)
+    assert rc == 0, rc
+
+
+qg, kg, vg = [t.clone().requires_grad_(True) for t in (q, k, v)]
+
+
+def lib_fwd_bwd():
+    y = _sdpa_key_bias_folded(qg, kg, vg, bias4, H, d)
+    torch.autograd.grad(y, (qg, kg, vg), do)
+
+
+with torch.no_grad():
+    lib_f = timeit(lambda: _sdpa_key_bias_folded(q, k, v, bias4, H, d))
+lib_fb = timeit(lib_fwd_bwd)
+print(f"backward: own {timeit(run_bwd):.1f} us (prep + dq only {timeit(lambda: run_bwd(False)):.1f} us); "
+      f"library fwd + bwd {lib_fb:.1f} us, fwd {lib_f:.1f} us -> bwd {lib_fb - lib_f:.1f} us")
+
 # the same comparison at the power-capped clock the training step runs at: a GEMM burn before each arm, SM clock sampled by NVML
 import pynvml  # noqa: E402
 pynvml.nvmlInit()
@@ -134,31 +162,3 @@ with torch.no_grad():
         a_us, a_mhz = capped(lambda: run(True))
         b_us, b_mhz = capped(lambda: _sdpa_key_bias_folded(q, k, v, bias4, H, d))
         print(f"after a GEMM burn: own {a_us:.1f} us @ {a_mhz} MHz, library path {b_us:.1f} us @ {b_mhz} MHz")
-
-# backward: own (prep + dq + dkv) against the library path's backward (fwd + bwd of the folded SDPA minus its fwd)
-do = torch.randn_like(q)
-dq_, dk_, dv_ = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
-ws = torch.empty(L.yat_xattn_bwd_workspace_bytes(B, H, Nq), dtype=torch.uint8, device=dev)
-run(True)
-
-
-def run_bwd(with_dkv=True):
-    rc = L.yat_xattn_bwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), bias.data_ptr(), o.data_ptr(), lse.data_ptr(), do.data_ptr(), B, H,
-                         Nq, Lk, d, C, C, d ** -0.5, dq_.data_ptr(), dk_.data_ptr() if with_dkv else None,
-                         dv_.data_ptr() if with_dkv else None, ws.data_ptr(), st)
-    assert rc == 0, rc
-
-
-qg, kg, vg = [t.clone().requires_grad_(True) for t in (q, k, v)]
-
-
-def lib_fwd_bwd():
-    y = _sdpa_key_bias_folded(qg, kg, vg, bias4, H, d)
-    torch.autograd.grad(y, (qg, kg, vg), do)
-
-
-with torch.no_grad():
-    lib_f = timeit(lambda: _sdpa_key_bias_folded(q, k, v, bias4, H, d))
-lib_fb = timeit(lib_fwd_bwd)
-print(f"backward: own {timeit(run_bwd):.1f} us (prep + dq only {timeit(lambda: run_bwd(False)):.1f} us); "
-      f"library fwd + bwd {lib_fb:.1f} us, fwd {lib_f:.1f} us -> bwd {lib_fb - lib_f:.1f} us")

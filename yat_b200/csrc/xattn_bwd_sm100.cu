@@ -344,7 +344,8 @@ struct DkvSmem {
   uint8_t kvb[2][kTBytes];                    // K block | V block ([2 halves][128 keys][64]); dK | dV leave from here
   uint8_t qd[kQdStages][2][kTBytes];          // ring of query tiles: Q_t | dO_t
   float lq[kQdStages][kQT], dd[kQdStages][kQT];   // per query of the tile: lse * log2(e), D
-  uint64_t kvb_full, kvb_empty, qd_full[kQdStages], qd_empty[kQdStages], st_full, pds_ready, dkv_full, dkv_empty, dkv_staged;
+  uint64_t kvb_full, kvb_empty, qd_full[kQdStages], qd_empty[kQdStages], st_full, dpt_full, p_ready, ds_ready;
+  uint64_t dkv_full, dkv_empty, dkv_staged;
   uint32_t tmem_base;
 };
 constexpr int kDkvSmemBytes = (int)sizeof(DkvSmem) + 1024;
@@ -383,7 +384,9 @@ xattn_dkv_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
       mbar_init(smem_u32(&S.qd_empty[s]), 1);
     }
     mbar_init(smem_u32(&S.st_full), 1);
-    mbar_init(smem_u32(&S.pds_ready), kSoftWarps);
+    mbar_init(smem_u32(&S.dpt_full), 1);
+    mbar_init(smem_u32(&S.p_ready), kSoftWarps);
+    mbar_init(smem_u32(&S.ds_ready), kSoftWarps);
     mbar_init(smem_u32(&S.dkv_full), 1);
     mbar_init(smem_u32(&S.dkv_empty), kSoftWarps);
     mbar_init(smem_u32(&S.dkv_staged), kSoftWarps);
@@ -436,45 +439,59 @@ xattn_dkv_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
         tc_fence_after();
         const uint64_t ka0 = make_smem_desc(smem_u32(&S.kvb[0][0]), 16, 1024, kLayoutSw128);
         const uint64_t va0 = make_smem_desc(smem_u32(&S.kvb[1][0]), 16, 1024, kLayoutSw128);
-        for (int t = 0; t < nT; ++t, ++tt) {
-          const uint32_t s = tt % kQdStages;
-          mbar_wait(smem_u32(&S.qd_full[s]), (tt / kQdStages) & 1);
+        // Two-phase hand-shake with the softmax warps (phase 1 reads S^T and writes P^T over it, phase 2 reads dP^T and writes
+        // dS^T over it), single TMEM buffers, everything overlapped through the in-order tensor pipe:
+        //   S^T_0 dP^T_0 | [P^T_t] dV_t  S^T_{t+1} | [dS^T_t] dK_t  dP^T_{t+1} | ...
+        auto issue_st = [&](uint32_t n) {          // S^T = K Q_t^T (keys along the lanes, the tile's queries along the columns)
+          const uint32_t s = n % kQdStages;
+          mbar_wait(smem_u32(&S.qd_full[s]), (n / kQdStages) & 1);
           tc_fence_after();
-          // S^T = K Q_t^T, dP^T = V dO_t^T (keys along the lanes, the tile's queries along the columns); in order behind
-          // the dV / dK MMAs of the previous tile, which read P^T / dS^T from the same columns
           const uint64_t qb0 = make_smem_desc(smem_u32(&S.qd[s][0][0]), 16, 1024, kLayoutSw128);
-          const uint64_t db0 = make_smem_desc(smem_u32(&S.qd[s][1][0]), 16, 1024, kLayoutSw128);
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks)
             if (ks < nK) {
               const uint32_t off = ((ks >> 2) * kTHalf + (ks & 3) * 32) >> 4;
               umma_bf16(tmem + kColST, ka0 + off, qb0 + off, kIdescTT, ks != 0);
             }
+          tc_commit(smem_u32(&S.st_full));
+        };
+        auto issue_dpt = [&](uint32_t n) {         // dP^T = V dO_t^T (the tile's qd_full has been observed by issue_st)
+          const uint32_t s = n % kQdStages;
+          const uint64_t db0 = make_smem_desc(smem_u32(&S.qd[s][1][0]), 16, 1024, kLayoutSw128);
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks)
             if (ks < nK) {
               const uint32_t off = ((ks >> 2) * kTHalf + (ks & 3) * 32) >> 4;
               umma_bf16(tmem + kColDPT, va0 + off, db0 + off, kIdescTT, ks != 0);
             }
-          tc_commit(smem_u32(&S.st_full));
-          mbar_wait(smem_u32(&S.pds_ready), tt & 1);
-          if (t == 0) mbar_wait(smem_u32(&S.dkv_empty), (ii & 1) ^ 1);    // the previous item's dV / dK have left TMEM
-          tc_fence_after();
+          tc_commit(smem_u32(&S.dpt_full));
+        };
+        issue_st(tt);
+        issue_dpt(tt);
+        for (int t = 0; t < nT; ++t, ++tt) {
+          const uint32_t s = tt % kQdStages;
           // dV += P^T dO_t, dK += dS^T Q_t: A from tensor memory (16 queries of K step ks as 8 packed columns at
           // 64 (ks >> 2) + 32 ((ks >> 1) & 1) + 8 (ks & 1)), B = the tile MN-major (K step of 16 query rows = 2 KB)
           const uint64_t dob = make_smem_desc(smem_u32(&S.qd[s][1][0]), kTHalf, 1024, kLayoutSw128);
           const uint64_t qmb = make_smem_desc(smem_u32(&S.qd[s][0][0]), kTHalf, 1024, kLayoutSw128);
+          mbar_wait(smem_u32(&S.p_ready), tt & 1);
+          if (t == 0) mbar_wait(smem_u32(&S.dkv_empty), (ii & 1) ^ 1);    // the previous item's dV / dK have left TMEM
+          tc_fence_after();
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks) {
             const uint32_t acol = 64 * (ks >> 2) + 32 * ((ks >> 1) & 1) + 8 * (ks & 1);
             umma_bf16_ts(tmem + kColDV, tmem + kColST + acol, dob + ((ks * 2048) >> 4), idesc_acc, (t | ks) != 0);
           }
+          if (t + 1 < nT) issue_st(tt + 1);         // behind dV_t in the pipe: the S^T columns are free
+          mbar_wait(smem_u32(&S.ds_ready), tt & 1);
+          tc_fence_after();
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks) {
             const uint32_t acol = 64 * (ks >> 2) + 32 * ((ks >> 1) & 1) + 8 * (ks & 1);
             umma_bf16_ts(tmem + kColDK, tmem + kColDPT + acol, qmb + ((ks * 2048) >> 4), idesc_acc, (t | ks) != 0);
           }
           tc_commit(smem_u32(&S.qd_empty[s]));
+          if (t + 1 < nT) issue_dpt(tt + 1);        // behind dK_t: the dP^T columns are free
           if (t == nT - 1) tc_commit(smem_u32(&S.dkv_full));
         }
       }
@@ -527,37 +544,58 @@ xattn_dkv_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
           const int qq = (t + 1) * kQT + (te & 127);
           if (qq < Nq) nxt = te < 128 ? __ldg(lrow + qq) * kLog2e : __ldg(drow + qq);
         }
+        // phase 1: S^T -> p (kept in registers), P^T (bf16 pairs) over the first 16 of each 32 score columns
         mbar_wait(smem_u32(&S.st_full), tt & 1);
         tc_fence_after();
+        f2 pr[2][16];
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {
-          uint32_t rs[32], rp[32];
+          uint32_t rs[32];
           const uint32_t col = wg * 64 + hh * 32;
           tmem_ld32(tmem + lane_base + kColST + col, rs);
-          tmem_ld32(tmem + lane_base + kColDPT + col, rp);
           tmem_ld_wait();
           const float4* l4 = reinterpret_cast<const float4*>(&S.lq[s][col]);
-          const float4* d4 = reinterpret_cast<const float4*>(&S.dd[s][col]);
-          uint32_t pp[16], ps[16];
+          uint32_t pp[16];
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
-            const float4 ll = l4[i], dv4 = d4[i];
+            const float4 ll = l4[i];
             float a0, a1, a2, a3;
             un2(fma2(mk2(__uint_as_float(rs[4 * i]), __uint_as_float(rs[4 * i + 1])), cs2, mk2(bk - ll.x, bk - ll.y)), a0, a1);
             un2(fma2(mk2(__uint_as_float(rs[4 * i + 2]), __uint_as_float(rs[4 * i + 3])), cs2, mk2(bk - ll.z, bk - ll.w)), a2, a3);
-            const f2 p01 = mk2(ex2(a0), ex2(a1)), p23 = mk2(ex2(a2), ex2(a3));
-            pp[2 * i] = pack2(p01);
-            pp[2 * i + 1] = pack2(p23);
-            ps[2 * i] = pack2(mul2(p01, add2(mk2(__uint_as_float(rp[4 * i]), __uint_as_float(rp[4 * i + 1])), mk2(-dv4.x, -dv4.y))));
-            ps[2 * i + 1] = pack2(mul2(p23, add2(mk2(__uint_as_float(rp[4 * i + 2]), __uint_as_float(rp[4 * i + 3])), mk2(-dv4.z, -dv4.w))));
+            pr[hh][2 * i] = mk2(ex2(a0), ex2(a1));
+            pr[hh][2 * i + 1] = mk2(ex2(a2), ex2(a3));
+            pp[2 * i] = pack2(pr[hh][2 * i]);
+            pp[2 * i + 1] = pack2(pr[hh][2 * i + 1]);
           }
           tmem_st16(tmem + lane_base + kColST + col, pp);
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&S.p_ready));
+        // phase 2: dP^T -> dS^T = p (dP^T - D) over the dP^T columns
+        mbar_wait(smem_u32(&S.dpt_full), tt & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          uint32_t rp[32];
+          const uint32_t col = wg * 64 + hh * 32;
+          tmem_ld32(tmem + lane_base + kColDPT + col, rp);
+          tmem_ld_wait();
+          const float4* d4 = reinterpret_cast<const float4*>(&S.dd[s][col]);
+          uint32_t ps[16];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 dv4 = d4[i];
+            ps[2 * i] = pack2(mul2(pr[hh][2 * i], add2(mk2(__uint_as_float(rp[4 * i]), __uint_as_float(rp[4 * i + 1])), mk2(-dv4.x, -dv4.y))));
+            ps[2 * i + 1] = pack2(mul2(pr[hh][2 * i + 1], add2(mk2(__uint_as_float(rp[4 * i + 2]), __uint_as_float(rp[4 * i + 3])), mk2(-dv4.z, -dv4.w))));
+          }
           tmem_st16(tmem + lane_base + kColDPT + col, ps);
         }
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&S.pds_ready));
+        if (lane == 0) mbar_arrive(smem_u32(&S.ds_ready));
         if (t + 1 < nT) {                       // the other stage's vectors were last read two tiles ago
           (te < 128 ? S.lq : S.dd)[(tt + 1) % kQdStages][te & 127] = nxt;
           named_bar_sync(1, kSoftThreads);
