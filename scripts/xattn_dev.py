@@ -162,3 +162,15 @@ with torch.no_grad():
         a_us, a_mhz = capped(lambda: run(True))
         b_us, b_mhz = capped(lambda: _sdpa_key_bias_folded(q, k, v, bias4, H, d))
         print(f"after a GEMM burn: own {a_us:.1f} us @ {a_mhz} MHz, library path {b_us:.1f} us @ {b_mhz} MHz")
+
+# per-kernel durations of one backward call
+from torch.profiler import ProfilerActivity, profile  # noqa: E402
+run_bwd()
+torch.cuda.synchronize()
+with profile(activities=[ProfilerActivity.CUDA]) as prof:
+    for _ in range(5):
+        run_bwd()
+    torch.cuda.synchronize()
+for ev in prof.key_averages():
+    if ev.device_time_total > 0:
+        print(f"   {ev.key[:70]:70s} {ev.device_time_total / ev.count:8.1f} us x{ev.count}")

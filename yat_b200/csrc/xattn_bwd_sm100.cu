@@ -5,10 +5,10 @@
 //   dQ_i = scale sum_j dS_ij k_j        dK_j = scale sum_i dS_ij q_i        dV_j = sum_i p_ij dO_i
 // (the backward of F.scaled_dot_product_attention inside diffusers' AttnProcessor2_0, reached from
 // utils/patch_sana_attention_layers.py:100-106).  Three kernels:
-//   prep   D[b, h, i] = sum_c dO . O                                   (one warp per token row and head; HBM-bound)
-//   dq     item = (batch, head, 128-query tile): S_j = Q K_j^T and dP_j = dO V_j^T per 64-key sub-chunk into one of two
-//          tensor-memory buffers, dS_j written back over S_j by the threads that own the rows (bf16 pairs), dQ += dS_j K_j
-//          with its A operand read from tensor memory - the same feedback as the forward's P V
+//   prep   D[b, h, i] = sum_c dO . O                                   (coalesced slab loads, fixed-order sums; HBM-bound)
+//   dq     item = (batch, head, 128-query tile): S_c = Q K_c^T and dP_c = dO V_c^T per 128-key chunk, p kept in registers,
+//          dS_c written back over dP_c by the threads that own the rows (bf16 pairs), dQ += dS_c K_c with its A operand read
+//          from tensor memory - the same feedback as the forward's P V
 //   dkv    item = (batch, head, 128-key block), K and V blocks resident, looping over the query tiles: S^T = K Q_t^T and
 //          dP^T = V dO_t^T (keys along the lanes), P^T and dS^T written back over them, dV += P^T dO_t, dK += dS^T Q_t
 // No probability ever touches shared memory; every reduction over keys or queries is an MMA.
@@ -24,8 +24,6 @@ constexpr int kKC = 64;                      // keys per sub-chunk (dq kernel)
 constexpr int kMaxKeys = 384;
 constexpr int kTHalf = kQT * 128;            // [128 rows][64 cols] bf16
 constexpr int kTBytes = 2 * kTHalf;          // 32 KB
-constexpr int kCHalf = kKC * 128;            // [64 keys][64 cols] bf16
-constexpr int kCBytes = 2 * kCHalf;          // 16 KB
 constexpr int kSoftWarps = 8, kSoftThreads = 32 * kSoftWarps;
 constexpr int kStoreWarp = 2 + kSoftWarps;
 constexpr int kThreads = 32 * (kStoreWarp + 1);
@@ -39,24 +37,34 @@ __device__ __forceinline__ float ex2(float x) {
 }
 
 // ------------------------------------------------------------------------------------------------ prep: D = rowsum(dO * O)
+// Block = 8 token rows: coalesced 128-bit loads over the whole [8, H*d] slab (one fp32 partial per 8 elements into shared
+// memory), then one thread per (row, head) adds that head's d / 8 partials in a fixed order.
+constexpr int kPrepRows = 8;
 __global__ void __launch_bounds__(256) xattn_prep_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
                                                          float* __restrict__ D, int64_t rows, int H, int d, int Nq) {
-  const int lane = threadIdx.x & 31;
-  const int64_t wid = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);      // (token row, head)
-  if (wid >= rows * H) return;
-  const int64_t r = wid / H;
-  const int h = (int)(wid - r * H);
-  const uint4* po = reinterpret_cast<const uint4*>(o + (r * H + h) * d);
-  const uint4* pd = reinterpret_cast<const uint4*>(d_o + (r * H + h) * d);
-  float acc = 0.f;
-  if (lane < d / 8) {
-    const uint4 a = ld_stream(po + lane), b = ld_stream(pd + lane);
+  extern __shared__ float part[];                                         // [kPrepRows][H * d / 8]
+  const int vec_per_row = H * d / 8, vec_per_head = d / 8;
+  const int64_t r0 = (int64_t)blockIdx.x * kPrepRows;
+  const int nrows = (int)(rows - r0 < kPrepRows ? rows - r0 : kPrepRows);
+  const uint4* po = reinterpret_cast<const uint4*>(o + r0 * H * d);
+  const uint4* pd = reinterpret_cast<const uint4*>(d_o + r0 * H * d);
+  for (int i = threadIdx.x; i < nrows * vec_per_row; i += 256) {
+    const uint4 a = ld_stream(po + i), b = ld_stream(pd + i);
     const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+    float acc = 0.f;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) acc += bf16_lo(aw[i]) * bf16_lo(bw[i]) + bf16_hi(aw[i]) * bf16_hi(bw[i]);
+    for (int j = 0; j < 4; ++j) acc += bf16_lo(aw[j]) * bf16_lo(bw[j]) + bf16_hi(aw[j]) * bf16_hi(bw[j]);
+    part[i] = acc;
   }
-  acc = warp_sum(acc);
-  if (lane == 0) D[((r / Nq) * H + h) * Nq + (r % Nq)] = acc;             // [B, H, Nq] like lse
+  __syncthreads();
+  for (int i = threadIdx.x; i < nrows * H; i += 256) {
+    const int rr = i / H, h = i - rr * H;
+    const float* p = part + rr * vec_per_row + h * vec_per_head;
+    float acc = 0.f;
+    for (int j = 0; j < vec_per_head; ++j) acc += p[j];
+    const int64_t r = r0 + rr;
+    D[((r / Nq) * H + h) * Nq + (r % Nq)] = acc;                          // [B, H, Nq] like lse
+  }
 }
 
 struct Item { int b, h, q0; };
@@ -70,21 +78,28 @@ __device__ __forceinline__ Item decode(int item, int n_qt, int H) {
 }
 
 // ------------------------------------------------------------------------------------------------ dq kernel
-constexpr int kDqStages = 5;
-constexpr uint32_t kColDQ = 256;
+// 128-key ring chunks (N = 128 MMAs: a 64-key MMA with both operands in shared memory is bound by its operand reads), single
+// TMEM buffers, two-phase hand-shake: phase 1 reads S_c and keeps p in registers, phase 2 reads dP_c and writes dS_c over the
+// dP columns; the in-order tensor pipe overlaps everything:  S_0 dP_0 | [p_c] S_{c+1} | [dS_c] dQ_c dP_{c+1} | ...
+constexpr int kKR = 128;                      // keys per ring chunk
+constexpr int kRHalf = kKR * 128;             // [128 keys][64 cols] bf16
+constexpr int kRBytes = 2 * kRHalf;           // 32 KB
+constexpr int kDqStages = 3;                  // V_c K_c V_{c+1}: V_c is free after dP_c (early), K_c after dQ_c
+constexpr uint32_t kColS = 0, kColDP = 128, kColDQ = 256;
 
 struct DqSmem {
   uint8_t qd[2][2][kTBytes];                 // [item buffer][Q | dO]; the dQ tile leaves from the Q half
-  uint8_t kv[kDqStages][kCBytes];            // ring: V_0 K_0 V_1 K_1 ... (V_j is free after dP_j, K_j after dQ += dS_j K_j)
-  float bias2[2][kMaxKeys];
-  uint64_t qd_full[2], kv_full[kDqStages], kv_empty[kDqStages], sd_full[2], ds_ready[2];
+  uint8_t kv[kDqStages][kRBytes];
+  float bias2[kMaxKeys];
+  uint64_t qd_full[2], kv_full[kDqStages], kv_empty[kDqStages], s_full, dp_full, p1_done, ds_ready;
   uint64_t dq_full, dq_empty, dq_staged;
   uint32_t tmem_base;
 };
 constexpr int kDqSmemBytes = (int)sizeof(DqSmem) + 1024;
 static_assert(kDqSmemBytes <= 232448, "xattn dq kernel exceeds the 227 KB shared-memory limit");
 
-constexpr uint32_t kIdescSd = make_idesc_bf16(128, kKC, 0, 0);   // Q K_j^T, dO V_j^T : A, B K-major
+constexpr uint32_t kIdescSd128 = make_idesc_bf16(128, 128, 0, 0);   // Q K_c^T, dO V_c^T : A, B K-major
+constexpr uint32_t kIdescSd64 = make_idesc_bf16(128, 64, 0, 0);     // last chunk with <= 64 keys
 
 __global__ void __launch_bounds__(kThreads, 1)
 xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_do,
@@ -97,19 +112,20 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_qt = (Nq + kQT - 1) / kQT;
   const int n_items = B * H * n_qt;
-  const int nC = (L + kKC - 1) / kKC;
+  const int nC = (L + kKC - 1) / kKC;          // 64-key sub-chunks
+  const int nR = (L + kKR - 1) / kKR;          // 128-key ring chunks
   const int nK = (d + 15) / 16;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(smem_u32(&S.qd_full[i]), 1);
-      mbar_init(smem_u32(&S.sd_full[i]), 1);
-      mbar_init(smem_u32(&S.ds_ready[i]), kSoftWarps);
-    }
+    for (int i = 0; i < 2; ++i) mbar_init(smem_u32(&S.qd_full[i]), 1);
     for (int s = 0; s < kDqStages; ++s) {
       mbar_init(smem_u32(&S.kv_full[s]), 1);
       mbar_init(smem_u32(&S.kv_empty[s]), 1);
     }
+    mbar_init(smem_u32(&S.s_full), 1);
+    mbar_init(smem_u32(&S.dp_full), 1);
+    mbar_init(smem_u32(&S.p1_done), kSoftWarps);
+    mbar_init(smem_u32(&S.ds_ready), kSoftWarps);
     mbar_init(smem_u32(&S.dq_full), 1);
     mbar_init(smem_u32(&S.dq_empty), kSoftWarps);
     mbar_init(smem_u32(&S.dq_staged), kSoftWarps);
@@ -128,76 +144,80 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   constexpr uint32_t tmem = 0;
 
   if (warp == 0) {
-    // ======================= TMA producer: the key ring =======================
+    // ======================= TMA producer: the key ring (V_c, K_c per chunk) =======================
     if (lane == 0) {
       uint32_t it = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const Item w = decode(item, n_qt, H);
-        for (int n = 0; n < 2 * nC; ++n, ++it) {
+        for (int n = 0; n < 2 * nR; ++n, ++it) {
           const CUtensorMap* tm = (n & 1) ? &tm_k : &tm_v;
           const uint32_t s = it % kDqStages, ph = (it / kDqStages) & 1;
           mbar_wait(smem_u32(&S.kv_empty[s]), ph ^ 1);
           const uint32_t full = smem_u32(&S.kv_full[s]);
-          mbar_arrive_expect_tx(full, kCBytes);
-          tma_load_4d(smem_u32(&S.kv[s][0]), tm, full, 0, w.h, (n >> 1) * kKC, w.b);
-          tma_load_4d(smem_u32(&S.kv[s][kCHalf]), tm, full, 64, w.h, (n >> 1) * kKC, w.b);
+          mbar_arrive_expect_tx(full, kRBytes);
+          tma_load_4d(smem_u32(&S.kv[s][0]), tm, full, 0, w.h, (n >> 1) * kKR, w.b);
+          tma_load_4d(smem_u32(&S.kv[s][kRHalf]), tm, full, 64, w.h, (n >> 1) * kKR, w.b);
         }
       }
     }
   } else if (warp == 1) {
     // ======================= tcgen05 issuer =======================
     if (lane == 0) {
-      uint32_t it0 = 0, qi = 0, sd_use[2] = {0, 0}, ds_use[2] = {0, 0};
-      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi, it0 += 2 * nC) {
+      uint32_t it0 = 0, qi = 0, cc = 0;            // cc: chunks handed to the softmax warps so far (parity of their barriers)
+      const uint32_t idesc_dq = make_idesc_bf16(128, (d + 15) & ~15, 0, 1);
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi, it0 += 2 * nR) {
         const uint32_t buf = qi & 1;
         mbar_wait(smem_u32(&S.qd_full[buf]), (qi >> 1) & 1);
         tc_fence_after();
         const uint64_t qa0 = make_smem_desc(smem_u32(&S.qd[buf][0][0]), 16, 1024, kLayoutSw128);
         const uint64_t da0 = make_smem_desc(smem_u32(&S.qd[buf][1][0]), 16, 1024, kLayoutSw128);
-        // S_j = Q K_j^T and dP_j = dO V_j^T into buffer j & 1 (columns 128 (j & 1) + {0, 64})
-        auto issue_sd = [&](int j) {
-          const uint32_t iv = it0 + 2 * j, ik = iv + 1, sv = iv % kDqStages, sk = ik % kDqStages, b = j & 1;
-          mbar_wait(smem_u32(&S.kv_full[sv]), (iv / kDqStages) & 1);
+        auto idesc_of = [&](int c) { return (nC - 2 * c >= 2) ? kIdescSd128 : kIdescSd64; };
+        auto issue_s = [&](int c) {                 // S_c = Q K_c^T
+          const uint32_t ik = it0 + 2 * c + 1, sk = ik % kDqStages;
           mbar_wait(smem_u32(&S.kv_full[sk]), (ik / kDqStages) & 1);
           tc_fence_after();
           const uint64_t kb0 = make_smem_desc(smem_u32(&S.kv[sk][0]), 16, 1024, kLayoutSw128);
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            if (ks < nK)
+              umma_bf16(tmem + kColS, qa0 + (((ks >> 2) * kTHalf + (ks & 3) * 32) >> 4),
+                        kb0 + (((ks >> 2) * kRHalf + (ks & 3) * 32) >> 4), idesc_of(c), ks != 0);
+          tc_commit(smem_u32(&S.s_full));
+        };
+        auto issue_dp = [&](int c) {                // dP_c = dO V_c^T
+          const uint32_t iv = it0 + 2 * c, sv = iv % kDqStages;
+          mbar_wait(smem_u32(&S.kv_full[sv]), (iv / kDqStages) & 1);
+          tc_fence_after();
           const uint64_t vb0 = make_smem_desc(smem_u32(&S.kv[sv][0]), 16, 1024, kLayoutSw128);
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks)
             if (ks < nK)
-              umma_bf16(tmem + b * 128, qa0 + (((ks >> 2) * kTHalf + (ks & 3) * 32) >> 4),
-                        kb0 + (((ks >> 2) * kCHalf + (ks & 3) * 32) >> 4), kIdescSd, ks != 0);
+              umma_bf16(tmem + kColDP, da0 + (((ks >> 2) * kTHalf + (ks & 3) * 32) >> 4),
+                        vb0 + (((ks >> 2) * kRHalf + (ks & 3) * 32) >> 4), idesc_of(c), ks != 0);
+          tc_commit(smem_u32(&S.kv_empty[sv]));        // V_c is done
+          tc_commit(smem_u32(&S.dp_full));
+        };
+        issue_s(0);
+        issue_dp(0);
+        for (int c = 0; c < nR; ++c, ++cc) {
+          mbar_wait(smem_u32(&S.p1_done), cc & 1);     // every softmax warp has read S_c
+          if (c + 1 < nR) issue_s(c + 1);
+          mbar_wait(smem_u32(&S.ds_ready), cc & 1);    // dS_c is in the dP columns
+          if (c == 0) mbar_wait(smem_u32(&S.dq_empty), (qi & 1) ^ 1);
+          tc_fence_after();
+          // dQ += dS_c K_c: A = dS_c in tensor memory (16 keys of K step ks as 8 packed columns at
+          // 64 (ks >> 2) + 32 ((ks >> 1) & 1) + 8 (ks & 1) of the dP region), B = K_c MN-major (K step of 16 keys = 2 KB)
+          const uint32_t ik = it0 + 2 * c + 1, sk = ik % kDqStages;
+          const uint64_t kb0 = make_smem_desc(smem_u32(&S.kv[sk][0]), kRHalf, 1024, kLayoutSw128);
+          const int nks = (nC - 2 * c >= 2) ? 8 : 4;
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks)
-            if (ks < nK)
-              umma_bf16(tmem + b * 128 + 64, da0 + (((ks >> 2) * kTHalf + (ks & 3) * 32) >> 4),
-                        vb0 + (((ks >> 2) * kCHalf + (ks & 3) * 32) >> 4), kIdescSd, ks != 0);
-          tc_commit(smem_u32(&S.kv_empty[sv]));        // V_j is done; K_j stays for dQ
-          tc_commit(smem_u32(&S.sd_full[b]));
-          ++sd_use[b];
-        };
-        // dQ += dS_j K_j: A = dS_j in tensor memory (bf16 pairs over the score columns, see the softmax warps), B = K_j
-        // MN-major (LBO = stride between the two 64-column halves, SBO = 8-key group, K step of 16 keys = 2 KB)
-        const uint32_t idesc_dq = make_idesc_bf16(128, (d + 15) & ~15, 0, 1);
-        auto issue_dq = [&](int j) {
-          const uint32_t ik = it0 + 2 * j + 1, sk = ik % kDqStages, b = j & 1;
-          mbar_wait(smem_u32(&S.ds_ready[b]), ds_use[b] & 1);
-          ++ds_use[b];
-          if (j == 0) mbar_wait(smem_u32(&S.dq_empty), (qi & 1) ^ 1);
-          tc_fence_after();
-          const uint64_t kb0 = make_smem_desc(smem_u32(&S.kv[sk][0]), kCHalf, 1024, kLayoutSw128);
-#pragma unroll
-          for (int ks = 0; ks < kKC / 16; ++ks)
-            umma_bf16_ts(tmem + kColDQ, tmem + b * 128 + (ks >> 1) * 32 + (ks & 1) * 8, kb0 + ((ks * 2048) >> 4), idesc_dq,
-                         (j | ks) != 0);
+            if (ks < nks)
+              umma_bf16_ts(tmem + kColDQ, tmem + kColDP + 64 * (ks >> 2) + 32 * ((ks >> 1) & 1) + 8 * (ks & 1),
+                           kb0 + ((ks * 2048) >> 4), idesc_dq, (c | ks) != 0);
           tc_commit(smem_u32(&S.kv_empty[sk]));
-          if (j == nC - 1) tc_commit(smem_u32(&S.dq_full));
-        };
-        issue_sd(0);
-        if (nC > 1) issue_sd(1);
-        for (int j = 0; j < nC; ++j) {
-          issue_dq(j);
-          if (j + 2 < nC) issue_sd(j + 2);     // in order behind dQ_j: buffer j & 1 is free
+          if (c == nR - 1) tc_commit(smem_u32(&S.dq_full));
+          if (c + 1 < nR) issue_dp(c + 1);             // behind dQ_c: the dP columns are free
         }
       }
     }
@@ -229,16 +249,15 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       tma_store_wait_all<0>();
     }
   } else {
-    // ======================= dS + epilogue warps =======================
+    // ======================= p / dS + epilogue warps =======================
     const int te = threadIdx.x - 64;              // 0..255
-    const int wg = te >> 7;                       // which 32 of a sub-chunk's 64 keys / which half of dQ
+    const int wg = te >> 7;                       // which 64 of a chunk's 128 keys / which half of dQ
     const int quad = warp & 3;
     const int row = quad * 32 + lane;
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
     const f2 cs2 = bc2(scale * kLog2e);
-    uint32_t qi = 0, sd_use[2] = {0, 0};
-    // per-item scalars and the sample's bias row are fetched one item ahead (registers), so no global latency sits between
-    // two items; the bias row alternates between two shared-memory buffers
+    uint32_t qi = 0, cc = 0;
+    // per-item scalars and the sample's bias row are fetched one item ahead (registers): no global latency between two items
     auto fetch = [&](int item, float& l2, float& dn, float& b0, float& b1) {
       const Item w = decode(item, n_qt, H);
       const bool valid = w.q0 + row < Nq;
@@ -251,54 +270,70 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         if (te + kSoftThreads < L) b1 = __ldg(bias + (int64_t)w.b * L + te + kSoftThreads);
       }
     };
-    auto put_bias = [&](uint32_t n, float b0, float b1) {
-      if (te < nC * kKC) S.bias2[n & 1][te] = te < L ? b0 * kLog2e : -INFINITY;
-      if (te + kSoftThreads < nC * kKC) S.bias2[n & 1][te + kSoftThreads] = te + kSoftThreads < L ? b1 * kLog2e : -INFINITY;
+    auto put_bias = [&](float b0, float b1) {
+      if (te < nR * kKR) S.bias2[te] = te < L ? b0 * kLog2e : -INFINITY;
+      if (te + kSoftThreads < nR * kKR) S.bias2[te + kSoftThreads] = te + kSoftThreads < L ? b1 * kLog2e : -INFINITY;
     };
     float n_l2 = 0.f, n_dn = 0.f, n_b0 = 0.f, n_b1 = 0.f;
     if ((int)blockIdx.x < n_items) {
       fetch(blockIdx.x, n_l2, n_dn, n_b0, n_b1);
-      put_bias(0, n_b0, n_b1);
+      put_bias(n_b0, n_b1);
       named_bar_sync(1, kSoftThreads);
     }
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++qi) {
       const float lse2 = n_l2;
       const f2 nd2 = bc2(n_dn);
-      const float* bs = S.bias2[qi & 1];
       const bool has_next = item + (int)gridDim.x < n_items;
       if (has_next) fetch(item + gridDim.x, n_l2, n_dn, n_b0, n_b1);
-      for (int j = 0; j < nC; ++j) {
-        const uint32_t b = j & 1;
-        mbar_wait(smem_u32(&S.sd_full[b]), sd_use[b] & 1);
-        ++sd_use[b];
+      for (int c = 0; c < nR; ++c, ++cc) {
+        // phase 1: p = 2^(s c + bias2 - lse2), kept in registers
+        mbar_wait(smem_u32(&S.s_full), cc & 1);
         tc_fence_after();
-        uint32_t rs[32], rp[32];
-        const uint32_t base = tmem + lane_base + b * 128 + wg * 32;
-        tmem_ld32(base, rs);
-        tmem_ld32(base + 64, rp);
-        tmem_ld_wait();
-        const float4* b4 = reinterpret_cast<const float4*>(bs + j * kKC + wg * 32);
-        uint32_t pk[16];
+        f2 pr[2][16];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float4 bb = b4[i];
-          float a0, a1, a2, a3;
-          un2(fma2(mk2(__uint_as_float(rs[4 * i]), __uint_as_float(rs[4 * i + 1])), cs2, mk2(bb.x - lse2, bb.y - lse2)), a0, a1);
-          un2(fma2(mk2(__uint_as_float(rs[4 * i + 2]), __uint_as_float(rs[4 * i + 3])), cs2, mk2(bb.z - lse2, bb.w - lse2)), a2, a3);
-          const f2 p01 = mk2(ex2(a0), ex2(a1)), p23 = mk2(ex2(a2), ex2(a3));
-          const f2 s01 = mul2(p01, add2(mk2(__uint_as_float(rp[4 * i]), __uint_as_float(rp[4 * i + 1])), nd2));
-          const f2 s23 = mul2(p23, add2(mk2(__uint_as_float(rp[4 * i + 2]), __uint_as_float(rp[4 * i + 3])), nd2));
-          pk[2 * i] = pack2(s01);
-          pk[2 * i + 1] = pack2(s23);
+        for (int hh = 0; hh < 2; ++hh) {
+          uint32_t rs[32];
+          const uint32_t col = wg * 64 + hh * 32;
+          tmem_ld32(tmem + lane_base + kColS + col, rs);
+          tmem_ld_wait();
+          const float4* b4 = reinterpret_cast<const float4*>(&S.bias2[c * kKR + col]);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 bb = b4[i];
+            float a0, a1, a2, a3;
+            un2(fma2(mk2(__uint_as_float(rs[4 * i]), __uint_as_float(rs[4 * i + 1])), cs2, mk2(bb.x - lse2, bb.y - lse2)), a0, a1);
+            un2(fma2(mk2(__uint_as_float(rs[4 * i + 2]), __uint_as_float(rs[4 * i + 3])), cs2, mk2(bb.z - lse2, bb.w - lse2)), a2, a3);
+            pr[hh][2 * i] = mk2(ex2(a0), ex2(a1));
+            pr[hh][2 * i + 1] = mk2(ex2(a2), ex2(a3));
+          }
         }
-        tmem_st16(base, pk);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&S.p1_done));
+        // phase 2: dS = p (dP - D) -> bf16 pairs over the first 16 of each 32 dP columns
+        mbar_wait(smem_u32(&S.dp_full), cc & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          uint32_t rp[32];
+          const uint32_t col = wg * 64 + hh * 32;
+          tmem_ld32(tmem + lane_base + kColDP + col, rp);
+          tmem_ld_wait();
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            pk[2 * i] = pack2(mul2(pr[hh][2 * i], add2(mk2(__uint_as_float(rp[4 * i]), __uint_as_float(rp[4 * i + 1])), nd2)));
+            pk[2 * i + 1] = pack2(mul2(pr[hh][2 * i + 1], add2(mk2(__uint_as_float(rp[4 * i + 2]), __uint_as_float(rp[4 * i + 3])), nd2)));
+          }
+          tmem_st16(tmem + lane_base + kColDP + col, pk);
+        }
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&S.ds_ready[b]));
+        if (lane == 0) mbar_arrive(smem_u32(&S.ds_ready));
       }
-      if (has_next) put_bias(qi + 1, n_b0, n_b1);     // that buffer was last read in the previous item (a barrier ago)
-      named_bar_sync(1, kSoftThreads);
+      named_bar_sync(1, kSoftThreads);                  // every warp has finished reading this item's bias row
+      if (has_next) put_bias(n_b0, n_b1);
       // ---- epilogue: scale dQ -> bf16 -> the item's Q buffer -> store thread
       mbar_wait(smem_u32(&S.dq_full), qi & 1);
       tc_fence_after();
@@ -326,6 +361,7 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&S.dq_staged));
+      named_bar_sync(1, kSoftThreads);                  // the next item's bias row is in place
     }
   }
 
@@ -333,7 +369,6 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem, kTmemCols);
 }
-
 
 // ------------------------------------------------------------------------------------------------ dkv kernel
 constexpr int kKB = 128;                      // keys per block (the lanes of S^T, dP^T, dV, dK)
@@ -655,6 +690,7 @@ extern "C" int yat_xattn_bwd(const void* q, const void* k, const void* v, const 
   YAT_REQUIRE(B > 0 && H > 0 && Nq > 0 && L > 0, YAT_ERR_BAD_ARG, "yat_xattn_bwd: non-positive dimension");
   YAT_REQUIRE(d >= 8 && d <= 128 && d % 8 == 0, YAT_ERR_UNSUPPORTED, "yat_xattn_bwd: head_dim %d not supported (8..128, multiple of 8)", d);
   YAT_REQUIRE(L <= kMaxKeys, YAT_ERR_UNSUPPORTED, "yat_xattn_bwd: %d keys exceed the %d supported", L, kMaxKeys);
+  YAT_REQUIRE((int64_t)H * d <= 12288, YAT_ERR_UNSUPPORTED, "yat_xattn_bwd: H * d = %lld exceeds 12288", (long long)H * d);
   YAT_REQUIRE(ldq >= (int64_t)H * d && ldq % 8 == 0 && ldkv >= (int64_t)H * d && ldkv % 8 == 0, YAT_ERR_BAD_ARG,
               "yat_xattn_bwd: row pitches %lld / %lld must be >= H*d and multiples of 8", (long long)ldq, (long long)ldkv);
   YAT_REQUIRE((((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)o | (uintptr_t)d_o | (uintptr_t)dq | (uintptr_t)dk |
@@ -662,15 +698,16 @@ extern "C" int yat_xattn_bwd(const void* q, const void* k, const void* v, const 
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t rows = (int64_t)B * Nq;
   float* D = (float*)workspace;
-  xattn_prep_kernel<<<(unsigned)((rows * H + 7) / 8), 256, 0, st>>>((const __nv_bfloat16*)o, (const __nv_bfloat16*)d_o, D, rows, H, d, Nq);
+  xattn_prep_kernel<<<(unsigned)((rows + kPrepRows - 1) / kPrepRows), 256, (size_t)kPrepRows * H * d / 8 * sizeof(float), st>>>(
+      (const __nv_bfloat16*)o, (const __nv_bfloat16*)d_o, D, rows, H, d, Nq);
   int rc = check_launch("xattn_prep");
   if (rc != YAT_OK) return rc;
   const uint64_t C = (uint64_t)H * d;
   CUtensorMap tq, tdo, tk, tv, tdq;
   if ((rc = make_tmap_heads_bf16(&tq, q, d, H, Nq, B, (uint64_t)ldq, kQT)) != YAT_OK) return rc;
   if ((rc = make_tmap_heads_bf16(&tdo, d_o, d, H, Nq, B, C, kQT)) != YAT_OK) return rc;
-  if ((rc = make_tmap_heads_bf16(&tk, k, d, H, L, B, (uint64_t)ldkv, kKC)) != YAT_OK) return rc;
-  if ((rc = make_tmap_heads_bf16(&tv, v, d, H, L, B, (uint64_t)ldkv, kKC)) != YAT_OK) return rc;
+  if ((rc = make_tmap_heads_bf16(&tk, k, d, H, L, B, (uint64_t)ldkv, kKR)) != YAT_OK) return rc;
+  if ((rc = make_tmap_heads_bf16(&tv, v, d, H, L, B, (uint64_t)ldkv, kKR)) != YAT_OK) return rc;
   if ((rc = make_tmap_heads_bf16(&tdq, dq, d, H, Nq, B, C, kQT)) != YAT_OK) return rc;
   static bool attr_set = false;
   if (!attr_set) {
