@@ -104,13 +104,15 @@ def test_backward_is_deterministic_and_matches_sdpa_autograd(cuda):
         assert _rel(x, g) < 8e-3
 
 
-def test_processor_opt_in_own_backward_matches_the_library_path(cuda):
-    """AttnProcessor2_0(own_backward=True): forward and every gradient of the attn2 module on the own kernels against the
-    default training path (cuDNN SDPA with the folded key bias)."""
+def test_processor_own_backward_matches_the_library_path(cuda):
+    """AttnProcessor2_0 with own_backward (the default training path of attn2): forward and every gradient of the module on the
+    own kernels against the library path (cuDNN SDPA with the folded key bias)."""
     from yat_b200 import _lib
     from yat_b200.attention import Attention, AttnProcessor2_0
     torch.manual_seed(0)
-    a1 = Attention(query_dim=224, cross_attention_dim=224, heads=2, dim_head=112, bias=True, processor=AttnProcessor2_0())
+    p1 = AttnProcessor2_0()
+    p1.own_backward = False                     # the library path: cuDNN SDPA with the key bias folded into a head column
+    a1 = Attention(query_dim=224, cross_attention_dim=224, heads=2, dim_head=112, bias=True, processor=p1)
     a1 = a1.to(cuda).to(torch.bfloat16)
     p2 = AttnProcessor2_0()
     p2.own_backward = True

@@ -108,7 +108,7 @@ def test_argument_errors(cuda):
 
 def test_processor_uses_the_own_forward_when_no_gradient_is_needed(cuda):
     """AttnProcessor2_0 (the block's attn2): under no_grad (exploration trials, the frozen preservation pass, sampling) the
-    cross-attention runs on yat_xattn_fwd; with a gradient it stays on the library path (there is no own backward).
+    cross-attention runs on yat_xattn_fwd alone; with own_backward off and a gradient needed it is the library path.
     Same module, same inputs: the two outputs agree to bf16 rounding."""
     from yat_b200 import _lib
     from yat_b200.attention import Attention, AttnProcessor2_0
@@ -124,9 +124,10 @@ def test_processor_uses_the_own_forward_when_no_gradient_is_needed(cuda):
     with torch.no_grad():
         y_own = attn(x, encoder_hidden_states=enc, attention_mask=mask)
     assert _lib.launch_counts["yat_xattn_fwd"] == before + 1
+    attn.processor.own_backward = False                               # library training path (own: tests/test_xattn_bwd_gpu.py)
     xg = x.clone().requires_grad_(True)
     y_lib = attn(xg, encoder_hidden_states=enc, attention_mask=mask)
-    assert _lib.launch_counts["yat_xattn_fwd"] == before + 1          # the training path did not take it
+    assert _lib.launch_counts["yat_xattn_fwd"] == before + 1          # the library path did not take it
     y_lib.sum().backward()
     assert xg.grad is not None and torch.isfinite(xg.grad).all()
     assert _rel(y_own, y_lib.detach()) < 6e-3

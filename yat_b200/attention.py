@@ -8,6 +8,7 @@ processors and PEFT configs rely on (``to_q to_k to_v to_out.0``, ``heads``, ``n
 ``AttnProcessor2_0`` (softmax SDPA, library call) is what ``patch_sana_attention_layers`` swaps in
 for ``modified_blocks`` and what cross-attention uses.
 """
+import os
 from typing import Optional
 
 import torch
@@ -157,21 +158,26 @@ def _sdpa_key_bias_folded(q, k, v, bias, H, d):
 _bias_f32_cache = {}
 
 
+def _bias_f32(bias, B, L):
+    """Additive key mask -> fp32 [B, L]; one entry cached so the 20 blocks of a pass that share the mask convert it once."""
+    if bias is None:
+        return None
+    key = (bias.data_ptr(), bias._version, bias.numel())
+    hit = _bias_f32_cache.get("b")
+    if hit is not None and hit[0] == key:
+        return hit[2]
+    bias_f = bias.reshape(B, L).float().contiguous()
+    _bias_f32_cache["b"] = (key, bias, bias_f)      # holding `bias` keeps its storage (and the pointer) alive
+    return bias_f
+
+
 def _xattn_own_forward(q, k, v, bias, H, d):
     """Forward-only cross-attention on the own tcgen05 kernel (``yat_xattn_fwd``, csrc/xattn_sm100.cu): no padded copies, the
     key bias read as it is.  q [B, N, H*d], k / v [B, L, H*d] bf16 token-major (row-pitched views allowed), bias [B, L]-shaped
     additive mask or None.  There is no own backward, so the caller uses this only when no gradient is needed."""
     B, N, _ = q.shape
     L = k.shape[1]
-    bias_f = None
-    if bias is not None:
-        key = (bias.data_ptr(), bias._version, bias.numel())
-        hit = _bias_f32_cache.get("b")
-        if hit is not None and hit[0] == key:
-            bias_f = hit[2]
-        else:
-            bias_f = bias.reshape(B, L).float().contiguous()
-            _bias_f32_cache["b"] = (key, bias, bias_f)      # holding `bias` keeps its storage (and the pointer) alive
+    bias_f = _bias_f32(bias, B, L)
     out = torch.empty((B, N, H * d), dtype=torch.bfloat16, device=q.device)
     with _lib.timed("xattn_fwd"):
         rc = _lib.lib().yat_xattn_fwd(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(bias_f), B, H, N, L, d, q.stride(1),
@@ -181,8 +187,8 @@ def _xattn_own_forward(q, k, v, bias, H, d):
 
 
 class _XAttnOwn(torch.autograd.Function):
-    """Cross-attention with both directions on the own tcgen05 kernels (yat_xattn_fwd / yat_xattn_bwd).  Opt-in
-    (``AttnProcessor2_0.own_backward``): measured slower than the library backward."""
+    """Cross-attention with both directions on the own tcgen05 kernels (yat_xattn_fwd / yat_xattn_bwd): the training path of
+    attn2 (``AttnProcessor2_0.own_backward``, default on; 408 against 478 us per SANA-1.6B layer)."""
 
     @staticmethod
     def forward(ctx, q, k, v, bias_f, H):
@@ -239,7 +245,8 @@ class AttnProcessor2_0:
     """Softmax scaled-dot-product attention (diffusers ``AttnProcessor2_0`` semantics)."""
     fold_key_mask = True
     own_forward = True          # no-grad forwards (exploration trials, the frozen preservation pass, sampling): yat_xattn_fwd
-    own_backward = False        # training forward + backward on yat_xattn_fwd / yat_xattn_bwd (opt-in: slower than cuDNN's)
+    # training forward + backward on yat_xattn_fwd / yat_xattn_bwd instead of cuDNN (YAT_XATTN_OWN_BACKWARD=0 / 1 overrides)
+    own_backward = os.environ.get("YAT_XATTN_OWN_BACKWARD", "1") == "1"
 
     def __call__(self, attn, hidden_states, encoder_hidden_states=None, attention_mask=None):
         B = hidden_states.shape[0]
@@ -253,8 +260,7 @@ class AttnProcessor2_0:
                 and attn.norm_q is None and attn.norm_k is None and d % 8 == 0
                 and attention_mask.numel() == B * attention_mask.shape[-1]):
             if self.own_backward and torch.is_grad_enabled() and _xattn_layout_ok(query, key, value, d):
-                bias_f = attention_mask.reshape(B, -1).float().contiguous()
-                out = _XAttnOwn.apply(query, key, value, bias_f, attn.heads)
+                out = _XAttnOwn.apply(query, key, value, _bias_f32(attention_mask, B, key.shape[1]), attn.heads)
             elif self.own_forward and _xattn_own_ok(query, key, value, d):
                 out = _xattn_own_forward(query, key, value, attention_mask, attn.heads, d)
             else:

@@ -285,9 +285,16 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       const f2 nd2 = bc2(n_dn);
       const bool has_next = item + (int)gridDim.x < n_items;
       if (has_next) fetch(item + gridDim.x, n_l2, n_dn, n_b0, n_b1);
+#ifdef YAT_BWD_PROBE
+      long long w_s = 0, w_dp = 0;
+      if (te == 0) TRACE(0, 10);
+#define XW(acc, ...) do { const long long t0_ = clock64(); __VA_ARGS__; acc += clock64() - t0_; } while (0)
+#else
+#define XW(acc, ...) do { __VA_ARGS__; } while (0)
+#endif
       for (int c = 0; c < nR; ++c, ++cc) {
         // phase 1: p = 2^(s c + bias2 - lse2), kept in registers
-        mbar_wait(smem_u32(&S.s_full), cc & 1);
+        XW(w_s, mbar_wait(smem_u32(&S.s_full), cc & 1));
         tc_fence_after();
         f2 pr[2][16];
 #pragma unroll
@@ -311,7 +318,7 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&S.p1_done));
         // phase 2: dS = p (dP - D) -> bf16 pairs over the first 16 of each 32 dP columns
-        mbar_wait(smem_u32(&S.dp_full), cc & 1);
+        XW(w_dp, mbar_wait(smem_u32(&S.dp_full), cc & 1));
         tc_fence_after();
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {
@@ -334,9 +341,13 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       }
       named_bar_sync(1, kSoftThreads);                  // every warp has finished reading this item's bias row
       if (has_next) put_bias(n_b0, n_b1);
+#ifdef YAT_BWD_PROBE
+      if (te == 0) { TRACE(0, 1000 + (int)(w_s >> 4)); TRACE(0, 2000 + (int)(w_dp >> 4)); TRACE(0, 15); }
+#endif
       // ---- epilogue: scale dQ -> bf16 -> the item's Q buffer -> store thread
       mbar_wait(smem_u32(&S.dq_full), qi & 1);
       tc_fence_after();
+      if (te == 0) TRACE(0, 16);
       {
         uint32_t ra[32], rb[32];
         tmem_ld32(tmem + lane_base + kColDQ + wg * 64, ra);
@@ -361,6 +372,7 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&S.dq_staged));
+      if (te == 0) TRACE(0, 17);
       named_bar_sync(1, kSoftThreads);                  // the next item's bias row is in place
     }
   }
@@ -679,6 +691,8 @@ xattn_dkv_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
 }  // namespace yat
 
 // ------------------------------------------------------------------ host side
+YAT_DEFINE_TRACE_API(yat_xbwd)
+
 extern "C" int64_t yat_xattn_bwd_workspace_bytes(int B, int H, int Nq) { return (int64_t)B * H * Nq * (int64_t)sizeof(float); }
 
 extern "C" int yat_xattn_bwd(const void* q, const void* k, const void* v, const void* bias, const void* o, const void* lse,
