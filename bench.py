@@ -451,8 +451,8 @@ def _standalone_kernels(device, pk):
     except Exception as e:  # noqa: BLE001 — reported, not hidden
         out["gemm_qkv_own_tcgen05"] = {"error": str(e)[:200]}
     # cross-attention forward of one SANA-1.6B layer (attn2: 20 heads x 112, 320 keys): own tcgen05 kernel vs the path the
-    # step runs (yat_head_pad x 2 + cuDNN SDPA with the key bias folded into an extra head column).  Used by gradient-free
-    # forwards only: there is no own backward, so the training forward keeps the library call.
+    # library path (yat_head_pad x 2 + cuDNN SDPA with the key bias folded into an extra head column, YAT_XATTN_OWN_BACKWARD=0);
+    # the step runs attn2 on the own forward + backward.
     try:
         from yat_b200 import _lib as _L
         from yat_b200.attention import _sdpa_key_bias_folded
@@ -481,7 +481,31 @@ def _standalone_kernels(device, pk):
                                         "library_path_us": ms_l * 1e3, "vs_library_time": ms_l / ms_o,
                                         "timing": "stand-alone", "what": "yat_xattn_fwd vs head_pad + cuDNN SDPA (folded key bias)"}
         out["xattn_fwd_own_tcgen05"]["frac"] = out["xattn_fwd_own_tcgen05"]["achieved"] / pk["bf16_tflops"]
-        del xq, xk, xv, xo, xlse
+        # backward: own (prep + dq + dkv kernels) against the library path's backward ((fwd + bwd) - fwd of the folded SDPA)
+        xdo = torch.randn_like(xq)
+        xdq, xdk, xdv = torch.empty_like(xq), torch.empty_like(xk), torch.empty_like(xv)
+        xws = torch.empty(L.yat_xattn_bwd_workspace_bytes(B, xh, N), dtype=torch.uint8, device=device)
+        own()
+        own_b = lambda: L.yat_xattn_bwd(xq.data_ptr(), xk.data_ptr(), xv.data_ptr(), xb.data_ptr(), xo.data_ptr(),  # noqa: E731
+                                        xlse.data_ptr(), xdo.data_ptr(), B, xh, N, xl, xd, xh * xd, xh * xd, xd ** -0.5,
+                                        xdq.data_ptr(), xdk.data_ptr(), xdv.data_ptr(), xws.data_ptr(), cs)
+        qg_, kg_, vg_ = [t.clone().requires_grad_(True) for t in (xq, xk, xv)]
+
+        def lib_fb():
+            torch.autograd.grad(_sdpa_key_bias_folded(qg_, kg_, vg_, xb4, xh, xd), (qg_, kg_, vg_), xdo)
+
+        ms_ob = ms_lfb = float("inf")
+        for _ in range(3):
+            ms_lfb = min(ms_lfb, timeit(lib_fb, iters=20, warm=3))
+            ms_ob = min(ms_ob, timeit(own_b, iters=20, warm=3))
+        fl_b = 2.5 * fl_x
+        out["xattn_bwd_own_tcgen05"] = {"bound": "tensor", "achieved": fl_b / (ms_ob * 1e-3) / 1e12, "peak": pk["bf16_tflops"],
+                                        "unit": "TFLOP/s", "us": ms_ob * 1e3, "flops": fl_b, "shape": [B, xh, N, xl, xd],
+                                        "library_fwd_bwd_us": ms_lfb * 1e3, "library_bwd_us": (ms_lfb - ms_l) * 1e3,
+                                        "vs_library_time": (ms_lfb - ms_l) / ms_ob, "timing": "stand-alone",
+                                        "what": "yat_xattn_bwd (prep + dq + dkv) vs the backward of head_pad + cuDNN SDPA"}
+        out["xattn_bwd_own_tcgen05"]["frac"] = out["xattn_bwd_own_tcgen05"]["achieved"] / pk["bf16_tflops"]
+        del xq, xk, xv, xo, xlse, xdo, xdq, xdk, xdv, xws, qg_, kg_, vg_
     except Exception as e:  # noqa: BLE001 — reported, not hidden
         out["xattn_fwd_own_tcgen05"] = {"error": str(e)[:200]}
     from yat_b200.linear_attention import _launch_fwd
