@@ -64,6 +64,8 @@ CASES = [
     (1, 4, 256, 384, 72, [333]),
     (3, 2, 128, 40, 128, None),
     (2, 5, 300, 192, 32, [192, 77]),
+    (1, 1, 1, 1, 8, None),
+    (2, 3, 129, 129, 16, [129, 5]),
 ]
 
 
