@@ -286,7 +286,7 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       const bool has_next = item + (int)gridDim.x < n_items;
       if (has_next) fetch(item + gridDim.x, n_l2, n_dn, n_b0, n_b1);
 #ifdef YAT_BWD_PROBE
-      long long w_s = 0, w_dp = 0;
+      long long w_s = 0, w_dp = 0, w_s0 = 0;
       if (te == 0) TRACE(0, 10);
 #define XW(acc, ...) do { const long long t0_ = clock64(); __VA_ARGS__; acc += clock64() - t0_; } while (0)
 #else
@@ -294,7 +294,7 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
 #endif
       for (int c = 0; c < nR; ++c, ++cc) {
         // phase 1: p = 2^(s c + bias2 - lse2), kept in registers
-        XW(w_s, mbar_wait(smem_u32(&S.s_full), cc & 1));
+        if (c == 0) XW(w_s0, mbar_wait(smem_u32(&S.s_full), cc & 1)); else XW(w_s, mbar_wait(smem_u32(&S.s_full), cc & 1));
         tc_fence_after();
         f2 pr[2][16];
 #pragma unroll
@@ -342,7 +342,7 @@ xattn_dq_sm100_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       named_bar_sync(1, kSoftThreads);                  // every warp has finished reading this item's bias row
       if (has_next) put_bias(n_b0, n_b1);
 #ifdef YAT_BWD_PROBE
-      if (te == 0) { TRACE(0, 1000 + (int)(w_s >> 4)); TRACE(0, 2000 + (int)(w_dp >> 4)); TRACE(0, 15); }
+      if (te == 0) { TRACE(0, 1000 + (int)(w_s >> 4)); TRACE(0, 2000 + (int)(w_dp >> 4)); TRACE(0, 3000 + (int)(w_s0 >> 4)); TRACE(0, 15); }
 #endif
       // ---- epilogue: scale dQ -> bf16 -> the item's Q buffer -> store thread
       mbar_wait(smem_u32(&S.dq_full), qi & 1);
