@@ -38,10 +38,14 @@ for p in params:
 wq = (torch.randn((3 * C, C), device=dev) / C ** 0.5).to(torch.bfloat16)
 xk, xv = [torch.randn((B, 320, C), device=dev).to(torch.bfloat16) for _ in range(2)]     # cross-attention: 20 heads x 112, 320 keys
 xo, xlse = torch.empty_like(q), torch.empty((B, 20, N), device=dev)
+xdq, xdk, xdv = torch.empty_like(q), torch.empty_like(xk), torch.empty_like(xv)
 from yat_b200 import _lib as _L  # noqa: E402
 for _ in range(reps):
     _L.lib().yat_xattn_fwd(q.data_ptr(), xk.data_ptr(), xv.data_ptr(), None, B, 20, N, 320, 112, C, C, 112 ** -0.5, xo.data_ptr(),
                            xlse.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    _xws = torch.empty(_L.lib().yat_xattn_bwd_workspace_bytes(B, 20, N), dtype=torch.uint8, device=dev)
+    _L.lib().yat_xattn_bwd(q.data_ptr(), xk.data_ptr(), xv.data_ptr(), None, xo.data_ptr(), xlse.data_ptr(), do.data_ptr(), B, 20, N, 320, 112,
+                           C, C, 112 ** -0.5, xdq.data_ptr(), xdk.data_ptr(), xdv.data_ptr(), _xws.data_ptr(), torch.cuda.current_stream().cuda_stream)
     with torch.no_grad():
         sana_linear_attention_proj(q, wq, H)          # fused projection + phase 1, then the state-mode attention forward
         gemm_bf16_tn(q.view(B * N, C), wq)            # the plain own GEMM of the same projection
